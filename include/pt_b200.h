@@ -1,0 +1,273 @@
+/*
+ * pt_b200.h — C-ABI of the B200-native wavefront path tracer.
+ *
+ * Drop-in boundary for ONE hot path of marko176/PathTracing (citations are
+ * file:line in the reference tree): BVH2/BVH4 TLAS+BLAS closest-hit and
+ * shadow-ray traversal plus the path-integrator bounce loop.  The reference has
+ * no FFI layer of its own: its API is a set of C++ classes
+ * (Scene / Mesh / BLASx / TLASx / Camera / Film / *Integrator).  This header
+ * is what those classes bind to once they are re-implemented as thin host
+ * objects (see pathtracing_b200/host/pt_host.hpp and INTEGRATION.md).
+ *
+ * Conventions: every function returns PT_OK (0) or a negative pt_status, except
+ * the *_add_* calls which return the new object's id (>= 0) or a negative
+ * status.  pt_last_error() returns a thread-local message for the last failure.
+ * Host arrays are borrowed for the duration of the call and copied; no torch
+ * types, no C++ types, plain pointers and sizes only.
+ */
+#ifndef PT_B200_H
+#define PT_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define PT_API __attribute__((visibility("default")))
+
+typedef enum pt_status {
+    PT_OK = 0,
+    PT_ERR_INVALID = -1,  /* bad argument / bad id / wrong state            */
+    PT_ERR_CUDA = -2,     /* CUDA runtime error (message in pt_last_error)  */
+    PT_ERR_NO_DEVICE = -3,/* no CUDA device: there is NO CPU fallback       */
+    PT_ERR_STATE = -4,    /* scene not committed / already committed        */
+    PT_ERR_NOMEM = -5
+} pt_status;
+
+/* ---- ray casting ------------------------------------------------------------
+ * replaces Scene::Intersect / Scene::IntersectPred (Scene.hpp:10-14,
+ * Scene.cpp:4-6,31-33) called per ray; here called per batch.               */
+
+/* 32 B ray.  replaces struct Ray (Ray.hpp:14-41): inv_dir is recomputed on the
+ * device with the reference's clamp (|d|<1e-32 -> 1e32).                    */
+typedef struct pt_ray {
+    float ox, oy, oz, tmax;
+    float dx, dy, dz, time;
+} pt_ray;
+
+#define PT_MISS 0xFFFFFFFFu
+
+/* 16 B hit record.  Carries what SurfaceInteraction (Interaction.hpp:36-51)
+ * is rebuilt from in the shade stage: t, the two barycentrics returned by
+ * glm::intersectRayTriangle (glm/gtx/intersect.inl:29-94) and the triangle
+ * index inside its BLAS (meshes concatenated in pt_scene_add_blas order).
+ * prim == PT_MISS and t == +inf on a miss.                                  */
+typedef struct pt_hit {
+    float t, u, v;
+    uint32_t prim;
+} pt_hit;
+
+/* ---- scene description -------------------------------------------------------- */
+
+typedef enum pt_tex_kind {
+    PT_TEX_SOLID = 0,     /* SolidColor        Texture.hpp:122-133  */
+    PT_TEX_IMAGE_U8 = 1,  /* ImageTexture      Texture.hpp:135-165  */
+    PT_TEX_IMAGE_F32 = 2, /* FloatImageTexture Texture.hpp:167-195  */
+    PT_TEX_CHECKER = 3,   /* CheckerTexture    Texture.hpp:197-214  */
+    PT_TEX_UV = 4,        /* UVTexture         Texture.hpp:216-223  */
+    PT_TEX_NORMAL = 5     /* NormalTexture     Texture.hpp:225-232  */
+} pt_tex_kind;
+
+typedef struct pt_texture_desc {
+    int32_t kind;           /* pt_tex_kind */
+    float color[3];         /* SOLID: albedo */
+    float color_scale[3];   /* Texture::colorScale (Texture.hpp:110) */
+    int32_t width, height, channels; /* IMAGE_*: texel grid, 1..4 channels  */
+    const void* pixels;     /* IMAGE_U8: uint8 (already sRGB->linear LUT'ed if
+                               the reference would load with gammaCorrection,
+                               Texture.cpp:10-18); IMAGE_F32: float          */
+    int32_t tex_a, tex_b;   /* CHECKER: the two child textures */
+    float uv_scale[2];      /* CHECKER: uvscale (invScale = 1/uvscale)       */
+} pt_texture_desc;
+
+typedef enum pt_mat_kind {
+    PT_MAT_DIFFUSE = 0,        /* MicrofacetDiffuse    Material.hpp:200-361 */
+    PT_MAT_DIELECTRIC = 1,     /* MicrofacetDielectric Material.hpp:363-598 */
+    PT_MAT_THIN_DIELECTRIC = 2,/* ThinDielectric       Material.hpp:601-657 */
+    PT_MAT_CONDUCTOR = 3       /* SpecularConductor    Material.hpp:660-673 */
+} pt_mat_kind;
+
+typedef enum pt_alpha_mode { /* AlphaMode, Material.hpp:176-198 */
+    PT_ALPHA_OPAQUE = 0,
+    PT_ALPHA_BLEND = 1,       /* the reference's default for Diffuse/Dielectric */
+    PT_ALPHA_MASK = 2
+} pt_alpha_mode;
+
+typedef struct pt_material_desc {
+    int32_t kind;        /* pt_mat_kind */
+    int32_t tex;         /* albedo texture id                                  */
+    int32_t norm;        /* normal-map texture id or -1                        */
+    int32_t rough;       /* roughness texture (.g used) or -1 -> default       */
+    int32_t metal;       /* metallic texture (.b used) or -1 -> default (0)    */
+    int32_t alpha;       /* alpha-mask texture (.r used) or -1                 */
+    float ri;            /* DIELECTRIC / THIN: refractive index                */
+    float albedo[3];     /* CONDUCTOR: Schlick F0 tint                         */
+    int32_t alpha_mode;  /* pt_alpha_mode (after setAlphaTester's demotion rule,
+                            Material.hpp:350-353, applied by the caller)       */
+    float alpha_cutoff;
+} pt_material_desc;
+
+typedef struct pt_medium_desc { /* HomogeneusMedium ctor, Medium.hpp:18-20 */
+    float sigma_a[3], sigma_s[3];
+    float g;             /* HenyeyGreenstein(g), clamped to +-0.99 */
+    float density;
+    float Le[3];
+    float le_density;
+} pt_medium_desc;
+
+/* One Mesh (Mesh.hpp:16-22).  normals/texcoords are per vertex and required;
+ * tangents may be NULL (Shape.cpp:228-238 fallback).  material < 0 makes the
+ * mesh a material-less medium boundary (Integrators.cpp:228-232).
+ * emissive_tex >= 0 turns every triangle into a two-sided AreaLight as
+ * Model::BuildBlas does (Model.hpp:47-59).                                   */
+typedef struct pt_mesh_desc {
+    const float* positions;   /* 3 * n_vertices */
+    const float* normals;     /* 3 * n_vertices */
+    const float* texcoords;   /* 2 * n_vertices */
+    const float* tangents;    /* 3 * n_vertices or NULL */
+    const uint32_t* indices;  /* 3 * n_triangles */
+    uint32_t n_vertices, n_triangles;
+    int32_t material, emissive_tex, medium;
+} pt_mesh_desc;
+
+typedef enum pt_light_kind {
+    PT_LIGHT_UNIFORM_INFINITE = 0, /* UniformInfiniteLight  Light.cpp:27-50   */
+    PT_LIGHT_GRADIENT_INFINITE = 1,/* FunctionInfiniteLight Light.cpp:53-108 with
+                                      the gradient sky every reference scene uses
+                                      (main.cpp:108-111):
+                                      scale*((1-a)*color + a*color_b), a=.5*(d.y+1) */
+    PT_LIGHT_TEXTURE_INFINITE = 2, /* TextureInfiniteLight  Light.cpp:110-200 */
+    PT_LIGHT_DISTANT = 3,          /* DistantLight          Light.cpp:202-227 */
+    PT_LIGHT_POINT = 4             /* PointLight            Light.cpp:229-251 */
+} pt_light_kind;
+
+typedef struct pt_light_desc {
+    int32_t kind;
+    float color[3];
+    float color_b[3];
+    float scale;        /* GRADIENT: multiplier; TEXTURE: LeScale */
+    float dir_or_pos[3];/* DISTANT: dir; POINT: p */
+    int32_t tex;        /* TEXTURE_INFINITE */
+    int32_t power_func; /* 0: sqrt(r) (default), 1: 4*r (PointLight default), 2: 4*sqrt(r) */
+} pt_light_desc;
+
+typedef struct pt_scene pt_scene;
+
+/* lifetime */
+PT_API int pt_device_count(void);
+PT_API pt_scene* pt_scene_create(int device);            /* NULL on failure   */
+PT_API void pt_scene_destroy(pt_scene*);
+PT_API const char* pt_last_error(void);
+
+/* build (before commit).  replaces the user-side object graph of
+ * examples/example_1.cpp:17-101.                                            */
+PT_API int pt_scene_add_texture(pt_scene*, const pt_texture_desc*);
+PT_API int pt_scene_add_material(pt_scene*, const pt_material_desc*);
+PT_API int pt_scene_add_medium(pt_scene*, const pt_medium_desc*);
+PT_API int pt_scene_add_mesh(pt_scene*, const pt_mesh_desc*);
+/* a BLAS = Model::BuildBlas<BLASx> over these meshes (Model.hpp:41-60)       */
+PT_API int pt_scene_add_blas(pt_scene*, const int32_t* mesh_ids, int n_meshes);
+/* transform: column-major 4x4 (glm::mat4) -> TransformedPrimitive
+ * (Primitive.hpp:37-50); NULL -> the BLAS itself is the TLAS primitive.      */
+PT_API int pt_scene_add_instance(pt_scene*, int blas_id, const float* transform16);
+PT_API int pt_scene_add_light(pt_scene*, const pt_light_desc*);
+PT_API int pt_scene_set_medium(pt_scene*, int medium_id); /* Scene::SetMedium  */
+
+/* Scene::BuildTlas<TLAS2|TLAS4> + BLAS2|BLAS4 build + upload.
+ * bvh_width in {2,4}.  light_sampler: 0 Uniform, 1 Power (LightSampler.cpp). */
+PT_API int pt_scene_commit(pt_scene*, int bvh_width, int light_sampler);
+
+/* scene bounds after commit: Scene::BoundingBox (Scene.cpp:45-47)           */
+PT_API int pt_scene_bounds(const pt_scene*, float bmin[3], float bmax[3]);
+
+/* ---- ray casting entry points ------------------------------------------------- */
+
+/* host buffers: H2D, kernel, D2H inside the call.  inst may be NULL.        */
+PT_API int pt_trace_closest(pt_scene*, const pt_ray* rays, size_t n,
+                            pt_hit* hits, uint32_t* inst);
+PT_API int pt_trace_any(pt_scene*, const pt_ray* rays, size_t n, uint8_t* occluded);
+
+/* device buffers (already resident in HBM), launched on `stream`
+ * (a cudaStream_t passed as void*; NULL = default stream); asynchronous.    */
+PT_API int pt_trace_closest_dev(pt_scene*, const void* d_rays, size_t n,
+                                void* d_hits, void* d_inst, void* stream);
+PT_API int pt_trace_any_dev(pt_scene*, const void* d_rays, size_t n,
+                            void* d_occluded, void* stream);
+
+/* traversal statistics of the last counted launch (for the roofline's
+ * algorithmic bytes): runs a counting build of the SAME
+ * traversal over device rays and returns totals.                            */
+typedef struct pt_trace_stats {
+    uint64_t rays;
+    uint64_t tlas_nodes;   /* TLAS inner-node (child-pair / cluster) visits  */
+    uint64_t blas_nodes;   /* BLAS inner-node visits                         */
+    uint64_t instances;    /* instance records entered                       */
+    uint64_t triangles;    /* triangle tests                                 */
+    uint64_t hits;
+} pt_trace_stats;
+PT_API int pt_trace_closest_stats(pt_scene*, const void* d_rays, size_t n,
+                                  pt_trace_stats* out);
+
+/* ---- rendering ---------------------------------------------------------------- */
+
+typedef struct pt_camera_desc { /* Camera ctor, Camera.hpp:6-20 */
+    float look_from[3], look_at[3];
+    float fov;             /* radians, horizontal (Camera.hpp:12) */
+    float focus_angle, focus_distance;
+    int32_t medium;        /* camera medium id or -1 */
+    float shutter_start, shutter_end;
+} pt_camera_desc;
+
+typedef enum pt_integrator_kind {
+    PT_INTEGRATOR_SIMPLE = 0, /* SimplePathIntegrator::Li Integrators.cpp:131-180 */
+    PT_INTEGRATOR_PATH = 1,   /* PathIntegrator::Li       Integrators.cpp:182-294 */
+    PT_INTEGRATOR_VOLPATH = 2 /* VolPathIntegrator::Li    Integrators.cpp:296-479 */
+} pt_integrator_kind;
+
+typedef enum pt_filter_kind {
+    PT_FILTER_BOX = 0, PT_FILTER_GAUSSIAN = 1, PT_FILTER_MITCHELL = 2, PT_FILTER_LANCZOS = 3
+} pt_filter_kind;
+
+typedef struct pt_render_params {
+    int32_t width, height;
+    int32_t spp;            /* exactly spp samples per pixel (adaptive loop of
+                               Integrators.cpp:59-86 disabled unless adaptive=1) */
+    int32_t max_depth;
+    int32_t integrator;     /* pt_integrator_kind */
+    int32_t sampler;        /* 0 UniformSampler, 1 StratifiedSampler */
+    int32_t strata_x, strata_y;
+    int32_t filter;         /* pt_filter_kind */
+    float filter_radius[2];
+    float filter_param[2];  /* gaussian sigma | mitchell b,c | lanczos tau */
+    uint64_t seed;
+    int32_t pass_begin;     /* sample passes [pass_begin, pass_end) with stride */
+    int32_t pass_stride;    /*   pass_stride: rank r of G renders r, r+G, ...   */
+    int32_t adaptive;       /* 1: per-pixel adaptive loop, up to 128 batches    */
+} pt_render_params;
+
+typedef struct pt_render_stats {
+    uint64_t samples;       /* camera samples traced                          */
+    uint64_t closest_rays;  /* extend rays                                    */
+    uint64_t shadow_rays;   /* NEE rays (any-hit or transmittance march legs) */
+    uint64_t kernel_launches;
+    double gpu_ms;          /* CUDA-event time of the whole render            */
+} pt_render_stats;
+
+/* Integrator::Render (Integrators.cpp:23-129) for the params' sample passes.
+ * Accumulates into the scene's device film (double RGBW, W*H*4), creating or
+ * clearing it when `clear` != 0.                                             */
+PT_API int pt_render(pt_scene*, const pt_camera_desc*, const pt_render_params*,
+                     int clear, pt_render_stats* stats);
+/* device film pointer (double[4*W*H], RGB sums * w and weight sums) for the
+ * caller's own collective (one ncclReduce).                   */
+PT_API int pt_film_device_ptr(pt_scene*, void** d_film, size_t* n_doubles);
+/* Film readback: rgbw[4*W*H] doubles, row 0 first (Film.hpp:125-132 layout). */
+PT_API int pt_film_download(pt_scene*, double* rgbw);
+PT_API int pt_film_upload(pt_scene*, const double* rgbw, int width, int height);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* PT_B200_H */

@@ -1,0 +1,409 @@
+// bvh_build.cpp — see bvh_build.hpp.  Compiled with -ffp-contract=off: the SAH
+// costs decide the topology and must not depend on FMA contraction.
+#include "bvh_build.hpp"
+
+#include <atomic>
+#include <cfloat>
+#include <cmath>
+#include <limits>
+#include <thread>
+
+namespace ptb {
+
+static inline float fmin2(float a, float b){ return b < a ? b : a; }   // glm::min
+static inline float fmax2(float a, float b){ return a < b ? b : a; }   // glm::max
+
+Box box_empty(){
+    Box b;
+    const float inf = std::numeric_limits<float>::infinity();
+    for(int k = 0; k < 3; k++){ b.lo[k] = inf; b.hi[k] = -inf; }
+    return b;
+}
+void box_grow(Box& b, const Box& o){
+    for(int k = 0; k < 3; k++){ b.lo[k] = fmin2(b.lo[k], o.lo[k]); b.hi[k] = fmax2(b.hi[k], o.hi[k]); }
+}
+void box_grow(Box& b, const float p[3]){
+    for(int k = 0; k < 3; k++){ b.lo[k] = fmin2(b.lo[k], p[k]); b.hi[k] = fmax2(b.hi[k], p[k]); }
+}
+float box_half_area(const Box& b){
+    const float ex = b.hi[0] - b.lo[0], ey = b.hi[1] - b.lo[1], ez = b.hi[2] - b.lo[2];
+    return ex * ey + ey * ez + ez * ex;
+}
+
+namespace {
+
+struct Item {
+    uint32_t index;
+    Box box;
+    float c[3];   // centroid = 0.5f * (hi + lo)  (BVH.hpp:89)
+};
+
+struct BinAcc {
+    Box box = box_empty();
+    uint32_t n = 0;
+};
+
+struct Builder {
+    std::vector<Item>& items;
+    std::vector<BuildNode>& nodes;
+    std::atomic<uint32_t> next { 0 };
+    uint32_t leaf_size;
+
+    Builder(std::vector<Item>& it, std::vector<BuildNode>& nd, uint32_t ls) : items(it), nodes(nd), leaf_size(ls){}
+
+    // Hoare-style in-place partition with the visiting order of a
+    // bidirectional std::partition, so item order inside leaves (and with it
+    // the winner among exactly tied hits) is the reference's.
+    uint32_t split_items(uint32_t first, uint32_t last, int axis, float pos){
+        while(true){
+            while(true){
+                if(first == last)return first;
+                if(items[first].c[axis] <= pos)++first; else break;
+            }
+            --last;
+            while(true){
+                if(first == last)return first;
+                if(!(items[last].c[axis] <= pos))--last; else break;
+            }
+            std::swap(items[first], items[last]);
+            ++first;
+        }
+    }
+
+    uint32_t build(uint32_t first, uint32_t last){
+        const uint32_t me = next.fetch_add(1, std::memory_order_relaxed);
+        BuildNode& node = nodes[me];
+        const uint32_t span = last - first;
+
+        float cmax[3] = { -FLT_MAX, -FLT_MAX, -FLT_MAX };
+        float cmin[3] = { FLT_MAX, FLT_MAX, FLT_MAX };
+        node.box = box_empty();
+        for(uint32_t i = first; i < last; i++){
+            box_grow(node.box, items[i].box);
+            for(int k = 0; k < 3; k++){
+                cmax[k] = fmax2(cmax[k], items[i].c[k]);
+                cmin[k] = fmin2(cmin[k], items[i].c[k]);
+            }
+        }
+        node.right = first;
+        node.count = span;
+        if(span <= leaf_size)return me;
+
+        int best_axis = 0;
+        float best_pos = 0.0f;
+        float best_cost = std::numeric_limits<float>::infinity();
+        const uint32_t nbins = span >= 1024 ? 32u : span >= 64 ? 16u : 8u;
+        BinAcc bins[32];
+        float right_area[31];
+
+        for(int axis = 0; axis < 3; axis++){
+            const float mx = cmax[axis], mn = cmin[axis];
+            if(std::fabs(mx - mn) <= FLT_EPSILON)continue;
+            for(uint32_t b = 0; b < nbins; b++)bins[b] = BinAcc();
+            float scale = nbins / (mx - mn);
+            for(uint32_t i = first; i < last; i++){
+                int id = (int)((items[i].c[axis] - mn) * scale);
+                if(id > (int)nbins - 1)id = (int)nbins - 1;
+                ++bins[id].n;
+                box_grow(bins[id].box, items[i].box);
+            }
+            Box rbox = box_empty(), lbox = box_empty();
+            for(uint32_t b = nbins - 1; b >= 1; b--){
+                box_grow(rbox, bins[b].box);
+                right_area[b - 1] = box_half_area(rbox);
+            }
+            scale = (mx - mn) / nbins;
+            uint32_t lsum = 0;
+            for(uint32_t b = 0; b + 1 < nbins; b++){
+                lsum += bins[b].n;
+                box_grow(lbox, bins[b].box);
+                // an empty side has area = inf*inf+... and count 0 -> NaN cost,
+                // which never compares < best (same as the reference)
+                const float cost = lsum * box_half_area(lbox) + (span - lsum) * right_area[b];
+                if(cost < best_cost){
+                    best_axis = axis;
+                    best_pos = mn + (b + 1) * scale;
+                    best_cost = cost;
+                }
+            }
+        }
+        const float parent_cost = box_half_area(node.box) * span;
+        if(best_cost >= parent_cost)return me;
+
+        const uint32_t mid = split_items(first, last, best_axis, best_pos);
+        if(mid == first || mid == last)return me;
+
+        uint32_t l, r;
+        if(span > 256u * 1024u){
+            std::thread t([&]{ l = build(first, mid); });
+            r = build(mid, last);
+            t.join();
+        } else{
+            l = build(first, mid);
+            r = build(mid, last);
+        }
+        // `node` stays valid: the vector is pre-sized and never reallocates
+        node.left = l;
+        node.right = r;
+        node.count = 0;
+        node.axis = (uint32_t)best_axis;
+        return me;
+    }
+};
+
+} // namespace
+
+BinaryBvh build_binary_bvh(const Box* boxes, uint32_t n, uint32_t leaf_size){
+    BinaryBvh out;
+    if(n == 0)return out;
+    std::vector<Item> items(n);
+    for(uint32_t i = 0; i < n; i++){
+        items[i].index = i;
+        items[i].box = boxes[i];
+        for(int k = 0; k < 3; k++)items[i].c[k] = 0.5f * (boxes[i].hi[k] + boxes[i].lo[k]);
+    }
+    out.nodes.resize(2 * (size_t)n - 1);
+    Builder b(items, out.nodes, leaf_size);
+    b.build(0, n);
+    out.nodes.resize(b.next.load());
+    out.order.resize(n);
+    for(uint32_t i = 0; i < n; i++)out.order[i] = items[i].index;
+    return out;
+}
+
+// ---- flattening ---------------------------------------------------------------------
+
+namespace {
+
+inline uint32_t leaf_ref(uint32_t first){ return REF_LEAF | first; }
+
+void mark_leaf(FlatBvh& f, const BuildNode& n){
+    f.leaf_last[n.right + n.count - 1] = 1;
+}
+
+// BVH2: DFS preorder over inner nodes; node k holds the boxes + refs of its two
+// children (what BVH2::Intersect reads from nodes[idx+1] and nodes[right]).
+uint32_t flatten2(FlatBvh& f, const BinaryBvh& b, uint32_t ni){
+    const BuildNode& n = b.nodes[ni];
+    if(n.count != 0){ mark_leaf(f, n); return leaf_ref(n.right); }
+    const uint32_t me = (uint32_t)f.n2.size();
+    f.n2.emplace_back();
+    const BuildNode& l = b.nodes[n.left];
+    const BuildNode& r = b.nodes[n.right];
+    const uint32_t r0 = flatten2(f, b, n.left);
+    const uint32_t r1 = flatten2(f, b, n.right);
+    Bvh2Node& o = f.n2[me];
+    for(int k = 0; k < 3; k++){
+        o.lo0[k] = l.box.lo[k]; o.hi0[k] = l.box.hi[k];
+        o.lo1[k] = r.box.lo[k]; o.hi1[k] = r.box.hi[k];
+    }
+    o.ref0 = r0; o.ref1 = r1; o.axis = n.axis; o.pad = 0;
+    return me;
+}
+
+// BVH4 collapse.  A cluster is described by a tiny expression tree over the
+// original binary nodes: Leafs of that tree become the cluster's lanes.
+struct Expr {
+    int lane = -1;          // >= 0: a lane holding binary node `node`
+    uint32_t node = 0;
+    uint32_t axis = 0;      // split axis (inner expr)
+    int l = -1, r = -1;     // children (indices into the per-cluster pool)
+};
+
+struct ClusterPlan {
+    Expr pool[7];
+    int used = 0;
+    int root = -1;
+    int add_lane(uint32_t node){ pool[used].node = node; pool[used].lane = 0; return used++; }
+    int add_split(uint32_t axis, int l, int r){ pool[used].axis = axis; pool[used].l = l; pool[used].r = r; pool[used].lane = -1; return used++; }
+};
+
+// Visit order for one octant: at every binary split the near side comes
+// first; a negative direction on the split axis makes the right side near
+// (this is what the 5x27x8 LUT of BVH.hpp:562-718 enumerates).
+void visit(const ClusterPlan& p, int e, unsigned octant, int* out, int& n){
+    const Expr& x = p.pool[e];
+    if(x.lane >= 0){ out[n++] = x.lane; return; }
+    const bool neg = (octant >> x.axis) & 1u;
+    visit(p, neg ? x.r : x.l, octant, out, n);
+    visit(p, neg ? x.l : x.r, octant, out, n);
+}
+
+uint32_t flatten4(FlatBvh& f, const BinaryBvh& b, uint32_t ni){
+    const BuildNode& n = b.nodes[ni];
+    if(n.count != 0){ mark_leaf(f, n); return leaf_ref(n.right); }
+    const uint32_t me = (uint32_t)f.n4.size();
+    f.n4.emplace_back();
+
+    const BuildNode& L = b.nodes[n.left];
+    const BuildNode& R = b.nodes[n.right];
+    const bool lleaf = L.count != 0, rleaf = R.count != 0;
+    ClusterPlan p;
+    // lane numbers follow BVH4::buildBVH4's slot choices (BVH.hpp:801-1015)
+    auto lane = [&](uint32_t node, int slot){ int e = p.add_lane(node); p.pool[e].lane = slot; return e; };
+    if(lleaf && rleaf){
+        p.root = p.add_split(n.axis, lane(n.left, 0), lane(n.right, 2));
+    } else if(lleaf){
+        const BuildNode& RL = b.nodes[R.left];
+        const BuildNode& RR = b.nodes[R.right];
+        if(RL.count != 0 && RR.count != 0){
+            int sub = p.add_split(R.axis, lane(R.left, 2), lane(R.right, 3));
+            p.root = p.add_split(n.axis, lane(n.left, 0), sub);
+        } else if(RL.count != 0){
+            int low = p.add_split(RR.axis, lane(RR.left, 2), lane(RR.right, 3));
+            int sub = p.add_split(R.axis, lane(R.left, 1), low);
+            p.root = p.add_split(n.axis, lane(n.left, 0), sub);
+        } else{
+            int low = p.add_split(RL.axis, lane(RL.left, 1), lane(RL.right, 2));
+            int sub = p.add_split(R.axis, low, lane(R.right, 3));
+            p.root = p.add_split(n.axis, lane(n.left, 0), sub);
+        }
+    } else if(rleaf){
+        const BuildNode& LL = b.nodes[L.left];
+        const BuildNode& LR = b.nodes[L.right];
+        if(LL.count != 0 && LR.count != 0){
+            int sub = p.add_split(L.axis, lane(L.left, 0), lane(L.right, 1));
+            p.root = p.add_split(n.axis, sub, lane(n.right, 2));
+        } else if(LL.count != 0){
+            int low = p.add_split(LR.axis, lane(LR.left, 1), lane(LR.right, 2));
+            int sub = p.add_split(L.axis, lane(L.left, 0), low);
+            p.root = p.add_split(n.axis, sub, lane(n.right, 3));
+        } else{
+            int low = p.add_split(LL.axis, lane(LL.left, 0), lane(LL.right, 1));
+            int sub = p.add_split(L.axis, low, lane(L.right, 2));
+            p.root = p.add_split(n.axis, sub, lane(n.right, 3));
+        }
+    } else{
+        int a = p.add_split(L.axis, lane(L.left, 0), lane(L.right, 1));
+        int c = p.add_split(R.axis, lane(R.left, 2), lane(R.right, 3));
+        p.root = p.add_split(n.axis, a, c);
+    }
+
+    uint32_t refs[4] = { REF_EMPTY, REF_EMPTY, REF_EMPTY, REF_EMPTY };
+    Box boxes[4];
+    for(int k = 0; k < 4; k++)for(int a = 0; a < 3; a++){ boxes[k].lo[a] = 0.0f; boxes[k].hi[a] = 0.0f; } // inactive lanes: zero boxes (BVH.hpp:46-48)
+    // children are emitted lane by lane in increasing lane order, as the
+    // reference recursion does
+    int by_lane[4] = { -1, -1, -1, -1 };
+    for(int e = 0; e < p.used; e++)if(p.pool[e].lane >= 0)by_lane[p.pool[e].lane] = e;
+    for(int k = 0; k < 4; k++){
+        if(by_lane[k] < 0)continue;
+        const uint32_t child = p.pool[by_lane[k]].node;
+        boxes[k] = b.nodes[child].box;
+        refs[k] = flatten4(f, b, child);
+    }
+    Bvh4Node& o = f.n4[me];
+    for(int k = 0; k < 4; k++){
+        o.xmin[k] = boxes[k].lo[0]; o.xmax[k] = boxes[k].hi[0];
+        o.ymin[k] = boxes[k].lo[1]; o.ymax[k] = boxes[k].hi[1];
+        o.zmin[k] = boxes[k].lo[2]; o.zmax[k] = boxes[k].hi[2];
+        o.ref[k] = refs[k];
+    }
+    for(unsigned oct = 0; oct < 8; oct++){
+        int seq[4], cnt = 0;
+        visit(p, p.root, oct, seq, cnt);
+        bool seen[4] = { false, false, false, false };
+        for(int k = 0; k < cnt; k++)seen[seq[k]] = true;
+        for(int k = 0; k < 4; k++)if(!seen[k])seq[cnt++] = k;   // absent lanes last; never pushed
+        o.order[oct] = (uint8_t)((seq[0] << 6) | (seq[1] << 4) | (seq[2] << 2) | seq[3]);
+    }
+    o.pad[0] = o.pad[1] = 0;
+    return me;
+}
+
+} // namespace
+
+FlatBvh flatten_bvh(const BinaryBvh& b, int width){
+    FlatBvh f;
+    f.width = width;
+    f.order = b.order;
+    f.leaf_last.assign(b.order.size(), 0);
+    if(b.nodes.empty())return f;
+    f.bounds = b.nodes[0].box;
+    if(width == 2){
+        f.n2.reserve(b.nodes.size() / 2 + 1);
+        f.root = flatten2(f, b, 0);
+    } else{
+        f.n4.reserve(b.nodes.size() / 3 + 1);
+        f.root = flatten4(f, b, 0);
+    }
+    return f;
+}
+
+// ---- small matrix helpers (column-major, glm operation order) -----------------------
+
+void mat4_inverse(const float m[16], float out[16]){
+#define M(c, r) m[(c) * 4 + (r)]
+    const float c00 = M(2, 2) * M(3, 3) - M(3, 2) * M(2, 3);
+    const float c02 = M(1, 2) * M(3, 3) - M(3, 2) * M(1, 3);
+    const float c03 = M(1, 2) * M(2, 3) - M(2, 2) * M(1, 3);
+    const float c04 = M(2, 1) * M(3, 3) - M(3, 1) * M(2, 3);
+    const float c06 = M(1, 1) * M(3, 3) - M(3, 1) * M(1, 3);
+    const float c07 = M(1, 1) * M(2, 3) - M(2, 1) * M(1, 3);
+    const float c08 = M(2, 1) * M(3, 2) - M(3, 1) * M(2, 2);
+    const float c10 = M(1, 1) * M(3, 2) - M(3, 1) * M(1, 2);
+    const float c11 = M(1, 1) * M(2, 2) - M(2, 1) * M(1, 2);
+    const float c12 = M(2, 0) * M(3, 3) - M(3, 0) * M(2, 3);
+    const float c14 = M(1, 0) * M(3, 3) - M(3, 0) * M(1, 3);
+    const float c15 = M(1, 0) * M(2, 3) - M(2, 0) * M(1, 3);
+    const float c16 = M(2, 0) * M(3, 2) - M(3, 0) * M(2, 2);
+    const float c18 = M(1, 0) * M(3, 2) - M(3, 0) * M(1, 2);
+    const float c19 = M(1, 0) * M(2, 2) - M(2, 0) * M(1, 2);
+    const float c20 = M(2, 0) * M(3, 1) - M(3, 0) * M(2, 1);
+    const float c22 = M(1, 0) * M(3, 1) - M(3, 0) * M(1, 1);
+    const float c23 = M(1, 0) * M(2, 1) - M(2, 0) * M(1, 1);
+    const float f0[4] = { c00, c00, c02, c03 }, f1[4] = { c04, c04, c06, c07 }, f2[4] = { c08, c08, c10, c11 };
+    const float f3[4] = { c12, c12, c14, c15 }, f4[4] = { c16, c16, c18, c19 }, f5[4] = { c20, c20, c22, c23 };
+    const float v0[4] = { M(1, 0), M(0, 0), M(0, 0), M(0, 0) };
+    const float v1[4] = { M(1, 1), M(0, 1), M(0, 1), M(0, 1) };
+    const float v2[4] = { M(1, 2), M(0, 2), M(0, 2), M(0, 2) };
+    const float v3[4] = { M(1, 3), M(0, 3), M(0, 3), M(0, 3) };
+    const float sa[4] = { 1, -1, 1, -1 }, sb[4] = { -1, 1, -1, 1 };
+    float inv[16];
+    for(int k = 0; k < 4; k++){
+        inv[0 * 4 + k] = ((v1[k] * f0[k] - v2[k] * f1[k]) + v3[k] * f2[k]) * sa[k];
+        inv[1 * 4 + k] = ((v0[k] * f0[k] - v2[k] * f3[k]) + v3[k] * f4[k]) * sb[k];
+        inv[2 * 4 + k] = ((v0[k] * f1[k] - v1[k] * f3[k]) + v3[k] * f5[k]) * sa[k];
+        inv[3 * 4 + k] = ((v0[k] * f2[k] - v1[k] * f4[k]) + v2[k] * f5[k]) * sb[k];
+    }
+    const float d0 = M(0, 0) * inv[0 * 4 + 0], d1 = M(0, 1) * inv[1 * 4 + 0], d2 = M(0, 2) * inv[2 * 4 + 0], d3 = M(0, 3) * inv[3 * 4 + 0];
+    const float det = (d0 + d1) + (d2 + d3);
+    const float inv_det = 1.0f / det;
+    for(int k = 0; k < 16; k++)out[k] = inv[k] * inv_det;
+#undef M
+}
+
+void mat3_normal_matrix(const float m4[16], float out[9]){
+#define M(c, r) m4[(c) * 4 + (r)]
+    const float ood = 1.0f / (
+        +M(0, 0) * (M(1, 1) * M(2, 2) - M(2, 1) * M(1, 2))
+        - M(1, 0) * (M(0, 1) * M(2, 2) - M(2, 1) * M(0, 2))
+        + M(2, 0) * (M(0, 1) * M(1, 2) - M(1, 1) * M(0, 2)));
+    float inv[9]; // inv[c*3+r]
+    inv[0 * 3 + 0] = +(M(1, 1) * M(2, 2) - M(2, 1) * M(1, 2)) * ood;
+    inv[1 * 3 + 0] = -(M(1, 0) * M(2, 2) - M(2, 0) * M(1, 2)) * ood;
+    inv[2 * 3 + 0] = +(M(1, 0) * M(2, 1) - M(2, 0) * M(1, 1)) * ood;
+    inv[0 * 3 + 1] = -(M(0, 1) * M(2, 2) - M(2, 1) * M(0, 2)) * ood;
+    inv[1 * 3 + 1] = +(M(0, 0) * M(2, 2) - M(2, 0) * M(0, 2)) * ood;
+    inv[2 * 3 + 1] = -(M(0, 0) * M(2, 1) - M(2, 0) * M(0, 1)) * ood;
+    inv[0 * 3 + 2] = +(M(0, 1) * M(1, 2) - M(1, 1) * M(0, 2)) * ood;
+    inv[1 * 3 + 2] = -(M(0, 0) * M(1, 2) - M(1, 0) * M(0, 2)) * ood;
+    inv[2 * 3 + 2] = +(M(0, 0) * M(1, 1) - M(1, 0) * M(0, 1)) * ood;
+    for(int c = 0; c < 3; c++)for(int r = 0; r < 3; r++)out[c * 3 + r] = inv[r * 3 + c]; // transpose
+#undef M
+}
+
+Box transform_box(const float m[16], const Box& b){
+    Box out = box_empty();
+    for(int n = 0; n < 8; n++){
+        const float x = (n & 1) ? b.hi[0] : b.lo[0];
+        const float y = (n & 2) ? b.hi[1] : b.lo[1];
+        const float z = (n & 4) ? b.hi[2] : b.lo[2];
+        float p[3];
+        for(int r = 0; r < 3; r++)p[r] = (m[0 * 4 + r] * x + m[1 * 4 + r] * y) + (m[2 * 4 + r] * z + m[3 * 4 + r] * 1.0f);
+        box_grow(out, p);
+    }
+    return out;
+}
+
+} // namespace ptb

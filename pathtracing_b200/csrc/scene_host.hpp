@@ -1,0 +1,106 @@
+// scene_host.hpp — host-side scene object behind the C-ABI (pt_scene).
+// Collects the POD description (pt_b200.h), builds BLAS/TLAS on the host
+// (bvh_build.hpp), packs everything into the device layout (pt_types.h,
+// shade_types.h) and uploads it once at commit.  The scene is immutable after
+// commit, like the reference's after Scene::BuildTlas (Scene.hpp:20-24).
+#pragma once
+#include <cstdint>
+#include <string>
+#include <vector>
+
+#include "../../include/pt_b200.h"
+#include "bvh_build.hpp"
+#include "pt_types.h"
+#include "shade_types.h"
+
+namespace ptb {
+
+struct HostTexture {
+    pt_texture_desc d;
+    std::vector<uint8_t> pixels;   // owned copy of image texels (u8 or f32 bytes)
+};
+
+struct HostMesh {
+    pt_mesh_desc d;
+    std::vector<float> pos, nrm, uv, tan;
+    std::vector<uint32_t> idx;
+};
+
+struct HostBlas {
+    std::vector<int> meshes;
+    // filled at commit
+    uint32_t n_tris = 0;
+    uint32_t tri_base = 0;        // offset of this BLAS's triangles in the global leaf-order array
+    uint32_t root = REF_EMPTY;    // rebased root ref
+    Box bounds = box_empty();
+    std::vector<uint32_t> tri_mesh_base; // per mesh: first BLAS-wide triangle id
+};
+
+struct HostInstance {
+    int blas;
+    bool has_xf;
+    float xf[16];
+};
+
+struct DeviceBuffers {
+    void* n2 = nullptr; void* n4 = nullptr; void* tris = nullptr; void* inst = nullptr;
+    // shading tables
+    void* meshes = nullptr; void* blas_info = nullptr; void* inst_shade = nullptr;
+    void* vtx_pos = nullptr; void* vtx_nrm = nullptr; void* vtx_uv = nullptr; void* vtx_tan = nullptr; void* indices = nullptr;
+    void* tri_light = nullptr; void* tri_mesh = nullptr; void* inst_light_base = nullptr; void* sampler_lights = nullptr; void* inf_lights = nullptr;
+    void* textures = nullptr; void* texels = nullptr; void* materials = nullptr; void* media = nullptr;
+    void* lights = nullptr; void* light_cdf = nullptr; void* env_cdf = nullptr;
+    void* film = nullptr;
+    void* work = nullptr;         // wavefront state arena
+    size_t work_bytes = 0;
+    // staging for the host-buffer ray-cast entry points
+    void* stage_rays = nullptr; void* stage_hits = nullptr; void* stage_inst = nullptr; void* stage_occ = nullptr;
+    size_t stage_cap = 0;
+    void* stats = nullptr;
+};
+
+} // namespace ptb
+
+struct pt_scene {
+    int device = 0;
+    bool committed = false;
+    int width = 0;
+    int light_sampler = 1;
+    std::vector<ptb::HostTexture> textures;
+    std::vector<pt_material_desc> materials;
+    std::vector<pt_medium_desc> media;
+    std::vector<ptb::HostMesh> meshes;
+    std::vector<ptb::HostBlas> blas;
+    std::vector<ptb::HostInstance> instances;
+    std::vector<pt_light_desc> lights;
+    int scene_medium = -1;
+
+    ptb::Box bounds = ptb::box_empty();
+    ptb::DevScene dev {};
+    ptb::ShadeScene shade {};
+    ptb::DeviceBuffers buf;
+    int film_w = 0, film_h = 0;
+    uint64_t total_tris = 0, total_nodes = 0;
+    void* stream = nullptr;       // internal stream for the host-buffer entry points
+    void* stream2 = nullptr;
+    void* ev[4] = { nullptr, nullptr, nullptr, nullptr };
+};
+
+namespace ptb {
+
+void set_error(const std::string& msg);
+const char* get_error();
+bool cuda_ok(int err, const char* what);     // records the message on failure
+
+int scene_commit(pt_scene* s, int width, int light_sampler);
+void scene_free_device(pt_scene* s);
+
+// trace.cu
+int launch_trace_closest(const DevScene& S, const void* d_rays, size_t n, void* d_hits, void* d_inst, void* stream);
+int launch_trace_any(const DevScene& S, const void* d_rays, size_t n, void* d_occ, void* stream);
+int launch_trace_stats(const DevScene& S, const void* d_rays, size_t n, void* d_counters /* 6 x u64 */, void* stream);
+
+// render.cu
+int render_passes(pt_scene* s, const pt_camera_desc* cam, const pt_render_params* rp, int clear, pt_render_stats* stats);
+
+} // namespace ptb

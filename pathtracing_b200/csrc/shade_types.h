@@ -1,0 +1,108 @@
+// shade_types.h — device tables read by the shade stage (materials, textures,
+// lights, media, per-mesh vertex data).  Plain PODs, uploaded once at commit.
+#pragma once
+#include <stdint.h>
+
+namespace ptb {
+
+struct DevMesh {
+    uint32_t vtx_base;       // first vertex in the global vertex arrays
+    uint32_t idx_base;       // first index (uint32) in the global index array
+    uint32_t prim_base;      // BLAS-wide id of this mesh's triangle 0
+    uint32_t has_tangents;
+    int32_t material;        // -1: medium boundary (no material)
+    int32_t emissive_tex;    // -1: not emissive
+    int32_t medium;          // -1: none
+    uint32_t pad;
+};
+
+struct DevBlasInfo {
+    uint32_t tri_base;       // offset of this BLAS in the per-triangle tables (original order)
+    uint32_t n_tris;
+};
+
+struct DevInstShade {
+    float fwd[12];           // rows 0..2 of transform, fwd[c*3+r]
+    float nrm[9];            // transpose(inverse(mat3(transform))), nrm[c*3+r]
+    float inv[12];           // rows 0..2 of inverse transform
+    float det;               // glm::determinant(transform) (TransformedLight::Power)
+    uint32_t blas;
+    uint32_t has_xf;
+};
+
+struct DevTexture {
+    int32_t kind;            // pt_tex_kind
+    float color[3];          // SOLID albedo
+    float scale[3];          // colorScale
+    int32_t w, h, ch;
+    unsigned long long texels; // byte offset into the texel blob
+    int32_t tex_a, tex_b;
+    float inv_scale[2];      // CHECKER: 1/uvscale
+};
+
+struct DevMaterial {
+    int32_t kind;            // pt_mat_kind
+    int32_t tex, norm, rough, metal, alpha;
+    float ri;
+    float albedo[3];
+    int32_t alpha_mode;
+    float alpha_cutoff;
+    float rough_default;     // used when rough < 0: 1 (Diffuse) / 0 (Dielectric)
+};
+
+struct DevMedium {
+    float sigma_a[3], sigma_s[3], sigma_t[3], Le[3];
+    float g;
+};
+
+enum DevLightKind : int32_t {
+    DL_UNIFORM_INF = 0, DL_GRADIENT_INF = 1, DL_TEXTURE_INF = 2, DL_DISTANT = 3, DL_POINT = 4, DL_AREA = 5
+};
+
+struct DevLight {
+    int32_t kind;
+    float color[3];
+    float color_b[3];
+    float scale;
+    float v[3];              // DISTANT dir / POINT position
+    int32_t tex;             // TEXTURE_INF texture | AREA emissive texture
+    float power;             // Light::Power() after PreProcess
+    float pmf;               // LightSampler::PMF(light)
+    // AREA: which triangle (object space data fetched from the mesh arrays)
+    uint32_t inst;           // instance id (transform) ; 0xFFFFFFFF for none
+    uint32_t mesh;
+    uint32_t tri;            // mesh-local triangle index
+    float area;              // TriangleShape::Area()
+    float total_weight;      // TEXTURE_INF: sum of the luminance table
+    uint32_t pad;
+};
+
+struct ShadeScene {
+    const DevMesh* meshes;
+    const DevBlasInfo* blas;
+    const DevInstShade* inst;
+    const float* pos;        // 3 floats per vertex
+    const float* nrm;
+    const float* uv;         // 2 floats per vertex
+    const float* tan;        // 3 floats per vertex (zeros if mesh has none)
+    const uint32_t* idx;
+    const uint32_t* tri_mesh;  // per BLAS-wide triangle (original order): mesh id
+    const int32_t* tri_light;  // per (instance-expanded) emissive triangle lookup, see light_base
+    const int32_t* inst_light_base; // per instance: offset into tri_light or -1 (no emissive mesh)
+    const DevTexture* textures;
+    const uint8_t* texels;
+    const DevMaterial* materials;
+    const DevMedium* media;
+    const DevLight* lights;    // all lights (also culled ones)
+    const int32_t* sampler_lights; // indices of the lights the sampler can pick
+    const float* sampler_cdf;  // running power sum (PowerLightSampler::Sample)
+    const int32_t* inf_lights; // indices of scene->infiniteLights
+    const float* env_cdf;      // TEXTURE_INF: running luminance sum (xSamples*ySamples)
+    int32_t n_lights, n_sampler_lights, n_inf_lights;
+    int32_t sampler_kind;      // 0 uniform, 1 power
+    float total_power;
+    int32_t scene_medium;
+    int32_t env_w, env_h;
+};
+
+} // namespace ptb
