@@ -1,0 +1,327 @@
+#!/usr/bin/env python
+"""bench.py — BASELINE.json's metric on its C2 config (ray-cast-only: 16 Mi random
+incoherent rays vs a synthetic 1M-triangle mesh, BVH4 closest-hit, BVH2 beside it).
+
+  python bench.py --gpus N --steps K --warmup W            # this repo's CUDA path
+  python bench.py --impl reference --gpus N ...            # the reference's own CPU code
+
+One JSON line on stdout (rank 0).  A "step" is one pass of the hot path over one batch
+of rays.  `value` is device-resident throughput (CUDA events, max over ranks); `e2e` is
+the same metric through the C-ABI's host-buffer entry point (pinned host rays in, host
+hits out, copies inside the timed region).
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import math
+import os
+import subprocess
+import sys
+import threading
+import time
+from pathlib import Path
+
+import numpy as np
+
+ROOT = Path(__file__).resolve().parent
+sys.path.insert(0, str(ROOT))
+
+METRIC = "incoherent closest-hit ray throughput"
+UNIT = "Mrays/s"
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--tris", type=int, default=1_000_000)
+    ap.add_argument("--rays", type=int, default=1 << 24)
+    ap.add_argument("--mesh", default="soup", choices=["soup", "terrain"])
+    ap.add_argument("--bvh", type=int, default=4, choices=[2, 4])
+    ap.add_argument("--no-extras", action="store_true", help="skip the BVH2 / any-hit / second-mesh side measurements")
+    ap.add_argument("--no-cpu", action="store_true")
+    return ap.parse_args()
+
+
+def make_scene(mesh, tris):
+    from pathtracing_b200 import synth
+    if mesh == "soup":
+        return synth.soup_scene(tris)
+    nx = int(round(math.sqrt(tris / 2.0 * 2.0))) + 1
+    nz = tris // (2 * (nx - 1)) + 1
+    return synth.terrain_scene(nx, nz)
+
+
+def workload_name(a):
+    return (f"C2 ray-cast: {a.rays} random incoherent rays (origin uniform in scene box, direction uniform on S2, "
+            f"tmax=inf) vs {a.tris}-triangle synthetic {a.mesh}, BVH{a.bvh} closest-hit")
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons DURING the timed region (B200_PROFILING.md)."""
+
+    def __init__(self, index):
+        self.rows = []
+        self.proc = None
+        q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+             "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--id={index}", f"--query-gpu={q}", "--format=csv,noheader,nounits", "-lms", "100"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append(line.strip())
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for r in self.rows:
+            f = [x.strip() for x in r.split(",")]
+            if len(f) < 7:
+                continue
+            try:
+                sm.append(float(f[0]))
+                mx.append(float(f[1]))
+            except ValueError:
+                continue
+            for n, v in zip(names, f[3:7]):
+                if v.lower().startswith("active"):
+                    reasons.add(n)
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def dist_env():
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    return rank, world, local
+
+
+# ---------------------------------------------------------------------------------------------
+# reference arm: the reference's own CPU implementation (oracle/_ref, Release flags) on host cores
+# ---------------------------------------------------------------------------------------------
+
+def cpu_reference_rate(a, desc, rays, budget_s=12.0, steps=1, warmup=0):
+    from oracle import refapi
+    flavour = "fast" if refapi.available("fast") else "strict"
+    kind = "reference"
+    ref = refapi.RefScene(desc, a.bvh, id_mode=False, flavour=flavour)
+    cores = ref.threads
+    pilot = min(len(rays), 100_000)
+    ref.trace_closest(rays[:pilot])
+    rate = pilot / max(ref.last_seconds, 1e-6)
+    n = int(min(len(rays), max(200_000, rate * budget_s)))
+    for _ in range(warmup):
+        ref.trace_closest(rays[:min(n, 200_000)])
+    secs = []
+    for _ in range(max(steps, 1)):
+        ref.trace_closest(rays[:n])
+        secs.append(ref.last_seconds)
+    mr = n / np.mean(secs) / 1e6
+    ref.close()
+    return {"value": mr, "unit": UNIT, "cores": cores, "kind": kind,
+            "sample": f"first {n} rays of the {len(rays)}-ray set, all {cores} host threads, reference compiled -O3 ({flavour})"}, float(np.mean(secs)) * 1e3
+
+
+def run_reference(a):
+    rank, world, local = dist_env()
+    if rank != 0:
+        return
+    from pathtracing_b200 import synth
+    desc = make_scene(a.mesh, a.tris)
+    pos_lo, pos_hi = bounds_of(desc)
+    rays = synth.random_rays(min(a.rays, 1 << 22), pos_lo, pos_hi)
+    budget = max(4.0, min(20.0, 150.0 / max(a.steps + a.warmup, 1)))
+    base, ms = cpu_reference_rate(a, desc, rays, budget_s=budget, steps=a.steps, warmup=min(a.warmup, 1))
+    line = {"impl": "reference", "metric": METRIC, "value": base["value"], "unit": UNIT, "n_gpus": a.gpus, "steps": a.steps,
+            "warmup": a.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "f32", "data": "synthetic", "config": {"workload": workload_name(a), "bvh": a.bvh},
+            "cpu_baseline": base,
+            "e2e": {"value": base["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+    print(json.dumps(line), flush=True)
+
+
+def bounds_of(desc):
+    lo = np.full(3, np.inf, np.float32)
+    hi = np.full(3, -np.inf, np.float32)
+    for arr in desc._keep:
+        if arr.dtype == np.float32 and arr.ndim == 2 and arr.shape[1] == 3:
+            lo = np.minimum(lo, arr.min(0))
+            hi = np.maximum(hi, arr.max(0))
+            break   # first float3 array of the single mesh = positions
+    return lo, hi
+
+
+# ---------------------------------------------------------------------------------------------
+# our arm
+# ---------------------------------------------------------------------------------------------
+
+def time_dev(fn, steps, warmup, torch, dist, world):
+    for _ in range(warmup):
+        fn()
+    torch.cuda.synchronize()
+    if world > 1:
+        dist.barrier()
+        torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(steps):
+        fn()
+    e1.record()
+    torch.cuda.synchronize()
+    if world > 1:
+        dist.barrier()
+    ms = e0.elapsed_time(e1)
+    if world > 1:
+        t = torch.tensor([ms], device="cuda", dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms = float(t.item())
+    return ms / steps
+
+
+def run_ours(a):
+    import torch
+    import torch.distributed as dist
+    from pathtracing_b200 import synth
+    from pathtracing_b200.scene import GpuScene
+
+    rank, world, local = dist_env()
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device — pathtracing_b200 has no CPU fallback")
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    desc = make_scene(a.mesh, a.tris)
+    t0 = time.perf_counter()
+    scene = GpuScene(desc, a.bvh, device=local)
+    build_s = time.perf_counter() - t0
+    lo, hi = scene.bounds()
+    n = a.rays
+    rays_np = synth.random_rays(n, lo, hi, seed=7 + rank)   # weak scaling: every rank traces its own n rays
+    host_rays = torch.empty(n * 32, dtype=torch.uint8).pin_memory()
+    host_rays.numpy()[:] = rays_np.view(np.uint8)
+    host_hits = torch.empty(n * 16, dtype=torch.uint8).pin_memory()
+    d_rays = host_rays.cuda(non_blocking=True)
+    d_hits = torch.empty(n * 16, dtype=torch.uint8, device="cuda")
+    torch.cuda.synchronize()
+    stream = torch.cuda.current_stream().cuda_stream
+
+    def step():
+        scene.trace_closest_dev(d_rays.data_ptr(), n, d_hits.data_ptr(), None, stream)
+
+    sampler = ClockSampler(local) if rank == 0 else None
+    ms = time_dev(step, a.steps, a.warmup, torch, dist, world)
+    clocks = sampler.stop() if sampler else None
+    value = world * n / (ms * 1e-3) / 1e6
+
+    # end to end through the host-buffer C-ABI call (H2D + kernel + D2H inside the timed region)
+    lib = scene.lib
+    hp, hh = host_rays.data_ptr(), host_hits.data_ptr()
+
+    def e2e_step():
+        rc = lib.pt_trace_closest(scene.h, hp, n, hh, None)
+        assert rc == 0, lib.pt_last_error()
+
+    for _ in range(max(1, min(a.warmup, 2))):
+        e2e_step()
+    if world > 1:
+        dist.barrier()
+    t0 = time.perf_counter()
+    e2e_steps = max(2, min(a.steps, 5))
+    for _ in range(e2e_steps):
+        e2e_step()
+    e2e_ms = (time.perf_counter() - t0) * 1e3 / e2e_steps
+    if world > 1:
+        t = torch.tensor([e2e_ms], device="cuda", dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        e2e_ms = float(t.item())
+    e2e_value = world * n / (e2e_ms * 1e-3) / 1e6
+    # the result really came back: hit count of the host buffer
+    hits_np = host_hits.numpy().view(np.dtype([("t", "<f4"), ("u", "<f4"), ("v", "<f4"), ("prim", "<u4")]))
+    hit_rate = float((hits_np["prim"] != 0xFFFFFFFF).mean())
+
+    if rank != 0:
+        if world > 1:
+            dist.barrier()
+            dist.destroy_process_group()
+        return
+
+    # roofline of the dominant (only) kernel: algorithmic bytes per ray from a counting build of the
+    # same traversal: 32 B ray + 16 B hit + nodes*S_node + tris*48 + instances*96
+    st = scene.trace_stats(d_rays.data_ptr(), n)
+    s_node = 64 if a.bvh == 2 else 128
+    nodes_per_ray = (st["tlas_nodes"] + st["blas_nodes"]) / n
+    tris_per_ray = st["triangles"] / n
+    inst_per_ray = st["instances"] / n
+    b_ray = 32 + 16 + nodes_per_ray * s_node + tris_per_ray * 48 + inst_per_ray * 96
+    peaks_file = ROOT / "MEASURED_PEAKS.json"
+    if peaks_file.exists():
+        peak, peak_src = json.loads(peaks_file.read_text())["hbm_gbs"], "measured (MEASURED_PEAKS.json hbm_gbs, burst copy)"
+    else:
+        peak, peak_src = 6650.0, "fallback (B200_PROFILING.md)"
+    achieved = n * b_ray / (ms * 1e-3) / 1e9
+    roofline = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": None,
+                "peak_source": peak_src, "kernel": f"k_trace_closest<{a.bvh}>", "bytes_per_ray": b_ray,
+                "nodes_per_ray": nodes_per_ray, "tris_per_ray": tris_per_ray, "instances_per_ray": inst_per_ray,
+                "note": "scene (nodes+triangles) is L2-resident at this size; DRAM traffic is rays+hits, see DESIGN.md"}
+
+    extras = {}
+    if not a.no_extras:
+        d_occ = torch.empty(n, dtype=torch.uint8, device="cuda")
+        ms_any = time_dev(lambda: scene.trace_any_dev(d_rays.data_ptr(), n, d_occ.data_ptr(), stream), max(2, a.steps // 2), 2, torch, dist, 1)
+        extras[f"any_hit_bvh{a.bvh}_mrays"] = n / (ms_any * 1e-3) / 1e6
+        other = 2 if a.bvh == 4 else 4
+        s2 = GpuScene(desc, other, device=local)
+        ms2 = time_dev(lambda: s2.trace_closest_dev(d_rays.data_ptr(), n, d_hits.data_ptr(), None, stream), max(2, a.steps // 2), 2, torch, dist, 1)
+        extras[f"closest_bvh{other}_mrays"] = n / (ms2 * 1e-3) / 1e6
+        s2.close()
+
+    cpu = None
+    if world == 1 and not a.no_cpu:
+        try:
+            cpu, _ = cpu_reference_rate(a, desc, rays_np[: 1 << 22])
+        except Exception as e:  # the oracle is a reported baseline, never a dependency of the product path
+            cpu = {"value": None, "unit": UNIT, "cores": os.cpu_count(), "kind": "reference", "sample": f"unavailable: {e}"}
+
+    chunks = (n + (1 << 20) - 1) >> 20
+    line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": a.steps, "warmup": a.warmup,
+            "ms_per_step": ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
+            "data": "synthetic",
+            "config": {"workload": workload_name(a), "bvh": a.bvh, "rays_per_gpu": n, "triangles": a.tris, "mesh": a.mesh,
+                       "parallelism": f"scene replicated, rays sharded x{world}, no collective",
+                       "l2": "ray+hit buffers (768 MiB per step) exceed the 126 MB L2; the 87 MB scene stays resident by design",
+                       "hit_rate": hit_rate, "scene_build_s": build_s},
+            "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": n * 32, "d2h_bytes_per_step": n * 16,
+                    "ms_per_step": e2e_ms, "api": "pt_trace_closest (pinned host buffers, 1 Mi-ray chunks over 2 streams)"},
+            "gpu_launches": a.steps, "gpu_launches_e2e": e2e_steps * chunks,
+            "clocks": clocks, "roofline": roofline, "cpu_baseline": cpu, "extras": extras}
+    print(json.dumps(line), flush=True)
+    scene.close()
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+def main():
+    a = parse()
+    if a.impl == "reference":
+        run_reference(a)
+    else:
+        run_ours(a)
+
+
+if __name__ == "__main__":
+    main()

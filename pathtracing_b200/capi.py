@@ -1,0 +1,158 @@
+"""ctypes binding of the C-ABI in include/pt_b200.h (libptb200.so).
+
+This is plumbing for tests / bench.py; the product is the shared library.  There
+is no CPU fallback: loading fails loudly when the CUDA extension has not been
+built, and scene creation fails when no CUDA device is present.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+from pathlib import Path
+
+import numpy as np
+
+_PKG = Path(__file__).resolve().parent
+LIB_PATH = _PKG / "libptb200.so"
+
+PT_MISS = 0xFFFFFFFF
+
+# ---- POD descriptors (mirror include/pt_b200.h) ------------------------------------
+
+
+class pt_texture_desc(C.Structure):
+    _fields_ = [("kind", C.c_int32), ("color", C.c_float * 3), ("color_scale", C.c_float * 3),
+                ("width", C.c_int32), ("height", C.c_int32), ("channels", C.c_int32),
+                ("pixels", C.c_void_p), ("tex_a", C.c_int32), ("tex_b", C.c_int32),
+                ("uv_scale", C.c_float * 2)]
+
+
+class pt_material_desc(C.Structure):
+    _fields_ = [("kind", C.c_int32), ("tex", C.c_int32), ("norm", C.c_int32), ("rough", C.c_int32),
+                ("metal", C.c_int32), ("alpha", C.c_int32), ("ri", C.c_float), ("albedo", C.c_float * 3),
+                ("alpha_mode", C.c_int32), ("alpha_cutoff", C.c_float)]
+
+
+class pt_medium_desc(C.Structure):
+    _fields_ = [("sigma_a", C.c_float * 3), ("sigma_s", C.c_float * 3), ("g", C.c_float),
+                ("density", C.c_float), ("Le", C.c_float * 3), ("le_density", C.c_float)]
+
+
+class pt_mesh_desc(C.Structure):
+    _fields_ = [("positions", C.c_void_p), ("normals", C.c_void_p), ("texcoords", C.c_void_p),
+                ("tangents", C.c_void_p), ("indices", C.c_void_p),
+                ("n_vertices", C.c_uint32), ("n_triangles", C.c_uint32),
+                ("material", C.c_int32), ("emissive_tex", C.c_int32), ("medium", C.c_int32)]
+
+
+class pt_light_desc(C.Structure):
+    _fields_ = [("kind", C.c_int32), ("color", C.c_float * 3), ("color_b", C.c_float * 3),
+                ("scale", C.c_float), ("dir_or_pos", C.c_float * 3), ("tex", C.c_int32),
+                ("power_func", C.c_int32)]
+
+
+class pt_camera_desc(C.Structure):
+    _fields_ = [("look_from", C.c_float * 3), ("look_at", C.c_float * 3), ("fov", C.c_float),
+                ("focus_angle", C.c_float), ("focus_distance", C.c_float), ("medium", C.c_int32),
+                ("shutter_start", C.c_float), ("shutter_end", C.c_float)]
+
+
+class pt_render_params(C.Structure):
+    _fields_ = [("width", C.c_int32), ("height", C.c_int32), ("spp", C.c_int32), ("max_depth", C.c_int32),
+                ("integrator", C.c_int32), ("sampler", C.c_int32), ("strata_x", C.c_int32),
+                ("strata_y", C.c_int32), ("filter", C.c_int32), ("filter_radius", C.c_float * 2),
+                ("filter_param", C.c_float * 2), ("seed", C.c_uint64), ("pass_begin", C.c_int32),
+                ("pass_stride", C.c_int32), ("adaptive", C.c_int32)]
+
+
+class pt_render_stats(C.Structure):
+    _fields_ = [("samples", C.c_uint64), ("closest_rays", C.c_uint64), ("shadow_rays", C.c_uint64),
+                ("kernel_launches", C.c_uint64), ("gpu_ms", C.c_double)]
+
+
+class pt_trace_stats(C.Structure):
+    _fields_ = [("rays", C.c_uint64), ("tlas_nodes", C.c_uint64), ("blas_nodes", C.c_uint64),
+                ("instances", C.c_uint64), ("triangles", C.c_uint64), ("hits", C.c_uint64)]
+
+
+RAY_DTYPE = np.dtype([("o", "<f4", 3), ("tmax", "<f4"), ("d", "<f4", 3), ("time", "<f4")])
+HIT_DTYPE = np.dtype([("t", "<f4"), ("u", "<f4"), ("v", "<f4"), ("prim", "<u4")])
+assert RAY_DTYPE.itemsize == 32 and HIT_DTYPE.itemsize == 16
+
+# enums
+TEX_SOLID, TEX_IMAGE_U8, TEX_IMAGE_F32, TEX_CHECKER, TEX_UV, TEX_NORMAL = range(6)
+MAT_DIFFUSE, MAT_DIELECTRIC, MAT_THIN_DIELECTRIC, MAT_CONDUCTOR = range(4)
+ALPHA_OPAQUE, ALPHA_BLEND, ALPHA_MASK = range(3)
+LIGHT_UNIFORM_INFINITE, LIGHT_GRADIENT_INFINITE, LIGHT_TEXTURE_INFINITE, LIGHT_DISTANT, LIGHT_POINT = range(5)
+INTEGRATOR_SIMPLE, INTEGRATOR_PATH, INTEGRATOR_VOLPATH = range(3)
+FILTER_BOX, FILTER_GAUSSIAN, FILTER_MITCHELL, FILTER_LANCZOS = range(4)
+
+EXPORTS = [
+    "pt_device_count", "pt_scene_create", "pt_scene_destroy", "pt_last_error",
+    "pt_scene_add_texture", "pt_scene_add_material", "pt_scene_add_medium", "pt_scene_add_mesh",
+    "pt_scene_add_blas", "pt_scene_add_instance", "pt_scene_add_light", "pt_scene_set_medium",
+    "pt_scene_commit", "pt_scene_bounds", "pt_trace_closest", "pt_trace_any",
+    "pt_trace_closest_dev", "pt_trace_any_dev", "pt_trace_closest_stats", "pt_render",
+    "pt_film_device_ptr", "pt_film_download", "pt_film_upload",
+]
+
+_lib = None
+
+
+class PtError(RuntimeError):
+    pass
+
+
+def load_library(path: os.PathLike | None = None) -> C.CDLL:
+    """dlopen libptb200.so and declare the signatures.  Raises if it is missing."""
+    global _lib
+    if _lib is not None and path is None:
+        return _lib
+    p = Path(path) if path else LIB_PATH
+    if not p.exists():
+        raise PtError(f"{p} not found: build the CUDA extension first (python -c 'import __graft_entry__ as g; g.build()')")
+    lib = C.CDLL(str(p))
+    vp, i, sz = C.c_void_p, C.c_int, C.c_size_t
+    lib.pt_device_count.restype = i
+    lib.pt_scene_create.restype = vp
+    lib.pt_scene_create.argtypes = [i]
+    lib.pt_scene_destroy.restype = None
+    lib.pt_scene_destroy.argtypes = [vp]
+    lib.pt_last_error.restype = C.c_char_p
+    for name, desc in (("pt_scene_add_texture", pt_texture_desc), ("pt_scene_add_material", pt_material_desc),
+                       ("pt_scene_add_medium", pt_medium_desc), ("pt_scene_add_mesh", pt_mesh_desc),
+                       ("pt_scene_add_light", pt_light_desc)):
+        f = getattr(lib, name)
+        f.restype = i
+        f.argtypes = [vp, C.POINTER(desc)]
+    lib.pt_scene_add_blas.restype = i
+    lib.pt_scene_add_blas.argtypes = [vp, C.POINTER(C.c_int32), i]
+    lib.pt_scene_add_instance.restype = i
+    lib.pt_scene_add_instance.argtypes = [vp, i, C.POINTER(C.c_float)]
+    lib.pt_scene_set_medium.restype = i
+    lib.pt_scene_set_medium.argtypes = [vp, i]
+    lib.pt_scene_commit.restype = i
+    lib.pt_scene_commit.argtypes = [vp, i, i]
+    lib.pt_scene_bounds.restype = i
+    lib.pt_scene_bounds.argtypes = [vp, C.POINTER(C.c_float), C.POINTER(C.c_float)]
+    lib.pt_trace_closest.restype = i
+    lib.pt_trace_closest.argtypes = [vp, vp, sz, vp, vp]
+    lib.pt_trace_any.restype = i
+    lib.pt_trace_any.argtypes = [vp, vp, sz, vp]
+    lib.pt_trace_closest_dev.restype = i
+    lib.pt_trace_closest_dev.argtypes = [vp, vp, sz, vp, vp, vp]
+    lib.pt_trace_any_dev.restype = i
+    lib.pt_trace_any_dev.argtypes = [vp, vp, sz, vp, vp]
+    lib.pt_trace_closest_stats.restype = i
+    lib.pt_trace_closest_stats.argtypes = [vp, vp, sz, C.POINTER(pt_trace_stats)]
+    lib.pt_render.restype = i
+    lib.pt_render.argtypes = [vp, C.POINTER(pt_camera_desc), C.POINTER(pt_render_params), i, C.POINTER(pt_render_stats)]
+    lib.pt_film_device_ptr.restype = i
+    lib.pt_film_device_ptr.argtypes = [vp, C.POINTER(vp), C.POINTER(sz)]
+    lib.pt_film_download.restype = i
+    lib.pt_film_download.argtypes = [vp, vp]
+    lib.pt_film_upload.restype = i
+    lib.pt_film_upload.argtypes = [vp, vp, i, i]
+    if path is None:
+        _lib = lib
+    return lib

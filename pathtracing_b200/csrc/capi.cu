@@ -46,104 +46,37 @@ const char* pt_last_error(void){ return get_error(); }
 
 int pt_scene_add_texture(pt_scene* s, const pt_texture_desc* d){
     PT_CHECK_OPEN(s);
-    if(!d){ set_error("null desc"); return PT_ERR_INVALID; }
-    HostTexture t;
-    t.d = *d;
-    const int ntex = (int)s->textures.size();
-    switch(d->kind){
-    case PT_TEX_SOLID: case PT_TEX_UV: case PT_TEX_NORMAL: break;
-    case PT_TEX_IMAGE_U8: case PT_TEX_IMAGE_F32: {
-        if(d->width <= 0 || d->height <= 0 || d->channels < 1 || d->channels > 4 || !d->pixels){ set_error("bad image texture"); return PT_ERR_INVALID; }
-        const size_t elems = (size_t)d->width * d->height * d->channels;
-        const size_t bytes = elems * (d->kind == PT_TEX_IMAGE_U8 ? 1 : 4);
-        t.pixels.assign((const uint8_t*)d->pixels, (const uint8_t*)d->pixels + bytes);
-        t.d.pixels = nullptr;
-        break;
-    }
-    case PT_TEX_CHECKER:
-        if(d->tex_a < 0 || d->tex_a >= ntex || d->tex_b < 0 || d->tex_b >= ntex){ set_error("checker child texture id out of range"); return PT_ERR_INVALID; }
-        break;
-    default: set_error("unknown texture kind"); return PT_ERR_INVALID;
-    }
-    s->textures.push_back(std::move(t));
-    return ntex;
+    return scene_add_texture(s, d);
 }
 
 int pt_scene_add_material(pt_scene* s, const pt_material_desc* d){
     PT_CHECK_OPEN(s);
-    if(!d){ set_error("null desc"); return PT_ERR_INVALID; }
-    const int ntex = (int)s->textures.size();
-    auto ok = [&](int id, bool required){ return (id >= 0 && id < ntex) || (!required && id < 0); };
-    switch(d->kind){
-    case PT_MAT_DIFFUSE: case PT_MAT_DIELECTRIC:
-        if(!ok(d->tex, true) || !ok(d->norm, false) || !ok(d->rough, false) || !ok(d->metal, false) || !ok(d->alpha, false)){ set_error("material texture id out of range"); return PT_ERR_INVALID; }
-        break;
-    case PT_MAT_THIN_DIELECTRIC:
-        if(!ok(d->tex, false)){ set_error("material texture id out of range"); return PT_ERR_INVALID; }
-        break;
-    case PT_MAT_CONDUCTOR: break;
-    default: set_error("unknown material kind"); return PT_ERR_INVALID;
-    }
-    s->materials.push_back(*d);
-    return (int)s->materials.size() - 1;
+    return scene_add_material(s, d);
 }
 
 int pt_scene_add_medium(pt_scene* s, const pt_medium_desc* d){
     PT_CHECK_OPEN(s);
-    if(!d){ set_error("null desc"); return PT_ERR_INVALID; }
-    s->media.push_back(*d);
-    return (int)s->media.size() - 1;
+    return scene_add_medium(s, d);
 }
 
 int pt_scene_add_mesh(pt_scene* s, const pt_mesh_desc* d){
     PT_CHECK_OPEN(s);
-    if(!d || !d->positions || !d->indices || !d->normals || !d->texcoords){ set_error("mesh needs positions, normals, texcoords and indices"); return PT_ERR_INVALID; }
-    if(d->material >= (int)s->materials.size() || d->emissive_tex >= (int)s->textures.size() || d->medium >= (int)s->media.size()){ set_error("mesh material/texture/medium id out of range"); return PT_ERR_INVALID; }
-    for(size_t i = 0; i < 3 * (size_t)d->n_triangles; i++)
-        if(d->indices[i] >= d->n_vertices){ set_error("mesh index out of range"); return PT_ERR_INVALID; }
-    HostMesh m;
-    m.d = *d;
-    m.pos.assign(d->positions, d->positions + 3 * (size_t)d->n_vertices);
-    m.nrm.assign(d->normals, d->normals + 3 * (size_t)d->n_vertices);
-    m.uv.assign(d->texcoords, d->texcoords + 2 * (size_t)d->n_vertices);
-    if(d->tangents)m.tan.assign(d->tangents, d->tangents + 3 * (size_t)d->n_vertices);
-    m.idx.assign(d->indices, d->indices + 3 * (size_t)d->n_triangles);
-    m.d.positions = m.d.normals = m.d.texcoords = m.d.tangents = nullptr; m.d.indices = nullptr;
-    s->meshes.push_back(std::move(m));
-    return (int)s->meshes.size() - 1;
+    return scene_add_mesh(s, d);
 }
 
 int pt_scene_add_blas(pt_scene* s, const int32_t* mesh_ids, int n){
     PT_CHECK_OPEN(s);
-    if(!mesh_ids || n <= 0){ set_error("a BLAS needs at least one mesh"); return PT_ERR_INVALID; }
-    HostBlas b;
-    for(int i = 0; i < n; i++){
-        if(mesh_ids[i] < 0 || mesh_ids[i] >= (int)s->meshes.size()){ set_error("mesh id out of range"); return PT_ERR_INVALID; }
-        b.meshes.push_back(mesh_ids[i]);
-    }
-    s->blas.push_back(std::move(b));
-    return (int)s->blas.size() - 1;
+    return scene_add_blas(s, mesh_ids, n);
 }
 
 int pt_scene_add_instance(pt_scene* s, int blas_id, const float* xf){
     PT_CHECK_OPEN(s);
-    if(blas_id < 0 || blas_id >= (int)s->blas.size()){ set_error("blas id out of range"); return PT_ERR_INVALID; }
-    HostInstance i;
-    i.blas = blas_id;
-    i.has_xf = xf != nullptr;
-    memset(i.xf, 0, sizeof i.xf);
-    if(xf)memcpy(i.xf, xf, sizeof i.xf);
-    else i.xf[0] = i.xf[5] = i.xf[10] = i.xf[15] = 1.0f;
-    s->instances.push_back(i);
-    return (int)s->instances.size() - 1;
+    return scene_add_instance(s, blas_id, xf);
 }
 
 int pt_scene_add_light(pt_scene* s, const pt_light_desc* d){
     PT_CHECK_OPEN(s);
-    if(!d || d->kind < 0 || d->kind > PT_LIGHT_POINT){ set_error("bad light"); return PT_ERR_INVALID; }
-    if(d->kind == PT_LIGHT_TEXTURE_INFINITE && (d->tex < 0 || d->tex >= (int)s->textures.size())){ set_error("light texture id out of range"); return PT_ERR_INVALID; }
-    s->lights.push_back(*d);
-    return (int)s->lights.size() - 1;
+    return scene_add_light(s, d);
 }
 
 int pt_scene_set_medium(pt_scene* s, int medium_id){

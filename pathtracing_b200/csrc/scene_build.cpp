@@ -1,0 +1,229 @@
+// scene_build.cpp — host-only half of the scene object: validation of the POD
+// description and packing of BLAS/TLAS into the device layout (no CUDA calls,
+// so the same code is exercised by the CPU-side emulation tests).
+#include <cstring>
+
+#include "scene_host.hpp"
+
+namespace ptb {
+
+static thread_local std::string g_err;
+void set_error(const std::string& msg){ g_err = msg; }
+const char* get_error(){ return g_err.c_str(); }
+
+int scene_add_texture(pt_scene* s, const pt_texture_desc* d){
+    if(!d){ set_error("null desc"); return PT_ERR_INVALID; }
+    HostTexture t;
+    t.d = *d;
+    const int ntex = (int)s->textures.size();
+    switch(d->kind){
+    case PT_TEX_SOLID: case PT_TEX_UV: case PT_TEX_NORMAL: break;
+    case PT_TEX_IMAGE_U8: case PT_TEX_IMAGE_F32: {
+        if(d->width <= 0 || d->height <= 0 || d->channels < 1 || d->channels > 4 || !d->pixels){ set_error("bad image texture"); return PT_ERR_INVALID; }
+        const size_t elems = (size_t)d->width * d->height * d->channels;
+        const size_t bytes = elems * (d->kind == PT_TEX_IMAGE_U8 ? 1 : 4);
+        t.pixels.assign((const uint8_t*)d->pixels, (const uint8_t*)d->pixels + bytes);
+        t.d.pixels = nullptr;
+        break;
+    }
+    case PT_TEX_CHECKER:
+        if(d->tex_a < 0 || d->tex_a >= ntex || d->tex_b < 0 || d->tex_b >= ntex){ set_error("checker child texture id out of range"); return PT_ERR_INVALID; }
+        break;
+    default: set_error("unknown texture kind"); return PT_ERR_INVALID;
+    }
+    s->textures.push_back(std::move(t));
+    return ntex;
+}
+
+int scene_add_material(pt_scene* s, const pt_material_desc* d){
+    if(!d){ set_error("null desc"); return PT_ERR_INVALID; }
+    const int ntex = (int)s->textures.size();
+    auto ok = [&](int id, bool required){ return (id >= 0 && id < ntex) || (!required && id < 0); };
+    switch(d->kind){
+    case PT_MAT_DIFFUSE: case PT_MAT_DIELECTRIC:
+        if(!ok(d->tex, true) || !ok(d->norm, false) || !ok(d->rough, false) || !ok(d->metal, false) || !ok(d->alpha, false)){ set_error("material texture id out of range"); return PT_ERR_INVALID; }
+        break;
+    case PT_MAT_THIN_DIELECTRIC:
+        if(!ok(d->tex, false)){ set_error("material texture id out of range"); return PT_ERR_INVALID; }
+        break;
+    case PT_MAT_CONDUCTOR: break;
+    default: set_error("unknown material kind"); return PT_ERR_INVALID;
+    }
+    s->materials.push_back(*d);
+    return (int)s->materials.size() - 1;
+}
+
+int scene_add_medium(pt_scene* s, const pt_medium_desc* d){
+    if(!d){ set_error("null desc"); return PT_ERR_INVALID; }
+    s->media.push_back(*d);
+    return (int)s->media.size() - 1;
+}
+
+int scene_add_mesh(pt_scene* s, const pt_mesh_desc* d){
+    if(!d || !d->positions || !d->indices || !d->normals || !d->texcoords){ set_error("mesh needs positions, normals, texcoords and indices"); return PT_ERR_INVALID; }
+    if(d->material >= (int)s->materials.size() || d->emissive_tex >= (int)s->textures.size() || d->medium >= (int)s->media.size()){ set_error("mesh material/texture/medium id out of range"); return PT_ERR_INVALID; }
+    for(size_t i = 0; i < 3 * (size_t)d->n_triangles; i++)
+        if(d->indices[i] >= d->n_vertices){ set_error("mesh index out of range"); return PT_ERR_INVALID; }
+    HostMesh m;
+    m.d = *d;
+    m.pos.assign(d->positions, d->positions + 3 * (size_t)d->n_vertices);
+    m.nrm.assign(d->normals, d->normals + 3 * (size_t)d->n_vertices);
+    m.uv.assign(d->texcoords, d->texcoords + 2 * (size_t)d->n_vertices);
+    if(d->tangents)m.tan.assign(d->tangents, d->tangents + 3 * (size_t)d->n_vertices);
+    m.idx.assign(d->indices, d->indices + 3 * (size_t)d->n_triangles);
+    m.d.positions = m.d.normals = m.d.texcoords = m.d.tangents = nullptr; m.d.indices = nullptr;
+    s->meshes.push_back(std::move(m));
+    return (int)s->meshes.size() - 1;
+}
+
+int scene_add_blas(pt_scene* s, const int32_t* mesh_ids, int n){
+    if(!mesh_ids || n <= 0){ set_error("a BLAS needs at least one mesh"); return PT_ERR_INVALID; }
+    HostBlas b;
+    for(int i = 0; i < n; i++){
+        if(mesh_ids[i] < 0 || mesh_ids[i] >= (int)s->meshes.size()){ set_error("mesh id out of range"); return PT_ERR_INVALID; }
+        b.meshes.push_back(mesh_ids[i]);
+    }
+    s->blas.push_back(std::move(b));
+    return (int)s->blas.size() - 1;
+}
+
+int scene_add_instance(pt_scene* s, int blas_id, const float* xf){
+    if(blas_id < 0 || blas_id >= (int)s->blas.size()){ set_error("blas id out of range"); return PT_ERR_INVALID; }
+    HostInstance i;
+    i.blas = blas_id;
+    i.has_xf = xf != nullptr;
+    memset(i.xf, 0, sizeof i.xf);
+    if(xf)memcpy(i.xf, xf, sizeof i.xf);
+    else i.xf[0] = i.xf[5] = i.xf[10] = i.xf[15] = 1.0f;
+    s->instances.push_back(i);
+    return (int)s->instances.size() - 1;
+}
+
+int scene_add_light(pt_scene* s, const pt_light_desc* d){
+    if(!d || d->kind < 0 || d->kind > PT_LIGHT_POINT){ set_error("bad light"); return PT_ERR_INVALID; }
+    if(d->kind == PT_LIGHT_TEXTURE_INFINITE && (d->tex < 0 || d->tex >= (int)s->textures.size())){ set_error("light texture id out of range"); return PT_ERR_INVALID; }
+    s->lights.push_back(*d);
+    return (int)s->lights.size() - 1;
+}
+
+// BLAS builds (Model::BuildBlas, Model.hpp:41-60), TLAS build (Scene::BuildTlas,
+// Scene.hpp:20-24) and packing into one node array / one triangle array.
+int pack_traversal(pt_scene* s, int width, PackedTraversal& P){
+    if(width != 2 && width != 4){ set_error("bvh_width must be 2 or 4"); return PT_ERR_INVALID; }
+    if(s->instances.empty()){ set_error("scene has no instances"); return PT_ERR_INVALID; }
+    std::vector<Bvh2Node>& n2 = P.n2;
+    std::vector<Bvh4Node>& n4 = P.n4;
+    std::vector<Tri>& tris = P.tris;
+
+    // ---- BLASes ---------------------------------------------------------------------
+    for(HostBlas& hb : s->blas){
+        hb.n_tris = 0;
+        hb.tri_mesh_base.clear();
+        for(int mi : hb.meshes){ hb.tri_mesh_base.push_back(hb.n_tris); hb.n_tris += s->meshes[mi].d.n_triangles; }
+        if(hb.n_tris == 0){ set_error("empty BLAS"); return PT_ERR_INVALID; }
+        if((uint64_t)tris.size() + hb.n_tris >= 0x7FFFFFFFull){ set_error("too many triangles"); return PT_ERR_INVALID; }
+        // per-triangle data in original (BLAS-wide) order
+        std::vector<Box> boxes(hb.n_tris);
+        std::vector<Tri> src(hb.n_tris);
+        uint32_t g = 0;
+        for(size_t k = 0; k < hb.meshes.size(); k++){
+            const int mi = hb.meshes[k];
+            const HostMesh& m = s->meshes[mi];
+            uint32_t flags = 0;
+            if(m.d.material >= 0){
+                const pt_material_desc& md = s->materials[m.d.material];
+                const bool tester = md.kind == PT_MAT_DIFFUSE || md.kind == PT_MAT_DIELECTRIC;
+                if(tester && md.alpha_mode != PT_ALPHA_OPAQUE){
+                    flags |= TRI_ALPHA_PATH;     // HasAlpha(), Material.hpp:330-332
+                    bool can_be_transparent = md.alpha >= 0;
+                    if(!can_be_transparent && md.tex >= 0){
+                        const pt_texture_desc& td = s->textures[md.tex].d;
+                        // Texture::alpha() is 1 unless an image has 4 channels (Texture.cpp:48-62)
+                        can_be_transparent = (td.kind == PT_TEX_IMAGE_U8 || td.kind == PT_TEX_IMAGE_F32 || td.kind == PT_TEX_CHECKER) && (td.kind == PT_TEX_CHECKER || td.channels == 4);
+                    }
+                    if(can_be_transparent)flags |= TRI_ALPHA_TEX;
+                }
+            }
+            for(uint32_t t = 0; t < m.d.n_triangles; t++, g++){
+                const uint32_t i0 = m.idx[3 * (size_t)t], i1 = m.idx[3 * (size_t)t + 1], i2 = m.idx[3 * (size_t)t + 2];
+                const float* p0 = &m.pos[3 * (size_t)i0]; const float* p1 = &m.pos[3 * (size_t)i1]; const float* p2 = &m.pos[3 * (size_t)i2];
+                Box bx = box_empty();
+                box_grow(bx, p0); box_grow(bx, p1); box_grow(bx, p2);   // TriangleShape::BoundingBox, Shape.cpp:270-276
+                boxes[g] = bx;
+                Tri& T = src[g];
+                for(int a = 0; a < 3; a++){ T.v0[a] = p0[a]; T.e1[a] = p1[a] - p0[a]; T.e2[a] = p2[a] - p0[a]; }
+                T.prim = g; T.mesh = (uint32_t)mi; T.flags = flags;
+            }
+        }
+        BinaryBvh bb = build_binary_bvh(boxes.data(), hb.n_tris);
+        FlatBvh fb = flatten_bvh(bb, width);
+        hb.tri_base = (uint32_t)tris.size();
+        hb.bounds = fb.bounds;
+        const uint32_t node_base = width == 2 ? (uint32_t)n2.size() : (uint32_t)n4.size();
+        auto rebase = [&](uint32_t ref) -> uint32_t{
+            if(ref == REF_EMPTY)return ref;
+            if(ref & REF_LEAF)return REF_LEAF | ((ref & ~REF_LEAF) + hb.tri_base);
+            return ref + node_base;
+        };
+        hb.root = rebase(fb.root);
+        if(width == 2){
+            for(Bvh2Node nd : fb.n2){ nd.ref0 = rebase(nd.ref0); nd.ref1 = rebase(nd.ref1); n2.push_back(nd); }
+        } else{
+            for(Bvh4Node nd : fb.n4){ for(int k = 0; k < 4; k++)nd.ref[k] = rebase(nd.ref[k]); n4.push_back(nd); }
+        }
+        for(uint32_t i = 0; i < hb.n_tris; i++){
+            Tri T = src[fb.order[i]];
+            if(fb.leaf_last[i])T.flags |= TRI_LAST;
+            tris.push_back(T);
+        }
+    }
+
+    // ---- TLAS -----------------------------------------------------------------------
+    const uint32_t ni = (uint32_t)s->instances.size();
+    std::vector<Box> iboxes(ni);
+    for(uint32_t i = 0; i < ni; i++){
+        const HostInstance& hi = s->instances[i];
+        if(hi.blas < 0 || hi.blas >= (int)s->blas.size()){ set_error("instance refers to an unknown BLAS"); return PT_ERR_INVALID; }
+        const Box& bb = s->blas[hi.blas].bounds;
+        iboxes[i] = hi.has_xf ? transform_box(hi.xf, bb) : bb;
+    }
+    BinaryBvh tb = build_binary_bvh(iboxes.data(), ni);
+    FlatBvh tf = flatten_bvh(tb, width);
+    s->bounds = tf.bounds;
+    const uint32_t tnode_base = width == 2 ? (uint32_t)n2.size() : (uint32_t)n4.size();
+    auto trebase = [&](uint32_t ref) -> uint32_t{
+        if(ref == REF_EMPTY || (ref & REF_LEAF))return ref;
+        return ref + tnode_base;
+    };
+    if(width == 2){
+        for(Bvh2Node nd : tf.n2){ nd.ref0 = trebase(nd.ref0); nd.ref1 = trebase(nd.ref1); n2.push_back(nd); }
+    } else{
+        for(Bvh4Node nd : tf.n4){ for(int k = 0; k < 4; k++)nd.ref[k] = trebase(nd.ref[k]); n4.push_back(nd); }
+    }
+    std::vector<Instance>& insts = P.insts;
+    insts.assign(ni, Instance());
+    for(uint32_t k = 0; k < ni; k++){
+        const uint32_t id = tf.order[k];
+        const HostInstance& hi = s->instances[id];
+        const HostBlas& hb = s->blas[hi.blas];
+        Instance& I = insts[k];
+        memset(&I, 0, sizeof I);
+        float inv[16];
+        if(hi.has_xf)mat4_inverse(hi.xf, inv);   // TransformedPrimitive ctor, Primitive.hpp:40
+        else{ memset(inv, 0, sizeof inv); inv[0] = inv[5] = inv[10] = inv[15] = 1.0f; }
+        for(int c = 0; c < 4; c++)for(int r = 0; r < 3; r++)I.inv[c * 3 + r] = inv[c * 4 + r];
+        I.root = hb.root;
+        I.flags = (hi.has_xf ? INST_XF : 0u) | (tf.leaf_last[k] ? INST_LAST : 0u);
+        I.id = id;
+        I.blas = (uint32_t)hi.blas;
+        for(int a = 0; a < 3; a++)I.blo[a] = hb.bounds.lo[a];
+        I.bhi0 = hb.bounds.hi[0]; I.bhi12[0] = hb.bounds.hi[1]; I.bhi12[1] = hb.bounds.hi[2];
+    }
+
+    P.tlas_root = trebase(tf.root);
+    P.bounds = tf.bounds;
+    P.inst_order = tf.order;
+    return PT_OK;
+}
+
+} // namespace ptb

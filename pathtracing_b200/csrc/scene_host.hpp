@@ -88,6 +88,26 @@ struct pt_scene {
 
 namespace ptb {
 
+struct PackedTraversal {
+    std::vector<Bvh2Node> n2;
+    std::vector<Bvh4Node> n4;
+    std::vector<Tri> tris;
+    std::vector<Instance> insts;      // TLAS leaf order
+    std::vector<uint32_t> inst_order; // leaf order -> instance id
+    uint32_t tlas_root = REF_EMPTY;
+    Box bounds = box_empty();
+};
+
+// scene_build.cpp (host only)
+int scene_add_texture(pt_scene* s, const pt_texture_desc* d);
+int scene_add_material(pt_scene* s, const pt_material_desc* d);
+int scene_add_medium(pt_scene* s, const pt_medium_desc* d);
+int scene_add_mesh(pt_scene* s, const pt_mesh_desc* d);
+int scene_add_blas(pt_scene* s, const int32_t* mesh_ids, int n);
+int scene_add_instance(pt_scene* s, int blas_id, const float* xf);
+int scene_add_light(pt_scene* s, const pt_light_desc* d);
+int pack_traversal(pt_scene* s, int width, PackedTraversal& out);
+
 void set_error(const std::string& msg);
 const char* get_error();
 bool cuda_ok(int err, const char* what);     // records the message on failure

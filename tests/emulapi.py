@@ -1,0 +1,121 @@
+"""TEST INFRASTRUCTURE ONLY — ctypes binding of tests/emul/libptemul.so: the product's
+packed scene + device traversal header compiled for the host (see tests/emul/emul.cpp)."""
+from __future__ import annotations
+
+import ctypes as C
+import subprocess
+from pathlib import Path
+
+import numpy as np
+
+from pathtracing_b200 import capi
+from pathtracing_b200.capi import pt_light_desc, pt_material_desc, pt_medium_desc, pt_mesh_desc, pt_texture_desc
+
+_DIR = Path(__file__).resolve().parent / "emul"
+_lib = None
+
+
+def load():
+    global _lib
+    if _lib is not None:
+        return _lib
+    subprocess.run(["make", "-s", "-C", str(_DIR)], check=True)
+    lib = C.CDLL(str(_DIR / "libptemul.so"))
+    vp, i, sz = C.c_void_p, C.c_int, C.c_size_t
+    lib.emul_scene_create.restype = vp
+    lib.emul_scene_destroy.argtypes = [vp]
+    lib.emul_last_error.restype = C.c_char_p
+    for name, desc in (("emul_scene_add_texture", pt_texture_desc), ("emul_scene_add_material", pt_material_desc),
+                       ("emul_scene_add_medium", pt_medium_desc), ("emul_scene_add_mesh", pt_mesh_desc),
+                       ("emul_scene_add_light", pt_light_desc)):
+        f = getattr(lib, name)
+        f.restype = i
+        f.argtypes = [vp, C.POINTER(desc)]
+    lib.emul_scene_add_blas.restype = i
+    lib.emul_scene_add_blas.argtypes = [vp, C.POINTER(C.c_int32), i]
+    lib.emul_scene_add_instance.restype = i
+    lib.emul_scene_add_instance.argtypes = [vp, i, C.POINTER(C.c_float)]
+    lib.emul_scene_commit.restype = i
+    lib.emul_scene_commit.argtypes = [vp, i]
+    lib.emul_scene_bounds.argtypes = [vp, C.POINTER(C.c_float), C.POINTER(C.c_float)]
+    lib.emul_node_count.argtypes = [vp]
+    lib.emul_trace_closest.restype = i
+    lib.emul_trace_closest.argtypes = [vp, vp, sz, vp, vp, vp]
+    lib.emul_trace_any.restype = i
+    lib.emul_trace_any.argtypes = [vp, vp, sz, vp]
+    _lib = lib
+    return lib
+
+
+class EmulScene:
+    def __init__(self, desc, bvh_width=4):
+        self.lib = load()
+        self.h = self.lib.emul_scene_create()
+        self.desc = desc
+        desc.replay(self)
+        self._ck(self.lib.emul_scene_commit(self.h, bvh_width))
+
+    def _ck(self, rc):
+        if rc < 0:
+            raise RuntimeError(f"emul error {rc}: {self.lib.emul_last_error().decode()}")
+        return rc
+
+    def add_texture(self, d):
+        return self._ck(self.lib.emul_scene_add_texture(self.h, C.byref(d)))
+
+    def add_material(self, d):
+        return self._ck(self.lib.emul_scene_add_material(self.h, C.byref(d)))
+
+    def add_medium(self, d):
+        return self._ck(self.lib.emul_scene_add_medium(self.h, C.byref(d)))
+
+    def add_mesh(self, d):
+        return self._ck(self.lib.emul_scene_add_mesh(self.h, C.byref(d)))
+
+    def add_blas(self, ids):
+        return self._ck(self.lib.emul_scene_add_blas(self.h, ids.ctypes.data_as(C.POINTER(C.c_int32)), len(ids)))
+
+    def add_instance(self, blas_id, xf):
+        p = xf.ctypes.data_as(C.POINTER(C.c_float)) if xf is not None else None
+        return self._ck(self.lib.emul_scene_add_instance(self.h, blas_id, p))
+
+    def add_light(self, d):
+        return self._ck(self.lib.emul_scene_add_light(self.h, C.byref(d)))
+
+    def set_medium(self, m):
+        return 0
+
+    def bounds(self):
+        lo, hi = (C.c_float * 3)(), (C.c_float * 3)()
+        self.lib.emul_scene_bounds(self.h, lo, hi)
+        return np.array(lo[:], np.float32), np.array(hi[:], np.float32)
+
+    def node_count(self):
+        return self.lib.emul_node_count(self.h)
+
+    def trace_closest(self, rays, want_inst=True):
+        rays = np.ascontiguousarray(rays, dtype=capi.RAY_DTYPE)
+        hits = np.empty(len(rays), dtype=capi.HIT_DTYPE)
+        inst = np.empty(len(rays), dtype=np.uint32) if want_inst else None
+        stats = np.zeros(4, np.uint64)
+        self._ck(self.lib.emul_trace_closest(self.h, rays.ctypes.data, len(rays), hits.ctypes.data,
+                                             inst.ctypes.data if want_inst else None, stats.ctypes.data))
+        self.last_stats = dict(zip(("tlas_nodes", "blas_nodes", "instances", "triangles"), (int(x) for x in stats)))
+        return hits, inst
+
+    def trace_any(self, rays):
+        rays = np.ascontiguousarray(rays, dtype=capi.RAY_DTYPE)
+        occ = np.empty(len(rays), dtype=np.uint8)
+        self._ck(self.lib.emul_trace_any(self.h, rays.ctypes.data, len(rays), occ.ctypes.data))
+        return occ
+
+    def close(self):
+        if self.h:
+            self.lib.emul_scene_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass

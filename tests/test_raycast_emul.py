@@ -1,0 +1,80 @@
+"""CPU tier: the product's host BVH build + flattening + the device traversal header
+compiled for the host (tests/emul) against the UNMODIFIED reference (oracle/_ref,
+-ffp-contract=off build).  Bit-exact primitive ids, instance ids and hit distances."""
+import numpy as np
+import pytest
+
+from conftest import needs_ref
+from pathtracing_b200 import synth
+
+
+def _cmp(desc, width, n_rays=40000, tmax=np.inf, seed=7):
+    from emulapi import EmulScene
+    from oracle.refapi import RefScene
+    ref = RefScene(desc, width, id_mode=True)
+    em = EmulScene(desc, width)
+    lo, hi = ref.bounds()
+    elo, ehi = em.bounds()
+    assert np.array_equal(lo, elo) and np.array_equal(hi, ehi)
+    rays = synth.random_rays(n_rays, lo, hi, seed=seed, tmax=tmax)
+    rh, ri = ref.trace_closest(rays, want_inst=True)
+    eh, ei = em.trace_closest(rays)
+    assert np.array_equal(rh["prim"], eh["prim"])
+    assert np.array_equal(rh["t"].view(np.uint32), eh["t"].view(np.uint32))
+    assert np.array_equal(ri, ei)
+    assert np.array_equal(ref.trace_any(rays), em.trace_any(rays))
+    return (rh["prim"] != 0xFFFFFFFF).mean()
+
+
+@needs_ref
+@pytest.mark.parametrize("width", [2, 4])
+@pytest.mark.parametrize("opaque", [False, True])
+def test_soup_bit_exact(width, opaque):
+    assert _cmp(synth.soup_scene(20000, opaque=opaque), width) > 0.05
+
+
+@needs_ref
+@pytest.mark.parametrize("width", [2, 4])
+def test_terrain_bit_exact(width):
+    assert _cmp(synth.terrain_scene(101, 81), width) > 0.2
+
+
+@needs_ref
+@pytest.mark.parametrize("width", [2, 4])
+def test_instances_bit_exact(width):
+    d = synth.instanced_scene(2, 16)
+    assert _cmp(d, width) > 0.1
+    _cmp(d, width, tmax=1.5, seed=11)
+
+
+@needs_ref
+@pytest.mark.parametrize("width", [2, 4])
+@pytest.mark.parametrize("n", [1, 2, 3, 5])
+def test_tiny_blas(width, n):
+    """root is a leaf (n<=2) or a partially filled cluster"""
+    _cmp(synth.soup_scene(n, seed=5), width, n_rays=2000)
+    d = synth.soup_scene(n, seed=5)
+    d.instances.clear()
+    d.instance(0, np.diag([2.0, 0.5, 1.5, 1.0]))
+    _cmp(d, width, n_rays=2000)
+
+
+@needs_ref
+def test_degenerate_identical_triangles():
+    """many coincident centroids: SAH cannot split, big leaves"""
+    pos = np.tile(np.array([[0, 0, 0], [1, 0, 0], [0, 1, 0]], np.float32), (40, 1))
+    idx = np.arange(120, dtype=np.uint32).reshape(-1, 3)
+    from pathtracing_b200.scene import SceneDesc
+    d = SceneDesc()
+    m = d.diffuse(d.solid((1, 1, 1)))
+    d.instance(d.add_blas([d.mesh(pos, idx, material=m)]))
+    from emulapi import EmulScene
+    from oracle.refapi import RefScene
+    for width in (2, 4):
+        ref, em = RefScene(d, width, id_mode=True), EmulScene(d, width)
+        rays = synth.random_rays(2000, (-0.5, -0.5, -1), (1.5, 1.5, 1))
+        rh, _ = ref.trace_closest(rays)
+        eh, _ = em.trace_closest(rays)
+        # all 40 triangles tie exactly: the LAST one tested wins (t == max is accepted)
+        assert np.array_equal(rh["prim"], eh["prim"])
+        assert np.array_equal(rh["t"].view(np.uint32), eh["t"].view(np.uint32))
