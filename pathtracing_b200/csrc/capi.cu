@@ -134,7 +134,7 @@ int pt_trace_closest(pt_scene* s, const pt_ray* rays, size_t n, pt_hit* hits, ui
         pt_hit* dh = (pt_hit*)b.stage_hits + off;
         uint32_t* di = (uint32_t*)b.stage_inst + off;
         if(!cuda_ok(cudaMemcpyAsync(dr, rays + off, m * sizeof(pt_ray), cudaMemcpyHostToDevice, st[k]), "H2D rays"))return PT_ERR_CUDA;
-        rc = launch_trace_closest(s->dev, dr, m, dh, inst ? di : nullptr, st[k]);
+        rc = launch_trace_closest(s, dr, m, dh, inst ? di : nullptr, st[k]);
         if(rc != PT_OK)return rc;
         if(!cuda_ok(cudaMemcpyAsync(hits + off, dh, m * sizeof(pt_hit), cudaMemcpyDeviceToHost, st[k]), "D2H hits"))return PT_ERR_CUDA;
         if(inst && !cuda_ok(cudaMemcpyAsync(inst + off, di, m * sizeof(uint32_t), cudaMemcpyDeviceToHost, st[k]), "D2H inst"))return PT_ERR_CUDA;
@@ -157,7 +157,7 @@ int pt_trace_any(pt_scene* s, const pt_ray* rays, size_t n, uint8_t* occluded){
         pt_ray* dr = (pt_ray*)b.stage_rays + off;
         uint8_t* dc = (uint8_t*)b.stage_occ + off;
         if(!cuda_ok(cudaMemcpyAsync(dr, rays + off, m * sizeof(pt_ray), cudaMemcpyHostToDevice, st[k]), "H2D rays"))return PT_ERR_CUDA;
-        rc = launch_trace_any(s->dev, dr, m, dc, st[k]);
+        rc = launch_trace_any(s, dr, m, dc, st[k]);
         if(rc != PT_OK)return rc;
         if(!cuda_ok(cudaMemcpyAsync(occluded + off, dc, m, cudaMemcpyDeviceToHost, st[k]), "D2H occ"))return PT_ERR_CUDA;
     }
@@ -168,13 +168,13 @@ int pt_trace_any(pt_scene* s, const pt_ray* rays, size_t n, uint8_t* occluded){
 int pt_trace_closest_dev(pt_scene* s, const void* d_rays, size_t n, void* d_hits, void* d_inst, void* stream){
     PT_CHECK_READY(s);
     if(n && (!d_rays || !d_hits)){ set_error("null buffer"); return PT_ERR_INVALID; }
-    return launch_trace_closest(s->dev, d_rays, n, d_hits, d_inst, stream);
+    return launch_trace_closest(s, d_rays, n, d_hits, d_inst, stream);
 }
 
 int pt_trace_any_dev(pt_scene* s, const void* d_rays, size_t n, void* d_occ, void* stream){
     PT_CHECK_READY(s);
     if(n && (!d_rays || !d_occ)){ set_error("null buffer"); return PT_ERR_INVALID; }
-    return launch_trace_any(s->dev, d_rays, n, d_occ, stream);
+    return launch_trace_any(s, d_rays, n, d_occ, stream);
 }
 
 int pt_trace_closest_stats(pt_scene* s, const void* d_rays, size_t n, pt_trace_stats* out){
@@ -182,7 +182,7 @@ int pt_trace_closest_stats(pt_scene* s, const void* d_rays, size_t n, pt_trace_s
     if(!out || (n && !d_rays)){ set_error("null buffer"); return PT_ERR_INVALID; }
     cudaStream_t st = (cudaStream_t)s->stream;
     if(!cuda_ok(cudaMemsetAsync(s->buf.stats, 0, 64, st), "memset"))return PT_ERR_CUDA;
-    int rc = launch_trace_stats(s->dev, d_rays, n, s->buf.stats, st);
+    int rc = launch_trace_stats(s, d_rays, n, s->buf.stats, st);
     if(rc != PT_OK)return rc;
     unsigned long long h[8];
     if(!cuda_ok(cudaMemcpyAsync(h, s->buf.stats, 64, cudaMemcpyDeviceToHost, st), "D2H stats") || !cuda_ok(cudaStreamSynchronize(st), "sync"))return PT_ERR_CUDA;

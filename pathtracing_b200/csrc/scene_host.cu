@@ -32,7 +32,7 @@ void scene_free_device(pt_scene* s){
     DeviceBuffers& b = s->buf;
     void** ptrs[] = { &b.n2, &b.n4, &b.tris, &b.inst, &b.meshes, &b.blas_info, &b.inst_shade, &b.vtx_pos, &b.vtx_nrm, &b.vtx_uv, &b.vtx_tan,
         &b.indices, &b.tri_light, &b.textures, &b.texels, &b.materials, &b.media, &b.lights, &b.light_cdf, &b.env_cdf, &b.film, &b.work,
-        &b.stage_rays, &b.stage_hits, &b.stage_inst, &b.stage_occ, &b.stats, &b.tri_mesh, &b.inst_light_base, &b.sampler_lights, &b.inf_lights };
+        &b.stage_rays, &b.stage_hits, &b.stage_inst, &b.stage_occ, &b.stats, &b.tri_mesh, &b.inst_light_base, &b.sampler_lights, &b.inf_lights, &b.cursors };
     for(void** p : ptrs){ if(*p){ cudaFree(*p); *p = nullptr; } }
     b.work_bytes = 0; b.stage_cap = 0;
 }
@@ -73,7 +73,8 @@ int scene_commit(pt_scene* s, int width, int light_sampler){
     if(!cuda_ok(cudaStreamCreateWithFlags(&st, cudaStreamNonBlocking), "cudaStreamCreate") ||
        !cuda_ok(cudaStreamCreateWithFlags(&st2, cudaStreamNonBlocking), "cudaStreamCreate")){ scene_free_device(s); return PT_ERR_CUDA; }
     s->stream = st; s->stream2 = st2;
-    if(!cuda_ok(cudaMalloc(&b.stats, 64), "cudaMalloc stats")){ scene_free_device(s); return PT_ERR_CUDA; }
+    if(!cuda_ok(cudaMalloc(&b.stats, 64), "cudaMalloc stats") ||
+       !cuda_ok(cudaMalloc(&b.cursors, kCursorRing * sizeof(unsigned long long)), "cudaMalloc cursors")){ scene_free_device(s); return PT_ERR_CUDA; }
     s->committed = true;
     return PT_OK;
 }

@@ -57,7 +57,10 @@ struct DeviceBuffers {
     void* stage_rays = nullptr; void* stage_hits = nullptr; void* stage_inst = nullptr; void* stage_occ = nullptr;
     size_t stage_cap = 0;
     void* stats = nullptr;
+    void* cursors = nullptr;      // ring of ray-dispenser cursors for the persistent kernels
 };
+
+constexpr unsigned kCursorRing = 256;
 
 } // namespace ptb
 
@@ -84,6 +87,7 @@ struct pt_scene {
     void* stream = nullptr;       // internal stream for the host-buffer entry points
     void* stream2 = nullptr;
     void* ev[4] = { nullptr, nullptr, nullptr, nullptr };
+    unsigned cursor_next = 0;
 };
 
 namespace ptb {
@@ -116,9 +120,9 @@ int scene_commit(pt_scene* s, int width, int light_sampler);
 void scene_free_device(pt_scene* s);
 
 // trace.cu
-int launch_trace_closest(const DevScene& S, const void* d_rays, size_t n, void* d_hits, void* d_inst, void* stream);
-int launch_trace_any(const DevScene& S, const void* d_rays, size_t n, void* d_occ, void* stream);
-int launch_trace_stats(const DevScene& S, const void* d_rays, size_t n, void* d_counters /* 6 x u64 */, void* stream);
+int launch_trace_closest(pt_scene* s, const void* d_rays, size_t n, void* d_hits, void* d_inst, void* stream);
+int launch_trace_any(pt_scene* s, const void* d_rays, size_t n, void* d_occ, void* stream);
+int launch_trace_stats(pt_scene* s, const void* d_rays, size_t n, void* d_counters /* 6 x u64 */, void* stream);
 
 // render.cu
 int render_passes(pt_scene* s, const pt_camera_desc* cam, const pt_render_params* rp, int clear, pt_render_stats* stats);

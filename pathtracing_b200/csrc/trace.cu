@@ -1,10 +1,13 @@
 // trace.cu — ray-cast kernels: batched Scene::Intersect / Scene::IntersectPred
-// (Scene.cpp:4-6,31-33) for BVH2 and BVH4, one thread per ray.
+// (Scene.cpp:4-6,31-33) for BVH2 and BVH4.
 //
-// Grid: ceil(n / 128) CTAs of 128 threads (4 warps); with <= 64 registers this
-// gives 16 CTAs = 64 warps per SM, i.e. full occupancy to hide the dependent
-// node-fetch latency that bounds incoherent traversal.  Rays are read as two
-// 128-bit loads, hits written as one 128-bit store.
+// Persistent warps: the grid is (#SMs x resident CTAs) and never larger; every
+// warp pulls chunks of kChunk consecutive rays from a global cursor and keeps
+// its 32 lanes busy by handing the next ray of the chunk to a lane the moment
+// its previous ray finishes (trace.cuh: one trav_step round per loop
+// iteration).  Rays are read as two 128-bit loads, hits written as one 128-bit
+// store.  No shared memory is used, so the whole 228 KB of the SM is L1 for
+// the upper tree levels and the per-lane stacks.
 #include <cstdio>
 #include "scene_host.hpp"
 #include "trace.cuh"
@@ -12,52 +15,78 @@
 namespace ptb {
 
 constexpr int kTraceBlock = 128;
+constexpr unsigned kChunk = 64;        // rays per cursor grab (one atomic per 64 rays)
+constexpr uint32_t kNoRay = 0xFFFFFFFFu;
 
-template <int WIDTH>
-__global__ void __launch_bounds__(kTraceBlock) k_trace_closest(DevScene S, const float4* __restrict__ rays, size_t n, float4* __restrict__ hits, uint32_t* __restrict__ inst){
-    const size_t i = (size_t)blockIdx.x * kTraceBlock + threadIdx.x;
-    if(i >= n)return;
-    const float4 a = __ldg(rays + 2 * i), b = __ldg(rays + 2 * i + 1);
-    RayCtx r;
-    make_ray(r, a.x, a.y, a.z, b.x, b.y, b.z);
-    HitRec h;
-    trace_scene<WIDTH, false, false>(S, r, a.w, h, nullptr, NoAlpha());
-    hits[i] = make_float4(h.t, h.u, h.v, __uint_as_float(h.prim));
-    if(inst)inst[i] = h.inst;
+// Warp-level ray dispenser.  base/avail are warp-uniform.
+struct RayFeed {
+    unsigned long long base;   // next ray of the current chunk
+    unsigned avail;            // rays left in the current chunk
+    bool exhausted;
+};
+
+__device__ __forceinline__ void feed_grab(RayFeed& f, unsigned long long* cursor, size_t n, unsigned lane){
+    unsigned long long b = 0;
+    if(lane == 0)b = atomicAdd(cursor, (unsigned long long)kChunk);
+    b = __shfl_sync(0xffffffffu, b, 0);
+    if(b >= n){ f.exhausted = true; f.avail = 0; return; }
+    f.base = b;
+    const unsigned long long left = n - b;
+    f.avail = left < kChunk ? (unsigned)left : kChunk;
 }
 
-template <int WIDTH>
-__global__ void __launch_bounds__(kTraceBlock) k_trace_any(DevScene S, const float4* __restrict__ rays, size_t n, uint8_t* __restrict__ occ){
-    const size_t i = (size_t)blockIdx.x * kTraceBlock + threadIdx.x;
-    if(i >= n)return;
-    const float4 a = __ldg(rays + 2 * i), b = __ldg(rays + 2 * i + 1);
-    RayCtx r;
-    make_ray(r, a.x, a.y, a.z, b.x, b.y, b.z);
-    HitRec h;
-    const bool o = trace_scene<WIDTH, true, false>(S, r, a.w, h, nullptr, NoAlpha());
-    occ[i] = o ? 1 : 0;
-}
-
-// counting build of the same closest-hit traversal (SURVEY.md §8d)
-template <int WIDTH>
-__global__ void __launch_bounds__(kTraceBlock) k_trace_stats(DevScene S, const float4* __restrict__ rays, size_t n, unsigned long long* __restrict__ out){
-    const size_t i = (size_t)blockIdx.x * kTraceBlock + threadIdx.x;
+template <int WIDTH, bool ANY, bool STATS>
+__global__ void __launch_bounds__(kTraceBlock) k_trace(DevScene S, const float4* __restrict__ rays, size_t n,
+                                                       float4* __restrict__ hits, uint32_t* __restrict__ inst, uint8_t* __restrict__ occ,
+                                                       unsigned long long* __restrict__ cursor, unsigned long long* __restrict__ stats){
+    uint2 stack[kStack];
+    TravState s;
+    s.flags = TF_DONE;
+    size_t idx = (size_t)-1;
+    const unsigned lane = threadIdx.x & 31u;
+    const unsigned lt = (1u << lane) - 1u;
+    RayFeed feed = { 0, 0, false };
     TraceCounters c = { 0, 0, 0, 0 };
     unsigned long long hitc = 0;
-    if(i < n){
-        const float4 a = __ldg(rays + 2 * i), b = __ldg(rays + 2 * i + 1);
-        RayCtx r;
-        make_ray(r, a.x, a.y, a.z, b.x, b.y, b.z);
-        HitRec h;
-        if(trace_scene<WIDTH, false, true>(S, r, a.w, h, &c, NoAlpha()))hitc = 1;
+
+    for(;;){
+        const unsigned need = __ballot_sync(0xffffffffu, (s.flags & TF_DONE) != 0);
+        if(need){
+            if(s.flags & TF_DONE){
+                if(idx != (size_t)-1){
+                    // retire the finished ray
+                    if(ANY)occ[idx] = (s.flags & TF_OCCLUDED) ? 1 : 0;
+                    else{
+                        const bool found = s.hprim != 0xFFFFFFFFu;
+                        if(!STATS || hits)hits[idx] = make_float4(found ? s.tmax : CUDART_INF_F, s.hu, s.hv, __uint_as_float(s.hprim));
+                        if(inst)inst[idx] = s.hinst;
+                        if(STATS && found)hitc++;
+                    }
+                    idx = (size_t)-1;
+                }
+            }
+            if(feed.avail == 0 && !feed.exhausted)feed_grab(feed, cursor, n, lane);
+            const unsigned rank = __popc(need & lt);
+            if((s.flags & TF_DONE) && rank < feed.avail){
+                idx = (size_t)(feed.base + rank);
+                trav_init<WIDTH>(s, S, __ldg(rays + 2 * idx), __ldg(rays + 2 * idx + 1));
+            }
+            const unsigned want = __popc(need);
+            const unsigned taken = want < feed.avail ? want : feed.avail;
+            feed.base += taken; feed.avail -= taken;
+            if(feed.exhausted && __all_sync(0xffffffffu, idx == (size_t)-1))break;
+        }
+        if(!(s.flags & TF_DONE))trav_step<WIDTH, ANY, STATS>(s, S, stack, rays, idx, STATS ? &c : nullptr, NoAlpha());
     }
-    // warp reduce, one atomic per warp per counter
-    unsigned long long v[5] = { c.tlas_nodes, c.blas_nodes, c.instances, c.triangles, hitc };
+    if(STATS){
+        // warp reduce, one atomic per warp per counter
+        unsigned long long v[5] = { c.tlas_nodes, c.blas_nodes, c.instances, c.triangles, hitc };
 #pragma unroll
-    for(int k = 0; k < 5; k++){
-        unsigned long long x = v[k];
-        for(int o = 16; o > 0; o >>= 1)x += __shfl_down_sync(0xffffffffu, x, o);
-        if((threadIdx.x & 31) == 0 && x)atomicAdd(out + k, x);
+        for(int k = 0; k < 5; k++){
+            unsigned long long x = v[k];
+            for(int o = 16; o > 0; o >>= 1)x += __shfl_down_sync(0xffffffffu, x, o);
+            if(lane == 0 && x)atomicAdd(stats + k, x);
+        }
     }
 }
 
@@ -67,31 +96,53 @@ static int check_launch(const char* what){
     return PT_OK;
 }
 
-int launch_trace_closest(const DevScene& S, const void* d_rays, size_t n, void* d_hits, void* d_inst, void* stream){
-    if(n == 0)return PT_OK;
-    const unsigned grid = (unsigned)((n + kTraceBlock - 1) / kTraceBlock);
-    cudaStream_t st = (cudaStream_t)stream;
-    if(S.width == 2)k_trace_closest<2><<<grid, kTraceBlock, 0, st>>>(S, (const float4*)d_rays, n, (float4*)d_hits, (uint32_t*)d_inst);
-    else k_trace_closest<4><<<grid, kTraceBlock, 0, st>>>(S, (const float4*)d_rays, n, (float4*)d_hits, (uint32_t*)d_inst);
-    return check_launch("k_trace_closest");
+// persistent grid size: resident CTAs of this kernel on this device (cached)
+template <class K>
+static unsigned persistent_grid(K kernel, int device, int& cache){
+    if(cache > 0)return (unsigned)cache;
+    int sms = 0, per_sm = 0;
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device);
+    cudaFuncSetAttribute(kernel, cudaFuncAttributePreferredSharedMemoryCarveout, 0);   // all L1
+    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, kTraceBlock, 0);
+    if(sms <= 0)sms = 148;
+    if(per_sm <= 0)per_sm = 1;
+    cache = sms * per_sm;
+    return (unsigned)cache;
 }
 
-int launch_trace_any(const DevScene& S, const void* d_rays, size_t n, void* d_occ, void* stream){
-    if(n == 0)return PT_OK;
-    const unsigned grid = (unsigned)((n + kTraceBlock - 1) / kTraceBlock);
+template <int WIDTH, bool ANY, bool STATS>
+static int launch(pt_scene* sc, const void* d_rays, size_t n, void* d_hits, void* d_inst, void* d_occ, void* d_stats, void* stream){
+    static int cache[8] = { 0, 0, 0, 0, 0, 0, 0, 0 };   // per device ordinal (one process drives at most 8 GPUs)
     cudaStream_t st = (cudaStream_t)stream;
-    if(S.width == 2)k_trace_any<2><<<grid, kTraceBlock, 0, st>>>(S, (const float4*)d_rays, n, (uint8_t*)d_occ);
-    else k_trace_any<4><<<grid, kTraceBlock, 0, st>>>(S, (const float4*)d_rays, n, (uint8_t*)d_occ);
-    return check_launch("k_trace_any");
+    auto kernel = k_trace<WIDTH, ANY, STATS>;
+    unsigned grid = persistent_grid(kernel, sc->device, cache[sc->device & 7]);
+    const size_t need_ctas = (n + kTraceBlock - 1) / kTraceBlock;
+    if(need_ctas < grid)grid = (unsigned)need_ctas;
+    // one cursor per launch from a small ring, so launches on different streams never share one
+    unsigned long long* cursor = (unsigned long long*)sc->buf.cursors + (sc->cursor_next++ % kCursorRing);
+    if(!cuda_ok(cudaMemsetAsync(cursor, 0, sizeof(unsigned long long), st), "cursor reset"))return PT_ERR_CUDA;
+    kernel<<<grid, kTraceBlock, 0, st>>>(sc->dev, (const float4*)d_rays, n, (float4*)d_hits, (uint32_t*)d_inst, (uint8_t*)d_occ,
+                                         cursor, (unsigned long long*)d_stats);
+    return check_launch("k_trace");
 }
 
-int launch_trace_stats(const DevScene& S, const void* d_rays, size_t n, void* d_counters, void* stream){
+int launch_trace_closest(pt_scene* sc, const void* d_rays, size_t n, void* d_hits, void* d_inst, void* stream){
     if(n == 0)return PT_OK;
-    const unsigned grid = (unsigned)((n + kTraceBlock - 1) / kTraceBlock);
-    cudaStream_t st = (cudaStream_t)stream;
-    if(S.width == 2)k_trace_stats<2><<<grid, kTraceBlock, 0, st>>>(S, (const float4*)d_rays, n, (unsigned long long*)d_counters);
-    else k_trace_stats<4><<<grid, kTraceBlock, 0, st>>>(S, (const float4*)d_rays, n, (unsigned long long*)d_counters);
-    return check_launch("k_trace_stats");
+    return sc->dev.width == 2 ? launch<2, false, false>(sc, d_rays, n, d_hits, d_inst, nullptr, nullptr, stream)
+                              : launch<4, false, false>(sc, d_rays, n, d_hits, d_inst, nullptr, nullptr, stream);
+}
+
+int launch_trace_any(pt_scene* sc, const void* d_rays, size_t n, void* d_occ, void* stream){
+    if(n == 0)return PT_OK;
+    return sc->dev.width == 2 ? launch<2, true, false>(sc, d_rays, n, nullptr, nullptr, d_occ, nullptr, stream)
+                              : launch<4, true, false>(sc, d_rays, n, nullptr, nullptr, d_occ, nullptr, stream);
+}
+
+// counting build of the same closest-hit traversal (SURVEY.md §8d)
+int launch_trace_stats(pt_scene* sc, const void* d_rays, size_t n, void* d_counters, void* stream){
+    if(n == 0)return PT_OK;
+    return sc->dev.width == 2 ? launch<2, false, true>(sc, d_rays, n, nullptr, nullptr, nullptr, d_counters, stream)
+                              : launch<4, false, true>(sc, d_rays, n, nullptr, nullptr, nullptr, d_counters, stream);
 }
 
 } // namespace ptb

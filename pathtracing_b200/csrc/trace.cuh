@@ -1,15 +1,26 @@
 // trace.cuh — device-side BVH2/BVH4 TLAS+BLAS traversal for sm_100a.
 //
-// One thread owns one ray.  Every node/triangle/instance record is fetched
-// with 128-bit loads (pt_types.h); the traversal stack lives in the thread's
-// local memory window (L1-resident).  The arithmetic of every box and triangle
-// test is written with explicit round-to-nearest intrinsics in the operation
-// order of the reference, so that no FMA contraction can change which
-// candidate wins (SURVEY.md §7 "hard part 1"):
+// One lane owns one ray and drives a small per-ray state machine (TravState +
+// one unified TLAS/BLAS stack in the lane's local-memory window).  One call of
+// trav_step() does at most: one pop, one inner-node test, one leaf item (one
+// triangle, one instance entry or one instance exit).  Kernels call it from a
+// persistent loop and refill finished lanes with new rays (trace.cu, render
+// kernels), so a warp never waits for its slowest ray and a leaf costs the
+// warp one triangle test per round instead of a whole nested loop
+// (profiles/r01_trace4_v1.md: the nested-loop version ran at 6.2 of 32 lanes).
+//
+// Every node/triangle/instance record is fetched with 128-bit loads
+// (pt_types.h).  The arithmetic of every box and triangle test is written with
+// explicit round-to-nearest intrinsics in the operation order of the
+// reference, so that no FMA contraction can change which candidate wins
+// (SURVEY.md §7 "hard part 1"); pushes and pops happen in the reference's
+// order, so exact ties resolve to the same triangle too:
 //   box     : AABB::HitDistance (AABB.hpp:72-111) / BVH4 SSE slab test (BVH.hpp:1142-1189)
 //   closest : glm::intersectRayTriangle (glm/gtx/intersect.inl:29-94) + Shape.cpp:204
 //   any-hit : TriangleShape::IntersectPred (Shape.cpp:246-268)
 //   instance: TransformedPrimitive::Intersect/IntersectPred (Primitive.cpp:41-66)
+//   BVH2    : BVH2::Intersect / IntersectPred (BVH.hpp:503-548, 476-500)
+//   BVH4    : BVH4::Intersect / IntersectPred (BVH.hpp:1111-1211, 1019-1109)
 #pragma once
 #include <cuda_runtime.h>
 #include <math_constants.h>
@@ -19,8 +30,8 @@ namespace ptb {
 
 constexpr float kShadowEps = 0.00001f;          // shadowEpsilon, AABB.hpp:6
 constexpr float kFltEps = 1.1920928955078125e-7f;
-constexpr int kStackTlas = 32;
-constexpr int kStackBlas = 64;
+constexpr int kStack = 96;                      // unified TLAS+BLAS stack (the reference: 32 + 32, unchecked)
+constexpr uint32_t REF_LEAVE = 0xFFFFFFFEu;     // stack sentinel: end of the current instance
 
 struct RayCtx {
     float ox, oy, oz, dx, dy, dz, ix, iy, iz;
@@ -129,157 +140,10 @@ __device__ __forceinline__ bool tri_any(const RayCtx& r, const TriData& T, float
 // Hook for alpha-tested materials (GeometricPrimitive::Intersect/IntersectPred,
 // Primitive.cpp:6-26).  The ray-cast entry points pass NoAlpha; the integrator
 // passes a functor that evaluates the material's alpha texture.
+// operator()(mesh, prim, inst_record, u, v) -> accept the hit?
 struct NoAlpha {
-    __device__ __forceinline__ bool operator()(uint32_t, uint32_t, float, float) const{ return true; }
+    __device__ __forceinline__ bool operator()(uint32_t, uint32_t, uint32_t, float, float) const{ return true; }
 };
-
-// Leaf loop: BVHBase::intersectPrimitives / intersectPrimitivesPred (BVH.hpp:107-135)
-template <bool ANY, bool STATS, class Alpha>
-__device__ __forceinline__ bool leaf_tris(const DevScene& S, const RayCtx& r, uint32_t first, float& tmax, HitRec& hit, TraceCounters* cnt, const Alpha& alpha){
-    bool found = false;
-    for(uint32_t i = first;; i++){
-        const TriData T = load_tri(S.tris, i);
-        const uint32_t flags = __float_as_uint(T.c.w);
-        if(STATS)cnt->triangles++;
-        float t, u, v;
-        if(ANY){
-            if(flags & TRI_ALPHA_PATH){
-                if(tri_closest(r, T, tmax, t, u, v)){
-                    if(!(flags & TRI_ALPHA_TEX) || alpha(__float_as_uint(T.b.w), __float_as_uint(T.a.w), u, v))return true;
-                }
-            } else if(tri_any(r, T, tmax))return true;
-        } else{
-            if(tri_closest(r, T, tmax, t, u, v)){
-                if(!(flags & TRI_ALPHA_TEX) || alpha(__float_as_uint(T.b.w), __float_as_uint(T.a.w), u, v)){
-                    tmax = t; hit.t = t; hit.u = u; hit.v = v; hit.prim = __float_as_uint(T.a.w);
-                    found = true;
-                }
-            }
-        }
-        if(flags & TRI_LAST)break;
-    }
-    return found;
-}
-
-// ---- BVH2 ---------------------------------------------------------------------------
-
-// BVH2::Intersect (BVH.hpp:503-548) / IntersectPred (:476-500) over one BLAS.
-template <bool ANY, bool STATS, class Alpha>
-__device__ __forceinline__ bool blas2(const DevScene& S, const RayCtx& r, uint32_t root, const float* rlo, const float* rhi, float& tmax, HitRec& hit, TraceCounters* cnt, const Alpha& alpha){
-    if(!box_hit2(r, rlo, rhi, tmax))return false;
-    uint32_t stack[kStackBlas];
-    int sp = 0;
-    stack[sp++] = root;
-    bool found = false;
-    while(sp){
-        const uint32_t ref = stack[--sp];
-        if(ref & REF_LEAF){
-            if(leaf_tris<ANY, STATS>(S, r, ref & ~REF_LEAF, tmax, hit, cnt, alpha)){
-                if(ANY)return true;
-                found = true;
-            }
-            continue;
-        }
-        const float4* p = reinterpret_cast<const float4*>(S.n2 + ref);
-        const float4 q0 = __ldg(p), q1 = __ldg(p + 1), q2 = __ldg(p + 2);
-        const uint4 q3 = __ldg(reinterpret_cast<const uint4*>(p + 3));
-        if(STATS)cnt->blas_nodes++;
-        float a0, b0, a1, b1;
-        slab(r, q0.x, q0.y, q0.z, q0.w, q1.x, q1.y, a0, b0);
-        slab(r, q1.z, q1.w, q2.x, q2.y, q2.z, q2.w, a1, b1);
-        const bool h0 = a0 <= b0 && b0 >= kShadowEps && a0 <= tmax;
-        const bool h1 = a1 <= b1 && b1 >= kShadowEps && a1 <= tmax;
-        if(ANY){
-            if(h0 && sp < kStackBlas)stack[sp++] = q3.x;
-            if(h1 && sp < kStackBlas)stack[sp++] = q3.y;
-        } else{
-            const float da = q3.z == 0 ? r.dx : (q3.z == 1 ? r.dy : r.dz);
-            if(da > 0.0f){      // child 0 is nearer: push 1 then 0
-                if(h1 && sp < kStackBlas)stack[sp++] = q3.y;
-                if(h0 && sp < kStackBlas)stack[sp++] = q3.x;
-            } else{
-                if(h0 && sp < kStackBlas)stack[sp++] = q3.x;
-                if(h1 && sp < kStackBlas)stack[sp++] = q3.y;
-            }
-        }
-    }
-    return found;
-}
-
-// ---- BVH4 ---------------------------------------------------------------------------
-
-struct Slab4 { float entry[4]; unsigned mask; };
-
-// 4-wide slab test of BVH4::Intersect (BVH.hpp:1142-1189): hit iff
-// tExit >= eps && tEntry < max && tEntry <= tExit  (note the strict '<').
-__device__ __forceinline__ Slab4 slab4(const RayCtx& r, const Bvh4Node* n, float tmax, uint4& refs, uint2& order){
-    const float4* p = reinterpret_cast<const float4*>(n);
-    const float4 xmin = __ldg(p), xmax = __ldg(p + 1), ymin = __ldg(p + 2), ymax = __ldg(p + 3), zmin = __ldg(p + 4), zmax = __ldg(p + 5);
-    refs = __ldg(reinterpret_cast<const uint4*>(p + 6));
-    const uint4 tail = __ldg(reinterpret_cast<const uint4*>(p + 7));
-    order = make_uint2(tail.x, tail.y);
-    Slab4 s; s.mask = 0;
-    float a, b;
-    slab(r, xmin.x, ymin.x, zmin.x, xmax.x, ymax.x, zmax.x, a, b); s.entry[0] = a; if(b >= kShadowEps && a < tmax && a <= b)s.mask |= 1u;
-    slab(r, xmin.y, ymin.y, zmin.y, xmax.y, ymax.y, zmax.y, a, b); s.entry[1] = a; if(b >= kShadowEps && a < tmax && a <= b)s.mask |= 2u;
-    slab(r, xmin.z, ymin.z, zmin.z, xmax.z, ymax.z, zmax.z, a, b); s.entry[2] = a; if(b >= kShadowEps && a < tmax && a <= b)s.mask |= 4u;
-    slab(r, xmin.w, ymin.w, zmin.w, xmax.w, ymax.w, zmax.w, a, b); s.entry[3] = a; if(b >= kShadowEps && a < tmax && a <= b)s.mask |= 8u;
-    return s;
-}
-
-__device__ __forceinline__ uint32_t pick4(const uint4& v, unsigned k){
-    return k == 0 ? v.x : (k == 1 ? v.y : (k == 2 ? v.z : v.w));
-}
-
-template <bool ANY, bool STATS, class Alpha>
-__device__ __forceinline__ bool blas4(const DevScene& S, const RayCtx& r, uint32_t root, float& tmax, HitRec& hit, TraceCounters* cnt, const Alpha& alpha){
-    uint32_t stack[kStackBlas];
-    float entry[kStackBlas];
-    int sp = 0;
-    entry[sp] = 0.0f;
-    stack[sp++] = root;
-    const unsigned octant = (r.dx < 0.0f ? 1u : 0u) | (r.dy < 0.0f ? 2u : 0u) | (r.dz < 0.0f ? 4u : 0u);
-    bool found = false;
-    while(sp){
-        --sp;
-        if(!ANY && entry[sp] > tmax)continue;       // BVH.hpp:1135
-        const uint32_t ref = stack[sp];
-        if(ref == REF_EMPTY)continue;
-        if(ref & REF_LEAF){
-            if(leaf_tris<ANY, STATS>(S, r, ref & ~REF_LEAF, tmax, hit, cnt, alpha)){
-                if(ANY)return true;
-                found = true;
-            }
-            continue;
-        }
-        uint4 refs; uint2 ord;
-        const Slab4 s = slab4(r, S.n4 + ref, tmax, refs, ord);
-        if(STATS)cnt->blas_nodes++;
-        if(ANY){
-            // BVH4::IntersectPred pushes lanes 0..3 unordered (BVH.hpp:1099-1102)
-#pragma unroll
-            for(unsigned k = 0; k < 4; k++)
-                if((s.mask >> k) & 1u){ if(sp < kStackBlas){ stack[sp++] = pick4(refs, k); } }
-        } else{
-            // visit order byte for this octant; push far -> near
-            const unsigned word = octant < 4 ? ord.x : ord.y;
-            const unsigned code = (word >> ((octant & 3u) * 8u)) & 0xFFu;
-#pragma unroll
-            for(int k = 0; k < 4; k++){
-                const unsigned lane = (code >> (2 * k)) & 3u;   // k=0 is the LAST visited lane
-                if((s.mask >> lane) & 1u){
-                    if(sp < kStackBlas){
-                        entry[sp] = lane == 0 ? s.entry[0] : (lane == 1 ? s.entry[1] : (lane == 2 ? s.entry[2] : s.entry[3]));
-                        stack[sp++] = pick4(refs, lane);
-                    }
-                }
-            }
-        }
-    }
-    return found;
-}
-
-// ---- instances ------------------------------------------------------------------------
 
 struct InstData { float4 m0, m1, m2; uint4 meta; float4 b0; float4 b1; };
 
@@ -300,128 +164,223 @@ __device__ __forceinline__ void xf_apply(const InstData& d, float x, float y, fl
     oz = f_add(f_add(f_mul(d.m0.z, x), f_mul(d.m1.y, y)), f_add(f_mul(d.m2.x, z), f_mul(d.m2.w, w)));
 }
 
-// One TLAS leaf: loop over its instances (BVHBase::intersectPrimitives over
-// shared_ptr<Primitive>), each either the BLAS itself or a TransformedPrimitive.
-template <int WIDTH, bool ANY, bool STATS, class Alpha>
-__device__ __forceinline__ bool leaf_instances(const DevScene& S, const RayCtx& r, uint32_t first, float& tmax, HitRec& hit, TraceCounters* cnt, const Alpha& alpha){
-    bool found = false;
-    for(uint32_t i = first;; i++){
-        const InstData d = load_inst(S.inst, i);
-        if(STATS)cnt->instances++;
-        const float rlo[3] = { d.b0.x, d.b0.y, d.b0.z }, rhi[3] = { d.b0.w, d.b1.x, d.b1.y };
-        bool h;
-        if(d.meta.y & INST_XF){
-            float ddx, ddy, ddz, oox, ooy, ooz;
-            xf_apply(d, r.dx, r.dy, r.dz, 0.0f, ddx, ddy, ddz);
-            const float len = sqrtf(f_add(f_add(f_mul(ddx, ddx), f_mul(ddy, ddy)), f_mul(ddz, ddz)));
-            xf_apply(d, r.ox, r.oy, r.oz, 1.0f, oox, ooy, ooz);
-            RayCtx lr;
-            make_ray(lr, oox, ooy, ooz, f_div(ddx, len), f_div(ddy, len), f_div(ddz, len));
-            float lmax = f_mul(tmax, len);
-            HitRec lh;
-            if(WIDTH == 2)h = blas2<ANY, STATS>(S, lr, d.meta.x, rlo, rhi, lmax, lh, cnt, alpha);
-            else h = blas4<ANY, STATS>(S, lr, d.meta.x, lmax, lh, cnt, alpha);
-            if(h && !ANY){
-                hit = lh;
-                hit.t = f_div(lh.t, len);   // Primitive.cpp:60
-                tmax = hit.t;
-            }
-        } else{
-            if(WIDTH == 2)h = blas2<ANY, STATS>(S, r, d.meta.x, rlo, rhi, tmax, hit, cnt, alpha);
-            else h = blas4<ANY, STATS>(S, r, d.meta.x, tmax, hit, cnt, alpha);
-        }
-        if(h){
-            if(ANY)return true;
-            hit.inst = d.meta.z;
-            found = true;
-        }
-        if(d.meta.y & INST_LAST)break;
-    }
-    return found;
+// ---- per-ray traversal state ------------------------------------------------------------
+
+enum : uint32_t {
+    TF_IN_INST = 1u,     // below a TLAS leaf: leaf refs now mean triangles
+    TF_XF = 2u,          // the current instance is a TransformedPrimitive: r/tmax are object space
+    TF_FOUND_LOCAL = 4u, // a hit was accepted inside the current instance
+    TF_DONE = 8u,
+    TF_OCCLUDED = 16u    // any-hit result
+};
+
+struct TravState {
+    RayCtx r;            // ray in the current space (world, or object space of the instance)
+    float tmax;          // closest accepted t so far, current space
+    float wtmax;         // world-space tmax saved while inside a transformed instance
+    float len;           // |M^-1 dir| of the current transformed instance
+    uint32_t cur;        // what to process next: inner ref | leaf ref | REF_LEAVE | REF_EMPTY (= pop)
+    int sp;
+    uint32_t flags;
+    uint32_t inst_rec;   // record index (leaf order) of the current instance
+    uint32_t inst_id;    // its id (pt_scene_add_instance order)
+    uint32_t octant;     // BVH4 visit-order selector: sign bits of r.d
+    float hu, hv;
+    uint32_t hprim, hinst;
+};
+
+__device__ __forceinline__ uint32_t ray_octant(const RayCtx& r){
+    return (r.dx < 0.0f ? 1u : 0u) | (r.dy < 0.0f ? 2u : 0u) | (r.dz < 0.0f ? 4u : 0u);
 }
 
-// ---- TLAS -----------------------------------------------------------------------------
+__device__ __forceinline__ void trav_push(uint2* stack, int& sp, uint32_t ref, float entry){
+    if(sp < kStack){ stack[sp] = make_uint2(ref, __float_as_uint(entry)); ++sp; }
+}
 
-// Scene::Intersect / IntersectPred (Scene.cpp:4-6,31-33) -> TLASx -> instances -> BLASx.
-template <int WIDTH, bool ANY, bool STATS, class Alpha>
-__device__ __forceinline__ bool trace_scene(const DevScene& S, const RayCtx& r, float tmax, HitRec& hit, TraceCounters* cnt, const Alpha& alpha){
-    hit.t = CUDART_INF_F; hit.u = 0.0f; hit.v = 0.0f; hit.prim = 0xFFFFFFFFu; hit.inst = 0xFFFFFFFFu;
-    bool found = false;
+// Scene::Intersect / IntersectPred entry (Scene.cpp:4-6,31-33).
+template <int WIDTH>
+__device__ __forceinline__ void trav_init(TravState& s, const DevScene& S, const float4 a, const float4 b){
+    make_ray(s.r, a.x, a.y, a.z, b.x, b.y, b.z);
+    s.tmax = a.w; s.wtmax = a.w; s.len = 1.0f;
+    s.sp = 0; s.flags = 0; s.inst_rec = 0; s.inst_id = 0xFFFFFFFFu;
+    s.hu = 0.0f; s.hv = 0.0f; s.hprim = 0xFFFFFFFFu; s.hinst = 0xFFFFFFFFu;
+    s.octant = ray_octant(s.r);
+    s.cur = S.tlas_root;
     if(WIDTH == 2){
-        if(!box_hit2(r, S.tlo, S.thi, tmax))return false;
-        uint32_t stack[kStackTlas];
-        int sp = 0;
-        stack[sp++] = S.tlas_root;
-        while(sp){
-            const uint32_t ref = stack[--sp];
-            if(ref & REF_LEAF){
-                if(leaf_instances<2, ANY, STATS>(S, r, ref & ~REF_LEAF, tmax, hit, cnt, alpha)){
-                    if(ANY)return true;
-                    found = true;
-                }
-                continue;
-            }
-            const float4* p = reinterpret_cast<const float4*>(S.n2 + ref);
-            const float4 q0 = __ldg(p), q1 = __ldg(p + 1), q2 = __ldg(p + 2);
-            const uint4 q3 = __ldg(reinterpret_cast<const uint4*>(p + 3));
-            if(STATS)cnt->tlas_nodes++;
-            float a0, b0, a1, b1;
-            slab(r, q0.x, q0.y, q0.z, q0.w, q1.x, q1.y, a0, b0);
-            slab(r, q1.z, q1.w, q2.x, q2.y, q2.z, q2.w, a1, b1);
-            const bool h0 = a0 <= b0 && b0 >= kShadowEps && a0 <= tmax;
-            const bool h1 = a1 <= b1 && b1 >= kShadowEps && a1 <= tmax;
-            const float da = q3.z == 0 ? r.dx : (q3.z == 1 ? r.dy : r.dz);
-            if(!ANY && da > 0.0f){
-                if(h1 && sp < kStackTlas)stack[sp++] = q3.y;
-                if(h0 && sp < kStackTlas)stack[sp++] = q3.x;
-            } else{
-                if(h0 && sp < kStackTlas)stack[sp++] = q3.x;
-                if(h1 && sp < kStackTlas)stack[sp++] = q3.y;
+        // BVH2::Intersect tests the root box first (BVH.hpp:504,477)
+        if(!box_hit2(s.r, S.tlo, S.thi, s.tmax)){ s.cur = REF_EMPTY; s.flags = TF_DONE; }
+    }
+}
+
+// ---- inner nodes ----------------------------------------------------------------------
+
+// BVH2 child-pair node.  Closest: push order by the sign of dir[node.axis]
+// (BVH.hpp:520-545); any-hit: child 0 then child 1 (BVH.hpp:489-490).
+template <bool ANY>
+__device__ __forceinline__ void node_step2(TravState& s, const DevScene& S, uint2* stack){
+    const float4* p = reinterpret_cast<const float4*>(S.n2 + s.cur);
+    const float4 q0 = __ldg(p), q1 = __ldg(p + 1), q2 = __ldg(p + 2);
+    const uint4 q3 = __ldg(reinterpret_cast<const uint4*>(p + 3));
+    float a0, b0, a1, b1;
+    slab(s.r, q0.x, q0.y, q0.z, q0.w, q1.x, q1.y, a0, b0);
+    slab(s.r, q1.z, q1.w, q2.x, q2.y, q2.z, q2.w, a1, b1);
+    const bool h0 = a0 <= b0 && b0 >= kShadowEps && a0 <= s.tmax;
+    const bool h1 = a1 <= b1 && b1 >= kShadowEps && a1 <= s.tmax;
+    bool near0 = false;   // any-hit: child 1 is pushed last, so it is visited first
+    if(!ANY){
+        const float da = q3.z == 0 ? s.r.dx : (q3.z == 1 ? s.r.dy : s.r.dz);
+        near0 = da > 0.0f;
+    }
+    const uint32_t nref = near0 ? q3.x : q3.y, fref = near0 ? q3.y : q3.x;
+    const bool hn = near0 ? h0 : h1, hf = near0 ? h1 : h0;
+    if(hn){
+        if(hf)trav_push(stack, s.sp, fref, 0.0f);
+        s.cur = nref;
+    } else s.cur = hf ? fref : REF_EMPTY;
+}
+
+__device__ __forceinline__ uint32_t pick4(const uint4& v, unsigned k){
+    return k == 0 ? v.x : (k == 1 ? v.y : (k == 2 ? v.z : v.w));
+}
+
+// BVH4 cluster: 4-wide slab test (BVH.hpp:1142-1189; hit iff tExit >= eps &&
+// tEntry < max && tEntry <= tExit, note the strict '<'), then the children
+// that were hit are pushed far -> near in the cluster's fixed visit order for
+// this ray octant (the folded LUT[signs][perm] / maskLUT of BVH.hpp:1193-1204).
+// The nearest one stays in s.cur instead of going through the stack: it was
+// just tested against the current tmax, so the pop-time cull cannot reject it.
+template <bool ANY>
+__device__ __forceinline__ void node_step4(TravState& s, const DevScene& S, uint2* stack){
+    const float4* p = reinterpret_cast<const float4*>(S.n4 + s.cur);
+    const float4 xmin = __ldg(p), xmax = __ldg(p + 1), ymin = __ldg(p + 2), ymax = __ldg(p + 3), zmin = __ldg(p + 4), zmax = __ldg(p + 5);
+    const uint4 refs = __ldg(reinterpret_cast<const uint4*>(p + 6));
+    const uint2 ord = __ldg(reinterpret_cast<const uint2*>(p + 7));
+    float e0, e1, e2, e3, x;
+    unsigned mask = 0;
+    const float tmax = s.tmax;
+    slab(s.r, xmin.x, ymin.x, zmin.x, xmax.x, ymax.x, zmax.x, e0, x); if(x >= kShadowEps && e0 < tmax && e0 <= x)mask |= 1u;
+    slab(s.r, xmin.y, ymin.y, zmin.y, xmax.y, ymax.y, zmax.y, e1, x); if(x >= kShadowEps && e1 < tmax && e1 <= x)mask |= 2u;
+    slab(s.r, xmin.z, ymin.z, zmin.z, xmax.z, ymax.z, zmax.z, e2, x); if(x >= kShadowEps && e2 < tmax && e2 <= x)mask |= 4u;
+    slab(s.r, xmin.w, ymin.w, zmin.w, xmax.w, ymax.w, zmax.w, e3, x); if(x >= kShadowEps && e3 < tmax && e3 <= x)mask |= 8u;
+    uint32_t cur = REF_EMPTY;
+    float cure = 0.0f;
+    if(mask){
+        const unsigned word = s.octant < 4 ? ord.x : ord.y;
+        const unsigned code = (word >> ((s.octant & 3u) * 8u)) & 0xFFu;
+#pragma unroll
+        for(int k = 0; k < 4; k++){
+            const unsigned lane = (code >> (2 * k)) & 3u;   // k = 0 is the LAST visited lane
+            if((mask >> lane) & 1u){
+                if(cur != REF_EMPTY)trav_push(stack, s.sp, cur, cure);
+                cur = pick4(refs, lane);
+                cure = lane == 0 ? e0 : (lane == 1 ? e1 : (lane == 2 ? e2 : e3));
             }
         }
-    } else{
-        uint32_t stack[kStackTlas];
-        float entry[kStackTlas];
-        int sp = 0;
-        entry[sp] = 0.0f;
-        stack[sp++] = S.tlas_root;
-        const unsigned octant = (r.dx < 0.0f ? 1u : 0u) | (r.dy < 0.0f ? 2u : 0u) | (r.dz < 0.0f ? 4u : 0u);
-        while(sp){
-            --sp;
-            if(!ANY && entry[sp] > tmax)continue;
-            const uint32_t ref = stack[sp];
-            if(ref == REF_EMPTY)continue;
-            if(ref & REF_LEAF){
-                if(leaf_instances<4, ANY, STATS>(S, r, ref & ~REF_LEAF, tmax, hit, cnt, alpha)){
-                    if(ANY)return true;
-                    found = true;
-                }
-                continue;
+    }
+    s.cur = cur;
+}
+
+// ---- one round of the state machine -------------------------------------------------------
+
+// Returns false once the ray is finished (s.flags & TF_DONE).
+// reload(ray index) -> the world-space ray is re-read from its buffer when a
+// transformed instance is left (cheaper than holding 9 more registers).
+template <int WIDTH, bool ANY, bool STATS, class Alpha>
+__device__ __forceinline__ void trav_step(TravState& s, const DevScene& S, uint2* stack, const float4* __restrict__ rays, size_t ray_idx,
+                                          TraceCounters* cnt, const Alpha& alpha){
+    // -- pop (BVH4 closest: cull by entry distance, BVH.hpp:1135) --
+    if(s.cur == REF_EMPTY){
+        while(s.sp > 0){
+            const uint2 e = stack[--s.sp];
+            if(WIDTH == 4 && !ANY && __uint_as_float(e.y) > s.tmax)continue;
+            if(e.x == REF_EMPTY)continue;      // empty lane of a cluster (BVH.hpp:38-43)
+            s.cur = e.x;
+            break;
+        }
+        if(s.cur == REF_EMPTY){ s.flags |= TF_DONE; return; }
+    }
+    // -- inner node --
+    if(!(s.cur & REF_LEAF)){
+        if(STATS){ if(s.flags & TF_IN_INST)cnt->blas_nodes++; else cnt->tlas_nodes++; }
+        if(WIDTH == 2)node_step2<ANY>(s, S, stack);
+        else node_step4<ANY>(s, S, stack);
+    }
+    // -- leaf items --
+    if((s.cur & REF_LEAF) && s.cur != REF_EMPTY){
+        if(s.cur == REF_LEAVE){
+            // end of TransformedPrimitive::Intersect (Primitive.cpp:54-63): t back to world space
+            if(s.flags & TF_XF){
+                const float4 a = __ldg(rays + 2 * ray_idx), b = __ldg(rays + 2 * ray_idx + 1);
+                make_ray(s.r, a.x, a.y, a.z, b.x, b.y, b.z);
+                s.octant = ray_octant(s.r);
+                s.tmax = (s.flags & TF_FOUND_LOCAL) ? f_div(s.tmax, s.len) : s.wtmax;
             }
-            uint4 refs; uint2 ord;
-            const Slab4 s = slab4(r, S.n4 + ref, tmax, refs, ord);
-            if(STATS)cnt->tlas_nodes++;
+            s.flags &= ~(TF_IN_INST | TF_XF | TF_FOUND_LOCAL);
+            s.cur = REF_EMPTY;
+        } else if(!(s.flags & TF_IN_INST)){
+            // TLAS leaf item: BVHBase::intersectPrimitives over shared_ptr<Primitive> (BVH.hpp:107-135),
+            // each either the BLAS itself or a TransformedPrimitive (Primitive.cpp:41-66)
+            const uint32_t i = s.cur & ~REF_LEAF;
+            const InstData d = load_inst(S.inst, i);
+            if(STATS)cnt->instances++;
+            if(!(d.meta.y & INST_LAST))trav_push(stack, s.sp, REF_LEAF | (i + 1), -CUDART_INF_F);
+            trav_push(stack, s.sp, REF_LEAVE, -CUDART_INF_F);
+            s.flags |= TF_IN_INST;
+            s.inst_rec = i; s.inst_id = d.meta.z;
+            if(d.meta.y & INST_XF){
+                float ddx, ddy, ddz, oox, ooy, ooz;
+                xf_apply(d, s.r.dx, s.r.dy, s.r.dz, 0.0f, ddx, ddy, ddz);
+                const float len = sqrtf(f_add(f_add(f_mul(ddx, ddx), f_mul(ddy, ddy)), f_mul(ddz, ddz)));
+                xf_apply(d, s.r.ox, s.r.oy, s.r.oz, 1.0f, oox, ooy, ooz);
+                make_ray(s.r, oox, ooy, ooz, f_div(ddx, len), f_div(ddy, len), f_div(ddz, len));
+                s.octant = ray_octant(s.r);
+                s.wtmax = s.tmax; s.len = len;
+                s.tmax = f_mul(s.tmax, len);
+                s.flags |= TF_XF;
+            }
+            s.cur = d.meta.x;
+            if(WIDTH == 2){
+                const float rlo[3] = { d.b0.x, d.b0.y, d.b0.z }, rhi[3] = { d.b0.w, d.b1.x, d.b1.y };
+                if(!box_hit2(s.r, rlo, rhi, s.tmax))s.cur = REF_EMPTY;
+            }
+        } else{
+            // BLAS leaf item: one triangle of BVHBase::intersectPrimitives[Pred] (BVH.hpp:107-135)
+            const uint32_t i = s.cur & ~REF_LEAF;
+            const TriData T = load_tri(S.tris, i);
+            const uint32_t tf = __float_as_uint(T.c.w);
+            if(STATS)cnt->triangles++;
+            float t, u, v;
             if(ANY){
-#pragma unroll
-                for(unsigned k = 0; k < 4; k++)
-                    if((s.mask >> k) & 1u){ if(sp < kStackTlas){ stack[sp++] = pick4(refs, k); } }
+                bool occ;
+                if(tf & TRI_ALPHA_PATH){
+                    // material->HasAlpha(): shape->Intersect + alpha test (Primitive.cpp:6-14)
+                    occ = tri_closest(s.r, T, s.tmax, t, u, v) &&
+                          (!(tf & TRI_ALPHA_TEX) || alpha(__float_as_uint(T.b.w), __float_as_uint(T.a.w), s.inst_rec, u, v));
+                } else occ = tri_any(s.r, T, s.tmax);
+                if(occ){ s.flags |= TF_OCCLUDED | TF_DONE; return; }
             } else{
-                const unsigned word = octant < 4 ? ord.x : ord.y;
-                const unsigned code = (word >> ((octant & 3u) * 8u)) & 0xFFu;
-#pragma unroll
-                for(int k = 0; k < 4; k++){
-                    const unsigned lane = (code >> (2 * k)) & 3u;
-                    if((s.mask >> lane) & 1u){
-                        if(sp < kStackTlas){
-                            entry[sp] = lane == 0 ? s.entry[0] : (lane == 1 ? s.entry[1] : (lane == 2 ? s.entry[2] : s.entry[3]));
-                            stack[sp++] = pick4(refs, lane);
-                        }
+                if(tri_closest(s.r, T, s.tmax, t, u, v)){
+                    if(!(tf & TRI_ALPHA_TEX) || alpha(__float_as_uint(T.b.w), __float_as_uint(T.a.w), s.inst_rec, u, v)){
+                        s.tmax = t; s.hu = u; s.hv = v; s.hprim = __float_as_uint(T.a.w); s.hinst = s.inst_id;
+                        s.flags |= TF_FOUND_LOCAL;
                     }
                 }
             }
+            s.cur = (tf & TRI_LAST) ? REF_EMPTY : (REF_LEAF | (i + 1));
         }
     }
-    return found;
+}
+
+// Whole-ray convenience wrapper (host emulation tests, counting kernel).
+template <int WIDTH, bool ANY, bool STATS, class Alpha>
+__device__ __forceinline__ bool trace_scene(const DevScene& S, const float4* __restrict__ rays, size_t ray_idx, HitRec& hit, TraceCounters* cnt, const Alpha& alpha){
+    uint2 stack[kStack];
+    TravState s;
+    trav_init<WIDTH>(s, S, __ldg(rays + 2 * ray_idx), __ldg(rays + 2 * ray_idx + 1));
+    while(!(s.flags & TF_DONE))trav_step<WIDTH, ANY, STATS>(s, S, stack, rays, ray_idx, cnt, alpha);
+    const bool found = s.hprim != 0xFFFFFFFFu;
+    hit.t = found ? s.tmax : CUDART_INF_F; hit.u = s.hu; hit.v = s.hv; hit.prim = s.hprim; hit.inst = s.hinst;
+    return ANY ? (s.flags & TF_OCCLUDED) != 0 : found;
 }
 
 } // namespace ptb

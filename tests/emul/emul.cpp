@@ -73,10 +73,10 @@ PT_API int emul_trace_closest(void* p, const pt_ray* rays, size_t n, pt_hit* hit
     std::vector<TraceCounters> cs(nt, TraceCounters{0, 0, 0, 0});
     auto work = [&](int tid){
         for(size_t i = tid; i < n; i += nt){
-            RayCtx r; make_ray(r, rays[i].ox, rays[i].oy, rays[i].oz, rays[i].dx, rays[i].dy, rays[i].dz);
             HitRec h;
-            if(D.width == 2)trace_scene<2, false, true>(D, r, rays[i].tmax, h, &cs[tid], NoAlpha());
-            else trace_scene<4, false, true>(D, r, rays[i].tmax, h, &cs[tid], NoAlpha());
+            const float4* rb = reinterpret_cast<const float4*>(rays);
+            if(D.width == 2)trace_scene<2, false, true>(D, rb, i, h, &cs[tid], NoAlpha());
+            else trace_scene<4, false, true>(D, rb, i, h, &cs[tid], NoAlpha());
             hits[i].t = h.t; hits[i].u = h.u; hits[i].v = h.v; hits[i].prim = h.prim;
             if(inst)inst[i] = h.inst;
         }
@@ -97,10 +97,10 @@ PT_API int emul_trace_any(void* p, const pt_ray* rays, size_t n, uint8_t* occ){
     int nt = (int)std::thread::hardware_concurrency(); if(nt < 1)nt = 1;
     auto work = [&](int tid){
         for(size_t i = tid; i < n; i += nt){
-            RayCtx r; make_ray(r, rays[i].ox, rays[i].oy, rays[i].oz, rays[i].dx, rays[i].dy, rays[i].dz);
             HitRec h;
-            bool o = D.width == 2 ? trace_scene<2, true, false>(D, r, rays[i].tmax, h, nullptr, NoAlpha())
-                                  : trace_scene<4, true, false>(D, r, rays[i].tmax, h, nullptr, NoAlpha());
+            const float4* rb = reinterpret_cast<const float4*>(rays);
+            bool o = D.width == 2 ? trace_scene<2, true, false>(D, rb, i, h, nullptr, NoAlpha())
+                                  : trace_scene<4, true, false>(D, rb, i, h, nullptr, NoAlpha());
             occ[i] = o ? 1 : 0;
         }
     };
