@@ -77,6 +77,21 @@ __device__ __forceinline__ bool box_hit2(const RayCtx& r, const float* lo, const
 
 struct TriData { float4 a, b, c; };
 
+// 256-bit read-only global load (LDG.E.256, sm_100+): a 128 B cluster arrives in
+// 4 L1 wavefronts per lane instead of 8 (profiles/r01_trace4_v2.md: the kernel is
+// bound by l1tex data-pipe wavefronts, not by bytes).  p must be 32 B aligned.
+struct F8 { float4 lo, hi; };
+__device__ __forceinline__ F8 ldg256(const void* p){
+    F8 r;
+#if defined(__CUDA_ARCH__)
+    asm("ld.global.nc.v8.f32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+        : "=f"(r.lo.x), "=f"(r.lo.y), "=f"(r.lo.z), "=f"(r.lo.w), "=f"(r.hi.x), "=f"(r.hi.y), "=f"(r.hi.z), "=f"(r.hi.w) : "l"(p));
+#else
+    r.lo = reinterpret_cast<const float4*>(p)[0]; r.hi = reinterpret_cast<const float4*>(p)[1];
+#endif
+    return r;
+}
+
 __device__ __forceinline__ TriData load_tri(const Tri* tris, uint32_t i){
     const float4* p = reinterpret_cast<const float4*>(tris + i);
     TriData t;
@@ -219,8 +234,9 @@ __device__ __forceinline__ void trav_init(TravState& s, const DevScene& S, const
 template <bool ANY>
 __device__ __forceinline__ void node_step2(TravState& s, const DevScene& S, uint2* stack){
     const float4* p = reinterpret_cast<const float4*>(S.n2 + s.cur);
-    const float4 q0 = __ldg(p), q1 = __ldg(p + 1), q2 = __ldg(p + 2);
-    const uint4 q3 = __ldg(reinterpret_cast<const uint4*>(p + 3));
+    const F8 w0 = ldg256(p), w1 = ldg256(p + 2);
+    const float4 q0 = w0.lo, q1 = w0.hi, q2 = w1.lo;
+    const uint4 q3 = make_uint4(__float_as_uint(w1.hi.x), __float_as_uint(w1.hi.y), __float_as_uint(w1.hi.z), __float_as_uint(w1.hi.w));
     float a0, b0, a1, b1;
     slab(s.r, q0.x, q0.y, q0.z, q0.w, q1.x, q1.y, a0, b0);
     slab(s.r, q1.z, q1.w, q2.x, q2.y, q2.z, q2.w, a1, b1);
@@ -252,9 +268,10 @@ __device__ __forceinline__ uint32_t pick4(const uint4& v, unsigned k){
 template <bool ANY>
 __device__ __forceinline__ void node_step4(TravState& s, const DevScene& S, uint2* stack){
     const float4* p = reinterpret_cast<const float4*>(S.n4 + s.cur);
-    const float4 xmin = __ldg(p), xmax = __ldg(p + 1), ymin = __ldg(p + 2), ymax = __ldg(p + 3), zmin = __ldg(p + 4), zmax = __ldg(p + 5);
-    const uint4 refs = __ldg(reinterpret_cast<const uint4*>(p + 6));
-    const uint2 ord = __ldg(reinterpret_cast<const uint2*>(p + 7));
+    const F8 wx = ldg256(p), wy = ldg256(p + 2), wz = ldg256(p + 4), wr = ldg256(p + 6);
+    const float4 xmin = wx.lo, xmax = wx.hi, ymin = wy.lo, ymax = wy.hi, zmin = wz.lo, zmax = wz.hi;
+    const uint4 refs = make_uint4(__float_as_uint(wr.lo.x), __float_as_uint(wr.lo.y), __float_as_uint(wr.lo.z), __float_as_uint(wr.lo.w));
+    const uint2 ord = make_uint2(__float_as_uint(wr.hi.x), __float_as_uint(wr.hi.y));
     float e0, e1, e2, e3, x;
     unsigned mask = 0;
     const float tmax = s.tmax;
