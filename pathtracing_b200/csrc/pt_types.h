@@ -87,6 +87,9 @@ struct DevScene {
     uint32_t tlas_root;      // ref into n2/n4 (or a leaf ref into inst)
     int width;               // 2 | 4
     float tlo[3], thi[3];    // TLAS root box (BVH2::Intersect tests it first)
+    uint32_t single_root;    // scene = one untransformed instance: its BLAS root ref (traversal starts
+                             // inside it, no TLAS leaf / instance record round trip); else REF_EMPTY
+    uint32_t single_id;      // that instance's id
 };
 
 } // namespace ptb

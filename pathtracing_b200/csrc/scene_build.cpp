@@ -220,6 +220,7 @@ int pack_traversal(pt_scene* s, int width, PackedTraversal& P){
         I.bhi0 = hb.bounds.hi[0]; I.bhi12[0] = hb.bounds.hi[1]; I.bhi12[1] = hb.bounds.hi[2];
     }
 
+    if(ni == 1 && !s->instances[0].has_xf){ P.single_root = s->blas[s->instances[0].blas].root; P.single_id = 0; }
     P.tlas_root = trebase(tf.root);
     P.bounds = tf.bounds;
     P.inst_order = tf.order;

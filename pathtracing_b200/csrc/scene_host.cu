@@ -62,6 +62,7 @@ int scene_commit(pt_scene* s, int width, int light_sampler){
     s->dev.tris = (const Tri*)b.tris; s->dev.inst = (const Instance*)b.inst;
     s->dev.tlas_root = P.tlas_root;
     s->dev.width = width;
+    s->dev.single_root = P.single_root; s->dev.single_id = P.single_id;
     for(int a = 0; a < 3; a++){ s->dev.tlo[a] = P.bounds.lo[a]; s->dev.thi[a] = P.bounds.hi[a]; }
     s->total_tris = tris.size();
     s->total_nodes = width == 2 ? n2.size() : n4.size();

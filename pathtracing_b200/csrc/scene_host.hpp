@@ -99,6 +99,7 @@ struct PackedTraversal {
     std::vector<Instance> insts;      // TLAS leaf order
     std::vector<uint32_t> inst_order; // leaf order -> instance id
     uint32_t tlas_root = REF_EMPTY;
+    uint32_t single_root = REF_EMPTY, single_id = 0;
     Box bounds = box_empty();
 };
 

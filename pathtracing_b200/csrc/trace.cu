@@ -9,6 +9,7 @@
 // store.  No shared memory is used, so the whole 228 KB of the SM is L1 for
 // the upper tree levels and the per-lane stacks.
 #include <cstdio>
+#include <cstdlib>
 #include "scene_host.hpp"
 #include "trace.cuh"
 
@@ -38,7 +39,8 @@ __device__ __forceinline__ void feed_grab(RayFeed& f, unsigned long long* cursor
 template <int WIDTH, bool ANY, bool STATS>
 __global__ void __launch_bounds__(kTraceBlock) k_trace(DevScene S, const float4* __restrict__ rays, size_t n,
                                                        float4* __restrict__ hits, uint32_t* __restrict__ inst, uint8_t* __restrict__ occ,
-                                                       unsigned long long* __restrict__ cursor, unsigned long long* __restrict__ stats){
+                                                       unsigned long long* __restrict__ cursor, unsigned long long* __restrict__ stats,
+                                                       unsigned refill_min){
     uint2 stack[kStack];
     TravState s;
     s.flags = TF_DONE;
@@ -51,7 +53,9 @@ __global__ void __launch_bounds__(kTraceBlock) k_trace(DevScene S, const float4*
 
     for(;;){
         const unsigned need = __ballot_sync(0xffffffffu, (s.flags & TF_DONE) != 0);
-        if(need){
+        // Refill in batches: the retire + fetch + init path runs with only the finished lanes
+        // active, so it is entered once `refill_min` lanes are waiting (or nothing else is left).
+        if(need && (__popc(need) >= (int)refill_min || feed.exhausted || need == 0xffffffffu)){
             if(s.flags & TF_DONE){
                 if(idx != (size_t)-1){
                     // retire the finished ray
@@ -110,6 +114,12 @@ static unsigned persistent_grid(K kernel, int device, int& cache){
     return (unsigned)cache;
 }
 
+static unsigned refill_min(){
+    static int v = -1;
+    if(v < 0){ const char* e = getenv("PTB_REFILL_MIN"); v = e ? atoi(e) : 4; if(v < 1)v = 1; if(v > 32)v = 32; }
+    return (unsigned)v;
+}
+
 template <int WIDTH, bool ANY, bool STATS>
 static int launch(pt_scene* sc, const void* d_rays, size_t n, void* d_hits, void* d_inst, void* d_occ, void* d_stats, void* stream){
     static int cache[8] = { 0, 0, 0, 0, 0, 0, 0, 0 };   // per device ordinal (one process drives at most 8 GPUs)
@@ -122,7 +132,7 @@ static int launch(pt_scene* sc, const void* d_rays, size_t n, void* d_hits, void
     unsigned long long* cursor = (unsigned long long*)sc->buf.cursors + (sc->cursor_next++ % kCursorRing);
     if(!cuda_ok(cudaMemsetAsync(cursor, 0, sizeof(unsigned long long), st), "cursor reset"))return PT_ERR_CUDA;
     kernel<<<grid, kTraceBlock, 0, st>>>(sc->dev, (const float4*)d_rays, n, (float4*)d_hits, (uint32_t*)d_inst, (uint8_t*)d_occ,
-                                         cursor, (unsigned long long*)d_stats);
+                                         cursor, (unsigned long long*)d_stats, refill_min());
     return check_launch("k_trace");
 }
 

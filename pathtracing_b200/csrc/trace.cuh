@@ -52,7 +52,12 @@ __device__ __forceinline__ float f_mul(float a, float b){ return __fmul_rn(a, b)
 __device__ __forceinline__ float f_div(float a, float b){ return __fdiv_rn(a, b); }
 
 // Ray ctor, Ray.hpp:32-37
-__device__ __forceinline__ float inv_dir(float d){ return fabsf(d) < 1e-32f ? 1e32f : f_div(1.0f, d); }
+#if defined(__CUDA_ARCH__)
+__device__ __forceinline__ float f_rcp(float a){ return __frcp_rn(a); }   // correctly rounded: == 1.0f / a
+#else
+__device__ __forceinline__ float f_rcp(float a){ return 1.0f / a; }
+#endif
+__device__ __forceinline__ float inv_dir(float d){ return fabsf(d) < 1e-32f ? 1e32f : f_rcp(d); }
 
 __device__ __forceinline__ void make_ray(RayCtx& r, float ox, float oy, float oz, float dx, float dy, float dz){
     r.ox = ox; r.oy = oy; r.oz = oz; r.dx = dx; r.dy = dy; r.dz = dz;
@@ -221,6 +226,10 @@ __device__ __forceinline__ void trav_init(TravState& s, const DevScene& S, const
     s.hu = 0.0f; s.hv = 0.0f; s.hprim = 0xFFFFFFFFu; s.hinst = 0xFFFFFFFFu;
     s.octant = ray_octant(s.r);
     s.cur = S.tlas_root;
+    if(S.single_root != REF_EMPTY){
+        // one untransformed instance: TLAS root box == BLAS root box, the leaf holds just this BLAS
+        s.cur = S.single_root; s.flags = TF_IN_INST; s.inst_id = S.single_id;
+    }
     if(WIDTH == 2){
         // BVH2::Intersect tests the root box first (BVH.hpp:504,477)
         if(!box_hit2(s.r, S.tlo, S.thi, s.tmax)){ s.cur = REF_EMPTY; s.flags = TF_DONE; }
@@ -279,21 +288,28 @@ __device__ __forceinline__ void node_step4(TravState& s, const DevScene& S, uint
     slab(s.r, xmin.y, ymin.y, zmin.y, xmax.y, ymax.y, zmax.y, e1, x); if(x >= kShadowEps && e1 < tmax && e1 <= x)mask |= 2u;
     slab(s.r, xmin.z, ymin.z, zmin.z, xmax.z, ymax.z, zmax.z, e2, x); if(x >= kShadowEps && e2 < tmax && e2 <= x)mask |= 4u;
     slab(s.r, xmin.w, ymin.w, zmin.w, xmax.w, ymax.w, zmax.w, e3, x); if(x >= kShadowEps && e3 < tmax && e3 <= x)mask |= 8u;
+    // branch-free: the selects stay SEL/predicated stores, the warp does not split per child
     uint32_t cur = REF_EMPTY;
     float cure = 0.0f;
-    if(mask){
-        const unsigned word = s.octant < 4 ? ord.x : ord.y;
-        const unsigned code = (word >> ((s.octant & 3u) * 8u)) & 0xFFu;
+    int sp = s.sp;
+    const unsigned word = s.octant < 4 ? ord.x : ord.y;
+    const unsigned code = (word >> ((s.octant & 3u) * 8u)) & 0xFFu;
 #pragma unroll
-        for(int k = 0; k < 4; k++){
-            const unsigned lane = (code >> (2 * k)) & 3u;   // k = 0 is the LAST visited lane
-            if((mask >> lane) & 1u){
-                if(cur != REF_EMPTY)trav_push(stack, s.sp, cur, cure);
-                cur = pick4(refs, lane);
-                cure = lane == 0 ? e0 : (lane == 1 ? e1 : (lane == 2 ? e2 : e3));
-            }
-        }
+    for(int k = 0; k < 4; k++){
+        const unsigned lane = (code >> (2 * k)) & 3u;   // k = 0 is the LAST visited lane
+        const bool hit = ((mask >> lane) & 1u) != 0;
+        const bool hi = (lane & 2u) != 0, lo = (lane & 1u) != 0;
+        const uint32_t ra = lo ? refs.y : refs.x, rb = lo ? refs.w : refs.z;
+        const float ea = lo ? e1 : e0, eb = lo ? e3 : e2;
+        const uint32_t r = hi ? rb : ra;
+        const float e = hi ? eb : ea;
+        const bool push = hit && cur != REF_EMPTY && sp < kStack;
+        if(push)stack[sp] = make_uint2(cur, __float_as_uint(cure));
+        sp += push ? 1 : 0;
+        cur = hit ? r : cur;
+        cure = hit ? e : cure;
     }
+    s.sp = sp;
     s.cur = cur;
 }
 

@@ -54,6 +54,7 @@ PT_API int emul_scene_commit(void* p, int width){
     if(rc != PT_OK)return rc;
     e->D.n2 = e->P.n2.data(); e->D.n4 = e->P.n4.data(); e->D.tris = e->P.tris.data(); e->D.inst = e->P.insts.data();
     e->D.tlas_root = e->P.tlas_root; e->D.width = width;
+    e->D.single_root = e->P.single_root; e->D.single_id = e->P.single_id;
     for(int a = 0; a < 3; a++){ e->D.tlo[a] = e->P.bounds.lo[a]; e->D.thi[a] = e->P.bounds.hi[a]; }
     return PT_OK;
 }
