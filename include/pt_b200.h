@@ -265,6 +265,9 @@ PT_API int pt_render(pt_scene*, const pt_camera_desc*, const pt_render_params*,
 PT_API int pt_film_device_ptr(pt_scene*, void** d_film, size_t* n_doubles);
 /* Film readback: rgbw[4*W*H] doubles, row 0 first (Film.hpp:125-132 layout). */
 PT_API int pt_film_download(pt_scene*, double* rgbw);
+/* per-pixel sum of squared sample radiance, sumsq[3*W*H] (sample assigned to pixel floor(p)): what
+ * VarianceEstimator (Util.hpp:8-43) accumulates per pixel in Integrators.cpp:78-81.             */
+PT_API int pt_film_download_sumsq(pt_scene*, double* sumsq);
 PT_API int pt_film_upload(pt_scene*, const double* rgbw, int width, int height);
 
 #ifdef __cplusplus

@@ -93,7 +93,7 @@ EXPORTS = [
     "pt_scene_add_blas", "pt_scene_add_instance", "pt_scene_add_light", "pt_scene_set_medium",
     "pt_scene_commit", "pt_scene_bounds", "pt_trace_closest", "pt_trace_any",
     "pt_trace_closest_dev", "pt_trace_any_dev", "pt_trace_closest_stats", "pt_render",
-    "pt_film_device_ptr", "pt_film_download", "pt_film_upload",
+    "pt_film_device_ptr", "pt_film_download", "pt_film_download_sumsq", "pt_film_upload",
 ]
 
 _lib = None
@@ -151,6 +151,8 @@ def load_library(path: os.PathLike | None = None) -> C.CDLL:
     lib.pt_film_device_ptr.argtypes = [vp, C.POINTER(vp), C.POINTER(sz)]
     lib.pt_film_download.restype = i
     lib.pt_film_download.argtypes = [vp, vp]
+    lib.pt_film_download_sumsq.restype = i
+    lib.pt_film_download_sumsq.argtypes = [vp, vp]
     lib.pt_film_upload.restype = i
     lib.pt_film_upload.argtypes = [vp, vp, i, i]
     if path is None:

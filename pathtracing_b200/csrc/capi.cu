@@ -214,11 +214,24 @@ int pt_film_download(pt_scene* s, double* rgbw){
     return PT_OK;
 }
 
+int pt_film_download_sumsq(pt_scene* s, double* sumsq){
+    PT_CHECK_READY(s);
+    if(!s->buf.film_sq || !sumsq){ set_error("no film"); return PT_ERR_STATE; }
+    if(!cuda_ok(cudaDeviceSynchronize(), "sync"))return PT_ERR_CUDA;
+    if(!cuda_ok(cudaMemcpy(sumsq, s->buf.film_sq, sizeof(double) * 3 * (size_t)s->film_w * s->film_h, cudaMemcpyDeviceToHost), "D2H film_sq"))return PT_ERR_CUDA;
+    return PT_OK;
+}
+
 int pt_film_upload(pt_scene* s, const double* rgbw, int width, int height){
     PT_CHECK_READY(s);
     if(!rgbw || width <= 0 || height <= 0){ set_error("bad film"); return PT_ERR_INVALID; }
     if(s->buf.film && (s->film_w != width || s->film_h != height)){ cudaFree(s->buf.film); s->buf.film = nullptr; }
-    if(!s->buf.film && !cuda_ok(cudaMalloc(&s->buf.film, sizeof(double) * 4 * (size_t)width * height), "cudaMalloc film"))return PT_ERR_CUDA;
+    if(!s->buf.film){
+        if(s->buf.film_sq){ cudaFree(s->buf.film_sq); s->buf.film_sq = nullptr; }
+        if(!cuda_ok(cudaMalloc(&s->buf.film, sizeof(double) * 4 * (size_t)width * height), "cudaMalloc film") ||
+           !cuda_ok(cudaMalloc(&s->buf.film_sq, sizeof(double) * 3 * (size_t)width * height), "cudaMalloc film_sq") ||
+           !cuda_ok(cudaMemset(s->buf.film_sq, 0, sizeof(double) * 3 * (size_t)width * height), "memset film_sq"))return PT_ERR_CUDA;
+    }
     s->film_w = width; s->film_h = height;
     if(!cuda_ok(cudaMemcpy(s->buf.film, rgbw, sizeof(double) * 4 * (size_t)width * height, cudaMemcpyHostToDevice), "H2D film"))return PT_ERR_CUDA;
     return PT_OK;

@@ -1,12 +1,541 @@
-// render.cu — wavefront path integrator (placeholder until the kernels land).
+// render.cu — wavefront path integrator: TileIntegrator::Render (Integrators.cpp:23-129) with
+// {Simple,,Vol}PathIntegrator::Li (:131-479) unrolled into kernels over ray queues.
+//
+// One batch = up to `cap` camera samples ("slots").  Per bounce:
+//   extend  : persistent closest-hit kernel over the compact ray queue (trace.cu)
+//   shade   : one thread per queue entry: rebuild the interaction, miss / emission with MIS,
+//             medium event, BSDF sample, NEE sample -> shadow queue, Russian roulette,
+//             continuation ray -> next queue (warp-aggregated compaction)
+//   connect : persistent any-hit kernel over the shadow queue, then the unoccluded
+//             contributions are added to their slot's radiance
+// and after the last bounce the slots are splatted into the double RGBW film
+// (FilmTile::Add, Film.hpp:65-82).  Path state lives in SoA arrays indexed by slot; queues
+// carry slot ids.  Every sample owns a PCG32 stream keyed by (seed, pixel, sample index),
+// so the image does not depend on batch size or on how passes are sharded over GPUs.
 #include <cuda_runtime.h>
+#include <math_constants.h>
+#include <algorithm>
+#include <cmath>
+#include <cstdlib>
+
 #include "scene_host.hpp"
+#include "shade_mat.cuh"
+#include "shade_light.cuh"
 
 namespace ptb {
 
-int render_passes(pt_scene*, const pt_camera_desc*, const pt_render_params*, int, pt_render_stats*){
-    set_error("pt_render: not implemented yet");
-    return PT_ERR_INVALID;
+struct CamParams {      // Camera ctor, Camera.hpp:7-20
+    V3 from, u, v, w;
+    float half_w, half_h, defocus_radius, focus_distance, focus_angle, shutter0, shutter1;
+    int medium;
+};
+
+struct FilterParams {   // Filter.hpp:29-144
+    int kind, rx, ry;   // integer splat radius = ceil(radius - 0.5)
+    float radx, rady;
+    double p0, p1, gx, gy, inv_integral;
+};
+
+struct Arena {
+    float4* rays[2]; uint32_t* qslot[2];
+    float4* hits; uint32_t* hinst;
+    float4* srays; uint32_t* sslot; float4* scontrib; uint8_t* socc;
+    float4* thr;        // throughput rgb, prevPDF
+    float4* rad;        // radiance rgb
+    uint32_t* depth;    // depth (low 16) | rr_depth (high 16)
+    uint32_t* mflag;    // bit0 spec, bits 1..: medium id + 1
+    uint64_t* rng;      // pcg state (inc is rebuilt from the sample id)
+    float2* spos;       // fractional sample position inside the pixel
+    uint32_t* counters; // [0] next-queue size, [1] shadow-queue size
+};
+
+struct BatchInfo {
+    uint64_t first;     // first global sample id of the batch: id = pass_k * W*H + pixel
+    uint32_t count;
+    int W, H, pass_begin, pass_stride, max_depth;
+    uint64_t seed;
+};
+
+__device__ __forceinline__ uint64_t stream_of(const BatchInfo& B, uint32_t slot, uint32_t& pixel, uint32_t& sample){
+    const uint64_t g = B.first + slot;
+    const uint64_t wh = (uint64_t)B.W * B.H;
+    pixel = (uint32_t)(g % wh);
+    sample = (uint32_t)(B.pass_begin + (g / wh) * B.pass_stride);
+    return (uint64_t)sample * wh + pixel;
+}
+
+// warp-aggregated queue append: one atomic per warp
+__device__ __forceinline__ uint32_t queue_slot(uint32_t* counter, bool want){
+    const unsigned m = __ballot_sync(0xffffffffu, want);
+    if(!m)return 0;
+    const unsigned lane = threadIdx.x & 31u;
+    const int leader = __ffs(m) - 1;
+    uint32_t base = 0;
+    if((int)lane == leader)base = atomicAdd(counter, (uint32_t)__popc(m));
+    base = __shfl_sync(0xffffffffu, base, leader);
+    return base + __popc(m & ((1u << lane) - 1u));
+}
+
+// ---- generate: StartPixelSample / getPixel2D / get1D / get2D / Camera::GenerateRay (Integrators.cpp:61-64) ----
+__global__ void __launch_bounds__(256) k_generate(Arena A, BatchInfo B, CamParams C){
+    const uint32_t slot = blockIdx.x * blockDim.x + threadIdx.x;
+    if(slot >= B.count)return;
+    uint32_t pixel, sample;
+    const uint64_t stream = stream_of(B, slot, pixel, sample);
+    Pcg g = pcg_seed(B.seed, stream);
+    const int x = (int)(pixel % (uint32_t)B.W), y = (int)(pixel / (uint32_t)B.W);
+    const double jx = rnd_double(g), jy = rnd_double(g);        // UniformSampler::getPixel2D
+    const float time = (float)rnd_double(g);
+    const float lx = (float)rnd_double(g), ly = (float)rnd_double(g);
+    const float px = (float)((double)x + jx), py = (float)((double)y + jy);   // GenerateRay takes a glm::vec2
+    const float uc = px / (float)B.W, vc = py / (float)B.H;
+    V3 dir = normalize(-C.w + ((2.0f * uc - 1.0f) * C.half_w) * C.u + ((2.0f * vc - 1.0f) * C.half_h) * C.v);
+    V3 org = C.from;
+    const float t = C.shutter0 + (C.shutter1 - C.shutter0) * time;
+    if(!(C.focus_distance == 0.0f || C.focus_angle == 0.0f)){
+        const float r = sqrtf(lx), th = 2.0f * kPi * ly;          // inUnitDisk, Random.hpp:60-64
+        const V3 off = (r * cosf(th)) * (C.u * C.defocus_radius) + (r * sinf(th)) * (C.v * C.defocus_radius);
+        dir = dir * C.focus_distance;
+        org = C.from + off;
+        dir = normalize(dir - off);
+    }
+    A.rays[0][2 * (size_t)slot] = make_float4(org.x, org.y, org.z, CUDART_INF_F);
+    A.rays[0][2 * (size_t)slot + 1] = make_float4(dir.x, dir.y, dir.z, t);
+    A.qslot[0][slot] = slot;
+    A.thr[slot] = make_float4(1.0f, 1.0f, 1.0f, 1.0f);
+    A.rad[slot] = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+    A.depth[slot] = 1u;                                          // `depth++ < maxDepth` already taken for bounce 1
+    A.mflag[slot] = 1u | ((uint32_t)(C.medium + 1) << 1);
+    A.rng[slot] = g.state;
+    A.spos[slot] = make_float2((float)jx, (float)jy);
+}
+
+// ---- connect: add the unoccluded NEE contributions (Integrators.cpp:243-244, 356, 398) ------
+__global__ void __launch_bounds__(256) k_connect(Arena A, uint32_t n){
+    const uint32_t k = blockIdx.x * blockDim.x + threadIdx.x;
+    if(k >= n || A.socc[k])return;
+    const uint32_t slot = A.sslot[k];
+    const float4 c = A.scontrib[k];
+    float4 r = A.rad[slot];
+    r.x += c.x; r.y += c.y; r.z += c.z;
+    A.rad[slot] = r;
+}
+
+// ---- film: FilmTile::Add + Film::Merge (Film.hpp:65-82,125-132) ------------------------------
+__device__ inline double filter_eval(const FilterParams& F, float x, float y){
+    switch(F.kind){
+    case PT_FILTER_BOX: return (fabsf(x) <= F.radx && fabsf(y) <= F.rady) ? 1.0 : 0.0;
+    case PT_FILTER_GAUSSIAN: {
+        const double s = F.p0, k = 0.5641895835477563 / (s * 1.4142135623730951);
+        const double gx = k * exp(-((double)x * x) / (2 * s * s)), gy = k * exp(-((double)y * y) / (2 * s * s));
+        return fmax(0.0, gx - F.gx) * fmax(0.0, gy - F.gy);
+    }
+    case PT_FILTER_MITCHELL: {
+        const double b = F.p0, c = F.p1;
+        double r = 1.0;
+        const double xs[2] = { 2.0 * x / F.radx, 2.0 * y / F.rady };
+        for(int k = 0; k < 2; k++){
+            const double a = fabs(xs[k]);
+            double m;
+            if(a <= 1.0)m = 1.0 / 6.0 * ((12 - 9 * b - 6 * c) * a * a * a + (-18 + 12 * b + 6 * c) * a * a + (6 - 2 * b));
+            else if(a <= 2.0)m = 1.0 / 6.0 * ((-b - 6 * c) * a * a * a + (6 * b + 30 * c) * a * a + (-12 * b - 48 * c) * a + (8 * b + 24 * c));
+            else m = 0.0;
+            r *= m;
+        }
+        return r;
+    }
+    default: {  // Lanczos: WindowedSinc(x, radius, tau)
+        double r = 1.0;
+        const double xs[2] = { x, y }, rs[2] = { F.radx, F.rady };
+        for(int k = 0; k < 2; k++){
+            const double a = xs[k];
+            double w;
+            if(fabs(a) > rs[k])w = 0.0;
+            else{
+                const double pi = 3.141592653589793;
+                const double s1 = (1.0 - a * a == 1.0) ? 1.0 : sin(pi * a) / (pi * a);
+                const double at = a / F.p0;
+                const double s2 = (1.0 - at * at == 1.0) ? 1.0 : sin(pi * at) / (pi * at);
+                w = s1 * s2;
+            }
+            r *= w;
+        }
+        return r;
+    }
+    }
+}
+
+__global__ void __launch_bounds__(256) k_film(Arena A, BatchInfo B, FilterParams F, double* __restrict__ film, double* __restrict__ film_sq){
+    const uint32_t slot = blockIdx.x * blockDim.x + threadIdx.x;
+    if(slot >= B.count)return;
+    uint32_t pixel, sample;
+    stream_of(B, slot, pixel, sample);
+    const int x = (int)(pixel % (uint32_t)B.W), y = (int)(pixel / (uint32_t)B.W);
+    const float4 r = A.rad[slot];
+    const float2 sp = A.spos[slot];
+    {   // per-pixel sum of squared sample radiance (owner pixel): the variance the 3-sigma parity test
+        // and VarianceEstimator (Util.hpp:8-43) need
+        double* q = film_sq + 3 * ((size_t)y * B.W + x);
+        atomicAdd(q, (double)r.x * r.x); atomicAdd(q + 1, (double)r.y * r.y); atomicAdd(q + 2, (double)r.z * r.z);
+    }
+    for(int dy = -F.ry; dy <= F.ry; dy++)for(int dx = -F.rx; dx <= F.rx; dx++){
+        const float fx = (float)((double)dx + 0.5 - (double)sp.x), fy = (float)((double)dy + 0.5 - (double)sp.y);   // Filter::Evaluate takes a glm::vec2
+        const double w = filter_eval(F, fx, fy) * F.inv_integral;
+        const int qx = x + dx, qy = y + dy;
+        if(w <= 0.0 || qx < 0 || qy < 0 || qx >= B.W || qy >= B.H)continue;
+        double* q = film + 4 * ((size_t)qy * B.W + qx);
+        atomicAdd(q, (double)r.x * w); atomicAdd(q + 1, (double)r.y * w); atomicAdd(q + 2, (double)r.z * w); atomicAdd(q + 3, w);
+    }
+}
+
+// ---- shade: one bounce of Li() for every queue entry ------------------------------------------
+
+struct NeeOut { bool want; V3 o, d; float tmax; V3 contrib; };
+
+// PathIntegrator::SampleLd (Integrators.cpp:260-294) / VolPathIntegrator::SampleLd (:426-479) up to the
+// visibility test, which the connect stage resolves.  `medium_pt`: the interaction is a medium event.
+template <int INTEG>
+__device__ inline void sample_ld(const ShadeScene& S, const SurfInt& si, bool medium_pt, V3 ip, V3 rd, float hg_g, int cur_medium,
+                                 float u_sel, float ux, float uy, Pcg& rng, NeeOut& out){
+    out.want = false;
+    const int li = pick_light(S, u_sel);
+    if(li < 0)return;
+    const DevLight& L = S.lights[li];
+    LightSmp ls;
+    light_sample(S, L, ux, uy, rng, ls);
+    V3 ldir; float t;
+    if(is_zero(ls.n)){ ldir = ls.dir; t = CUDART_INF_F; }
+    else{
+        ldir = ls.p - ip;
+        t = length(ldir) - kEps;
+        if(INTEG == PT_INTEGRATOR_VOLPATH)t -= kEps;
+    }
+    const V3 sd = normalize(ldir);
+    float pmf = L.pmf_sample;
+    if(pmf <= 0.0f)return;
+    V3 f; float spdf;
+    if(medium_pt){
+        spdf = phase_hg(dot(rd, sd), hg_g);
+        f = v3(spdf);
+    } else{
+        const float d = dot(si.ns, sd);
+        if(d * dot(rd, si.ns) >= 0.0f)return;
+        f = mat_eval(S, si, rd, sd) * fabsf(d);
+        spdf = mat_pdf(S, si, rd, sd);
+    }
+    if(INTEG == PT_INTEGRATOR_VOLPATH && is_zero(f))return;
+    V3 c;
+    if(light_is_delta(L))c = ls.L * f / pmf;
+    else{
+        pmf *= light_pdf_sampled(S, L, ls.p, ls.n, ip, sd);
+        if(pmf <= 0.0f)return;
+        const float w2 = pmf * pmf, w1 = spdf * spdf;
+        c = light_L_sampled(S, L, ls, sd) * f * (w2 / (w1 + w2)) / pmf;
+    }
+    if(INTEG == PT_INTEGRATOR_VOLPATH && cur_medium >= 0)c = c * medium_Tr(S.media[cur_medium], t);   // Scene::IntersectTr, miss leg (Scene.cpp:13-17)
+    out.want = true; out.o = ip; out.d = sd; out.tmax = t; out.contrib = c;
+}
+
+template <int INTEG>
+__global__ void __launch_bounds__(128) k_shade(Arena A, ShadeScene S, BatchInfo B, uint32_t n, int cur){
+    const uint32_t j = blockIdx.x * blockDim.x + threadIdx.x;
+    bool cont = false, nee = false;
+    V3 no = v3(0.0f), nd = v3(0.0f); float ntime = 0.0f;
+    NeeOut ne; ne.want = false;
+    uint32_t slot = 0;
+    if(j < n){
+        slot = A.qslot[cur][j];
+        const float4 ra = A.rays[cur][2 * (size_t)j], rb = A.rays[cur][2 * (size_t)j + 1];
+        const V3 ro = v3(ra.x, ra.y, ra.z), rd = v3(rb.x, rb.y, rb.z);
+        ntime = rb.w;
+        const float4 h = A.hits[j];
+        const uint32_t prim = __float_as_uint(h.w);
+        float4 thr4 = A.thr[slot];
+        V3 att = v3(thr4.x, thr4.y, thr4.z);
+        float prev_pdf = thr4.w;
+        float4 rad4 = A.rad[slot];
+        V3 outp = v3(rad4.x, rad4.y, rad4.z);
+        uint32_t dw = A.depth[slot], mf = A.mflag[slot];
+        uint32_t depth = dw & 0xFFFFu, rr_depth = dw >> 16;
+        bool spec = (mf & 1u) != 0;
+        int medium = (int)(mf >> 1) - 1;
+        uint32_t pixel, sample;
+        Pcg g; g.inc = (stream_of(B, slot, pixel, sample) << 1u) | 1u; g.state = A.rng[slot];
+
+        if(prim == 0xFFFFFFFFu){
+            // miss: infinite lights (Integrators.cpp:136-141, 197-207, 308-330)
+            for(int k = 0; k < S.n_inf_lights; k++){
+                const DevLight& L = S.lights[S.inf_lights[k]];
+                const V3 le = inf_Le(S, L, rd);
+                if(INTEG == PT_INTEGRATOR_SIMPLE || spec)outp += att * le;
+                else if(prev_pdf > 0.0f){
+                    const float lp = L.pmf_sample * light_pdf_sampled(S, L, v3(0.0f), v3(0.0f), ro, rd);
+                    outp += att * le * (prev_pdf * prev_pdf / (prev_pdf * prev_pdf + lp * lp));
+                }
+            }
+        } else{
+            SurfInt si;
+            build_interaction(S, ro, rd, h.x, h.y, h.z, prim, A.hinst[j], si);
+            bool med_event = false; float med_dist = 0.0f;
+            int ray_medium = -1;        // ray.medium while this bounce is evaluated (the shadow ray inherits it)
+            if(INTEG == PT_INTEGRATOR_VOLPATH){
+                if(medium < 0)medium = S.scene_medium;                           // Integrators.cpp:340-341
+                ray_medium = medium;
+                if(medium >= 0)att *= medium_sample(S.media[medium], si.t, g, med_event, med_dist);
+            }
+            float r[8]; float rr;
+            if(INTEG == PT_INTEGRATOR_SIMPLE){
+                r[0] = (float)rnd_double(g); r[1] = (float)rnd_double(g); r[4] = (float)rnd_double(g); rr = (float)rnd_double(g);
+                r[2] = r[3] = r[5] = r[6] = r[7] = 0.0f;
+            } else{
+#pragma unroll
+                for(int k = 0; k < 8; k++)r[k] = rnd_x8(g);                       // Sampler::get2Dx4f
+                rr = INTEG == PT_INTEGRATOR_VOLPATH ? (float)rnd_double(g) : r[6];
+            }
+            bool alive = true, skip_rr = false;
+            if(INTEG == PT_INTEGRATOR_VOLPATH && med_event){
+                // medium event (Integrators.cpp:356-362)
+                const DevMedium& M = S.media[medium];
+                const V3 mp = ro + med_dist * rd;
+                sample_ld<INTEG>(S, si, true, mp, rd, M.g, medium, r[5], r[2], r[3], g, ne);
+                if(ne.want)ne.contrib = att * ne.contrib;
+                outp += att * ld3(M.Le);
+                no = mp; nd = hg_sample(M.g, rd, r[6], r[7]);
+                medium = dot(nd, si.n) < 0.0f ? si.medium : -1;                  // interaction.getMedium(scattered)
+                spec = false;
+            } else{
+                // emitted radiance with MIS against NEE (Integrators.cpp:153-156, 217-226, 364-373)
+                if(si.light >= 0){
+                    const DevLight& L = S.lights[si.light];
+                    const V3 le = tex_eval(S, L.tex, si.u, si.v, si.ns);          // AreaLight::L, two-sided
+                    if(!is_zero(le)){
+                        if(INTEG == PT_INTEGRATOR_SIMPLE || spec)outp += att * le;
+                        else if(prev_pdf > 0.0f){
+                            // PMF and PDF of interaction.AreaLight: the inner, untransformed light, world-space p / n
+                            const float lp = L.pmf_hit * tri_pdf(si.p, si.n, ro, rd, L.area);
+                            outp += att * le * (prev_pdf * prev_pdf / (prev_pdf * prev_pdf + lp * lp));
+                        }
+                    }
+                }
+                if(INTEG == PT_INTEGRATOR_VOLPATH)spec = false;                   // Integrators.cpp:374
+                if(si.mat < 0){
+                    // medium boundary (Integrators.cpp:158-161, 228-232, 378-382): continue without RR
+                    if(INTEG == PT_INTEGRATOR_PATH)spec = true;
+                    no = ro + si.t * rd; nd = rd;
+                    if(INTEG == PT_INTEGRATOR_VOLPATH)medium = dot(rd, si.n) < 0.0f ? si.medium : -1;
+                    skip_rr = true;
+                } else{
+                    Scatter sc;
+                    if(!mat_scatter(S, si, ro, rd, r[4], r[0], r[1], sc))alive = false;   // absorbed
+                    else{
+                        if(INTEG == PT_INTEGRATOR_VOLPATH){
+                            int nm = dot(sc.d, si.n) < 0.0f ? si.medium : -1;
+                            if(!(sc.flags & BX_TRANSMISSIVE) && dot(rd, si.ns) <= 0.0f)nm = medium;   // Integrators.cpp:389-394
+                            medium = nm;
+                        }
+                        if(INTEG != PT_INTEGRATOR_SIMPLE){
+                            spec = (sc.flags & BX_SPECULAR) != 0;
+                            if(!spec){
+                                sample_ld<INTEG>(S, si, false, si.p, rd, 0.0f, ray_medium, r[5], r[2], r[3], g, ne);
+                                if(ne.want)ne.contrib = att * ne.contrib;
+                                prev_pdf = mat_pdf(S, si, rd, sc.d);
+                            }
+                        }
+                        att *= sc.f * (fabsf(dot(si.ns, sc.d)) / sc.pdf);
+                        no = sc.o; nd = sc.d;
+                    }
+                }
+            }
+            if(alive && !skip_rr){
+                // Russian roulette (Integrators.cpp:171-175, 249-253, 411-416)
+                if(rr_depth++ > 3){
+                    const float q = fminf(0.95f, fmaxf(fmaxf(att.x, att.y), att.z));
+                    if(rr >= q)alive = false;
+                    else att = att / q;
+                }
+            }
+            // loop condition of the next iteration: depth++ < maxDepth && sum(attenuation) > 0
+            if(alive && (int)depth < B.max_depth && (att.x + att.y + att.z) > 0.0f){ cont = true; depth++; }
+        }
+        nee = ne.want;
+        A.thr[slot] = make_float4(att.x, att.y, att.z, prev_pdf);
+        A.rad[slot] = make_float4(outp.x, outp.y, outp.z, 0.0f);
+        A.depth[slot] = depth | (rr_depth << 16);
+        A.mflag[slot] = (spec ? 1u : 0u) | ((uint32_t)(medium + 1) << 1);
+        A.rng[slot] = g.state;
+    }
+    const uint32_t qn = queue_slot(A.counters + 0, cont);
+    if(cont){
+        A.rays[cur ^ 1][2 * (size_t)qn] = make_float4(no.x, no.y, no.z, CUDART_INF_F);
+        A.rays[cur ^ 1][2 * (size_t)qn + 1] = make_float4(nd.x, nd.y, nd.z, ntime);
+        A.qslot[cur ^ 1][qn] = slot;
+    }
+    const uint32_t qs = queue_slot(A.counters + 1, nee);
+    if(nee){
+        A.srays[2 * (size_t)qs] = make_float4(ne.o.x, ne.o.y, ne.o.z, ne.tmax);
+        A.srays[2 * (size_t)qs + 1] = make_float4(ne.d.x, ne.d.y, ne.d.z, ntime);
+        A.sslot[qs] = slot;
+        A.scontrib[qs] = make_float4(ne.contrib.x, ne.contrib.y, ne.contrib.z, 0.0f);
+    }
+}
+
+// ---- host driver --------------------------------------------------------------------------------
+
+static int make_filter(const pt_render_params* rp, FilterParams& F){
+    F.kind = rp->filter; F.radx = rp->filter_radius[0]; F.rady = rp->filter_radius[1];
+    F.p0 = rp->filter_param[0]; F.p1 = rp->filter_param[1]; F.gx = F.gy = 0.0;
+    if(!(F.radx > 0.0f) || !(F.rady > 0.0f)){ set_error("filter radius must be positive"); return PT_ERR_INVALID; }
+    F.rx = (int)std::ceil(F.radx - 0.5f); F.ry = (int)std::ceil(F.rady - 0.5f);     // FilmTile ctor, Film.hpp:58
+    double integral = 1.0;
+    switch(rp->filter){
+    case PT_FILTER_BOX: integral = 4.0 * F.radx * F.rady; break;
+    case PT_FILTER_GAUSSIAN: {
+        const double s = F.p0;
+        if(!(s > 0)){ set_error("gaussian sigma must be positive"); return PT_ERR_INVALID; }
+        auto G = [&](double x){ return 0.5641895835477563 / (s * 1.4142135623730951) * std::exp(-(x * x) / (2 * s * s)); };
+        auto GI = [&](double x0, double x1){ const double r2 = s * 1.4142135623730951; return 0.5 * (std::erf(-x0 / r2) - std::erf(-x1 / r2)); };
+        F.gx = G(F.radx); F.gy = G(F.rady);
+        integral = (GI(-F.radx, F.radx) - 2 * F.radx * F.gx) * (GI(-F.rady, F.rady) - 2 * F.rady * F.gy);
+        break;
+    }
+    case PT_FILTER_MITCHELL: integral = (double)F.radx * F.rady / 4.0; break;
+    case PT_FILTER_LANCZOS: {
+        // LanczosFilter::Integral (Filter.hpp:126-139): 256x256 strata over [-r, r]^2 with "area" 2*rx*ry;
+        // strata centres here instead of an unseeded jitter
+        if(!(F.p0 > 0)){ set_error("lanczos tau must be positive"); return PT_ERR_INVALID; }
+        auto sinc = [](double x){ const double pi = 3.141592653589793; return (1.0 - x * x == 1.0) ? 1.0 : std::sin(pi * x) / (pi * x); };
+        auto ws = [&](double x, double r){ return std::fabs(x) > r ? 0.0 : sinc(x) * sinc(x / F.p0); };
+        double acc = 0;
+        for(int y = 0; y < 256; y++)for(int x = 0; x < 256; x++){
+            const float ux = (float)((x + 0.5) / 256.0), uy = (float)((y + 0.5) / 256.0);
+            const float px = -F.radx + 2 * F.radx * ux, py = -F.rady + 2 * F.rady * uy;
+            acc += ws(px, F.radx) * ws(py, F.rady);
+        }
+        integral = 2.0 * F.radx * F.rady * acc / 65536.0;
+        break;
+    }
+    default: set_error("unknown filter"); return PT_ERR_INVALID;
+    }
+    F.inv_integral = 1.0 / integral;
+    return PT_OK;
+}
+
+static void make_camera(const pt_camera_desc* c, int W, int H, CamParams& C){
+    const V3 from = v3(c->look_from[0], c->look_from[1], c->look_from[2]), at = v3(c->look_at[0], c->look_at[1], c->look_at[2]);
+    C.from = from;
+    C.w = normalize(from - at);
+    C.u = normalize(cross(v3(0, 1, 0), C.w));
+    C.v = cross(C.w, C.u);
+    C.defocus_radius = (float)(c->focus_distance * std::tan(c->focus_angle / 2.0));
+    C.half_w = (float)std::tan(c->fov * 0.5);
+    C.half_h = C.half_w * (float)H / (float)W;
+    C.focus_distance = c->focus_distance; C.focus_angle = c->focus_angle;
+    C.shutter0 = c->shutter_start; C.shutter1 = c->shutter_end;
+    C.medium = c->medium;
+}
+
+static bool carve(char*& p, void** out, size_t bytes){ *out = p; p += (bytes + 255) & ~(size_t)255; return true; }
+
+static size_t arena_layout(char* base, Arena& A, size_t cap){
+    char* p = base;
+    carve(p, (void**)&A.rays[0], cap * 32); carve(p, (void**)&A.rays[1], cap * 32);
+    carve(p, (void**)&A.qslot[0], cap * 4); carve(p, (void**)&A.qslot[1], cap * 4);
+    carve(p, (void**)&A.hits, cap * 16); carve(p, (void**)&A.hinst, cap * 4);
+    carve(p, (void**)&A.srays, cap * 32); carve(p, (void**)&A.sslot, cap * 4); carve(p, (void**)&A.scontrib, cap * 16); carve(p, (void**)&A.socc, cap);
+    carve(p, (void**)&A.thr, cap * 16); carve(p, (void**)&A.rad, cap * 16); carve(p, (void**)&A.depth, cap * 4); carve(p, (void**)&A.mflag, cap * 4);
+    carve(p, (void**)&A.rng, cap * 8); carve(p, (void**)&A.spos, cap * 8); carve(p, (void**)&A.counters, 256);
+    return (size_t)(p - base);
+}
+
+int render_passes(pt_scene* s, const pt_camera_desc* cam, const pt_render_params* rp, int clear, pt_render_stats* stats){
+    const int W = rp->width, H = rp->height;
+    if(W <= 0 || H <= 0 || W > 65535 || H > 65535){ set_error("bad resolution"); return PT_ERR_INVALID; }   // Film stores uint16_t (Film.hpp:266-267)
+    if(rp->spp <= 0 || rp->max_depth < 0 || rp->pass_stride <= 0 || rp->pass_begin < 0){ set_error("bad spp / depth / pass range"); return PT_ERR_INVALID; }
+    if(rp->integrator < PT_INTEGRATOR_SIMPLE || rp->integrator > PT_INTEGRATOR_VOLPATH){ set_error("unknown integrator"); return PT_ERR_INVALID; }
+    if(rp->sampler != 0){ set_error("StratifiedSampler is not built yet: use sampler = 0 (UniformSampler)"); return PT_ERR_INVALID; }
+    if(rp->adaptive){ set_error("adaptive sampling is not built yet: use adaptive = 0 (exactly spp samples per pixel)"); return PT_ERR_INVALID; }
+    if(cam->medium >= (int)s->media.size()){ set_error("camera medium id out of range"); return PT_ERR_INVALID; }
+    FilterParams F;
+    int rc = make_filter(rp, F);
+    if(rc != PT_OK)return rc;
+    CamParams C;
+    make_camera(cam, W, H, C);
+    cudaStream_t st = (cudaStream_t)s->stream;
+    DeviceBuffers& b = s->buf;
+    const size_t film_bytes = sizeof(double) * 4 * (size_t)W * H;
+    if(b.film && (s->film_w != W || s->film_h != H)){ cudaFree(b.film); b.film = nullptr; }
+    if(!b.film){
+        if(b.film_sq){ cudaFree(b.film_sq); b.film_sq = nullptr; }
+        if(!cuda_ok(cudaMalloc(&b.film, film_bytes), "cudaMalloc film") || !cuda_ok(cudaMalloc(&b.film_sq, film_bytes / 4 * 3), "cudaMalloc film_sq"))return PT_ERR_CUDA;
+        clear = 1;
+    }
+    s->film_w = W; s->film_h = H;
+    if(clear && (!cuda_ok(cudaMemsetAsync(b.film, 0, film_bytes, st), "film clear") ||
+                 !cuda_ok(cudaMemsetAsync(b.film_sq, 0, film_bytes / 4 * 3, st), "film clear")))return PT_ERR_CUDA;
+
+    // passes of this call: pass_begin, pass_begin + stride, ... < spp
+    const uint64_t n_pass = rp->pass_begin >= rp->spp ? 0 : (uint64_t)(rp->spp - rp->pass_begin + rp->pass_stride - 1) / rp->pass_stride;
+    const uint64_t total = n_pass * (uint64_t)W * H;
+    size_t cap = 4u << 20;
+    if(const char* e = getenv("PTB_BATCH")){ const long long v = atoll(e); if(v >= 1024)cap = (size_t)v; }
+    if(cap > total)cap = (size_t)std::max<uint64_t>(total, 1);
+    Arena A;
+    const size_t need = arena_layout(nullptr, A, cap);
+    if(need > b.work_bytes){
+        if(b.work){ cudaFree(b.work); b.work = nullptr; b.work_bytes = 0; }
+        if(!cuda_ok(cudaMalloc(&b.work, need), "cudaMalloc wavefront arena"))return PT_ERR_NOMEM;
+        b.work_bytes = need;
+    }
+    arena_layout((char*)b.work, A, cap);
+    uint32_t* h_counters = nullptr;
+    if(!cuda_ok(cudaMallocHost(&h_counters, 64), "pinned counters"))return PT_ERR_CUDA;
+    cudaEvent_t e0, e1;
+    cudaEventCreate(&e0); cudaEventCreate(&e1);
+    cudaEventRecord(e0, st);
+    pt_render_stats R {};
+    auto fail = [&](int code){ cudaFreeHost(h_counters); cudaEventDestroy(e0); cudaEventDestroy(e1); return code; };
+
+    for(uint64_t first = 0; first < total; first += cap){
+        BatchInfo B;
+        B.first = first; B.count = (uint32_t)std::min<uint64_t>(cap, total - first);
+        B.W = W; B.H = H; B.pass_begin = rp->pass_begin; B.pass_stride = rp->pass_stride; B.max_depth = rp->max_depth; B.seed = rp->seed;
+        k_generate<<<(B.count + 255) / 256, 256, 0, st>>>(A, B, C);
+        R.kernel_launches++;
+        uint32_t n = rp->max_depth > 0 ? B.count : 0;    // `depth++ < maxDepth` fails at once: black samples
+        int cur = 0;
+        while(n > 0){
+            rc = launch_trace_closest(s, A.rays[cur], n, A.hits, A.hinst, st);
+            if(rc != PT_OK)return fail(rc);
+            R.closest_rays += n; R.kernel_launches++;
+            if(!cuda_ok(cudaMemsetAsync(A.counters, 0, 8, st), "counter reset"))return fail(PT_ERR_CUDA);
+            const unsigned grid = (n + 127) / 128;
+            switch(rp->integrator){
+            case PT_INTEGRATOR_SIMPLE: k_shade<PT_INTEGRATOR_SIMPLE><<<grid, 128, 0, st>>>(A, s->shade, B, n, cur); break;
+            case PT_INTEGRATOR_PATH: k_shade<PT_INTEGRATOR_PATH><<<grid, 128, 0, st>>>(A, s->shade, B, n, cur); break;
+            default: k_shade<PT_INTEGRATOR_VOLPATH><<<grid, 128, 0, st>>>(A, s->shade, B, n, cur); break;
+            }
+            R.kernel_launches++;
+            if(!cuda_ok(cudaMemcpyAsync(h_counters, A.counters, 8, cudaMemcpyDeviceToHost, st), "counters D2H") ||
+               !cuda_ok(cudaStreamSynchronize(st), "shade"))return fail(PT_ERR_CUDA);
+            const uint32_t n_next = h_counters[0], n_sh = h_counters[1];
+            if(n_sh > 0){
+                rc = launch_trace_any(s, A.srays, n_sh, A.socc, st);
+                if(rc != PT_OK)return fail(rc);
+                k_connect<<<(n_sh + 255) / 256, 256, 0, st>>>(A, n_sh);
+                R.shadow_rays += n_sh; R.kernel_launches += 2;
+            }
+            n = n_next; cur ^= 1;
+        }
+        k_film<<<(B.count + 255) / 256, 256, 0, st>>>(A, B, F, (double*)b.film, (double*)b.film_sq);
+        R.kernel_launches++;
+        R.samples += B.count;
+    }
+    cudaEventRecord(e1, st);
+    if(!cuda_ok(cudaStreamSynchronize(st), "render"))return fail(PT_ERR_CUDA);
+    float ms = 0; cudaEventElapsedTime(&ms, e0, e1);
+    R.gpu_ms = ms;
+    if(stats)*stats = R;
+    return fail(PT_OK);
 }
 
 } // namespace ptb

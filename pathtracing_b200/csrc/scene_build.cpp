@@ -81,6 +81,9 @@ int scene_add_blas(pt_scene* s, const int32_t* mesh_ids, int n){
     HostBlas b;
     for(int i = 0; i < n; i++){
         if(mesh_ids[i] < 0 || mesh_ids[i] >= (int)s->meshes.size()){ set_error("mesh id out of range"); return PT_ERR_INVALID; }
+        // a Mesh belongs to one Model / BLAS (Model.hpp:41-60); share geometry through instances instead
+        for(const HostBlas& o : s->blas)for(int m : o.meshes)if(m == mesh_ids[i]){ set_error("mesh already belongs to another BLAS"); return PT_ERR_INVALID; }
+        for(int m : b.meshes)if(m == mesh_ids[i]){ set_error("mesh listed twice in one BLAS"); return PT_ERR_INVALID; }
         b.meshes.push_back(mesh_ids[i]);
     }
     s->blas.push_back(std::move(b));

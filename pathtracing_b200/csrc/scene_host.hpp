@@ -51,6 +51,7 @@ struct DeviceBuffers {
     void* textures = nullptr; void* texels = nullptr; void* materials = nullptr; void* media = nullptr;
     void* lights = nullptr; void* light_cdf = nullptr; void* env_cdf = nullptr;
     void* film = nullptr;
+    void* film_sq = nullptr;      // per-pixel sum of squared sample radiance, double[3*W*H]
     void* work = nullptr;         // wavefront state arena
     size_t work_bytes = 0;
     // staging for the host-buffer ray-cast entry points

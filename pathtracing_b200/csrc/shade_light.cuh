@@ -1,0 +1,155 @@
+// shade_light.cuh — LightSampler::{Sample,PMF} (LightSampler.cpp), Light::{sample,
+// PDF,L} for every light class (Light.cpp) incl. TransformedLight, and the
+// homogeneous medium + Henyey-Greenstein phase function (Medium.hpp,
+// PhaseFunction.cpp).
+#pragma once
+#include "shade.cuh"
+
+namespace ptb {
+
+// UniformLightSampler::Sample (LightSampler.cpp:7-11) / PowerLightSampler::Sample (:34-46)
+__device__ inline int pick_light(const ShadeScene& S, float u){
+    const int n = S.n_sampler_lights;
+    if(n == 0)return -1;
+    if(S.sampler_kind == 0){
+        int i = (int)(u * n);
+        if(i > n - 1)i = n - 1;
+        return S.sampler_lights[i];
+    }
+    // first i with cdf[i] >= u * totalPower, else the last light; the cdf is the reference's running float sum
+    const float power = u * S.total_power;
+    int lo = 0, hi = n;
+    while(lo < hi){
+        const int mid = (lo + hi) >> 1;
+        if(S.sampler_cdf[mid] >= power)hi = mid; else lo = mid + 1;
+    }
+    if(lo >= n)lo = n - 1;
+    return S.sampler_lights[lo];
+}
+
+// LightSample (Light.hpp:6-14) with what SampleLd needs from it
+struct LightSmp {
+    V3 L;          // radiance carried by the sample (delta lights only)
+    V3 p, n;       // sampled point / normal; n == 0 marks a direction sample (isDeltaInteraction)
+    V3 dir;
+    float u, v;    // texcoords of the sampled point
+};
+
+__device__ inline void tri_vertices(const ShadeScene& S, const DevLight& L, V3& v0, V3& v1, V3& v2, uint32_t& i0, uint32_t& i1, uint32_t& i2){
+    const DevMesh& m = S.meshes[L.mesh];
+    i0 = m.vtx_base + S.idx[m.idx_base + 3 * L.tri]; i1 = m.vtx_base + S.idx[m.idx_base + 3 * L.tri + 1]; i2 = m.vtx_base + S.idx[m.idx_base + 3 * L.tri + 2];
+    v0 = ld3(S.pos + 3 * (size_t)i0); v1 = ld3(S.pos + 3 * (size_t)i1); v2 = ld3(S.pos + 3 * (size_t)i2);
+}
+
+// Light::sample(uv, time).  `rng` feeds TextureInfiniteLight::sample's extra random_float (Light.cpp:120).
+__device__ inline void light_sample(const ShadeScene& S, const DevLight& L, float ux, float uy, Pcg& rng, LightSmp& o){
+    o.L = v3(0.0f); o.p = v3(0.0f); o.n = v3(0.0f); o.dir = v3(0.0f); o.u = 0.0f; o.v = 0.0f;
+    switch(L.kind){
+    case DL_UNIFORM_INF: o.dir = sphere_dir(ux, uy); o.L = ld3(L.color); break;                  // Light.cpp:35-42
+    case DL_GRADIENT_INF: o.dir = sphere_dir(ux, uy); o.L = inf_Le(S, L, o.dir); break;          // Light.cpp:61-68
+    case DL_TEXTURE_INF: {                                                                       // Light.cpp:118-144
+        const float weight = rnd_float(rng) * L.total_weight;
+        const int n = S.env_w * S.env_h;
+        int lo = 0, hi = n;                      // std::upper_bound: first cdf > weight
+        while(lo < hi){ const int mid = (lo + hi) >> 1; if(S.env_cdf[mid] > weight)hi = mid; else lo = mid + 1; }
+        const int cx = lo % S.env_h, cy = lo / S.env_h;     // the reference decodes both with ySamples
+        o.dir = sphere_dir((cx + ux) / (float)S.env_w, (cy + uy) / (float)S.env_h);
+        break;
+    }
+    case DL_DISTANT: o.dir = normalize(ld3(L.v) + sphere_dir(ux, uy) * 0.02f); o.L = ld3(L.color); o.u = ux; o.v = uy; break;   // Light.cpp:208-215
+    case DL_POINT: o.p = ld3(L.v); o.n = v3(1.0f); o.L = ld3(L.color); o.u = ux; o.v = uy; break;                             // Light.cpp:235-237
+    default: {
+        // AreaLight::sample -> TriangleShape::Sample (Shape.cpp:277-297): no fold of u+v > 1
+        V3 v0, v1, v2; uint32_t i0, i1, i2;
+        tri_vertices(S, L, v0, v1, v2, i0, i1, i2);
+        const float w = 1.0f - ux - uy;
+        V3 n = normalize(cross(v1 - v0, v2 - v0));
+        if(n.x != n.x)n = v3(0.0f);
+        o.p = ux * v1 + uy * v2 + w * v0; o.n = n;
+        o.u = ux * S.uv[2 * (size_t)i1] + uy * S.uv[2 * (size_t)i2] + w * S.uv[2 * (size_t)i0];
+        o.v = ux * S.uv[2 * (size_t)i1 + 1] + uy * S.uv[2 * (size_t)i2 + 1] + w * S.uv[2 * (size_t)i0 + 1];
+        const DevInstShade& I = S.inst[L.inst];
+        if(I.has_xf){                                   // TransformedLight::sample (Light.cpp:306-312)
+            o.p = xf_point(I.fwd, o.p);
+            o.n = m3_mul(I.nrm, o.n);
+        }
+        break;
+    }
+    }
+}
+
+PT_HDI bool light_is_delta(const DevLight& L){ return L.kind == DL_DISTANT || L.kind == DL_POINT; }
+
+// TriangleShape::PDF(interaction, ray) (Shape.cpp:308-315)
+PT_HDI float tri_pdf(V3 p, V3 n, V3 ro, V3 rd, float area){
+    const V3 to = p - ro;
+    const float d2 = dot(to, to);
+    const float c = fabsf(dot(-rd, n));
+    if(area == 0.0f || c == 0.0f || n.x != n.x)return 0.0f;
+    return d2 / (c * area);
+}
+
+// Light::PDF(interaction, ray) of the light object the sampler holds (TransformedLight for xf instances)
+__device__ inline float light_pdf_sampled(const ShadeScene& S, const DevLight& L, V3 p, V3 n, V3 ro, V3 rd){
+    switch(L.kind){
+    case DL_UNIFORM_INF: case DL_GRADIENT_INF: return 1.0f / (4.0f * kPi);
+    case DL_TEXTURE_INF: {                                                                       // Light.cpp:146-150
+        const float cell = 4.0f * kPi / (float)(S.env_w * S.env_h);
+        return (lum(inf_Le(S, L, rd)) / L.total_weight) * (1.0f / cell);
+    }
+    case DL_DISTANT: case DL_POINT: return 0.0f;
+    default: {
+        const DevInstShade& I = S.inst[L.inst];
+        if(I.has_xf){                                    // TransformedLight::PDF (Light.cpp:318-325)
+            const V3 pl = xf_point(I.inv, p);
+            const V3 nl = normalize(xf_vec(I.inv, n));
+            return tri_pdf(pl, nl, xf_point(I.inv, ro), normalize(xf_vec(I.inv, rd)), L.area);
+        }
+        return tri_pdf(p, n, ro, rd, L.area);
+    }
+    }
+}
+
+// Light::L(lightSample.interaction, shadow_ray) as SampleLd calls it on the sampled light
+__device__ inline V3 light_L_sampled(const ShadeScene& S, const DevLight& L, const LightSmp& ls, V3 rd){
+    if(L.kind <= DL_TEXTURE_INF)return inf_Le(S, L, rd);
+    if(L.kind != DL_AREA)return v3(0.0f);
+    // TransformedLight::L builds a fresh SurfaceInteraction: its uv is (0,0) (Light.cpp:300-305)
+    if(S.inst[L.inst].has_xf)return tex_eval(S, L.tex, 0.0f, 0.0f, v3(0.0f));
+    return tex_eval(S, L.tex, ls.u, ls.v, v3(0.0f));
+}
+
+// ---- media (Medium.hpp:14-61, PhaseFunction.cpp:4-26) ---------------------------------------
+PT_HDI V3 medium_Tr(const DevMedium& M, float t){
+    const float tt = fminf(t, 3.402823466e+38f);
+    return v3(expf(-M.sigma_t[0] * tt), expf(-M.sigma_t[1] * tt), expf(-M.sigma_t[2] * tt));
+}
+// HomogeneusMedium::Sample: returns the throughput factor; sampled = a medium event before t, at `dist`
+PT_HDI V3 medium_sample(const DevMedium& M, float t, Pcg& rng, bool& sampled, float& dist){
+    int ch = (int)(3.0f * rnd_float(rng));
+    if(ch > 2)ch = 2;
+    dist = fminf((float)(-log(1.0 - (double)rnd_float(rng))) / M.sigma_t[ch], t);
+    sampled = dist < t;
+    const V3 tr = medium_Tr(M, dist);
+    const V3 st = ld3(M.sigma_t);
+    const V3 dens = sampled ? st * tr : tr;
+    const float pdf = (dens.x + dens.y + dens.z) / 3.0f;
+    return sampled ? (tr * ld3(M.sigma_s) / pdf) : (tr / pdf);
+}
+PT_HDI float phase_hg(float c, float g){
+    const float denom = 1.0f + g * g + 2.0f * g * c;
+    return 0.25f * kInvPi * (1.0f - g * g) / (denom * sqrtf(denom));
+}
+PT_HDI V3 hg_sample(float g, V3 in, float u0, float u1){
+    float c;
+    if(fabsf(g) < 1e-3f)c = 1.0f - 2.0f * u0;
+    else{
+        const float sqr = (1.0f - g * g) / (1.0f - g + 2.0f * g * u0);
+        c = (1.0f + g * g - sqr * sqr) / (2.0f * g);
+    }
+    const float s = sqrtf(fmaxf(0.0f, 1.0f - c * c));
+    const float phi = 2.0f * kPi * u1;
+    return normalize(to_world(onb_from_normal(in), v3(s * cosf(phi), s * sinf(phi), c)));
+}
+
+} // namespace ptb

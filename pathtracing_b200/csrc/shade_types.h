@@ -22,12 +22,13 @@ struct DevBlasInfo {
 };
 
 struct DevInstShade {
-    float fwd[12];           // rows 0..2 of transform, fwd[c*3+r]
+    float fwd[12];           // rows 0..2 of transform, fwd[c*3+r] (c = 0..3, translation c = 3)
     float nrm[9];            // transpose(inverse(mat3(transform))), nrm[c*3+r]
     float inv[12];           // rows 0..2 of inverse transform
     float det;               // glm::determinant(transform) (TransformedLight::Power)
     uint32_t blas;
     uint32_t has_xf;
+    int32_t light_base;      // first DevLight of this instance's emissive triangles, or -1
 };
 
 struct DevTexture {
@@ -47,7 +48,6 @@ struct DevMaterial {
     float albedo[3];
     int32_t alpha_mode;
     float alpha_cutoff;
-    float rough_default;     // used when rough < 0: 1 (Diffuse) / 0 (Dielectric)
 };
 
 struct DevMedium {
@@ -66,15 +66,14 @@ struct DevLight {
     float scale;
     float v[3];              // DISTANT dir / POINT position
     int32_t tex;             // TEXTURE_INF texture | AREA emissive texture
-    float power;             // Light::Power() after PreProcess
-    float pmf;               // LightSampler::PMF(light)
-    // AREA: which triangle (object space data fetched from the mesh arrays)
-    uint32_t inst;           // instance id (transform) ; 0xFFFFFFFF for none
-    uint32_t mesh;
-    uint32_t tri;            // mesh-local triangle index
-    float area;              // TriangleShape::Area()
+    float pmf_sample;        // LightSampler::PMF(light) of the light object the sampler holds
+    float pmf_hit;           // AREA: LightSampler::PMF(interaction.AreaLight) — the inner, untransformed light
+    uint32_t valid;          // AREA: 0 if Model::BuildBlas dropped it (Power <= FLT_EPSILON): not emissive at all
+    uint32_t inst;           // AREA: instance id
+    uint32_t mesh;           // AREA: scene mesh id
+    uint32_t tri;            // AREA: mesh-local triangle index
+    float area;              // AREA: TriangleShape::Area() in object space
     float total_weight;      // TEXTURE_INF: sum of the luminance table
-    uint32_t pad;
 };
 
 struct ShadeScene {
@@ -87,17 +86,16 @@ struct ShadeScene {
     const float* tan;        // 3 floats per vertex (zeros if mesh has none)
     const uint32_t* idx;
     const uint32_t* tri_mesh;  // per BLAS-wide triangle (original order): mesh id
-    const int32_t* tri_light;  // per (instance-expanded) emissive triangle lookup, see light_base
-    const int32_t* inst_light_base; // per instance: offset into tri_light or -1 (no emissive mesh)
+    const int32_t* tri_emis;   // per BLAS-wide triangle: ordinal among the BLAS's emissive triangles, or -1
     const DevTexture* textures;
     const uint8_t* texels;
     const DevMaterial* materials;
     const DevMedium* media;
-    const DevLight* lights;    // all lights (also culled ones)
+    const DevLight* lights;    // all lights (also the ones the sampler culled)
     const int32_t* sampler_lights; // indices of the lights the sampler can pick
-    const float* sampler_cdf;  // running power sum (PowerLightSampler::Sample)
+    const float* sampler_cdf;  // running power sum (PowerLightSampler::Sample walks it)
     const int32_t* inf_lights; // indices of scene->infiniteLights
-    const float* env_cdf;      // TEXTURE_INF: running luminance sum (xSamples*ySamples)
+    const float* env_cdf;      // TEXTURE_INF: running luminance sum (env_w*env_h cells)
     int32_t n_lights, n_sampler_lights, n_inf_lights;
     int32_t sampler_kind;      // 0 uniform, 1 power
     float total_power;

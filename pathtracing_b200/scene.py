@@ -298,6 +298,12 @@ class GpuScene:
         self._ck(self.lib.pt_film_download(self.h, out.ctypes.data))
         return out
 
+    def film_sumsq(self):
+        h, w = self._film_shape
+        out = np.empty((h, w, 3), np.float64)
+        self._ck(self.lib.pt_film_download_sumsq(self.h, out.ctypes.data))
+        return out
+
     def film_device_ptr(self):
         p, n = C.c_void_p(), C.c_size_t()
         self._ck(self.lib.pt_film_device_ptr(self.h, C.byref(p), C.byref(n)))

@@ -183,7 +183,7 @@ def instanced_scene(subdiv: int = 3, n_instances: int = 24, seed: int = 3, with_
     return d
 
 
-def cornell_scene(light_scale: float = 15.0, tess: int = 1):
+def cornell_scene(light_scale: float = 15.0, light_size: float = 0.3):
     """C1: procedural Cornell box as triangle meshes, Lambertian (MicrofacetDiffuse,
     roughness 1) walls + a two-triangle parallelogram area light."""
     d = SceneDesc()
@@ -204,7 +204,8 @@ def cornell_scene(light_scale: float = 15.0, tess: int = 1):
     add(quad((1, 0, 0), (0, 0, 1), (0, 1, 0)), green)        # right x=1
     add(box((0.53, 0.0, 0.09), (0.83, 0.3, 0.39), rot_y=-0.3), white)
     add(box((0.15, 0.0, 0.45), (0.45, 0.6, 0.75), rot_y=0.35), white)
-    add(quad((0.35, 0.998, 0.35), (0.3, 0, 0), (0, 0, 0.3)), black, emissive=emit)
+    lo = 0.5 - light_size / 2
+    add(quad((lo, 0.998, lo), (light_size, 0, 0), (0, 0, light_size)), black, emissive=emit)
     b = d.add_blas(meshes)
     d.instance(b)
     cam = camera_desc((0.5, 0.5, 2.4), (0.5, 0.5, 0.0), fov=2 * math.atan(0.5 / 1.4) * 1.0)

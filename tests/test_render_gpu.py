@@ -1,0 +1,134 @@
+"""GPU tier: the wavefront integrator (pt_render through the C-ABI) against the UNMODIFIED
+reference integrators (oracle/_ref: {Simple,,Vol}PathIntegrator::Li driven by the fixed-spp
+mirror of TileIntegrator::Render in oracle/ref_driver.cpp).
+
+The reference seeds its RNG from std::random_device, so parity is statistical (north_star):
+  * converged images agree to relative MSE <= 1e-3,
+  * per-pixel means agree within 3 sigma (sigma from the per-pixel sample variance of both
+    estimators), checked as: the fraction of pixels beyond 3 sigma is
+    what a normal law allows (plus slack for heavy tails) and the mean z-score shows no bias.
+"""
+import math
+
+import numpy as np
+import pytest
+
+from conftest import needs_ref
+from pathtracing_b200 import capi, synth
+from pathtracing_b200.scene import GpuScene, render_params
+
+pytestmark = pytest.mark.gpu
+
+
+def film_mean(rgbw):
+    w = np.maximum(rgbw[..., 3:4], 1e-300)
+    return rgbw[..., :3] / w
+
+
+def compare(desc, cam, width, height, spp, depth, integrator=capi.INTEGRATOR_PATH, bvh=4, light_sampler=1,
+            rel_mse=1e-3, z_frac=0.02, z_bias=0.06, filt=capi.FILTER_BOX, radius=(0.5, 0.5), fparam=(0.0, 0.0)):
+    from oracle.refapi import RefScene
+    params = render_params(width, height, spp, depth, integrator=integrator, filter=filt, filter_radius=radius,
+                           filter_param=fparam, seed=1234)
+    ref = RefScene(desc, bvh, light_sampler=light_sampler, count_rays=True, flavour="fast" if __import__("oracle.refapi").refapi.available("fast") else "strict")
+    r_rgbw, r_sq, r_stats = ref.render(cam, params)
+    gpu = GpuScene(desc, bvh, light_sampler=light_sampler)
+    g_stats = gpu.render(cam, params)
+    g_rgbw = gpu.film()
+    g_sq = gpu.film_sumsq()
+    gpu.close()
+    ref.close()
+    assert g_stats["samples"] == width * height * spp == r_stats["samples"]
+    a, b = film_mean(g_rgbw), film_mean(r_rgbw)
+    assert np.isfinite(a).all()
+    mse = float(((a - b) ** 2).sum() / max((b ** 2).sum(), 1e-30))
+    out = {"rel_mse": mse, "gpu_mean": a.mean(axis=(0, 1)), "ref_mean": b.mean(axis=(0, 1)),
+           "gpu_rays": (g_stats["closest_rays"], g_stats["shadow_rays"]), "ref_rays": (r_stats["closest_rays"], r_stats["shadow_rays"])}
+    if filt == capi.FILTER_BOX:
+        # per-pixel z-score with the sample variance of BOTH estimators (symmetric, so that the
+        # correlation between a pixel's mean and its own variance estimate cancels under H0)
+        var = (np.maximum(r_sq / spp - b ** 2, 0.0) + np.maximum(g_sq / spp - a ** 2, 0.0)) * spp / max(spp - 1, 1)
+        sigma = np.sqrt(var / spp)
+        ok = sigma > 1e-12
+        z = (a - b)[ok] / sigma[ok]
+        out["z_frac"] = float((np.abs(z) > 3).mean())
+        out["z_bias"] = float(z.mean())
+        # pixels with zero reference variance must agree almost exactly (e.g. directly seen light, black)
+        flat = ~ok
+        if flat.any():
+            assert np.allclose(a[flat], b[flat], rtol=2e-2, atol=2e-3), out
+        assert out["z_frac"] <= z_frac, out
+        assert abs(out["z_bias"]) <= z_bias, out
+    assert mse <= rel_mse, out
+    # global energy: means agree to 1 %
+    assert np.allclose(out["gpu_mean"], out["ref_mean"], rtol=1e-2, atol=1e-4), out
+    return out
+
+
+@needs_ref
+def test_cornell_path_nee_mis():
+    """C1: Cornell box, Lambertian + area light, NEE + MIS, depth 8."""
+    desc, cam = synth.cornell_scene()
+    out = compare(desc, cam, 64, 64, 2048, 8)
+    # rays per sample in the same ballpark (same termination statistics)
+    g = out["gpu_rays"][0] / out["ref_rays"][0]
+    assert 0.97 < g < 1.03, out
+
+
+@needs_ref
+def test_cornell_bvh2_uniform_light_sampler():
+    desc, cam = synth.cornell_scene()
+    compare(desc, cam, 48, 48, 1024, 5, bvh=2, light_sampler=0, rel_mse=3e-3)
+
+
+@needs_ref
+def test_cornell_simple_integrator():
+    """SimplePathIntegrator: BSDF sampling only (a19)."""
+    desc, cam = synth.cornell_scene(light_scale=4.0, light_size=0.7)
+    compare(desc, cam, 32, 32, 4096, 6, integrator=capi.INTEGRATOR_SIMPLE, rel_mse=4e-3)
+
+
+@needs_ref
+@pytest.mark.parametrize("filt,radius,fparam", [(capi.FILTER_GAUSSIAN, (1.5, 1.5), (0.5, 0.0)),
+                                               (capi.FILTER_MITCHELL, (1.5, 1.5), (1 / 3, 1 / 3)),
+                                               (capi.FILTER_LANCZOS, (1.5, 1.5), (3.0, 0.0))])
+def test_film_filters(filt, radius, fparam):
+    desc, cam = synth.cornell_scene()
+    compare(desc, cam, 48, 48, 1024, 4, filt=filt, radius=radius, fparam=fparam, rel_mse=2e-3)
+
+
+def test_pass_sharding_is_independent_of_rank_count():
+    """sample passes {r, r+G, ...} over G 'ranks' accumulate to the 1-rank film (same sample set)."""
+    desc, cam = synth.cornell_scene()
+    gpu = GpuScene(desc, 4)
+    p = render_params(40, 40, 12, 4, seed=9)
+    gpu.render(cam, p)
+    one = gpu.film().copy()
+    for r in range(3):
+        gpu.render(cam, render_params(40, 40, 12, 4, seed=9, pass_begin=r, pass_stride=3), clear=(r == 0))
+    three = gpu.film()
+    assert np.array_equal(one[..., 3], three[..., 3])
+    assert np.allclose(one[..., :3], three[..., :3], rtol=1e-9, atol=1e-12)
+    # and of the batch size
+    import os
+    os.environ["PTB_BATCH"] = "5000"
+    gpu.render(cam, p)
+    small = gpu.film()
+    del os.environ["PTB_BATCH"]
+    assert np.allclose(one[..., :3], small[..., :3], rtol=1e-9, atol=1e-12)
+    gpu.close()
+
+
+def test_render_error_paths():
+    desc, cam = synth.cornell_scene()
+    gpu = GpuScene(desc, 4)
+    with pytest.raises(capi.PtError):
+        gpu.render(cam, render_params(0, 10, 1, 1))
+    with pytest.raises(capi.PtError):
+        gpu.render(cam, render_params(8, 8, 1, 1, integrator=7))
+    with pytest.raises(capi.PtError):
+        gpu.film_device_ptr() if False else gpu.render(cam, render_params(8, 8, 1, 1, filter=9))
+    st = gpu.render(cam, render_params(8, 8, 2, 0))      # max depth 0: black, but counted
+    assert st["samples"] == 128 and st["closest_rays"] == 0
+    assert gpu.film()[..., :3].sum() == 0
+    gpu.close()
