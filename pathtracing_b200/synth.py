@@ -210,3 +210,85 @@ def cornell_scene(light_scale: float = 15.0, light_size: float = 0.3):
     d.instance(b)
     cam = camera_desc((0.5, 0.5, 2.4), (0.5, 0.5, 0.0), fov=2 * math.atan(0.5 / 1.4) * 1.0)
     return d, cam
+
+
+def trs(translate=(0, 0, 0), scale=1.0, rot_axis=(0, 1, 0), rot_angle=0.0):
+    axis = np.asarray(rot_axis, np.float64)
+    axis = axis / np.linalg.norm(axis)
+    K = np.array([[0, -axis[2], axis[1]], [axis[2], 0, -axis[0]], [-axis[1], axis[0], 0]])
+    R = np.eye(3) + math.sin(rot_angle) * K + (1 - math.cos(rot_angle)) * (K @ K)
+    M = np.eye(4)
+    M[:3, :3] = R * scale
+    M[:3, 3] = translate
+    return M.astype(np.float32)
+
+
+def procedural_textures(size=64, seed=11):
+    """Generated albedo / roughness-metallic / normal-map images (u8, 3 channels), the 'procedural
+    textures' of C4/C5: the reference can only load image files, so its harness writes these very
+    pixels to PNG and loads them back (oracle/ref_driver.cpp)."""
+    rng = np.random.default_rng(seed)
+    y, x = np.mgrid[0:size, 0:size].astype(np.float32) / size
+    albedo = np.stack([0.55 + 0.4 * np.sin(6.28 * 3 * x) * np.cos(6.28 * 2 * y), 0.5 + 0.35 * np.cos(6.28 * 2 * x + 1.0),
+                       0.45 + 0.3 * np.sin(6.28 * (x + y) * 2)], -1)
+    albedo = np.clip(albedo + 0.05 * rng.standard_normal(albedo.shape), 0.05, 0.95)
+    rough = np.clip(0.25 + 0.5 * (0.5 + 0.5 * np.sin(6.28 * 4 * x) * np.sin(6.28 * 4 * y)), 0.05, 1.0)
+    metal = (np.sin(6.28 * 2 * (x - y)) > 0.3).astype(np.float32)
+    orm = np.stack([np.ones_like(rough), rough, metal], -1)           # roughness in .g, metallic in .b
+    nx, ny = 0.35 * np.sin(6.28 * 5 * x), 0.35 * np.cos(6.28 * 5 * y)
+    nz = np.sqrt(np.maximum(1 - nx * nx - ny * ny, 0.05))
+    nm = np.stack([nx, ny, nz], -1) * 0.5 + 0.5
+    to8 = lambda a: np.ascontiguousarray(np.clip(np.round(a * 255), 0, 255).astype(np.uint8))
+    return to8(albedo), to8(orm), to8(nm)
+
+
+def materials_scene(subdiv=3, sky=True, point_light=False, distant_light=False):
+    """C3-style: instanced icospheres (TransformedPrimitive) with the four README materials +
+    ThinDielectric on a textured ground, a transformed emissive quad (TransformedLight) and a gradient sky."""
+    d = SceneDesc()
+    alb, orm, nm = procedural_textures()
+    t_alb, t_orm, t_nm = d.image_u8(alb), d.image_u8(orm), d.image_u8(nm)
+    white = d.solid((0.8, 0.8, 0.8))
+    ground_tex = d.checker(d.solid((0.75, 0.75, 0.75)), d.solid((0.2, 0.25, 0.3)), (0.125, 0.125))
+    mats = [
+        d.dielectric(1.5, d.solid((0.95, 0.97, 1.0)), rough=d.solid((0.15, 0.15, 0.15))),     # rough glass
+        d.diffuse(d.solid((0.95, 0.64, 0.54)), rough=d.solid((0.3, 0.3, 0.3)), metal=d.solid((1, 1, 1))),   # rough copper
+        d.diffuse(d.solid((0.2, 0.5, 0.8))),                                                   # Lambertian
+        d.conductor((0.9, 0.85, 0.6)),                                                         # mirror
+        d.dielectric(1.5, white),                                                              # smooth glass
+        d.thin_dielectric(1.5, d.solid((0.9, 1.0, 0.9))),
+        d.diffuse(t_alb, norm=-1, rough=t_orm, metal=t_orm),                                   # textured metal/rough
+    ]
+    pos, idx, nrm, uv = icosphere(subdiv, 1.0)
+    blas = [d.add_blas([d.mesh(pos, idx, nrm, uv, material=m)]) for m in mats]
+    rng = np.random.default_rng(5)
+    for k, b in enumerate(blas):
+        ang = 2 * math.pi * k / len(blas)
+        d.instance(b, trs((1.9 * math.cos(ang), 0.5 + 0.1 * (k % 2), 1.9 * math.sin(ang)), 0.5 + 0.05 * (k % 3),
+                          rng.normal(size=3), rng.random() * 6.28))
+    # ground with a normal map and explicit tangents, untransformed
+    gp, gi, gn, gu = quad((-4, 0, -4), (0, 0, 8), (8, 0, 0))
+    gt = np.tile(np.array([[0, 0, 1]], np.float32), (4, 1))
+    gmat = d.diffuse(ground_tex, norm=t_nm, rough=d.solid((0.6, 0.6, 0.6)))
+    d.instance(d.add_blas([d.mesh(gp, gi, gn, gu * 4.0, tangents=gt, material=gmat)]))
+    # emissive quad inside a rotated + scaled instance
+    lp, li, ln, lu = quad((-0.5, 0, -0.5), (1, 0, 0), (0, 0, 1))
+    emit = d.solid((1.0, 0.9, 0.75), scale=(12, 12, 12))
+    lb = d.add_blas([d.mesh(lp, li, ln, lu, material=d.diffuse(d.solid((0, 0, 0))), emissive_tex=emit)])
+    d.instance(lb, trs((0.3, 2.6, 0.2), 1.4, (1, 0, 0.3), 0.5))
+    if sky:
+        d.light(capi.LIGHT_GRADIENT_INFINITE, color=(1.0, 1.0, 1.0), color_b=(0.5, 0.7, 1.0), scale=0.6)
+    if point_light:
+        d.light(capi.LIGHT_POINT, color=(6, 5, 4), v=(-1.5, 2.0, 1.0), power_func=1)
+    if distant_light:
+        d.light(capi.LIGHT_DISTANT, color=(1.5, 1.4, 1.2), v=(0.4, 1.0, 0.3))
+    cam = camera_desc((0.0, 2.2, 5.2), (0.0, 0.5, 0.0), fov=0.9)
+    return d, cam
+
+
+def medium_scene(subdiv=2, g=0.75, density=0.1):
+    """C4-style: the materials scene inside a global HomogeneusMedium (Scene::SetMedium), rendered
+    with VolPathIntegrator: NEE + MIS through the medium."""
+    d, cam = materials_scene(subdiv, sky=True)
+    d.scene_medium = d.medium((0.5, 0.5, 0.5), (2.0, 2.2, 2.6), g, density=density)
+    return d, cam
