@@ -192,6 +192,65 @@ def time_dev(fn, steps, warmup, torch, dist, world):
     return ms / steps
 
 
+def bench_render(a, torch, dist, world, rank, local):
+    """C1 (BASELINE configs[0]): procedural Cornell box 512x512, 16 spp, depth 8, NEE+MIS, PathIntegrator.
+    Sample passes sharded over the ranks, one NCCL reduce of the film (strong scaling: total work fixed)."""
+    from pathtracing_b200 import capi, multi, synth
+    from pathtracing_b200.scene import GpuScene, render_params
+    desc, cam = synth.cornell_scene()
+    scene = GpuScene(desc, 4, device=local)
+    W = H = 512
+    spp, depth = 16, 8
+    params = render_params(W, H, spp, depth, integrator=capi.INTEGRATOR_PATH, seed=1)
+    steps = max(2, min(a.steps, 5))
+    st = None
+    for _ in range(2):
+        st, film = multi.render_sharded(scene, cam, params, dist if world > 1 else None)
+    torch.cuda.synchronize()
+    if world > 1:
+        dist.barrier()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    rays = 0
+    for _ in range(steps):
+        st, film = multi.render_sharded(scene, cam, params, dist if world > 1 else None)
+        rays += st["closest_rays"] + st["shadow_rays"]
+    e1.record()
+    torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1) / steps
+    if world > 1:
+        t = torch.tensor([ms, float(rays)], device="cuda", dtype=torch.float64)
+        dist.all_reduce(t[:1], op=dist.ReduceOp.MAX)
+        dist.all_reduce(t[1:], op=dist.ReduceOp.SUM)
+        ms, rays = float(t[0].item()), float(t[1].item())
+    out = None
+    if rank == 0:
+        img = film.cpu().numpy().reshape(H, W, 4)
+        out = {"workload": "C1 Cornell 512x512, 16 spp, depth 8, NEE+MIS, PathIntegrator, BVH4", "msamples_per_s": W * H * spp / (ms * 1e-3) / 1e6,
+               "mrays_per_s": rays / steps / (ms * 1e-3) / 1e6, "ms_per_frame": ms, "n_gpus": world, "scaling": "strong",
+               "collective": "one reduce(sum) of 4*W*H float64 film accumulators" if world > 1 else "none",
+               "kernel_launches_per_frame": int(st["kernel_launches"]), "mean_weight": float(img[..., 3].mean()),
+               "mean_radiance": float((img[..., :3] / np.maximum(img[..., 3:4], 1e-300)).mean())}
+    scene.close()
+    return out
+
+
+def cpu_render_rate(a):
+    from oracle import refapi
+    from pathtracing_b200 import capi, synth
+    from pathtracing_b200.scene import render_params
+    desc, cam = synth.cornell_scene()
+    flavour = "fast" if refapi.available("fast") else "strict"
+    ref = refapi.RefScene(desc, 4, count_rays=True, flavour=flavour)
+    params = render_params(256, 256, 16, 8, integrator=capi.INTEGRATOR_PATH)
+    _, _, st = ref.render(cam, params, want_sumsq=False)
+    cores = ref.threads
+    ref.close()
+    return {"msamples_per_s": st["samples"] / st["seconds"] / 1e6, "mrays_per_s": (st["closest_rays"] + st["shadow_rays"]) / st["seconds"] / 1e6,
+            "cores": cores, "kind": "reference",
+            "sample": f"256x256 crop-equivalent of C1 at 16 spp ({st['samples']} samples), fixed-spp mirror of TileIntegrator::Render, reference compiled -O3 ({flavour})"}
+
+
 def run_ours(a):
     import torch
     import torch.distributed as dist
@@ -253,6 +312,10 @@ def run_ours(a):
     hits_np = host_hits.numpy().view(np.dtype([("t", "<f4"), ("u", "<f4"), ("v", "<f4"), ("prim", "<u4")]))
     hit_rate = float((hits_np["prim"] != 0xFFFFFFFF).mean())
 
+    render_extra = None
+    if not a.no_extras:
+        render_extra = bench_render(a, torch, dist, world, rank, local)   # collective: every rank takes part
+
     if rank != 0:
         if world > 1:
             dist.barrier()
@@ -274,7 +337,7 @@ def run_ours(a):
         peak, peak_src = 6650.0, "fallback (B200_PROFILING.md)"
     achieved = n * b_ray / (ms * 1e-3) / 1e9
     roofline = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": None,
-                "peak_source": peak_src, "kernel": f"k_trace_closest<{a.bvh}>", "bytes_per_ray": b_ray,
+                "peak_source": peak_src, "kernel": f"k_trace<{a.bvh},false,false>", "bytes_per_ray": b_ray,
                 "nodes_per_ray": nodes_per_ray, "tris_per_ray": tris_per_ray, "instances_per_ray": inst_per_ray,
                 "note": "scene (nodes+triangles) is L2-resident at this size; DRAM traffic is rays+hits, see DESIGN.md"}
 
@@ -288,6 +351,14 @@ def run_ours(a):
         ms2 = time_dev(lambda: s2.trace_closest_dev(d_rays.data_ptr(), n, d_hits.data_ptr(), None, stream), max(2, a.steps // 2), 2, torch, dist, 1)
         extras[f"closest_bvh{other}_mrays"] = n / (ms2 * 1e-3) / 1e6
         s2.close()
+
+    if render_extra is not None:
+        extras["c1_render"] = render_extra
+        if world == 1 and not a.no_cpu:
+            try:
+                extras["c1_render"]["cpu_reference"] = cpu_render_rate(a)
+            except Exception as e:
+                extras["c1_render"]["cpu_reference"] = {"unavailable": str(e)}
 
     cpu = None
     if world == 1 and not a.no_cpu:

@@ -1,0 +1,62 @@
+"""Multi-GPU plumbing: scene replicated per rank, sample passes sharded
+(rank r renders passes r, r+G, ...), ONE reduce(sum) of the film accumulators to rank 0.
+
+torch.distributed is plumbing only: NCCL over NVLink for device films, gloo for the CPU-side
+tests of the same logic.  The reference has no counterpart: its only shared state is the
+atomic<double> film that worker threads merge into (Film.hpp:125-132, 244-249).
+"""
+from __future__ import annotations
+
+import numpy as np
+
+
+def shard_passes(spp: int, world: int, rank: int):
+    """Sample-pass indices rank `rank` of `world` renders: rank, rank+world, ... < spp."""
+    return list(range(rank, spp, world))
+
+
+def pass_range(params, world: int, rank: int):
+    """Return a copy of pt_render_params restricted to this rank's passes."""
+    import copy
+    p = copy.copy(params)
+    p.pass_begin = rank
+    p.pass_stride = world
+    return p
+
+
+class _DevArray:
+    """__cuda_array_interface__ view of a raw device pointer (the film the C-ABI exposes)."""
+
+    def __init__(self, ptr: int, n: int, typestr="<f8"):
+        self.__cuda_array_interface__ = {"shape": (n,), "typestr": typestr, "data": (ptr, False), "version": 3}
+
+
+def film_tensor(scene):
+    """torch view (no copy) of the scene's device film: float64[4*W*H]."""
+    import torch
+    ptr, n = scene.film_device_ptr()
+    return torch.as_tensor(_DevArray(ptr, n), device=f"cuda:{torch.cuda.current_device()}")
+
+
+def reduce_film(film, dist, dst: int = 0):
+    """The single collective of the path: sum of RGBW accumulators to rank `dst` (in place)."""
+    if dist is not None and dist.is_initialized() and dist.get_world_size() > 1:
+        dist.reduce(film, dst=dst, op=dist.ReduceOp.SUM)
+    return film
+
+
+def render_sharded(scene, cam, params, dist=None):
+    """Render this rank's passes and reduce the film to rank 0.  Returns (stats, film tensor);
+    the tensor holds the complete image on rank 0 only."""
+    world = dist.get_world_size() if dist is not None and dist.is_initialized() else 1
+    rank = dist.get_rank() if world > 1 else 0
+    stats = scene.render(cam, pass_range(params, world, rank), clear=True)
+    film = film_tensor(scene)
+    reduce_film(film, dist)
+    return stats, film
+
+
+def resolve(rgbw: np.ndarray):
+    """Film pixel value = sum(RGB*w) / sum(w)  (Film.hpp:161)."""
+    w = np.maximum(rgbw[..., 3:4], 1e-300)
+    return rgbw[..., :3] / w
