@@ -53,6 +53,11 @@ def render_sharded(scene, cam, params, dist=None):
     stats = scene.render(cam, pass_range(params, world, rank), clear=True)
     film = film_tensor(scene)
     reduce_film(film, dist)
+    if world > 1:
+        # the scene renders on its own stream: the reduce (queued behind torch's current stream) has to
+        # finish before the next pt_render clears or accumulates into the same film
+        import torch
+        torch.cuda.synchronize()
     return stats, film
 
 

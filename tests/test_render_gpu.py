@@ -166,3 +166,17 @@ def test_volpath_homogeneous_medium():
 def test_volpath_without_medium_equals_reference():
     desc, cam = synth.cornell_scene()
     compare(desc, cam, 40, 40, 1024, 6, integrator=capi.INTEGRATOR_VOLPATH)
+
+
+def test_film_tensor_view_and_single_rank_reduce():
+    """multi.render_sharded on one rank: the torch view aliases the device film (no copy)."""
+    import torch
+    from pathtracing_b200 import multi
+    desc, cam = synth.cornell_scene()
+    gpu = GpuScene(desc, 4)
+    p = render_params(32, 32, 4, 3, seed=3)
+    st, film = multi.render_sharded(gpu, cam, p, None)
+    host = gpu.film()
+    assert torch.equal(film.cpu(), torch.from_numpy(host.reshape(-1)))
+    assert float(host[..., 3].min()) == 4.0 == float(host[..., 3].max())
+    gpu.close()
