@@ -6,8 +6,9 @@
 // its 32 lanes busy by handing the next ray of the chunk to a lane the moment
 // its previous ray finishes (trace.cuh: one trav_step round per loop
 // iteration).  Rays are read as two 128-bit loads, hits written as one 128-bit
-// store.  No shared memory is used, so the whole 228 KB of the SM is L1 for
-// the upper tree levels and the per-lane stacks.
+// store.  The first 16 stack entries of every lane live in shared memory (128 KB per
+// SM at 8 CTAs), deeper ones spill to local memory; the remaining ~90 KB stay L1 for
+// the upper tree levels (PTB_STACK_SMEM=0|8|16|24 selects the split; 16 measured best).
 #include <cstdio>
 #include <cstdlib>
 #include "scene_host.hpp"
@@ -36,12 +37,16 @@ __device__ __forceinline__ void feed_grab(RayFeed& f, unsigned long long* cursor
     f.avail = left < kChunk ? (unsigned)left : kChunk;
 }
 
-template <int WIDTH, bool ANY, bool STATS>
+template <int WIDTH, bool ANY, bool STATS, int KS>
 __global__ void __launch_bounds__(kTraceBlock) k_trace(DevScene S, const float4* __restrict__ rays, size_t n,
                                                        float4* __restrict__ hits, uint32_t* __restrict__ inst, uint8_t* __restrict__ occ,
                                                        unsigned long long* __restrict__ cursor, unsigned long long* __restrict__ stats,
                                                        unsigned refill_min){
-    uint2 stack[kStack];
+    extern __shared__ uint2 smem_stack[];            // KS rows of kTraceBlock entries
+    uint2 spill[kStack - KS];
+    TravStack<KS, KS ? kTraceBlock : 1> stack;
+    if constexpr(KS > 0)stack.sm = smem_stack + threadIdx.x;
+    stack.lm = spill;
     TravState s;
     s.flags = TF_DONE;
     size_t idx = (size_t)-1;
@@ -100,40 +105,57 @@ static int check_launch(const char* what){
     return PT_OK;
 }
 
-// persistent grid size: resident CTAs of this kernel on this device (cached)
+// persistent grid size: resident CTAs of this kernel on this device (cached per instantiation)
 template <class K>
-static unsigned persistent_grid(K kernel, int device, int& cache){
+static unsigned persistent_grid(K kernel, int device, size_t smem, int& cache){
     if(cache > 0)return (unsigned)cache;
     int sms = 0, per_sm = 0;
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device);
-    cudaFuncSetAttribute(kernel, cudaFuncAttributePreferredSharedMemoryCarveout, 0);   // all L1
-    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, kTraceBlock, 0);
+    if(smem == 0)cudaFuncSetAttribute(kernel, cudaFuncAttributePreferredSharedMemoryCarveout, 0);   // all L1
+    else cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, kTraceBlock, smem);
     if(sms <= 0)sms = 148;
     if(per_sm <= 0)per_sm = 1;
     cache = sms * per_sm;
     return (unsigned)cache;
 }
 
-static unsigned refill_min(){
-    static int v = -1;
-    if(v < 0){ const char* e = getenv("PTB_REFILL_MIN"); v = e ? atoi(e) : 4; if(v < 1)v = 1; if(v > 32)v = 32; }
-    return (unsigned)v;
+static int env_int(const char* name, int dflt, int lo, int hi){
+    const char* e = getenv(name);
+    int v = e ? atoi(e) : dflt;
+    return v < lo ? lo : (v > hi ? hi : v);
 }
+static unsigned refill_min(){ static int v = env_int("PTB_REFILL_MIN", 4, 1, 32); return (unsigned)v; }
+// shared-memory stack rows per lane: 0 (all local), 8, 16 or 24
+static int stack_rows(){ static int v = env_int("PTB_STACK_SMEM", 16, 0, 24); return v; }
 
-template <int WIDTH, bool ANY, bool STATS>
-static int launch(pt_scene* sc, const void* d_rays, size_t n, void* d_hits, void* d_inst, void* d_occ, void* d_stats, void* stream){
+template <int WIDTH, bool ANY, bool STATS, int KS>
+static int launch_ks(pt_scene* sc, const void* d_rays, size_t n, void* d_hits, void* d_inst, void* d_occ, void* d_stats, void* stream){
     static int cache[8] = { 0, 0, 0, 0, 0, 0, 0, 0 };   // per device ordinal (one process drives at most 8 GPUs)
     cudaStream_t st = (cudaStream_t)stream;
-    auto kernel = k_trace<WIDTH, ANY, STATS>;
-    unsigned grid = persistent_grid(kernel, sc->device, cache[sc->device & 7]);
+    auto kernel = k_trace<WIDTH, ANY, STATS, KS>;
+    const size_t smem = (size_t)KS * kTraceBlock * sizeof(uint2);
+    unsigned grid = persistent_grid(kernel, sc->device, smem, cache[sc->device & 7]);
     const size_t need_ctas = (n + kTraceBlock - 1) / kTraceBlock;
     if(need_ctas < grid)grid = (unsigned)need_ctas;
     // one cursor per launch from a small ring, so launches on different streams never share one
     unsigned long long* cursor = (unsigned long long*)sc->buf.cursors + (sc->cursor_next++ % kCursorRing);
     if(!cuda_ok(cudaMemsetAsync(cursor, 0, sizeof(unsigned long long), st), "cursor reset"))return PT_ERR_CUDA;
-    kernel<<<grid, kTraceBlock, 0, st>>>(sc->dev, (const float4*)d_rays, n, (float4*)d_hits, (uint32_t*)d_inst, (uint8_t*)d_occ,
-                                         cursor, (unsigned long long*)d_stats, refill_min());
+    kernel<<<grid, kTraceBlock, smem, st>>>(sc->dev, (const float4*)d_rays, n, (float4*)d_hits, (uint32_t*)d_inst, (uint8_t*)d_occ,
+                                            cursor, (unsigned long long*)d_stats, refill_min());
     return check_launch("k_trace");
+}
+
+template <int WIDTH, bool ANY, bool STATS>
+static int launch(pt_scene* sc, const void* d_rays, size_t n, void* d_hits, void* d_inst, void* d_occ, void* d_stats, void* stream){
+    if constexpr(STATS)return launch_ks<WIDTH, ANY, STATS, 0>(sc, d_rays, n, d_hits, d_inst, d_occ, d_stats, stream);
+    else{
+    const int ks = stack_rows();
+    if(ks >= 24)return launch_ks<WIDTH, ANY, STATS, 24>(sc, d_rays, n, d_hits, d_inst, d_occ, d_stats, stream);
+    if(ks >= 16)return launch_ks<WIDTH, ANY, STATS, 16>(sc, d_rays, n, d_hits, d_inst, d_occ, d_stats, stream);
+    if(ks >= 8)return launch_ks<WIDTH, ANY, STATS, 8>(sc, d_rays, n, d_hits, d_inst, d_occ, d_stats, stream);
+    return launch_ks<WIDTH, ANY, STATS, 0>(sc, d_rays, n, d_hits, d_inst, d_occ, d_stats, stream);
+    }
 }
 
 int launch_trace_closest(pt_scene* sc, const void* d_rays, size_t n, void* d_hits, void* d_inst, void* stream){

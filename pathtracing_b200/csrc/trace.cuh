@@ -1,7 +1,7 @@
 // trace.cuh — device-side BVH2/BVH4 TLAS+BLAS traversal for sm_100a.
 //
 // One lane owns one ray and drives a small per-ray state machine (TravState +
-// one unified TLAS/BLAS stack in the lane's local-memory window).  One call of
+// one unified TLAS/BLAS stack: shared memory for the first rows, local memory beyond).  One call of
 // trav_step() does at most: one pop, one inner-node test, one leaf item (one
 // triangle, one instance entry or one instance exit).  Kernels call it from a
 // persistent loop and refill finished lanes with new rays (trace.cu, render
@@ -9,8 +9,8 @@
 // warp one triangle test per round instead of a whole nested loop
 // (profiles/r01_trace4_v1.md: the nested-loop version ran at 6.2 of 32 lanes).
 //
-// Every node/triangle/instance record is fetched with 128-bit loads
-// (pt_types.h).  The arithmetic of every box and triangle test is written with
+// Node records are fetched with 256-bit loads, triangles and instances with
+// 128-bit loads (pt_types.h).  The arithmetic of every box and triangle test is written with
 // explicit round-to-nearest intrinsics in the operation order of the
 // reference, so that no FMA contraction can change which candidate wins
 // (SURVEY.md §7 "hard part 1"); pushes and pops happen in the reference's
@@ -213,8 +213,28 @@ __device__ __forceinline__ uint32_t ray_octant(const RayCtx& r){
     return (r.dx < 0.0f ? 1u : 0u) | (r.dy < 0.0f ? 2u : 0u) | (r.dz < 0.0f ? 4u : 0u);
 }
 
-__device__ __forceinline__ void trav_push(uint2* stack, int& sp, uint32_t ref, float entry){
-    if(sp < kStack){ stack[sp] = make_uint2(ref, __float_as_uint(entry)); ++sp; }
+// Traversal stack: the first KS entries of every lane live in shared memory (row = level, column =
+// thread: a warp's 64-bit accesses are conflict-free whatever level each lane is at), deeper entries
+// spill to the lane's local-memory window.  profiles/r01_trace4_v4.md: with the whole stack in local
+// memory 58 % of the pops missed L1 and the stack lines evicted the upper tree levels.
+template <int KS, int STRIDE>
+struct TravStack {
+    uint2* sm;      // &smem[threadIdx.x]
+    uint2* lm;      // kStack - KS local entries
+    __device__ __forceinline__ void st(int i, uint2 v) const{ if(i < KS)sm[i * STRIDE] = v; else lm[i - KS] = v; }
+    __device__ __forceinline__ uint2 ld(int i) const{ return i < KS ? sm[i * STRIDE] : lm[i - KS]; }
+};
+template <>
+struct TravStack<0, 1> {    // all local (host emulation, tiny launches)
+    uint2* lm;
+    __device__ __forceinline__ void st(int i, uint2 v) const{ lm[i] = v; }
+    __device__ __forceinline__ uint2 ld(int i) const{ return lm[i]; }
+};
+using LocalStack = TravStack<0, 1>;
+
+template <class STK>
+__device__ __forceinline__ void trav_push(const STK& stack, int& sp, uint32_t ref, float entry){
+    if(sp < kStack){ stack.st(sp, make_uint2(ref, __float_as_uint(entry))); ++sp; }
 }
 
 // Scene::Intersect / IntersectPred entry (Scene.cpp:4-6,31-33).
@@ -240,8 +260,8 @@ __device__ __forceinline__ void trav_init(TravState& s, const DevScene& S, const
 
 // BVH2 child-pair node.  Closest: push order by the sign of dir[node.axis]
 // (BVH.hpp:520-545); any-hit: child 0 then child 1 (BVH.hpp:489-490).
-template <bool ANY>
-__device__ __forceinline__ void node_step2(TravState& s, const DevScene& S, uint2* stack){
+template <bool ANY, class STK>
+__device__ __forceinline__ void node_step2(TravState& s, const DevScene& S, const STK& stack){
     const float4* p = reinterpret_cast<const float4*>(S.n2 + s.cur);
     const F8 w0 = ldg256(p), w1 = ldg256(p + 2);
     const float4 q0 = w0.lo, q1 = w0.hi, q2 = w1.lo;
@@ -274,8 +294,8 @@ __device__ __forceinline__ uint32_t pick4(const uint4& v, unsigned k){
 // this ray octant (the folded LUT[signs][perm] / maskLUT of BVH.hpp:1193-1204).
 // The nearest one stays in s.cur instead of going through the stack: it was
 // just tested against the current tmax, so the pop-time cull cannot reject it.
-template <bool ANY>
-__device__ __forceinline__ void node_step4(TravState& s, const DevScene& S, uint2* stack){
+template <bool ANY, class STK>
+__device__ __forceinline__ void node_step4(TravState& s, const DevScene& S, const STK& stack){
     const float4* p = reinterpret_cast<const float4*>(S.n4 + s.cur);
     const F8 wx = ldg256(p), wy = ldg256(p + 2), wz = ldg256(p + 4), wr = ldg256(p + 6);
     const float4 xmin = wx.lo, xmax = wx.hi, ymin = wy.lo, ymax = wy.hi, zmin = wz.lo, zmax = wz.hi;
@@ -304,7 +324,7 @@ __device__ __forceinline__ void node_step4(TravState& s, const DevScene& S, uint
         const uint32_t r = hi ? rb : ra;
         const float e = hi ? eb : ea;
         const bool push = hit && cur != REF_EMPTY && sp < kStack;
-        if(push)stack[sp] = make_uint2(cur, __float_as_uint(cure));
+        if(push)stack.st(sp, make_uint2(cur, __float_as_uint(cure)));
         sp += push ? 1 : 0;
         cur = hit ? r : cur;
         cure = hit ? e : cure;
@@ -318,13 +338,13 @@ __device__ __forceinline__ void node_step4(TravState& s, const DevScene& S, uint
 // Returns false once the ray is finished (s.flags & TF_DONE).
 // reload(ray index) -> the world-space ray is re-read from its buffer when a
 // transformed instance is left (cheaper than holding 9 more registers).
-template <int WIDTH, bool ANY, bool STATS, class Alpha>
-__device__ __forceinline__ void trav_step(TravState& s, const DevScene& S, uint2* stack, const float4* __restrict__ rays, size_t ray_idx,
+template <int WIDTH, bool ANY, bool STATS, class STK, class Alpha>
+__device__ __forceinline__ void trav_step(TravState& s, const DevScene& S, const STK& stack, const float4* __restrict__ rays, size_t ray_idx,
                                           TraceCounters* cnt, const Alpha& alpha){
     // -- pop (BVH4 closest: cull by entry distance, BVH.hpp:1135) --
     if(s.cur == REF_EMPTY){
         while(s.sp > 0){
-            const uint2 e = stack[--s.sp];
+            const uint2 e = stack.ld(--s.sp);
             if(WIDTH == 4 && !ANY && __uint_as_float(e.y) > s.tmax)continue;
             if(e.x == REF_EMPTY)continue;      // empty lane of a cluster (BVH.hpp:38-43)
             s.cur = e.x;
@@ -407,7 +427,8 @@ __device__ __forceinline__ void trav_step(TravState& s, const DevScene& S, uint2
 // Whole-ray convenience wrapper (host emulation tests, counting kernel).
 template <int WIDTH, bool ANY, bool STATS, class Alpha>
 __device__ __forceinline__ bool trace_scene(const DevScene& S, const float4* __restrict__ rays, size_t ray_idx, HitRec& hit, TraceCounters* cnt, const Alpha& alpha){
-    uint2 stack[kStack];
+    uint2 stack_mem[kStack];
+    LocalStack stack; stack.lm = stack_mem;
     TravState s;
     trav_init<WIDTH>(s, S, __ldg(rays + 2 * ray_idx), __ldg(rays + 2 * ray_idx + 1));
     while(!(s.flags & TF_DONE))trav_step<WIDTH, ANY, STATS>(s, S, stack, rays, ray_idx, cnt, alpha);
