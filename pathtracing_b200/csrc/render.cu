@@ -53,6 +53,7 @@ struct BatchInfo {
     uint64_t first;     // first global sample id of the batch: id = pass_k * W*H + pixel
     uint32_t count;
     int W, H, pass_begin, pass_stride, max_depth;
+    int sampler, sx, sy;   // 0 UniformSampler | 1 StratifiedSampler(sx, sy)
     uint64_t seed;
 };
 
@@ -84,9 +85,24 @@ __global__ void __launch_bounds__(256) k_generate(Arena A, BatchInfo B, CamParam
     const uint64_t stream = stream_of(B, slot, pixel, sample);
     Pcg g = pcg_seed(B.seed, stream);
     const int x = (int)(pixel % (uint32_t)B.W), y = (int)(pixel / (uint32_t)B.W);
-    const double jx = rnd_double(g), jy = rnd_double(g);        // UniformSampler::getPixel2D
-    const float time = (float)rnd_double(g);
-    const float lx = (float)rnd_double(g), ly = (float)rnd_double(g);
+    double jx, jy; float time, lx, ly;
+    if(B.sampler == 0){
+        jx = rnd_double(g); jy = rnd_double(g);                 // UniformSampler::getPixel2D
+        time = (float)rnd_double(g);
+        lx = (float)rnd_double(g); ly = (float)rnd_double(g);
+    } else{
+        // StratifiedSampler (Sampler.hpp:73-151): dimensions 0-1 pixel, 2 time, 3-4 lens; the stratum of
+        // sample `index` is a hash-seeded permutation, the jitter inside it is random_float()
+        const uint32_t nS = (uint32_t)(B.sx * B.sy);
+        uint32_t st = permutation_element(sample, nS, (uint32_t)hash_ppd((uint32_t)x, (uint32_t)y, 0));
+        jx = ((double)(st % (uint32_t)B.sx) + (double)rnd_float(g)) / (double)B.sx;
+        jy = ((double)(st / (uint32_t)B.sx) + (double)rnd_float(g)) / (double)B.sy;
+        st = permutation_element(sample, nS, (uint32_t)hash_ppd((uint32_t)x, (uint32_t)y, 2));
+        time = (float)(((double)st + (double)rnd_float(g)) / (double)nS);
+        st = permutation_element(sample, nS, (uint32_t)hash_ppd((uint32_t)x, (uint32_t)y, 3));
+        lx = (float)(((double)(st % (uint32_t)B.sx) + (double)rnd_float(g)) / (double)B.sx);
+        ly = (float)(((double)(st / (uint32_t)B.sx) + (double)rnd_float(g)) / (double)B.sy);
+    }
     const float px = (float)((double)x + jx), py = (float)((double)y + jy);   // GenerateRay takes a glm::vec2
     const float uc = px / (float)B.W, vc = py / (float)B.H;
     V3 dir = normalize(-C.w + ((2.0f * uc - 1.0f) * C.half_w) * C.u + ((2.0f * vc - 1.0f) * C.half_h) * C.v);
@@ -260,7 +276,7 @@ __global__ void __launch_bounds__(128) k_shade(Arena A, ShadeScene S, BatchInfo 
         bool spec = (mf & 1u) != 0;
         int medium = (int)(mf >> 1) - 1;
         uint32_t pixel, sample;
-        Pcg g; g.inc = (stream_of(B, slot, pixel, sample) << 1u) | 1u; g.state = A.rng[slot];
+        Pcg g; g.inc = pcg_inc(B.seed, stream_of(B, slot, pixel, sample)); g.state = A.rng[slot];
 
         if(prim == 0xFFFFFFFFu){
             // miss: infinite lights (Integrators.cpp:136-141, 197-207, 308-330)
@@ -452,7 +468,9 @@ int render_passes(pt_scene* s, const pt_camera_desc* cam, const pt_render_params
     if(W <= 0 || H <= 0 || W > 65535 || H > 65535){ set_error("bad resolution"); return PT_ERR_INVALID; }   // Film stores uint16_t (Film.hpp:266-267)
     if(rp->spp <= 0 || rp->max_depth < 0 || rp->pass_stride <= 0 || rp->pass_begin < 0){ set_error("bad spp / depth / pass range"); return PT_ERR_INVALID; }
     if(rp->integrator < PT_INTEGRATOR_SIMPLE || rp->integrator > PT_INTEGRATOR_VOLPATH){ set_error("unknown integrator"); return PT_ERR_INVALID; }
-    if(rp->sampler != 0){ set_error("StratifiedSampler is not built yet: use sampler = 0 (UniformSampler)"); return PT_ERR_INVALID; }
+    if(rp->sampler != 0 && rp->sampler != 1){ set_error("unknown sampler"); return PT_ERR_INVALID; }
+    if(rp->sampler == 1 && (rp->strata_x <= 0 || rp->strata_y <= 0 || rp->strata_x * rp->strata_y != rp->spp)){
+        set_error("StratifiedSampler: spp must equal strata_x * strata_y (Sampler.hpp:84)"); return PT_ERR_INVALID; }
     if(rp->adaptive){ set_error("adaptive sampling is not built yet: use adaptive = 0 (exactly spp samples per pixel)"); return PT_ERR_INVALID; }
     if(cam->medium >= (int)s->media.size()){ set_error("camera medium id out of range"); return PT_ERR_INVALID; }
     FilterParams F;
@@ -499,6 +517,7 @@ int render_passes(pt_scene* s, const pt_camera_desc* cam, const pt_render_params
         BatchInfo B;
         B.first = first; B.count = (uint32_t)std::min<uint64_t>(cap, total - first);
         B.W = W; B.H = H; B.pass_begin = rp->pass_begin; B.pass_stride = rp->pass_stride; B.max_depth = rp->max_depth; B.seed = rp->seed;
+        B.sampler = rp->sampler; B.sx = rp->strata_x; B.sy = rp->strata_y;
         k_generate<<<(B.count + 255) / 256, 256, 0, st>>>(A, B, C);
         R.kernel_launches++;
         uint32_t n = rp->max_depth > 0 ? B.count : 0;    // `depth++ < maxDepth` fails at once: black samples

@@ -144,7 +144,7 @@ int pack_traversal(pt_scene* s, int width, PackedTraversal& P){
                         // Texture::alpha() is 1 unless an image has 4 channels (Texture.cpp:48-62)
                         can_be_transparent = (td.kind == PT_TEX_IMAGE_U8 || td.kind == PT_TEX_IMAGE_F32 || td.kind == PT_TEX_CHECKER) && (td.kind == PT_TEX_CHECKER || td.channels == 4);
                     }
-                    if(can_be_transparent)flags |= TRI_ALPHA_TEX;
+                    if(can_be_transparent){ flags |= TRI_ALPHA_TEX; s->has_alpha_tex = true; }
                 }
             }
             for(uint32_t t = 0; t < m.d.n_triangles; t++, g++){

@@ -89,6 +89,8 @@ struct pt_scene {
     void* stream2 = nullptr;
     void* ev[4] = { nullptr, nullptr, nullptr, nullptr };
     unsigned cursor_next = 0;
+    bool has_alpha_tex = false;   // some triangle carries TRI_ALPHA_TEX: traversal must evaluate Material::Alpha
+    uint64_t alpha_salt = 0;      // advances per launch (AlphaTester Blend draws)
 };
 
 namespace ptb {

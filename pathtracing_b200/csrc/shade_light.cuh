@@ -8,7 +8,7 @@
 namespace ptb {
 
 // UniformLightSampler::Sample (LightSampler.cpp:7-11) / PowerLightSampler::Sample (:34-46)
-__device__ inline int pick_light(const ShadeScene& S, float u){
+__host__ __device__ inline int pick_light(const ShadeScene& S, float u){
     const int n = S.n_sampler_lights;
     if(n == 0)return -1;
     if(S.sampler_kind == 0){
@@ -35,14 +35,14 @@ struct LightSmp {
     float u, v;    // texcoords of the sampled point
 };
 
-__device__ inline void tri_vertices(const ShadeScene& S, const DevLight& L, V3& v0, V3& v1, V3& v2, uint32_t& i0, uint32_t& i1, uint32_t& i2){
+__host__ __device__ inline void tri_vertices(const ShadeScene& S, const DevLight& L, V3& v0, V3& v1, V3& v2, uint32_t& i0, uint32_t& i1, uint32_t& i2){
     const DevMesh& m = S.meshes[L.mesh];
     i0 = m.vtx_base + S.idx[m.idx_base + 3 * L.tri]; i1 = m.vtx_base + S.idx[m.idx_base + 3 * L.tri + 1]; i2 = m.vtx_base + S.idx[m.idx_base + 3 * L.tri + 2];
     v0 = ld3(S.pos + 3 * (size_t)i0); v1 = ld3(S.pos + 3 * (size_t)i1); v2 = ld3(S.pos + 3 * (size_t)i2);
 }
 
 // Light::sample(uv, time).  `rng` feeds TextureInfiniteLight::sample's extra random_float (Light.cpp:120).
-__device__ inline void light_sample(const ShadeScene& S, const DevLight& L, float ux, float uy, Pcg& rng, LightSmp& o){
+__host__ __device__ inline void light_sample(const ShadeScene& S, const DevLight& L, float ux, float uy, Pcg& rng, LightSmp& o){
     o.L = v3(0.0f); o.p = v3(0.0f); o.n = v3(0.0f); o.dir = v3(0.0f); o.u = 0.0f; o.v = 0.0f;
     switch(L.kind){
     case DL_UNIFORM_INF: o.dir = sphere_dir(ux, uy); o.L = ld3(L.color); break;                  // Light.cpp:35-42
@@ -90,7 +90,7 @@ PT_HDI float tri_pdf(V3 p, V3 n, V3 ro, V3 rd, float area){
 }
 
 // Light::PDF(interaction, ray) of the light object the sampler holds (TransformedLight for xf instances)
-__device__ inline float light_pdf_sampled(const ShadeScene& S, const DevLight& L, V3 p, V3 n, V3 ro, V3 rd){
+__host__ __device__ inline float light_pdf_sampled(const ShadeScene& S, const DevLight& L, V3 p, V3 n, V3 ro, V3 rd){
     switch(L.kind){
     case DL_UNIFORM_INF: case DL_GRADIENT_INF: return 1.0f / (4.0f * kPi);
     case DL_TEXTURE_INF: {                                                                       // Light.cpp:146-150
@@ -111,7 +111,7 @@ __device__ inline float light_pdf_sampled(const ShadeScene& S, const DevLight& L
 }
 
 // Light::L(lightSample.interaction, shadow_ray) as SampleLd calls it on the sampled light
-__device__ inline V3 light_L_sampled(const ShadeScene& S, const DevLight& L, const LightSmp& ls, V3 rd){
+__host__ __device__ inline V3 light_L_sampled(const ShadeScene& S, const DevLight& L, const LightSmp& ls, V3 rd){
     if(L.kind <= DL_TEXTURE_INF)return inf_Le(S, L, rd);
     if(L.kind != DL_AREA)return v3(0.0f);
     // TransformedLight::L builds a fresh SurfaceInteraction: its uv is (0,0) (Light.cpp:300-305)

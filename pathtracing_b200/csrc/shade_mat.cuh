@@ -37,7 +37,7 @@ PT_HDI bool diff_f(const ShadeScene& S, const DevMaterial& M, const SurfInt& si,
     return true;
 }
 
-__device__ inline bool diffuse_scatter(const ShadeScene& S, const DevMaterial& M, const SurfInt& si, V3 rd, float u, float ux, float uy, Scatter& out){
+__host__ __device__ inline bool diffuse_scatter(const ShadeScene& S, const DevMaterial& M, const SurfInt& si, V3 rd, float u, float ux, float uy, Scatter& out){
     const float rough = diff_roughness(S, M, si);
     const Onb tbn = onb_from_normal(dot(rd, si.ns) > 0.0f ? -si.ns : si.ns);
     const Ggx g = { rough * rough };
@@ -63,7 +63,7 @@ __device__ inline bool diffuse_scatter(const ShadeScene& S, const DevMaterial& M
     return true;
 }
 
-__device__ inline float diffuse_pdf(const ShadeScene& S, const DevMaterial& M, const SurfInt& si, V3 in, V3 outd){
+__host__ __device__ inline float diffuse_pdf(const ShadeScene& S, const DevMaterial& M, const SurfInt& si, V3 in, V3 outd){
     const float rough = diff_roughness(S, M, si);
     const Ggx g = { rough * rough };
     const Onb tbn = onb_from_normal(dot(in, si.ns) > 0.0f ? -si.ns : si.ns);
@@ -75,7 +75,7 @@ __device__ inline float diffuse_pdf(const ShadeScene& S, const DevMaterial& M, c
     return d + sp;
 }
 
-__device__ inline V3 diffuse_eval(const ShadeScene& S, const DevMaterial& M, const SurfInt& si, V3 in, V3 outd){
+__host__ __device__ inline V3 diffuse_eval(const ShadeScene& S, const DevMaterial& M, const SurfInt& si, V3 in, V3 outd){
     const Onb tbn = onb_from_normal(dot(in, si.ns) > 0.0f ? -si.ns : si.ns);
     const V3 wo = to_local(tbn, -in), wi = to_local(tbn, outd);
     const V3 wh = normalize(wo + wi);
@@ -91,7 +91,7 @@ PT_HDI float diel_roughness(const ShadeScene& S, const DevMaterial& M, const Sur
     return M.rough >= 0 ? tex_eval(S, M.rough, si.u, si.v, si.ns).y : 0.0f;
 }
 
-__device__ inline bool dielectric_scatter(const ShadeScene& S, const DevMaterial& M, const SurfInt& si, V3 ro, V3 rd, float u, float ux, float uy, Scatter& out){
+__host__ __device__ inline bool dielectric_scatter(const ShadeScene& S, const DevMaterial& M, const SurfInt& si, V3 ro, V3 rd, float u, float ux, float uy, Scatter& out){
     const float rough = diel_roughness(S, M, si);
     const Ggx g = { rough * rough };
     const Onb tbn = onb_from_frame(si.ns, si.tangent);
@@ -142,7 +142,7 @@ __device__ inline bool dielectric_scatter(const ShadeScene& S, const DevMaterial
 }
 
 // common front of MicrofacetDielectric::PDF / calc_attenuation (Material.hpp:497-523, 540-566)
-__device__ inline bool diel_half(const DevMaterial& M, V3 wo, V3 wi, V3& wh, bool& reflect, float& etap){
+__host__ __device__ inline bool diel_half(const DevMaterial& M, V3 wo, V3 wi, V3& wh, bool& reflect, float& etap){
     const float co = wo.z, ci = wi.z;
     reflect = ci * co > 0.0f;
     etap = 1.0f;
@@ -155,7 +155,7 @@ __device__ inline bool diel_half(const DevMaterial& M, V3 wo, V3 wi, V3& wh, boo
     return true;
 }
 
-__device__ inline float dielectric_pdf(const ShadeScene& S, const DevMaterial& M, const SurfInt& si, V3 in, V3 outd){
+__host__ __device__ inline float dielectric_pdf(const ShadeScene& S, const DevMaterial& M, const SurfInt& si, V3 in, V3 outd){
     const float rough = diel_roughness(S, M, si);
     const Ggx g = { rough * rough };
     if(M.ri == 1.0f || g.a < 1e-6f)return 0.0f;
@@ -170,7 +170,7 @@ __device__ inline float dielectric_pdf(const ShadeScene& S, const DevMaterial& M
     return pdf * (fabsf(dot(wi, wh)) / (s * s)) * T / (R + T);
 }
 
-__device__ inline V3 dielectric_eval(const ShadeScene& S, const DevMaterial& M, const SurfInt& si, V3 in, V3 outd){
+__host__ __device__ inline V3 dielectric_eval(const ShadeScene& S, const DevMaterial& M, const SurfInt& si, V3 in, V3 outd){
     const float rough = diel_roughness(S, M, si);
     const Ggx g = { rough * rough };
     if(M.ri == 1.0f || g.a < 1e-6f)return v3(0.0f);
@@ -188,7 +188,7 @@ __device__ inline V3 dielectric_eval(const ShadeScene& S, const DevMaterial& M, 
 }
 
 // ---- ThinDielectric (Material.hpp:601-657), SpecularConductor (:660-673) -------------------
-__device__ inline bool thin_scatter(const ShadeScene& S, const DevMaterial& M, const SurfInt& si, V3 ro, V3 rd, float u, Scatter& out){
+__host__ __device__ inline bool thin_scatter(const ShadeScene& S, const DevMaterial& M, const SurfInt& si, V3 ro, V3 rd, float u, Scatter& out){
     const Onb tbn = onb_from_frame(si.ns, si.tangent);
     const V3 wo = to_local(tbn, -rd);
     const V3 Ng = dot(rd, si.n) > 0.0f ? -si.n : si.n;
@@ -211,7 +211,7 @@ __device__ inline bool thin_scatter(const ShadeScene& S, const DevMaterial& M, c
     return true;
 }
 
-__device__ inline bool conductor_scatter(const DevMaterial& M, const SurfInt& si, V3 rd, Scatter& out){
+__host__ __device__ inline bool conductor_scatter(const DevMaterial& M, const SurfInt& si, V3 rd, Scatter& out){
     out.o = si.p; out.d = reflect3(rd, si.ns);
     const float d = dot(out.d, si.ns);
     if(d <= 0.0f)return false;
@@ -221,7 +221,7 @@ __device__ inline bool conductor_scatter(const DevMaterial& M, const SurfInt& si
 }
 
 // ---- dispatch (the reference's virtual calls) ------------------------------------------------
-__device__ inline bool mat_scatter(const ShadeScene& S, const SurfInt& si, V3 ro, V3 rd, float u, float ux, float uy, Scatter& out){
+__host__ __device__ inline bool mat_scatter(const ShadeScene& S, const SurfInt& si, V3 ro, V3 rd, float u, float ux, float uy, Scatter& out){
     const DevMaterial& M = S.materials[si.mat];
     switch(M.kind){
     case PT_MAT_DIFFUSE: return diffuse_scatter(S, M, si, rd, u, ux, uy, out);
@@ -230,13 +230,13 @@ __device__ inline bool mat_scatter(const ShadeScene& S, const SurfInt& si, V3 ro
     default: return conductor_scatter(M, si, rd, out);
     }
 }
-__device__ inline float mat_pdf(const ShadeScene& S, const SurfInt& si, V3 in, V3 outd){
+__host__ __device__ inline float mat_pdf(const ShadeScene& S, const SurfInt& si, V3 in, V3 outd){
     const DevMaterial& M = S.materials[si.mat];
     if(M.kind == PT_MAT_DIFFUSE)return diffuse_pdf(S, M, si, in, outd);
     if(M.kind == PT_MAT_DIELECTRIC)return dielectric_pdf(S, M, si, in, outd);
     return 0.0f;                                                  // Material.hpp:157-159, 651-653
 }
-__device__ inline V3 mat_eval(const ShadeScene& S, const SurfInt& si, V3 in, V3 outd){
+__host__ __device__ inline V3 mat_eval(const ShadeScene& S, const SurfInt& si, V3 in, V3 outd){
     const DevMaterial& M = S.materials[si.mat];
     if(M.kind == PT_MAT_DIFFUSE)return diffuse_eval(S, M, si, in, outd);
     if(M.kind == PT_MAT_DIELECTRIC)return dielectric_eval(S, M, si, in, outd);

@@ -67,9 +67,20 @@ PT_HDI uint32_t pcg_next(Pcg& g){
     const uint32_t rot = (uint32_t)(old >> 59u);
     return (xorshifted >> rot) | (xorshifted << ((32u - rot) & 31u));
 }
+// One generator per camera sample.  PCG streams that share a seed and differ only in a small increment
+// are strongly correlated (the states stay an affine function of each other), which showed up as a
+// per-pixel variance ~3x what the sample variance predicts; so both the start state and the increment
+// come out of a 64-bit finaliser (splitmix64) of (seed, sample stream).
+PT_HDI uint64_t mix64(uint64_t x){
+    x += 0x9E3779B97F4A7C15ull;
+    x = (x ^ (x >> 30)) * 0xBF58476D1CE4E5B9ull;
+    x = (x ^ (x >> 27)) * 0x94D049BB133111EBull;
+    return x ^ (x >> 31);
+}
+PT_HDI uint64_t pcg_inc(uint64_t seed, uint64_t stream){ return (mix64(mix64(stream) ^ (seed * 0xD1B54A32D192ED03ull)) << 1u) | 1u; }
 PT_HDI Pcg pcg_seed(uint64_t seed, uint64_t stream){
-    Pcg g; g.state = 0; g.inc = (stream << 1u) | 1u;
-    pcg_next(g); g.state += seed; pcg_next(g);
+    Pcg g; g.state = 0; g.inc = pcg_inc(seed, stream);
+    pcg_next(g); g.state += mix64(mix64(seed) + stream); pcg_next(g);
     return g;
 }
 // RandomFloatx8 lane (Random.hpp:22-44): float(u32) * (1/0xFFFFFFFF) — may return exactly 1
@@ -83,6 +94,29 @@ PT_HDI float rnd_float(Pcg& g){
 PT_HDI double rnd_double(Pcg& g){
     const uint64_t hi = pcg_next(g), lo = pcg_next(g);
     return (double)(((hi << 32) | lo) >> 11) * (1.0 / 9007199254740992.0);
+}
+
+// ---- StratifiedSampler helpers (Util.hpp:45-73, 75-168) ----------------------------------------
+// Hash(px, py, dimension): MurmurHash64A over {uint32 px, uint32 py, uint64 dimension}, seed 0
+PT_HDI uint64_t hash_ppd(uint32_t px, uint32_t py, uint64_t dim){
+    const uint64_t m = 0xc6a4a7935bd1e995ull;
+    uint64_t h = 0ull ^ (16ull * m);
+    uint64_t k = (uint64_t)px | ((uint64_t)py << 32);
+    k *= m; k ^= k >> 47; k *= m; h ^= k; h *= m;
+    k = dim;
+    k *= m; k ^= k >> 47; k *= m; h ^= k; h *= m;
+    h ^= h >> 47; h *= m; h ^= h >> 47;
+    return h;
+}
+PT_HDI uint32_t permutation_element(uint32_t i, uint32_t l, uint32_t p){
+    uint32_t w = l - 1;
+    w |= w >> 1; w |= w >> 2; w |= w >> 4; w |= w >> 8; w |= w >> 16;
+    do{
+        i ^= p; i *= 0xe170893du; i ^= p >> 16; i ^= (i & w) >> 4; i ^= p >> 8; i *= 0x0929eb3fu; i ^= p >> 23;
+        i ^= (i & w) >> 1; i *= 1u | p >> 27; i *= 0x6935fa69u; i ^= (i & w) >> 11; i *= 0x74dcb303u;
+        i ^= (i & w) >> 2; i *= 0x9e501cc3u; i ^= (i & w) >> 2; i *= 0xc860a3dfu; i &= w; i ^= i >> 5;
+    } while(i >= l);
+    return (i + p) % l;
 }
 
 // ---- textures (Texture.hpp:108-231, Texture.cpp:38-94) ------------------------------------

@@ -13,6 +13,7 @@
 #include <cstdlib>
 #include "scene_host.hpp"
 #include "trace.cuh"
+#include "alpha.cuh"
 
 namespace ptb {
 
@@ -37,11 +38,11 @@ __device__ __forceinline__ void feed_grab(RayFeed& f, unsigned long long* cursor
     f.avail = left < kChunk ? (unsigned)left : kChunk;
 }
 
-template <int WIDTH, bool ANY, bool STATS, int KS>
+template <int WIDTH, bool ANY, bool STATS, int KS, class Alpha>
 __global__ void __launch_bounds__(kTraceBlock) k_trace(DevScene S, const float4* __restrict__ rays, size_t n,
                                                        float4* __restrict__ hits, uint32_t* __restrict__ inst, uint8_t* __restrict__ occ,
                                                        unsigned long long* __restrict__ cursor, unsigned long long* __restrict__ stats,
-                                                       unsigned refill_min){
+                                                       unsigned refill_min, const Alpha alpha){
     extern __shared__ uint2 smem_stack[];            // KS rows of kTraceBlock entries
     uint2 spill[kStack - KS];
     TravStack<KS, KS ? kTraceBlock : 1> stack;
@@ -85,7 +86,7 @@ __global__ void __launch_bounds__(kTraceBlock) k_trace(DevScene S, const float4*
             feed.base += taken; feed.avail -= taken;
             if(feed.exhausted && __all_sync(0xffffffffu, idx == (size_t)-1))break;
         }
-        if(!(s.flags & TF_DONE))trav_step<WIDTH, ANY, STATS>(s, S, stack, rays, idx, STATS ? &c : nullptr, NoAlpha());
+        if(!(s.flags & TF_DONE))trav_step<WIDTH, ANY, STATS>(s, S, stack, rays, idx, STATS ? &c : nullptr, alpha);
     }
     if(STATS){
         // warp reduce, one atomic per warp per counter
@@ -129,11 +130,11 @@ static unsigned refill_min(){ static int v = env_int("PTB_REFILL_MIN", 4, 1, 32)
 // shared-memory stack rows per lane: 0 (all local), 8, 16 or 24
 static int stack_rows(){ static int v = env_int("PTB_STACK_SMEM", 16, 0, 24); return v; }
 
-template <int WIDTH, bool ANY, bool STATS, int KS>
-static int launch_ks(pt_scene* sc, const void* d_rays, size_t n, void* d_hits, void* d_inst, void* d_occ, void* d_stats, void* stream){
+template <int WIDTH, bool ANY, bool STATS, int KS, class Alpha>
+static int launch_ks(pt_scene* sc, const void* d_rays, size_t n, void* d_hits, void* d_inst, void* d_occ, void* d_stats, void* stream, const Alpha& alpha){
     static int cache[8] = { 0, 0, 0, 0, 0, 0, 0, 0 };   // per device ordinal (one process drives at most 8 GPUs)
     cudaStream_t st = (cudaStream_t)stream;
-    auto kernel = k_trace<WIDTH, ANY, STATS, KS>;
+    auto kernel = k_trace<WIDTH, ANY, STATS, KS, Alpha>;
     const size_t smem = (size_t)KS * kTraceBlock * sizeof(uint2);
     unsigned grid = persistent_grid(kernel, sc->device, smem, cache[sc->device & 7]);
     const size_t need_ctas = (n + kTraceBlock - 1) / kTraceBlock;
@@ -142,19 +143,26 @@ static int launch_ks(pt_scene* sc, const void* d_rays, size_t n, void* d_hits, v
     unsigned long long* cursor = (unsigned long long*)sc->buf.cursors + (sc->cursor_next++ % kCursorRing);
     if(!cuda_ok(cudaMemsetAsync(cursor, 0, sizeof(unsigned long long), st), "cursor reset"))return PT_ERR_CUDA;
     kernel<<<grid, kTraceBlock, smem, st>>>(sc->dev, (const float4*)d_rays, n, (float4*)d_hits, (uint32_t*)d_inst, (uint8_t*)d_occ,
-                                            cursor, (unsigned long long*)d_stats, refill_min());
+                                            cursor, (unsigned long long*)d_stats, refill_min(), alpha);
     return check_launch("k_trace");
 }
 
 template <int WIDTH, bool ANY, bool STATS>
 static int launch(pt_scene* sc, const void* d_rays, size_t n, void* d_hits, void* d_inst, void* d_occ, void* d_stats, void* stream){
-    if constexpr(STATS)return launch_ks<WIDTH, ANY, STATS, 0>(sc, d_rays, n, d_hits, d_inst, d_occ, d_stats, stream);
+    if constexpr(STATS)return launch_ks<WIDTH, ANY, STATS, 0>(sc, d_rays, n, d_hits, d_inst, d_occ, d_stats, stream, NoAlpha());
     else{
     const int ks = stack_rows();
-    if(ks >= 24)return launch_ks<WIDTH, ANY, STATS, 24>(sc, d_rays, n, d_hits, d_inst, d_occ, d_stats, stream);
-    if(ks >= 16)return launch_ks<WIDTH, ANY, STATS, 16>(sc, d_rays, n, d_hits, d_inst, d_occ, d_stats, stream);
-    if(ks >= 8)return launch_ks<WIDTH, ANY, STATS, 8>(sc, d_rays, n, d_hits, d_inst, d_occ, d_stats, stream);
-    return launch_ks<WIDTH, ANY, STATS, 0>(sc, d_rays, n, d_hits, d_inst, d_occ, d_stats, stream);
+    if(sc->has_alpha_tex){
+        // some triangle's material can reject a hit: the kernel variant that evaluates Material::Alpha
+        const AlphaTex at = { sc->shade, sc->alpha_salt += 0x9E3779B97F4A7C15ull };
+        if(ks >= 16)return launch_ks<WIDTH, ANY, STATS, 16>(sc, d_rays, n, d_hits, d_inst, d_occ, d_stats, stream, at);
+        return launch_ks<WIDTH, ANY, STATS, 0>(sc, d_rays, n, d_hits, d_inst, d_occ, d_stats, stream, at);
+    }
+    const NoAlpha na;
+    if(ks >= 24)return launch_ks<WIDTH, ANY, STATS, 24>(sc, d_rays, n, d_hits, d_inst, d_occ, d_stats, stream, na);
+    if(ks >= 16)return launch_ks<WIDTH, ANY, STATS, 16>(sc, d_rays, n, d_hits, d_inst, d_occ, d_stats, stream, na);
+    if(ks >= 8)return launch_ks<WIDTH, ANY, STATS, 8>(sc, d_rays, n, d_hits, d_inst, d_occ, d_stats, stream, na);
+    return launch_ks<WIDTH, ANY, STATS, 0>(sc, d_rays, n, d_hits, d_inst, d_occ, d_stats, stream, na);
     }
 }
 

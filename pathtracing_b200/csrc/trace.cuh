@@ -160,9 +160,9 @@ __device__ __forceinline__ bool tri_any(const RayCtx& r, const TriData& T, float
 // Hook for alpha-tested materials (GeometricPrimitive::Intersect/IntersectPred,
 // Primitive.cpp:6-26).  The ray-cast entry points pass NoAlpha; the integrator
 // passes a functor that evaluates the material's alpha texture.
-// operator()(mesh, prim, inst_record, u, v) -> accept the hit?
+// operator()(mesh, prim, inst_record, u, v, ray index) -> accept the hit?
 struct NoAlpha {
-    __device__ __forceinline__ bool operator()(uint32_t, uint32_t, uint32_t, float, float) const{ return true; }
+    __device__ __forceinline__ bool operator()(uint32_t, uint32_t, uint32_t, float, float, size_t) const{ return true; }
 };
 
 struct InstData { float4 m0, m1, m2; uint4 meta; float4 b0; float4 b1; };
@@ -408,12 +408,12 @@ __device__ __forceinline__ void trav_step(TravState& s, const DevScene& S, const
                 if(tf & TRI_ALPHA_PATH){
                     // material->HasAlpha(): shape->Intersect + alpha test (Primitive.cpp:6-14)
                     occ = tri_closest(s.r, T, s.tmax, t, u, v) &&
-                          (!(tf & TRI_ALPHA_TEX) || alpha(__float_as_uint(T.b.w), __float_as_uint(T.a.w), s.inst_rec, u, v));
+                          (!(tf & TRI_ALPHA_TEX) || alpha(__float_as_uint(T.b.w), __float_as_uint(T.a.w), s.inst_rec, u, v, ray_idx));
                 } else occ = tri_any(s.r, T, s.tmax);
                 if(occ){ s.flags |= TF_OCCLUDED | TF_DONE; return; }
             } else{
                 if(tri_closest(s.r, T, s.tmax, t, u, v)){
-                    if(!(tf & TRI_ALPHA_TEX) || alpha(__float_as_uint(T.b.w), __float_as_uint(T.a.w), s.inst_rec, u, v)){
+                    if(!(tf & TRI_ALPHA_TEX) || alpha(__float_as_uint(T.b.w), __float_as_uint(T.a.w), s.inst_rec, u, v, ray_idx)){
                         s.tmax = t; s.hu = u; s.hv = v; s.hprim = __float_as_uint(T.a.w); s.hinst = s.inst_id;
                         s.flags |= TF_FOUND_LOCAL;
                     }

@@ -292,3 +292,31 @@ def medium_scene(subdiv=2, g=0.75, density=0.1):
     d, cam = materials_scene(subdiv, sky=True)
     d.scene_medium = d.medium((0.5, 0.5, 0.5), (2.0, 2.2, 2.6), g, density=density)
     return d, cam
+
+
+def alpha_scene(mode=capi.ALPHA_MASK, four_channel=False):
+    """Cornell box with alpha-tested cut-out cards (Material::Alpha inside traversal, Primitive.cpp:6-26):
+    one untransformed card and one inside a rotated instance.  mode = Mask (deterministic) or Blend
+    (stochastic).  four_channel: the opacity comes from the albedo image's 4th channel
+    (Texture::alpha) instead of a separate alpha texture."""
+    d, cam = cornell_scene()
+    n = 32
+    y, x = np.mgrid[0:n, 0:n].astype(np.float32) / n
+    opacity = np.clip(0.5 + 0.5 * np.sin(6.28 * 2 * x) * np.cos(6.28 * 2 * y), 0.0, 1.0)
+    rgb = np.stack([0.2 + 0.6 * x, 0.7 - 0.4 * y, 0.3 + 0 * x], -1)
+    to8 = lambda a: np.ascontiguousarray(np.clip(np.round(a * 255), 0, 255).astype(np.uint8))
+    if four_channel:
+        tex = d.image_u8(to8(np.concatenate([rgb, opacity[..., None]], -1)))
+        mat = d.diffuse(tex, alpha_mode=mode, alpha_cutoff=0.5)
+    else:
+        tex = d.image_u8(to8(rgb))
+        a_tex = d.image_u8(to8(np.repeat(opacity[..., None], 3, -1)))
+        mat = d.diffuse(tex, alpha=a_tex, alpha_mode=mode, alpha_cutoff=0.5)
+    glass = d.dielectric(1.5, d.solid((1.0, 1.0, 1.0)), alpha=d.checker(d.solid((1, 1, 1)), d.solid((0.25, 0.25, 0.25)), (0.25, 0.25)),
+                         alpha_mode=mode)
+    q = quad((0.1, 0.15, 0.9), (0.45, 0, 0), (0, 0.6, 0))
+    d.instance(d.add_blas([d.mesh(q[0], q[1], q[2], q[3], material=mat)]))
+    q2 = quad((-0.5, -0.5, 0.0), (1, 0, 0), (0, 1, 0))
+    b2 = d.add_blas([d.mesh(q2[0], q2[1], q2[2], q2[3], material=glass)])
+    d.instance(b2, trs((0.72, 0.5, 1.1), 0.4, (0, 1, 0), -0.5))
+    return d, cam

@@ -142,3 +142,67 @@ def test_error_paths():
     g = GpuScene(d, 4)
     assert lib.pt_scene_commit(g.h, 4, 1) == -4   # PT_ERR_STATE: already committed
     g.close()
+
+
+def _alpha_rays(n, seed=3):
+    """Rays from in front of the Cornell opening towards the cards (most of them hit a card first)."""
+    rng = np.random.default_rng(seed)
+    o = np.stack([rng.uniform(0.05, 0.95, n), rng.uniform(0.1, 0.9, n), np.full(n, 2.0)], -1).astype(np.float32)
+    tgt = np.stack([rng.uniform(0.05, 0.95, n), rng.uniform(0.1, 0.9, n), np.full(n, 0.9)], -1).astype(np.float32)
+    d = tgt - o
+    d /= np.linalg.norm(d, axis=1, keepdims=True)
+    from pathtracing_b200 import capi
+    rays = np.zeros(n, dtype=capi.RAY_DTYPE)
+    rays["o"], rays["d"] = o, d
+    rays["tmax"] = np.inf
+    return rays
+
+
+@needs_ref
+@pytest.mark.parametrize("width", [2, 4])
+@pytest.mark.parametrize("four_channel", [False, True])
+def test_alpha_mask_inside_traversal_bit_exact(width, four_channel):
+    """AlphaMode::Mask is deterministic: rejected candidates let the ray continue to exactly the hit the
+    reference finds (Primitive.cpp:15-18), for closest-hit and for the any-hit path (Primitive.cpp:6-11)."""
+    from oracle.refapi import RefScene
+    from pathtracing_b200 import capi
+    desc, _ = synth.alpha_scene(capi.ALPHA_MASK, four_channel)
+    ref, gpu = RefScene(desc, width), GpuScene(desc, width)
+    rays = _alpha_rays(60000)
+    rh, _ = ref.trace_closest(rays)
+    gh, gi = gpu.trace_closest(rays)
+    assert np.array_equal(rh["t"].view(np.uint32), gh["t"].view(np.uint32))
+    hit = gh["prim"] != 0xFFFFFFFF
+    # the cards are instances 1 and 2: some rays stop on them, some pass through the cut-outs
+    assert 0.05 < (gi[hit] == 1).mean() < 0.6 and (gi[hit] == 2).any() and (gi[hit] == 0).mean() > 0.2
+    rays["tmax"] = 1.6
+    assert np.array_equal(ref.trace_any(rays), gpu.trace_any(rays))
+    gpu.close(); ref.close()
+
+
+@needs_ref
+def test_alpha_blend_inside_traversal_statistics():
+    """AlphaMode::Blend accepts a candidate with probability alpha(uv): per-ray outcomes differ from the
+    reference's (its draw is an unseeded thread-local PCG), the acceptance rate per opacity bin may not."""
+    from oracle.refapi import RefScene
+    from pathtracing_b200 import capi
+    desc, _ = synth.alpha_scene(capi.ALPHA_BLEND)
+    ref, gpu = RefScene(desc, 4), GpuScene(desc, 4)
+    rays = _alpha_rays(400000)
+    rh, ri = ref.trace_closest(rays, want_inst=True)
+    gh, gi = gpu.trace_closest(rays)
+    # card 1 is the nearest surface wherever it is hit: its hits have t below any other surface's
+    for k in (1, 2):
+        pr, pg = float((ri == k).mean()), float((gi == k).mean())
+        se = np.sqrt(pr * (1 - pr) / len(rays) * 2)
+        assert abs(pr - pg) < 5 * se + 1e-4, (k, pr, pg)
+    t_r, t_g = rh["t"][np.isfinite(rh["t"])], gh["t"][np.isfinite(gh["t"])]
+    assert abs(t_r.mean() - t_g.mean()) < 5 * np.sqrt((t_r.var() + t_g.var()) / len(t_r))
+    rays["tmax"] = 1.6
+    o_r, o_g = ref.trace_any(rays).mean(), gpu.trace_any(rays).mean()
+    assert abs(o_r - o_g) < 5 * np.sqrt(o_r * (1 - o_r) * 2 / len(rays)) + 1e-4, (o_r, o_g)
+    # two launches draw differently (the salt advances)
+    gh2, _ = gpu.trace_closest(rays)
+    gh3, _ = gpu.trace_closest(rays)
+    assert (gh2["t"] != gh3["t"]).mean() > 0.01
+    gpu.close(); ref.close()
