@@ -518,19 +518,29 @@ PT_API int ref_render(void* p, const pt_camera_desc* cd, const pt_render_params*
             FilmTile tile = film->GetFilmTile({ {minX,minY},{maxX,maxY} });
             for(int y = minY;y < maxY;y++){
                 for(int x = minX;x < maxX;x++){
-                    for(uint32_t si = 0;si < spp;si++){
-                        cloned->StartPixelSample({ x,y }, si);
-                        glm::dvec2 pp = glm::dvec2 { x,y } + cloned->getPixel2D();
-                        float time = cloned->get1D();
-                        Ray ray = camera->GenerateRay(pp, time, cloned->get2D());
-                        glm::dvec3 color = integrator->Li(ray);
-                        tile.Add(pp, color);
-                        if(sumsq){
-                            // owner pixel is this thread's tile: no race
-                            double* q = sumsq + 3 * ((size_t)y * W + x);
-                            q[0] += color.x * color.x; q[1] += color.y * color.y; q[2] += color.z * color.z;
+                    // rp->adaptive: the stopping rule of TileIntegrator::Render (Integrators.cpp:59-86) with the
+                    // reference's own VarianceEstimator; otherwise exactly one round of spp samples
+                    VarianceEstimator estimator[3];
+                    while(estimator[0].Samples() < (rp->adaptive ? 128u : 1u) * spp){
+                        for(uint32_t si = 0;si < spp;si++){
+                            cloned->StartPixelSample({ x,y }, si);
+                            glm::dvec2 pp = glm::dvec2 { x,y } + cloned->getPixel2D();
+                            float time = cloned->get1D();
+                            Ray ray = camera->GenerateRay(pp, time, cloned->get2D());
+                            glm::dvec3 color = integrator->Li(ray);
+                            tile.Add(pp, color);
+                            if(sumsq){
+                                // owner pixel is this thread's tile: no race
+                                double* q = sumsq + 3 * ((size_t)y * W + x);
+                                q[0] += color.x * color.x; q[1] += color.y * color.y; q[2] += color.z * color.z;
+                            }
+                            ++mySamples;
+                            color *= glm::dvec3(0.2126f, 0.7152f, 0.0722f);
+                            estimator[0].Add(color[0]); estimator[1].Add(color[1]); estimator[2].Add(color[2]);
                         }
-                        ++mySamples;
+                        const float minRelativeVariance = 1.5;
+                        if(estimator[0].RelativeVariance() <= minRelativeVariance && estimator[1].RelativeVariance() <= minRelativeVariance &&
+                           estimator[2].RelativeVariance() <= minRelativeVariance)break;
                     }
                 }
             }

@@ -55,13 +55,22 @@ struct BatchInfo {
     int W, H, pass_begin, pass_stride, max_depth;
     int sampler, sx, sy;   // 0 UniformSampler | 1 StratifiedSampler(sx, sy)
     uint64_t seed;
+    // adaptive rounds after the first: only the pixels still listed get samples; id = k * n_list + j
+    // -> pixel list[j], sample index sample_base + k
+    const uint32_t* list;
+    uint32_t n_list, sample_base;
 };
 
 __device__ __forceinline__ uint64_t stream_of(const BatchInfo& B, uint32_t slot, uint32_t& pixel, uint32_t& sample){
     const uint64_t g = B.first + slot;
     const uint64_t wh = (uint64_t)B.W * B.H;
-    pixel = (uint32_t)(g % wh);
-    sample = (uint32_t)(B.pass_begin + (g / wh) * B.pass_stride);
+    if(B.list){
+        pixel = B.list[g % B.n_list];
+        sample = B.sample_base + (uint32_t)(g / B.n_list);
+    } else{
+        pixel = (uint32_t)(g % wh);
+        sample = (uint32_t)(B.pass_begin + (g / wh) * B.pass_stride);
+    }
     return (uint64_t)sample * wh + pixel;
 }
 
@@ -94,12 +103,13 @@ __global__ void __launch_bounds__(256) k_generate(Arena A, BatchInfo B, CamParam
         // StratifiedSampler (Sampler.hpp:73-151): dimensions 0-1 pixel, 2 time, 3-4 lens; the stratum of
         // sample `index` is a hash-seeded permutation, the jitter inside it is random_float()
         const uint32_t nS = (uint32_t)(B.sx * B.sy);
-        uint32_t st = permutation_element(sample, nS, (uint32_t)hash_ppd((uint32_t)x, (uint32_t)y, 0));
+        const uint32_t index = sample - B.sample_base;           // sample_index restarts every adaptive round (Integrators.cpp:60)
+        uint32_t st = permutation_element(index, nS, (uint32_t)hash_ppd((uint32_t)x, (uint32_t)y, 0));
         jx = ((double)(st % (uint32_t)B.sx) + (double)rnd_float(g)) / (double)B.sx;
         jy = ((double)(st / (uint32_t)B.sx) + (double)rnd_float(g)) / (double)B.sy;
-        st = permutation_element(sample, nS, (uint32_t)hash_ppd((uint32_t)x, (uint32_t)y, 2));
+        st = permutation_element(index, nS, (uint32_t)hash_ppd((uint32_t)x, (uint32_t)y, 2));
         time = (float)(((double)st + (double)rnd_float(g)) / (double)nS);
-        st = permutation_element(sample, nS, (uint32_t)hash_ppd((uint32_t)x, (uint32_t)y, 3));
+        st = permutation_element(index, nS, (uint32_t)hash_ppd((uint32_t)x, (uint32_t)y, 3));
         lx = (float)(((double)(st % (uint32_t)B.sx) + (double)rnd_float(g)) / (double)B.sx);
         ly = (float)(((double)(st / (uint32_t)B.sx) + (double)rnd_float(g)) / (double)B.sy);
     }
@@ -181,7 +191,8 @@ __device__ inline double filter_eval(const FilterParams& F, float x, float y){
     }
 }
 
-__global__ void __launch_bounds__(256) k_film(Arena A, BatchInfo B, FilterParams F, double* __restrict__ film, double* __restrict__ film_sq){
+// est: this call's per-pixel estimator sums for the adaptive loop, 6 doubles per pixel {sum rgb, sum of squares rgb}, or null
+__global__ void __launch_bounds__(256) k_film(Arena A, BatchInfo B, FilterParams F, double* __restrict__ film, double* __restrict__ film_sq, double* __restrict__ est){
     const uint32_t slot = blockIdx.x * blockDim.x + threadIdx.x;
     if(slot >= B.count)return;
     uint32_t pixel, sample;
@@ -193,6 +204,11 @@ __global__ void __launch_bounds__(256) k_film(Arena A, BatchInfo B, FilterParams
         // and VarianceEstimator (Util.hpp:8-43) need
         double* q = film_sq + 3 * ((size_t)y * B.W + x);
         atomicAdd(q, (double)r.x * r.x); atomicAdd(q + 1, (double)r.y * r.y); atomicAdd(q + 2, (double)r.z * r.z);
+        if(est){
+            double* e = est + 6 * ((size_t)y * B.W + x);
+            atomicAdd(e, (double)r.x); atomicAdd(e + 1, (double)r.y); atomicAdd(e + 2, (double)r.z);
+            atomicAdd(e + 3, (double)r.x * r.x); atomicAdd(e + 4, (double)r.y * r.y); atomicAdd(e + 5, (double)r.z * r.z);
+        }
     }
     for(int dy = -F.ry; dy <= F.ry; dy++)for(int dx = -F.rx; dx <= F.rx; dx++){
         const float fx = (float)((double)dx + 0.5 - (double)sp.x), fy = (float)((double)dy + 0.5 - (double)sp.y);   // Filter::Evaluate takes a glm::vec2
@@ -202,6 +218,30 @@ __global__ void __launch_bounds__(256) k_film(Arena A, BatchInfo B, FilterParams
         double* q = film + 4 * ((size_t)qy * B.W + qx);
         atomicAdd(q, (double)r.x * w); atomicAdd(q + 1, (double)r.y * w); atomicAdd(q + 2, (double)r.z * w); atomicAdd(q + 3, w);
     }
+}
+
+// ---- adaptive loop: the per-pixel stopping rule of TileIntegrator::Render (Integrators.cpp:59-86) ----
+// After a round of spp samples a pixel goes on while any channel's RelativeVariance
+// (1.96 * sqrt(Var / n) / mean, 0 when mean == 0; Util.hpp:38-40) exceeds 1.5 and n < 128 * spp.  The
+// reference weights the channels by the luminance coefficients first; the ratio does not change.
+// in == null: every pixel was sampled this round.  n = samples per pixel so far.
+__global__ void __launch_bounds__(256) k_adapt(const double* __restrict__ est, const uint32_t* __restrict__ in, uint32_t n_in,
+                                               uint32_t* __restrict__ out, uint32_t* __restrict__ n_out, double n){
+    const uint32_t j = blockIdx.x * blockDim.x + threadIdx.x;
+    bool more = false;
+    uint32_t pixel = 0;
+    if(j < n_in){
+        pixel = in ? in[j] : j;
+        const double* e = est + 6 * (size_t)pixel;
+        for(int c = 0; c < 3; c++){
+            const double mean = e[c] / n;
+            const double var = n > 1.0 ? fmax(0.0, e[3 + c] - n * mean * mean) / (n - 1.0) : 0.0;
+            const double rel = mean == 0.0 ? 0.0 : 1.96 * sqrt(var / n) / mean;
+            more = more || !(rel <= 1.5);
+        }
+    }
+    const uint32_t at = queue_slot(n_out, more);
+    if(more)out[at] = pixel;
 }
 
 // ---- shade: one bounce of Li() for every queue entry ------------------------------------------
@@ -471,7 +511,8 @@ int render_passes(pt_scene* s, const pt_camera_desc* cam, const pt_render_params
     if(rp->sampler != 0 && rp->sampler != 1){ set_error("unknown sampler"); return PT_ERR_INVALID; }
     if(rp->sampler == 1 && (rp->strata_x <= 0 || rp->strata_y <= 0 || rp->strata_x * rp->strata_y != rp->spp)){
         set_error("StratifiedSampler: spp must equal strata_x * strata_y (Sampler.hpp:84)"); return PT_ERR_INVALID; }
-    if(rp->adaptive){ set_error("adaptive sampling is not built yet: use adaptive = 0 (exactly spp samples per pixel)"); return PT_ERR_INVALID; }
+    if(rp->adaptive && (rp->pass_begin != 0 || rp->pass_stride != 1)){
+        set_error("adaptive sampling decides per pixel from all of its samples: it cannot be combined with pass sharding"); return PT_ERR_INVALID; }
     if(cam->medium >= (int)s->media.size()){ set_error("camera medium id out of range"); return PT_ERR_INVALID; }
     FilterParams F;
     int rc = make_filter(rp, F);
@@ -505,6 +546,20 @@ int render_passes(pt_scene* s, const pt_camera_desc* cam, const pt_render_params
         b.work_bytes = need;
     }
     arena_layout((char*)b.work, A, cap);
+    // adaptive loop state: estimator sums (6 doubles / pixel), two pixel lists, a counter
+    const size_t npix = (size_t)W * H;
+    double* est = nullptr; uint32_t* lists[2] = { nullptr, nullptr }; uint32_t* list_n = nullptr;
+    if(rp->adaptive){
+        const size_t bytes = npix * (48 + 8) + 256;
+        if(bytes > b.adapt_bytes){
+            if(b.adapt){ cudaFree(b.adapt); b.adapt = nullptr; b.adapt_bytes = 0; }
+            if(!cuda_ok(cudaMalloc(&b.adapt, bytes), "cudaMalloc adaptive state"))return PT_ERR_NOMEM;
+            b.adapt_bytes = bytes;
+        }
+        est = (double*)b.adapt;
+        lists[0] = (uint32_t*)(est + 6 * npix); lists[1] = lists[0] + npix; list_n = lists[1] + npix;
+        if(!cuda_ok(cudaMemsetAsync(est, 0, 48 * npix, st), "estimator clear"))return PT_ERR_CUDA;
+    }
     uint32_t* h_counters = nullptr;
     if(!cuda_ok(cudaMallocHost(&h_counters, 64), "pinned counters"))return PT_ERR_CUDA;
     cudaEvent_t e0, e1;
@@ -513,20 +568,23 @@ int render_passes(pt_scene* s, const pt_camera_desc* cam, const pt_render_params
     pt_render_stats R {};
     auto fail = [&](int code){ cudaFreeHost(h_counters); cudaEventDestroy(e0); cudaEventDestroy(e1); return code; };
 
-    for(uint64_t first = 0; first < total; first += cap){
+    // one set of samples through the wavefront: `count` camera samples in batches of at most `cap`
+    auto run = [&](uint64_t count, const uint32_t* list, uint32_t n_list, uint32_t sample_base) -> int {
+      for(uint64_t first = 0; first < count; first += cap){
         BatchInfo B;
-        B.first = first; B.count = (uint32_t)std::min<uint64_t>(cap, total - first);
+        B.first = first; B.count = (uint32_t)std::min<uint64_t>(cap, count - first);
         B.W = W; B.H = H; B.pass_begin = rp->pass_begin; B.pass_stride = rp->pass_stride; B.max_depth = rp->max_depth; B.seed = rp->seed;
         B.sampler = rp->sampler; B.sx = rp->strata_x; B.sy = rp->strata_y;
+        B.list = list; B.n_list = n_list; B.sample_base = sample_base;
         k_generate<<<(B.count + 255) / 256, 256, 0, st>>>(A, B, C);
         R.kernel_launches++;
         uint32_t n = rp->max_depth > 0 ? B.count : 0;    // `depth++ < maxDepth` fails at once: black samples
         int cur = 0;
         while(n > 0){
-            rc = launch_trace_closest(s, A.rays[cur], n, A.hits, A.hinst, st);
-            if(rc != PT_OK)return fail(rc);
+            int rc = launch_trace_closest(s, A.rays[cur], n, A.hits, A.hinst, st);
+            if(rc != PT_OK)return rc;
             R.closest_rays += n; R.kernel_launches++;
-            if(!cuda_ok(cudaMemsetAsync(A.counters, 0, 8, st), "counter reset"))return fail(PT_ERR_CUDA);
+            if(!cuda_ok(cudaMemsetAsync(A.counters, 0, 8, st), "counter reset"))return PT_ERR_CUDA;
             const unsigned grid = (n + 127) / 128;
             switch(rp->integrator){
             case PT_INTEGRATOR_SIMPLE: k_shade<PT_INTEGRATOR_SIMPLE><<<grid, 128, 0, st>>>(A, s->shade, B, n, cur); break;
@@ -535,19 +593,41 @@ int render_passes(pt_scene* s, const pt_camera_desc* cam, const pt_render_params
             }
             R.kernel_launches++;
             if(!cuda_ok(cudaMemcpyAsync(h_counters, A.counters, 8, cudaMemcpyDeviceToHost, st), "counters D2H") ||
-               !cuda_ok(cudaStreamSynchronize(st), "shade"))return fail(PT_ERR_CUDA);
+               !cuda_ok(cudaStreamSynchronize(st), "shade"))return PT_ERR_CUDA;
             const uint32_t n_next = h_counters[0], n_sh = h_counters[1];
             if(n_sh > 0){
                 rc = launch_trace_any(s, A.srays, n_sh, A.socc, st);
-                if(rc != PT_OK)return fail(rc);
+                if(rc != PT_OK)return rc;
                 k_connect<<<(n_sh + 255) / 256, 256, 0, st>>>(A, n_sh);
                 R.shadow_rays += n_sh; R.kernel_launches += 2;
             }
             n = n_next; cur ^= 1;
         }
-        k_film<<<(B.count + 255) / 256, 256, 0, st>>>(A, B, F, (double*)b.film, (double*)b.film_sq);
+        k_film<<<(B.count + 255) / 256, 256, 0, st>>>(A, B, F, (double*)b.film, (double*)b.film_sq, est);
         R.kernel_launches++;
         R.samples += B.count;
+      }
+      return PT_OK;
+    };
+
+    rc = run(total, nullptr, 0, 0);
+    if(rc != PT_OK)return fail(rc);
+    if(rp->adaptive){
+        // rounds 2..128 over the pixels the stopping rule keeps (Integrators.cpp:59,82-85)
+        const uint32_t* in = nullptr;
+        uint32_t n_in = (uint32_t)npix;
+        for(int round = 1; round < 128 && n_in > 0; round++){
+            uint32_t* out = lists[round & 1];
+            if(!cuda_ok(cudaMemsetAsync(list_n, 0, 4, st), "list reset"))return fail(PT_ERR_CUDA);
+            k_adapt<<<(n_in + 255) / 256, 256, 0, st>>>(est, in, n_in, out, list_n, (double)round * rp->spp);
+            R.kernel_launches++;
+            if(!cuda_ok(cudaMemcpyAsync(h_counters + 8, list_n, 4, cudaMemcpyDeviceToHost, st), "list size D2H") ||
+               !cuda_ok(cudaStreamSynchronize(st), "adapt"))return fail(PT_ERR_CUDA);
+            n_in = h_counters[8]; in = out;
+            if(n_in == 0)break;
+            rc = run((uint64_t)n_in * rp->spp, in, n_in, (uint32_t)round * (uint32_t)rp->spp);
+            if(rc != PT_OK)return fail(rc);
+        }
     }
     cudaEventRecord(e1, st);
     if(!cuda_ok(cudaStreamSynchronize(st), "render"))return fail(PT_ERR_CUDA);

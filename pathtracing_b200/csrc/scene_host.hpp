@@ -54,6 +54,8 @@ struct DeviceBuffers {
     void* film_sq = nullptr;      // per-pixel sum of squared sample radiance, double[3*W*H]
     void* work = nullptr;         // wavefront state arena
     size_t work_bytes = 0;
+    void* adapt = nullptr;        // adaptive loop: per-pixel estimator sums + pixel lists
+    size_t adapt_bytes = 0;
     // staging for the host-buffer ray-cast entry points
     void* stage_rays = nullptr; void* stage_hits = nullptr; void* stage_inst = nullptr; void* stage_occ = nullptr;
     size_t stage_cap = 0;

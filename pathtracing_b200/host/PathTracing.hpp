@@ -1,0 +1,870 @@
+// PathTracing.hpp — the reference's C++20 object API (Scene / Mesh / Model / BLASx / TLASx / Camera /
+// Film / Sampler / *Integrator, examples/example_1.cpp:17-122) as thin host objects over the C-ABI of
+// include/pt_b200.h.  The objects hold plain descriptions; nothing is traced on the CPU.  The GPU scene
+// is assembled and committed the first time an integrator renders (or a ray is cast), because the
+// reference lets the light sampler be attached after Scene::BuildTlas (example_1.cpp:97-102).
+//
+// Same class names, constructor signatures and method names as the reference headers cited per class.
+// What has no GPU counterpart yet is a compile-time absence (SphereShape / QuadShape, BVH8, file-loading
+// texture ctors, per-triangle GeometricPrimitive lists), not a silent approximation.
+#pragma once
+#include <cmath>
+#include <cstdint>
+#include <cstdio>
+#include <cstring>
+#include <fstream>
+#include <functional>
+#include <limits>
+#include <memory>
+#include <stdexcept>
+#include <string>
+#include <unordered_map>
+#include <vector>
+
+#include <glm/glm.hpp>
+
+#include "pt_b200.h"
+
+namespace ptb_host {
+
+inline void check(int rc, const char* what){
+    if(rc < 0)throw std::runtime_error(std::string(what) + ": " + pt_last_error());
+}
+
+// Collects ids while the object graph is lowered into one pt_scene.
+struct Builder {
+    pt_scene* scene = nullptr;
+    std::unordered_map<const void*, int> ids;     // texture / material / medium / mesh / blas object -> id
+    int lookup(const void* p) const{ auto it = ids.find(p); return it == ids.end() ? -1 : it->second; }
+};
+
+} // namespace ptb_host
+
+// ---- Ray.hpp:14-41, AABB.hpp:9-70, Interaction.hpp:36-51 ------------------------------------------
+class Medium;
+struct Ray {
+    Ray() = default;
+    Ray(const glm::vec3& origin, const glm::vec3& direction, float time = 0.0f, const std::shared_ptr<Medium>& medium = nullptr)
+        : origin(origin), dir(direction), time(time), medium(medium){}
+    glm::vec3 at(float t) const{ return origin + dir * t; }
+    glm::vec3 origin { 0, 0, 0 }, dir { 0, 0, 1 };
+    float time = 0.0f;
+    std::shared_ptr<Medium> medium;
+};
+
+struct AABB {
+    glm::vec3 min { std::numeric_limits<float>::infinity() }, max { -std::numeric_limits<float>::infinity() };
+    void Expand(const glm::vec3& p){
+        for(int a = 0; a < 3; a++){ if(p[a] < min[a])min[a] = p[a]; if(p[a] > max[a])max[a] = p[a]; }
+    }
+};
+
+// What one GPU hit record carries back; the shading frame itself is rebuilt on the device
+// (csrc/shade.cuh build_interaction) and never crosses the boundary.
+struct SurfaceInteraction {
+    glm::vec3 p { 0, 0, 0 };
+    float t = std::numeric_limits<float>::infinity();
+    glm::vec2 barycentric { 0, 0 };
+    uint32_t primitive = PT_MISS;    // triangle index inside its BLAS
+    uint32_t instance = PT_MISS;     // index in Scene::Add order
+};
+
+// ---- Texture.hpp:108-232 --------------------------------------------------------------------------
+class Texture {
+public:
+    Texture(const glm::vec3& colorScale = glm::vec3(1, 1, 1)) : colorScale(colorScale){}
+    virtual ~Texture() = default;
+    virtual int Channels() const{ return 3; }
+    int Emit(ptb_host::Builder& b) const{
+        int id = b.lookup(this);
+        if(id >= 0)return id;
+        pt_texture_desc d;
+        std::memset(&d, 0, sizeof d);
+        d.color_scale[0] = colorScale.x; d.color_scale[1] = colorScale.y; d.color_scale[2] = colorScale.z;
+        d.tex_a = d.tex_b = -1;
+        Describe(b, d);
+        id = pt_scene_add_texture(b.scene, &d);
+        ptb_host::check(id, "pt_scene_add_texture");
+        b.ids[this] = id;
+        return id;
+    }
+protected:
+    virtual void Describe(ptb_host::Builder& b, pt_texture_desc& d) const = 0;
+    glm::vec3 colorScale;
+};
+
+class SolidColor : public Texture {
+public:
+    SolidColor(const glm::vec3& color, const glm::vec3& colorScale = glm::vec3(1)) : Texture(colorScale), color(color){}
+    SolidColor(float r, float g, float b) : SolidColor(glm::vec3(r, g, b)){}
+protected:
+    void Describe(ptb_host::Builder&, pt_texture_desc& d) const override{
+        d.kind = PT_TEX_SOLID; d.color[0] = color.x; d.color[1] = color.y; d.color[2] = color.z;
+    }
+private:
+    glm::vec3 color;
+};
+
+// The reference builds image textures from a file name (stb_image, Texture.cpp:4-36).  Decoding is host
+// I/O outside the hot path: here the caller hands over the decoded texels (row 0 first, 1-4 channels,
+// sRGB->linear already applied if the reference would have loaded with gammaCorrection).
+class ImageTexture : public Texture {
+public:
+    ImageTexture(std::vector<uint8_t> texels, int width, int height, int channels, const glm::vec3& colorScale = glm::vec3(1))
+        : Texture(colorScale), texels(std::move(texels)), width(width), height(height), channels(channels){
+        if((size_t)width * height * channels != this->texels.size())throw std::invalid_argument("ImageTexture: texel count");
+    }
+    int Channels() const override{ return channels; }
+protected:
+    void Describe(ptb_host::Builder&, pt_texture_desc& d) const override{
+        d.kind = PT_TEX_IMAGE_U8; d.width = width; d.height = height; d.channels = channels; d.pixels = texels.data();
+    }
+private:
+    std::vector<uint8_t> texels;
+    int width, height, channels;
+};
+
+class FloatImageTexture : public Texture {
+public:
+    FloatImageTexture(std::vector<float> texels, int width, int height, int channels, const glm::vec3& colorScale = glm::vec3(1))
+        : Texture(colorScale), texels(std::move(texels)), width(width), height(height), channels(channels){
+        if((size_t)width * height * channels != this->texels.size())throw std::invalid_argument("FloatImageTexture: texel count");
+    }
+    int Channels() const override{ return channels; }
+protected:
+    void Describe(ptb_host::Builder&, pt_texture_desc& d) const override{
+        d.kind = PT_TEX_IMAGE_F32; d.width = width; d.height = height; d.channels = channels; d.pixels = texels.data();
+    }
+private:
+    std::vector<float> texels;
+    int width, height, channels;
+};
+
+class CheckerTexture : public Texture {
+public:
+    CheckerTexture(const std::shared_ptr<Texture>& textureA, const std::shared_ptr<Texture>& textureB, const glm::vec2& uvscale,
+                   const glm::vec3& colorScale = glm::vec3(1)) : Texture(colorScale), tex1(textureA), tex2(textureB), uvscale(uvscale){}
+    int Channels() const override{ return tex1->Channels(); }
+protected:
+    void Describe(ptb_host::Builder& b, pt_texture_desc& d) const override{
+        d.kind = PT_TEX_CHECKER; d.tex_a = tex1->Emit(b); d.tex_b = tex2->Emit(b); d.uv_scale[0] = uvscale.x; d.uv_scale[1] = uvscale.y;
+    }
+private:
+    std::shared_ptr<Texture> tex1, tex2;
+    glm::vec2 uvscale;
+};
+
+class UVTexture : public Texture {
+protected:
+    void Describe(ptb_host::Builder&, pt_texture_desc& d) const override{ d.kind = PT_TEX_UV; }
+};
+class NormalTexture : public Texture {
+protected:
+    void Describe(ptb_host::Builder&, pt_texture_desc& d) const override{ d.kind = PT_TEX_NORMAL; }
+};
+
+// ---- Material.hpp:147-673 -------------------------------------------------------------------------
+enum class AlphaMode { Opaque, Blend, Mask };
+struct AlphaTester {
+    AlphaTester(AlphaMode mode, float cutoff = 0.5f) : mode(mode), cutoff(cutoff){}
+    AlphaTester() = default;
+    AlphaMode mode = AlphaMode::Blend;      // the reference's default (Material.hpp:196)
+    float cutoff = 0.5f;
+};
+
+class Material {
+public:
+    virtual ~Material() = default;
+    int Emit(ptb_host::Builder& b) const{
+        int id = b.lookup(this);
+        if(id >= 0)return id;
+        pt_material_desc d;
+        std::memset(&d, 0, sizeof d);
+        d.tex = d.norm = d.rough = d.metal = d.alpha = -1;
+        d.ri = 1.0f; d.alpha_mode = PT_ALPHA_BLEND; d.alpha_cutoff = 0.5f;
+        Describe(b, d);
+        id = pt_scene_add_material(b.scene, &d);
+        ptb_host::check(id, "pt_scene_add_material");
+        b.ids[this] = id;
+        return id;
+    }
+protected:
+    virtual void Describe(ptb_host::Builder& b, pt_material_desc& d) const = 0;
+    static int opt(ptb_host::Builder& b, const std::shared_ptr<Texture>& t){ return t ? t->Emit(b) : -1; }
+    static int mode(const AlphaTester& t){ return t.mode == AlphaMode::Opaque ? PT_ALPHA_OPAQUE : t.mode == AlphaMode::Mask ? PT_ALPHA_MASK : PT_ALPHA_BLEND; }
+};
+
+class MicrofacetDiffuse : public Material {
+public:
+    MicrofacetDiffuse(const glm::vec3& albedo) : MicrofacetDiffuse(std::make_shared<SolidColor>(albedo)){}
+    MicrofacetDiffuse(const std::shared_ptr<Texture>& tex, const std::shared_ptr<Texture>& norm = nullptr,
+                      const std::shared_ptr<Texture>& roughnessTexture = std::make_shared<SolidColor>(glm::vec3(1)),
+                      const std::shared_ptr<Texture>& metallicTexture = std::make_shared<SolidColor>(glm::vec3(0)),
+                      const std::shared_ptr<Texture>& alpha = nullptr)
+        : tex(tex), norm(norm), roughnessTexture(roughnessTexture), metallicTexture(metallicTexture), alpha(alpha){}
+    // Material.hpp:350-353: without an alpha texture or a 4-channel albedo the tester is demoted to Opaque
+    void setAlphaTester(AlphaTester tester){
+        alphaTester = tester;
+        if(alpha == nullptr && tex->Channels() != 4)alphaTester.mode = AlphaMode::Opaque;
+    }
+protected:
+    void Describe(ptb_host::Builder& b, pt_material_desc& d) const override{
+        d.kind = PT_MAT_DIFFUSE; d.tex = tex->Emit(b); d.norm = opt(b, norm); d.rough = opt(b, roughnessTexture);
+        d.metal = opt(b, metallicTexture); d.alpha = opt(b, alpha); d.alpha_mode = mode(alphaTester); d.alpha_cutoff = alphaTester.cutoff;
+    }
+private:
+    std::shared_ptr<Texture> tex, norm, roughnessTexture, metallicTexture, alpha;
+    AlphaTester alphaTester;
+};
+
+class MicrofacetDielectric : public Material {
+public:
+    MicrofacetDielectric(float refIndex, const glm::vec3& albedo) : MicrofacetDielectric(refIndex, std::make_shared<SolidColor>(albedo)){}
+    MicrofacetDielectric(float refIndex, float roughness, const glm::vec3& albedo)
+        : MicrofacetDielectric(refIndex, std::make_shared<SolidColor>(albedo), nullptr, std::make_shared<SolidColor>(glm::vec3(roughness))){}
+    MicrofacetDielectric(float refIndex, const std::shared_ptr<Texture>& tex, const std::shared_ptr<Texture>& norm = nullptr,
+                         const std::shared_ptr<Texture>& roughnessTexture = std::make_shared<SolidColor>(glm::vec3(0.0f)),
+                         const std::shared_ptr<Texture>& alpha = nullptr)
+        : ri(refIndex), tex(tex), norm(norm), roughnessTexture(roughnessTexture), alpha(alpha){}
+    void setAlphaTester(AlphaTester tester){
+        alphaTester = tester;
+        if(alpha == nullptr && tex->Channels() != 4)alphaTester.mode = AlphaMode::Opaque;
+    }
+protected:
+    void Describe(ptb_host::Builder& b, pt_material_desc& d) const override{
+        d.kind = PT_MAT_DIELECTRIC; d.ri = ri; d.tex = tex->Emit(b); d.norm = opt(b, norm); d.rough = opt(b, roughnessTexture);
+        d.alpha = opt(b, alpha); d.alpha_mode = mode(alphaTester); d.alpha_cutoff = alphaTester.cutoff;
+    }
+private:
+    float ri;
+    std::shared_ptr<Texture> tex, norm, roughnessTexture, alpha;
+    AlphaTester alphaTester;
+};
+
+class ThinDielectric : public Material {
+public:
+    ThinDielectric(float eta, const std::shared_ptr<Texture>& tex) : ri(eta), albedo(tex != nullptr ? tex : std::make_shared<SolidColor>(glm::vec3(1))){}
+protected:
+    void Describe(ptb_host::Builder& b, pt_material_desc& d) const override{ d.kind = PT_MAT_THIN_DIELECTRIC; d.ri = ri; d.tex = albedo->Emit(b); }
+private:
+    float ri;
+    std::shared_ptr<Texture> albedo;
+};
+
+class SpecularConductor : public Material {
+public:
+    SpecularConductor(const glm::vec3& albedo) : albedo(albedo){}
+protected:
+    void Describe(ptb_host::Builder&, pt_material_desc& d) const override{
+        d.kind = PT_MAT_CONDUCTOR; d.albedo[0] = albedo.x; d.albedo[1] = albedo.y; d.albedo[2] = albedo.z;
+    }
+private:
+    glm::vec3 albedo;
+};
+
+// ---- PhaseFunction.hpp:10-30, Medium.hpp:5-61 ------------------------------------------------------
+class PhaseFunction {
+public:
+    virtual ~PhaseFunction() = default;
+    virtual float G() const = 0;
+};
+class HenyeyGreenstein : public PhaseFunction {
+public:
+    HenyeyGreenstein(float G) : g(glm::clamp(G, -0.99f, 0.99f)){}
+    float G() const override{ return g; }
+private:
+    float g;
+};
+
+class Medium {
+public:
+    virtual ~Medium() = default;
+    virtual int Emit(ptb_host::Builder& b) const = 0;
+};
+class HomogeneusMedium : public Medium {
+public:
+    HomogeneusMedium(const glm::vec3& sigma_a, const glm::vec3& sigma_s, const std::shared_ptr<PhaseFunction> phaseFunction, float density = 1.0f,
+                     const glm::vec3& Le = glm::vec3 { 0, 0, 0 }, float LeDensity = 1.0f)
+        : sigma_a(sigma_a), sigma_s(sigma_s), phase(phaseFunction), density(density), Le(Le), LeDensity(LeDensity){}
+    int Emit(ptb_host::Builder& b) const override{
+        int id = b.lookup(this);
+        if(id >= 0)return id;
+        pt_medium_desc d;
+        for(int a = 0; a < 3; a++){ d.sigma_a[a] = sigma_a[a]; d.sigma_s[a] = sigma_s[a]; d.Le[a] = Le[a]; }
+        d.g = phase ? phase->G() : 0.0f; d.density = density; d.le_density = LeDensity;
+        id = pt_scene_add_medium(b.scene, &d);
+        ptb_host::check(id, "pt_scene_add_medium");
+        b.ids[this] = id;
+        return id;
+    }
+private:
+    glm::vec3 sigma_a, sigma_s;
+    std::shared_ptr<PhaseFunction> phase;
+    float density;
+    glm::vec3 Le;
+    float LeDensity;
+};
+
+// ---- Mesh.hpp:14-95 ---------------------------------------------------------------------------------
+class Mesh {
+public:
+    Mesh(const std::vector<uint32_t>& indices, const std::vector<glm::vec3>& vertices, const std::vector<glm::vec3>& tangents,
+         const std::vector<glm::vec3>& normals, const std::vector<glm::vec2>& texCoords, const std::shared_ptr<Material>& mat,
+         const std::shared_ptr<Texture>& emissiveTex, const std::shared_ptr<Medium>& meshMedium)
+        : indices(indices), vertices(vertices), tangents(tangents), normals(normals), texCoords(texCoords), material(mat),
+          emissiveTexture(emissiveTex), medium(meshMedium){
+        if(normals.size() != vertices.size() || texCoords.size() != vertices.size())throw std::invalid_argument("Mesh: normals and texCoords are per vertex");
+        if(!tangents.empty() && tangents.size() != vertices.size())throw std::invalid_argument("Mesh: tangents are per vertex or empty");
+    }
+    uint32_t GetTriangleCount() const{ return (uint32_t)(indices.size() / 3); }
+    uint32_t GetVertexCount() const{ return (uint32_t)vertices.size(); }
+    const std::vector<uint32_t>& GetIndices() const{ return indices; }
+    const std::vector<glm::vec3>& GetVertices() const{ return vertices; }
+    const std::vector<glm::vec3>& GetTangents() const{ return tangents; }
+    const std::vector<glm::vec3>& GetNormals() const{ return normals; }
+    const std::vector<glm::vec2>& GetTexCoords() const{ return texCoords; }
+    std::shared_ptr<Material> GetMaterial() const{ return material; }
+    std::shared_ptr<Texture> GetEmissiveTexture() const{ return emissiveTexture; }
+    std::shared_ptr<Medium> GetMedium() const{ return medium; }
+
+    // material / medium overrides as Model::BuildBlas(material, medium) applies them (Model.hpp:62-80)
+    int Emit(ptb_host::Builder& b, const std::shared_ptr<Material>& matOverride, const std::shared_ptr<Medium>& medOverride, bool overridden) const{
+        static_assert(sizeof(glm::vec3) == 12 && sizeof(glm::vec2) == 8, "glm vectors must be tightly packed");
+        pt_mesh_desc d;
+        d.positions = &vertices[0].x; d.normals = &normals[0].x; d.texcoords = &texCoords[0].x;
+        d.tangents = tangents.empty() ? nullptr : &tangents[0].x;
+        d.indices = indices.data();
+        d.n_vertices = GetVertexCount(); d.n_triangles = GetTriangleCount();
+        const std::shared_ptr<Material>& m = overridden ? matOverride : material;
+        const std::shared_ptr<Medium>& md = overridden ? medOverride : medium;
+        d.material = m ? m->Emit(b) : -1;
+        d.emissive_tex = emissiveTexture ? emissiveTexture->Emit(b) : -1;
+        d.medium = md ? md->Emit(b) : -1;
+        const int id = pt_scene_add_mesh(b.scene, &d);
+        ptb_host::check(id, "pt_scene_add_mesh");
+        return id;
+    }
+private:
+    std::vector<uint32_t> indices;
+    std::vector<glm::vec3> vertices, tangents, normals;
+    std::vector<glm::vec2> texCoords;
+    std::shared_ptr<Material> material;
+    std::shared_ptr<Texture> emissiveTexture;
+    std::shared_ptr<Medium> medium;
+};
+
+// ---- Light.hpp:16-251 -------------------------------------------------------------------------------
+// Power functions are std::function<float(float)> in the reference; the three every reference scene
+// uses are selectable by value here (pt_light_desc::power_func).
+enum class PowerFunction { SqrtR = 0, FourR = 1, FourSqrtR = 2 };
+
+class Light {
+public:
+    virtual ~Light() = default;
+    virtual bool IsSceneLights() const{ return false; }
+    virtual void Describe(ptb_host::Builder&, pt_light_desc&) const{}
+    int Emit(ptb_host::Builder& b) const{
+        pt_light_desc d;
+        std::memset(&d, 0, sizeof d);
+        d.tex = -1; d.scale = 1.0f;
+        Describe(b, d);
+        const int id = pt_scene_add_light(b.scene, &d);
+        ptb_host::check(id, "pt_scene_add_light");
+        return id;
+    }
+protected:
+    static void set3(float* o, const glm::vec3& v){ o[0] = v.x; o[1] = v.y; o[2] = v.z; }
+};
+class InfiniteLight : public Light {};
+
+class UniformInfiniteLight : public InfiniteLight {
+public:
+    UniformInfiniteLight(const glm::vec3& light_color, PowerFunction powerFunc = PowerFunction::SqrtR) : color(light_color), pf(powerFunc){}
+    void Describe(ptb_host::Builder&, pt_light_desc& d) const override{ d.kind = PT_LIGHT_UNIFORM_INFINITE; set3(d.color, color); d.power_func = (int)pf; }
+private:
+    glm::vec3 color; PowerFunction pf;
+};
+
+// The sky every reference scene passes to FunctionInfiniteLight (main.cpp:108-111):
+// scale * ((1-a) * horizon + a * zenith), a = (dir.y + 1) / 2.  Callable, so the same object also
+// satisfies the reference's std::function<glm::vec3(const Ray&)> parameter.
+struct GradientSky {
+    glm::vec3 horizon { 1, 1, 1 }, zenith { 0.5f, 0.7f, 1.0f };
+    float scale = 1.0f;
+    glm::vec3 operator()(const Ray& ray) const{
+        const float a = 0.5f * (ray.dir.y + 1.0f);
+        return scale * ((1.0f - a) * horizon + a * zenith);
+    }
+};
+class FunctionInfiniteLight : public InfiniteLight {
+public:
+    FunctionInfiniteLight(const GradientSky& lightFunc, PowerFunction powerFunc = PowerFunction::SqrtR) : sky(lightFunc), pf(powerFunc){}
+    void Describe(ptb_host::Builder&, pt_light_desc& d) const override{
+        d.kind = PT_LIGHT_GRADIENT_INFINITE; set3(d.color, sky.horizon); set3(d.color_b, sky.zenith); d.scale = sky.scale; d.power_func = (int)pf;
+    }
+private:
+    GradientSky sky; PowerFunction pf;
+};
+
+class TextureInfiniteLight : public InfiniteLight {
+public:
+    TextureInfiniteLight(const std::shared_ptr<Texture>& tex, float LeScale = 1.0f, PowerFunction powerFunc = PowerFunction::SqrtR) : tex(tex), LeScale(LeScale), pf(powerFunc){}
+    void Describe(ptb_host::Builder& b, pt_light_desc& d) const override{ d.kind = PT_LIGHT_TEXTURE_INFINITE; d.tex = tex->Emit(b); d.scale = LeScale; d.power_func = (int)pf; }
+private:
+    std::shared_ptr<Texture> tex; float LeScale; PowerFunction pf;
+};
+
+class DistantLight : public Light {
+public:
+    DistantLight(const glm::vec3& light_dir, const glm::vec3& light_color, PowerFunction powerFunc = PowerFunction::SqrtR) : dir(light_dir), color(light_color), pf(powerFunc){}
+    void Describe(ptb_host::Builder&, pt_light_desc& d) const override{ d.kind = PT_LIGHT_DISTANT; set3(d.dir_or_pos, dir); set3(d.color, color); d.power_func = (int)pf; }
+private:
+    glm::vec3 dir, color; PowerFunction pf;
+};
+
+class PointLight : public Light {
+public:
+    PointLight(const glm::vec3& p, const glm::vec3& light_color, PowerFunction powerFunc = PowerFunction::FourR) : p(p), color(light_color), pf(powerFunc){}
+    void Describe(ptb_host::Builder&, pt_light_desc& d) const override{ d.kind = PT_LIGHT_POINT; set3(d.dir_or_pos, p); set3(d.color, color); d.power_func = (int)pf; }
+private:
+    glm::vec3 p, color; PowerFunction pf;
+};
+
+// What Scene::GetLights() hands to LightSampler::Add: "every area light of every emissive mesh (through
+// its instance transform) plus the scene's infinite lights".  The GPU scene derives that list itself at
+// commit (csrc/shade_tables.cpp build_lights), in the reference's order.
+class SceneLights : public Light {
+public:
+    bool IsSceneLights() const override{ return true; }
+};
+
+// ---- Primitive.hpp:7-50, Model.hpp:14-80, BVH.hpp:554-555,1219-1220 -----------------------------------
+struct BLAS2 { static constexpr int width = 2; };
+struct BLAS4 { static constexpr int width = 4; };
+struct TLAS2 { static constexpr int width = 2; };
+struct TLAS4 { static constexpr int width = 4; };
+
+class Primitive {
+public:
+    virtual ~Primitive() = default;
+    // adds this primitive's instance(s) to the scene being assembled; transform = column-major mat4 or null
+    virtual void Lower(ptb_host::Builder& b, const glm::mat4* transform) const = 0;
+    virtual int RequiredWidth() const{ return 0; }     // BLAS width this primitive was built with (0: any)
+};
+
+// A bottom-level structure over meshes.  The reference's Model imports a file through assimp
+// (Model.cpp:22-357, host I/O outside the hot path); here the meshes are handed over directly — the
+// constructor the reference keeps commented out at Model.hpp:18.
+class Model : public Primitive {
+public:
+    Model(std::vector<std::shared_ptr<Mesh>> meshes) : meshes(std::move(meshes)){}
+    std::vector<std::shared_ptr<Mesh>> GetMeshes() const{ return meshes; }
+    template <typename T> void BuildBlas(){ width = T::width; overridden = false; }
+    template <typename T> void BuildBlas(const std::shared_ptr<Material>& material, const std::shared_ptr<Medium>& medium){
+        width = T::width; overridden = true; matOverride = material; medOverride = medium;
+    }
+    int RequiredWidth() const override{ return width; }
+    void Lower(ptb_host::Builder& b, const glm::mat4* transform) const override{
+        if(width == 0)throw std::logic_error("Model::BuildBlas<BLAS2|BLAS4>() was not called");
+        int blas = b.lookup(this);
+        if(blas < 0){
+            std::vector<int32_t> ids;
+            for(const std::shared_ptr<Mesh>& m : meshes)ids.push_back(m->Emit(b, matOverride, medOverride, overridden));
+            blas = pt_scene_add_blas(b.scene, ids.data(), (int)ids.size());
+            ptb_host::check(blas, "pt_scene_add_blas");
+            b.ids[this] = blas;
+        }
+        ptb_host::check(pt_scene_add_instance(b.scene, blas, transform ? &(*transform)[0][0] : nullptr), "pt_scene_add_instance");
+    }
+private:
+    std::vector<std::shared_ptr<Mesh>> meshes;
+    int width = 0;
+    bool overridden = false;
+    std::shared_ptr<Material> matOverride;
+    std::shared_ptr<Medium> medOverride;
+};
+
+class TransformedPrimitive : public Primitive {
+public:
+    TransformedPrimitive(const std::shared_ptr<Primitive>& primitive, const glm::mat4& transform) : primitive(primitive), transform(transform){}
+    int RequiredWidth() const override{ return primitive->RequiredWidth(); }
+    void Lower(ptb_host::Builder& b, const glm::mat4* outer) const override{
+        // the reference nests TransformedPrimitives by composing ray transforms; the GPU TLAS holds one
+        // transform per instance, and the per-level renormalisation of the ray direction is not associative
+        if(outer)throw std::logic_error("nested TransformedPrimitive is not supported");
+        primitive->Lower(b, &transform);
+    }
+private:
+    std::shared_ptr<Primitive> primitive;
+    glm::mat4 transform;
+};
+
+// ---- LightSampler.hpp:5-60 ----------------------------------------------------------------------------
+class LightSampler {
+public:
+    virtual ~LightSampler() = default;
+    virtual int Kind() const = 0;                      // pt_scene_commit's light_sampler argument
+    void Add(const std::shared_ptr<Light>& light){
+        if(light->IsSceneLights())sceneLights = true;
+        else lights.push_back(light);
+    }
+    void Add(const std::vector<std::shared_ptr<Light>>& ls){ for(const std::shared_ptr<Light>& l : ls)Add(l); }
+    // powers, culling (< 0.01) and the cdf are computed at commit (csrc/shade_tables.cpp)
+    void PreProcess(const AABB&){}
+    bool HasSceneLights() const{ return sceneLights; }
+    const std::vector<std::shared_ptr<Light>>& ExtraLights() const{ return lights; }
+private:
+    std::vector<std::shared_ptr<Light>> lights;       // lights the user added on top of Scene::GetLights()
+    bool sceneLights = false;
+};
+class UniformLightSampler : public LightSampler { public: int Kind() const override{ return 0; } };
+class PowerLightSampler : public LightSampler { public: int Kind() const override{ return 1; } };
+
+// ---- Scene.hpp:5-40 -------------------------------------------------------------------------------------
+class Scene {
+public:
+    Scene() = default;
+    Scene(const std::shared_ptr<Medium>& medium) : sceneMedium(medium){}
+    Scene(const Scene&) = delete;
+    Scene& operator=(const Scene&) = delete;
+    ~Scene(){ if(gpu)pt_scene_destroy(gpu); }
+
+    void Add(const std::shared_ptr<Primitive>& ptr){ primitives.push_back(ptr); Invalidate(); }
+    std::vector<std::shared_ptr<Light>> GetLights() const{ return { std::make_shared<SceneLights>() }; }
+    template <typename T> void BuildTlas(){ tlasWidth = T::width; Invalidate(); }
+    std::shared_ptr<Medium> GetMedium() const{ return sceneMedium; }
+    void SetMedium(const std::shared_ptr<Medium>& medium){ sceneMedium = medium; Invalidate(); }
+    void SetDevice(int ordinal){ device = ordinal; Invalidate(); }
+
+    AABB BoundingBox(){
+        AABB b;
+        ptb_host::check(pt_scene_bounds(Commit(nullptr), &b.min.x, &b.max.x), "pt_scene_bounds");
+        return b;
+    }
+
+    // one ray through the GPU (a kernel launch per call: use the batch forms for throughput)
+    bool Intersect(const Ray& ray, SurfaceInteraction& interaction, float max = std::numeric_limits<float>::infinity()){
+        const pt_ray r = { ray.origin.x, ray.origin.y, ray.origin.z, max, ray.dir.x, ray.dir.y, ray.dir.z, ray.time };
+        pt_hit h; uint32_t inst = PT_MISS;
+        IntersectBatch(&r, 1, &h, &inst);
+        if(h.prim == PT_MISS)return false;
+        interaction.t = h.t; interaction.p = ray.at(h.t); interaction.barycentric = { h.u, h.v };
+        interaction.primitive = h.prim; interaction.instance = inst;
+        return true;
+    }
+    bool IntersectPred(const Ray& ray, float max = std::numeric_limits<float>::infinity()){
+        const pt_ray r = { ray.origin.x, ray.origin.y, ray.origin.z, max, ray.dir.x, ray.dir.y, ray.dir.z, ray.time };
+        uint8_t occ = 0;
+        IntersectPredBatch(&r, 1, &occ);
+        return occ != 0;
+    }
+    void IntersectBatch(const pt_ray* rays, size_t n, pt_hit* hits, uint32_t* instances = nullptr){
+        ptb_host::check(pt_trace_closest(Commit(nullptr), rays, n, hits, instances), "pt_trace_closest");
+    }
+    void IntersectPredBatch(const pt_ray* rays, size_t n, uint8_t* occluded){
+        ptb_host::check(pt_trace_any(Commit(nullptr), rays, n, occluded), "pt_trace_any");
+    }
+
+    std::vector<std::shared_ptr<InfiniteLight>> infiniteLights;
+
+    // Lowers the object graph into a pt_scene and commits it; cached until the graph or the light
+    // sampler changes.  sampler == nullptr: ray casting only (PowerLightSampler tables are built anyway).
+    pt_scene* Commit(const LightSampler* sampler, const std::shared_ptr<Medium>& cameraMedium = nullptr){
+        if(tlasWidth == 0)throw std::logic_error("Scene::BuildTlas<TLAS2|TLAS4>() was not called");
+        const int kind = sampler ? sampler->Kind() : 1;
+        std::vector<const void*> key;
+        for(const auto& l : infiniteLights)key.push_back(l.get());
+        if(sampler)for(const auto& l : sampler->ExtraLights())key.push_back(l.get());
+        if(sampler && !sampler->HasSceneLights())throw std::logic_error("LightSampler::Add(scene->GetLights()) was not called");
+        const bool newMedium = cameraMedium && MediumId(cameraMedium.get()) < 0;
+        if(gpu && !newMedium && (sampler == nullptr || (kind == committedKind && key == committedKey)))return gpu;
+        if(gpu){ pt_scene_destroy(gpu); gpu = nullptr; }
+        ptb_host::Builder b;
+        b.scene = pt_scene_create(device);
+        if(!b.scene)throw std::runtime_error(std::string("pt_scene_create: ") + pt_last_error());
+        try{
+            for(const std::shared_ptr<Primitive>& p : primitives){
+                const int w = p->RequiredWidth();
+                if(w != 0 && w != tlasWidth)throw std::logic_error("BLAS and TLAS widths must match (BLAS2+TLAS2 or BLAS4+TLAS4)");
+                p->Lower(b, nullptr);
+            }
+            for(const auto& l : infiniteLights)l->Emit(b);
+            if(sampler)for(const auto& l : sampler->ExtraLights())l->Emit(b);
+            if(cameraMedium)cameraMedium->Emit(b);
+            if(sceneMedium)ptb_host::check(pt_scene_set_medium(b.scene, sceneMedium->Emit(b)), "pt_scene_set_medium");
+            ptb_host::check(pt_scene_commit(b.scene, tlasWidth, kind), "pt_scene_commit");
+        } catch(...){
+            pt_scene_destroy(b.scene);
+            throw;
+        }
+        gpu = b.scene; committedKind = kind; committedKey = key; media = b.ids;
+        return gpu;
+    }
+    // id of a medium object in the committed scene (camera medium), -1 if it is not part of it
+    int MediumId(const Medium* m) const{ auto it = media.find(m); return it == media.end() ? -1 : it->second; }
+private:
+    void Invalidate(){ if(gpu){ pt_scene_destroy(gpu); gpu = nullptr; } }
+    std::vector<std::shared_ptr<Primitive>> primitives;
+    std::shared_ptr<Medium> sceneMedium;
+    int tlasWidth = 0, device = 0;
+    pt_scene* gpu = nullptr;
+    int committedKind = -1;
+    std::vector<const void*> committedKey;
+    std::unordered_map<const void*, int> media;
+};
+
+// ---- Filter.hpp:29-144 ------------------------------------------------------------------------------------
+class Filter {
+public:
+    virtual ~Filter() = default;
+    virtual glm::vec2 Radius() const = 0;
+    virtual void Describe(pt_render_params& rp) const = 0;
+protected:
+    static void radius(pt_render_params& rp, const glm::vec2& r){ rp.filter_radius[0] = r.x; rp.filter_radius[1] = r.y; }
+};
+class BoxFilter : public Filter {
+public:
+    BoxFilter(const glm::vec2& filterRadius = glm::vec2 { 0.5f }) : r(filterRadius){}
+    glm::vec2 Radius() const override{ return r; }
+    void Describe(pt_render_params& rp) const override{ rp.filter = PT_FILTER_BOX; radius(rp, r); }
+private:
+    glm::vec2 r;
+};
+class GaussianFilter : public Filter {
+public:
+    GaussianFilter(const glm::vec2& filterRadius = glm::vec2 { 1.5f }, double sigma = 0.5) : r(filterRadius), sigma(sigma){}
+    glm::vec2 Radius() const override{ return r; }
+    void Describe(pt_render_params& rp) const override{ rp.filter = PT_FILTER_GAUSSIAN; radius(rp, r); rp.filter_param[0] = (float)sigma; }
+private:
+    glm::vec2 r; double sigma;
+};
+class MitchellFilter : public Filter {
+public:
+    MitchellFilter(const glm::vec2& radius = glm::vec2 { 1.5f }, double b = 1.0 / 3.0, double c = 1.0 / 3.0) : r(radius), b(b), c(c){}
+    glm::vec2 Radius() const override{ return r; }
+    void Describe(pt_render_params& rp) const override{ rp.filter = PT_FILTER_MITCHELL; radius(rp, r); rp.filter_param[0] = (float)b; rp.filter_param[1] = (float)c; }
+private:
+    glm::vec2 r; double b, c;
+};
+class LanczosFilter : public Filter {
+public:
+    LanczosFilter(const glm::vec2& filterRadius = glm::vec2 { 1.5f }, double tau = 3) : r(filterRadius), tau(tau){}
+    glm::vec2 Radius() const override{ return r; }
+    void Describe(pt_render_params& rp) const override{ rp.filter = PT_FILTER_LANCZOS; radius(rp, r); rp.filter_param[0] = (float)tau; }
+private:
+    glm::vec2 r; double tau;
+};
+
+// ---- Film.hpp:22-47,112-225 ---------------------------------------------------------------------------------
+inline double luminance(const glm::dvec3& v){ return 0.2126 * v.x + 0.7152 * v.y + 0.0722 * v.z; }
+// Reinhard-Jodie: blend of luminance-based and per-channel Reinhard, weighted by the per-channel result
+inline glm::vec3 reinhard_jodie(glm::vec3 c){
+    const glm::dvec3 color(c);
+    const double l = luminance(color);
+    glm::dvec3 out;
+    for(int a = 0; a < 3; a++){
+        const double t = color[a] / (1.0 + color[a]);
+        out[a] = (color[a] / (1.0 + l)) * (1.0 - t) + t * t;
+    }
+    return glm::vec3(out);
+}
+inline glm::vec3 ACESFilm(glm::vec3 c){
+    glm::vec3 out;
+    for(int a = 0; a < 3; a++){
+        const double x = c[a];
+        out[a] = (float)glm::clamp((x * (2.51 * x + 0.03)) / (x * (2.43 * x + 0.59) + 0.14), 0.0, 1.0);
+    }
+    return out;
+}
+inline double linear_to_sRGB(double linear){
+    linear = glm::clamp(linear, 0.0, 1.0);
+    return linear < 0.0031308 ? 12.92 * linear : 1.055 * std::pow(linear, 1.0 / 2.4) - 0.055;
+}
+
+class Film {
+public:
+    Film(const glm::ivec2& resolution, const std::shared_ptr<Filter>& filter, double maxComponentValue = std::numeric_limits<double>::infinity())
+        : xResolution(resolution.x), yResolution(resolution.y), screen(4 * (size_t)resolution.x * resolution.y, 0.0), filter(filter){
+        if(std::isfinite(maxComponentValue))throw std::invalid_argument("Film: maxComponentValue clamping is not available on the GPU path");
+    }
+    void Clear(){ screen.assign(screen.size(), 0.0); }
+    glm::ivec2 Resolution() const{ return { xResolution, yResolution }; }
+    const std::shared_ptr<Filter>& GetFilter() const{ return filter; }
+
+    // Film::Merge (Film.hpp:125-132) for a whole-frame accumulator downloaded from the device
+    void Merge(const std::vector<double>& rgbw){
+        if(rgbw.size() != screen.size())throw std::invalid_argument("Film::Merge: size");
+        for(size_t i = 0; i < screen.size(); i++)screen[i] += rgbw[i];
+    }
+    // sum(RGB * w) / sum(w) (Film.hpp:161), row 0 = bottom row as the reference stores it
+    glm::dvec3 Pixel(int x, int y) const{
+        const double* q = &screen[4 * ((size_t)y * xResolution + x)];
+        return glm::dvec3(q[0], q[1], q[2]) * (1.0 / q[3]);
+    }
+    const std::vector<double>& Accumulators() const{ return screen; }
+
+    void setOutputPath(const std::string& path){ outputPath = path; }
+    // binary PPM, top row first, tone-mapped then sRGB-encoded (Film.hpp:154-170)
+    void WritePPM(const std::string& filename, const std::function<glm::vec3(glm::vec3)>& toneMapper = reinhard_jodie) const{
+        std::ofstream out((outputPath.empty() ? filename : outputPath) + ".ppm", std::ios::binary);
+        if(!out)throw std::runtime_error("Film::WritePPM: cannot open output file");
+        out << "P6\n" << xResolution << " " << yResolution << "\n255\n";
+        for(int i = yResolution - 1; i >= 0; i--)for(int j = 0; j < xResolution; j++){
+            const glm::vec3 c = toneMapper(glm::vec3(Pixel(j, i)));
+            for(int a = 0; a < 3; a++)out << (char)(255.999 * std::max(0.0, std::min(1.0, linear_to_sRGB((double)c[a]))));
+        }
+    }
+private:
+    int xResolution, yResolution;
+    std::vector<double> screen;             // RGB sums * w and weight sums, 4 doubles per pixel
+    std::shared_ptr<Filter> filter;
+    std::string outputPath;
+};
+
+// ---- Camera.hpp:4-60 --------------------------------------------------------------------------------------------
+class Camera {
+public:
+    Camera(const glm::vec3& lookFrom, const glm::vec3& lookAt, float fov, const std::shared_ptr<Film>& film) : Camera(lookFrom, lookAt, fov, film, 0, 0){}
+    Camera(const glm::vec3& lookFrom, const glm::vec3& lookAt, float fov, const std::shared_ptr<Film>& film, float FocusAngle, float FocusDistance,
+           const std::shared_ptr<Medium>& medium = nullptr)
+        : lookFrom(lookFrom), lookAt(lookAt), Fov(fov), film(film), focusAngle(FocusAngle), focusDistance(FocusDistance), medium(medium){}
+    Camera(const glm::vec3& lookFrom, const glm::vec3& lookAt, float fov, const std::shared_ptr<Film>& film, const glm::vec2& shutterBounds)
+        : Camera(lookFrom, lookAt, fov, film, 0, 0){ shutter = shutterBounds; }
+    std::shared_ptr<Film> GetFilm() const{ return film; }
+    std::shared_ptr<Medium> GetMedium() const{ return medium; }
+    void SetMedium(const std::shared_ptr<Medium>& m){ medium = m; }
+    pt_camera_desc Describe(int mediumId) const{
+        pt_camera_desc c;
+        for(int a = 0; a < 3; a++){ c.look_from[a] = lookFrom[a]; c.look_at[a] = lookAt[a]; }
+        c.fov = Fov; c.focus_angle = focusAngle; c.focus_distance = focusDistance; c.medium = mediumId;
+        c.shutter_start = shutter.x; c.shutter_end = shutter.y;
+        return c;
+    }
+private:
+    glm::vec3 lookFrom, lookAt;
+    float Fov;                               // radians (Camera.hpp:12)
+    std::shared_ptr<Film> film;
+    float focusAngle, focusDistance;
+    std::shared_ptr<Medium> medium;
+    glm::vec2 shutter { 0.0f, 1.0f };
+};
+
+// ---- Sampler.hpp:9-151 --------------------------------------------------------------------------------------------
+class Sampler {
+public:
+    virtual ~Sampler() = default;
+    virtual unsigned int SamplesPerPixel() const = 0;
+    virtual void Describe(pt_render_params& rp) const = 0;
+};
+class UniformSampler : public Sampler {
+public:
+    UniformSampler(unsigned int samples) : samples(samples){}
+    unsigned int SamplesPerPixel() const override{ return samples; }
+    void Describe(pt_render_params& rp) const override{ rp.sampler = 0; rp.spp = (int32_t)samples; rp.strata_x = rp.strata_y = 1; }
+private:
+    unsigned int samples;
+};
+class StratifiedSampler : public Sampler {
+public:
+    StratifiedSampler(unsigned int xSamples, unsigned int ySamples) : xSamples(xSamples), ySamples(ySamples){}
+    unsigned int SamplesPerPixel() const override{ return xSamples * ySamples; }
+    void Describe(pt_render_params& rp) const override{ rp.sampler = 1; rp.spp = (int32_t)(xSamples * ySamples); rp.strata_x = (int32_t)xSamples; rp.strata_y = (int32_t)ySamples; }
+private:
+    unsigned int xSamples, ySamples;
+};
+
+// ---- Integrators.hpp:10-70 ---------------------------------------------------------------------------------------------
+class Integrator {
+public:
+    Integrator(const std::shared_ptr<Scene>& scene, const std::shared_ptr<Camera>& camera, const std::shared_ptr<Sampler>& sampler)
+        : scene(scene), camera(camera), sampler(sampler){}
+    virtual ~Integrator() = default;
+    // Runs the whole frame on the GPU and merges it into the camera's Film.  threadCount is accepted for
+    // source compatibility; the wavefront kernels size themselves to the device.
+    virtual void Render(unsigned int threadCount = 0) const = 0;
+    bool Intersect(const Ray& ray, SurfaceInteraction& interaction, float max = std::numeric_limits<float>::infinity()) const{ return scene->Intersect(ray, interaction, max); }
+    bool Unoccluded(const Ray& ray, float t) const{ return !scene->IntersectPred(ray, t); }
+protected:
+    std::shared_ptr<Scene> scene;
+    std::shared_ptr<Camera> camera;
+    std::shared_ptr<Sampler> sampler;
+};
+
+class TileIntegrator : public Integrator {
+public:
+    TileIntegrator(const std::shared_ptr<Scene>& scene, const std::shared_ptr<Camera>& camera, const std::shared_ptr<Sampler>& sampler)
+        : Integrator(scene, camera, sampler){}
+    void Render(unsigned int = 0) const override{
+        const std::shared_ptr<Film> film = camera->GetFilm();
+        pt_scene* s = scene->Commit(Sampler_(), camera->GetMedium());
+        pt_render_params rp;
+        std::memset(&rp, 0, sizeof rp);
+        const glm::ivec2 res = film->Resolution();
+        rp.width = res.x; rp.height = res.y;
+        rp.max_depth = (int32_t)MaxDepth(); rp.integrator = Kind();
+        sampler->Describe(rp);
+        film->GetFilter()->Describe(rp);
+        rp.seed = seed; rp.pass_begin = 0; rp.pass_stride = 1;
+        rp.adaptive = adaptive ? 1 : 0;
+        const pt_camera_desc cd = camera->Describe(camera->GetMedium() ? scene->MediumId(camera->GetMedium().get()) : -1);
+        pt_render_stats st;
+        ptb_host::check(pt_render(s, &cd, &rp, 1, &st), "pt_render");
+        std::vector<double> rgbw(4 * (size_t)res.x * res.y);
+        ptb_host::check(pt_film_download(s, rgbw.data()), "pt_film_download");
+        film->Merge(rgbw);
+        stats = st;
+        ++seed;     // a second Render() into the same Film adds independent samples, as the reference's unseeded generators do
+    }
+    // extensions: the reference's generators are seeded from std::random_device and its adaptive loop
+    // (Integrators.cpp:59-86) is always on
+    void SetSeed(uint64_t s){ seed = s; }
+    void SetAdaptive(bool on){ adaptive = on; }
+    const pt_render_stats& LastStats() const{ return stats; }
+protected:
+    virtual int Kind() const = 0;
+    virtual uint32_t MaxDepth() const = 0;
+    virtual const LightSampler* Sampler_() const{ return nullptr; }
+private:
+    mutable uint64_t seed = 1;
+    bool adaptive = true;
+    mutable pt_render_stats stats {};
+};
+
+class SimplePathIntegrator : public TileIntegrator {
+public:
+    SimplePathIntegrator(const std::shared_ptr<Scene>& scene, const std::shared_ptr<Camera>& camera, const std::shared_ptr<Sampler>& sampler, uint32_t maxDepth)
+        : TileIntegrator(scene, camera, sampler), maxDepth(maxDepth){}
+protected:
+    int Kind() const override{ return PT_INTEGRATOR_SIMPLE; }
+    uint32_t MaxDepth() const override{ return maxDepth; }
+private:
+    uint32_t maxDepth;
+};
+
+class PathIntegrator : public TileIntegrator {
+public:
+    PathIntegrator(const std::shared_ptr<Scene>& scene, const std::shared_ptr<Camera>& camera, const std::shared_ptr<Sampler>& sampler,
+                   const std::shared_ptr<LightSampler>& lightSampler, uint32_t maxDepth)
+        : TileIntegrator(scene, camera, sampler), lightSampler(lightSampler), maxDepth(maxDepth){}
+protected:
+    int Kind() const override{ return PT_INTEGRATOR_PATH; }
+    uint32_t MaxDepth() const override{ return maxDepth; }
+    const LightSampler* Sampler_() const override{ return lightSampler.get(); }
+private:
+    std::shared_ptr<LightSampler> lightSampler;
+    uint32_t maxDepth;
+};
+
+class VolPathIntegrator : public TileIntegrator {
+public:
+    VolPathIntegrator(const std::shared_ptr<Scene>& scene, const std::shared_ptr<Camera>& camera, const std::shared_ptr<Sampler>& sampler,
+                      const std::shared_ptr<LightSampler>& lightSampler, uint32_t maxDepth)
+        : TileIntegrator(scene, camera, sampler), lightSampler(lightSampler), maxDepth(maxDepth){}
+protected:
+    int Kind() const override{ return PT_INTEGRATOR_VOLPATH; }
+    uint32_t MaxDepth() const override{ return maxDepth; }
+    const LightSampler* Sampler_() const override{ return lightSampler.get(); }
+private:
+    std::shared_ptr<LightSampler> lightSampler;
+    uint32_t maxDepth;
+};

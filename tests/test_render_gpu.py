@@ -208,6 +208,52 @@ def test_volpath_without_medium_equals_reference():
     compare(desc, cam, 40, 40, 1024, 6, integrator=capi.INTEGRATOR_VOLPATH)
 
 
+@needs_ref
+@pytest.mark.parametrize("integrator,spp", [(capi.INTEGRATOR_SIMPLE, 4), (capi.INTEGRATOR_PATH, 2)])
+def test_adaptive_sampling_loop(integrator, spp):
+    """TileIntegrator::Render's per-pixel stopping rule (Integrators.cpp:59-86): rounds of spp samples until
+    every channel's 95 % interval is within 1.5 x its mean, at most 128 rounds.  With a box filter the film
+    weight of a pixel IS its sample count, so the rule itself can be compared: total samples, the
+    distribution of rounds per pixel, and where in the image the extra rounds go."""
+    from oracle.refapi import RefScene
+    desc, cam = synth.cornell_scene(light_scale=40.0, light_size=0.12)
+    W = H = 48
+    p = render_params(W, H, spp, 5, integrator=integrator, seed=9, adaptive=1)
+    ref = RefScene(desc, 4, flavour="fast" if __import__("oracle.refapi").refapi.available("fast") else "strict")
+    r_rgbw, _, r_stats = ref.render(cam, p)
+    ref.close()
+    gpu = GpuScene(desc, 4)
+    g_stats = gpu.render(cam, p)
+    g_rgbw = gpu.film()
+    gpu.close()
+    rn, gn = r_rgbw[..., 3] / spp, g_rgbw[..., 3] / spp                 # rounds per pixel
+    assert np.allclose(gn, np.round(gn)) and gn.min() >= 1 and gn.max() <= 128
+    assert g_stats["samples"] == int(round(g_rgbw[..., 3].sum())) and r_stats["samples"] == int(round(r_rgbw[..., 3].sum()))
+    assert rn.max() > 4, "scene too easy: the reference never iterates"
+    # the total is dominated by the few pixels that run to the 128-round cap: loose; the rule itself is
+    # compared through the distribution of rounds per pixel
+    assert abs(g_stats["samples"] / r_stats["samples"] - 1.0) < 0.3, (g_stats["samples"], r_stats["samples"])
+    npx = W * H
+    for lo, hi in ((1, 1), (2, 3), (4, 11), (12, 128)):
+        cr, cg = int(((rn >= lo) & (rn <= hi)).sum()), int(((gn >= lo) & (gn <= hi)).sum())
+        pr = max(cr, cg, 1) / npx
+        assert abs(cr - cg) <= 5.0 * np.sqrt(2 * npx * pr * (1 - pr)) + 4, ((lo, hi), cr, cg)
+    if integrator == capi.INTEGRATOR_PATH:
+        # and it iterates in the same places (penumbra, ceiling): block-averaged "needed more than one round" maps
+        blk = lambda a: (a > 1).reshape(H // 8, 8, W // 8, 8).mean(axis=(1, 3)).ravel()
+        assert np.corrcoef(blk(gn), blk(rn))[0, 1] > 0.7
+    a, b = film_mean(g_rgbw), film_mean(r_rgbw)
+    assert np.allclose(a.mean(axis=(0, 1)), b.mean(axis=(0, 1)), rtol=0.25)     # a few samples per pixel: sanity only
+
+
+def test_adaptive_rejects_pass_sharding():
+    desc, cam = synth.cornell_scene()
+    gpu = GpuScene(desc, 4)
+    with pytest.raises(capi.PtError, match="pass sharding"):
+        gpu.render(cam, render_params(16, 16, 4, 3, adaptive=1, pass_begin=1, pass_stride=2))
+    gpu.close()
+
+
 def test_sample_streams_are_independent():
     """Two renders with different seeds must differ per pixel by what their own sample variance predicts
     (z ~ N(0,1)).  Guards the per-sample generator seeding: PCG streams that differ only in a small
