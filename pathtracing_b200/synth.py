@@ -320,3 +320,174 @@ def alpha_scene(mode=capi.ALPHA_MASK, four_channel=False):
     b2 = d.add_blas([d.mesh(q2[0], q2[1], q2[2], q2[3], material=glass)])
     d.instance(b2, trs((0.72, 0.5, 1.1), 0.4, (0, 1, 0), -0.5))
     return d, cam
+
+
+# ---- BASELINE configs[2..4] at full scale ----------------------------------------------------
+
+def displaced_sphere(subdiv: int, seed: int, amp: float = 0.08):
+    """An icosphere with smooth radial noise and recomputed vertex normals: a 'model' BLAS."""
+    pos, idx, nrm, uv = icosphere(subdiv)
+    rng = np.random.default_rng(seed)
+    k = rng.normal(size=(4, 3)) * 3.0
+    ph = rng.random(4) * 6.28
+    r = 1.0 + amp * sum(np.sin(pos @ k[j] + ph[j]) for j in range(4)) / 2.0
+    pos = (pos * r[:, None]).astype(np.float32)
+    fn = np.cross(pos[idx[:, 1]] - pos[idx[:, 0]], pos[idx[:, 2]] - pos[idx[:, 0]])
+    vn = np.zeros_like(pos, dtype=np.float64)
+    for c in range(3):
+        np.add.at(vn, idx[:, c], fn)
+    vn /= np.maximum(np.linalg.norm(vn, axis=1, keepdims=True), 1e-20)
+    return pos, idx, vn.astype(np.float32), uv
+
+
+def c3_scene(subdiv: int = 6, n_instances: int = 122, seed: int = 3):
+    """C3: instanced scene, ~10 M triangles through the TLAS (122 x 81 920-triangle BLASes at the
+    defaults), materials round-robin {rough dielectric, rough metal, Lambertian, specular conductor},
+    checkered ground, gradient sky + a quad light."""
+    d = SceneDesc()
+    mats = [d.dielectric(1.5, d.solid((0.95, 0.97, 1.0)), rough=d.solid((0.15, 0.15, 0.15))),
+            d.diffuse(d.solid((0.95, 0.64, 0.54)), rough=d.solid((0.3, 0.3, 0.3)), metal=d.solid((1, 1, 1))),
+            d.diffuse(d.solid((0.2, 0.5, 0.8))),
+            d.conductor((0.9, 0.85, 0.6))]
+    blas = []
+    for k, m in enumerate(mats):
+        pos, idx, nrm, uv = displaced_sphere(subdiv, seed + k)
+        blas.append(d.add_blas([d.mesh(pos, idx, nrm, uv, material=m)]))
+    rng = np.random.default_rng(seed)
+    side = int(math.ceil(math.sqrt(n_instances)))
+    for k in range(n_instances):
+        gx, gz = k % side, k // side
+        M = trs(((gx - side / 2 + 0.5) * 2.6 + rng.normal() * 0.2, 1.0 + rng.random() * 1.5, (gz - side / 2 + 0.5) * 2.6 + rng.normal() * 0.2),
+                0.8 + 0.4 * rng.random(), rng.normal(size=3), rng.random() * 6.28)
+        d.instance(blas[k % len(blas)], M)
+    ext = side * 2.6
+    gp, gi, gn, gu = quad((-ext, 0, -ext), (0, 0, 2 * ext), (2 * ext, 0, 0))
+    ground = d.diffuse(d.checker(d.solid((0.75, 0.75, 0.75)), d.solid((0.2, 0.25, 0.3)), (0.02, 0.02)))
+    d.instance(d.add_blas([d.mesh(gp, gi, gn, gu, material=ground)]))
+    lp, li, ln, lu = quad((-3, 0, -3), (6, 0, 0), (0, 0, 6))
+    emit = d.solid((1.0, 0.9, 0.75), scale=(20, 20, 20))
+    lb = d.add_blas([d.mesh(lp, li, ln, lu, material=d.diffuse(d.solid((0, 0, 0))), emissive_tex=emit)])
+    d.instance(lb, trs((0.0, 9.0, 0.0), 1.0, (1, 0, 0), math.pi))       # facing down
+    d.light(capi.LIGHT_GRADIENT_INFINITE, color=(1.0, 0.85, 0.55), color_b=(0.45, 0.65, 1.0), scale=1.5)
+    cam = camera_desc((0.0, 7.0, ext * 0.95), (0.0, 1.0, 0.0), fov=1.0)
+    return d, cam
+
+
+def c4_scene(tex_size: int = 1024, subdiv: int = 5):
+    """C4: the materials scene with generated tex_size^2 albedo / roughness-metallic / normal-map images
+    inside a global HomogeneusMedium (HG g = 0.75, density 0.1; main.cpp:174,266-268): NEE + MIS through media."""
+    d = SceneDesc()
+    alb, orm, nm = procedural_textures(tex_size)
+    t_alb, t_orm, t_nm = d.image_u8(alb), d.image_u8(orm), d.image_u8(nm)
+    mats = [d.diffuse(t_alb, norm=t_nm, rough=t_orm, metal=t_orm),
+            d.dielectric(1.5, d.solid((0.95, 0.97, 1.0)), rough=d.solid((0.1, 0.1, 0.1))),
+            d.diffuse(t_alb, rough=d.solid((0.5, 0.5, 0.5))),
+            d.conductor((0.9, 0.85, 0.6))]
+    rng = np.random.default_rng(5)
+    for k in range(16):
+        pos, idx, nrm, uv = displaced_sphere(subdiv, 20 + k)
+        b = d.add_blas([d.mesh(pos, idx, nrm, uv, material=mats[k % 4])])
+        ang = 2 * math.pi * k / 16
+        rad = 2.2 + 1.6 * (k % 2)
+        d.instance(b, trs((rad * math.cos(ang), 0.6 + 0.2 * (k % 3), rad * math.sin(ang)), 0.55, rng.normal(size=3), rng.random() * 6.28))
+    gp, gi, gn, gu = quad((-8, 0, -8), (0, 0, 16), (16, 0, 0))
+    gt = np.tile(np.array([[0, 0, 1]], np.float32), (4, 1))
+    d.instance(d.add_blas([d.mesh(gp, gi, gn, gu * 6.0, tangents=gt, material=d.diffuse(t_alb, norm=t_nm, rough=t_orm))]))
+    lp, li, ln, lu = quad((-1, 0, -1), (2, 0, 0), (0, 0, 2))
+    emit = d.solid((1.0, 0.9, 0.75), scale=(25, 25, 25))
+    lb = d.add_blas([d.mesh(lp, li, ln, lu, material=d.diffuse(d.solid((0, 0, 0))), emissive_tex=emit)])
+    d.instance(lb, trs((0.0, 5.0, 0.0), 1.0, (1, 0, 0), math.pi))
+    d.light(capi.LIGHT_GRADIENT_INFINITE, color=(1.0, 1.0, 1.0), color_b=(0.5, 0.7, 1.0), scale=0.4)
+    d.scene_medium = d.medium((0.5, 0.5, 0.5), (2.0, 2.2, 2.6), 0.75, density=0.1)
+    cam = camera_desc((0.0, 2.4, 7.0), (0.0, 0.6, 0.0), fov=0.9)
+    return d, cam
+
+
+def hdr_sky(w: int = 1024, h: int = 512, seed: int = 2):
+    """A generated HDR environment (float RGB): gradient sky, a bright sun disc, soft clouds."""
+    rng = np.random.default_rng(seed)
+    v, u = np.mgrid[0:h, 0:w].astype(np.float32)
+    u, v = (u + 0.5) / w, (v + 0.5) / h
+    theta = v * math.pi
+    up = np.cos(theta)
+    sky = np.stack([0.35 + 0.3 * (1 - up), 0.5 + 0.25 * (1 - up), 0.9 + 0 * up], -1) * np.clip(0.4 + 0.6 * up, 0.05, 1)[..., None]
+    clouds = sum(np.sin(6.28 * (kx * u + ky * v) + p) for kx, ky, p in rng.normal(size=(6, 3)) * np.array([4, 3, 3]))
+    sky *= (1.0 + 0.15 * np.tanh(clouds))[..., None]
+    su, sv = 0.3, 0.28
+    dsun = np.hypot((u - su) * 2 * np.sin(theta), v - sv)
+    sky += (np.exp(-(dsun / 0.01) ** 2) * 400.0)[..., None] * np.array([1.0, 0.9, 0.7], np.float32)
+    # as decoded from a Radiance .hdr file: the only way the reference can be given an HDR texture
+    return rgbe_roundtrip(sky.astype(np.float32))
+
+
+def c5_scene(grid: int = 2237, n_textures: int = 64, tex_size: int = 256, seed: int = 8, env: bool = True, n_lights: int = 8, n_objects: int = 24):
+    """C5: ~10 M UNIQUE triangles (a grid x grid displaced terrain = 2*(grid-1)^2 triangles, split into
+    n_textures patches each with its own generated albedo/roughness images), scattered emissive and glass
+    objects, an HDR environment through TextureInfiniteLight."""
+    d = SceneDesc()
+    pos, tri, uv = terrain(grid, grid, seed, height=0.35, octaves=7)
+    pos = (pos * np.array([40.0, 6.0, 40.0], np.float32) - np.array([20.0, 3.0, 20.0], np.float32)).astype(np.float32)
+    # smooth normals from the height field
+    fn = np.cross(pos[tri[:, 1]] - pos[tri[:, 0]], pos[tri[:, 2]] - pos[tri[:, 0]]).astype(np.float32)
+    vn = np.zeros_like(pos)
+    for c in range(3):
+        np.add.at(vn, tri[:, c], fn)
+    vn /= np.maximum(np.linalg.norm(vn, axis=1, keepdims=True), 1e-20)
+    rng = np.random.default_rng(seed)
+    patches = int(math.isqrt(n_textures))
+    cell = (grid - 1) // patches
+    quad_x = (np.arange(len(tri)) // 2) % (grid - 1)
+    quad_z = (np.arange(len(tri)) // 2) // (grid - 1)
+    pid = np.minimum(quad_z // cell, patches - 1) * patches + np.minimum(quad_x // cell, patches - 1)
+    meshes = []
+    y, x = np.mgrid[0:tex_size, 0:tex_size].astype(np.float32) / tex_size
+    for p in range(patches * patches):
+        f = rng.random(6) * 5 + 1
+        alb = np.stack([0.45 + 0.35 * np.sin(6.28 * f[0] * x) * np.cos(6.28 * f[1] * y), 0.45 + 0.3 * np.cos(6.28 * f[2] * (x + y)),
+                        0.35 + 0.25 * np.sin(6.28 * f[3] * y)], -1)
+        rough = np.clip(0.4 + 0.4 * np.sin(6.28 * f[4] * x) * np.sin(6.28 * f[5] * y), 0.05, 1.0)
+        orm = np.stack([np.ones_like(rough), rough, np.zeros_like(rough)], -1)
+        to8 = lambda a: np.ascontiguousarray(np.clip(np.round(a * 255), 0, 255).astype(np.uint8))
+        m = d.diffuse(d.image_u8(to8(alb)), rough=d.image_u8(to8(orm)))
+        sel = tri[pid == p]
+        used, inv = np.unique(sel, return_inverse=True)
+        meshes.append(d.mesh(pos[used], inv.reshape(-1, 3).astype(np.uint32), vn[used], (uv[used] * patches * 4).astype(np.float32), material=m))
+    d.instance(d.add_blas(meshes))
+    glass = d.dielectric(1.5, d.solid((0.97, 0.98, 1.0)))
+    metal = d.diffuse(d.solid((0.9, 0.7, 0.4)), rough=d.solid((0.25, 0.25, 0.25)), metal=d.solid((1, 1, 1)))
+    sp, si, sn, su = displaced_sphere(5, 99)
+    bg, bm = d.add_blas([d.mesh(sp, si, sn, su, material=glass)]), d.add_blas([d.mesh(sp, si, sn, su, material=metal)])
+    for k in range(n_objects):
+        c = (rng.random(2) - 0.5) * 30
+        d.instance(bg if k % 2 else bm, trs((c[0], 2.5 + rng.random() * 2, c[1]), 0.6 + 0.5 * rng.random(), rng.normal(size=3), rng.random() * 6.28))
+    lp, li, ln, lu = quad((-0.5, 0, -0.5), (1, 0, 0), (0, 0, 1))
+    emit = d.solid((1.0, 0.8, 0.5), scale=(30, 30, 30))
+    lb = d.add_blas([d.mesh(lp, li, ln, lu, material=d.diffuse(d.solid((0, 0, 0))), emissive_tex=emit)])
+    for k in range(n_lights):
+        c = (rng.random(2) - 0.5) * 24
+        d.instance(lb, trs((c[0], 5.0 + rng.random(), c[1]), 1.5, (1, 0, 0), math.pi))
+    if env:
+        d.light(capi.LIGHT_TEXTURE_INFINITE, tex=d.image_f32(hdr_sky()), scale=1.0, power_func=2)
+    else:
+        d.light(capi.LIGHT_GRADIENT_INFINITE, color=(1.0, 1.0, 1.0), color_b=(0.5, 0.7, 1.0), scale=0.8)
+    cam = camera_desc((0.0, 6.0, 24.0), (0.0, 0.5, 0.0), fov=1.0)
+    return d, cam
+
+
+def rgbe_roundtrip(img: np.ndarray) -> np.ndarray:
+    """What a float RGB image becomes after being written as Radiance .hdr and loaded back (shared 8-bit
+    exponent, 8-bit TRUNCATED mantissas): the reference can only build FloatImageTexture from a file, so
+    these are the texels it actually sees.  Mirrors the float32 arithmetic of the stb encoder/decoder the
+    reference vendors (checked against it in tests/test_synth_cpu.py)."""
+    a = np.ascontiguousarray(img, dtype=np.float32)
+    assert a.shape[-1] == 3
+    mx = a.max(axis=-1)
+    mant, expo = np.frexp(mx.astype(np.float64))
+    with np.errstate(divide="ignore", invalid="ignore"):
+        normalize = (mant.astype(np.float32) * np.float32(256.0) / mx).astype(np.float32)
+    small = mx < np.float32(1e-32)
+    bytes_ = np.where(small[..., None], 0, (a * normalize[..., None]).astype(np.float32)).astype(np.int64) & 0xFF
+    e = np.where(small, 0, expo + 128).astype(np.int64)
+    f1 = np.ldexp(np.float32(1.0), (e - 136).astype(np.int32)).astype(np.float32)
+    out = np.where((e != 0)[..., None], bytes_.astype(np.float32) * f1[..., None], np.float32(0.0))
+    return np.ascontiguousarray(out.astype(np.float32))

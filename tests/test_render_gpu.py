@@ -203,6 +203,28 @@ def test_volpath_homogeneous_medium():
 
 
 @needs_ref
+def test_c3_instanced_materials_small():
+    """C3 at test size: the same builder as the bench scene (instanced displaced spheres, four materials,
+    checkered ground, transformed quad light, gradient sky)."""
+    desc, cam = synth.c3_scene(subdiv=2, n_instances=9)
+    compare(desc, cam, 64, 36, 1024, 10)
+
+
+@needs_ref
+def test_c4_medium_textures_small():
+    desc, cam = synth.c4_scene(tex_size=64, subdiv=2)
+    compare(desc, cam, 48, 27, 1024, 12, integrator=capi.INTEGRATOR_VOLPATH)
+
+
+@needs_ref
+def test_c5_terrain_hdr_environment_small():
+    """C5 at test size: multi-mesh terrain BLAS with per-patch image textures, glass / metal instances,
+    emissive quads and an HDR environment through TextureInfiniteLight (importance-sampled sun)."""
+    desc, cam = synth.c5_scene(grid=48, n_textures=4, tex_size=16)
+    compare(desc, cam, 48, 27, 2048, 8)
+
+
+@needs_ref
 def test_volpath_without_medium_equals_reference():
     desc, cam = synth.cornell_scene()
     compare(desc, cam, 40, 40, 1024, 6, integrator=capi.INTEGRATOR_VOLPATH)
