@@ -43,6 +43,7 @@ def parse():
     ap.add_argument("--bvh", type=int, default=4, choices=[2, 4])
     ap.add_argument("--no-extras", action="store_true", help="skip the BVH2 / any-hit / second-mesh side measurements")
     ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--renders", default="c1,c3,c4", help="render configs measured as extras: subset of c1,c3,c4,c5 (c5 builds a 10 M-triangle BVH: ~40 s)")
     return ap.parse_args()
 
 
@@ -192,19 +193,35 @@ def time_dev(fn, steps, warmup, torch, dist, world):
     return ms / steps
 
 
-def bench_render(a, torch, dist, world, rank, local):
-    """C1 (BASELINE configs[0]): procedural Cornell box 512x512, 16 spp, depth 8, NEE+MIS, PathIntegrator.
-    Sample passes sharded over the ranks, one NCCL reduce of the film (strong scaling: total work fixed)."""
-    from pathtracing_b200 import capi, multi, synth
+def render_configs():
+    """BASELINE.json configs[0], [2], [3], [4] as (key, workload text, scene builder, W, H, spp, depth, integrator)."""
+    from pathtracing_b200 import capi, synth
+    return {
+        "c1": ("C1 Cornell 512x512, 16 spp, depth 8, NEE+MIS, PathIntegrator, BVH4", synth.cornell_scene, 512, 512, 16, 8, capi.INTEGRATOR_PATH),
+        "c3": ("C3 instanced 10 M triangles (122 x 81 920-triangle BLAS instances via TLAS4/BLAS4), rough dielectric / rough metal / "
+               "Lambertian / specular conductor, 1920x1080, 64 spp, depth 8, PathIntegrator", synth.c3_scene, 1920, 1080, 64, 8, capi.INTEGRATOR_PATH),
+        "c4": ("C4 homogeneous medium (HG g=0.75) + generated 1024^2 albedo/roughness/normal textures, NEE+MIS through media, "
+               "1920x1080, 128 spp, depth 8, VolPathIntegrator", synth.c4_scene, 1920, 1080, 128, 8, capi.INTEGRATOR_VOLPATH),
+        "c5": ("C5 10 M unique triangles, 64 generated texture sets + HDR environment (TextureInfiniteLight), 1920x1080, depth 128, "
+               "64 of the config's 1024 spp (the rate is per sample), PathIntegrator", synth.c5_scene, 1920, 1080, 64, 128, capi.INTEGRATOR_PATH),
+    }
+
+
+def bench_render(a, key, torch, dist, world, rank, local):
+    """One render config: sample passes sharded over the ranks, one NCCL reduce of the film per frame
+    (strong scaling: total work fixed).  Frame time = CUDA events around render + reduce, max over ranks."""
+    from pathtracing_b200 import multi
     from pathtracing_b200.scene import GpuScene, render_params
-    desc, cam = synth.cornell_scene()
+    name, builder, W, H, spp, depth, integ = render_configs()[key]
+    t0 = time.perf_counter()
+    desc, cam = builder()
     scene = GpuScene(desc, 4, device=local)
-    W = H = 512
-    spp, depth = 16, 8
-    params = render_params(W, H, spp, depth, integrator=capi.INTEGRATOR_PATH, seed=1)
-    steps = max(2, min(a.steps, 5))
+    build_s = time.perf_counter() - t0
+    params = render_params(W, H, spp, depth, integrator=integ, seed=1)
+    heavy = W * H * spp > (1 << 25)
+    steps = 2 if heavy else max(2, min(a.steps, 5))
     st = None
-    for _ in range(2):
+    for _ in range(1 if heavy else 2):
         st, film = multi.render_sharded(scene, cam, params, dist if world > 1 else None)
     torch.cuda.synchronize()
     if world > 1:
@@ -212,9 +229,11 @@ def bench_render(a, torch, dist, world, rank, local):
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record()
     rays = 0
+    launches = 0
     for _ in range(steps):
         st, film = multi.render_sharded(scene, cam, params, dist if world > 1 else None)
         rays += st["closest_rays"] + st["shadow_rays"]
+        launches += st["kernel_launches"]
     e1.record()
     torch.cuda.synchronize()
     ms = e0.elapsed_time(e1) / steps
@@ -226,10 +245,11 @@ def bench_render(a, torch, dist, world, rank, local):
     out = None
     if rank == 0:
         img = film.cpu().numpy().reshape(H, W, 4)
-        out = {"workload": "C1 Cornell 512x512, 16 spp, depth 8, NEE+MIS, PathIntegrator, BVH4", "msamples_per_s": W * H * spp / (ms * 1e-3) / 1e6,
-               "mrays_per_s": rays / steps / (ms * 1e-3) / 1e6, "ms_per_frame": ms, "n_gpus": world, "scaling": "strong",
+        out = {"workload": name, "msamples_per_s": W * H * spp / (ms * 1e-3) / 1e6,
+               "mrays_per_s": rays / steps / (ms * 1e-3) / 1e6, "rays_per_sample": rays / steps / (W * H * spp), "ms_per_frame": ms,
+               "n_gpus": world, "scaling": "strong", "frames_timed": steps, "scene_build_s": build_s,
                "collective": "one reduce(sum) of 4*W*H float64 film accumulators" if world > 1 else "none",
-               "kernel_launches_per_frame": int(st["kernel_launches"]), "mean_weight": float(img[..., 3].mean()),
+               "kernel_launches_per_frame": int(launches // steps), "mean_weight": float(img[..., 3].mean()),
                "mean_radiance": float((img[..., :3] / np.maximum(img[..., 3:4], 1e-300)).mean())}
     scene.close()
     return out
@@ -312,9 +332,10 @@ def run_ours(a):
     hits_np = host_hits.numpy().view(np.dtype([("t", "<f4"), ("u", "<f4"), ("v", "<f4"), ("prim", "<u4")]))
     hit_rate = float((hits_np["prim"] != 0xFFFFFFFF).mean())
 
-    render_extra = None
+    render_extras = {}
     if not a.no_extras:
-        render_extra = bench_render(a, torch, dist, world, rank, local)   # collective: every rank takes part
+        for key in [k for k in a.renders.split(",") if k]:
+            render_extras[key] = bench_render(a, key, torch, dist, world, rank, local)   # collective: every rank takes part
 
     if rank != 0:
         if world > 1:
@@ -352,8 +373,9 @@ def run_ours(a):
         extras[f"closest_bvh{other}_mrays"] = n / (ms2 * 1e-3) / 1e6
         s2.close()
 
-    if render_extra is not None:
-        extras["c1_render"] = render_extra
+    for key, val in render_extras.items():
+        extras[f"{key}_render"] = val
+    if "c1" in render_extras:
         if world == 1 and not a.no_cpu:
             try:
                 extras["c1_render"]["cpu_reference"] = cpu_render_rate(a)

@@ -46,12 +46,12 @@ struct Arena {
     uint32_t* mflag;    // bit0 spec, bits 1..: medium id + 1
     uint64_t* rng;      // pcg state (inc is rebuilt from the sample id)
     float2* spos;       // fractional sample position inside the pixel
-    uint32_t* counters; // [0] next-queue size, [1] shadow-queue size
+    uint64_t* gid;      // which camera sample lives in the slot (index into this call's sample sequence)
+    uint32_t* done;     // slots whose path ended in the last shade pass: splatted, then handed to new samples
+    uint32_t* counters; // [0] next-queue size, [1] shadow-queue size, [2] done-list size
 };
 
-struct BatchInfo {
-    uint64_t first;     // first global sample id of the batch: id = pass_k * W*H + pixel
-    uint32_t count;
+struct BatchInfo {     // how a sample id maps to (pixel, sample index): id = pass_k * W*H + pixel
     int W, H, pass_begin, pass_stride, max_depth;
     int sampler, sx, sy;   // 0 UniformSampler | 1 StratifiedSampler(sx, sy)
     uint64_t seed;
@@ -61,8 +61,7 @@ struct BatchInfo {
     uint32_t n_list, sample_base;
 };
 
-__device__ __forceinline__ uint64_t stream_of(const BatchInfo& B, uint32_t slot, uint32_t& pixel, uint32_t& sample){
-    const uint64_t g = B.first + slot;
+__device__ __forceinline__ uint64_t stream_of(const BatchInfo& B, uint64_t g, uint32_t& pixel, uint32_t& sample){
     const uint64_t wh = (uint64_t)B.W * B.H;
     if(B.list){
         pixel = B.list[g % B.n_list];
@@ -87,11 +86,15 @@ __device__ __forceinline__ uint32_t queue_slot(uint32_t* counter, bool want){
 }
 
 // ---- generate: StartPixelSample / getPixel2D / get1D / get2D / Camera::GenerateRay (Integrators.cpp:61-64) ----
-__global__ void __launch_bounds__(256) k_generate(Arena A, BatchInfo B, CamParams C){
-    const uint32_t slot = blockIdx.x * blockDim.x + threadIdx.x;
-    if(slot >= B.count)return;
+// n_new camera samples gid_first.. go into the slots free[i] (or free_base + i) and onto the end of queue `cur`
+__global__ void __launch_bounds__(256) k_generate(Arena A, BatchInfo B, CamParams C, uint32_t n_new, uint64_t gid_first,
+                                                  const uint32_t* __restrict__ free, uint32_t q_off, int cur){
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if(i >= n_new)return;
+    const uint32_t slot = free ? free[i] : i;
+    const uint64_t gid = gid_first + i;
     uint32_t pixel, sample;
-    const uint64_t stream = stream_of(B, slot, pixel, sample);
+    const uint64_t stream = stream_of(B, gid, pixel, sample);
     Pcg g = pcg_seed(B.seed, stream);
     const int x = (int)(pixel % (uint32_t)B.W), y = (int)(pixel / (uint32_t)B.W);
     double jx, jy; float time, lx, ly;
@@ -125,9 +128,11 @@ __global__ void __launch_bounds__(256) k_generate(Arena A, BatchInfo B, CamParam
         org = C.from + off;
         dir = normalize(dir - off);
     }
-    A.rays[0][2 * (size_t)slot] = make_float4(org.x, org.y, org.z, CUDART_INF_F);
-    A.rays[0][2 * (size_t)slot + 1] = make_float4(dir.x, dir.y, dir.z, t);
-    A.qslot[0][slot] = slot;
+    const size_t q = (size_t)q_off + i;
+    A.rays[cur][2 * q] = make_float4(org.x, org.y, org.z, CUDART_INF_F);
+    A.rays[cur][2 * q + 1] = make_float4(dir.x, dir.y, dir.z, t);
+    A.qslot[cur][q] = slot;
+    A.gid[slot] = gid;
     A.thr[slot] = make_float4(1.0f, 1.0f, 1.0f, 1.0f);
     A.rad[slot] = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
     A.depth[slot] = 1u;                                          // `depth++ < maxDepth` already taken for bounce 1
@@ -192,11 +197,13 @@ __device__ inline double filter_eval(const FilterParams& F, float x, float y){
 }
 
 // est: this call's per-pixel estimator sums for the adaptive loop, 6 doubles per pixel {sum rgb, sum of squares rgb}, or null
-__global__ void __launch_bounds__(256) k_film(Arena A, BatchInfo B, FilterParams F, double* __restrict__ film, double* __restrict__ film_sq, double* __restrict__ est){
-    const uint32_t slot = blockIdx.x * blockDim.x + threadIdx.x;
-    if(slot >= B.count)return;
+__global__ void __launch_bounds__(256) k_film(Arena A, BatchInfo B, FilterParams F, double* __restrict__ film, double* __restrict__ film_sq, double* __restrict__ est,
+                                              const uint32_t* __restrict__ done, uint32_t n_done){
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if(i >= n_done)return;
+    const uint32_t slot = done ? done[i] : i;
     uint32_t pixel, sample;
-    stream_of(B, slot, pixel, sample);
+    stream_of(B, A.gid[slot], pixel, sample);
     const int x = (int)(pixel % (uint32_t)B.W), y = (int)(pixel / (uint32_t)B.W);
     const float4 r = A.rad[slot];
     const float2 sp = A.spos[slot];
@@ -316,7 +323,7 @@ __global__ void __launch_bounds__(128) k_shade(Arena A, ShadeScene S, BatchInfo 
         bool spec = (mf & 1u) != 0;
         int medium = (int)(mf >> 1) - 1;
         uint32_t pixel, sample;
-        Pcg g; g.inc = pcg_inc(B.seed, stream_of(B, slot, pixel, sample)); g.state = A.rng[slot];
+        Pcg g; g.inc = pcg_inc(B.seed, stream_of(B, A.gid[slot], pixel, sample)); g.state = A.rng[slot];
 
         if(prim == 0xFFFFFFFFu){
             // miss: infinite lights (Integrators.cpp:136-141, 197-207, 308-330)
@@ -426,6 +433,9 @@ __global__ void __launch_bounds__(128) k_shade(Arena A, ShadeScene S, BatchInfo 
         A.rays[cur ^ 1][2 * (size_t)qn + 1] = make_float4(nd.x, nd.y, nd.z, ntime);
         A.qslot[cur ^ 1][qn] = slot;
     }
+    const bool ended = j < n && !cont;
+    const uint32_t qd = queue_slot(A.counters + 2, ended);
+    if(ended)A.done[qd] = slot;
     const uint32_t qs = queue_slot(A.counters + 1, nee);
     if(nee){
         A.srays[2 * (size_t)qs] = make_float4(ne.o.x, ne.o.y, ne.o.z, ne.tmax);
@@ -499,7 +509,8 @@ static size_t arena_layout(char* base, Arena& A, size_t cap){
     carve(p, (void**)&A.hits, cap * 16); carve(p, (void**)&A.hinst, cap * 4);
     carve(p, (void**)&A.srays, cap * 32); carve(p, (void**)&A.sslot, cap * 4); carve(p, (void**)&A.scontrib, cap * 16); carve(p, (void**)&A.socc, cap);
     carve(p, (void**)&A.thr, cap * 16); carve(p, (void**)&A.rad, cap * 16); carve(p, (void**)&A.depth, cap * 4); carve(p, (void**)&A.mflag, cap * 4);
-    carve(p, (void**)&A.rng, cap * 8); carve(p, (void**)&A.spos, cap * 8); carve(p, (void**)&A.counters, 256);
+    carve(p, (void**)&A.rng, cap * 8); carve(p, (void**)&A.spos, cap * 8); carve(p, (void**)&A.gid, cap * 8); carve(p, (void**)&A.done, cap * 4);
+    carve(p, (void**)&A.counters, 256);
     return (size_t)(p - base);
 }
 
@@ -568,23 +579,34 @@ int render_passes(pt_scene* s, const pt_camera_desc* cam, const pt_render_params
     pt_render_stats R {};
     auto fail = [&](int code){ cudaFreeHost(h_counters); cudaEventDestroy(e0); cudaEventDestroy(e1); return code; };
 
-    // one set of samples through the wavefront: `count` camera samples in batches of at most `cap`
+    // one set of `count` camera samples through the wavefront.  The slot pool stays full: the slots whose
+    // paths ended in a shade pass are splatted and handed to the next camera samples straight away, so the
+    // long tail of deep paths is paid once per call and not once per batch.
     auto run = [&](uint64_t count, const uint32_t* list, uint32_t n_list, uint32_t sample_base) -> int {
-      for(uint64_t first = 0; first < count; first += cap){
         BatchInfo B;
-        B.first = first; B.count = (uint32_t)std::min<uint64_t>(cap, count - first);
         B.W = W; B.H = H; B.pass_begin = rp->pass_begin; B.pass_stride = rp->pass_stride; B.max_depth = rp->max_depth; B.seed = rp->seed;
         B.sampler = rp->sampler; B.sx = rp->strata_x; B.sy = rp->strata_y;
         B.list = list; B.n_list = n_list; B.sample_base = sample_base;
-        k_generate<<<(B.count + 255) / 256, 256, 0, st>>>(A, B, C);
-        R.kernel_launches++;
-        uint32_t n = rp->max_depth > 0 ? B.count : 0;    // `depth++ < maxDepth` fails at once: black samples
+        uint64_t next_gid = 0;
+        if(rp->max_depth <= 0){
+            // `depth++ < maxDepth` fails at once: black samples that still carry their filter weight
+            while(next_gid < count){
+                const uint32_t m = (uint32_t)std::min<uint64_t>(cap, count - next_gid);
+                k_generate<<<(m + 255) / 256, 256, 0, st>>>(A, B, C, m, next_gid, nullptr, 0, 0);
+                k_film<<<(m + 255) / 256, 256, 0, st>>>(A, B, F, (double*)b.film, (double*)b.film_sq, est, nullptr, m);
+                R.kernel_launches += 2; R.samples += m; next_gid += m;
+            }
+            return PT_OK;
+        }
+        uint32_t n = (uint32_t)std::min<uint64_t>(cap, count);
         int cur = 0;
+        k_generate<<<(n + 255) / 256, 256, 0, st>>>(A, B, C, n, 0, nullptr, 0, cur);
+        R.kernel_launches++; R.samples += n; next_gid = n;
         while(n > 0){
             int rc = launch_trace_closest(s, A.rays[cur], n, A.hits, A.hinst, st);
             if(rc != PT_OK)return rc;
             R.closest_rays += n; R.kernel_launches++;
-            if(!cuda_ok(cudaMemsetAsync(A.counters, 0, 8, st), "counter reset"))return PT_ERR_CUDA;
+            if(!cuda_ok(cudaMemsetAsync(A.counters, 0, 12, st), "counter reset"))return PT_ERR_CUDA;
             const unsigned grid = (n + 127) / 128;
             switch(rp->integrator){
             case PT_INTEGRATOR_SIMPLE: k_shade<PT_INTEGRATOR_SIMPLE><<<grid, 128, 0, st>>>(A, s->shade, B, n, cur); break;
@@ -592,22 +614,28 @@ int render_passes(pt_scene* s, const pt_camera_desc* cam, const pt_render_params
             default: k_shade<PT_INTEGRATOR_VOLPATH><<<grid, 128, 0, st>>>(A, s->shade, B, n, cur); break;
             }
             R.kernel_launches++;
-            if(!cuda_ok(cudaMemcpyAsync(h_counters, A.counters, 8, cudaMemcpyDeviceToHost, st), "counters D2H") ||
+            if(!cuda_ok(cudaMemcpyAsync(h_counters, A.counters, 12, cudaMemcpyDeviceToHost, st), "counters D2H") ||
                !cuda_ok(cudaStreamSynchronize(st), "shade"))return PT_ERR_CUDA;
-            const uint32_t n_next = h_counters[0], n_sh = h_counters[1];
+            const uint32_t n_next = h_counters[0], n_sh = h_counters[1], n_done = h_counters[2];
             if(n_sh > 0){
                 rc = launch_trace_any(s, A.srays, n_sh, A.socc, st);
                 if(rc != PT_OK)return rc;
                 k_connect<<<(n_sh + 255) / 256, 256, 0, st>>>(A, n_sh);
                 R.shadow_rays += n_sh; R.kernel_launches += 2;
             }
+            if(n_done > 0){
+                // after k_connect: a path may end in the very pass that queued its last shadow ray
+                k_film<<<(n_done + 255) / 256, 256, 0, st>>>(A, B, F, (double*)b.film, (double*)b.film_sq, est, A.done, n_done);
+                R.kernel_launches++;
+            }
             n = n_next; cur ^= 1;
+            if(n_done > 0 && next_gid < count){
+                const uint32_t m = (uint32_t)std::min<uint64_t>(n_done, count - next_gid);
+                k_generate<<<(m + 255) / 256, 256, 0, st>>>(A, B, C, m, next_gid, A.done, n, cur);
+                R.kernel_launches++; R.samples += m; next_gid += m; n += m;
+            }
         }
-        k_film<<<(B.count + 255) / 256, 256, 0, st>>>(A, B, F, (double*)b.film, (double*)b.film_sq, est);
-        R.kernel_launches++;
-        R.samples += B.count;
-      }
-      return PT_OK;
+        return PT_OK;
     };
 
     rc = run(total, nullptr, 0, 0);
