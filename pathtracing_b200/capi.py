@@ -14,6 +14,8 @@ import numpy as np
 
 _PKG = Path(__file__).resolve().parent
 LIB_PATH = _PKG / "libptb200.so"
+if os.environ.get("PTB_LIB"):            # kernel experiments: an alternative build of the same C-ABI
+    LIB_PATH = Path(os.environ["PTB_LIB"])
 
 PT_MISS = 0xFFFFFFFF
 

@@ -14,6 +14,8 @@
 // so the image does not depend on batch size or on how passes are sharded over GPUs.
 #include <cuda_runtime.h>
 #include <math_constants.h>
+#include <chrono>
+#include <vector>
 #include <algorithm>
 #include <cmath>
 #include <cstdlib>
@@ -258,7 +260,7 @@ struct NeeOut { bool want; V3 o, d; float tmax; V3 contrib; };
 // PathIntegrator::SampleLd (Integrators.cpp:260-294) / VolPathIntegrator::SampleLd (:426-479) up to the
 // visibility test, which the connect stage resolves.  `medium_pt`: the interaction is a medium event.
 template <int INTEG>
-__device__ inline void sample_ld(const ShadeScene& S, const SurfInt& si, bool medium_pt, V3 ip, V3 rd, float hg_g, int cur_medium,
+__device__ inline void sample_ld(const ShadeScene& S, const SurfInt& si, const MatCtx& mc, bool medium_pt, V3 ip, V3 rd, float hg_g, int cur_medium,
                                  float u_sel, float ux, float uy, Pcg& rng, NeeOut& out){
     out.want = false;
     const int li = pick_light(S, u_sel);
@@ -283,8 +285,8 @@ __device__ inline void sample_ld(const ShadeScene& S, const SurfInt& si, bool me
     } else{
         const float d = dot(si.ns, sd);
         if(d * dot(rd, si.ns) >= 0.0f)return;
-        f = mat_eval(S, si, rd, sd) * fabsf(d);
-        spdf = mat_pdf(S, si, rd, sd);
+        f = mat_eval(mc, si, rd, sd) * fabsf(d);
+        spdf = mat_pdf(mc, si, rd, sd);
     }
     if(INTEG == PT_INTEGRATOR_VOLPATH && is_zero(f))return;
     V3 c;
@@ -356,11 +358,12 @@ __global__ void __launch_bounds__(128) k_shade(Arena A, ShadeScene S, BatchInfo 
                 rr = INTEG == PT_INTEGRATOR_VOLPATH ? (float)rnd_double(g) : r[6];
             }
             bool alive = true, skip_rr = false;
+            MatCtx mc; mc.kind = PT_MAT_CONDUCTOR; mc.ri = 1.0f; mc.color = v3(0.0f); mc.rough = 0.0f; mc.metallic = 0.0f;
             if(INTEG == PT_INTEGRATOR_VOLPATH && med_event){
                 // medium event (Integrators.cpp:356-362)
                 const DevMedium& M = S.media[medium];
                 const V3 mp = ro + med_dist * rd;
-                sample_ld<INTEG>(S, si, true, mp, rd, M.g, medium, r[5], r[2], r[3], g, ne);
+                sample_ld<INTEG>(S, si, mc, true, mp, rd, M.g, medium, r[5], r[2], r[3], g, ne);
                 if(ne.want)ne.contrib = att * ne.contrib;
                 outp += att * ld3(M.Le);
                 no = mp; nd = hg_sample(M.g, rd, r[6], r[7]);
@@ -389,7 +392,8 @@ __global__ void __launch_bounds__(128) k_shade(Arena A, ShadeScene S, BatchInfo 
                     skip_rr = true;
                 } else{
                     Scatter sc;
-                    if(!mat_scatter(S, si, ro, rd, r[4], r[0], r[1], sc))alive = false;   // absorbed
+                    mat_fetch(S, si, mc);
+                    if(!mat_scatter(mc, si, ro, rd, r[4], r[0], r[1], sc))alive = false;   // absorbed
                     else{
                         if(INTEG == PT_INTEGRATOR_VOLPATH){
                             int nm = dot(sc.d, si.n) < 0.0f ? si.medium : -1;
@@ -399,9 +403,9 @@ __global__ void __launch_bounds__(128) k_shade(Arena A, ShadeScene S, BatchInfo 
                         if(INTEG != PT_INTEGRATOR_SIMPLE){
                             spec = (sc.flags & BX_SPECULAR) != 0;
                             if(!spec){
-                                sample_ld<INTEG>(S, si, false, si.p, rd, 0.0f, ray_medium, r[5], r[2], r[3], g, ne);
+                                sample_ld<INTEG>(S, si, mc, false, si.p, rd, 0.0f, ray_medium, r[5], r[2], r[3], g, ne);
                                 if(ne.want)ne.contrib = att * ne.contrib;
-                                prev_pdf = mat_pdf(S, si, rd, sc.d);
+                                prev_pdf = mat_pdf(mc, si, rd, sc.d);
                             }
                         }
                         att *= sc.f * (fabsf(dot(si.ns, sc.d)) / sc.pdf);
@@ -514,6 +518,33 @@ static size_t arena_layout(char* base, Arena& A, size_t cap){
     return (size_t)(p - base);
 }
 
+// PTB_PROFILE=1: an event after every launch group, so the stream time of a frame can be split by kernel
+// without a profiler (the intervals include the idle time before the group starts).
+struct StageLog {
+    bool on = false;
+    cudaStream_t st = nullptr;
+    std::vector<std::pair<int, cudaEvent_t>> marks;
+    void mark(int tag){
+        if(!on)return;
+        cudaEvent_t e; cudaEventCreate(&e); cudaEventRecord(e, st);
+        marks.push_back({ tag, e });
+    }
+    void report(){
+        if(!on || marks.size() < 2)return;
+        static const char* names[] = { "start", "generate", "trace_closest", "shade", "counters+sync", "trace_any+connect", "film", "adapt" };
+        double acc[8] = { 0, 0, 0, 0, 0, 0, 0, 0 };
+        for(size_t i = 1; i < marks.size(); i++){
+            float ms = 0; cudaEventElapsedTime(&ms, marks[i - 1].second, marks[i].second);
+            acc[marks[i].first] += ms;
+        }
+        fprintf(stderr, "[ptb] stages:");
+        for(int k = 1; k < 8; k++)if(acc[k] > 0)fprintf(stderr, " %s %.3f ms;", names[k], acc[k]);
+        fprintf(stderr, "\n");
+        for(auto& m : marks)cudaEventDestroy(m.second);
+        marks.clear();
+    }
+};
+
 int render_passes(pt_scene* s, const pt_camera_desc* cam, const pt_render_params* rp, int clear, pt_render_stats* stats){
     const int W = rp->width, H = rp->height;
     if(W <= 0 || H <= 0 || W > 65535 || H > 65535){ set_error("bad resolution"); return PT_ERR_INVALID; }   // Film stores uint16_t (Film.hpp:266-267)
@@ -582,6 +613,10 @@ int render_passes(pt_scene* s, const pt_camera_desc* cam, const pt_render_params
     // one set of `count` camera samples through the wavefront.  The slot pool stays full: the slots whose
     // paths ended in a shade pass are splatted and handed to the next camera samples straight away, so the
     // long tail of deep paths is paid once per call and not once per batch.
+    double host_wait_s = 0.0; unsigned iterations = 0;
+    StageLog log; log.on = getenv("PTB_PROFILE") != nullptr; log.st = st;
+    log.mark(0);
+    const auto t_host0 = std::chrono::steady_clock::now();
     auto run = [&](uint64_t count, const uint32_t* list, uint32_t n_list, uint32_t sample_base) -> int {
         BatchInfo B;
         B.W = W; B.H = H; B.pass_begin = rp->pass_begin; B.pass_stride = rp->pass_stride; B.max_depth = rp->max_depth; B.seed = rp->seed;
@@ -602,10 +637,12 @@ int render_passes(pt_scene* s, const pt_camera_desc* cam, const pt_render_params
         int cur = 0;
         k_generate<<<(n + 255) / 256, 256, 0, st>>>(A, B, C, n, 0, nullptr, 0, cur);
         R.kernel_launches++; R.samples += n; next_gid = n;
+        log.mark(1);
         while(n > 0){
             int rc = launch_trace_closest(s, A.rays[cur], n, A.hits, A.hinst, st);
             if(rc != PT_OK)return rc;
             R.closest_rays += n; R.kernel_launches++;
+            log.mark(2);
             if(!cuda_ok(cudaMemsetAsync(A.counters, 0, 12, st), "counter reset"))return PT_ERR_CUDA;
             const unsigned grid = (n + 127) / 128;
             switch(rp->integrator){
@@ -614,25 +651,33 @@ int render_passes(pt_scene* s, const pt_camera_desc* cam, const pt_render_params
             default: k_shade<PT_INTEGRATOR_VOLPATH><<<grid, 128, 0, st>>>(A, s->shade, B, n, cur); break;
             }
             R.kernel_launches++;
+            log.mark(3);
+            const auto tw0 = std::chrono::steady_clock::now();
             if(!cuda_ok(cudaMemcpyAsync(h_counters, A.counters, 12, cudaMemcpyDeviceToHost, st), "counters D2H") ||
                !cuda_ok(cudaStreamSynchronize(st), "shade"))return PT_ERR_CUDA;
+            host_wait_s += std::chrono::duration<double>(std::chrono::steady_clock::now() - tw0).count();
+            iterations++;
+            log.mark(4);
             const uint32_t n_next = h_counters[0], n_sh = h_counters[1], n_done = h_counters[2];
             if(n_sh > 0){
                 rc = launch_trace_any(s, A.srays, n_sh, A.socc, st);
                 if(rc != PT_OK)return rc;
                 k_connect<<<(n_sh + 255) / 256, 256, 0, st>>>(A, n_sh);
                 R.shadow_rays += n_sh; R.kernel_launches += 2;
+                log.mark(5);
             }
             if(n_done > 0){
                 // after k_connect: a path may end in the very pass that queued its last shadow ray
                 k_film<<<(n_done + 255) / 256, 256, 0, st>>>(A, B, F, (double*)b.film, (double*)b.film_sq, est, A.done, n_done);
                 R.kernel_launches++;
+                log.mark(6);
             }
             n = n_next; cur ^= 1;
             if(n_done > 0 && next_gid < count){
                 const uint32_t m = (uint32_t)std::min<uint64_t>(n_done, count - next_gid);
                 k_generate<<<(m + 255) / 256, 256, 0, st>>>(A, B, C, m, next_gid, A.done, n, cur);
                 R.kernel_launches++; R.samples += m; next_gid += m; n += m;
+                log.mark(1);
             }
         }
         return PT_OK;
@@ -661,6 +706,12 @@ int render_passes(pt_scene* s, const pt_camera_desc* cam, const pt_render_params
     if(!cuda_ok(cudaStreamSynchronize(st), "render"))return fail(PT_ERR_CUDA);
     float ms = 0; cudaEventElapsedTime(&ms, e0, e1);
     R.gpu_ms = ms;
+    if(getenv("PTB_PROFILE")){
+        const double host_s = std::chrono::duration<double>(std::chrono::steady_clock::now() - t_host0).count();
+        log.report();
+        fprintf(stderr, "[ptb] render: %.3f ms on the stream, host %.3f ms of which %.3f ms waiting for counters, %u iterations, %llu launches\n",
+                ms, host_s * 1e3, host_wait_s * 1e3, iterations, (unsigned long long)R.kernel_launches);
+    }
     if(stats)*stats = R;
     return fail(PT_OK);
 }

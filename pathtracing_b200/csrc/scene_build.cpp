@@ -111,6 +111,16 @@ int scene_add_light(pt_scene* s, const pt_light_desc* d){
 
 // BLAS builds (Model::BuildBlas, Model.hpp:41-60), TLAS build (Scene::BuildTlas,
 // Scene.hpp:20-24) and packing into one node array / one triangle array.
+// Texture::alpha() is 1 unless an image has 4 channels (Texture.cpp:46-62,72-88); a checker forwards to
+// its children (Texture.cpp:90-94)
+static bool texture_alpha_below_one(const pt_scene* s, int tex, int depth){
+    if(tex < 0 || depth > 8)return false;
+    const pt_texture_desc& td = s->textures[tex].d;
+    if(td.kind == PT_TEX_IMAGE_U8 || td.kind == PT_TEX_IMAGE_F32)return td.channels == 4;
+    if(td.kind == PT_TEX_CHECKER)return texture_alpha_below_one(s, td.tex_a, depth + 1) || texture_alpha_below_one(s, td.tex_b, depth + 1);
+    return false;
+}
+
 int pack_traversal(pt_scene* s, int width, PackedTraversal& P){
     if(width != 2 && width != 4){ set_error("bvh_width must be 2 or 4"); return PT_ERR_INVALID; }
     if(s->instances.empty()){ set_error("scene has no instances"); return PT_ERR_INVALID; }
@@ -139,11 +149,7 @@ int pack_traversal(pt_scene* s, int width, PackedTraversal& P){
                 if(tester && md.alpha_mode != PT_ALPHA_OPAQUE){
                     flags |= TRI_ALPHA_PATH;     // HasAlpha(), Material.hpp:330-332
                     bool can_be_transparent = md.alpha >= 0;
-                    if(!can_be_transparent && md.tex >= 0){
-                        const pt_texture_desc& td = s->textures[md.tex].d;
-                        // Texture::alpha() is 1 unless an image has 4 channels (Texture.cpp:48-62)
-                        can_be_transparent = (td.kind == PT_TEX_IMAGE_U8 || td.kind == PT_TEX_IMAGE_F32 || td.kind == PT_TEX_CHECKER) && (td.kind == PT_TEX_CHECKER || td.channels == 4);
-                    }
+                    if(!can_be_transparent && md.tex >= 0)can_be_transparent = texture_alpha_below_one(s, md.tex, 0);
                     if(can_be_transparent){ flags |= TRI_ALPHA_TEX; s->has_alpha_tex = true; }
                 }
             }

@@ -45,7 +45,7 @@ PT_HDI V3 sample_normal_map(const ShadeScene& S, int mat, V3 ns, V3 tangent, flo
 
 // TriangleShape::Intersect's shading frame (Shape.cpp:205-243) + GeometricPrimitive::Intersect's
 // stamping (Primitive.cpp:20-24) + TransformedPrimitive::Intersect's world transform (Primitive.cpp:54-63)
-__host__ __device__ inline void build_interaction(const ShadeScene& S, V3 ro, V3 rd, float t, float bu, float bv, uint32_t prim, uint32_t inst, SurfInt& si){
+PT_HDN void build_interaction(const ShadeScene& S, V3 ro, V3 rd, float t, float bu, float bv, uint32_t prim, uint32_t inst, SurfInt& si){
     const DevInstShade& I = S.inst[inst];
     const DevBlasInfo bi = S.blas[I.blas];
     const uint32_t mesh = S.tri_mesh[bi.tri_base + prim];

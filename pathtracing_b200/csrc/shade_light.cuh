@@ -42,7 +42,7 @@ __host__ __device__ inline void tri_vertices(const ShadeScene& S, const DevLight
 }
 
 // Light::sample(uv, time).  `rng` feeds TextureInfiniteLight::sample's extra random_float (Light.cpp:120).
-__host__ __device__ inline void light_sample(const ShadeScene& S, const DevLight& L, float ux, float uy, Pcg& rng, LightSmp& o){
+PT_HDN void light_sample(const ShadeScene& S, const DevLight& L, float ux, float uy, Pcg& rng, LightSmp& o){
     o.L = v3(0.0f); o.p = v3(0.0f); o.n = v3(0.0f); o.dir = v3(0.0f); o.u = 0.0f; o.v = 0.0f;
     switch(L.kind){
     case DL_UNIFORM_INF: o.dir = sphere_dir(ux, uy); o.L = ld3(L.color); break;                  // Light.cpp:35-42
@@ -90,7 +90,7 @@ PT_HDI float tri_pdf(V3 p, V3 n, V3 ro, V3 rd, float area){
 }
 
 // Light::PDF(interaction, ray) of the light object the sampler holds (TransformedLight for xf instances)
-__host__ __device__ inline float light_pdf_sampled(const ShadeScene& S, const DevLight& L, V3 p, V3 n, V3 ro, V3 rd){
+PT_HDN float light_pdf_sampled(const ShadeScene& S, const DevLight& L, V3 p, V3 n, V3 ro, V3 rd){
     switch(L.kind){
     case DL_UNIFORM_INF: case DL_GRADIENT_INF: return 1.0f / (4.0f * kPi);
     case DL_TEXTURE_INF: {                                                                       // Light.cpp:146-150

@@ -12,20 +12,36 @@ struct Scatter {
     V3 o, d;            // scattered ray
 };
 
-// MicrofacetDiffuse::GetRoughness / GetMetallic (Material.hpp:272-278); ctor defaults :204
-PT_HDI float diff_roughness(const ShadeScene& S, const DevMaterial& M, const SurfInt& si){
-    const float g = M.rough >= 0 ? tex_eval(S, M.rough, si.u, si.v, si.ns).y : 1.0f;
-    return fmaxf(g, 0.0001f);
+// The material of one hit with its textures already evaluated at the hit's uv.  scatter / PDF /
+// calc_attenuation of the reference each look the same textures up again (Material.hpp:241-262,
+// 272-278, 309-323 ...); the values are identical, so they are fetched once per hit here.
+struct MatCtx {
+    int kind;
+    float ri;
+    V3 color;           // albedo texture (white for a ThinDielectric without one); conductor: F0 tint
+    float rough;        // Diffuse: max(texture.g, 1e-4), default 1 (Material.hpp:204,272-275); Dielectric: texture.g, default 0
+    float metallic;     // Diffuse: texture.b, default 0 (Material.hpp:276-278)
+};
+
+PT_HDN void mat_fetch(const ShadeScene& S, const SurfInt& si, MatCtx& m){
+    const DevMaterial& M = S.materials[si.mat];
+    m.kind = M.kind; m.ri = M.ri; m.rough = 0.0f; m.metallic = 0.0f;
+    if(M.kind == PT_MAT_CONDUCTOR){ m.color = ld3(M.albedo); return; }
+    m.color = M.tex >= 0 ? tex_eval(S, M.tex, si.u, si.v, si.ns) : v3(1.0f);
+    if(M.kind == PT_MAT_THIN_DIELECTRIC)return;
+    const float g = M.rough >= 0 ? tex_eval(S, M.rough, si.u, si.v, si.ns).y : (M.kind == PT_MAT_DIFFUSE ? 1.0f : 0.0f);
+    if(M.kind == PT_MAT_DIFFUSE){
+        m.rough = fmaxf(g, 0.0001f);
+        m.metallic = M.metal >= 0 ? tex_eval(S, M.metal, si.u, si.v, si.ns).z : 0.0f;
+    } else m.rough = g;
 }
-PT_HDI float diff_metallic(const ShadeScene& S, const DevMaterial& M, const SurfInt& si){
-    return M.metal >= 0 ? tex_eval(S, M.metal, si.u, si.v, si.ns).z : 0.0f;
-}
+
 PT_HDI float diff_prob(float r){ return r >= 0.7f ? 1.0f : 0.5f; }
 
 // shared tail of MicrofacetDiffuse::scatter / calc_attenuation (Material.hpp:241-262, 309-323)
-PT_HDI bool diff_f(const ShadeScene& S, const DevMaterial& M, const SurfInt& si, Ggx g, V3 wo, V3 wi, V3 wh, V3& f){
-    const V3 color = tex_eval(S, M.tex, si.u, si.v, si.ns);
-    const float metallic = diff_metallic(S, M, si);
+PT_HDI bool diff_f(const MatCtx& M, Ggx g, V3 wo, V3 wi, V3 wh, V3& f){
+    const V3 color = M.color;
+    const float metallic = M.metallic;
     const V3 F0 = v3(0.04f) * (1.0f - metallic) + color * metallic;       // glm::mix
     const V3 F = fresnel_schlick(dot(wi, wh), F0);
     const V3 num = (ggx_D(g, wh) * ggx_G(g, wo, wi)) * F;
@@ -37,8 +53,8 @@ PT_HDI bool diff_f(const ShadeScene& S, const DevMaterial& M, const SurfInt& si,
     return true;
 }
 
-__host__ __device__ inline bool diffuse_scatter(const ShadeScene& S, const DevMaterial& M, const SurfInt& si, V3 rd, float u, float ux, float uy, Scatter& out){
-    const float rough = diff_roughness(S, M, si);
+__host__ __device__ inline bool diffuse_scatter(const MatCtx& M, const SurfInt& si, V3 rd, float u, float ux, float uy, Scatter& out){
+    const float rough = M.rough;
     const Onb tbn = onb_from_normal(dot(rd, si.ns) > 0.0f ? -si.ns : si.ns);
     const Ggx g = { rough * rough };
     const float prob = diff_prob(rough);
@@ -58,13 +74,13 @@ __host__ __device__ inline bool diffuse_scatter(const ShadeScene& S, const DevMa
     const float dpdf = prob * wi.z * kInvPi;
     const float spdf = (1.0f - prob) * ggx_pdf(g, wo, wh) / (4.0f * fabsf(dot(wo, wh)));
     out.pdf = dpdf + spdf;
-    if(!diff_f(S, M, si, g, wo, wi, wh, out.f))return false;
+    if(!diff_f(M, g, wo, wi, wh, out.f))return false;
     out.o = si.p; out.d = to_world(tbn, wi); out.flags = 0;
     return true;
 }
 
-__host__ __device__ inline float diffuse_pdf(const ShadeScene& S, const DevMaterial& M, const SurfInt& si, V3 in, V3 outd){
-    const float rough = diff_roughness(S, M, si);
+__host__ __device__ inline float diffuse_pdf(const MatCtx& M, const SurfInt& si, V3 in, V3 outd){
+    const float rough = M.rough;
     const Ggx g = { rough * rough };
     const Onb tbn = onb_from_normal(dot(in, si.ns) > 0.0f ? -si.ns : si.ns);
     const V3 wo = to_local(tbn, -in);
@@ -75,31 +91,27 @@ __host__ __device__ inline float diffuse_pdf(const ShadeScene& S, const DevMater
     return d + sp;
 }
 
-__host__ __device__ inline V3 diffuse_eval(const ShadeScene& S, const DevMaterial& M, const SurfInt& si, V3 in, V3 outd){
+__host__ __device__ inline V3 diffuse_eval(const MatCtx& M, const SurfInt& si, V3 in, V3 outd){
     const Onb tbn = onb_from_normal(dot(in, si.ns) > 0.0f ? -si.ns : si.ns);
     const V3 wo = to_local(tbn, -in), wi = to_local(tbn, outd);
     const V3 wh = normalize(wo + wi);
-    const float rough = diff_roughness(S, M, si);
+    const float rough = M.rough;
     const Ggx g = { rough * rough };
     V3 f;
-    if(!diff_f(S, M, si, g, wo, wi, wh, f))return v3(0.0f);
+    if(!diff_f(M, g, wo, wi, wh, f))return v3(0.0f);
     return f;
 }
 
 // ---- MicrofacetDielectric (Material.hpp:363-598) -------------------------------------------
-PT_HDI float diel_roughness(const ShadeScene& S, const DevMaterial& M, const SurfInt& si){
-    return M.rough >= 0 ? tex_eval(S, M.rough, si.u, si.v, si.ns).y : 0.0f;
-}
-
-__host__ __device__ inline bool dielectric_scatter(const ShadeScene& S, const DevMaterial& M, const SurfInt& si, V3 ro, V3 rd, float u, float ux, float uy, Scatter& out){
-    const float rough = diel_roughness(S, M, si);
+__host__ __device__ inline bool dielectric_scatter(const MatCtx& M, const SurfInt& si, V3 ro, V3 rd, float u, float ux, float uy, Scatter& out){
+    const float rough = M.rough;
     const Ggx g = { rough * rough };
     const Onb tbn = onb_from_frame(si.ns, si.tangent);
     const V3 wo = to_local(tbn, -rd);
     const float eta = dot(-rd, si.ns) > 0.0f ? 1.0f / M.ri : M.ri;
     const V3 Ng = dot(rd, si.n) > 0.0f ? -si.n : si.n;
     const V3 at = ro + si.t * rd;
-    const V3 color = tex_eval(S, M.tex, si.u, si.v, si.ns);
+    const V3 color = M.color;
     if(M.ri == 1.0f || g.a < 1e-6f){
         const V3 N = dot(rd, si.ns) > 0.0f ? -si.ns : si.ns;
         const float R = fresnel_dielectric(wo.z, M.ri), T = 1.0f - R;
@@ -142,7 +154,7 @@ __host__ __device__ inline bool dielectric_scatter(const ShadeScene& S, const De
 }
 
 // common front of MicrofacetDielectric::PDF / calc_attenuation (Material.hpp:497-523, 540-566)
-__host__ __device__ inline bool diel_half(const DevMaterial& M, V3 wo, V3 wi, V3& wh, bool& reflect, float& etap){
+__host__ __device__ inline bool diel_half(const MatCtx& M, V3 wo, V3 wi, V3& wh, bool& reflect, float& etap){
     const float co = wo.z, ci = wi.z;
     reflect = ci * co > 0.0f;
     etap = 1.0f;
@@ -155,8 +167,8 @@ __host__ __device__ inline bool diel_half(const DevMaterial& M, V3 wo, V3 wi, V3
     return true;
 }
 
-__host__ __device__ inline float dielectric_pdf(const ShadeScene& S, const DevMaterial& M, const SurfInt& si, V3 in, V3 outd){
-    const float rough = diel_roughness(S, M, si);
+__host__ __device__ inline float dielectric_pdf(const MatCtx& M, const SurfInt& si, V3 in, V3 outd){
+    const float rough = M.rough;
     const Ggx g = { rough * rough };
     if(M.ri == 1.0f || g.a < 1e-6f)return 0.0f;
     const Onb tbn = onb_from_frame(si.ns, si.tangent);
@@ -170,8 +182,8 @@ __host__ __device__ inline float dielectric_pdf(const ShadeScene& S, const DevMa
     return pdf * (fabsf(dot(wi, wh)) / (s * s)) * T / (R + T);
 }
 
-__host__ __device__ inline V3 dielectric_eval(const ShadeScene& S, const DevMaterial& M, const SurfInt& si, V3 in, V3 outd){
-    const float rough = diel_roughness(S, M, si);
+__host__ __device__ inline V3 dielectric_eval(const MatCtx& M, const SurfInt& si, V3 in, V3 outd){
+    const float rough = M.rough;
     const Ggx g = { rough * rough };
     if(M.ri == 1.0f || g.a < 1e-6f)return v3(0.0f);
     const Onb tbn = onb_from_frame(si.ns, si.tangent);
@@ -179,7 +191,7 @@ __host__ __device__ inline V3 dielectric_eval(const ShadeScene& S, const DevMate
     V3 wh; bool reflect; float etap;
     if(!diel_half(M, wo, wi, wh, reflect, etap))return v3(0.0f);
     const float F = fresnel_dielectric(dot(wo, wh), M.ri);
-    const V3 color = tex_eval(S, M.tex, si.u, si.v, si.ns);
+    const V3 color = M.color;
     if(reflect)return color * (ggx_D(g, wh) * ggx_G(g, wo, wi) * F / fabsf(4.0f * wi.z * wo.z));
     const float s = dot(wi, wh) + dot(wo, wh) / etap;
     const float denom = s * s * wi.z * wo.z;
@@ -188,7 +200,7 @@ __host__ __device__ inline V3 dielectric_eval(const ShadeScene& S, const DevMate
 }
 
 // ---- ThinDielectric (Material.hpp:601-657), SpecularConductor (:660-673) -------------------
-__host__ __device__ inline bool thin_scatter(const ShadeScene& S, const DevMaterial& M, const SurfInt& si, V3 ro, V3 rd, float u, Scatter& out){
+__host__ __device__ inline bool thin_scatter(const MatCtx& M, const SurfInt& si, V3 ro, V3 rd, float u, Scatter& out){
     const Onb tbn = onb_from_frame(si.ns, si.tangent);
     const V3 wo = to_local(tbn, -rd);
     const V3 Ng = dot(rd, si.n) > 0.0f ? -si.n : si.n;
@@ -206,40 +218,37 @@ __host__ __device__ inline bool thin_scatter(const ShadeScene& S, const DevMater
         out.f = v3(T / fabsf(dot(si.ns, out.d)));
         out.pdf = T / (R + T);
     }
-    if(M.tex >= 0)out.f *= tex_eval(S, M.tex, si.u, si.v, si.ns);
+    out.f *= M.color;
     out.flags = BX_TRANSMISSIVE | BX_SPECULAR;
     return true;
 }
 
-__host__ __device__ inline bool conductor_scatter(const DevMaterial& M, const SurfInt& si, V3 rd, Scatter& out){
+__host__ __device__ inline bool conductor_scatter(const MatCtx& M, const SurfInt& si, V3 rd, Scatter& out){
     out.o = si.p; out.d = reflect3(rd, si.ns);
     const float d = dot(out.d, si.ns);
     if(d <= 0.0f)return false;
-    out.f = fresnel_schlick(dot(si.ns, -rd), ld3(M.albedo)) / d;
+    out.f = fresnel_schlick(dot(si.ns, -rd), M.color) / d;
     out.pdf = 1.0f; out.flags = BX_SPECULAR;
     return true;
 }
 
 // ---- dispatch (the reference's virtual calls) ------------------------------------------------
-__host__ __device__ inline bool mat_scatter(const ShadeScene& S, const SurfInt& si, V3 ro, V3 rd, float u, float ux, float uy, Scatter& out){
-    const DevMaterial& M = S.materials[si.mat];
+PT_HDN bool mat_scatter(const MatCtx& M, const SurfInt& si, V3 ro, V3 rd, float u, float ux, float uy, Scatter& out){
     switch(M.kind){
-    case PT_MAT_DIFFUSE: return diffuse_scatter(S, M, si, rd, u, ux, uy, out);
-    case PT_MAT_DIELECTRIC: return dielectric_scatter(S, M, si, ro, rd, u, ux, uy, out);
-    case PT_MAT_THIN_DIELECTRIC: return thin_scatter(S, M, si, ro, rd, u, out);
+    case PT_MAT_DIFFUSE: return diffuse_scatter(M, si, rd, u, ux, uy, out);
+    case PT_MAT_DIELECTRIC: return dielectric_scatter(M, si, ro, rd, u, ux, uy, out);
+    case PT_MAT_THIN_DIELECTRIC: return thin_scatter(M, si, ro, rd, u, out);
     default: return conductor_scatter(M, si, rd, out);
     }
 }
-__host__ __device__ inline float mat_pdf(const ShadeScene& S, const SurfInt& si, V3 in, V3 outd){
-    const DevMaterial& M = S.materials[si.mat];
-    if(M.kind == PT_MAT_DIFFUSE)return diffuse_pdf(S, M, si, in, outd);
-    if(M.kind == PT_MAT_DIELECTRIC)return dielectric_pdf(S, M, si, in, outd);
+PT_HDN float mat_pdf(const MatCtx& M, const SurfInt& si, V3 in, V3 outd){
+    if(M.kind == PT_MAT_DIFFUSE)return diffuse_pdf(M, si, in, outd);
+    if(M.kind == PT_MAT_DIELECTRIC)return dielectric_pdf(M, si, in, outd);
     return 0.0f;                                                  // Material.hpp:157-159, 651-653
 }
-__host__ __device__ inline V3 mat_eval(const ShadeScene& S, const SurfInt& si, V3 in, V3 outd){
-    const DevMaterial& M = S.materials[si.mat];
-    if(M.kind == PT_MAT_DIFFUSE)return diffuse_eval(S, M, si, in, outd);
-    if(M.kind == PT_MAT_DIELECTRIC)return dielectric_eval(S, M, si, in, outd);
+PT_HDN V3 mat_eval(const MatCtx& M, const SurfInt& si, V3 in, V3 outd){
+    if(M.kind == PT_MAT_DIFFUSE)return diffuse_eval(M, si, in, outd);
+    if(M.kind == PT_MAT_DIELECTRIC)return dielectric_eval(M, si, in, outd);
     if(M.kind == PT_MAT_THIN_DIELECTRIC)return v3(0.0f);
     return v3(1.0f);                                              // Material base class, Material.hpp:153-155
 }

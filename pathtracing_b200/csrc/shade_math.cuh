@@ -9,6 +9,18 @@
 #include "shade_types.h"
 
 #define PT_HDI __host__ __device__ __forceinline__
+// The big evaluators (texture, material, light, interaction).  k_shade stalls on instruction fetch (ncu:
+// stalled_no_instruction dominates), so code size matters; measured on B200 (Cornell 1024^2 x 16 spp, shade
+// stage): IEEE inline 16.3 ms (460 KB of SASS), IEEE calls 22.1, fast-math calls 17.5 (92 KB), fast-math
+// inline 11.2 (256 KB).  Calls lose to inlining despite the smaller code (ShadeScene is copied to a
+// stack frame, live registers spill around each call), so inline + fast math is the default.
+#if !defined(PTB_SHADE_NOINLINE)
+#define PT_HDN __host__ __device__ __forceinline__
+#elif defined(__CUDACC__)
+#define PT_HDN static __host__ __device__ __noinline__
+#else
+#define PT_HDN static __attribute__((noinline))
+#endif
 
 namespace ptb {
 
@@ -129,30 +141,50 @@ PT_HDI float texel_ch(const ShadeScene& S, const DevTexture& t, int x, int y, in
     return reinterpret_cast<const float*>(S.texels + t.texels)[o];
 }
 
-PT_HDI V3 tex_image(const ShadeScene& S, const DevTexture& t, float u, float v){
+// ImageTexture::Evaluate / FloatImageTexture::Evaluate: bilinear over the four texels around
+// uv * res - 0.5 with repeat wrap.  GetChannelAt(p, 1..3): channels beyond the image's own count read
+// neighbouring bytes in the reference; synthetic textures always carry >= 3 channels.
+PT_HDI V3 tex_image(const uint8_t* texels, const DevTexture& t, float u, float v){
     const float x = u * t.w - 0.5f, y = v * t.h - 0.5f;
     const int xi = (int)floorf(x), yi = (int)floorf(y);
     const float dx = x - xi, dy = y - yi;
-    V3 acc = v3(0.0f);
-    // GetChannelAt(p, 1..3): channels beyond the image's own count read neighbouring bytes in the
-    // reference; synthetic textures always carry >= 3 channels
-    const float w00 = (1 - dx) * (1 - dy), w10 = dx * (1 - dy), w01 = (1 - dx) * dy, w11 = dx * dy;
+    const int x0 = wrap_index(xi, t.w), x1 = x0 + 1 == t.w ? 0 : x0 + 1;
+    const int y0 = wrap_index(yi, t.h), y1 = y0 + 1 == t.h ? 0 : y0 + 1;
     const int c1 = t.ch > 1 ? 1 : 0, c2 = t.ch > 2 ? 2 : 0;
-#define PT_TX(X, Y) v3(texel_ch(S, t, X, Y, 0), texel_ch(S, t, X, Y, c1), texel_ch(S, t, X, Y, c2))
-    acc = w00 * PT_TX(xi, yi) + w10 * PT_TX(xi + 1, yi) + w01 * PT_TX(xi, yi + 1) + w11 * PT_TX(xi + 1, yi + 1);
-#undef PT_TX
-    return acc;
+    const size_t o00 = ((size_t)y0 * t.w + x0) * t.ch, o10 = ((size_t)y0 * t.w + x1) * t.ch;
+    const size_t o01 = ((size_t)y1 * t.w + x0) * t.ch, o11 = ((size_t)y1 * t.w + x1) * t.ch;
+    V3 a, b, c, d;
+    if(t.kind == PT_TEX_IMAGE_U8){
+        const uint8_t* px = texels + t.texels;
+        a = v3(px[o00] / 255.0f, px[o00 + c1] / 255.0f, px[o00 + c2] / 255.0f);
+        b = v3(px[o10] / 255.0f, px[o10 + c1] / 255.0f, px[o10 + c2] / 255.0f);
+        c = v3(px[o01] / 255.0f, px[o01 + c1] / 255.0f, px[o01 + c2] / 255.0f);
+        d = v3(px[o11] / 255.0f, px[o11 + c1] / 255.0f, px[o11 + c2] / 255.0f);
+    } else{
+        const float* px = reinterpret_cast<const float*>(texels + t.texels);
+        a = v3(px[o00], px[o00 + c1], px[o00 + c2]); b = v3(px[o10], px[o10 + c1], px[o10 + c2]);
+        c = v3(px[o01], px[o01 + c1], px[o01 + c2]); d = v3(px[o11], px[o11 + c1], px[o11 + c2]);
+    }
+    return ((1 - dx) * (1 - dy)) * a + (dx * (1 - dy)) * b + ((1 - dx) * dy) * c + (dx * dy) * d;
 }
 
 // Texture::Evaluate(interaction): uv and (for NormalTexture) the shading normal
-PT_HDI V3 tex_eval(const ShadeScene& S, int id, float u, float v, V3 ns){
+// One real function on the device (PT_TEX_CALL): inlined at its ~12 call sites it was most of k_shade's
+// code.  It takes the two table pointers by value so that no ShadeScene copy is needed for the call.
+#if defined(__CUDACC__) && !defined(PTB_TEX_INLINE)
+#define PT_TEX_CALL static __host__ __device__ __noinline__
+#else
+#define PT_TEX_CALL PT_HDI
+#endif
+PT_TEX_CALL V3 tex_eval_tables(const DevTexture* textures, const uint8_t* texels, int id, float u, float v, V3 ns){
     V3 scale = v3(1.0f);
+#pragma unroll 1
     for(int guard = 0; guard < 8; guard++){
-        const DevTexture& t = S.textures[id];
+        const DevTexture& t = textures[id];
         const V3 sc = scale * ld3(t.scale);
         switch(t.kind){
         case PT_TEX_SOLID: return sc * ld3(t.color);
-        case PT_TEX_IMAGE_U8: case PT_TEX_IMAGE_F32: return sc * tex_image(S, t, u, v);
+        case PT_TEX_IMAGE_U8: case PT_TEX_IMAGE_F32: return sc * tex_image(texels, t, u, v);
         case PT_TEX_UV: return sc * v3(u, v, 0.0f);
         case PT_TEX_NORMAL: return sc * ns;
         case PT_TEX_CHECKER: {
@@ -166,9 +198,10 @@ PT_HDI V3 tex_eval(const ShadeScene& S, int id, float u, float v, V3 ns){
     }
     return v3(0.0f);
 }
+PT_HDI V3 tex_eval(const ShadeScene& S, int id, float u, float v, V3 ns){ return tex_eval_tables(S.textures, S.texels, id, u, v, ns); }
 
 // Texture::alpha(uv) (Texture.cpp:48-94): 1 unless a 4-channel image
-PT_HDI float tex_alpha(const ShadeScene& S, int id, float u, float v){
+PT_HDN float tex_alpha(const ShadeScene& S, int id, float u, float v){
     for(int guard = 0; guard < 8; guard++){
         const DevTexture& t = S.textures[id];
         if(t.kind == PT_TEX_CHECKER){
