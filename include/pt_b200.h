@@ -253,6 +253,9 @@ typedef struct pt_render_stats {
     uint64_t shadow_rays;   /* NEE rays (any-hit or transmittance march legs) */
     uint64_t kernel_launches;
     double gpu_ms;          /* CUDA-event time of the whole render            */
+    uint64_t nonfinite_samples; /* samples whose radiance came out NaN/inf (e.g. the inf * 0 of a
+                               grazing GGX D, Material.hpp:73-86) and were left out of the film:
+                               the reference would add them and lose the pixel               */
 } pt_render_stats;
 
 /* Integrator::Render (Integrators.cpp:23-129) for the params' sample passes.

@@ -69,7 +69,7 @@ class pt_render_params(C.Structure):
 
 class pt_render_stats(C.Structure):
     _fields_ = [("samples", C.c_uint64), ("closest_rays", C.c_uint64), ("shadow_rays", C.c_uint64),
-                ("kernel_launches", C.c_uint64), ("gpu_ms", C.c_double)]
+                ("kernel_launches", C.c_uint64), ("gpu_ms", C.c_double), ("nonfinite_samples", C.c_uint64)]
 
 
 class pt_trace_stats(C.Structure):

@@ -50,7 +50,7 @@ struct Arena {
     float2* spos;       // fractional sample position inside the pixel
     uint64_t* gid;      // which camera sample lives in the slot (index into this call's sample sequence)
     uint32_t* done;     // slots whose path ended in the last shade pass: splatted, then handed to new samples
-    uint32_t* counters; // [0] next-queue size, [1] shadow-queue size, [2] done-list size
+    uint32_t* counters; // [0] next-queue size, [1] shadow-queue size, [2] done-list size, [3] non-finite samples of the call
 };
 
 struct BatchInfo {     // how a sample id maps to (pixel, sample index): id = pass_k * W*H + pixel
@@ -209,6 +209,10 @@ __global__ void __launch_bounds__(256) k_film(Arena A, BatchInfo B, FilterParams
     const int x = (int)(pixel % (uint32_t)B.W), y = (int)(pixel / (uint32_t)B.W);
     const float4 r = A.rad[slot];
     const float2 sp = A.spos[slot];
+    if(!(fabsf(r.x) <= 3.0e38f && fabsf(r.y) <= 3.0e38f && fabsf(r.z) <= 3.0e38f)){
+        atomicAdd(A.counters + 3, 1u);       // non-finite radiance: counted, not splatted (one NaN would own the pixel)
+        return;
+    }
     {   // per-pixel sum of squared sample radiance (owner pixel): the variance the 3-sigma parity test
         // and VarianceEstimator (Util.hpp:8-43) need
         double* q = film_sq + 3 * ((size_t)y * B.W + x);
@@ -301,6 +305,7 @@ __device__ inline void sample_ld(const ShadeScene& S, const SurfInt& si, const M
     out.want = true; out.o = ip; out.d = sd; out.tmax = t; out.contrib = c;
 }
 
+// 96 registers: forcing 6 or 8 resident CTAs (80 / 64 registers, spills) measured slower
 template <int INTEG>
 __global__ void __launch_bounds__(128) k_shade(Arena A, ShadeScene S, BatchInfo B, uint32_t n, int cur){
     const uint32_t j = blockIdx.x * blockDim.x + threadIdx.x;
@@ -607,6 +612,7 @@ int render_passes(pt_scene* s, const pt_camera_desc* cam, const pt_render_params
     cudaEvent_t e0, e1;
     cudaEventCreate(&e0); cudaEventCreate(&e1);
     cudaEventRecord(e0, st);
+    if(!cuda_ok(cudaMemsetAsync(A.counters, 0, 16, st), "counter reset"))return PT_ERR_CUDA;
     pt_render_stats R {};
     auto fail = [&](int code){ cudaFreeHost(h_counters); cudaEventDestroy(e0); cudaEventDestroy(e1); return code; };
 
@@ -703,7 +709,9 @@ int render_passes(pt_scene* s, const pt_camera_desc* cam, const pt_render_params
         }
     }
     cudaEventRecord(e1, st);
+    if(!cuda_ok(cudaMemcpyAsync(h_counters + 12, A.counters + 3, 4, cudaMemcpyDeviceToHost, st), "counters D2H"))return fail(PT_ERR_CUDA);
     if(!cuda_ok(cudaStreamSynchronize(st), "render"))return fail(PT_ERR_CUDA);
+    R.nonfinite_samples = h_counters[12];
     float ms = 0; cudaEventElapsedTime(&ms, e0, e1);
     R.gpu_ms = ms;
     if(getenv("PTB_PROFILE")){

@@ -28,7 +28,7 @@ def test_library_exports_every_declared_symbol():
 def test_struct_sizes_match_header():
     assert C.sizeof(capi.pt_trace_stats) == 48
     assert capi.RAY_DTYPE.itemsize == 32 and capi.HIT_DTYPE.itemsize == 16
-    assert C.sizeof(capi.pt_render_stats) == 40
+    assert C.sizeof(capi.pt_render_stats) == 48
 
 
 def test_no_device_is_a_loud_error():
