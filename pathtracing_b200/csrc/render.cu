@@ -607,14 +607,16 @@ int render_passes(pt_scene* s, const pt_camera_desc* cam, const pt_render_params
         lists[0] = (uint32_t*)(est + 6 * npix); lists[1] = lists[0] + npix; list_n = lists[1] + npix;
         if(!cuda_ok(cudaMemsetAsync(est, 0, 48 * npix, st), "estimator clear"))return PT_ERR_CUDA;
     }
-    uint32_t* h_counters = nullptr;
-    if(!cuda_ok(cudaMallocHost(&h_counters, 64), "pinned counters"))return PT_ERR_CUDA;
+    // pinned once per scene: cudaMallocHost / cudaFreeHost per frame cost milliseconds (more with other
+    // large pinned buffers mapped in the process) and synchronise the device
+    if(!b.h_counters && !cuda_ok(cudaMallocHost(&b.h_counters, 64), "pinned counters"))return PT_ERR_CUDA;
+    uint32_t* h_counters = (uint32_t*)b.h_counters;
     cudaEvent_t e0, e1;
     cudaEventCreate(&e0); cudaEventCreate(&e1);
     cudaEventRecord(e0, st);
     if(!cuda_ok(cudaMemsetAsync(A.counters, 0, 16, st), "counter reset"))return PT_ERR_CUDA;
     pt_render_stats R {};
-    auto fail = [&](int code){ cudaFreeHost(h_counters); cudaEventDestroy(e0); cudaEventDestroy(e1); return code; };
+    auto fail = [&](int code){ cudaEventDestroy(e0); cudaEventDestroy(e1); return code; };
 
     // one set of `count` camera samples through the wavefront.  The slot pool stays full: the slots whose
     // paths ended in a shade pass are splatted and handed to the next camera samples straight away, so the

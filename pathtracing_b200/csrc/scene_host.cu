@@ -34,6 +34,7 @@ void scene_free_device(pt_scene* s){
         &b.indices, &b.tri_light, &b.textures, &b.texels, &b.materials, &b.media, &b.lights, &b.light_cdf, &b.env_cdf, &b.film, &b.work, &b.adapt,
         &b.stage_rays, &b.stage_hits, &b.stage_inst, &b.stage_occ, &b.stats, &b.tri_mesh, &b.inst_light_base, &b.sampler_lights, &b.inf_lights, &b.cursors, &b.film_sq };
     for(void** p : ptrs){ if(*p){ cudaFree(*p); *p = nullptr; } }
+    if(b.h_counters){ cudaFreeHost(b.h_counters); b.h_counters = nullptr; }
     b.work_bytes = 0; b.adapt_bytes = 0; b.stage_cap = 0;
 }
 

@@ -54,6 +54,7 @@ struct DeviceBuffers {
     void* film_sq = nullptr;      // per-pixel sum of squared sample radiance, double[3*W*H]
     void* work = nullptr;         // wavefront state arena
     size_t work_bytes = 0;
+    void* h_counters = nullptr;   // pinned host words the wavefront loop reads queue sizes into
     void* adapt = nullptr;        // adaptive loop: per-pixel estimator sums + pixel lists
     size_t adapt_bytes = 0;
     // staging for the host-buffer ray-cast entry points
