@@ -182,8 +182,9 @@ PT_API int ref_scene_add_texture(void* p, const pt_texture_desc* d){
     case PT_TEX_CHECKER:
         t = std::make_shared<CheckerTexture>(s->textures.at(d->tex_a), s->textures.at(d->tex_b), glm::vec2(d->uv_scale[0], d->uv_scale[1]), scale);
         break;
-    case PT_TEX_UV: t = std::make_shared<UVTexture>(); break;
-    case PT_TEX_NORMAL: t = std::make_shared<NormalTexture>(); break;
+    // UVTexture / NormalTexture only have the implicit default constructor (Texture.hpp:215-232): colorScale is 1
+    case PT_TEX_UV: if(scale != glm::vec3(1))return PT_ERR_INVALID; t = std::make_shared<UVTexture>(); break;
+    case PT_TEX_NORMAL: if(scale != glm::vec3(1))return PT_ERR_INVALID; t = std::make_shared<NormalTexture>(); break;
     default: return PT_ERR_INVALID;
     }
     s->textures.push_back(t);

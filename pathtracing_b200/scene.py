@@ -65,6 +65,12 @@ class SceneDesc:
         assert pixels.dtype == np.float32
         return self._tex(capi.TEX_IMAGE_F32, pixels=pixels, scale=scale)
 
+    def uv_texture(self, scale=(1, 1, 1)):
+        return self._tex(capi.TEX_UV, scale=scale)
+
+    def normal_texture(self, scale=(1, 1, 1)):
+        return self._tex(capi.TEX_NORMAL, scale=scale)
+
     def checker(self, tex_a, tex_b, uv_scale, scale=(1, 1, 1)):
         return self._tex(capi.TEX_CHECKER, tex_a=tex_a, tex_b=tex_b, uv_scale=uv_scale, scale=scale)
 

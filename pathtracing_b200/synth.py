@@ -491,3 +491,27 @@ def rgbe_roundtrip(img: np.ndarray) -> np.ndarray:
     f1 = np.ldexp(np.float32(1.0), (e - 136).astype(np.int32)).astype(np.float32)
     out = np.where((e != 0)[..., None], bytes_.astype(np.float32) * f1[..., None], np.float32(0.0))
     return np.ascontiguousarray(out.astype(np.float32))
+
+
+def misc_scene(uv_tex=True, normal_tex=True, thin=True, lens=True, uniform_sky=True, metal_half=True):
+    """The corners the other scenes leave out: UniformInfiniteLight, UVTexture / NormalTexture albedos, a
+    thin-lens camera (focus angle and distance), ThinDielectric with an albedo texture, a one-channel-scaled
+    SolidColor (Texture::colorScale)."""
+    d = SceneDesc()
+    gp, gi, gn, gu = quad((-3, 0, -3), (0, 0, 6), (6, 0, 0))
+    ground = d.uv_texture() if uv_tex else d.solid((0.5, 0.5, 0.5))
+    d.instance(d.add_blas([d.mesh(gp, gi, gn, gu, material=d.diffuse(ground))]))
+    pos, idx, nrm, uv = icosphere(3)
+    plain = d.diffuse(d.solid((0.6, 0.6, 0.6)))
+    mats = [d.diffuse(d.normal_texture(), rough=d.solid((0.4, 0.4, 0.4))) if normal_tex else plain,
+            d.thin_dielectric(1.5, d.solid((0.8, 0.9, 1.0), scale=(1.0, 0.9, 0.8))) if thin else plain,
+            d.diffuse(d.solid((0.9, 0.4, 0.3)), rough=d.solid((0.2, 0.2, 0.2)), metal=d.solid((0.5, 0.5, 0.5))) if metal_half else plain]
+    for k, m in enumerate(mats):
+        b = d.add_blas([d.mesh(pos, idx, nrm, uv, material=m)])
+        d.instance(b, trs((-1.4 + 1.4 * k, 0.6, -0.5 * k), 0.55, (0.3, 1, 0.2), 0.7 * k))
+    if uniform_sky:
+        d.light(capi.LIGHT_UNIFORM_INFINITE, color=(0.7, 0.8, 1.0))
+    else:
+        d.light(capi.LIGHT_GRADIENT_INFINITE, color=(0.7, 0.8, 1.0), color_b=(0.7, 0.8, 1.0), scale=1.0)
+    cam = camera_desc((0.0, 1.3, 3.2), (0.0, 0.5, 0.0), fov=0.9, focus_angle=0.12 if lens else 0.0, focus_distance=3.3 if lens else 0.0)
+    return d, cam

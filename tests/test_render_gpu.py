@@ -225,6 +225,12 @@ def test_c5_terrain_hdr_environment_small():
 
 
 @needs_ref
+def test_misc_uniform_sky_uv_normal_textures_thin_lens():
+    desc, cam = synth.misc_scene()
+    compare(desc, cam, 64, 48, 1024, 8)
+
+
+@needs_ref
 def test_volpath_without_medium_equals_reference():
     desc, cam = synth.cornell_scene()
     compare(desc, cam, 40, 40, 1024, 6, integrator=capi.INTEGRATOR_VOLPATH)
