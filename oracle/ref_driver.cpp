@@ -63,6 +63,7 @@ struct RefScene {
     std::vector<std::shared_ptr<Primitive>> topLevel;    // per instance
     std::shared_ptr<Scene> scene;
     std::shared_ptr<LightSampler> lightSampler;
+    std::vector<std::shared_ptr<Light>> allLights;       // what was handed to lightSampler->Add, in order
     int width = 0;
     bool idMode = false;
 };
@@ -372,8 +373,9 @@ PT_API int ref_scene_commit(void* p, int bvh_width, int light_sampler, int id_mo
         }
     }
     // examples/example_1.cpp:99-101
-    s->lightSampler->Add(s->scene->GetLights());
-    for(auto& l : extra)s->lightSampler->Add(l);
+    s->allLights = s->scene->GetLights();
+    for(auto& l : extra)s->allLights.push_back(l);
+    s->lightSampler->Add(s->allLights);
     s->lightSampler->PreProcess(s->scene->BoundingBox());
     std::cout.rdbuf(old);
     return PT_OK;
@@ -580,6 +582,138 @@ PT_API int ref_render_stock(void* p, const pt_camera_desc* cd, const pt_render_p
     integrator->Render(threads);
     if(seconds)*seconds = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
     std::cout.rdbuf(old);
+    return PT_OK;
+}
+
+} // extern "C"
+
+
+// ---- deterministic unit probes (tests/test_shading_units.py): the reference's own shading routines at
+// caller-chosen inputs, next to tests/emul's host build of the product's shade*.cuh ------------------------
+extern "C" {
+
+// per ray, PT_UNIT_STRIDE floats (layout mirrored by tests/emul/emul.cpp emul_unit_shade):
+//  0 hit | 1-3 p | 4-6 n | 7-9 ns | 10-12 tangent | 13-14 uv | 15 t | 16 material id | 17 has area light
+//  18 scatter ok | 19-21 f | 22 pdf | 23 flags | 24-26 scattered origin | 27-29 scattered dir
+//  30-32 calc_attenuation(sampled dir) | 33 PDF(sampled dir) | 34-36 calc_attenuation(w2) | 37 PDF(w2)
+//  38-40 AreaLight::L(si, ray) | 41 AreaLight PMF | 42 AreaLight PDF(si, ray)
+// in: per ray u, ux, uy, w2.xyz (6 floats)
+PT_API int ref_unit_shade(void* p, const pt_ray* rays, size_t n, const float* in, float* out, int stride){
+    RefScene* s = static_cast<RefScene*>(p);
+    if(!s->scene || stride < 43)return PT_ERR_STATE;
+    for(size_t i = 0;i < n;i++){
+        float* o = out + i * (size_t)stride;
+        for(int k = 0;k < stride;k++)o[k] = 0.0f;
+        const pt_ray& r = rays[i];
+        Ray ray(glm::vec3(r.ox, r.oy, r.oz), glm::vec3(r.dx, r.dy, r.dz), r.time);
+        SurfaceInteraction si;
+        if(!s->scene->Intersect(ray, si, r.tmax))continue;
+        o[0] = 1.0f;
+        for(int k = 0;k < 3;k++){ o[1 + k] = si.p[k]; o[4 + k] = si.n[k]; o[7 + k] = si.ns[k]; o[10 + k] = si.tangent[k]; }
+        o[13] = si.uv.x; o[14] = si.uv.y; o[15] = si.t;
+        o[16] = -1.0f;
+        for(size_t m = 0;m < s->materials.size();m++)if(s->materials[m] == si.mat)o[16] = (float)m;
+        o[17] = si.AreaLight ? 1.0f : 0.0f;
+        const float* q = in + 6 * i;
+        if(si.mat){
+            Ray scattered;
+            std::optional<BxDFSample> bs = si.mat->scatter(ray, si, scattered, q[0], glm::vec2(q[1], q[2]));
+            if(bs){
+                o[18] = 1.0f;
+                for(int k = 0;k < 3;k++){ o[19 + k] = bs->f[k]; o[24 + k] = scattered.origin[k]; o[27 + k] = scattered.dir[k]; }
+                o[22] = bs->pdf; o[23] = (float)bs->flags;
+                glm::vec3 a = si.mat->calc_attenuation(ray, si, scattered);
+                for(int k = 0;k < 3;k++)o[30 + k] = a[k];
+                o[33] = si.mat->PDF(ray, si, scattered);
+            }
+            Ray other(si.p, glm::normalize(glm::vec3(q[3], q[4], q[5])), r.time);
+            glm::vec3 a2 = si.mat->calc_attenuation(ray, si, other);
+            for(int k = 0;k < 3;k++)o[34 + k] = a2[k];
+            o[37] = si.mat->PDF(ray, si, other);
+        }
+        if(si.AreaLight){
+            glm::vec3 L = si.AreaLight->L(si, ray);
+            for(int k = 0;k < 3;k++)o[38 + k] = L[k];
+            o[41] = s->lightSampler->PMF(si.AreaLight);
+            o[42] = si.AreaLight->PDF(si, ray);
+        }
+    }
+    return PT_OK;
+}
+
+PT_API int ref_unit_light_count(void* p){ return (int)static_cast<RefScene*>(p)->allLights.size(); }
+
+// per light: 0 Power | 1 PMF | 2 isDelta
+PT_API int ref_unit_lights(void* p, float* out){
+    RefScene* s = static_cast<RefScene*>(p);
+    for(size_t k = 0;k < s->allLights.size();k++){
+        out[3 * k] = s->allLights[k]->Power(); out[3 * k + 1] = s->lightSampler->PMF(s->allLights[k]); out[3 * k + 2] = s->allLights[k]->isDelta() ? 1.0f : 0.0f;
+    }
+    return PT_OK;
+}
+
+// Light::sample(uv) of light k and what SampleLd evaluates next for a shading point ip (Integrators.cpp:260-294):
+// in: ux, uy, ip.xyz | out: 0-2 sample.L | 3-5 p | 6-8 n | 9-10 uv | 11-13 dir | 14-16 shadow dir | 17 t | 18 PDF(sample, shadow ray) | 19-21 L(sample, shadow ray)
+PT_API int ref_unit_light_sample(void* p, int k, size_t n, const float* in, float* out, int stride){
+    RefScene* s = static_cast<RefScene*>(p);
+    if(k < 0 || k >= (int)s->allLights.size() || stride < 22)return PT_ERR_INVALID;
+    const std::shared_ptr<Light>& light = s->allLights[k];
+    for(size_t i = 0;i < n;i++){
+        const float* q = in + 5 * i;
+        float* o = out + i * (size_t)stride;
+        LightSample ls = light->sample(glm::vec2(q[0], q[1]), 0.0f);
+        glm::vec3 ip(q[2], q[3], q[4]), lightDir; float t;
+        if(ls.isDeltaInteraction()){ lightDir = ls.dir; t = std::numeric_limits<float>::infinity(); }
+        else{ lightDir = ls.interaction.p - ip; t = glm::length(lightDir) - shadowEpsilon; }
+        Ray shadow(ip, glm::normalize(lightDir), 0.0f);
+        for(int c = 0;c < 3;c++){ o[c] = ls.L[c]; o[3 + c] = ls.interaction.p[c]; o[6 + c] = ls.interaction.n[c]; o[11 + c] = ls.dir[c]; o[14 + c] = shadow.dir[c]; }
+        o[9] = ls.interaction.uv.x; o[10] = ls.interaction.uv.y; o[17] = t;
+        o[18] = light->PDF(ls.interaction, shadow);
+        glm::vec3 L = light->L(ls.interaction, shadow);
+        for(int c = 0;c < 3;c++)o[19 + c] = L[c];
+    }
+    return PT_OK;
+}
+
+// infinite lights seen by an escaping ray: sum over scene->infiniteLights of Le(ray), and each one's PDF * PMF
+PT_API int ref_unit_escape(void* p, size_t n, const float* dirs, float* out){
+    RefScene* s = static_cast<RefScene*>(p);
+    for(size_t i = 0;i < n;i++){
+        Ray ray(glm::vec3(0), glm::normalize(glm::vec3(dirs[3 * i], dirs[3 * i + 1], dirs[3 * i + 2])), 0.0f);
+        glm::vec3 le(0); float pp = 0;
+        for(auto& l : s->scene->infiniteLights){ le += l->Le(ray); pp += s->lightSampler->PMF(l) * l->PDF(GeometricInteraction {}, ray); }
+        out[4 * i] = le.x; out[4 * i + 1] = le.y; out[4 * i + 2] = le.z; out[4 * i + 3] = pp;
+    }
+    return PT_OK;
+}
+
+// Camera::GenerateRay(p, time, lens) for n samples: in px, py, time, lx, ly | out origin, dir, time
+PT_API int ref_unit_camera(const pt_camera_desc* cd, int W, int H, size_t n, const double* in, float* out){
+    auto film = std::make_shared<Film>(glm::ivec2 { W, H }, std::make_shared<BoxFilter>());
+    glm::vec3 from(cd->look_from[0], cd->look_from[1], cd->look_from[2]), at(cd->look_at[0], cd->look_at[1], cd->look_at[2]);
+    std::shared_ptr<Camera> camera;
+    if(cd->focus_angle == 0 || cd->focus_distance == 0)camera = std::make_shared<Camera>(from, at, cd->fov, film, glm::vec2(cd->shutter_start, cd->shutter_end));
+    else camera = std::make_shared<Camera>(from, at, cd->fov, film, cd->focus_angle, cd->focus_distance, nullptr);
+    for(size_t i = 0;i < n;i++){
+        const double* q = in + 5 * i;
+        Ray r = camera->GenerateRay(glm::dvec2(q[0], q[1]), (float)q[2], glm::vec2((float)q[3], (float)q[4]));
+        for(int c = 0;c < 3;c++){ out[7 * i + c] = r.origin[c]; out[7 * i + 3 + c] = r.dir[c]; }
+        out[7 * i + 6] = r.time;
+    }
+    return PT_OK;
+}
+
+// StratifiedSampler's building blocks (Util.hpp:45-168) and the phase function (PhaseFunction.cpp:4-26)
+PT_API uint32_t ref_unit_permutation_element(uint32_t i, uint32_t l, uint32_t p){ return (uint32_t)PermutationElement(i, l, p); }
+PT_API uint64_t ref_unit_hash(uint32_t px, uint32_t py, uint64_t dim){ return Hash(px, py, dim); }
+PT_API int ref_unit_hg(float g, size_t n, const float* in, float* out){
+    HenyeyGreenstein hg(g);
+    for(size_t i = 0;i < n;i++){
+        const float* q = in + 5 * i;
+        glm::vec3 wi = glm::normalize(glm::vec3(q[0], q[1], q[2])), wo;
+        float pdf = hg.Sample(wi, wo, glm::vec2(q[3], q[4]));
+        out[5 * i] = wo.x; out[5 * i + 1] = wo.y; out[5 * i + 2] = wo.z; out[5 * i + 3] = pdf; out[5 * i + 4] = hg.PDF(wi, wo);
+    }
     return PT_OK;
 }
 

@@ -23,14 +23,9 @@
 #include "scene_host.hpp"
 #include "shade_mat.cuh"
 #include "shade_light.cuh"
+#include "camera.cuh"
 
 namespace ptb {
-
-struct CamParams {      // Camera ctor, Camera.hpp:7-20
-    V3 from, u, v, w;
-    float half_w, half_h, defocus_radius, focus_distance, focus_angle, shutter0, shutter1;
-    int medium;
-};
 
 struct FilterParams {   // Filter.hpp:29-144
     int kind, rx, ry;   // integer splat radius = ceil(radius - 0.5)
@@ -119,17 +114,8 @@ __global__ void __launch_bounds__(256) k_generate(Arena A, BatchInfo B, CamParam
         ly = (float)(((double)(st / (uint32_t)B.sx) + (double)rnd_float(g)) / (double)B.sy);
     }
     const float px = (float)((double)x + jx), py = (float)((double)y + jy);   // GenerateRay takes a glm::vec2
-    const float uc = px / (float)B.W, vc = py / (float)B.H;
-    V3 dir = normalize(-C.w + ((2.0f * uc - 1.0f) * C.half_w) * C.u + ((2.0f * vc - 1.0f) * C.half_h) * C.v);
-    V3 org = C.from;
-    const float t = C.shutter0 + (C.shutter1 - C.shutter0) * time;
-    if(!(C.focus_distance == 0.0f || C.focus_angle == 0.0f)){
-        const float r = sqrtf(lx), th = 2.0f * kPi * ly;          // inUnitDisk, Random.hpp:60-64
-        const V3 off = (r * cosf(th)) * (C.u * C.defocus_radius) + (r * sinf(th)) * (C.v * C.defocus_radius);
-        dir = dir * C.focus_distance;
-        org = C.from + off;
-        dir = normalize(dir - off);
-    }
+    V3 org, dir; float t;
+    camera_ray(C, B.W, B.H, px, py, time, lx, ly, org, dir, t);
     const size_t q = (size_t)q_off + i;
     A.rays[cur][2 * q] = make_float4(org.x, org.y, org.z, CUDART_INF_F);
     A.rays[cur][2 * q + 1] = make_float4(dir.x, dir.y, dir.z, t);
@@ -493,20 +479,6 @@ static int make_filter(const pt_render_params* rp, FilterParams& F){
     }
     F.inv_integral = 1.0 / integral;
     return PT_OK;
-}
-
-static void make_camera(const pt_camera_desc* c, int W, int H, CamParams& C){
-    const V3 from = v3(c->look_from[0], c->look_from[1], c->look_from[2]), at = v3(c->look_at[0], c->look_at[1], c->look_at[2]);
-    C.from = from;
-    C.w = normalize(from - at);
-    C.u = normalize(cross(v3(0, 1, 0), C.w));
-    C.v = cross(C.w, C.u);
-    C.defocus_radius = (float)(c->focus_distance * std::tan(c->focus_angle / 2.0));
-    C.half_w = (float)std::tan(c->fov * 0.5);
-    C.half_h = C.half_w * (float)H / (float)W;
-    C.focus_distance = c->focus_distance; C.focus_angle = c->focus_angle;
-    C.shutter0 = c->shutter_start; C.shutter1 = c->shutter_end;
-    C.medium = c->medium;
 }
 
 static bool carve(char*& p, void** out, size_t bytes){ *out = p; p += (bytes + 255) & ~(size_t)255; return true; }

@@ -26,6 +26,10 @@ template <class T> static inline T __ldg(const T* p){ return *p; }
 
 #include "../../pathtracing_b200/csrc/scene_host.hpp"
 #include "../../pathtracing_b200/csrc/trace.cuh"
+#include "../../pathtracing_b200/csrc/shade_tables.hpp"
+#include "../../pathtracing_b200/csrc/shade_mat.cuh"
+#include "../../pathtracing_b200/csrc/shade_light.cuh"
+#include "../../pathtracing_b200/csrc/camera.cuh"
 
 using namespace ptb;
 
@@ -33,6 +37,8 @@ struct EmulScene {
     pt_scene s;
     PackedTraversal P;
     DevScene D;
+    ShadeTables T;          // host copies of the shading tables (emul_shade_tables)
+    bool shaded = false;
 };
 
 extern "C" {
@@ -108,6 +114,144 @@ PT_API int emul_trace_any(void* p, const pt_ray* rays, size_t n, uint8_t* occ){
     std::vector<std::thread> pool;
     for(int t = 0; t < nt; t++)pool.emplace_back(work, t);
     for(auto& t : pool)t.join();
+    return PT_OK;
+}
+
+} // extern "C"
+
+
+// ---- deterministic unit probes of the product's shade*.cuh compiled for the host (IEEE math, no fast-math):
+// the same record layouts as oracle/ref_driver.cpp ref_unit_* ------------------------------------------------
+extern "C" {
+
+PT_API int emul_shade_tables(void* p, int light_sampler){
+    EmulScene* e = (EmulScene*)p;
+    e->s.light_sampler = light_sampler;
+    int rc = build_shade_tables_host(&e->s, e->P.inst_order, e->T);
+    e->shaded = rc == PT_OK;
+    return rc;
+}
+
+PT_API int emul_unit_shade(void* p, const pt_ray* rays, size_t n, const float* in, float* out, int stride){
+    EmulScene* e = (EmulScene*)p;
+    if(!e->shaded || stride < 43)return PT_ERR_STATE;
+    const ShadeScene& S = e->T.view;
+    const float4* rb = reinterpret_cast<const float4*>(rays);
+    for(size_t i = 0; i < n; i++){
+        float* o = out + i * (size_t)stride;
+        for(int k = 0; k < stride; k++)o[k] = 0.0f;
+        HitRec h;
+        const bool hit = e->D.width == 2 ? trace_scene<2, false, false>(e->D, rb, i, h, nullptr, NoAlpha())
+                                         : trace_scene<4, false, false>(e->D, rb, i, h, nullptr, NoAlpha());
+        if(!hit)continue;
+        const V3 ro = v3(rays[i].ox, rays[i].oy, rays[i].oz), rd = v3(rays[i].dx, rays[i].dy, rays[i].dz);
+        SurfInt si;
+        build_interaction(S, ro, rd, h.t, h.u, h.v, h.prim, h.inst, si);
+        o[0] = 1.0f;
+        const V3 vs[4] = { si.p, si.n, si.ns, si.tangent };
+        for(int k = 0; k < 4; k++){ o[1 + 3 * k] = vs[k].x; o[2 + 3 * k] = vs[k].y; o[3 + 3 * k] = vs[k].z; }
+        o[13] = si.u; o[14] = si.v; o[15] = si.t; o[16] = (float)si.mat; o[17] = si.light >= 0 ? 1.0f : 0.0f;
+        const float* q = in + 6 * i;
+        if(si.mat >= 0){
+            MatCtx mc;
+            mat_fetch(S, si, mc);
+            Scatter sc;
+            if(mat_scatter(mc, si, ro, rd, q[0], q[1], q[2], sc)){
+                o[18] = 1.0f;
+                o[19] = sc.f.x; o[20] = sc.f.y; o[21] = sc.f.z; o[22] = sc.pdf; o[23] = (float)sc.flags;
+                o[24] = sc.o.x; o[25] = sc.o.y; o[26] = sc.o.z; o[27] = sc.d.x; o[28] = sc.d.y; o[29] = sc.d.z;
+                const V3 a = mat_eval(mc, si, rd, sc.d);
+                o[30] = a.x; o[31] = a.y; o[32] = a.z; o[33] = mat_pdf(mc, si, rd, sc.d);
+            }
+            const V3 w2 = normalize(v3(q[3], q[4], q[5]));
+            const V3 a2 = mat_eval(mc, si, rd, w2);
+            o[34] = a2.x; o[35] = a2.y; o[36] = a2.z; o[37] = mat_pdf(mc, si, rd, w2);
+        }
+        if(si.light >= 0){
+            const DevLight& L = S.lights[si.light];
+            const V3 le = tex_eval(S, L.tex, si.u, si.v, si.ns);       // what k_shade evaluates on an emissive hit
+            o[38] = le.x; o[39] = le.y; o[40] = le.z; o[41] = L.pmf_hit; o[42] = tri_pdf(si.p, si.n, ro, rd, L.area);
+        }
+    }
+    return PT_OK;
+}
+
+PT_API int emul_unit_light_count(void* p){ return (int)((EmulScene*)p)->T.lights.size(); }
+
+// per light: 0 power is not stored per light on the device (only the sampler's cdf): pmf_sample | 1 pmf_hit | 2 delta | 3 valid
+PT_API int emul_unit_lights(void* p, float* out){
+    EmulScene* e = (EmulScene*)p;
+    for(size_t k = 0; k < e->T.lights.size(); k++){
+        const DevLight& L = e->T.lights[k];
+        out[4 * k] = L.pmf_sample; out[4 * k + 1] = L.pmf_hit; out[4 * k + 2] = light_is_delta(L) ? 1.0f : 0.0f; out[4 * k + 3] = (float)L.valid;
+    }
+    return PT_OK;
+}
+
+PT_API int emul_unit_light_sample(void* p, int k, size_t n, const float* in, float* out, int stride){
+    EmulScene* e = (EmulScene*)p;
+    if(k < 0 || k >= (int)e->T.lights.size() || stride < 22)return PT_ERR_INVALID;
+    const ShadeScene& S = e->T.view;
+    const DevLight& L = S.lights[k];
+    Pcg rng = pcg_seed(1, 1);
+    for(size_t i = 0; i < n; i++){
+        const float* q = in + 5 * i;
+        float* o = out + i * (size_t)stride;
+        LightSmp ls;
+        light_sample(S, L, q[0], q[1], rng, ls);
+        const V3 ip = v3(q[2], q[3], q[4]);
+        V3 ldir; float t;
+        if(is_zero(ls.n)){ ldir = ls.dir; t = INFINITY; }
+        else{ ldir = ls.p - ip; t = length(ldir) - kEps; }
+        const V3 sd = normalize(ldir);
+        o[0] = ls.L.x; o[1] = ls.L.y; o[2] = ls.L.z; o[3] = ls.p.x; o[4] = ls.p.y; o[5] = ls.p.z; o[6] = ls.n.x; o[7] = ls.n.y; o[8] = ls.n.z;
+        o[9] = ls.u; o[10] = ls.v; o[11] = ls.dir.x; o[12] = ls.dir.y; o[13] = ls.dir.z; o[14] = sd.x; o[15] = sd.y; o[16] = sd.z; o[17] = t;
+        o[18] = light_pdf_sampled(S, L, ls.p, ls.n, ip, sd);
+        const V3 Lv = light_L_sampled(S, L, ls, sd);
+        o[19] = Lv.x; o[20] = Lv.y; o[21] = Lv.z;
+    }
+    return PT_OK;
+}
+
+PT_API int emul_unit_escape(void* p, size_t n, const float* dirs, float* out){
+    EmulScene* e = (EmulScene*)p;
+    const ShadeScene& S = e->T.view;
+    for(size_t i = 0; i < n; i++){
+        const V3 rd = normalize(v3(dirs[3 * i], dirs[3 * i + 1], dirs[3 * i + 2]));
+        V3 le = v3(0.0f); float pp = 0.0f;
+        for(int k = 0; k < S.n_inf_lights; k++){
+            const DevLight& L = S.lights[S.inf_lights[k]];
+            le += inf_Le(S, L, rd);
+            pp += L.pmf_sample * light_pdf_sampled(S, L, v3(0.0f), v3(0.0f), v3(0.0f), rd);
+        }
+        out[4 * i] = le.x; out[4 * i + 1] = le.y; out[4 * i + 2] = le.z; out[4 * i + 3] = pp;
+    }
+    return PT_OK;
+}
+
+PT_API int emul_unit_camera(const pt_camera_desc* cd, int W, int H, size_t n, const double* in, float* out){
+    CamParams C;
+    make_camera(cd, W, H, C);
+    for(size_t i = 0; i < n; i++){
+        const double* q = in + 5 * i;
+        V3 o, d; float t;
+        camera_ray(C, W, H, (float)q[0], (float)q[1], (float)q[2], (float)q[3], (float)q[4], o, d, t);
+        out[7 * i] = o.x; out[7 * i + 1] = o.y; out[7 * i + 2] = o.z; out[7 * i + 3] = d.x; out[7 * i + 4] = d.y; out[7 * i + 5] = d.z; out[7 * i + 6] = t;
+    }
+    return PT_OK;
+}
+
+PT_API uint32_t emul_unit_permutation_element(uint32_t i, uint32_t l, uint32_t p){ return permutation_element(i, l, p); }
+PT_API uint64_t emul_unit_hash(uint32_t px, uint32_t py, uint64_t dim){ return hash_ppd(px, py, dim); }
+PT_API int emul_unit_hg(float g, size_t n, const float* in, float* out){
+    const float gc = fminf(fmaxf(g, -0.99f), 0.99f);        // HenyeyGreenstein ctor clamp (PhaseFunction.hpp:20), applied at pt_scene_add_medium
+    for(size_t i = 0; i < n; i++){
+        const float* q = in + 5 * i;
+        const V3 wi = normalize(v3(q[0], q[1], q[2]));
+        const V3 wo = hg_sample(gc, wi, q[3], q[4]);
+        const float pdf = phase_hg(dot(wi, wo), gc);
+        out[5 * i] = wo.x; out[5 * i + 1] = wo.y; out[5 * i + 2] = wo.z; out[5 * i + 3] = pdf; out[5 * i + 4] = pdf;
+    }
     return PT_OK;
 }
 
