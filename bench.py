@@ -40,7 +40,7 @@ def parse():
     ap.add_argument("--tris", type=int, default=1_000_000)
     ap.add_argument("--rays", type=int, default=1 << 24)
     ap.add_argument("--mesh", default="soup", choices=["soup", "terrain"])
-    ap.add_argument("--bvh", type=int, default=4, choices=[2, 4])
+    ap.add_argument("--bvh", type=int, default=4, choices=[2, 4, 8])
     ap.add_argument("--no-extras", action="store_true", help="skip the BVH2 / any-hit / second-mesh side measurements")
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--renders", default="c1,c3,c4", help="render configs measured as extras: subset of c1,c3,c4,c5 (c5 builds a 10 M-triangle BVH: ~40 s)")
@@ -346,7 +346,7 @@ def run_ours(a):
     # roofline of the dominant (only) kernel: algorithmic bytes per ray from a counting build of the
     # same traversal: 32 B ray + 16 B hit + nodes*S_node + tris*48 + instances*96
     st = scene.trace_stats(d_rays.data_ptr(), n)
-    s_node = 64 if a.bvh == 2 else 128
+    s_node = {2: 64, 4: 128, 8: 256}[a.bvh]
     nodes_per_ray = (st["tlas_nodes"] + st["blas_nodes"]) / n
     tris_per_ray = st["triangles"] / n
     inst_per_ray = st["instances"] / n
@@ -372,6 +372,12 @@ def run_ours(a):
         ms2 = time_dev(lambda: s2.trace_closest_dev(d_rays.data_ptr(), n, d_hits.data_ptr(), None, stream), max(2, a.steps // 2), 2, torch, dist, 1)
         extras[f"closest_bvh{other}_mrays"] = n / (ms2 * 1e-3) / 1e6
         s2.close()
+        s8 = GpuScene(desc, 8, device=local)
+        ms8 = time_dev(lambda: s8.trace_closest_dev(d_rays.data_ptr(), n, d_hits.data_ptr(), None, stream), max(2, a.steps // 2), 2, torch, dist, 1)
+        extras["closest_bvh8_mrays"] = n / (ms8 * 1e-3) / 1e6
+        st8 = s8.trace_stats(d_rays.data_ptr(), n)
+        extras["bvh8_nodes_per_ray"] = (st8["tlas_nodes"] + st8["blas_nodes"]) / n
+        s8.close()
 
     for key, val in render_extras.items():
         extras[f"{key}_render"] = val

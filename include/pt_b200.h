@@ -175,8 +175,8 @@ PT_API int pt_scene_add_instance(pt_scene*, int blas_id, const float* transform1
 PT_API int pt_scene_add_light(pt_scene*, const pt_light_desc*);
 PT_API int pt_scene_set_medium(pt_scene*, int medium_id); /* Scene::SetMedium  */
 
-/* Scene::BuildTlas<TLAS2|TLAS4> + BLAS2|BLAS4 build + upload.
- * bvh_width in {2,4}.  light_sampler: 0 Uniform, 1 Power (LightSampler.cpp). */
+/* Scene::BuildTlas<TLAS2|TLAS4|TLAS8> + BLAS2|BLAS4|BLAS8 build + upload.
+ * bvh_width in {2,4,8} (BLAS8/TLAS8, BVH.hpp:1228-1552).  light_sampler: 0 Uniform, 1 Power (LightSampler.cpp). */
 PT_API int pt_scene_commit(pt_scene*, int bvh_width, int light_sampler);
 
 /* scene bounds after commit: Scene::BoundingBox (Scene.cpp:45-47)           */

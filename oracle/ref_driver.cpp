@@ -319,14 +319,15 @@ extern "C" {
 // count_rays: 1 = wrap the TLAS in a CountingPrimitive.
 PT_API int ref_scene_commit(void* p, int bvh_width, int light_sampler, int id_mode, int count_rays){
     RefScene* s = static_cast<RefScene*>(p);
-    if(bvh_width != 2 && bvh_width != 4)return PT_ERR_INVALID;
+    if(bvh_width != 2 && bvh_width != 4 && bvh_width != 8)return PT_ERR_INVALID;
     s->width = bvh_width;
     s->idMode = id_mode != 0;
     std::streambuf* old = std::cout.rdbuf(nullptr); // the BVH ctors print timings
     s->blasTris.resize(s->blasDescs.size());
     for(size_t b = 0;b < s->blasDescs.size();b++){
         s->blas.push_back(bvh_width == 2 ? buildBlas<BLAS2>(s, s->blasDescs[b], s->blasTris[b])
-            : buildBlas<BLAS4>(s, s->blasDescs[b], s->blasTris[b]));
+            : bvh_width == 4 ? buildBlas<BLAS4>(s, s->blasDescs[b], s->blasTris[b])
+            : buildBlas<BLAS8>(s, s->blasDescs[b], s->blasTris[b]));
     }
     std::shared_ptr<Medium> sceneMed = s->sceneMedium >= 0 ? s->media[s->sceneMedium] : nullptr;
     s->scene = std::make_shared<Scene>(sceneMed);
@@ -338,13 +339,15 @@ PT_API int ref_scene_commit(void* p, int bvh_width, int light_sampler, int id_mo
     if(count_rays){
         std::shared_ptr<Primitive> inner;
         if(bvh_width == 2)inner = std::make_shared<TLAS2>(s->topLevel);
-        else inner = std::make_shared<TLAS4>(s->topLevel);
+        else if(bvh_width == 4)inner = std::make_shared<TLAS4>(s->topLevel);
+        else inner = std::make_shared<TLAS8>(s->topLevel);
         s->scene->Add(std::make_shared<CountingPrimitive>(inner));
     } else{
         for(auto& prim : s->topLevel)s->scene->Add(prim);
     }
     if(bvh_width == 2)s->scene->BuildTlas<TLAS2>();
-    else s->scene->BuildTlas<TLAS4>();
+    else if(bvh_width == 4)s->scene->BuildTlas<TLAS4>();
+    else s->scene->BuildTlas<TLAS8>();
 
     if(light_sampler == 0)s->lightSampler = std::make_shared<UniformLightSampler>();
     else s->lightSampler = std::make_shared<PowerLightSampler>();

@@ -42,9 +42,10 @@ BinaryBvh build_binary_bvh(const Box* boxes, uint32_t n, uint32_t leaf_size = 2)
 // relative to this hierarchy's own arrays (offset it when packing several
 // BLASes into one device array).
 struct FlatBvh {
-    int width = 0;                 // 2 or 4
+    int width = 0;                 // 2, 4 or 8
     std::vector<Bvh2Node> n2;
     std::vector<Bvh4Node> n4;
+    std::vector<Bvh8Node> n8;
     uint32_t root = REF_EMPTY;
     Box bounds = box_empty();
     std::vector<uint32_t> order;   // leaf order -> original item index

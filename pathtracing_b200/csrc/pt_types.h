@@ -47,6 +47,18 @@ struct alignas(16) Bvh4Node {
 };
 static_assert(sizeof(Bvh4Node) == 128, "Bvh4Node must be 128 B");
 
+// BVH8 cluster, 256 B = eight 32 B sectors.  Same content as BVH8_CLUSTER (BVH.hpp:1241-1257) with the child
+// boxes stored as two 4-lane halves (half h holds lanes 4h..4h+3: xmin[4] xmax[4] ymin[4] ymax[4] zmin[4]
+// zmax[4]) so that a half is three 256-bit loads and eight slab tests never hold 48 box floats at once.
+// order[octant]: the visit sequence of BVH8::buildPerm (BVH.hpp:1356-1372), nearest lane in bits 0-2,
+// absent lanes last (never pushed).
+struct alignas(32) Bvh8Node {
+    float box[2][6][4];
+    uint32_t ref[8];
+    uint32_t order[8];
+};
+static_assert(sizeof(Bvh8Node) == 256, "Bvh8Node must be 256 B");
+
 // Triangle in leaf order, 48 B: vertex 0 and the two edges exactly as
 // glm::intersectRayTriangle forms them (edge = v - v0 is a single correctly
 // rounded subtraction, so precomputing it is bit-identical).
@@ -82,10 +94,11 @@ constexpr uint32_t INST_XF = 2u;         // TransformedPrimitive (Primitive.cpp:
 struct DevScene {
     const Bvh2Node* n2;      // BVH2 nodes: all BLASes, then the TLAS
     const Bvh4Node* n4;      // BVH4 clusters: all BLASes, then the TLAS
+    const Bvh8Node* n8;      // BVH8 clusters: all BLASes, then the TLAS
     const Tri* tris;         // all BLAS triangles in leaf order
     const Instance* inst;    // instances in TLAS leaf order
     uint32_t tlas_root;      // ref into n2/n4 (or a leaf ref into inst)
-    int width;               // 2 | 4
+    int width;               // 2 | 4 | 8
     float tlo[3], thi[3];    // TLAS root box (BVH2::Intersect tests it first)
     uint32_t single_root;    // scene = one untransformed instance: its BLAS root ref (traversal starts
                              // inside it, no TLAS leaf / instance record round trip); else REF_EMPTY

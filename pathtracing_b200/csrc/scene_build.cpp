@@ -122,7 +122,7 @@ static bool texture_alpha_below_one(const pt_scene* s, int tex, int depth){
 }
 
 int pack_traversal(pt_scene* s, int width, PackedTraversal& P){
-    if(width != 2 && width != 4){ set_error("bvh_width must be 2 or 4"); return PT_ERR_INVALID; }
+    if(width != 2 && width != 4 && width != 8){ set_error("bvh_width must be 2, 4 or 8"); return PT_ERR_INVALID; }
     if(s->instances.empty()){ set_error("scene has no instances"); return PT_ERR_INVALID; }
     std::vector<Bvh2Node>& n2 = P.n2;
     std::vector<Bvh4Node>& n4 = P.n4;
@@ -168,7 +168,7 @@ int pack_traversal(pt_scene* s, int width, PackedTraversal& P){
         FlatBvh fb = flatten_bvh(bb, width);
         hb.tri_base = (uint32_t)tris.size();
         hb.bounds = fb.bounds;
-        const uint32_t node_base = width == 2 ? (uint32_t)n2.size() : (uint32_t)n4.size();
+        const uint32_t node_base = width == 2 ? (uint32_t)n2.size() : width == 4 ? (uint32_t)n4.size() : (uint32_t)P.n8.size();
         auto rebase = [&](uint32_t ref) -> uint32_t{
             if(ref == REF_EMPTY)return ref;
             if(ref & REF_LEAF)return REF_LEAF | ((ref & ~REF_LEAF) + hb.tri_base);
@@ -177,8 +177,10 @@ int pack_traversal(pt_scene* s, int width, PackedTraversal& P){
         hb.root = rebase(fb.root);
         if(width == 2){
             for(Bvh2Node nd : fb.n2){ nd.ref0 = rebase(nd.ref0); nd.ref1 = rebase(nd.ref1); n2.push_back(nd); }
-        } else{
+        } else if(width == 4){
             for(Bvh4Node nd : fb.n4){ for(int k = 0; k < 4; k++)nd.ref[k] = rebase(nd.ref[k]); n4.push_back(nd); }
+        } else{
+            for(Bvh8Node nd : fb.n8){ for(int k = 0; k < 8; k++)nd.ref[k] = rebase(nd.ref[k]); P.n8.push_back(nd); }
         }
         for(uint32_t i = 0; i < hb.n_tris; i++){
             Tri T = src[fb.order[i]];
@@ -199,15 +201,17 @@ int pack_traversal(pt_scene* s, int width, PackedTraversal& P){
     BinaryBvh tb = build_binary_bvh(iboxes.data(), ni);
     FlatBvh tf = flatten_bvh(tb, width);
     s->bounds = tf.bounds;
-    const uint32_t tnode_base = width == 2 ? (uint32_t)n2.size() : (uint32_t)n4.size();
+    const uint32_t tnode_base = width == 2 ? (uint32_t)n2.size() : width == 4 ? (uint32_t)n4.size() : (uint32_t)P.n8.size();
     auto trebase = [&](uint32_t ref) -> uint32_t{
         if(ref == REF_EMPTY || (ref & REF_LEAF))return ref;
         return ref + tnode_base;
     };
     if(width == 2){
         for(Bvh2Node nd : tf.n2){ nd.ref0 = trebase(nd.ref0); nd.ref1 = trebase(nd.ref1); n2.push_back(nd); }
-    } else{
+    } else if(width == 4){
         for(Bvh4Node nd : tf.n4){ for(int k = 0; k < 4; k++)nd.ref[k] = trebase(nd.ref[k]); n4.push_back(nd); }
+    } else{
+        for(Bvh8Node nd : tf.n8){ for(int k = 0; k < 8; k++)nd.ref[k] = trebase(nd.ref[k]); P.n8.push_back(nd); }
     }
     std::vector<Instance>& insts = P.insts;
     insts.assign(ni, Instance());

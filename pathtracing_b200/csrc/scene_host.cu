@@ -30,7 +30,7 @@ int build_shade_tables(pt_scene* s, const std::vector<uint32_t>& inst_order);   
 
 void scene_free_device(pt_scene* s){
     DeviceBuffers& b = s->buf;
-    void** ptrs[] = { &b.n2, &b.n4, &b.tris, &b.inst, &b.meshes, &b.blas_info, &b.inst_shade, &b.vtx_pos, &b.vtx_nrm, &b.vtx_uv, &b.vtx_tan,
+    void** ptrs[] = { &b.n2, &b.n4, &b.n8, &b.tris, &b.inst, &b.meshes, &b.blas_info, &b.inst_shade, &b.vtx_pos, &b.vtx_nrm, &b.vtx_uv, &b.vtx_tan,
         &b.indices, &b.tri_light, &b.textures, &b.texels, &b.materials, &b.media, &b.lights, &b.light_cdf, &b.env_cdf, &b.film, &b.work, &b.adapt,
         &b.stage_rays, &b.stage_hits, &b.stage_inst, &b.stage_occ, &b.stats, &b.tri_mesh, &b.inst_light_base, &b.sampler_lights, &b.inf_lights, &b.cursors, &b.film_sq };
     for(void** p : ptrs){ if(*p){ cudaFree(*p); *p = nullptr; } }
@@ -54,19 +54,19 @@ int scene_commit(pt_scene* s, int width, int light_sampler){
 
     // ---- upload ---------------------------------------------------------------------
     DeviceBuffers& b = s->buf;
-    if(!upload(&b.n2, n2, "upload bvh2 nodes") || !upload(&b.n4, n4, "upload bvh4 clusters") ||
+    if(!upload(&b.n2, n2, "upload bvh2 nodes") || !upload(&b.n4, n4, "upload bvh4 clusters") || !upload(&b.n8, P.n8, "upload bvh8 clusters") ||
        !upload(&b.tris, tris, "upload triangles") || !upload(&b.inst, insts, "upload instances")){
         scene_free_device(s);
         return PT_ERR_CUDA;
     }
-    s->dev.n2 = (const Bvh2Node*)b.n2; s->dev.n4 = (const Bvh4Node*)b.n4;
+    s->dev.n2 = (const Bvh2Node*)b.n2; s->dev.n4 = (const Bvh4Node*)b.n4; s->dev.n8 = (const Bvh8Node*)b.n8;
     s->dev.tris = (const Tri*)b.tris; s->dev.inst = (const Instance*)b.inst;
     s->dev.tlas_root = P.tlas_root;
     s->dev.width = width;
     s->dev.single_root = P.single_root; s->dev.single_id = P.single_id;
     for(int a = 0; a < 3; a++){ s->dev.tlo[a] = P.bounds.lo[a]; s->dev.thi[a] = P.bounds.hi[a]; }
     s->total_tris = tris.size();
-    s->total_nodes = width == 2 ? n2.size() : n4.size();
+    s->total_nodes = width == 2 ? n2.size() : width == 4 ? n4.size() : P.n8.size();
 
     int rc = build_shade_tables(s, P.inst_order);
     if(rc != PT_OK){ scene_free_device(s); return rc; }

@@ -43,7 +43,7 @@ struct HostInstance {
 };
 
 struct DeviceBuffers {
-    void* n2 = nullptr; void* n4 = nullptr; void* tris = nullptr; void* inst = nullptr;
+    void* n2 = nullptr; void* n4 = nullptr; void* n8 = nullptr; void* tris = nullptr; void* inst = nullptr;
     // shading tables
     void* meshes = nullptr; void* blas_info = nullptr; void* inst_shade = nullptr;
     void* vtx_pos = nullptr; void* vtx_nrm = nullptr; void* vtx_uv = nullptr; void* vtx_tan = nullptr; void* indices = nullptr;
@@ -101,6 +101,7 @@ namespace ptb {
 struct PackedTraversal {
     std::vector<Bvh2Node> n2;
     std::vector<Bvh4Node> n4;
+    std::vector<Bvh8Node> n8;
     std::vector<Tri> tris;
     std::vector<Instance> insts;      // TLAS leaf order
     std::vector<uint32_t> inst_order; // leaf order -> instance id

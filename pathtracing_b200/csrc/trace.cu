@@ -159,6 +159,10 @@ static int launch(pt_scene* sc, const void* d_rays, size_t n, void* d_hits, void
         return launch_ks<WIDTH, ANY, STATS, 0>(sc, d_rays, n, d_hits, d_inst, d_occ, d_stats, stream, at);
     }
     const NoAlpha na;
+    if constexpr(WIDTH == 8){
+        if(ks >= 16)return launch_ks<WIDTH, ANY, STATS, 16>(sc, d_rays, n, d_hits, d_inst, d_occ, d_stats, stream, na);
+        return launch_ks<WIDTH, ANY, STATS, 0>(sc, d_rays, n, d_hits, d_inst, d_occ, d_stats, stream, na);
+    }
     if(ks >= 24)return launch_ks<WIDTH, ANY, STATS, 24>(sc, d_rays, n, d_hits, d_inst, d_occ, d_stats, stream, na);
     if(ks >= 16)return launch_ks<WIDTH, ANY, STATS, 16>(sc, d_rays, n, d_hits, d_inst, d_occ, d_stats, stream, na);
     if(ks >= 8)return launch_ks<WIDTH, ANY, STATS, 8>(sc, d_rays, n, d_hits, d_inst, d_occ, d_stats, stream, na);
@@ -169,20 +173,23 @@ static int launch(pt_scene* sc, const void* d_rays, size_t n, void* d_hits, void
 int launch_trace_closest(pt_scene* sc, const void* d_rays, size_t n, void* d_hits, void* d_inst, void* stream){
     if(n == 0)return PT_OK;
     return sc->dev.width == 2 ? launch<2, false, false>(sc, d_rays, n, d_hits, d_inst, nullptr, nullptr, stream)
-                              : launch<4, false, false>(sc, d_rays, n, d_hits, d_inst, nullptr, nullptr, stream);
+         : sc->dev.width == 4 ? launch<4, false, false>(sc, d_rays, n, d_hits, d_inst, nullptr, nullptr, stream)
+                              : launch<8, false, false>(sc, d_rays, n, d_hits, d_inst, nullptr, nullptr, stream);
 }
 
 int launch_trace_any(pt_scene* sc, const void* d_rays, size_t n, void* d_occ, void* stream){
     if(n == 0)return PT_OK;
     return sc->dev.width == 2 ? launch<2, true, false>(sc, d_rays, n, nullptr, nullptr, d_occ, nullptr, stream)
-                              : launch<4, true, false>(sc, d_rays, n, nullptr, nullptr, d_occ, nullptr, stream);
+         : sc->dev.width == 4 ? launch<4, true, false>(sc, d_rays, n, nullptr, nullptr, d_occ, nullptr, stream)
+                              : launch<8, true, false>(sc, d_rays, n, nullptr, nullptr, d_occ, nullptr, stream);
 }
 
 // counting build of the same closest-hit traversal
 int launch_trace_stats(pt_scene* sc, const void* d_rays, size_t n, void* d_counters, void* stream){
     if(n == 0)return PT_OK;
     return sc->dev.width == 2 ? launch<2, false, true>(sc, d_rays, n, nullptr, nullptr, nullptr, d_counters, stream)
-                              : launch<4, false, true>(sc, d_rays, n, nullptr, nullptr, nullptr, d_counters, stream);
+         : sc->dev.width == 4 ? launch<4, false, true>(sc, d_rays, n, nullptr, nullptr, nullptr, d_counters, stream)
+                              : launch<8, false, true>(sc, d_rays, n, nullptr, nullptr, nullptr, d_counters, stream);
 }
 
 } // namespace ptb

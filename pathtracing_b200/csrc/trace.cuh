@@ -333,6 +333,55 @@ __device__ __forceinline__ void node_step4(TravState& s, const DevScene& S, cons
     s.cur = cur;
 }
 
+// BVH8 cluster (BVH8::Intersect / IntersectPred, BVH.hpp:1374-1540): the same slab test and strict
+// `tEntry < max` as BVH4, children pushed in the per-octant order of buildPerm so that the nearest pops
+// first, entry-distance cull at pop.  Two 4-lane halves of three 256-bit loads each, one for the refs, and
+// the 4-byte visit code of this ray's octant: all eight sectors of the cluster.
+template <class T>
+__device__ __forceinline__ T sel8(const T (&a)[8], unsigned lane){
+    const bool b0 = (lane & 1u) != 0, b1 = (lane & 2u) != 0, b2 = (lane & 4u) != 0;
+    const T t0 = b0 ? a[1] : a[0], t1 = b0 ? a[3] : a[2], t2 = b0 ? a[5] : a[4], t3 = b0 ? a[7] : a[6];
+    const T u0 = b1 ? t1 : t0, u1 = b1 ? t3 : t2;
+    return b2 ? u1 : u0;
+}
+
+template <bool ANY, class STK>
+__device__ __forceinline__ void node_step8(TravState& s, const DevScene& S, const STK& stack){
+    const float4* p = reinterpret_cast<const float4*>(S.n8 + s.cur);
+    float e[8], x;
+    unsigned mask = 0;
+    const float tmax = s.tmax;
+#pragma unroll
+    for(int h = 0; h < 2; h++){
+        const F8 wx = ldg256(p + 6 * h), wy = ldg256(p + 6 * h + 2), wz = ldg256(p + 6 * h + 4);
+        slab(s.r, wx.lo.x, wy.lo.x, wz.lo.x, wx.hi.x, wy.hi.x, wz.hi.x, e[4 * h + 0], x); if(x >= kShadowEps && e[4 * h + 0] < tmax && e[4 * h + 0] <= x)mask |= 1u << (4 * h);
+        slab(s.r, wx.lo.y, wy.lo.y, wz.lo.y, wx.hi.y, wy.hi.y, wz.hi.y, e[4 * h + 1], x); if(x >= kShadowEps && e[4 * h + 1] < tmax && e[4 * h + 1] <= x)mask |= 2u << (4 * h);
+        slab(s.r, wx.lo.z, wy.lo.z, wz.lo.z, wx.hi.z, wy.hi.z, wz.hi.z, e[4 * h + 2], x); if(x >= kShadowEps && e[4 * h + 2] < tmax && e[4 * h + 2] <= x)mask |= 4u << (4 * h);
+        slab(s.r, wx.lo.w, wy.lo.w, wz.lo.w, wx.hi.w, wy.hi.w, wz.hi.w, e[4 * h + 3], x); if(x >= kShadowEps && e[4 * h + 3] < tmax && e[4 * h + 3] <= x)mask |= 8u << (4 * h);
+    }
+    const F8 wr = ldg256(p + 12);
+    const uint32_t refs[8] = { __float_as_uint(wr.lo.x), __float_as_uint(wr.lo.y), __float_as_uint(wr.lo.z), __float_as_uint(wr.lo.w),
+                               __float_as_uint(wr.hi.x), __float_as_uint(wr.hi.y), __float_as_uint(wr.hi.z), __float_as_uint(wr.hi.w) };
+    const unsigned code = __ldg(reinterpret_cast<const unsigned*>(p + 14) + s.octant);
+    uint32_t cur = REF_EMPTY;
+    float cure = 0.0f;
+    int sp = s.sp;
+#pragma unroll
+    for(int k = 7; k >= 0; k--){                 // far to near: the nearest hit lane ends up in `cur`
+        const unsigned lane = (code >> (3 * k)) & 7u;
+        const uint32_t r = sel8(refs, lane);
+        const float en = sel8(e, lane);
+        const bool hit = ((mask >> lane) & 1u) != 0 && r != REF_EMPTY;   // absent lanes have zero boxes, never children
+        const bool push = hit && cur != REF_EMPTY && sp < kStack;
+        if(push)stack.st(sp, make_uint2(cur, __float_as_uint(cure)));
+        sp += push ? 1 : 0;
+        cur = hit ? r : cur;
+        cure = hit ? en : cure;
+    }
+    s.sp = sp;
+    s.cur = cur;
+}
+
 // ---- one round of the state machine -------------------------------------------------------
 
 // Returns false once the ray is finished (s.flags & TF_DONE).
@@ -345,7 +394,7 @@ __device__ __forceinline__ void trav_step(TravState& s, const DevScene& S, const
     if(s.cur == REF_EMPTY){
         while(s.sp > 0){
             const uint2 e = stack.ld(--s.sp);
-            if(WIDTH == 4 && !ANY && __uint_as_float(e.y) > s.tmax)continue;
+            if(WIDTH >= 4 && !ANY && __uint_as_float(e.y) > s.tmax)continue;
             if(e.x == REF_EMPTY)continue;      // empty lane of a cluster (BVH.hpp:38-43)
             s.cur = e.x;
             break;
@@ -356,7 +405,8 @@ __device__ __forceinline__ void trav_step(TravState& s, const DevScene& S, const
     if(!(s.cur & REF_LEAF)){
         if(STATS){ if(s.flags & TF_IN_INST)cnt->blas_nodes++; else cnt->tlas_nodes++; }
         if(WIDTH == 2)node_step2<ANY>(s, S, stack);
-        else node_step4<ANY>(s, S, stack);
+        else if(WIDTH == 4)node_step4<ANY>(s, S, stack);
+        else node_step8<ANY>(s, S, stack);
     }
     // -- leaf items --
     if((s.cur & REF_LEAF) && s.cur != REF_EMPTY){

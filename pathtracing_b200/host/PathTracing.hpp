@@ -438,11 +438,13 @@ public:
     bool IsSceneLights() const override{ return true; }
 };
 
-// ---- Primitive.hpp:7-50, Model.hpp:14-80, BVH.hpp:554-555,1219-1220 -----------------------------------
+// ---- Primitive.hpp:7-50, Model.hpp:14-80, BVH.hpp:554-555,1219-1220,1550-1551 -----------------------------------
 struct BLAS2 { static constexpr int width = 2; };
 struct BLAS4 { static constexpr int width = 4; };
+struct BLAS8 { static constexpr int width = 8; };
 struct TLAS2 { static constexpr int width = 2; };
 struct TLAS4 { static constexpr int width = 4; };
+struct TLAS8 { static constexpr int width = 8; };
 
 class Primitive {
 public:
@@ -465,7 +467,7 @@ public:
     }
     int RequiredWidth() const override{ return width; }
     void Lower(ptb_host::Builder& b, const glm::mat4* transform) const override{
-        if(width == 0)throw std::logic_error("Model::BuildBlas<BLAS2|BLAS4>() was not called");
+        if(width == 0)throw std::logic_error("Model::BuildBlas<BLAS2|BLAS4|BLAS8>() was not called");
         int blas = b.lookup(this);
         if(blas < 0){
             std::vector<int32_t> ids;
@@ -570,7 +572,7 @@ public:
     // Lowers the object graph into a pt_scene and commits it; cached until the graph or the light
     // sampler changes.  sampler == nullptr: ray casting only (PowerLightSampler tables are built anyway).
     pt_scene* Commit(const LightSampler* sampler, const std::shared_ptr<Medium>& cameraMedium = nullptr){
-        if(tlasWidth == 0)throw std::logic_error("Scene::BuildTlas<TLAS2|TLAS4>() was not called");
+        if(tlasWidth == 0)throw std::logic_error("Scene::BuildTlas<TLAS2|TLAS4|TLAS8>() was not called");
         const int kind = sampler ? sampler->Kind() : 1;
         std::vector<const void*> key;
         for(const auto& l : infiniteLights)key.push_back(l.get());
@@ -585,7 +587,7 @@ public:
         try{
             for(const std::shared_ptr<Primitive>& p : primitives){
                 const int w = p->RequiredWidth();
-                if(w != 0 && w != tlasWidth)throw std::logic_error("BLAS and TLAS widths must match (BLAS2+TLAS2 or BLAS4+TLAS4)");
+                if(w != 0 && w != tlasWidth)throw std::logic_error("BLAS and TLAS widths must match (BLAS2+TLAS2, BLAS4+TLAS4 or BLAS8+TLAS8)");
                 p->Lower(b, nullptr);
             }
             for(const auto& l : infiniteLights)l->Emit(b);

@@ -58,7 +58,7 @@ PT_API int emul_scene_commit(void* p, int width){
     EmulScene* e = (EmulScene*)p;
     int rc = pack_traversal(&e->s, width, e->P);
     if(rc != PT_OK)return rc;
-    e->D.n2 = e->P.n2.data(); e->D.n4 = e->P.n4.data(); e->D.tris = e->P.tris.data(); e->D.inst = e->P.insts.data();
+    e->D.n2 = e->P.n2.data(); e->D.n4 = e->P.n4.data(); e->D.n8 = e->P.n8.data(); e->D.tris = e->P.tris.data(); e->D.inst = e->P.insts.data();
     e->D.tlas_root = e->P.tlas_root; e->D.width = width;
     e->D.single_root = e->P.single_root; e->D.single_id = e->P.single_id;
     for(int a = 0; a < 3; a++){ e->D.tlo[a] = e->P.bounds.lo[a]; e->D.thi[a] = e->P.bounds.hi[a]; }
@@ -71,7 +71,7 @@ PT_API int emul_scene_bounds(void* p, float lo[3], float hi[3]){
     return PT_OK;
 }
 
-PT_API int emul_node_count(void* p){ EmulScene* e = (EmulScene*)p; return (int)(e->D.width == 2 ? e->P.n2.size() : e->P.n4.size()); }
+PT_API int emul_node_count(void* p){ EmulScene* e = (EmulScene*)p; return (int)(e->D.width == 2 ? e->P.n2.size() : e->D.width == 4 ? e->P.n4.size() : e->P.n8.size()); }
 
 PT_API int emul_trace_closest(void* p, const pt_ray* rays, size_t n, pt_hit* hits, uint32_t* inst, unsigned long long* stats){
     EmulScene* e = (EmulScene*)p;
@@ -83,7 +83,8 @@ PT_API int emul_trace_closest(void* p, const pt_ray* rays, size_t n, pt_hit* hit
             HitRec h;
             const float4* rb = reinterpret_cast<const float4*>(rays);
             if(D.width == 2)trace_scene<2, false, true>(D, rb, i, h, &cs[tid], NoAlpha());
-            else trace_scene<4, false, true>(D, rb, i, h, &cs[tid], NoAlpha());
+            else if(D.width == 4)trace_scene<4, false, true>(D, rb, i, h, &cs[tid], NoAlpha());
+            else trace_scene<8, false, true>(D, rb, i, h, &cs[tid], NoAlpha());
             hits[i].t = h.t; hits[i].u = h.u; hits[i].v = h.v; hits[i].prim = h.prim;
             if(inst)inst[i] = h.inst;
         }
@@ -107,7 +108,8 @@ PT_API int emul_trace_any(void* p, const pt_ray* rays, size_t n, uint8_t* occ){
             HitRec h;
             const float4* rb = reinterpret_cast<const float4*>(rays);
             bool o = D.width == 2 ? trace_scene<2, true, false>(D, rb, i, h, nullptr, NoAlpha())
-                                  : trace_scene<4, true, false>(D, rb, i, h, nullptr, NoAlpha());
+                   : D.width == 4 ? trace_scene<4, true, false>(D, rb, i, h, nullptr, NoAlpha())
+                                  : trace_scene<8, true, false>(D, rb, i, h, nullptr, NoAlpha());
             occ[i] = o ? 1 : 0;
         }
     };
@@ -142,7 +144,8 @@ PT_API int emul_unit_shade(void* p, const pt_ray* rays, size_t n, const float* i
         for(int k = 0; k < stride; k++)o[k] = 0.0f;
         HitRec h;
         const bool hit = e->D.width == 2 ? trace_scene<2, false, false>(e->D, rb, i, h, nullptr, NoAlpha())
-                                         : trace_scene<4, false, false>(e->D, rb, i, h, nullptr, NoAlpha());
+                       : e->D.width == 4 ? trace_scene<4, false, false>(e->D, rb, i, h, nullptr, NoAlpha())
+                                         : trace_scene<8, false, false>(e->D, rb, i, h, nullptr, NoAlpha());
         if(!hit)continue;
         const V3 ro = v3(rays[i].ox, rays[i].oy, rays[i].oz), rd = v3(rays[i].dx, rays[i].dy, rays[i].dz);
         SurfInt si;

@@ -27,20 +27,20 @@ def _cmp(desc, width, n_rays=40000, tmax=np.inf, seed=7):
 
 
 @needs_ref
-@pytest.mark.parametrize("width", [2, 4])
+@pytest.mark.parametrize("width", [2, 4, 8])
 @pytest.mark.parametrize("opaque", [False, True])
 def test_soup_bit_exact(width, opaque):
     assert _cmp(synth.soup_scene(20000, opaque=opaque), width) > 0.05
 
 
 @needs_ref
-@pytest.mark.parametrize("width", [2, 4])
+@pytest.mark.parametrize("width", [2, 4, 8])
 def test_terrain_bit_exact(width):
     assert _cmp(synth.terrain_scene(101, 81), width) > 0.2
 
 
 @needs_ref
-@pytest.mark.parametrize("width", [2, 4])
+@pytest.mark.parametrize("width", [2, 4, 8])
 def test_instances_bit_exact(width):
     d = synth.instanced_scene(2, 16)
     assert _cmp(d, width) > 0.1
@@ -48,7 +48,7 @@ def test_instances_bit_exact(width):
 
 
 @needs_ref
-@pytest.mark.parametrize("width", [2, 4])
+@pytest.mark.parametrize("width", [2, 4, 8])
 @pytest.mark.parametrize("n", [1, 2, 3, 5])
 def test_tiny_blas(width, n):
     """root is a leaf (n<=2) or a partially filled cluster"""
@@ -70,7 +70,7 @@ def test_degenerate_identical_triangles():
     d.instance(d.add_blas([d.mesh(pos, idx, material=m)]))
     from emulapi import EmulScene
     from oracle.refapi import RefScene
-    for width in (2, 4):
+    for width in (2, 4, 8):
         ref, em = RefScene(d, width, id_mode=True), EmulScene(d, width)
         rays = synth.random_rays(2000, (-0.5, -0.5, -1), (1.5, 1.5, 1))
         rh, _ = ref.trace_closest(rays)

@@ -31,7 +31,7 @@ def _cmp(desc, width, n_rays=200000, tmax=np.inf, seed=7):
 
 
 @needs_ref
-@pytest.mark.parametrize("width", [2, 4])
+@pytest.mark.parametrize("width", [2, 4, 8])
 @pytest.mark.parametrize("opaque", [False, True])
 def test_soup_bit_exact(width, opaque):
     rh = _cmp(synth.soup_scene(100000, opaque=opaque), width)
@@ -39,13 +39,13 @@ def test_soup_bit_exact(width, opaque):
 
 
 @needs_ref
-@pytest.mark.parametrize("width", [2, 4])
+@pytest.mark.parametrize("width", [2, 4, 8])
 def test_terrain_bit_exact(width):
     _cmp(synth.terrain_scene(301, 201), width)
 
 
 @needs_ref
-@pytest.mark.parametrize("width", [2, 4])
+@pytest.mark.parametrize("width", [2, 4, 8])
 def test_instances_bit_exact(width):
     d = synth.instanced_scene(3, 24)
     _cmp(d, width, n_rays=100000)
@@ -53,14 +53,14 @@ def test_instances_bit_exact(width):
 
 
 @needs_ref
-@pytest.mark.parametrize("width", [2, 4])
+@pytest.mark.parametrize("width", [2, 4, 8])
 @pytest.mark.parametrize("n", [1, 2, 3, 5])
 def test_tiny_blas(width, n):
     _cmp(synth.soup_scene(n, seed=5), width, n_rays=3000)
 
 
 @needs_ref
-@pytest.mark.parametrize("width", [2, 4])
+@pytest.mark.parametrize("width", [2, 4, 8])
 def test_against_default_release_build(width):
     """Reference compiled with its own Release flags contracts mul+add into FMA; ids must
     still agree except for near-ties, t within a few ulp."""
@@ -159,7 +159,7 @@ def _alpha_rays(n, seed=3):
 
 
 @needs_ref
-@pytest.mark.parametrize("width", [2, 4])
+@pytest.mark.parametrize("width", [2, 4, 8])
 @pytest.mark.parametrize("four_channel", [False, True])
 def test_alpha_mask_inside_traversal_bit_exact(width, four_channel):
     """AlphaMode::Mask is deterministic: rejected candidates let the ray continue to exactly the hit the

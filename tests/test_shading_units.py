@@ -84,7 +84,7 @@ def _close(x, y, rtol, atol, what, frac=0.0):
 
 
 @needs_ref
-@pytest.mark.parametrize("width", [2, 4])
+@pytest.mark.parametrize("width", [2, 4, 8])
 def test_surface_interaction_and_materials(libs, width):
     """Shape.cpp:205-243 + Primitive.cpp:20-24,54-63 (p, n, ns, tangent, uv incl. normal maps and instance
     transforms) and Material::{scatter, calc_attenuation, PDF} of all four material classes."""
