@@ -132,6 +132,22 @@ typedef struct pt_mesh_desc {
     int32_t material, emissive_tex, medium;
 } pt_mesh_desc;
 
+/* An analytic shape placed directly in the TLAS: GeometricPrimitive(shape, material, areaLight, medium)
+ * handed to Scene::Add (Primitive.hpp:17-33, examples/example_1.cpp:37-66) with a SphereShape
+ * (Shape.hpp:21-45, Shape.cpp:3-81) or a QuadShape (Shape.hpp:118-175, Shape.cpp:316-359).          */
+typedef enum pt_shape_kind { PT_SHAPE_SPHERE = 0, PT_SHAPE_QUAD = 1 } pt_shape_kind;
+
+typedef struct pt_shape_desc {
+    int32_t kind;           /* pt_shape_kind */
+    float p[3];             /* SPHERE: center; QUAD: origin Q */
+    float u[3], v[3];       /* QUAD: edge vectors */
+    float radius;           /* SPHERE */
+    int32_t material;       /* -1: medium boundary (Integrators.cpp:228-232) */
+    int32_t medium;         /* -1: none */
+    int32_t emissive_tex;   /* >= 0: the primitive carries AreaLight(shape, texture, one_sided) (Light.hpp:179-206) */
+    int32_t one_sided;
+} pt_shape_desc;
+
 typedef enum pt_light_kind {
     PT_LIGHT_UNIFORM_INFINITE = 0, /* UniformInfiniteLight  Light.cpp:27-50   */
     PT_LIGHT_GRADIENT_INFINITE = 1,/* FunctionInfiniteLight Light.cpp:53-108 with
@@ -172,6 +188,9 @@ PT_API int pt_scene_add_blas(pt_scene*, const int32_t* mesh_ids, int n_meshes);
 /* transform: column-major 4x4 (glm::mat4) -> TransformedPrimitive
  * (Primitive.hpp:37-50); NULL -> the BLAS itself is the TLAS primitive.      */
 PT_API int pt_scene_add_instance(pt_scene*, int blas_id, const float* transform16);
+/* returns the primitive's id in the same sequence as pt_scene_add_instance (Scene::Add order).
+ * A hit on a shape reports prim = 0 and inst = this id; u, v = the quad's (alpha, beta), 0 for a sphere. */
+PT_API int pt_scene_add_shape(pt_scene*, const pt_shape_desc*);
 PT_API int pt_scene_add_light(pt_scene*, const pt_light_desc*);
 PT_API int pt_scene_set_medium(pt_scene*, int medium_id); /* Scene::SetMedium  */
 

@@ -43,7 +43,7 @@ struct RefMesh {
 };
 
 struct RefBlasDesc { std::vector<int> meshes; };
-struct RefInstDesc { int blas; bool has_xf; glm::mat4 xf; };
+struct RefInstDesc { int blas; bool has_xf; glm::mat4 xf; pt_shape_desc shape; };   // blas < 0: an analytic shape
 
 struct RefScene {
     std::vector<std::shared_ptr<Texture>> textures;
@@ -66,6 +66,7 @@ struct RefScene {
     std::vector<std::shared_ptr<Light>> allLights;       // what was handed to lightSampler->Add, in order
     int width = 0;
     bool idMode = false;
+    bool hasShapes = false;
 };
 
 std::function<float(float)> powerFunc(int k){
@@ -281,6 +282,16 @@ PT_API int ref_scene_add_instance(void* p, int blas, const float* xf){
     return (int)s->instDescs.size() - 1;
 }
 
+// GeometricPrimitive(shape, material, areaLight, medium) handed to Scene::Add (examples/example_1.cpp:37-66)
+PT_API int ref_scene_add_shape(void* p, const pt_shape_desc* d){
+    RefScene* s = static_cast<RefScene*>(p);
+    RefInstDesc i;
+    i.blas = -1; i.has_xf = false; i.shape = *d;
+    s->instDescs.push_back(i);
+    s->hasShapes = true;
+    return (int)s->instDescs.size() - 1;
+}
+
 PT_API int ref_scene_add_light(void* p, const pt_light_desc* d){
     RefScene* s = static_cast<RefScene*>(p);
     s->lightDescs.push_back(*d);
@@ -332,6 +343,16 @@ PT_API int ref_scene_commit(void* p, int bvh_width, int light_sampler, int id_mo
     std::shared_ptr<Medium> sceneMed = s->sceneMedium >= 0 ? s->media[s->sceneMedium] : nullptr;
     s->scene = std::make_shared<Scene>(sceneMed);
     for(const RefInstDesc& i : s->instDescs){
+        if(i.blas < 0){
+            const pt_shape_desc& d = i.shape;
+            std::shared_ptr<Shape> shape;
+            if(d.kind == PT_SHAPE_SPHERE)shape = std::make_shared<SphereShape>(glm::vec3(d.p[0], d.p[1], d.p[2]), d.radius);
+            else shape = std::make_shared<QuadShape>(glm::vec3(d.p[0], d.p[1], d.p[2]), glm::vec3(d.u[0], d.u[1], d.u[2]), glm::vec3(d.v[0], d.v[1], d.v[2]));
+            std::shared_ptr<AreaLight> area = d.emissive_tex >= 0 ? std::make_shared<AreaLight>(shape, s->textures.at(d.emissive_tex), d.one_sided != 0) : nullptr;
+            s->topLevel.push_back(std::make_shared<GeometricPrimitive>(shape, d.material >= 0 ? s->materials.at(d.material) : nullptr, area,
+                                                                       d.medium >= 0 ? s->media.at(d.medium) : nullptr));
+            continue;
+        }
         std::shared_ptr<Primitive> prim = s->blas.at(i.blas);
         if(i.has_xf)prim = std::make_shared<TransformedPrimitive>(prim, i.xf);
         s->topLevel.push_back(prim);
@@ -412,20 +433,26 @@ PT_API int ref_trace_closest(void* p, const pt_ray* rays, size_t n, pt_hit* hits
                 if(inst)inst[i] = PT_MISS;
             } else{
                 h.t = si.t;
-                if(s->idMode){
+                uint32_t best = PT_MISS;
+                if(inst || s->hasShapes){
+                    float max = r.tmax;
+                    for(size_t k = 0;k < s->topLevel.size();k++){
+                        SurfaceInteraction tmp;
+                        if(s->topLevel[k]->Intersect(ray, tmp, max)){ max = tmp.t; best = (uint32_t)k; }
+                    }
+                    if(inst)inst[i] = best;
+                }
+                if(best != PT_MISS && s->instDescs[best].blas < 0){
+                    // a sphere / quad: prim 0; u, v = the quad's (alpha, beta), 0 for a sphere (include/pt_b200.h)
+                    h.prim = 0;
+                    h.u = s->instDescs[best].shape.kind == PT_SHAPE_QUAD ? si.uv.x : 0.0f;
+                    h.v = s->instDescs[best].shape.kind == PT_SHAPE_QUAD ? si.uv.y : 0.0f;
+                } else if(s->idMode){
                     uint32_t lo = (uint32_t)std::lround(si.uv.x), hi = (uint32_t)std::lround(si.uv.y);
                     h.prim = lo | (hi << 12);
                     h.u = h.v = std::numeric_limits<float>::quiet_NaN();
                 } else{
                     h.prim = PT_MISS - 1; h.u = si.uv.x; h.v = si.uv.y;
-                }
-                if(inst){
-                    float max = r.tmax; uint32_t best = PT_MISS;
-                    for(size_t k = 0;k < s->topLevel.size();k++){
-                        SurfaceInteraction tmp;
-                        if(s->topLevel[k]->Intersect(ray, tmp, max)){ max = tmp.t; best = (uint32_t)k; }
-                    }
-                    inst[i] = best;
                 }
             }
             hits[i] = h;

@@ -13,7 +13,7 @@ from pathlib import Path
 import numpy as np
 
 from pathtracing_b200 import capi
-from pathtracing_b200.capi import (pt_camera_desc, pt_light_desc, pt_material_desc, pt_medium_desc, pt_mesh_desc,
+from pathtracing_b200.capi import (pt_camera_desc, pt_light_desc, pt_material_desc, pt_medium_desc, pt_mesh_desc, pt_shape_desc,
                                    pt_render_params, pt_texture_desc)
 
 _DIR = Path(__file__).resolve().parent
@@ -45,7 +45,7 @@ def load(flavour="strict") -> C.CDLL:
     lib.ref_hardware_threads.restype = i
     for name, desc in (("ref_scene_add_texture", pt_texture_desc), ("ref_scene_add_material", pt_material_desc),
                        ("ref_scene_add_medium", pt_medium_desc), ("ref_scene_add_mesh", pt_mesh_desc),
-                       ("ref_scene_add_light", pt_light_desc)):
+                       ("ref_scene_add_light", pt_light_desc), ("ref_scene_add_shape", pt_shape_desc)):
         f = getattr(lib, name)
         f.restype = i
         f.argtypes = [vp, C.POINTER(desc)]
@@ -110,6 +110,9 @@ class RefScene:
     def add_instance(self, blas_id, xf):
         p = xf.ctypes.data_as(C.POINTER(C.c_float)) if xf is not None else None
         return self._ck(self.lib.ref_scene_add_instance(self.h, blas_id, p))
+
+    def add_shape(self, d):
+        return self._ck(self.lib.ref_scene_add_shape(self.h, C.byref(d)))
 
     def add_light(self, d):
         return self._ck(self.lib.ref_scene_add_light(self.h, C.byref(d)))

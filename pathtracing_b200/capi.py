@@ -47,6 +47,12 @@ class pt_mesh_desc(C.Structure):
                 ("material", C.c_int32), ("emissive_tex", C.c_int32), ("medium", C.c_int32)]
 
 
+class pt_shape_desc(C.Structure):
+    _fields_ = [("kind", C.c_int32), ("p", C.c_float * 3), ("u", C.c_float * 3), ("v", C.c_float * 3),
+                ("radius", C.c_float), ("material", C.c_int32), ("medium", C.c_int32),
+                ("emissive_tex", C.c_int32), ("one_sided", C.c_int32)]
+
+
 class pt_light_desc(C.Structure):
     _fields_ = [("kind", C.c_int32), ("color", C.c_float * 3), ("color_b", C.c_float * 3),
                 ("scale", C.c_float), ("dir_or_pos", C.c_float * 3), ("tex", C.c_int32),
@@ -87,12 +93,13 @@ MAT_DIFFUSE, MAT_DIELECTRIC, MAT_THIN_DIELECTRIC, MAT_CONDUCTOR = range(4)
 ALPHA_OPAQUE, ALPHA_BLEND, ALPHA_MASK = range(3)
 LIGHT_UNIFORM_INFINITE, LIGHT_GRADIENT_INFINITE, LIGHT_TEXTURE_INFINITE, LIGHT_DISTANT, LIGHT_POINT = range(5)
 INTEGRATOR_SIMPLE, INTEGRATOR_PATH, INTEGRATOR_VOLPATH = range(3)
+SHAPE_SPHERE, SHAPE_QUAD = range(2)
 FILTER_BOX, FILTER_GAUSSIAN, FILTER_MITCHELL, FILTER_LANCZOS = range(4)
 
 EXPORTS = [
     "pt_device_count", "pt_scene_create", "pt_scene_destroy", "pt_last_error",
     "pt_scene_add_texture", "pt_scene_add_material", "pt_scene_add_medium", "pt_scene_add_mesh",
-    "pt_scene_add_blas", "pt_scene_add_instance", "pt_scene_add_light", "pt_scene_set_medium",
+    "pt_scene_add_blas", "pt_scene_add_instance", "pt_scene_add_shape", "pt_scene_add_light", "pt_scene_set_medium",
     "pt_scene_commit", "pt_scene_bounds", "pt_trace_closest", "pt_trace_any",
     "pt_trace_closest_dev", "pt_trace_any_dev", "pt_trace_closest_stats", "pt_render",
     "pt_film_device_ptr", "pt_film_download", "pt_film_download_sumsq", "pt_film_upload",
@@ -123,7 +130,7 @@ def load_library(path: os.PathLike | None = None) -> C.CDLL:
     lib.pt_last_error.restype = C.c_char_p
     for name, desc in (("pt_scene_add_texture", pt_texture_desc), ("pt_scene_add_material", pt_material_desc),
                        ("pt_scene_add_medium", pt_medium_desc), ("pt_scene_add_mesh", pt_mesh_desc),
-                       ("pt_scene_add_light", pt_light_desc)):
+                       ("pt_scene_add_light", pt_light_desc), ("pt_scene_add_shape", pt_shape_desc)):
         f = getattr(lib, name)
         f.restype = i
         f.argtypes = [vp, C.POINTER(desc)]

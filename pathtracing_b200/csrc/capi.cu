@@ -74,6 +74,11 @@ int pt_scene_add_instance(pt_scene* s, int blas_id, const float* xf){
     return scene_add_instance(s, blas_id, xf);
 }
 
+int pt_scene_add_shape(pt_scene* s, const pt_shape_desc* d){
+    PT_CHECK_OPEN(s);
+    return scene_add_shape(s, d);
+}
+
 int pt_scene_add_light(pt_scene* s, const pt_light_desc* d){
     PT_CHECK_OPEN(s);
     return scene_add_light(s, d);

@@ -89,6 +89,8 @@ struct alignas(16) Instance {
 static_assert(sizeof(Instance) == 96, "Instance must be 96 B");
 constexpr uint32_t INST_LAST = 1u;
 constexpr uint32_t INST_XF = 2u;         // TransformedPrimitive (Primitive.cpp:41-66)
+constexpr uint32_t INST_SPHERE = 4u;     // not a BLAS: GeometricPrimitive(SphereShape), constants packed in the record (scene_build.cpp pack_shape)
+constexpr uint32_t INST_QUAD = 8u;       // GeometricPrimitive(QuadShape)
 
 // Everything a traversal kernel needs, passed by value as a kernel argument.
 struct DevScene {

@@ -24,6 +24,8 @@
 #include "shade_mat.cuh"
 #include "shade_light.cuh"
 #include "camera.cuh"
+#include "trace.cuh"
+#include "alpha.cuh"
 
 namespace ptb {
 
@@ -56,6 +58,7 @@ struct BatchInfo {     // how a sample id maps to (pixel, sample index): id = pa
     // -> pixel list[j], sample index sample_base + k
     const uint32_t* list;
     uint32_t n_list, sample_base;
+    int tr_walk;           // VolPath in a scene with material-less medium boundaries: shadow rays take the IntersectTr walk
 };
 
 __device__ __forceinline__ uint64_t stream_of(const BatchInfo& B, uint64_t g, uint32_t& pixel, uint32_t& sample){
@@ -138,6 +141,54 @@ __global__ void __launch_bounds__(256) k_connect(Arena A, uint32_t n){
     float4 r = A.rad[slot];
     r.x += c.x; r.y += c.y; r.z += c.z;
     A.rad[slot] = r;
+}
+
+// ---- connect through medium boundaries: Scene::IntersectTr (Scene.cpp:8-29) ---------------------------
+// VolPathIntegrator::SampleLd (Integrators.cpp:466) does not ask "is anything in the way" but walks the
+// shadow ray with closest hits: a primitive without a material (a medium boundary) lets it through and
+// switches the medium, transmittance is collected per segment, the first primitive WITH a material blocks.
+// One lane walks one shadow ray start to end (whole-ray traversal, local stack): only scenes that hold
+// such boundaries take this path, everything else keeps the any-hit kernel + k_connect.
+template <int WIDTH, class Alpha>
+__global__ void __launch_bounds__(128) k_shadow_tr(Arena A, DevScene D, ShadeScene S, uint32_t n, Alpha alpha){
+    const uint32_t k = blockIdx.x * blockDim.x + threadIdx.x;
+    if(k >= n)return;
+    RayRegs ray; ray.a = A.srays[2 * (size_t)k]; ray.b = A.srays[2 * (size_t)k + 1];
+    const float4 c = A.scontrib[k];
+    int med = __float_as_int(c.w);
+    const V3 d = v3(ray.b.x, ray.b.y, ray.b.z);
+    V3 tr = v3(1.0f);
+    bool blocked = false;
+    for(int seg = 0; seg < 256 && ray.a.w > 0.0f; seg++){
+        HitRec h;
+        if(!trace_scene<WIDTH, false, false>(D, ray, k, h, nullptr, alpha)){
+            if(med >= 0)tr *= medium_Tr(S.media[med], ray.a.w);
+            break;
+        }
+        if(med >= 0)tr *= medium_Tr(S.media[med], h.t);
+        SurfInt si;
+        const V3 o = v3(ray.a.x, ray.a.y, ray.a.z);
+        build_interaction(S, o, d, h.t, h.u, h.v, h.prim, h.inst, si);
+        if(si.mat >= 0){ blocked = true; break; }
+        const V3 q = o + h.t * d;
+        med = dot(d, si.n) < 0.0f ? si.medium : -1;                   // interaction.getMedium(ray.dir)
+        ray.a = make_float4(q.x, q.y, q.z, ray.a.w - h.t);
+    }
+    if(blocked)return;
+    const uint32_t slot = A.sslot[k];
+    float4 r = A.rad[slot];
+    r.x += c.x * tr.x; r.y += c.y * tr.y; r.z += c.z * tr.z;
+    A.rad[slot] = r;
+}
+
+template <class Alpha>
+static void launch_shadow_tr(const Arena& A, const pt_scene* s, uint32_t n, cudaStream_t st, const Alpha& alpha){
+    const unsigned grid = (n + 127) / 128;
+    switch(s->dev.width){
+    case 2: k_shadow_tr<2><<<grid, 128, 0, st>>>(A, s->dev, s->shade, n, alpha); break;
+    case 4: k_shadow_tr<4><<<grid, 128, 0, st>>>(A, s->dev, s->shade, n, alpha); break;
+    default: k_shadow_tr<8><<<grid, 128, 0, st>>>(A, s->dev, s->shade, n, alpha); break;
+    }
 }
 
 // ---- film: FilmTile::Add + Film::Merge (Film.hpp:65-82,125-132) ------------------------------
@@ -245,14 +296,14 @@ __global__ void __launch_bounds__(256) k_adapt(const double* __restrict__ est, c
 
 // ---- shade: one bounce of Li() for every queue entry ------------------------------------------
 
-struct NeeOut { bool want; V3 o, d; float tmax; V3 contrib; };
+struct NeeOut { bool want; V3 o, d; float tmax; V3 contrib; int medium; };
 
 // PathIntegrator::SampleLd (Integrators.cpp:260-294) / VolPathIntegrator::SampleLd (:426-479) up to the
 // visibility test, which the connect stage resolves.  `medium_pt`: the interaction is a medium event.
 template <int INTEG>
 __device__ inline void sample_ld(const ShadeScene& S, const SurfInt& si, const MatCtx& mc, bool medium_pt, V3 ip, V3 rd, float hg_g, int cur_medium,
-                                 float u_sel, float ux, float uy, Pcg& rng, NeeOut& out){
-    out.want = false;
+                                 float u_sel, float ux, float uy, Pcg& rng, bool tr_walk, NeeOut& out){
+    out.want = false; out.medium = cur_medium;
     const int li = pick_light(S, u_sel);
     if(li < 0)return;
     const DevLight& L = S.lights[li];
@@ -287,7 +338,7 @@ __device__ inline void sample_ld(const ShadeScene& S, const SurfInt& si, const M
         const float w2 = pmf * pmf, w1 = spdf * spdf;
         c = light_L_sampled(S, L, ls, sd) * f * (w2 / (w1 + w2)) / pmf;
     }
-    if(INTEG == PT_INTEGRATOR_VOLPATH && cur_medium >= 0)c = c * medium_Tr(S.media[cur_medium], t);   // Scene::IntersectTr, miss leg (Scene.cpp:13-17)
+    if(INTEG == PT_INTEGRATOR_VOLPATH && cur_medium >= 0 && !tr_walk)c = c * medium_Tr(S.media[cur_medium], t);   // Scene::IntersectTr, miss leg (Scene.cpp:13-17)
     out.want = true; out.o = ip; out.d = sd; out.tmax = t; out.contrib = c;
 }
 
@@ -354,7 +405,7 @@ __global__ void __launch_bounds__(128) k_shade(Arena A, ShadeScene S, BatchInfo 
                 // medium event (Integrators.cpp:356-362)
                 const DevMedium& M = S.media[medium];
                 const V3 mp = ro + med_dist * rd;
-                sample_ld<INTEG>(S, si, mc, true, mp, rd, M.g, medium, r[5], r[2], r[3], g, ne);
+                sample_ld<INTEG>(S, si, mc, true, mp, rd, M.g, medium, r[5], r[2], r[3], g, B.tr_walk != 0, ne);
                 if(ne.want)ne.contrib = att * ne.contrib;
                 outp += att * ld3(M.Le);
                 no = mp; nd = hg_sample(M.g, rd, r[6], r[7]);
@@ -364,12 +415,12 @@ __global__ void __launch_bounds__(128) k_shade(Arena A, ShadeScene S, BatchInfo 
                 // emitted radiance with MIS against NEE (Integrators.cpp:153-156, 217-226, 364-373)
                 if(si.light >= 0){
                     const DevLight& L = S.lights[si.light];
-                    const V3 le = tex_eval(S, L.tex, si.u, si.v, si.ns);          // AreaLight::L, two-sided
+                    const V3 le = area_L(S, L, si.n, si.ns, si.u, si.v, rd);      // AreaLight::L
                     if(!is_zero(le)){
                         if(INTEG == PT_INTEGRATOR_SIMPLE || spec)outp += att * le;
                         else if(prev_pdf > 0.0f){
                             // PMF and PDF of interaction.AreaLight: the inner, untransformed light, world-space p / n
-                            const float lp = L.pmf_hit * tri_pdf(si.p, si.n, ro, rd, L.area);
+                            const float lp = L.pmf_hit * area_pdf(L, si.p, si.n, ro, rd);
                             outp += att * le * (prev_pdf * prev_pdf / (prev_pdf * prev_pdf + lp * lp));
                         }
                     }
@@ -394,7 +445,7 @@ __global__ void __launch_bounds__(128) k_shade(Arena A, ShadeScene S, BatchInfo 
                         if(INTEG != PT_INTEGRATOR_SIMPLE){
                             spec = (sc.flags & BX_SPECULAR) != 0;
                             if(!spec){
-                                sample_ld<INTEG>(S, si, mc, false, si.p, rd, 0.0f, ray_medium, r[5], r[2], r[3], g, ne);
+                                sample_ld<INTEG>(S, si, mc, false, si.p, rd, 0.0f, ray_medium, r[5], r[2], r[3], g, B.tr_walk != 0, ne);
                                 if(ne.want)ne.contrib = att * ne.contrib;
                                 prev_pdf = mat_pdf(mc, si, rd, sc.d);
                             }
@@ -436,7 +487,7 @@ __global__ void __launch_bounds__(128) k_shade(Arena A, ShadeScene S, BatchInfo 
         A.srays[2 * (size_t)qs] = make_float4(ne.o.x, ne.o.y, ne.o.z, ne.tmax);
         A.srays[2 * (size_t)qs + 1] = make_float4(ne.d.x, ne.d.y, ne.d.z, ntime);
         A.sslot[qs] = slot;
-        A.scontrib[qs] = make_float4(ne.contrib.x, ne.contrib.y, ne.contrib.z, 0.0f);
+        A.scontrib[qs] = make_float4(ne.contrib.x, ne.contrib.y, ne.contrib.z, __int_as_float(ne.medium));
     }
 }
 
@@ -594,6 +645,7 @@ int render_passes(pt_scene* s, const pt_camera_desc* cam, const pt_render_params
     // paths ended in a shade pass are splatted and handed to the next camera samples straight away, so the
     // long tail of deep paths is paid once per call and not once per batch.
     double host_wait_s = 0.0; unsigned iterations = 0;
+    const bool tr_walk = rp->integrator == PT_INTEGRATOR_VOLPATH && s->has_boundary;
     StageLog log; log.on = getenv("PTB_PROFILE") != nullptr; log.st = st;
     log.mark(0);
     const auto t_host0 = std::chrono::steady_clock::now();
@@ -602,6 +654,7 @@ int render_passes(pt_scene* s, const pt_camera_desc* cam, const pt_render_params
         B.W = W; B.H = H; B.pass_begin = rp->pass_begin; B.pass_stride = rp->pass_stride; B.max_depth = rp->max_depth; B.seed = rp->seed;
         B.sampler = rp->sampler; B.sx = rp->strata_x; B.sy = rp->strata_y;
         B.list = list; B.n_list = n_list; B.sample_base = sample_base;
+        B.tr_walk = tr_walk ? 1 : 0;
         uint64_t next_gid = 0;
         if(rp->max_depth <= 0){
             // `depth++ < maxDepth` fails at once: black samples that still carry their filter weight
@@ -639,7 +692,12 @@ int render_passes(pt_scene* s, const pt_camera_desc* cam, const pt_render_params
             iterations++;
             log.mark(4);
             const uint32_t n_next = h_counters[0], n_sh = h_counters[1], n_done = h_counters[2];
-            if(n_sh > 0){
+            if(n_sh > 0 && tr_walk){
+                if(s->has_alpha_tex)launch_shadow_tr(A, s, n_sh, st, AlphaTex { s->shade, s->alpha_salt += 0x9E3779B97F4A7C15ull });
+                else launch_shadow_tr(A, s, n_sh, st, NoAlpha());
+                R.shadow_rays += n_sh; R.kernel_launches++;
+                log.mark(5);
+            } else if(n_sh > 0){
                 rc = launch_trace_any(s, A.srays, n_sh, A.socc, st);
                 if(rc != PT_OK)return rc;
                 k_connect<<<(n_sh + 255) / 256, 256, 0, st>>>(A, n_sh);

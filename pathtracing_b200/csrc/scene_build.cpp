@@ -1,6 +1,7 @@
 // scene_build.cpp — host-only half of the scene object: validation of the POD
 // description and packing of BLAS/TLAS into the device layout (no CUDA calls,
 // so the same code is exercised by the CPU-side emulation tests).
+#include <cmath>
 #include <cstring>
 
 #include "scene_host.hpp"
@@ -98,6 +99,20 @@ int scene_add_instance(pt_scene* s, int blas_id, const float* xf){
     memset(i.xf, 0, sizeof i.xf);
     if(xf)memcpy(i.xf, xf, sizeof i.xf);
     else i.xf[0] = i.xf[5] = i.xf[10] = i.xf[15] = 1.0f;
+    memset(&i.shape, 0, sizeof i.shape);
+    s->instances.push_back(i);
+    return (int)s->instances.size() - 1;
+}
+
+int scene_add_shape(pt_scene* s, const pt_shape_desc* d){
+    if(!d || (d->kind != PT_SHAPE_SPHERE && d->kind != PT_SHAPE_QUAD)){ set_error("bad shape"); return PT_ERR_INVALID; }
+    if(d->material >= (int)s->materials.size() || d->emissive_tex >= (int)s->textures.size() || d->medium >= (int)s->media.size()){ set_error("shape material/texture/medium id out of range"); return PT_ERR_INVALID; }
+    if(d->kind == PT_SHAPE_SPHERE && !(d->radius > 0.0f)){ set_error("sphere radius must be positive"); return PT_ERR_INVALID; }
+    HostInstance i;
+    i.blas = -1; i.has_xf = false;
+    memset(i.xf, 0, sizeof i.xf);
+    i.xf[0] = i.xf[5] = i.xf[10] = i.xf[15] = 1.0f;
+    i.shape = *d;
     s->instances.push_back(i);
     return (int)s->instances.size() - 1;
 }
@@ -121,6 +136,54 @@ static bool texture_alpha_below_one(const pt_scene* s, int tex, int depth){
     return false;
 }
 
+// TRI_ALPHA_* flags of a material: HasAlpha() (Material.hpp:330-332) and whether Alpha() can ever reject
+static uint32_t material_alpha_flags(const pt_scene* s, int mat){
+    if(mat < 0)return 0u;
+    const pt_material_desc& md = s->materials[mat];
+    const bool tester = md.kind == PT_MAT_DIFFUSE || md.kind == PT_MAT_DIELECTRIC;
+    if(!tester || md.alpha_mode == PT_ALPHA_OPAQUE)return 0u;
+    bool can_be_transparent = md.alpha >= 0;
+    if(!can_be_transparent && md.tex >= 0)can_be_transparent = texture_alpha_below_one(s, md.tex, 0);
+    return TRI_ALPHA_PATH | (can_be_transparent ? TRI_ALPHA_TEX : 0u);
+}
+
+// SphereShape ctor (Shape.hpp:23-27) / QuadShape ctor (Shape.hpp:120-130): AABB::Expand over the same points
+static Box shape_box(const pt_shape_desc& d){
+    Box b = box_empty();
+    if(d.kind == PT_SHAPE_SPHERE){
+        const float lo[3] = { d.p[0] - d.radius, d.p[1] - d.radius, d.p[2] - d.radius }, hi[3] = { d.p[0] + d.radius, d.p[1] + d.radius, d.p[2] + d.radius };
+        box_grow(b, lo); box_grow(b, hi);
+    } else{
+        float a[3], c[3], e[3];
+        for(int k = 0; k < 3; k++){ a[k] = (d.p[k] + d.u[k]) + d.v[k]; c[k] = d.p[k] + d.u[k]; e[k] = d.p[k] + d.v[k]; }
+        box_grow(b, d.p); box_grow(b, a); box_grow(b, c); box_grow(b, e);
+    }
+    return b;
+}
+
+// The shape's constants in the 96 B instance record (pt_types.h): inv[0..11] and blo/bhi0 are reused.
+//  sphere: inv[0..2] center, inv[3] radius
+//  quad  : inv[0..2] Q, inv[3..5] u, inv[6..8] v, inv[9..11] normal, blo[0..2] w = n / dot(n, n), bhi0 = D = dot(normal, Q)
+static void pack_shape(const pt_shape_desc& d, Instance& I){
+    if(d.kind == PT_SHAPE_SPHERE){
+        I.flags = INST_SPHERE;
+        for(int k = 0; k < 3; k++)I.inv[k] = d.p[k];
+        I.inv[3] = d.radius;
+        return;
+    }
+    I.flags = INST_QUAD;
+    const float* u = d.u; const float* v = d.v;
+    const float n[3] = { u[1] * v[2] - v[1] * u[2], u[2] * v[0] - v[2] * u[0], u[0] * v[1] - v[0] * u[1] };   // glm::cross
+    const float nn = n[0] * n[0] + n[1] * n[1] + n[2] * n[2];
+    const float inv_len = 1.0f / std::sqrt(nn);                                                                 // glm::normalize = v * inversesqrt(dot)
+    for(int k = 0; k < 3; k++){
+        I.inv[k] = d.p[k]; I.inv[3 + k] = u[k]; I.inv[6 + k] = v[k];
+        I.inv[9 + k] = n[k] * inv_len;
+        I.blo[k] = n[k] / nn;
+    }
+    I.bhi0 = I.inv[9] * d.p[0] + I.inv[10] * d.p[1] + I.inv[11] * d.p[2];
+}
+
 int pack_traversal(pt_scene* s, int width, PackedTraversal& P){
     if(width != 2 && width != 4 && width != 8){ set_error("bvh_width must be 2, 4 or 8"); return PT_ERR_INVALID; }
     if(s->instances.empty()){ set_error("scene has no instances"); return PT_ERR_INVALID; }
@@ -142,17 +205,9 @@ int pack_traversal(pt_scene* s, int width, PackedTraversal& P){
         for(size_t k = 0; k < hb.meshes.size(); k++){
             const int mi = hb.meshes[k];
             const HostMesh& m = s->meshes[mi];
-            uint32_t flags = 0;
-            if(m.d.material >= 0){
-                const pt_material_desc& md = s->materials[m.d.material];
-                const bool tester = md.kind == PT_MAT_DIFFUSE || md.kind == PT_MAT_DIELECTRIC;
-                if(tester && md.alpha_mode != PT_ALPHA_OPAQUE){
-                    flags |= TRI_ALPHA_PATH;     // HasAlpha(), Material.hpp:330-332
-                    bool can_be_transparent = md.alpha >= 0;
-                    if(!can_be_transparent && md.tex >= 0)can_be_transparent = texture_alpha_below_one(s, md.tex, 0);
-                    if(can_be_transparent){ flags |= TRI_ALPHA_TEX; s->has_alpha_tex = true; }
-                }
-            }
+            const uint32_t flags = material_alpha_flags(s, m.d.material);
+            if(m.d.material < 0)s->has_boundary = true;
+            if(flags & TRI_ALPHA_TEX)s->has_alpha_tex = true;
             for(uint32_t t = 0; t < m.d.n_triangles; t++, g++){
                 const uint32_t i0 = m.idx[3 * (size_t)t], i1 = m.idx[3 * (size_t)t + 1], i2 = m.idx[3 * (size_t)t + 2];
                 const float* p0 = &m.pos[3 * (size_t)i0]; const float* p1 = &m.pos[3 * (size_t)i1]; const float* p2 = &m.pos[3 * (size_t)i2];
@@ -194,7 +249,12 @@ int pack_traversal(pt_scene* s, int width, PackedTraversal& P){
     std::vector<Box> iboxes(ni);
     for(uint32_t i = 0; i < ni; i++){
         const HostInstance& hi = s->instances[i];
-        if(hi.blas < 0 || hi.blas >= (int)s->blas.size()){ set_error("instance refers to an unknown BLAS"); return PT_ERR_INVALID; }
+        if(hi.blas < 0){
+            if(material_alpha_flags(s, hi.shape.material) & TRI_ALPHA_TEX){ set_error("alpha-tested materials on sphere / quad shapes are not supported"); return PT_ERR_INVALID; }
+            if(hi.shape.material < 0)s->has_boundary = true;
+            iboxes[i] = shape_box(hi.shape); continue;
+        }
+        if(hi.blas >= (int)s->blas.size()){ set_error("instance refers to an unknown BLAS"); return PT_ERR_INVALID; }
         const Box& bb = s->blas[hi.blas].bounds;
         iboxes[i] = hi.has_xf ? transform_box(hi.xf, bb) : bb;
     }
@@ -218,9 +278,15 @@ int pack_traversal(pt_scene* s, int width, PackedTraversal& P){
     for(uint32_t k = 0; k < ni; k++){
         const uint32_t id = tf.order[k];
         const HostInstance& hi = s->instances[id];
-        const HostBlas& hb = s->blas[hi.blas];
         Instance& I = insts[k];
         memset(&I, 0, sizeof I);
+        if(hi.blas < 0){
+            pack_shape(hi.shape, I);
+            I.flags |= tf.leaf_last[k] ? INST_LAST : 0u;
+            I.id = id;
+            continue;
+        }
+        const HostBlas& hb = s->blas[hi.blas];
         float inv[16];
         if(hi.has_xf)mat4_inverse(hi.xf, inv);   // TransformedPrimitive ctor, Primitive.hpp:40
         else{ memset(inv, 0, sizeof inv); inv[0] = inv[5] = inv[10] = inv[15] = 1.0f; }
@@ -233,7 +299,7 @@ int pack_traversal(pt_scene* s, int width, PackedTraversal& P){
         I.bhi0 = hb.bounds.hi[0]; I.bhi12[0] = hb.bounds.hi[1]; I.bhi12[1] = hb.bounds.hi[2];
     }
 
-    if(ni == 1 && !s->instances[0].has_xf){ P.single_root = s->blas[s->instances[0].blas].root; P.single_id = 0; }
+    if(ni == 1 && !s->instances[0].has_xf && s->instances[0].blas >= 0){ P.single_root = s->blas[s->instances[0].blas].root; P.single_id = 0; }
     P.tlas_root = trebase(tf.root);
     P.bounds = tf.bounds;
     P.inst_order = tf.order;

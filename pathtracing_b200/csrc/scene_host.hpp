@@ -36,10 +36,11 @@ struct HostBlas {
     std::vector<uint32_t> tri_mesh_base; // per mesh: first BLAS-wide triangle id
 };
 
-struct HostInstance {
-    int blas;
+struct HostInstance {        // one top-level primitive (Scene::Add order)
+    int blas;                // >= 0: a BLAS, optionally transformed; -1: an analytic shape
     bool has_xf;
     float xf[16];
+    pt_shape_desc shape;     // blas < 0
 };
 
 struct DeviceBuffers {
@@ -93,6 +94,7 @@ struct pt_scene {
     void* ev[4] = { nullptr, nullptr, nullptr, nullptr };
     unsigned cursor_next = 0;
     bool has_alpha_tex = false;   // some triangle carries TRI_ALPHA_TEX: traversal must evaluate Material::Alpha
+    bool has_boundary = false;    // some primitive has no material (a medium boundary): VolPath shadow rays walk through it
     uint64_t alpha_salt = 0;      // advances per launch (AlphaTester Blend draws)
 };
 
@@ -117,6 +119,7 @@ int scene_add_medium(pt_scene* s, const pt_medium_desc* d);
 int scene_add_mesh(pt_scene* s, const pt_mesh_desc* d);
 int scene_add_blas(pt_scene* s, const int32_t* mesh_ids, int n);
 int scene_add_instance(pt_scene* s, int blas_id, const float* xf);
+int scene_add_shape(pt_scene* s, const pt_shape_desc* d);
 int scene_add_light(pt_scene* s, const pt_light_desc* d);
 int pack_traversal(pt_scene* s, int width, PackedTraversal& out);
 

@@ -47,6 +47,25 @@ PT_HDI V3 sample_normal_map(const ShadeScene& S, int mat, V3 ns, V3 tangent, flo
 // stamping (Primitive.cpp:20-24) + TransformedPrimitive::Intersect's world transform (Primitive.cpp:54-63)
 PT_HDN void build_interaction(const ShadeScene& S, V3 ro, V3 rd, float t, float bu, float bv, uint32_t prim, uint32_t inst, SurfInt& si){
     const DevInstShade& I = S.inst[inst];
+    if(I.shape >= 0){
+        // SphereShape::Intersect (Shape.cpp:11-20) / QuadShape::Intersect (Shape.cpp:333-340)
+        const V3 at = ro + t * rd;
+        V3 ns, n;
+        if(I.shape == PT_SHAPE_SPHERE){
+            ns = normalize(at - ld3(I.fwd)); n = ns;
+            sphere_uv(n, si.u, si.v);
+        } else{
+            n = ld3(I.fwd + 9);
+            ns = dot(rd, n) > 0.0f ? -n : n;
+            si.u = bu; si.v = bv;
+        }
+        const V3 up = fabsf(ns.x) > 0.9999f ? v3(0, 1, 0) : v3(1, 0, 0);
+        si.tangent = normalize(cross(up, ns));
+        si.p = at + kEps * ns; si.n = n; si.ns = ns; si.t = t;
+        si.mat = I.material; si.medium = I.medium; si.emis_tex = -1;
+        si.light = I.light_base;
+        return;
+    }
     const DevBlasInfo bi = S.blas[I.blas];
     const uint32_t mesh = S.tri_mesh[bi.tri_base + prim];
     const DevMesh m = S.meshes[mesh];

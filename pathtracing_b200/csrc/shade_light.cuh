@@ -58,6 +58,23 @@ PT_HDN void light_sample(const ShadeScene& S, const DevLight& L, float ux, float
     }
     case DL_DISTANT: o.dir = normalize(ld3(L.v) + sphere_dir(ux, uy) * 0.02f); o.L = ld3(L.color); o.u = ux; o.v = uy; break;   // Light.cpp:208-215
     case DL_POINT: o.p = ld3(L.v); o.n = v3(1.0f); o.L = ld3(L.color); o.u = ux; o.v = uy; break;                             // Light.cpp:235-237
+    case DL_SPHERE: {                                                                            // SphereShape::Sample, Shape.cpp:73-81
+        const float* g = S.inst[L.inst].fwd;
+        const float z = 1.0f - 2.0f * ux;
+        const float r = sqrtf(1.0f - z * z);
+        const float phi = 2.0f * kPi * uy;
+        const V3 c = ld3(g);
+        o.p = c + g[3] * v3(r * cosf(phi), r * sinf(phi), z);
+        o.n = normalize(o.p - c);
+        sphere_uv(o.p, o.u, o.v);                      // GetSphereUV of the point, not of the normal
+        break;
+    }
+    case DL_QUAD: {                                                                              // QuadShape::Sample, Shape.hpp:139-141: uv stays (0,0)
+        const float* g = S.inst[L.inst].fwd;
+        o.p = ld3(g) + ux * ld3(g + 3) + uy * ld3(g + 6);
+        o.n = ld3(g + 9);
+        break;
+    }
     default: {
         // AreaLight::sample -> TriangleShape::Sample (Shape.cpp:277-297): no fold of u+v > 1
         V3 v0, v1, v2; uint32_t i0, i1, i2;
@@ -89,6 +106,24 @@ PT_HDI float tri_pdf(V3 p, V3 n, V3 ro, V3 rd, float area){
     return d2 / (c * area);
 }
 
+// AreaLight::PDF(interaction, ray) (Light.cpp:267-272) for the light on a hit or sampled point, world space:
+// TriangleShape::PDF (Shape.cpp:308-315), SphereShape::PDF (Shape.cpp:64-71), QuadShape::PDF (Shape.hpp:151-158)
+PT_HDI float area_pdf(const DevLight& L, V3 p, V3 n, V3 ro, V3 rd){
+    if(L.kind == DL_AREA)return tri_pdf(p, n, ro, rd, L.area);
+    if(L.one_sided && !(dot(-rd, n) > 0.0f))return 0.0f;
+    const V3 to = p - ro;
+    const float d2 = dot(to, to);
+    const float c = fabsf(dot(-rd, n));
+    if(L.kind == DL_SPHERE ? (L.area * c == 0.0f) : (L.area == 0.0f))return 0.0f;
+    return d2 / (c * L.area);
+}
+
+// AreaLight::L (Light.cpp:257-260)
+PT_HDI V3 area_L(const ShadeScene& S, const DevLight& L, V3 n, V3 ns, float u, float v, V3 rd){
+    if(L.one_sided && dot(rd, n) > 0.0f)return v3(0.0f);
+    return tex_eval(S, L.tex, u, v, ns);
+}
+
 // Light::PDF(interaction, ray) of the light object the sampler holds (TransformedLight for xf instances)
 PT_HDN float light_pdf_sampled(const ShadeScene& S, const DevLight& L, V3 p, V3 n, V3 ro, V3 rd){
     switch(L.kind){
@@ -98,6 +133,7 @@ PT_HDN float light_pdf_sampled(const ShadeScene& S, const DevLight& L, V3 p, V3 
         return (lum(inf_Le(S, L, rd)) / L.total_weight) * (1.0f / cell);
     }
     case DL_DISTANT: case DL_POINT: return 0.0f;
+    case DL_SPHERE: case DL_QUAD: return area_pdf(L, p, n, ro, rd);
     default: {
         const DevInstShade& I = S.inst[L.inst];
         if(I.has_xf){                                    // TransformedLight::PDF (Light.cpp:318-325)
@@ -113,6 +149,7 @@ PT_HDN float light_pdf_sampled(const ShadeScene& S, const DevLight& L, V3 p, V3 
 // Light::L(lightSample.interaction, shadow_ray) as SampleLd calls it on the sampled light
 __host__ __device__ inline V3 light_L_sampled(const ShadeScene& S, const DevLight& L, const LightSmp& ls, V3 rd){
     if(L.kind <= DL_TEXTURE_INF)return inf_Le(S, L, rd);
+    if(L.kind >= DL_SPHERE)return area_L(S, L, ls.n, v3(0.0f), ls.u, ls.v, rd);
     if(L.kind != DL_AREA)return v3(0.0f);
     // TransformedLight::L builds a fresh SurfaceInteraction: its uv is (0,0) (Light.cpp:300-305)
     if(S.inst[L.inst].has_xf)return tex_eval(S, L.tex, 0.0f, 0.0f, v3(0.0f));

@@ -8,7 +8,7 @@
 #include <thread>
 
 #include "shade_tables.hpp"
-#include "shade_math.cuh"
+#include "shade_light.cuh"
 
 namespace ptb {
 
@@ -77,6 +77,21 @@ static void build_geometry(pt_scene* s, ShadeTables& T){
     }
     for(const HostInstance& hi : s->instances){
         DevInstShade d {};
+        d.shape = -1; d.material = -1; d.medium = -1;
+        if(hi.blas < 0){
+            const pt_shape_desc& sd = hi.shape;
+            d.shape = sd.kind; d.material = sd.material; d.medium = sd.medium; d.light_base = -1;
+            for(int k = 0; k < 3; k++)d.fwd[k] = sd.p[k];
+            if(sd.kind == PT_SHAPE_SPHERE)d.fwd[3] = sd.radius;
+            else{
+                const V3 u = ld3(sd.u), v = ld3(sd.v);
+                const V3 n = normalize(cross(u, v));                      // QuadShape ctor, Shape.hpp:121-122
+                for(int k = 0; k < 3; k++){ d.fwd[3 + k] = sd.u[k]; d.fwd[6 + k] = sd.v[k]; }
+                d.fwd[9] = n.x; d.fwd[10] = n.y; d.fwd[11] = n.z;
+            }
+            T.inst.push_back(d);
+            continue;
+        }
         float inv[16], nm[9];
         mat4_inverse(hi.xf, inv);
         mat3_normal_matrix(hi.xf, nm);
@@ -146,6 +161,24 @@ static float area_light_power(const ShadeTables& T, const DevMesh& m, uint32_t t
     return (float)(2.0 * area * l);
 }
 
+// AreaLight::PreProcess for a sphere / quad light: (oneSided ? 1 : 2) * Area * luminance(mean emissive)
+static float shape_light_power(const ShadeTables& T, const DevLight& L, float& area_out){
+    const float* g = T.inst[L.inst].fwd;
+    const float area = L.kind == DL_SPHERE ? 4.0f * kPi * g[3] * g[3]                     // Shape.cpp:58-60
+                                           : length(cross(ld3(g + 3), ld3(g + 6)));       // Shape.hpp:143-145
+    area_out = area;
+    double acc[3] = { 0, 0, 0 };
+    Pcg unused {};
+    for(int j = 0; j < 16; j++)for(int i = 0; i < 16; i++){
+        LightSmp ls;
+        light_sample(T.view, L, (i + 0.5f) / 16.0f, (j + 0.5f) / 16.0f, unused, ls);
+        const V3 e = tex_eval(T.view, L.tex, ls.u, ls.v, v3(0.0f));
+        acc[0] += e.x; acc[1] += e.y; acc[2] += e.z;
+    }
+    const double l = 0.2126 * (acc[0] / 256.0) + 0.7152 * (acc[1] / 256.0) + 0.0722 * (acc[2] / 256.0);
+    return (float)((L.one_sided ? 1.0 : 2.0) * area * l);
+}
+
 static void build_env_table(const ShadeTables& T, DevLight& L, std::vector<float>& cdf, int xs, int ys){
     // TextureInfiniteLight::PreProcess (Light.cpp:166-200), including its cell decode
     // (x = k % ySamples, y = k / ySamples for both axes).  2x2 strata centres per cell
@@ -182,6 +215,19 @@ static int build_lights(pt_scene* s, ShadeTables& T, const std::vector<uint32_t>
     // every instance is one light (Model::BuildBlas, Model.hpp:47-59; TransformedPrimitive::GetLights)
     for(uint32_t id : inst_order){
         const HostInstance& hinst = s->instances[id];
+        if(hinst.blas < 0){
+            // GeometricPrimitive::GetLights (Primitive.cpp:28-30): its AreaLight, if any
+            if(hinst.shape.emissive_tex < 0)continue;
+            DevLight L {};
+            L.kind = hinst.shape.kind == PT_SHAPE_SPHERE ? DL_SPHERE : DL_QUAD;
+            L.tex = hinst.shape.emissive_tex; L.inst = id; L.valid = 1u; L.one_sided = hinst.shape.one_sided ? 1u : 0u;
+            T.view.inst = T.inst.data();
+            const float p = shape_light_power(T, L, L.area);
+            T.inst[id].light_base = (int32_t)T.lights.size();
+            T.lights.push_back(L);
+            power.push_back(p); power_inner.push_back(p);
+            continue;
+        }
         const HostBlas& hb = s->blas[hinst.blas];
         bool any = false;
         for(int mi : hb.meshes)if(s->meshes[mi].d.emissive_tex >= 0)any = true;

@@ -28,7 +28,14 @@ struct DevInstShade {
     float det;               // glm::determinant(transform) (TransformedLight::Power)
     uint32_t blas;
     uint32_t has_xf;
-    int32_t light_base;      // first DevLight of this instance's emissive triangles, or -1
+    int32_t light_base;      // first DevLight of this instance's emissive triangles (shape: its AreaLight), or -1
+    // GeometricPrimitive over an analytic shape (shape >= 0): no BLAS, no transform; fwd[] then holds the
+    // shape constants in the layout of the traversal record (scene_build.cpp pack_shape):
+    //   sphere: fwd[0..2] center, fwd[3] radius        quad: fwd[0..2] Q, [3..5] u, [6..8] v, [9..11] normal
+    int32_t shape;           // -1 | pt_shape_kind
+    int32_t material;        // shape: material id or -1 (medium boundary)
+    int32_t medium;          // shape: medium id or -1
+    uint32_t pad;
 };
 
 struct DevTexture {
@@ -56,7 +63,8 @@ struct DevMedium {
 };
 
 enum DevLightKind : int32_t {
-    DL_UNIFORM_INF = 0, DL_GRADIENT_INF = 1, DL_TEXTURE_INF = 2, DL_DISTANT = 3, DL_POINT = 4, DL_AREA = 5
+    DL_UNIFORM_INF = 0, DL_GRADIENT_INF = 1, DL_TEXTURE_INF = 2, DL_DISTANT = 3, DL_POINT = 4, DL_AREA = 5,
+    DL_SPHERE = 6, DL_QUAD = 7      // AreaLight over a SphereShape / QuadShape (geometry in S.inst[L.inst].fwd)
 };
 
 struct DevLight {
@@ -74,6 +82,7 @@ struct DevLight {
     uint32_t tri;            // AREA: mesh-local triangle index
     float area;              // AREA: TriangleShape::Area() in object space
     float total_weight;      // TEXTURE_INF: sum of the luminance table
+    uint32_t one_sided;      // SPHERE / QUAD: AreaLight::oneSided (mesh lights are always two-sided, Model.hpp:50)
 };
 
 struct ShadeScene {

@@ -54,7 +54,9 @@ __device__ __forceinline__ float f_div(float a, float b){ return __fdiv_rn(a, b)
 // Ray ctor, Ray.hpp:32-37
 #if defined(__CUDA_ARCH__)
 __device__ __forceinline__ float f_rcp(float a){ return __frcp_rn(a); }   // correctly rounded: == 1.0f / a
+__device__ __forceinline__ float f_sqrt(float a){ return __fsqrt_rn(a); }
 #else
+__device__ __forceinline__ float f_sqrt(float a){ return sqrtf(a); }
 __device__ __forceinline__ float f_rcp(float a){ return 1.0f / a; }
 #endif
 __device__ __forceinline__ float inv_dir(float d){ return fabsf(d) < 1e-32f ? 1e32f : f_rcp(d); }
@@ -174,6 +176,42 @@ __device__ __forceinline__ InstData load_inst(const Instance* inst, uint32_t i){
     d.meta = __ldg(reinterpret_cast<const uint4*>(p + 3));
     d.b0 = __ldg(p + 4); d.b1 = __ldg(p + 5);
     return d;
+}
+
+// SphereShape::Intersect / IntersectPred (Shape.cpp:3-56): both roots, strict `eps < t < max`.
+// Record layout: scene_build.cpp pack_shape.
+__device__ __forceinline__ bool sphere_hit(const RayCtx& r, const InstData& d, float tmax, float& t){
+    const float ocx = f_sub(r.ox, d.m0.x), ocy = f_sub(r.oy, d.m0.y), ocz = f_sub(r.oz, d.m0.z);
+    const float a = f_add(f_add(f_mul(r.dx, r.dx), f_mul(r.dy, r.dy)), f_mul(r.dz, r.dz));
+    const float b = f_add(f_add(f_mul(ocx, r.dx), f_mul(ocy, r.dy)), f_mul(ocz, r.dz));
+    const float c = f_sub(f_add(f_add(f_mul(ocx, ocx), f_mul(ocy, ocy)), f_mul(ocz, ocz)), f_mul(d.m0.w, d.m0.w));
+    const float disc = f_sub(f_mul(b, b), f_mul(a, c));
+    if(!(disc > 0.0f))return false;
+    const float sq = f_sqrt(disc);
+    t = f_div(f_sub(-b, sq), a);
+    if(t < tmax && t > kShadowEps)return true;
+    t = f_div(f_add(-b, sq), a);
+    return t < tmax && t > kShadowEps;
+}
+
+// QuadShape::Intersect / IntersectPred (Shape.cpp:316-359): plane hit with the normal turned against the
+// ray, `eps <= t <= max`, then the (alpha, beta) interior test.
+__device__ __forceinline__ bool quad_hit(const RayCtx& r, const InstData& d, float tmax, float& t, float& alpha, float& beta){
+    const float Qx = d.m0.x, Qy = d.m0.y, Qz = d.m0.z, ux = d.m0.w, uy = d.m1.x, uz = d.m1.y, vx = d.m1.z, vy = d.m1.w, vz = d.m2.x;
+    float nx = d.m2.y, ny = d.m2.z, nz = d.m2.w, D = d.b0.w;
+    const float wx = d.b0.x, wy = d.b0.y, wz = d.b0.z;
+    if(f_add(f_add(f_mul(r.dx, nx), f_mul(r.dy, ny)), f_mul(r.dz, nz)) > 0.0f){ nx = -nx; ny = -ny; nz = -nz; D = -D; }
+    const float denom = f_add(f_add(f_mul(nx, r.dx), f_mul(ny, r.dy)), f_mul(nz, r.dz));
+    if(fabsf(denom) < 1e-8f)return false;
+    t = f_div(f_sub(D, f_add(f_add(f_mul(nx, r.ox), f_mul(ny, r.oy)), f_mul(nz, r.oz))), denom);
+    if(t < kShadowEps || t > tmax)return false;
+    const float hx = f_sub(f_add(r.ox, f_mul(t, r.dx)), Qx), hy = f_sub(f_add(r.oy, f_mul(t, r.dy)), Qy), hz = f_sub(f_add(r.oz, f_mul(t, r.dz)), Qz);
+    // alpha = dot(w, cross(planar_hit, v)), beta = dot(w, cross(u, planar_hit))
+    const float ax = f_sub(f_mul(hy, vz), f_mul(vy, hz)), ay = f_sub(f_mul(hz, vx), f_mul(vz, hx)), az = f_sub(f_mul(hx, vy), f_mul(vx, hy));
+    const float bx = f_sub(f_mul(uy, hz), f_mul(hy, uz)), by = f_sub(f_mul(uz, hx), f_mul(hz, ux)), bz = f_sub(f_mul(ux, hy), f_mul(hx, uy));
+    alpha = f_add(f_add(f_mul(wx, ax), f_mul(wy, ay)), f_mul(wz, az));
+    beta = f_add(f_add(f_mul(wx, bx), f_mul(wy, by)), f_mul(wz, bz));
+    return alpha >= 0.0f && alpha <= 1.0f && beta >= 0.0f && beta <= 1.0f;
 }
 
 // glm mat4 * vec4 restricted to xyz: (m0*x + m1*y) + (m2*z + m3*w)
@@ -384,11 +422,17 @@ __device__ __forceinline__ void node_step8(TravState& s, const DevScene& S, cons
 
 // ---- one round of the state machine -------------------------------------------------------
 
-// Returns false once the ray is finished (s.flags & TF_DONE).
-// reload(ray index) -> the world-space ray is re-read from its buffer when a
-// transformed instance is left (cheaper than holding 9 more registers).
-template <int WIDTH, bool ANY, bool STATS, class STK, class Alpha>
-__device__ __forceinline__ void trav_step(TravState& s, const DevScene& S, const STK& stack, const float4* __restrict__ rays, size_t ray_idx,
+// Where the world-space ray comes from: a ray buffer (read-only loads), or registers for a caller that
+// changes the ray between traversals inside one kernel (the Scene::IntersectTr walk in render.cu).
+struct RayRegs { float4 a, b; };
+__device__ __forceinline__ void fetch_ray(const float4* rays, size_t i, float4& a, float4& b){ a = __ldg(rays + 2 * i); b = __ldg(rays + 2 * i + 1); }
+__device__ __forceinline__ void fetch_ray(const RayRegs& r, size_t, float4& a, float4& b){ a = r.a; b = r.b; }
+
+// One round; the ray is finished once s.flags & TF_DONE.
+// The world-space ray is re-read from its source when a transformed instance is left (cheaper than
+// holding 9 more registers).
+template <int WIDTH, bool ANY, bool STATS, class STK, class Alpha, class RAYS>
+__device__ __forceinline__ void trav_step(TravState& s, const DevScene& S, const STK& stack, const RAYS& rays, size_t ray_idx,
                                           TraceCounters* cnt, const Alpha& alpha){
     // -- pop (BVH4 closest: cull by entry distance, BVH.hpp:1135) --
     if(s.cur == REF_EMPTY){
@@ -413,7 +457,8 @@ __device__ __forceinline__ void trav_step(TravState& s, const DevScene& S, const
         if(s.cur == REF_LEAVE){
             // end of TransformedPrimitive::Intersect (Primitive.cpp:54-63): t back to world space
             if(s.flags & TF_XF){
-                const float4 a = __ldg(rays + 2 * ray_idx), b = __ldg(rays + 2 * ray_idx + 1);
+                float4 a, b;
+                fetch_ray(rays, ray_idx, a, b);
                 make_ray(s.r, a.x, a.y, a.z, b.x, b.y, b.z);
                 s.octant = ray_octant(s.r);
                 s.tmax = (s.flags & TF_FOUND_LOCAL) ? f_div(s.tmax, s.len) : s.wtmax;
@@ -426,6 +471,17 @@ __device__ __forceinline__ void trav_step(TravState& s, const DevScene& S, const
             const uint32_t i = s.cur & ~REF_LEAF;
             const InstData d = load_inst(S.inst, i);
             if(STATS)cnt->instances++;
+            if(d.meta.y & (INST_SPHERE | INST_QUAD)){
+                // GeometricPrimitive over an analytic shape sitting directly in the TLAS leaf
+                float t, u = 0.0f, v = 0.0f;
+                const bool hit = (d.meta.y & INST_SPHERE) ? sphere_hit(s.r, d, s.tmax, t) : quad_hit(s.r, d, s.tmax, t, u, v);
+                if(hit){
+                    if(ANY){ s.flags |= TF_OCCLUDED | TF_DONE; return; }
+                    s.tmax = t; s.hu = u; s.hv = v; s.hprim = 0u; s.hinst = d.meta.z;
+                }
+                s.cur = (d.meta.y & INST_LAST) ? REF_EMPTY : (REF_LEAF | (i + 1));
+                return;
+            }
             if(!(d.meta.y & INST_LAST))trav_push(stack, s.sp, REF_LEAF | (i + 1), -CUDART_INF_F);
             trav_push(stack, s.sp, REF_LEAVE, -CUDART_INF_F);
             s.flags |= TF_IN_INST;
@@ -433,7 +489,7 @@ __device__ __forceinline__ void trav_step(TravState& s, const DevScene& S, const
             if(d.meta.y & INST_XF){
                 float ddx, ddy, ddz, oox, ooy, ooz;
                 xf_apply(d, s.r.dx, s.r.dy, s.r.dz, 0.0f, ddx, ddy, ddz);
-                const float len = sqrtf(f_add(f_add(f_mul(ddx, ddx), f_mul(ddy, ddy)), f_mul(ddz, ddz)));
+                const float len = f_sqrt(f_add(f_add(f_mul(ddx, ddx), f_mul(ddy, ddy)), f_mul(ddz, ddz)));
                 xf_apply(d, s.r.ox, s.r.oy, s.r.oz, 1.0f, oox, ooy, ooz);
                 make_ray(s.r, oox, ooy, ooz, f_div(ddx, len), f_div(ddy, len), f_div(ddz, len));
                 s.octant = ray_octant(s.r);
@@ -475,12 +531,14 @@ __device__ __forceinline__ void trav_step(TravState& s, const DevScene& S, const
 }
 
 // Whole-ray convenience wrapper (host emulation tests, counting kernel).
-template <int WIDTH, bool ANY, bool STATS, class Alpha>
-__device__ __forceinline__ bool trace_scene(const DevScene& S, const float4* __restrict__ rays, size_t ray_idx, HitRec& hit, TraceCounters* cnt, const Alpha& alpha){
+template <int WIDTH, bool ANY, bool STATS, class Alpha, class RAYS>
+__device__ __forceinline__ bool trace_scene(const DevScene& S, const RAYS& rays, size_t ray_idx, HitRec& hit, TraceCounters* cnt, const Alpha& alpha){
     uint2 stack_mem[kStack];
     LocalStack stack; stack.lm = stack_mem;
     TravState s;
-    trav_init<WIDTH>(s, S, __ldg(rays + 2 * ray_idx), __ldg(rays + 2 * ray_idx + 1));
+    float4 ra, rb;
+    fetch_ray(rays, ray_idx, ra, rb);
+    trav_init<WIDTH>(s, S, ra, rb);
     while(!(s.flags & TF_DONE))trav_step<WIDTH, ANY, STATS>(s, S, stack, rays, ray_idx, cnt, alpha);
     const bool found = s.hprim != 0xFFFFFFFFu;
     hit.t = found ? s.tmax : CUDART_INF_F; hit.u = s.hu; hit.v = s.hv; hit.prim = s.hprim; hit.inst = s.hinst;

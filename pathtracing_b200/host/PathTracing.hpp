@@ -430,6 +430,61 @@ private:
     glm::vec3 p, color; PowerFunction pf;
 };
 
+// ---- Shape.hpp:8-175: the analytic shapes a GeometricPrimitive can carry into the TLAS ---------------------
+class Shape {
+public:
+    virtual ~Shape() = default;
+    virtual void Describe(pt_shape_desc& d) const = 0;
+    virtual AABB BoundingBox() const = 0;
+    virtual float Area() const = 0;
+};
+
+class SphereShape : public Shape {
+public:
+    SphereShape(const glm::vec3& sphereCenter, float sphereRadius) : center(sphereCenter), radius(sphereRadius){}
+    void Describe(pt_shape_desc& d) const override{
+        d.kind = PT_SHAPE_SPHERE; d.radius = radius;
+        for(int a = 0; a < 3; a++)d.p[a] = center[a];
+    }
+    AABB BoundingBox() const override{ AABB b; b.Expand(center - glm::vec3(radius)); b.Expand(center + glm::vec3(radius)); return b; }
+    float Area() const override{ return 4.0f * 3.14159265358979323846f * radius * radius; }
+private:
+    glm::vec3 center; float radius;
+};
+
+class QuadShape : public Shape {
+public:
+    QuadShape(const glm::vec3& origin, const glm::vec3& u, const glm::vec3& v) : Q(origin), u(u), v(v){}
+    void Describe(pt_shape_desc& d) const override{
+        d.kind = PT_SHAPE_QUAD;
+        for(int a = 0; a < 3; a++){ d.p[a] = Q[a]; d.u[a] = u[a]; d.v[a] = v[a]; }
+    }
+    AABB BoundingBox() const override{ AABB b; b.Expand(Q); b.Expand(Q + u + v); b.Expand(Q + u); b.Expand(Q + v); return b; }
+    float Area() const override{ return glm::length(glm::cross(u, v)); }
+private:
+    glm::vec3 Q, u, v;
+};
+
+// Light.hpp:179-206.  An AreaLight reaches the light sampler through Scene::GetLights() (the
+// GeometricPrimitive that carries it), exactly as in the reference; it cannot be added on its own.
+class AreaLight : public Light {
+public:
+    AreaLight(const std::shared_ptr<Shape>& light_shape, const glm::vec3& light_color, bool oneSided = false)
+        : shape(light_shape), emissiveTexture(std::make_shared<SolidColor>(light_color)), oneSided(oneSided){}
+    AreaLight(const std::shared_ptr<Shape>& light_shape, const std::shared_ptr<Texture>& emissiveTex, bool oneSided = false)
+        : shape(light_shape), emissiveTexture(emissiveTex), oneSided(oneSided){}
+    void Describe(ptb_host::Builder&, pt_light_desc&) const override{
+        throw std::logic_error("AreaLight: hand it to a GeometricPrimitive and add scene->GetLights() to the light sampler");
+    }
+    std::shared_ptr<Shape> getShape() const{ return shape; }
+    const std::shared_ptr<Texture>& EmissiveTexture() const{ return emissiveTexture; }
+    bool OneSided() const{ return oneSided; }
+private:
+    std::shared_ptr<Shape> shape;
+    std::shared_ptr<Texture> emissiveTexture;
+    bool oneSided;
+};
+
 // What Scene::GetLights() hands to LightSampler::Add: "every area light of every emissive mesh (through
 // its instance transform) plus the scene's infinite lights".  The GPU scene derives that list itself at
 // commit (csrc/shade_tables.cpp build_lights), in the reference's order.
@@ -452,6 +507,34 @@ public:
     // adds this primitive's instance(s) to the scene being assembled; transform = column-major mat4 or null
     virtual void Lower(ptb_host::Builder& b, const glm::mat4* transform) const = 0;
     virtual int RequiredWidth() const{ return 0; }     // BLAS width this primitive was built with (0: any)
+};
+
+// Primitive.hpp:17-33: shape + material + area light + medium, added to the Scene directly (examples/example_1.cpp:52-66).
+// material == nullptr: a medium boundary.  The area light must be built over the same shape.
+class GeometricPrimitive : public Primitive {
+public:
+    GeometricPrimitive(const std::shared_ptr<Shape>& shape, const std::shared_ptr<Material>& material, const std::shared_ptr<AreaLight>& areaLight = nullptr,
+                       const std::shared_ptr<Medium>& medium = nullptr)
+        : shape(shape), material(material), areaLight(areaLight), medium(medium){
+        if(!shape)throw std::invalid_argument("GeometricPrimitive: null shape");
+        if(areaLight && areaLight->getShape() != shape)throw std::invalid_argument("GeometricPrimitive: the AreaLight must be built over the primitive's own shape");
+    }
+    void Lower(ptb_host::Builder& b, const glm::mat4* transform) const override{
+        if(transform)throw std::logic_error("TransformedPrimitive over a sphere / quad GeometricPrimitive is not supported: transform the shape's constants instead");
+        pt_shape_desc d;
+        std::memset(&d, 0, sizeof d);
+        shape->Describe(d);
+        d.material = material ? material->Emit(b) : -1;
+        d.medium = medium ? medium->Emit(b) : -1;
+        d.emissive_tex = areaLight ? areaLight->EmissiveTexture()->Emit(b) : -1;
+        d.one_sided = areaLight && areaLight->OneSided() ? 1 : 0;
+        ptb_host::check(pt_scene_add_shape(b.scene, &d), "pt_scene_add_shape");
+    }
+private:
+    std::shared_ptr<Shape> shape;
+    std::shared_ptr<Material> material;
+    std::shared_ptr<AreaLight> areaLight;
+    std::shared_ptr<Medium> medium;
 };
 
 // A bottom-level structure over meshes.  The reference's Model imports a file through assimp

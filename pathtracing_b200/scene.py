@@ -14,7 +14,7 @@ from dataclasses import dataclass, field
 import numpy as np
 
 from . import capi
-from .capi import (PtError, pt_camera_desc, pt_light_desc, pt_material_desc, pt_medium_desc, pt_mesh_desc,
+from .capi import (PtError, pt_camera_desc, pt_light_desc, pt_material_desc, pt_medium_desc, pt_mesh_desc, pt_shape_desc,
                    pt_render_params, pt_render_stats, pt_texture_desc, pt_trace_stats)
 
 
@@ -146,6 +146,24 @@ class SceneDesc:
         self.instances.append((blas_id, transform))
         return len(self.instances) - 1
 
+    def _shape(self, kind, p, u, v, radius, material, medium, emissive_tex, one_sided):
+        d = pt_shape_desc()
+        d.kind = kind
+        _f3(d.p, p)
+        _f3(d.u, u)
+        _f3(d.v, v)
+        d.radius, d.material, d.medium, d.emissive_tex, d.one_sided = radius, material, medium, emissive_tex, int(one_sided)
+        self.instances.append((-1, d))
+        return len(self.instances) - 1
+
+    def sphere(self, center, radius, material=-1, medium=-1, emissive_tex=-1, one_sided=False):
+        """GeometricPrimitive(SphereShape(center, radius), material, AreaLight(shape, emissive_tex, one_sided), medium)"""
+        return self._shape(capi.SHAPE_SPHERE, center, (0, 0, 0), (0, 0, 0), radius, material, medium, emissive_tex, one_sided)
+
+    def quad(self, q, u, v, material=-1, medium=-1, emissive_tex=-1, one_sided=False):
+        """GeometricPrimitive(QuadShape(Q, u, v), ...)"""
+        return self._shape(capi.SHAPE_QUAD, q, u, v, 0.0, material, medium, emissive_tex, one_sided)
+
     # -- lights -----------------------------------------------------------------------
     def light(self, kind, color=(0, 0, 0), color_b=(0, 0, 0), scale=1.0, v=(0, 0, 0), tex=-1, power_func=0):
         d = pt_light_desc()
@@ -170,7 +188,10 @@ class SceneDesc:
         for ids in self.blas:
             b.add_blas(ids)
         for blas_id, xf in self.instances:
-            b.add_instance(blas_id, xf)
+            if blas_id < 0:
+                b.add_shape(xf)
+            else:
+                b.add_instance(blas_id, xf)
         for d in self.lights:
             b.add_light(d)
         if self.scene_medium >= 0:
@@ -251,6 +272,9 @@ class GpuScene:
     def add_instance(self, blas_id, xf):
         p = xf.ctypes.data_as(C.POINTER(C.c_float)) if xf is not None else None
         return self._ck(self.lib.pt_scene_add_instance(self.h, blas_id, p))
+
+    def add_shape(self, d):
+        return self._ck(self.lib.pt_scene_add_shape(self.h, C.byref(d)))
 
     def add_light(self, d):
         return self._ck(self.lib.pt_scene_add_light(self.h, C.byref(d)))

@@ -515,3 +515,45 @@ def misc_scene(uv_tex=True, normal_tex=True, thin=True, lens=True, uniform_sky=T
         d.light(capi.LIGHT_GRADIENT_INFINITE, color=(0.7, 0.8, 1.0), color_b=(0.7, 0.8, 1.0), scale=1.0)
     cam = camera_desc((0.0, 1.3, 3.2), (0.0, 0.5, 0.0), fov=0.9, focus_angle=0.12 if lens else 0.0, focus_distance=3.3 if lens else 0.0)
     return d, cam
+
+
+def shapes_scene(mesh=True, quad_light=True, sphere_light=True, one_sided=True, boundary=False, sky=True, n_spheres=9, seed=4):
+    """main.cpp-style scene made of analytic GeometricPrimitives: a huge checker ground QuadShape, a row of
+    SphereShapes with the README materials, a QuadShape AreaLight (one-sided or not), an emissive SphereShape
+    with a textured AreaLight, optionally one transformed triangle mesh in the same TLAS and a material-less
+    medium-boundary sphere (VolPathIntegrator)."""
+    d = SceneDesc()
+    rng = np.random.default_rng(seed)
+    ground = d.diffuse(d.checker(d.solid((0.8, 0.8, 0.8)), d.solid((0.2, 0.3, 0.1)), (0.002, 0.002)))
+    d.quad((-100, -0.3, -100), (1000, 0, 0), (0, 0, 1000), material=ground)
+    mats = [
+        d.diffuse(d.solid((0.1, 0.2, 0.5))),
+        d.dielectric(1.5, d.solid((1, 1, 1))),
+        d.conductor((0.8, 0.6, 0.2)),
+        d.diffuse(d.solid((0.95, 0.64, 0.54)), rough=d.solid((0.25, 0.25, 0.25)), metal=d.solid((1, 1, 1))),
+        d.dielectric(1.5, d.solid((0.9, 1.0, 0.9)), rough=d.solid((0.2, 0.2, 0.2))),
+        d.thin_dielectric(1.5, d.solid((1.0, 0.9, 0.9))),
+        d.diffuse(d.checker(d.solid((0.9, 0.1, 0.1)), d.solid((0.9, 0.9, 0.9)), (0.1, 0.1))),
+    ]
+    for k in range(n_spheres):
+        x = -2.4 + 4.8 * (k + 0.5) / n_spheres
+        r = 0.18 + 0.12 * rng.random()
+        d.sphere((x, -0.3 + r + 0.4 * (k % 3 == 1), -0.6 * (k % 2) + 0.2 * rng.standard_normal()), r, material=mats[k % len(mats)])
+    if mesh:
+        pos, idx, nrm, uv = icosphere(2, 1.0)
+        b = d.add_blas([d.mesh(pos, idx, nrm, uv, material=mats[3])])
+        d.instance(b, trs((0.2, 0.25, -1.6), 0.55, (0.2, 1, 0.1), 0.8))
+        d.instance(b)
+    black = d.diffuse(d.solid((0, 0, 0)))
+    if quad_light:
+        d.quad((0.5, 1.9, 0.3), (-1.0, 0, 0), (0, 0.3, -0.8), material=black, emissive_tex=d.solid((1, 0.95, 0.85), scale=(14, 14, 14)), one_sided=one_sided)
+    if sphere_light:
+        glow = d.checker(d.solid((6, 2, 1)), d.solid((1, 3, 6)), (0.125, 0.125))
+        d.sphere((-1.6, 1.0, -1.0), 0.3, material=d.diffuse(d.solid((0.1, 0.1, 0.1))), emissive_tex=glow)
+    if boundary:
+        fog = d.medium((0.01, 0.9, 0.9), (1.0, 0.1, 0.1), 0.8, density=5.0)
+        d.sphere((1.3, 0.3, 0.4), 0.6, material=-1, medium=fog)
+    if sky:
+        d.light(capi.LIGHT_GRADIENT_INFINITE, color=(1.0, 1.0, 1.0), color_b=(0.5, 0.7, 1.0), scale=0.4)
+    cam = camera_desc((0.0, 1.1, 4.0), (0.0, 0.3, 0.0), fov=0.9)
+    return d, cam

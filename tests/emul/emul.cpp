@@ -52,6 +52,7 @@ PT_API int emul_scene_add_medium(void* p, const pt_medium_desc* d){ return scene
 PT_API int emul_scene_add_mesh(void* p, const pt_mesh_desc* d){ return scene_add_mesh(&((EmulScene*)p)->s, d); }
 PT_API int emul_scene_add_blas(void* p, const int32_t* ids, int n){ return scene_add_blas(&((EmulScene*)p)->s, ids, n); }
 PT_API int emul_scene_add_instance(void* p, int b, const float* xf){ return scene_add_instance(&((EmulScene*)p)->s, b, xf); }
+PT_API int emul_scene_add_shape(void* p, const pt_shape_desc* d){ return scene_add_shape(&((EmulScene*)p)->s, d); }
 PT_API int emul_scene_add_light(void* p, const pt_light_desc* d){ return scene_add_light(&((EmulScene*)p)->s, d); }
 
 PT_API int emul_scene_commit(void* p, int width){
@@ -172,8 +173,8 @@ PT_API int emul_unit_shade(void* p, const pt_ray* rays, size_t n, const float* i
         }
         if(si.light >= 0){
             const DevLight& L = S.lights[si.light];
-            const V3 le = tex_eval(S, L.tex, si.u, si.v, si.ns);       // what k_shade evaluates on an emissive hit
-            o[38] = le.x; o[39] = le.y; o[40] = le.z; o[41] = L.pmf_hit; o[42] = tri_pdf(si.p, si.n, ro, rd, L.area);
+            const V3 le = area_L(S, L, si.n, si.ns, si.u, si.v, rd);   // what k_shade evaluates on an emissive hit
+            o[38] = le.x; o[39] = le.y; o[40] = le.z; o[41] = L.pmf_hit; o[42] = area_pdf(L, si.p, si.n, ro, rd);
         }
     }
     return PT_OK;

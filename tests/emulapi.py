@@ -9,7 +9,7 @@ from pathlib import Path
 import numpy as np
 
 from pathtracing_b200 import capi
-from pathtracing_b200.capi import pt_light_desc, pt_material_desc, pt_medium_desc, pt_mesh_desc, pt_texture_desc
+from pathtracing_b200.capi import pt_light_desc, pt_material_desc, pt_medium_desc, pt_mesh_desc, pt_shape_desc, pt_texture_desc
 
 _DIR = Path(__file__).resolve().parent / "emul"
 _lib = None
@@ -27,7 +27,7 @@ def load():
     lib.emul_last_error.restype = C.c_char_p
     for name, desc in (("emul_scene_add_texture", pt_texture_desc), ("emul_scene_add_material", pt_material_desc),
                        ("emul_scene_add_medium", pt_medium_desc), ("emul_scene_add_mesh", pt_mesh_desc),
-                       ("emul_scene_add_light", pt_light_desc)):
+                       ("emul_scene_add_light", pt_light_desc), ("emul_scene_add_shape", pt_shape_desc)):
         f = getattr(lib, name)
         f.restype = i
         f.argtypes = [vp, C.POINTER(desc)]
@@ -78,6 +78,9 @@ class EmulScene:
     def add_instance(self, blas_id, xf):
         p = xf.ctypes.data_as(C.POINTER(C.c_float)) if xf is not None else None
         return self._ck(self.lib.emul_scene_add_instance(self.h, blas_id, p))
+
+    def add_shape(self, d):
+        return self._ck(self.lib.emul_scene_add_shape(self.h, C.byref(d)))
 
     def add_light(self, d):
         return self._ck(self.lib.emul_scene_add_light(self.h, C.byref(d)))

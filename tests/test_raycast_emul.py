@@ -78,3 +78,48 @@ def test_degenerate_identical_triangles():
         # all 40 triangles tie exactly: the LAST one tested wins (t == max is accepted)
         assert np.array_equal(rh["prim"], eh["prim"])
         assert np.array_equal(rh["t"].view(np.uint32), eh["t"].view(np.uint32))
+
+
+@needs_ref
+@pytest.mark.parametrize("width", [2, 4, 8])
+def test_shapes_bit_exact(width):
+    """SphereShape / QuadShape GeometricPrimitives in the TLAS next to BLAS instances (Shape.cpp:3-56, 316-359)"""
+    d, _ = synth.shapes_scene()
+    from emulapi import EmulScene
+    from oracle.refapi import RefScene
+    ref, em = RefScene(d, width, id_mode=True), EmulScene(d, width)
+    lo, hi = ref.bounds()
+    elo, ehi = em.bounds()
+    assert np.array_equal(lo, elo) and np.array_equal(hi, ehi)
+    for seed, tmax, box in ((7, np.inf, ((-3, -0.3, -2.5), (3, 2.2, 1.5))), (9, 2.0, ((-3, -0.3, -2.5), (3, 2.2, 1.5))), (11, np.inf, (lo, hi))):
+        rays = synth.random_rays(30000, box[0], box[1], seed=seed, tmax=tmax)
+        rh, ri = ref.trace_closest(rays, want_inst=True)
+        eh, ei = em.trace_closest(rays)
+        assert np.array_equal(ri, ei)
+        assert np.array_equal(rh["prim"], eh["prim"])
+        assert np.array_equal(rh["t"].view(np.uint32), eh["t"].view(np.uint32))
+        shape_hit = np.isin(ri, [k for k, (b, _) in enumerate(d.instances) if b < 0])
+        assert np.array_equal(rh["u"][shape_hit].view(np.uint32), eh["u"][shape_hit].view(np.uint32))
+        assert np.array_equal(rh["v"][shape_hit].view(np.uint32), eh["v"][shape_hit].view(np.uint32))
+        assert np.array_equal(ref.trace_any(rays), em.trace_any(rays))
+        if seed == 7:
+            assert shape_hit.mean() > 0.3 and (~shape_hit & (rh["prim"] != 0xFFFFFFFF)).mean() > 0.02
+
+
+@needs_ref
+def test_shapes_only_scene():
+    """no BLAS at all: the TLAS holds only analytic shapes; also a single-shape scene (TLAS root is a leaf)"""
+    from emulapi import EmulScene
+    from oracle.refapi import RefScene
+    d, _ = synth.shapes_scene(mesh=False)
+    from pathtracing_b200.scene import SceneDesc
+    one = SceneDesc()
+    one.sphere((0.1, 0.2, 0.3), 0.7, material=one.diffuse(one.solid((1, 1, 1))))
+    for desc, box in ((d, ((-3, -0.3, -2.5), (3, 2.2, 1.5))), (one, ((-1, -1, -1), (1, 1, 1)))):
+        for width in (2, 4, 8):
+            ref, em = RefScene(desc, width, id_mode=True), EmulScene(desc, width)
+            rays = synth.random_rays(8000, box[0], box[1], seed=3)
+            rh, ri = ref.trace_closest(rays, want_inst=True)
+            eh, ei = em.trace_closest(rays)
+            assert np.array_equal(ri, ei) and np.array_equal(rh["t"].view(np.uint32), eh["t"].view(np.uint32))
+            assert np.array_equal(ref.trace_any(rays), em.trace_any(rays))

@@ -206,3 +206,29 @@ def test_alpha_blend_inside_traversal_statistics():
     gh3, _ = gpu.trace_closest(rays)
     assert (gh2["t"] != gh3["t"]).mean() > 0.01
     gpu.close(); ref.close()
+
+
+@needs_ref
+@pytest.mark.parametrize("width", [2, 4, 8])
+@pytest.mark.parametrize("mesh", [True, False])
+def test_sphere_and_quad_shapes_bit_exact(width, mesh):
+    """SphereShape / QuadShape GeometricPrimitives as TLAS leaf items (Shape.cpp:3-56, 316-359), alone and
+    next to BLAS instances: ids, t and the quad's (alpha, beta) bit-exact, any-hit equal."""
+    from oracle.refapi import RefScene
+    d, _ = synth.shapes_scene(mesh=mesh)
+    ref, gpu = RefScene(d, width, id_mode=True), GpuScene(d, width)
+    lo, hi = ref.bounds()
+    glo, ghi = gpu.bounds()
+    assert np.array_equal(lo, glo) and np.array_equal(hi, ghi)
+    shapes = [k for k, (b, _) in enumerate(d.instances) if b < 0]
+    for seed, tmax, box in ((7, np.inf, ((-3, -0.3, -2.5), (3, 2.2, 1.5))), (9, 2.0, ((-3, -0.3, -2.5), (3, 2.2, 1.5))), (11, np.inf, (lo, hi))):
+        rays = synth.random_rays(100000, box[0], box[1], seed=seed, tmax=tmax)
+        rh, ri = ref.trace_closest(rays, want_inst=True)
+        gh, gi = gpu.trace_closest(rays)
+        assert np.array_equal(ri, gi) and np.array_equal(rh["prim"], gh["prim"])
+        assert np.array_equal(rh["t"].view(np.uint32), gh["t"].view(np.uint32))
+        sh = np.isin(ri, shapes)
+        assert np.array_equal(rh["u"][sh].view(np.uint32), gh["u"][sh].view(np.uint32))
+        assert np.array_equal(rh["v"][sh].view(np.uint32), gh["v"][sh].view(np.uint32))
+        assert np.array_equal(ref.trace_any(rays), gpu.trace_any(rays))
+    gpu.close()

@@ -231,6 +231,39 @@ def test_misc_uniform_sky_uv_normal_textures_thin_lens():
 
 
 @needs_ref
+@pytest.mark.parametrize("one_sided", [True, False])
+def test_sphere_and_quad_shapes_path(one_sided):
+    """main.cpp-style scene of analytic GeometricPrimitives: checker ground QuadShape, SphereShapes with every
+    material, a QuadShape AreaLight (one- / two-sided), an emissive textured SphereShape, a mesh instance."""
+    desc, cam = synth.shapes_scene(one_sided=one_sided)
+    compare(desc, cam, 64, 48, 1024, 10)
+
+
+@needs_ref
+def test_sphere_and_quad_shapes_simple_integrator_bvh8_uniform_lights():
+    desc, cam = synth.shapes_scene()
+    compare(desc, cam, 48, 36, 1024, 6, integrator=capi.INTEGRATOR_SIMPLE, bvh=8)
+    compare(desc, cam, 48, 36, 512, 6, bvh=2, light_sampler=0)
+
+
+@needs_ref
+def test_medium_boundary_sphere_volpath_intersect_tr():
+    """A material-less SphereShape holding a HomogeneusMedium (main.cpp:208): the path passes through the
+    boundary and switches medium (Integrators.cpp:378-382), shadow rays walk through it collecting
+    transmittance (Scene::IntersectTr, Scene.cpp:8-29)."""
+    desc, cam = synth.shapes_scene(boundary=True)
+    compare(desc, cam, 64, 48, 1024, 12, integrator=capi.INTEGRATOR_VOLPATH)
+
+
+@needs_ref
+def test_medium_boundary_sphere_path_integrator():
+    """PathIntegrator with the same boundary: camera paths continue through it (Integrators.cpp:228-232),
+    shadow rays are blocked by it (Unoccluded -> IntersectPred)."""
+    desc, cam = synth.shapes_scene(boundary=True)
+    compare(desc, cam, 48, 36, 1024, 8)
+
+
+@needs_ref
 def test_volpath_without_medium_equals_reference():
     desc, cam = synth.cornell_scene()
     compare(desc, cam, 40, 40, 1024, 6, integrator=capi.INTEGRATOR_VOLPATH)

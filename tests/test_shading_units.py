@@ -222,3 +222,63 @@ def test_henyey_greenstein(libs, g):
     emu.emul_unit_hg(g, n, inp.ctypes.data, b.ctypes.data)
     _close(a[:, :3], b[:, :3], 1e-4, 2e-5, "HenyeyGreenstein::Sample direction", frac=1e-3)
     _close(a[:, 3:], b[:, 3:], 1e-3, 1e-6, "HenyeyGreenstein pdf", frac=1e-3)
+
+
+@needs_ref
+@pytest.mark.parametrize("one_sided", [False, True])
+def test_sphere_and_quad_shapes(libs, one_sided):
+    """SphereShape / QuadShape interactions (Shape.cpp:3-37, 316-341), their AreaLights (one- and two-sided:
+    Light.cpp:257-287) incl. Sample / PDF / L / Power, next to a triangle mesh in the same TLAS."""
+    ref, emu = libs
+    desc, cam = synth.shapes_scene(one_sided=one_sided)
+    r, e = _scenes(desc, 4)
+    rays = _camera_rays(cam, 64, 48, 20000, 5)
+    a, _ = _shade(libs, r, e, rays)
+    hit = a[:, 0] == 1
+    rng = np.random.default_rng(2)
+    d2 = rng.normal(size=(hit.sum(), 3)).astype(np.float32)
+    d2 /= np.linalg.norm(d2, axis=1, keepdims=True)
+    r2 = np.zeros(hit.sum(), capi.RAY_DTYPE)
+    r2["o"], r2["d"], r2["tmax"] = a[hit, 1:4] + 1e-3 * d2, d2, np.inf
+    # rays aimed at the two lights from all around (front and back of the one-sided quad)
+    tgt = np.where(rng.random((6000, 1)) < 0.5, np.array([[0.0, 2.05, -0.1]]), np.array([[-1.6, 1.0, -1.0]])) + rng.normal(size=(6000, 3)) * 0.25
+    o3 = rng.uniform((-3, 0, -3), (3, 4, 3), (6000, 3))
+    d3 = tgt - o3
+    d3 /= np.linalg.norm(d3, axis=1, keepdims=True)
+    r3 = np.zeros(6000, capi.RAY_DTYPE)
+    r3["o"], r3["d"], r3["tmax"] = o3.astype(np.float32), d3.astype(np.float32), np.inf
+    seen_lights = 0
+    for rr in (rays, r2, r3):
+        a, b = _shade(libs, r, e, rr)
+        assert np.array_equal(a[:, 0], b[:, 0])
+        h = a[:, 0] == 1
+        assert np.array_equal(a[h, 16], b[h, 16]) and np.array_equal(a[h, 17], b[h, 17])
+        assert np.array_equal(a[h, 15].view(np.uint32), b[h, 15].view(np.uint32))
+        _close(a[h, 1:16], b[h, 1:16], 2e-5, 2e-6, "interaction", frac=1e-4)     # atan2 / acos round-off in GetSphereUV
+        ok = h & (a[:, 16] >= 0)
+        assert np.array_equal(a[ok, 18], b[ok, 18])
+        s = ok & (a[:, 18] == 1)
+        _close(a[s, 24:30], b[s, 24:30], 1e-4, 1e-5, "scattered ray", frac=2e-3)
+        _close(a[s, 19:23], b[s, 19:23], 2e-3, 1e-6, "f, pdf", frac=5e-3)
+        em = h & (a[:, 17] == 1)
+        seen_lights += int(em.sum())
+        if em.any():
+            _close(a[em, 38:43], b[em, 38:43], 1e-4, 1e-7, "emission, PMF, PDF of the hit light")
+    assert seen_lights > 500
+    n = ref.ref_unit_light_count(r.h)
+    assert n == emu.emul_unit_light_count(e.h) == 3
+    ra, eb = np.zeros((n, 3), np.float32), np.zeros((n, 4), np.float32)
+    ref.ref_unit_lights(r.h, ra.ctypes.data)
+    emu.emul_unit_lights(e.h, eb.ctypes.data)
+    _close(ra[:, 1], eb[:, 0], 2e-3, 1e-6, "sampler PMF per light (the reference jitters its 256 power samples)")
+    m = 3000
+    for k in range(n):
+        inp = np.ascontiguousarray(np.concatenate([rng.random((m, 2)), rng.uniform(-2, 3, (m, 3))], 1).astype(np.float32))
+        a, b = np.zeros((m, 22), np.float32), np.zeros((m, 22), np.float32)
+        assert ref.ref_unit_light_sample(r.h, k, m, inp.ctypes.data, a.ctypes.data, 22) == 0
+        assert emu.emul_unit_light_sample(e.h, k, m, inp.ctypes.data, b.ctypes.data, 22) == 0
+        if not a[:, 6:9].any():
+            a[:, 9:11] = b[:, 9:11] = 0
+        _close(a[:, :18], b[:, :18], 1e-4, 1e-5, f"light {k}: sample, shadow ray", frac=1e-3)
+        _close(a[:, 18:22], b[:, 18:22], 2e-3, 1e-6, f"light {k}: PDF and L along the shadow ray", frac=2e-3)
+    r.close(); e.close()
