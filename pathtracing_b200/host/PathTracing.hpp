@@ -799,6 +799,58 @@ public:
             for(int a = 0; a < 3; a++)out << (char)(255.999 * std::max(0.0, std::min(1.0, linear_to_sRGB((double)c[a]))));
         }
     }
+    // PNG, 8-bit RGB, top row first (Film.hpp:172-194).  The image data goes into stored (uncompressed)
+    // deflate blocks: a valid PNG without a compressor.
+    void WritePNG(const std::string& filename, const std::function<glm::vec3(glm::vec3)>& toneMapper = reinhard_jodie) const{
+        std::vector<uint8_t> raw;
+        raw.reserve((size_t)yResolution * (3 * (size_t)xResolution + 1));
+        for(int i = yResolution - 1; i >= 0; i--){
+            raw.push_back(0);                                       // filter type: none
+            for(int j = 0; j < xResolution; j++){
+                const glm::vec3 c = toneMapper(glm::vec3(Pixel(j, i)));
+                for(int a = 0; a < 3; a++)raw.push_back((uint8_t)(255.999 * std::max(0.0, std::min(1.0, linear_to_sRGB((double)c[a])))));
+            }
+        }
+        std::vector<uint8_t> z = { 0x78, 0x01 };                    // zlib header, then stored blocks of <= 65535 bytes
+        uint32_t s1 = 1, s2 = 0;
+        for(size_t off = 0; off < raw.size() || off == 0; ){
+            const size_t n = std::min<size_t>(65535, raw.size() - off);
+            z.push_back(off + n >= raw.size() ? 1 : 0);
+            z.push_back((uint8_t)(n & 255)); z.push_back((uint8_t)(n >> 8)); z.push_back((uint8_t)(~n & 255)); z.push_back((uint8_t)((~n >> 8) & 255));
+            for(size_t k = 0; k < n; k++){ const uint8_t v = raw[off + k]; z.push_back(v); s1 = (s1 + v) % 65521u; s2 = (s2 + s1) % 65521u; }
+            off += n;
+            if(n == 0)break;
+        }
+        const uint32_t adler = (s2 << 16) | s1;
+        for(int k = 3; k >= 0; k--)z.push_back((uint8_t)(adler >> (8 * k)));
+        std::ofstream out((outputPath.empty() ? filename : outputPath) + ".png", std::ios::binary);
+        if(!out)throw std::runtime_error("Film::WritePNG: cannot open output file");
+        auto chunk = [&](const char* type, const std::vector<uint8_t>& data){
+            std::vector<uint8_t> buf(type, type + 4);
+            buf.insert(buf.end(), data.begin(), data.end());
+            uint32_t crc = 0xFFFFFFFFu;
+            for(uint8_t v : buf){ crc ^= v; for(int k = 0; k < 8; k++)crc = (crc >> 1) ^ (0xEDB88320u & (0u - (crc & 1u))); }
+            crc = ~crc;
+            const uint32_t len = (uint32_t)data.size();
+            for(int k = 3; k >= 0; k--)out.put((char)(len >> (8 * k)));
+            out.write((const char*)buf.data(), (std::streamsize)buf.size());
+            for(int k = 3; k >= 0; k--)out.put((char)(crc >> (8 * k)));
+        };
+        out.write("\x89PNG\r\n\x1a\n", 8);
+        std::vector<uint8_t> hdr;
+        for(uint32_t v : { (uint32_t)xResolution, (uint32_t)yResolution })for(int k = 3; k >= 0; k--)hdr.push_back((uint8_t)(v >> (8 * k)));
+        for(uint8_t v : { 8, 2, 0, 0, 0 })hdr.push_back(v);        // 8 bits, RGB, deflate, adaptive filtering, no interlace
+        chunk("IHDR", hdr);
+        chunk("IDAT", z);
+        chunk("IEND", {});
+    }
+    // The reference encodes JPEG through stb_image_write (Film.hpp:196-217), a third-party encoder outside
+    // this path: the same tone-mapped image is written losslessly as <filename>.png instead.
+    void WriteJPG(const std::string& filename, int /*quality*/, const std::function<glm::vec3(glm::vec3)>& toneMapper = reinhard_jodie) const{
+        static bool told = false;
+        if(!told){ told = true; std::fprintf(stderr, "Film::WriteJPG: no JPEG encoder on this path, writing %s.png\n", filename.c_str()); }
+        WritePNG(filename, toneMapper);
+    }
 private:
     int xResolution, yResolution;
     std::vector<double> screen;             // RGB sums * w and weight sums, 4 doubles per pixel
@@ -952,4 +1004,44 @@ protected:
 private:
     std::shared_ptr<LightSampler> lightSampler;
     uint32_t maxDepth;
+};
+
+// ---- ResourceManager.hpp:8-105: name-keyed caches of textures and models ----------------------------------------
+// Textures and meshes are plain shared objects here (the scene is lowered to the device at commit), so the
+// manager is just the caches; the file-importing entry points (GetImageTexture, CacheModel: stb / assimp)
+// are host I/O outside this path.
+class ResourceManager {
+public:
+    static ResourceManager& get_instance(){ static ResourceManager instance; return instance; }
+    ResourceManager(const ResourceManager&) = delete;
+    ResourceManager& operator=(const ResourceManager&) = delete;
+
+    template <typename T, typename... Args>
+    [[nodiscard]] std::shared_ptr<Texture> GetTexture(const std::string& name, Args&&... args){
+        static_assert(std::is_base_of_v<Texture, T>, "GetTexture<T>: T must be a Texture");
+        if(name.empty())return nullptr;
+        auto it = textureCache.find(name);
+        if(it != textureCache.end())return it->second;
+        return textureCache.try_emplace(name, std::make_shared<T>(std::forward<Args>(args)...)).first->second;
+    }
+    template <typename... Args>
+    [[nodiscard]] std::shared_ptr<Mesh> getMesh(Args&&... args){
+        meshCache.push_back(std::make_shared<Mesh>(std::forward<Args>(args)...));
+        return meshCache.back();
+    }
+    // the reference's CacheModel imports `path` through assimp; here the model is handed over ready-made
+    std::shared_ptr<Model> CacheModel(const std::string& name, const std::shared_ptr<Model>& model){ return modelCache.try_emplace(name, model).first->second; }
+    [[nodiscard]] std::shared_ptr<Model> GetModel(const std::string& name){
+        auto it = modelCache.find(name);
+        return it != modelCache.end() ? it->second : nullptr;
+    }
+    void releaseTextureCache(){ textureCache.clear(); }
+    void releaseMeshCache(){ meshCache.clear(); }
+    void releaseModelCache(){ modelCache.clear(); }
+    void releaseAll(){ releaseTextureCache(); releaseMeshCache(); releaseModelCache(); }
+private:
+    ResourceManager() = default;
+    std::unordered_map<std::string, std::shared_ptr<Texture>> textureCache;
+    std::unordered_map<std::string, std::shared_ptr<Model>> modelCache;
+    std::vector<std::shared_ptr<Mesh>> meshCache;
 };
