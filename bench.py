@@ -328,6 +328,19 @@ def run_ours(a):
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         e2e_ms = float(t.item())
     e2e_value = world * n / (e2e_ms * 1e-3) / 1e6
+    # what the PCIe link of this box gives the same pinned buffers (plain copies, CUDA events): the floor of e2e
+    pcie = {}
+    for name, dst, src in (("h2d", d_rays, host_rays), ("d2h", host_hits, d_hits)):
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        dst.copy_(src, non_blocking=True)
+        torch.cuda.synchronize()
+        e0.record()
+        for _ in range(3):
+            dst.copy_(src, non_blocking=True)
+        e1.record()
+        torch.cuda.synchronize()
+        pcie[name] = 3 * src.numel() * src.element_size() / (e0.elapsed_time(e1) * 1e-3) / 1e9
+    e2e_floor_ms = max(n * 32 / pcie["h2d"], n * 16 / pcie["d2h"]) / 1e6
     # the result really came back: hit count of the host buffer
     hits_np = host_hits.numpy().view(np.dtype([("t", "<f4"), ("u", "<f4"), ("v", "<f4"), ("prim", "<u4")]))
     hit_rate = float((hits_np["prim"] != 0xFFFFFFFF).mean())
@@ -357,10 +370,17 @@ def run_ours(a):
     else:
         peak, peak_src = 6650.0, "fallback (B200_PROFILING.md)"
     achieved = n * b_ray / (ms * 1e-3) / 1e9
-    roofline = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": None,
+    # DRAM bytes of the dominant kernel from the committed `ncu --set full` capture (profiles/r01_trace4_v5.md:
+    # dram__bytes_read 1.77 GB + dram__bytes_write 0.094 GB for a 4,194,304-ray launch of this workload), per ray
+    # times the rays of one bench launch.  Only the default workload was captured.
+    default_workload = a.bvh == 4 and a.mesh == "soup" and a.tris == 1_000_000
+    traffic = (1.77e9 + 0.094e9) / 4194304 * n if default_workload else None
+    roofline = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": traffic,
+                "traffic_source": "profiles/r01_trace4_v5.md (ncu --set full of a 4 Mi-ray launch, scaled per ray)" if default_workload else None,
+                "algorithmic_bytes": n * b_ray,
                 "peak_source": peak_src, "kernel": f"k_trace<{a.bvh},false,false>", "bytes_per_ray": b_ray,
                 "nodes_per_ray": nodes_per_ray, "tris_per_ray": tris_per_ray, "instances_per_ray": inst_per_ray,
-                "note": "scene (nodes+triangles) is L2-resident at this size; DRAM traffic is rays+hits, see DESIGN.md"}
+                "note": "scene (nodes+triangles) is L2-resident at this size: DRAM traffic is ~12x BELOW the algorithmic bytes, the kernel is bound by L1 data-pipe wavefronts (DESIGN.md 4.1)"}
 
     extras = {}
     if not a.no_extras:
@@ -395,7 +415,11 @@ def run_ours(a):
         except Exception as e:  # the oracle is a reported baseline, never a dependency of the product path
             cpu = {"value": None, "unit": UNIT, "cores": os.cpu_count(), "kind": "reference", "sample": f"unavailable: {e}"}
 
-    chunks = (n + (1 << 20) - 1) >> 20
+    full = int(os.environ.get("PTB_CHUNK", 4 << 20))
+    chunks, off = 0, 0
+    while off < n:         # csrc/capi.cu trace_pipelined: 1/8, 1/2, then full chunks
+        off += max(1024, full // 8 if chunks == 0 else full // 2 if chunks == 1 else full)
+        chunks += 1
     line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": a.steps, "warmup": a.warmup,
             "ms_per_step": ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
             "data": "synthetic",
@@ -404,7 +428,9 @@ def run_ours(a):
                        "l2": "ray+hit buffers (768 MiB per step) exceed the 126 MB L2; the 87 MB scene stays resident by design",
                        "hit_rate": hit_rate, "scene_build_s": build_s},
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": n * 32, "d2h_bytes_per_step": n * 16,
-                    "ms_per_step": e2e_ms, "api": "pt_trace_closest (pinned host buffers, 1 Mi-ray chunks over 2 streams)"},
+                    "ms_per_step": e2e_ms, "api": f"pt_trace_closest (pinned host buffers, {chunks} chunks through a 3-stream H2D / trace / D2H pipeline)",
+                    "pcie_h2d_gbs": pcie["h2d"], "pcie_d2h_gbs": pcie["d2h"], "pcie_floor_ms": e2e_floor_ms,
+                    "note": "floor = the slower of the two plain pinned copies of one step's buffers on this box"},
             "gpu_launches": a.steps, "gpu_launches_e2e": e2e_steps * chunks,
             "clocks": clocks, "roofline": roofline, "cpu_baseline": cpu, "extras": extras}
     print(json.dumps(line), flush=True)

@@ -1,5 +1,6 @@
 // capi.cu — the extern "C" surface declared in include/pt_b200.h.
 #include <cuda_runtime.h>
+#include <cstdlib>
 #include <cstring>
 #include <new>
 
@@ -11,6 +12,71 @@ using namespace ptb;
 #define PT_CHECK_OPEN(s) do{ PT_CHECK_SCENE(s); if((s)->committed){ set_error("scene already committed"); return PT_ERR_STATE; } }while(0)
 #define PT_CHECK_READY(s) do{ PT_CHECK_SCENE(s); if(!(s)->committed){ set_error("scene not committed"); return PT_ERR_STATE; } \
     if(!cuda_ok(cudaSetDevice((s)->device), "cudaSetDevice"))return PT_ERR_CUDA; }while(0)
+
+static int ensure_stage(pt_scene* s, size_t n){
+    DeviceBuffers& b = s->buf;
+    if(n <= b.stage_cap)return PT_OK;
+    void** ptrs[] = { &b.stage_rays, &b.stage_hits, &b.stage_inst, &b.stage_occ };
+    for(void** p : ptrs){ if(*p){ cudaFree(*p); *p = nullptr; } }
+    b.stage_cap = 0;
+    if(!cuda_ok(cudaMalloc(&b.stage_rays, n * sizeof(pt_ray)), "cudaMalloc rays") ||
+       !cuda_ok(cudaMalloc(&b.stage_hits, n * sizeof(pt_hit)), "cudaMalloc hits") ||
+       !cuda_ok(cudaMalloc(&b.stage_inst, n * sizeof(uint32_t)), "cudaMalloc inst") ||
+       !cuda_ok(cudaMalloc(&b.stage_occ, n), "cudaMalloc occ"))return PT_ERR_CUDA;
+    b.stage_cap = n;
+    return PT_OK;
+}
+
+// Host-buffer entry points: a three-stage pipeline over three streams.  Chunk k is copied in on the H2D
+// stream, traced on the compute stream once its copy has landed, and copied out on the D2H stream once its
+// kernel is done — so the kernels run back to back while both PCIe directions stay busy (full duplex).  The
+// first chunks are small so that the compute stream starts early; the staging buffers hold the whole batch,
+// so no chunk ever waits for a buffer.
+static size_t chunk_rays(){
+    static size_t v = 0;
+    if(!v){
+        v = 4u << 20;
+        if(const char* e = getenv("PTB_CHUNK")){ const long long x = atoll(e); if(x >= 1024)v = (size_t)x; }
+    }
+    return v;
+}
+
+static cudaEvent_t pipeline_event(pt_scene* s, size_t i){
+    while(s->events.size() <= i){
+        cudaEvent_t e = nullptr;
+        if(!cuda_ok(cudaEventCreateWithFlags(&e, cudaEventDisableTiming), "cudaEventCreate"))return nullptr;
+        s->events.push_back(e);
+    }
+    return (cudaEvent_t)s->events[i];
+}
+
+// launch(off, m, stream) queues the kernel for rays [off, off+m); copy_out(off, m, stream) queues its D2H copies
+template <class Launch, class CopyOut>
+static int trace_pipelined(pt_scene* s, const pt_ray* rays, size_t n, Launch launch, CopyOut copy_out){
+    int rc = ensure_stage(s, n);
+    if(rc != PT_OK)return rc;
+    cudaStream_t compute = (cudaStream_t)s->stream, in = (cudaStream_t)s->stream2, out = (cudaStream_t)s->stream3;
+    pt_ray* d_rays = (pt_ray*)s->buf.stage_rays;
+    const size_t full = chunk_rays();
+    size_t k = 0;
+    for(size_t off = 0; off < n; k++){
+        size_t m = k == 0 ? full / 8 : k == 1 ? full / 2 : full;      // ramp up: 1/8, 1/2, then full chunks
+        if(m < 1024)m = 1024;
+        if(m > n - off)m = n - off;
+        cudaEvent_t landed = pipeline_event(s, 2 * k), traced = pipeline_event(s, 2 * k + 1);
+        if(!landed || !traced)return PT_ERR_CUDA;
+        if(!cuda_ok(cudaMemcpyAsync(d_rays + off, rays + off, m * sizeof(pt_ray), cudaMemcpyHostToDevice, in), "H2D rays") ||
+           !cuda_ok(cudaEventRecord(landed, in), "event") || !cuda_ok(cudaStreamWaitEvent(compute, landed, 0), "wait"))return PT_ERR_CUDA;
+        rc = launch(off, m, compute);
+        if(rc != PT_OK)return rc;
+        if(!cuda_ok(cudaEventRecord(traced, compute), "event") || !cuda_ok(cudaStreamWaitEvent(out, traced, 0), "wait"))return PT_ERR_CUDA;
+        rc = copy_out(off, m, out);
+        if(rc != PT_OK)return rc;
+        off += m;
+    }
+    if(!cuda_ok(cudaStreamSynchronize(out), "sync") || !cuda_ok(cudaStreamSynchronize(compute), "sync") || !cuda_ok(cudaStreamSynchronize(in), "sync"))return PT_ERR_CUDA;
+    return PT_OK;
+}
 
 extern "C" {
 
@@ -38,6 +104,8 @@ void pt_scene_destroy(pt_scene* s){
         scene_free_device(s);
         if(s->stream)cudaStreamDestroy((cudaStream_t)s->stream);
         if(s->stream2)cudaStreamDestroy((cudaStream_t)s->stream2);
+        if(s->stream3)cudaStreamDestroy((cudaStream_t)s->stream3);
+        for(void* e : s->events)cudaEventDestroy((cudaEvent_t)e);
     }
     delete s;
 }
@@ -105,69 +173,32 @@ int pt_scene_bounds(const pt_scene* s, float bmin[3], float bmax[3]){
 
 // ---- ray casting -------------------------------------------------------------------
 
-static int ensure_stage(pt_scene* s, size_t n){
-    DeviceBuffers& b = s->buf;
-    if(n <= b.stage_cap)return PT_OK;
-    void** ptrs[] = { &b.stage_rays, &b.stage_hits, &b.stage_inst, &b.stage_occ };
-    for(void** p : ptrs){ if(*p){ cudaFree(*p); *p = nullptr; } }
-    b.stage_cap = 0;
-    if(!cuda_ok(cudaMalloc(&b.stage_rays, n * sizeof(pt_ray)), "cudaMalloc rays") ||
-       !cuda_ok(cudaMalloc(&b.stage_hits, n * sizeof(pt_hit)), "cudaMalloc hits") ||
-       !cuda_ok(cudaMalloc(&b.stage_inst, n * sizeof(uint32_t)), "cudaMalloc inst") ||
-       !cuda_ok(cudaMalloc(&b.stage_occ, n), "cudaMalloc occ"))return PT_ERR_CUDA;
-    b.stage_cap = n;
-    return PT_OK;
-}
-
-// Host-buffer entry points.  The batch is cut into chunks that ping-pong over
-// two streams so that the H2D copy of chunk k+1, the kernel of chunk k and the
-// D2H copy of chunk k-1 overlap (full-duplex PCIe + compute).
-static const size_t kChunk = 1u << 20;
-
 int pt_trace_closest(pt_scene* s, const pt_ray* rays, size_t n, pt_hit* hits, uint32_t* inst){
     PT_CHECK_READY(s);
     if(n == 0)return PT_OK;
     if(!rays || !hits){ set_error("null buffer"); return PT_ERR_INVALID; }
-    int rc = ensure_stage(s, n);
-    if(rc != PT_OK)return rc;
     DeviceBuffers& b = s->buf;
-    cudaStream_t st[2] = { (cudaStream_t)s->stream, (cudaStream_t)s->stream2 };
-    int k = 0;
-    for(size_t off = 0; off < n; off += kChunk, k ^= 1){
-        const size_t m = n - off < kChunk ? n - off : kChunk;
-        pt_ray* dr = (pt_ray*)b.stage_rays + off;
-        pt_hit* dh = (pt_hit*)b.stage_hits + off;
-        uint32_t* di = (uint32_t*)b.stage_inst + off;
-        if(!cuda_ok(cudaMemcpyAsync(dr, rays + off, m * sizeof(pt_ray), cudaMemcpyHostToDevice, st[k]), "H2D rays"))return PT_ERR_CUDA;
-        rc = launch_trace_closest(s, dr, m, dh, inst ? di : nullptr, st[k]);
-        if(rc != PT_OK)return rc;
-        if(!cuda_ok(cudaMemcpyAsync(hits + off, dh, m * sizeof(pt_hit), cudaMemcpyDeviceToHost, st[k]), "D2H hits"))return PT_ERR_CUDA;
-        if(inst && !cuda_ok(cudaMemcpyAsync(inst + off, di, m * sizeof(uint32_t), cudaMemcpyDeviceToHost, st[k]), "D2H inst"))return PT_ERR_CUDA;
-    }
-    if(!cuda_ok(cudaStreamSynchronize(st[0]), "sync") || !cuda_ok(cudaStreamSynchronize(st[1]), "sync"))return PT_ERR_CUDA;
-    return PT_OK;
+    return trace_pipelined(s, rays, n,
+        [&](size_t off, size_t m, cudaStream_t st){
+            return launch_trace_closest(s, (pt_ray*)b.stage_rays + off, m, (pt_hit*)b.stage_hits + off, inst ? (uint32_t*)b.stage_inst + off : nullptr, st);
+        },
+        [&](size_t off, size_t m, cudaStream_t st){
+            if(!cuda_ok(cudaMemcpyAsync(hits + off, (pt_hit*)b.stage_hits + off, m * sizeof(pt_hit), cudaMemcpyDeviceToHost, st), "D2H hits"))return (int)PT_ERR_CUDA;
+            if(inst && !cuda_ok(cudaMemcpyAsync(inst + off, (uint32_t*)b.stage_inst + off, m * sizeof(uint32_t), cudaMemcpyDeviceToHost, st), "D2H inst"))return (int)PT_ERR_CUDA;
+            return (int)PT_OK;
+        });
 }
 
 int pt_trace_any(pt_scene* s, const pt_ray* rays, size_t n, uint8_t* occluded){
     PT_CHECK_READY(s);
     if(n == 0)return PT_OK;
     if(!rays || !occluded){ set_error("null buffer"); return PT_ERR_INVALID; }
-    int rc = ensure_stage(s, n);
-    if(rc != PT_OK)return rc;
     DeviceBuffers& b = s->buf;
-    cudaStream_t st[2] = { (cudaStream_t)s->stream, (cudaStream_t)s->stream2 };
-    int k = 0;
-    for(size_t off = 0; off < n; off += kChunk, k ^= 1){
-        const size_t m = n - off < kChunk ? n - off : kChunk;
-        pt_ray* dr = (pt_ray*)b.stage_rays + off;
-        uint8_t* dc = (uint8_t*)b.stage_occ + off;
-        if(!cuda_ok(cudaMemcpyAsync(dr, rays + off, m * sizeof(pt_ray), cudaMemcpyHostToDevice, st[k]), "H2D rays"))return PT_ERR_CUDA;
-        rc = launch_trace_any(s, dr, m, dc, st[k]);
-        if(rc != PT_OK)return rc;
-        if(!cuda_ok(cudaMemcpyAsync(occluded + off, dc, m, cudaMemcpyDeviceToHost, st[k]), "D2H occ"))return PT_ERR_CUDA;
-    }
-    if(!cuda_ok(cudaStreamSynchronize(st[0]), "sync") || !cuda_ok(cudaStreamSynchronize(st[1]), "sync"))return PT_ERR_CUDA;
-    return PT_OK;
+    return trace_pipelined(s, rays, n,
+        [&](size_t off, size_t m, cudaStream_t st){ return launch_trace_any(s, (pt_ray*)b.stage_rays + off, m, (uint8_t*)b.stage_occ + off, st); },
+        [&](size_t off, size_t m, cudaStream_t st){
+            return cuda_ok(cudaMemcpyAsync(occluded + off, (uint8_t*)b.stage_occ + off, m, cudaMemcpyDeviceToHost, st), "D2H occ") ? (int)PT_OK : (int)PT_ERR_CUDA;
+        });
 }
 
 int pt_trace_closest_dev(pt_scene* s, const void* d_rays, size_t n, void* d_hits, void* d_inst, void* stream){

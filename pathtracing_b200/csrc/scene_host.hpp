@@ -90,8 +90,9 @@ struct pt_scene {
     int film_w = 0, film_h = 0;
     uint64_t total_tris = 0, total_nodes = 0;
     void* stream = nullptr;       // internal stream for the host-buffer entry points
-    void* stream2 = nullptr;
-    void* ev[4] = { nullptr, nullptr, nullptr, nullptr };
+    void* stream2 = nullptr;      // H2D stage of the host-buffer pipeline
+    void* stream3 = nullptr;      // D2H stage
+    std::vector<void*> events;    // cudaEvent_t pool of the pipeline (no timing)
     unsigned cursor_next = 0;
     bool has_alpha_tex = false;   // some triangle carries TRI_ALPHA_TEX: traversal must evaluate Material::Alpha
     bool has_boundary = false;    // some primitive has no material (a medium boundary): VolPath shadow rays walk through it
