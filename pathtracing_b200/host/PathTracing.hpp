@@ -769,9 +769,9 @@ inline double linear_to_sRGB(double linear){
 class Film {
 public:
     Film(const glm::ivec2& resolution, const std::shared_ptr<Filter>& filter, double maxComponentValue = std::numeric_limits<double>::infinity())
-        : xResolution(resolution.x), yResolution(resolution.y), screen(4 * (size_t)resolution.x * resolution.y, 0.0), filter(filter){
-        if(std::isfinite(maxComponentValue))throw std::invalid_argument("Film: maxComponentValue clamping is not available on the GPU path");
-    }
+        : xResolution(resolution.x), yResolution(resolution.y), screen(4 * (size_t)resolution.x * resolution.y, 0.0), filter(filter), maxComponent(maxComponentValue){}
+    // stored and never read, exactly as in the reference (Film.hpp:114,270: no sample is ever clamped there)
+    double MaxComponentValue() const{ return maxComponent; }
     void Clear(){ screen.assign(screen.size(), 0.0); }
     glm::ivec2 Resolution() const{ return { xResolution, yResolution }; }
     const std::shared_ptr<Filter>& GetFilter() const{ return filter; }
@@ -855,6 +855,7 @@ private:
     int xResolution, yResolution;
     std::vector<double> screen;             // RGB sums * w and weight sums, 4 doubles per pixel
     std::shared_ptr<Filter> filter;
+    double maxComponent;
     std::string outputPath;
 };
 
