@@ -198,6 +198,39 @@ PT_API int pt_scene_set_medium(pt_scene*, int medium_id); /* Scene::SetMedium  *
  * bvh_width in {2,4,8} (BLAS8/TLAS8, BVH.hpp:1228-1552).  light_sampler: 0 Uniform, 1 Power (LightSampler.cpp). */
 PT_API int pt_scene_commit(pt_scene*, int bvh_width, int light_sampler);
 
+/* Where the binary binned-SAH build (BVHBase::BuildBaseThreaded, BVH.hpp:290-390) of every BLAS and of the
+ * TLAS runs.  PT_BUILDER_GPU takes the same decisions with the same float operations on the device
+ * (csrc/bvh_build_gpu.cu) and yields the same tree and leaf order as PT_BUILDER_HOST, so the packed
+ * BVH2 / BVH4 / BVH8 arrays are byte-identical; hierarchies under 4096 items stay on the host (launch
+ * overhead).  Call before pt_scene_commit.                                                              */
+typedef enum pt_builder { PT_BUILDER_HOST = 0, PT_BUILDER_GPU = 1 } pt_builder;
+PT_API int pt_scene_set_builder(pt_scene*, int builder);
+
+typedef struct pt_build_stats {   /* wall-clock split of the last pt_scene_commit */
+    double total_s;
+    double pack_s;          /* triangle records + BVH builds + flattening (includes bvh2_s, flatten_s) */
+    double bvh2_s;          /* binary SAH builds (host: CPU time; GPU: upload + kernels + download)    */
+    double flatten_s;       /* BuildBVH2 / buildBVH4 / buildBVH8 collapse (host)                      */
+    double upload_s;        /* traversal arrays H2D                                                   */
+    double shade_tables_s;  /* shading / light tables + their upload                                  */
+    float gpu_build_ms;     /* PT_BUILDER_GPU: build kernels (CUDA events)                            */
+    float gpu_upload_ms, gpu_download_ms;
+    int32_t builder, gpu_levels;
+    uint32_t gpu_subtrees;
+    uint64_t gpu_items;     /* items that went through the GPU builder                                */
+} pt_build_stats;
+PT_API int pt_scene_build_stats(const pt_scene*, pt_build_stats*);
+
+/* Stand-alone binary build = BVHBase::BuildBVHBase (BVH.hpp:95-105) over n boxes {lo[3], hi[3]}.
+ * nodes[0] is the root, nodes are numbered in DFS preorder (left subtree first); inner: count = 0,
+ * left / right = children, axis = split axis; leaf: right = first item (position in `order`), count > 0.
+ * order[n]: item index per leaf-order position.  node_capacity >= 2n - 1.  builder as above; PT_BUILDER_HOST
+ * needs no device.                                                                                       */
+typedef struct pt_bvh2_node { float lo[3], hi[3]; uint32_t left, right, count, axis; } pt_bvh2_node;
+PT_API int pt_build_bvh2(int device, int builder, const float* boxes6, uint32_t n,
+                         pt_bvh2_node* nodes, uint32_t node_capacity, uint32_t* n_nodes, uint32_t* order,
+                         float* gpu_build_ms);
+
 /* scene bounds after commit: Scene::BoundingBox (Scene.cpp:45-47)           */
 PT_API int pt_scene_bounds(const pt_scene*, float bmin[3], float bmax[3]);
 

@@ -83,6 +83,17 @@ class pt_trace_stats(C.Structure):
                 ("instances", C.c_uint64), ("triangles", C.c_uint64), ("hits", C.c_uint64)]
 
 
+class pt_build_stats(C.Structure):
+    _fields_ = [("total_s", C.c_double), ("pack_s", C.c_double), ("bvh2_s", C.c_double), ("flatten_s", C.c_double),
+                ("upload_s", C.c_double), ("shade_tables_s", C.c_double), ("gpu_build_ms", C.c_float),
+                ("gpu_upload_ms", C.c_float), ("gpu_download_ms", C.c_float), ("builder", C.c_int32),
+                ("gpu_levels", C.c_int32), ("gpu_subtrees", C.c_uint32), ("gpu_items", C.c_uint64)]
+
+
+BVH2_NODE_DTYPE = np.dtype([("lo", "<f4", 3), ("hi", "<f4", 3), ("left", "<u4"), ("right", "<u4"), ("count", "<u4"), ("axis", "<u4")])
+assert BVH2_NODE_DTYPE.itemsize == 40
+BUILDER_HOST, BUILDER_GPU = range(2)
+
 RAY_DTYPE = np.dtype([("o", "<f4", 3), ("tmax", "<f4"), ("d", "<f4", 3), ("time", "<f4")])
 HIT_DTYPE = np.dtype([("t", "<f4"), ("u", "<f4"), ("v", "<f4"), ("prim", "<u4")])
 assert RAY_DTYPE.itemsize == 32 and HIT_DTYPE.itemsize == 16
@@ -100,7 +111,7 @@ EXPORTS = [
     "pt_device_count", "pt_scene_create", "pt_scene_destroy", "pt_last_error",
     "pt_scene_add_texture", "pt_scene_add_material", "pt_scene_add_medium", "pt_scene_add_mesh",
     "pt_scene_add_blas", "pt_scene_add_instance", "pt_scene_add_shape", "pt_scene_add_light", "pt_scene_set_medium",
-    "pt_scene_commit", "pt_scene_bounds", "pt_trace_closest", "pt_trace_any",
+    "pt_scene_commit", "pt_scene_set_builder", "pt_scene_build_stats", "pt_build_bvh2", "pt_scene_bounds", "pt_trace_closest", "pt_trace_any",
     "pt_trace_closest_dev", "pt_trace_any_dev", "pt_trace_closest_stats", "pt_render",
     "pt_film_device_ptr", "pt_film_download", "pt_film_download_sumsq", "pt_film_upload",
 ]
@@ -142,6 +153,12 @@ def load_library(path: os.PathLike | None = None) -> C.CDLL:
     lib.pt_scene_set_medium.argtypes = [vp, i]
     lib.pt_scene_commit.restype = i
     lib.pt_scene_commit.argtypes = [vp, i, i]
+    lib.pt_scene_set_builder.restype = i
+    lib.pt_scene_set_builder.argtypes = [vp, i]
+    lib.pt_scene_build_stats.restype = i
+    lib.pt_scene_build_stats.argtypes = [vp, C.POINTER(pt_build_stats)]
+    lib.pt_build_bvh2.restype = i
+    lib.pt_build_bvh2.argtypes = [i, i, vp, C.c_uint32, vp, C.c_uint32, C.POINTER(C.c_uint32), vp, C.POINTER(C.c_float)]
     lib.pt_scene_bounds.restype = i
     lib.pt_scene_bounds.argtypes = [vp, C.POINTER(C.c_float), C.POINTER(C.c_float)]
     lib.pt_trace_closest.restype = i
@@ -167,3 +184,20 @@ def load_library(path: os.PathLike | None = None) -> C.CDLL:
     if path is None:
         _lib = lib
     return lib
+
+
+def build_bvh2(boxes: np.ndarray, builder: int = BUILDER_HOST, device: int = 0):
+    """pt_build_bvh2: binary binned-SAH build over (n, 6) float32 boxes {lo, hi}.
+    Returns (nodes[BVH2_NODE_DTYPE] in DFS preorder, order[u32], gpu_build_ms)."""
+    lib = load_library()
+    boxes = np.ascontiguousarray(boxes, dtype=np.float32).reshape(-1, 6)
+    n = len(boxes)
+    cap = max(2 * n - 1, 1)
+    nodes = np.zeros(cap, dtype=BVH2_NODE_DTYPE)
+    order = np.zeros(max(n, 1), dtype=np.uint32)
+    nn = C.c_uint32(0)
+    ms = C.c_float(0)
+    rc = lib.pt_build_bvh2(device, builder, boxes.ctypes.data, n, nodes.ctypes.data, cap, C.byref(nn), order.ctypes.data, C.byref(ms))
+    if rc < 0:
+        raise PtError(f"pt error {rc}: {lib.pt_last_error().decode()}")
+    return nodes[:nn.value], order[:n], ms.value

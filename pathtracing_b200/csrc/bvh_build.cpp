@@ -1,6 +1,7 @@
 // bvh_build.cpp — see bvh_build.hpp.  Compiled with -ffp-contract=off: the SAH
 // costs decide the topology and must not depend on FMA contraction.
 #include "bvh_build.hpp"
+#include "scene_host.hpp"
 #include <cstring>
 
 #include <atomic>
@@ -388,6 +389,25 @@ FlatBvh flatten_bvh(const BinaryBvh& b, int width){
         f.root = flatten8(f, b, 0);
     }
     return f;
+}
+
+BinaryBvh canonical_bvh(const BinaryBvh& b){
+    BinaryBvh out;
+    out.order = b.order;
+    if(b.nodes.empty())return out;
+    out.nodes.reserve(b.nodes.size());
+    struct Item { uint32_t src, parent; bool is_right; };
+    std::vector<Item> stack;
+    stack.push_back({ 0u, 0xFFFFFFFFu, false });
+    while(!stack.empty()){
+        const Item it = stack.back(); stack.pop_back();
+        const uint32_t me = (uint32_t)out.nodes.size();
+        out.nodes.push_back(b.nodes[it.src]);
+        if(it.parent != 0xFFFFFFFFu){ if(it.is_right)out.nodes[it.parent].right = me; else out.nodes[it.parent].left = me; }
+        const BuildNode& n = b.nodes[it.src];
+        if(n.count == 0){ stack.push_back({ n.right, me, true }); stack.push_back({ n.left, me, false }); }
+    }
+    return out;
 }
 
 // ---- small matrix helpers (column-major, glm operation order) -----------------------

@@ -164,6 +164,47 @@ int pt_scene_commit(pt_scene* s, int bvh_width, int light_sampler){
     return scene_commit(s, bvh_width, light_sampler);
 }
 
+int pt_scene_set_builder(pt_scene* s, int builder){
+    PT_CHECK_OPEN(s);
+    if(builder != PT_BUILDER_HOST && builder != PT_BUILDER_GPU){ set_error("unknown builder"); return PT_ERR_INVALID; }
+    s->builder = builder;
+    return PT_OK;
+}
+
+int pt_scene_build_stats(const pt_scene* s, pt_build_stats* out){
+    PT_CHECK_SCENE(s);
+    if(!out){ set_error("null stats"); return PT_ERR_INVALID; }
+    if(!s->committed){ set_error("scene not committed"); return PT_ERR_STATE; }
+    *out = s->build_stats;
+    return PT_OK;
+}
+
+int pt_build_bvh2(int device, int builder, const float* boxes6, uint32_t n, pt_bvh2_node* nodes, uint32_t node_capacity,
+                  uint32_t* n_nodes, uint32_t* order, float* gpu_build_ms){
+    static_assert(sizeof(pt_bvh2_node) == sizeof(BuildNode), "pt_bvh2_node must match BuildNode");
+    if(!boxes6 || !nodes || !n_nodes || !order){ set_error("null buffer"); return PT_ERR_INVALID; }
+    if(n == 0){ *n_nodes = 0; return PT_OK; }
+    if((uint64_t)node_capacity < 2ull * n - 1){ set_error("node_capacity must be >= 2n - 1"); return PT_ERR_INVALID; }
+    BinaryBvh b;
+    if(builder == PT_BUILDER_HOST)b = build_binary_bvh((const Box*)boxes6, n);
+    else if(builder == PT_BUILDER_GPU){
+        const int nd = pt_device_count();
+        if(nd <= 0){ set_error("no CUDA device: pathtracing_b200 has no CPU fallback"); return PT_ERR_NO_DEVICE; }
+        if(device < 0 || device >= nd){ set_error("bad device index"); return PT_ERR_INVALID; }
+        if(!cuda_ok(cudaSetDevice(device), "cudaSetDevice"))return PT_ERR_CUDA;
+        GpuBuildTimes gt;
+        const int rc = build_binary_bvh_gpu((const Box*)boxes6, n, 2, b, &gt);
+        if(rc != PT_OK)return rc;
+        if(gpu_build_ms)*gpu_build_ms = gt.build_ms;
+    } else{ set_error("unknown builder"); return PT_ERR_INVALID; }
+    const BinaryBvh c = canonical_bvh(b);
+    if(c.nodes.size() > node_capacity){ set_error("internal: node count exceeds 2n - 1"); return PT_ERR_INVALID; }
+    memcpy(nodes, c.nodes.data(), c.nodes.size() * sizeof(BuildNode));
+    memcpy(order, c.order.data(), (size_t)n * 4);
+    *n_nodes = (uint32_t)c.nodes.size();
+    return PT_OK;
+}
+
 int pt_scene_bounds(const pt_scene* s, float bmin[3], float bmax[3]){
     PT_CHECK_SCENE(s);
     if(!s->committed){ set_error("scene not committed"); return PT_ERR_STATE; }

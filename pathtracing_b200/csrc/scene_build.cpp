@@ -1,6 +1,7 @@
 // scene_build.cpp — host-only half of the scene object: validation of the POD
 // description and packing of BLAS/TLAS into the device layout (no CUDA calls,
 // so the same code is exercised by the CPU-side emulation tests).
+#include <chrono>
 #include <cmath>
 #include <cstring>
 
@@ -184,7 +185,7 @@ static void pack_shape(const pt_shape_desc& d, Instance& I){
     I.bhi0 = I.inv[9] * d.p[0] + I.inv[10] * d.p[1] + I.inv[11] * d.p[2];
 }
 
-int pack_traversal(pt_scene* s, int width, PackedTraversal& P){
+int pack_traversal(pt_scene* s, int width, PackedTraversal& P, BvhBuilder builder, void* user){
     if(width != 2 && width != 4 && width != 8){ set_error("bvh_width must be 2, 4 or 8"); return PT_ERR_INVALID; }
     if(s->instances.empty()){ set_error("scene has no instances"); return PT_ERR_INVALID; }
     std::vector<Bvh2Node>& n2 = P.n2;
@@ -219,8 +220,15 @@ int pack_traversal(pt_scene* s, int width, PackedTraversal& P){
                 T.prim = g; T.mesh = (uint32_t)mi; T.flags = flags;
             }
         }
-        BinaryBvh bb = build_binary_bvh(boxes.data(), hb.n_tris);
+        const auto tb0 = std::chrono::steady_clock::now();
+        BinaryBvh bb;
+        if(builder){ const int brc = builder(boxes.data(), hb.n_tris, bb, user); if(brc != PT_OK)return brc; }
+        else bb = build_binary_bvh(boxes.data(), hb.n_tris);
+        const auto tb1 = std::chrono::steady_clock::now();
         FlatBvh fb = flatten_bvh(bb, width);
+        const auto tb2 = std::chrono::steady_clock::now();
+        s->build_stats.bvh2_s += std::chrono::duration<double>(tb1 - tb0).count();
+        s->build_stats.flatten_s += std::chrono::duration<double>(tb2 - tb1).count();
         hb.tri_base = (uint32_t)tris.size();
         hb.bounds = fb.bounds;
         const uint32_t node_base = width == 2 ? (uint32_t)n2.size() : width == 4 ? (uint32_t)n4.size() : (uint32_t)P.n8.size();
@@ -258,8 +266,14 @@ int pack_traversal(pt_scene* s, int width, PackedTraversal& P){
         const Box& bb = s->blas[hi.blas].bounds;
         iboxes[i] = hi.has_xf ? transform_box(hi.xf, bb) : bb;
     }
-    BinaryBvh tb = build_binary_bvh(iboxes.data(), ni);
+    const auto tt0 = std::chrono::steady_clock::now();
+    BinaryBvh tb;
+    if(builder){ const int brc = builder(iboxes.data(), ni, tb, user); if(brc != PT_OK)return brc; }
+    else tb = build_binary_bvh(iboxes.data(), ni);
+    const auto tt1 = std::chrono::steady_clock::now();
     FlatBvh tf = flatten_bvh(tb, width);
+    s->build_stats.bvh2_s += std::chrono::duration<double>(tt1 - tt0).count();
+    s->build_stats.flatten_s += std::chrono::duration<double>(std::chrono::steady_clock::now() - tt1).count();
     s->bounds = tf.bounds;
     const uint32_t tnode_base = width == 2 ? (uint32_t)n2.size() : width == 4 ? (uint32_t)n4.size() : (uint32_t)P.n8.size();
     auto trebase = [&](uint32_t ref) -> uint32_t{

@@ -2,7 +2,9 @@
 // one upload.  Replaces Model::BuildBlas (Model.hpp:41-60) + Scene::BuildTlas
 // (Scene.hpp:20-24) + the light-sampler wiring of examples/example_1.cpp:99-101.
 #include <cuda_runtime.h>
+#include <chrono>
 #include <cmath>
+#include <cstdlib>
 #include <cstring>
 #include <thread>
 
@@ -44,9 +46,20 @@ int scene_commit(pt_scene* s, int width, int light_sampler){
     s->width = width;
     s->light_sampler = light_sampler;
 
+    const auto t0 = std::chrono::steady_clock::now();
+    s->build_stats = pt_build_stats {};
+    s->build_stats.builder = s->builder;
+    GpuBuildTimes gt;
+    // small hierarchies (a TLAS of a few instances, a two-triangle light) are not worth the launches
+    static const uint32_t gpu_min = []{ const char* e = getenv("PTB_GPU_BUILD_MIN"); return e ? (uint32_t)atoll(e) : 4096u; }();
+    auto gpu_builder = [](const Box* boxes, uint32_t n, BinaryBvh& out, void* user) -> int{
+        if(n < gpu_min){ out = build_binary_bvh(boxes, n); return PT_OK; }
+        return build_binary_bvh_gpu(boxes, n, 2, out, (GpuBuildTimes*)user);
+    };
     PackedTraversal P;
-    int prc = pack_traversal(s, width, P);
+    int prc = s->builder == PT_BUILDER_GPU ? pack_traversal(s, width, P, gpu_builder, &gt) : pack_traversal(s, width, P);
     if(prc != PT_OK)return prc;
+    const auto t1 = std::chrono::steady_clock::now();
     std::vector<Bvh2Node>& n2 = P.n2;
     std::vector<Bvh4Node>& n4 = P.n4;
     std::vector<Tri>& tris = P.tris;
@@ -68,6 +81,7 @@ int scene_commit(pt_scene* s, int width, int light_sampler){
     s->total_tris = tris.size();
     s->total_nodes = width == 2 ? n2.size() : width == 4 ? n4.size() : P.n8.size();
 
+    const auto t2 = std::chrono::steady_clock::now();
     int rc = build_shade_tables(s, P.inst_order);
     if(rc != PT_OK){ scene_free_device(s); return rc; }
 
@@ -79,6 +93,12 @@ int scene_commit(pt_scene* s, int width, int light_sampler){
     if(!cuda_ok(cudaMalloc(&b.stats, 64), "cudaMalloc stats") ||
        !cuda_ok(cudaMalloc(&b.cursors, kCursorRing * sizeof(unsigned long long)), "cudaMalloc cursors")){ scene_free_device(s); return PT_ERR_CUDA; }
     s->committed = true;
+    const auto t3 = std::chrono::steady_clock::now();
+    auto sec = [](auto a, auto b){ return std::chrono::duration<double>(b - a).count(); };
+    pt_build_stats& bs = s->build_stats;
+    bs.total_s = sec(t0, t3); bs.pack_s = sec(t0, t1); bs.upload_s = sec(t1, t2); bs.shade_tables_s = sec(t2, t3);
+    bs.gpu_build_ms = gt.build_ms; bs.gpu_upload_ms = gt.upload_ms; bs.gpu_download_ms = gt.download_ms;
+    bs.gpu_levels = gt.levels; bs.gpu_subtrees = gt.subtrees; bs.gpu_items = gt.items;
     return PT_OK;
 }
 

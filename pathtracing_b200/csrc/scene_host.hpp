@@ -67,6 +67,14 @@ struct DeviceBuffers {
 
 constexpr unsigned kCursorRing = 256;
 
+// bvh_build_gpu.cu: accumulated over the BLAS / TLAS builds of one commit
+struct GpuBuildTimes {
+    float upload_ms = 0, build_ms = 0, download_ms = 0;
+    int levels = 0;              // level-synchronous rounds of the large phase
+    uint32_t subtrees = 0;       // shared-memory subtree CTAs
+    uint64_t items = 0;
+};
+
 } // namespace ptb
 
 struct pt_scene {
@@ -97,6 +105,8 @@ struct pt_scene {
     bool has_alpha_tex = false;   // some triangle carries TRI_ALPHA_TEX: traversal must evaluate Material::Alpha
     bool has_boundary = false;    // some primitive has no material (a medium boundary): VolPath shadow rays walk through it
     uint64_t alpha_salt = 0;      // advances per launch (AlphaTester Blend draws)
+    int builder = 0;              // pt_builder: where the binary SAH build runs
+    pt_build_stats build_stats {};
 };
 
 namespace ptb {
@@ -122,7 +132,13 @@ int scene_add_blas(pt_scene* s, const int32_t* mesh_ids, int n);
 int scene_add_instance(pt_scene* s, int blas_id, const float* xf);
 int scene_add_shape(pt_scene* s, const pt_shape_desc* d);
 int scene_add_light(pt_scene* s, const pt_light_desc* d);
-int pack_traversal(pt_scene* s, int width, PackedTraversal& out);
+// builder: binary build used for every BLAS and the TLAS (null = build_binary_bvh on the host); returns PT_OK or an error
+using BvhBuilder = int (*)(const Box* boxes, uint32_t n, BinaryBvh& out, void* user);
+int pack_traversal(pt_scene* s, int width, PackedTraversal& out, BvhBuilder builder = nullptr, void* user = nullptr);
+int build_binary_bvh_gpu(const Box* boxes, uint32_t n, uint32_t leaf_size, BinaryBvh& out, GpuBuildTimes* times);   // bvh_build_gpu.cu
+// BinaryBvh with nodes renumbered in DFS preorder (left subtree first), the host builder's own numbering
+// below 256 Ki items; makes trees from different builders comparable array by array
+BinaryBvh canonical_bvh(const BinaryBvh& b);
 
 void set_error(const std::string& msg);
 const char* get_error();

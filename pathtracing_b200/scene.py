@@ -235,15 +235,21 @@ def render_params(width, height, spp, max_depth, integrator=capi.INTEGRATOR_PATH
 class GpuScene:
     """A committed scene on one B200, through the C-ABI only."""
 
-    def __init__(self, desc: SceneDesc, bvh_width=4, light_sampler=1, device=0):
+    def __init__(self, desc: SceneDesc, bvh_width=4, light_sampler=1, device=0, builder=capi.BUILDER_HOST):
         self.lib = capi.load_library()
         self.h = self.lib.pt_scene_create(device)
         if not self.h:
             raise PtError(self._err())
         self.desc = desc
         desc.replay(self)
+        self._ck(self.lib.pt_scene_set_builder(self.h, builder))
         self._ck(self.lib.pt_scene_commit(self.h, bvh_width, light_sampler))
         self.bvh_width = bvh_width
+
+    def build_stats(self) -> dict:
+        st = capi.pt_build_stats()
+        self._ck(self.lib.pt_scene_build_stats(self.h, C.byref(st)))
+        return {k: getattr(st, k) for k, _ in st._fields_}
 
     def _err(self):
         return self.lib.pt_last_error().decode()
