@@ -313,6 +313,15 @@ typedef struct pt_render_stats {
 /* Integrator::Render (Integrators.cpp:23-129) for the params' sample passes.
  * Accumulates into the scene's device film (double RGBW, W*H*4), creating or
  * clearing it when `clear` != 0.                                             */
+/* Multi-GPU adaptive sampling: when the sample passes of an adaptive render are sharded over
+ * ranks (pass_begin / pass_stride), every rank must apply the stopping rule of Integrators.cpp:82-85 to the
+ * SAME per-pixel statistics.  After each round pt_render calls `sum(user, d_buf, n, stream)`, which must add
+ * the n doubles at device pointer d_buf over all ranks in place (ncclAllReduce / torch.distributed.all_reduce)
+ * and return 0 once the result is visible to work queued on `stream` (a cudaStream_t).  Not needed for
+ * fixed-spp renders, whose only collective is the final film reduce.                                       */
+typedef int (*pt_allreduce_fn)(void* user, void* d_buf, size_t n_doubles, void* stream);
+PT_API int pt_scene_set_allreduce(pt_scene*, pt_allreduce_fn sum, void* user);
+
 PT_API int pt_render(pt_scene*, const pt_camera_desc*, const pt_render_params*,
                      int clear, pt_render_stats* stats);
 /* device film pointer (double[4*W*H], RGB sums * w and weight sums) for the

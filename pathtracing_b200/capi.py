@@ -90,6 +90,8 @@ class pt_build_stats(C.Structure):
                 ("gpu_levels", C.c_int32), ("gpu_subtrees", C.c_uint32), ("gpu_items", C.c_uint64)]
 
 
+ALLREDUCE_FN = C.CFUNCTYPE(C.c_int, C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p)     # pt_allreduce_fn
+
 BVH2_NODE_DTYPE = np.dtype([("lo", "<f4", 3), ("hi", "<f4", 3), ("left", "<u4"), ("right", "<u4"), ("count", "<u4"), ("axis", "<u4")])
 assert BVH2_NODE_DTYPE.itemsize == 40
 BUILDER_HOST, BUILDER_GPU = range(2)
@@ -111,7 +113,7 @@ EXPORTS = [
     "pt_device_count", "pt_scene_create", "pt_scene_destroy", "pt_last_error",
     "pt_scene_add_texture", "pt_scene_add_material", "pt_scene_add_medium", "pt_scene_add_mesh",
     "pt_scene_add_blas", "pt_scene_add_instance", "pt_scene_add_shape", "pt_scene_add_light", "pt_scene_set_medium",
-    "pt_scene_commit", "pt_scene_set_builder", "pt_scene_build_stats", "pt_build_bvh2", "pt_scene_bounds", "pt_trace_closest", "pt_trace_any",
+    "pt_scene_commit", "pt_scene_set_builder", "pt_scene_set_allreduce", "pt_scene_build_stats", "pt_build_bvh2", "pt_scene_bounds", "pt_trace_closest", "pt_trace_any",
     "pt_trace_closest_dev", "pt_trace_any_dev", "pt_trace_closest_stats", "pt_render",
     "pt_film_device_ptr", "pt_film_download", "pt_film_download_sumsq", "pt_film_upload",
 ]
@@ -155,6 +157,8 @@ def load_library(path: os.PathLike | None = None) -> C.CDLL:
     lib.pt_scene_commit.argtypes = [vp, i, i]
     lib.pt_scene_set_builder.restype = i
     lib.pt_scene_set_builder.argtypes = [vp, i]
+    lib.pt_scene_set_allreduce.restype = i
+    lib.pt_scene_set_allreduce.argtypes = [vp, ALLREDUCE_FN, vp]
     lib.pt_scene_build_stats.restype = i
     lib.pt_scene_build_stats.argtypes = [vp, C.POINTER(pt_build_stats)]
     lib.pt_build_bvh2.restype = i

@@ -171,6 +171,12 @@ int pt_scene_set_builder(pt_scene* s, int builder){
     return PT_OK;
 }
 
+int pt_scene_set_allreduce(pt_scene* s, pt_allreduce_fn sum, void* user){
+    PT_CHECK_SCENE(s);
+    s->allreduce = sum; s->allreduce_user = user;
+    return PT_OK;
+}
+
 int pt_scene_build_stats(const pt_scene* s, pt_build_stats* out){
     PT_CHECK_SCENE(s);
     if(!out){ set_error("null stats"); return PT_ERR_INVALID; }

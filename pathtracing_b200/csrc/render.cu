@@ -65,7 +65,7 @@ __device__ __forceinline__ uint64_t stream_of(const BatchInfo& B, uint64_t g, ui
     const uint64_t wh = (uint64_t)B.W * B.H;
     if(B.list){
         pixel = B.list[g % B.n_list];
-        sample = B.sample_base + (uint32_t)(g / B.n_list);
+        sample = B.sample_base + (uint32_t)B.pass_begin + (uint32_t)(g / B.n_list) * (uint32_t)B.pass_stride;
     } else{
         pixel = (uint32_t)(g % wh);
         sample = (uint32_t)(B.pass_begin + (g / wh) * B.pass_stride);
@@ -292,6 +292,12 @@ __global__ void __launch_bounds__(256) k_adapt(const double* __restrict__ est, c
     }
     const uint32_t at = queue_slot(n_out, more);
     if(more)out[at] = pixel;
+}
+
+// est += round; round = 0 (sharded adaptive rounds, after the all-reduce of `round`)
+__global__ void __launch_bounds__(256) k_est_merge(double* __restrict__ est, double* __restrict__ round, size_t n){
+    const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if(i < n){ est[i] += round[i]; round[i] = 0.0; }
 }
 
 // ---- shade: one bounce of Li() for every queue entry ------------------------------------------
@@ -581,8 +587,9 @@ int render_passes(pt_scene* s, const pt_camera_desc* cam, const pt_render_params
     if(rp->sampler != 0 && rp->sampler != 1){ set_error("unknown sampler"); return PT_ERR_INVALID; }
     if(rp->sampler == 1 && (rp->strata_x <= 0 || rp->strata_y <= 0 || rp->strata_x * rp->strata_y != rp->spp)){
         set_error("StratifiedSampler: spp must equal strata_x * strata_y (Sampler.hpp:84)"); return PT_ERR_INVALID; }
-    if(rp->adaptive && (rp->pass_begin != 0 || rp->pass_stride != 1)){
-        set_error("adaptive sampling decides per pixel from all of its samples: it cannot be combined with pass sharding"); return PT_ERR_INVALID; }
+    const bool sharded_adaptive = rp->adaptive && (rp->pass_begin != 0 || rp->pass_stride != 1);
+    if(sharded_adaptive && !s->allreduce){
+        set_error("adaptive sampling decides per pixel from all of its samples: with pass sharding the ranks must sum their per-pixel statistics every round (pt_scene_set_allreduce)"); return PT_ERR_INVALID; }
     if(cam->medium >= (int)s->media.size()){ set_error("camera medium id out of range"); return PT_ERR_INVALID; }
     FilterParams F;
     int rc = make_filter(rp, F);
@@ -618,9 +625,9 @@ int render_passes(pt_scene* s, const pt_camera_desc* cam, const pt_render_params
     arena_layout((char*)b.work, A, cap);
     // adaptive loop state: estimator sums (6 doubles / pixel), two pixel lists, a counter
     const size_t npix = (size_t)W * H;
-    double* est = nullptr; uint32_t* lists[2] = { nullptr, nullptr }; uint32_t* list_n = nullptr;
+    double* est = nullptr; double* est_round = nullptr; uint32_t* lists[2] = { nullptr, nullptr }; uint32_t* list_n = nullptr;
     if(rp->adaptive){
-        const size_t bytes = npix * (48 + 8) + 256;
+        const size_t bytes = npix * (48 + 8 + (sharded_adaptive ? 48 : 0)) + 256;
         if(bytes > b.adapt_bytes){
             if(b.adapt){ cudaFree(b.adapt); b.adapt = nullptr; b.adapt_bytes = 0; }
             if(!cuda_ok(cudaMalloc(&b.adapt, bytes), "cudaMalloc adaptive state"))return PT_ERR_NOMEM;
@@ -629,6 +636,12 @@ int render_passes(pt_scene* s, const pt_camera_desc* cam, const pt_render_params
         est = (double*)b.adapt;
         lists[0] = (uint32_t*)(est + 6 * npix); lists[1] = lists[0] + npix; list_n = lists[1] + npix;
         if(!cuda_ok(cudaMemsetAsync(est, 0, 48 * npix, st), "estimator clear"))return PT_ERR_CUDA;
+        if(sharded_adaptive){
+            // this rank's sums of the current round; after the all-reduce they are added to `est`, which
+            // therefore holds the same global totals on every rank
+            est_round = (double*)((char*)b.adapt + npix * (48 + 8) + 256);
+            if(!cuda_ok(cudaMemsetAsync(est_round, 0, 48 * npix, st), "estimator clear"))return PT_ERR_CUDA;
+        }
     }
     // pinned once per scene: cudaMallocHost / cudaFreeHost per frame cost milliseconds (more with other
     // large pinned buffers mapped in the process) and synchronise the device
@@ -656,12 +669,13 @@ int render_passes(pt_scene* s, const pt_camera_desc* cam, const pt_render_params
         B.list = list; B.n_list = n_list; B.sample_base = sample_base;
         B.tr_walk = tr_walk ? 1 : 0;
         uint64_t next_gid = 0;
+        if(count == 0)return PT_OK;                   // more ranks than samples per round
         if(rp->max_depth <= 0){
             // `depth++ < maxDepth` fails at once: black samples that still carry their filter weight
             while(next_gid < count){
                 const uint32_t m = (uint32_t)std::min<uint64_t>(cap, count - next_gid);
                 k_generate<<<(m + 255) / 256, 256, 0, st>>>(A, B, C, m, next_gid, nullptr, 0, 0);
-                k_film<<<(m + 255) / 256, 256, 0, st>>>(A, B, F, (double*)b.film, (double*)b.film_sq, est, nullptr, m);
+                k_film<<<(m + 255) / 256, 256, 0, st>>>(A, B, F, (double*)b.film, (double*)b.film_sq, est_round ? est_round : est, nullptr, m);
                 R.kernel_launches += 2; R.samples += m; next_gid += m;
             }
             return PT_OK;
@@ -706,7 +720,7 @@ int render_passes(pt_scene* s, const pt_camera_desc* cam, const pt_render_params
             }
             if(n_done > 0){
                 // after k_connect: a path may end in the very pass that queued its last shadow ray
-                k_film<<<(n_done + 255) / 256, 256, 0, st>>>(A, B, F, (double*)b.film, (double*)b.film_sq, est, A.done, n_done);
+                k_film<<<(n_done + 255) / 256, 256, 0, st>>>(A, B, F, (double*)b.film, (double*)b.film_sq, est_round ? est_round : est, A.done, n_done);
                 R.kernel_launches++;
                 log.mark(6);
             }
@@ -723,6 +737,15 @@ int render_passes(pt_scene* s, const pt_camera_desc* cam, const pt_render_params
 
     rc = run(total, nullptr, 0, 0);
     if(rc != PT_OK)return fail(rc);
+    // sharded adaptive rounds: sum this round's statistics over the ranks, fold them into the totals
+    auto merge_round = [&]() -> int{
+        if(!est_round)return PT_OK;
+        if(!cuda_ok(cudaStreamSynchronize(st), "adaptive round"))return PT_ERR_CUDA;
+        if(s->allreduce(s->allreduce_user, est_round, 6 * npix, st) != 0){ set_error("all-reduce callback failed"); return PT_ERR_STATE; }
+        k_est_merge<<<(unsigned)((6 * npix + 255) / 256), 256, 0, st>>>(est, est_round, 6 * npix);
+        R.kernel_launches++;
+        return PT_OK;
+    };
     if(rp->adaptive){
         // rounds 2..128 over the pixels the stopping rule keeps (Integrators.cpp:59,82-85)
         const uint32_t* in = nullptr;
@@ -730,13 +753,15 @@ int render_passes(pt_scene* s, const pt_camera_desc* cam, const pt_render_params
         for(int round = 1; round < 128 && n_in > 0; round++){
             uint32_t* out = lists[round & 1];
             if(!cuda_ok(cudaMemsetAsync(list_n, 0, 4, st), "list reset"))return fail(PT_ERR_CUDA);
+            rc = merge_round();
+            if(rc != PT_OK)return fail(rc);
             k_adapt<<<(n_in + 255) / 256, 256, 0, st>>>(est, in, n_in, out, list_n, (double)round * rp->spp);
             R.kernel_launches++;
             if(!cuda_ok(cudaMemcpyAsync(h_counters + 8, list_n, 4, cudaMemcpyDeviceToHost, st), "list size D2H") ||
                !cuda_ok(cudaStreamSynchronize(st), "adapt"))return fail(PT_ERR_CUDA);
             n_in = h_counters[8]; in = out;
             if(n_in == 0)break;
-            rc = run((uint64_t)n_in * rp->spp, in, n_in, (uint32_t)round * (uint32_t)rp->spp);
+            rc = run((uint64_t)n_in * n_pass, in, n_in, (uint32_t)round * (uint32_t)rp->spp);
             if(rc != PT_OK)return fail(rc);
         }
     }

@@ -105,6 +105,8 @@ struct pt_scene {
     bool has_alpha_tex = false;   // some triangle carries TRI_ALPHA_TEX: traversal must evaluate Material::Alpha
     bool has_boundary = false;    // some primitive has no material (a medium boundary): VolPath shadow rays walk through it
     uint64_t alpha_salt = 0;      // advances per launch (AlphaTester Blend draws)
+    pt_allreduce_fn allreduce = nullptr;   // sums a device buffer over the ranks that shard this scene's sample passes
+    void* allreduce_user = nullptr;
     int builder = 0;              // pt_builder: where the binary SAH build runs
     pt_build_stats build_stats {};
 };

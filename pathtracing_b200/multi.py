@@ -45,11 +45,43 @@ def reduce_film(film, dist, dst: int = 0):
     return film
 
 
+def make_allreduce(dist, cuda: bool = True):
+    """pt_allreduce_fn over torch.distributed: sums n doubles at a raw pointer over all ranks, in place.
+    Used by adaptive renders whose passes are sharded (every rank must see the same per-pixel statistics,
+    Integrators.cpp:82-85).  cuda=False wraps a host pointer instead (gloo tests of this glue).
+    Keep the returned object alive for as long as the scene may call it."""
+    import ctypes as C
+
+    from .capi import ALLREDUCE_FN
+
+    def _sum(user, ptr, n, stream):
+        try:
+            import torch
+            if cuda:
+                t = torch.as_tensor(_DevArray(ptr, n), device=f"cuda:{torch.cuda.current_device()}")
+                torch.cuda.synchronize()              # the scene's stream is not torch's
+                dist.all_reduce(t, op=dist.ReduceOp.SUM)
+                torch.cuda.synchronize()
+            else:
+                a = np.ctypeslib.as_array(C.cast(ptr, C.POINTER(C.c_double)), shape=(n,))
+                t = torch.from_numpy(a)
+                dist.all_reduce(t, op=dist.ReduceOp.SUM)
+            return 0
+        except Exception as e:  # never unwind through the C caller
+            print(f"[pathtracing_b200] all-reduce callback failed: {e!r}", flush=True)
+            return 1
+
+    return ALLREDUCE_FN(_sum)
+
+
 def render_sharded(scene, cam, params, dist=None):
     """Render this rank's passes and reduce the film to rank 0.  Returns (stats, film tensor);
     the tensor holds the complete image on rank 0 only."""
     world = dist.get_world_size() if dist is not None and dist.is_initialized() else 1
     rank = dist.get_rank() if world > 1 else 0
+    if world > 1 and params.adaptive and getattr(scene, "_allreduce", None) is None:
+        scene._allreduce = make_allreduce(dist)
+        scene._ck(scene.lib.pt_scene_set_allreduce(scene.h, scene._allreduce, None))
     stats = scene.render(cam, pass_range(params, world, rank), clear=True)
     film = film_tensor(scene)
     reduce_film(film, dist)

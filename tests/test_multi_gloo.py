@@ -64,6 +64,28 @@ def test_two_rank_reduce_equals_single_rank(tmp_path):
     assert np.allclose(img, want[..., :3] / SPP)
 
 
+def _allreduce_worker(rank, world, port, out):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    cb = multi.make_allreduce(dist, cuda=False)        # the pt_allreduce_fn pt_render calls between adaptive rounds
+    stats = np.arange(6 * 5, dtype=np.float64) * (rank + 1)
+    rc = cb(None, stats.ctypes.data, stats.size, None)
+    assert rc == 0
+    if rank == 0:
+        np.save(out, stats)
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+@pytest.mark.timeout(120)
+def test_adaptive_round_allreduce_callback(tmp_path):
+    """the per-round sum of the per-pixel estimator statistics (sharded adaptive renders), through the
+    same ctypes callback type the C-ABI takes"""
+    out = str(tmp_path / "stats.npy")
+    mp.spawn(_allreduce_worker, args=(2, _free_port(), out), nprocs=2, join=True)
+    assert np.array_equal(np.load(out), np.arange(30, dtype=np.float64) * 3)
+
+
 def test_shards_partition_the_passes():
     for spp in (1, 2, 7, 16, 1024):
         for world in (1, 2, 3, 4, 8):

@@ -315,6 +315,72 @@ def test_adaptive_rejects_pass_sharding():
     gpu.close()
 
 
+def test_adaptive_with_pass_sharding_equals_single_rank():
+    """Two ranks (two scenes on this GPU, one host thread each) shard the passes of an adaptive render and sum
+    their per-pixel statistics every round through pt_scene_set_allreduce: every pixel must stop after the
+    same round as in the single-rank render, and the summed films must agree (sample streams are keyed by
+    (pixel, sample index), so the two runs draw identical samples)."""
+    import threading
+
+    import torch
+
+    from pathtracing_b200 import multi
+    desc, cam = synth.cornell_scene(light_scale=40.0, light_size=0.12)
+    W = H = 40
+    spp = 4
+    one = GpuScene(desc, 4)
+    one.render(cam, render_params(W, H, spp, 5, seed=5, adaptive=1))
+    ref = one.film()
+    one.close()
+    assert (ref[..., 3] / spp).max() > 3, "scene too easy: no pixel iterates"
+
+    G = 2
+    scenes = [GpuScene(desc, 4) for _ in range(G)]
+    barrier = threading.Barrier(G)
+    bufs = [None] * G
+    calls = [0] * G
+    keep = []
+
+    def make_cb(r):
+        def cb(user, ptr, n, stream):
+            bufs[r] = torch.as_tensor(multi._DevArray(ptr, n), device="cuda:0")
+            calls[r] += 1
+            barrier.wait()
+            if r == 0:
+                total = bufs[0] + bufs[1]
+                bufs[0].copy_(total); bufs[1].copy_(total)
+                torch.cuda.synchronize()
+            barrier.wait()
+            return 0
+        return capi.ALLREDUCE_FN(cb)
+
+    errors = []
+
+    def work(r):
+        try:
+            keep.append(make_cb(r))
+            scenes[r]._ck(scenes[r].lib.pt_scene_set_allreduce(scenes[r].h, keep[-1], None))
+            scenes[r].render(cam, render_params(W, H, spp, 5, seed=5, adaptive=1, pass_begin=r, pass_stride=G))
+        except Exception as e:
+            errors.append(e)
+            barrier.abort()
+
+    threads = [threading.Thread(target=work, args=(r,)) for r in range(G)]
+    for t in threads:
+        t.start()
+    for t in threads:
+        t.join(timeout=300)
+    assert not errors, errors
+    assert calls[0] == calls[1] and calls[0] >= 3
+    films = [sc.film() for sc in scenes]
+    for sc in scenes:
+        sc.close()
+    total = films[0] + films[1]
+    assert np.array_equal(total[..., 3], ref[..., 3])                      # same number of rounds for every pixel
+    assert np.allclose(total[..., :3], ref[..., :3], rtol=1e-9, atol=1e-12)
+    assert films[0][..., 3].sum() > 0 and films[1][..., 3].sum() > 0
+
+
 def test_sample_streams_are_independent():
     """Two renders with different seeds must differ per pixel by what their own sample variance predicts
     (z ~ N(0,1)).  Guards the per-sample generator seeding: PCG streams that differ only in a small
