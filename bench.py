@@ -255,20 +255,25 @@ def bench_render(a, key, torch, dist, world, rank, local):
     return out
 
 
-def cpu_render_rate(a):
+def cpu_render_rate(a, key="c1"):
+    """The reference's own integrator (oracle/_ref, all host threads) on the SAME scene as render config `key`,
+    on a bounded sample: a reduced resolution (same camera, so the same mix of paths) and few spp."""
     from oracle import refapi
-    from pathtracing_b200 import capi, synth
     from pathtracing_b200.scene import render_params
-    desc, cam = synth.cornell_scene()
+    name, builder, W, H, spp, depth, integ = render_configs()[key]
+    w, h, s = {"c1": (256, 256, 16), "c3": (480, 270, 4), "c4": (480, 270, 4), "c5": (240, 135, 2)}[key]
+    t0 = time.perf_counter()
+    desc, cam = builder()
     flavour = "fast" if refapi.available("fast") else "strict"
     ref = refapi.RefScene(desc, 4, count_rays=True, flavour=flavour)
-    params = render_params(256, 256, 16, 8, integrator=capi.INTEGRATOR_PATH)
+    build_s = time.perf_counter() - t0
+    params = render_params(w, h, s, depth, integrator=integ)
     _, _, st = ref.render(cam, params, want_sumsq=False)
     cores = ref.threads
     ref.close()
     return {"msamples_per_s": st["samples"] / st["seconds"] / 1e6, "mrays_per_s": (st["closest_rays"] + st["shadow_rays"]) / st["seconds"] / 1e6,
-            "cores": cores, "kind": "reference",
-            "sample": f"256x256 crop-equivalent of C1 at 16 spp ({st['samples']} samples), fixed-spp mirror of TileIntegrator::Render, reference compiled -O3 ({flavour})"}
+            "cores": cores, "kind": "reference", "scene_build_s": build_s,
+            "sample": f"{w}x{h} at {s} spp of the same scene and camera ({st['samples']} samples), fixed-spp mirror of TileIntegrator::Render, reference compiled -O3 ({flavour})"}
 
 
 def run_ours(a):
@@ -401,12 +406,12 @@ def run_ours(a):
 
     for key, val in render_extras.items():
         extras[f"{key}_render"] = val
-    if "c1" in render_extras:
+    for key in render_extras:
         if world == 1 and not a.no_cpu:
             try:
-                extras["c1_render"]["cpu_reference"] = cpu_render_rate(a)
+                extras[f"{key}_render"]["cpu_reference"] = cpu_render_rate(a, key)
             except Exception as e:
-                extras["c1_render"]["cpu_reference"] = {"unavailable": str(e)}
+                extras[f"{key}_render"]["cpu_reference"] = {"unavailable": str(e)}
 
     cpu = None
     if world == 1 and not a.no_cpu:

@@ -543,6 +543,9 @@ private:
 class Model : public Primitive {
 public:
     Model(std::vector<std::shared_ptr<Mesh>> meshes) : meshes(std::move(meshes)){}
+    // Model(path) (Model.cpp:14-18): the reference imports through assimp; here Wavefront OBJ / MTL (ObjImport.hpp).
+    // Throws where the reference prints "Failed to load model" and carries on with an empty model.
+    explicit Model(const std::string& path);
     std::vector<std::shared_ptr<Mesh>> GetMeshes() const{ return meshes; }
     template <typename T> void BuildBlas(){ width = T::width; overridden = false; }
     template <typename T> void BuildBlas(const std::shared_ptr<Material>& material, const std::shared_ptr<Medium>& medium){
@@ -1030,7 +1033,21 @@ public:
         meshCache.push_back(std::make_shared<Mesh>(std::forward<Args>(args)...));
         return meshCache.back();
     }
-    // the reference's CacheModel imports `path` through assimp; here the model is handed over ready-made
+    // ResourceManager::CacheModel<BLASx>(name, path[, material, medium]) (ResourceManager.hpp:45-55): import + BuildBlas
+    template <typename T, typename... Args>
+    std::shared_ptr<Model> CacheModel(const std::string& name, const std::string& path, Args&&... args){
+        auto it = modelCache.find(name);
+        if(it != modelCache.end())return it->second;
+        std::shared_ptr<Model> ptr = std::make_shared<Model>(path);
+        ptr->template BuildBlas<T>(std::forward<Args>(args)...);
+        return modelCache.try_emplace(name, ptr).first->second;
+    }
+    template <typename T, typename... Args>
+    std::shared_ptr<Model> CacheOverwriteModel(const std::string& name, const std::string& path, Args&&... args){
+        modelCache.erase(name);
+        return CacheModel<T>(name, path, std::forward<Args>(args)...);
+    }
+    // extension: a model that was assembled in memory
     std::shared_ptr<Model> CacheModel(const std::string& name, const std::shared_ptr<Model>& model){ return modelCache.try_emplace(name, model).first->second; }
     [[nodiscard]] std::shared_ptr<Model> GetModel(const std::string& name){
         auto it = modelCache.find(name);
@@ -1046,3 +1063,6 @@ private:
     std::unordered_map<std::string, std::shared_ptr<Model>> modelCache;
     std::vector<std::shared_ptr<Mesh>> meshCache;
 };
+
+#include "ObjImport.hpp"
+inline Model::Model(const std::string& path) : meshes(ptb_host::load_obj(path)){}

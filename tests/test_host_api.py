@@ -165,3 +165,89 @@ def test_shapes_example_renders_on_the_gpu(tmp_path):
         assert img.shape == (90, 160, 3) and 20 < img.mean() < 240
     sky, floor = _read_png(tmp_path / "shapes_path.png")[:10].mean(axis=(0, 1)), _read_png(tmp_path / "shapes_path.png")[-10:].mean(axis=(0, 1))
     assert sky[2] > sky[0] and abs(float(floor.mean()) - float(sky.mean())) > 5      # blue sky on top, checker floor below
+
+
+OBJ = """# a cube of quads without normals (smooth normals are generated), a textured floor, an emissive quad
+mtllib scene.mtl
+v 0 0 0
+v 1 0 0
+v 1 1 0
+v 0 1 0
+v 0 0 1
+v 1 0 1
+v 1 1 1
+v 0 1 1
+usemtl cube
+f 1 4 3 2
+f 5 6 7 8
+f 1 5 8 4
+f 2 3 7 6
+f 1 2 6 5
+f -5 -1 -2 -6
+v -2 -0.01 -2
+v 3 -0.01 -2
+v 3 -0.01 3
+v -2 -0.01 3
+vt 0 0
+vt 1 0
+vt 1 1
+vt 0 1
+vn 0 1 0
+usemtl floor
+f 9/1/1 12/4/1 11/3/1 10/2/1
+v 0 2.5 0
+v 1 2.5 0
+v 1 2.5 1
+v 0 2.5 1
+usemtl lamp
+f 13//1 14//1 15//1
+f 13//1 15//1 16//1
+l 1 2
+"""
+MTL = """newmtl cube
+Kd 0.05 0.05 0.05
+Ks 0.0 0.0 0.0
+Ni 1.5
+newmtl floor
+Kd 0.8 0.8 0.8
+map_Kd -s 1 1 1 checker.ppm
+newmtl lamp
+Kd 0 0 0
+Ke 12 11 9
+"""
+
+
+def _write_obj(d):
+    (d / "scene.obj").write_text(OBJ)
+    (d / "scene.mtl").write_text(MTL)
+    px = bytes(((x // 4 + y // 4) % 2) * 200 + 30 for y in range(16) for x in range(16) for _ in range(3))
+    (d / "checker.ppm").write_bytes(b"P6\n# generated\n16 16\n255\n" + px)
+
+
+def test_obj_import_model_from_path(tmp_path):
+    """Model(path) / ResourceManager::CacheModel<BLAS4>(name, path) (Model.cpp:14-18, ResourceManager.hpp:45-55)
+    over the OBJ / MTL reader: one mesh per material, polygons fan-triangulated, identical corners joined, negative
+    indices, generated normals, tangents only where there are texture coordinates, PPM map_Kd, Ke emitters."""
+    _write_obj(tmp_path)
+    _compile(tmp_path / "obj_model", HOST / "glm_min", ROOT / "examples" / "obj_model.cpp")
+    r = subprocess.run([str(tmp_path / "obj_model"), str(tmp_path / "scene.obj")], capture_output=True, text=True, cwd=tmp_path)
+    assert r.returncode == 0, r.stderr
+    out = json.loads(r.stdout)
+    assert out["meshes"] == 3 and out["triangles"] == 12 + 2 + 2
+    assert out["vertices"] == 8 + 4 + 4                      # cube corners joined across its six faces
+    assert out["emissive_meshes"] == 1 and out["meshes_with_tangents"] == 1
+    assert out["lo"] == [-2, -0.01, -2] and out["hi"] == [3, 2.5, 3]
+    r = subprocess.run([str(tmp_path / "obj_model"), str(tmp_path / "missing.obj")], capture_output=True, text=True, cwd=tmp_path)
+    assert r.returncode != 0 and "cannot open" in r.stderr
+
+
+@pytest.mark.gpu
+def test_obj_import_renders_on_the_gpu(tmp_path):
+    _write_obj(tmp_path)
+    _compile(tmp_path / "obj_model", HOST / "glm_min", ROOT / "examples" / "obj_model.cpp")
+    r = subprocess.run([str(tmp_path / "obj_model"), str(tmp_path / "scene.obj"), "96", "96", "32"], capture_output=True, text=True, cwd=tmp_path, timeout=300)
+    assert r.returncode == 0, r.stderr
+    out = json.loads(r.stdout)
+    assert out["samples"] == 96 * 96 * 32
+    assert all(0.05 < v < 5.0 for v in out["mean"])
+    assert (tmp_path / "obj_model.ppm").stat().st_size > 96 * 96 * 3
