@@ -191,6 +191,15 @@ PT_API int pt_scene_add_instance(pt_scene*, int blas_id, const float* transform1
 /* returns the primitive's id in the same sequence as pt_scene_add_instance (Scene::Add order).
  * A hit on a shape reports prim = 0 and inst = this id; u, v = the quad's (alpha, beta), 0 for a sphere. */
 PT_API int pt_scene_add_shape(pt_scene*, const pt_shape_desc*);
+/* TransformedPrimitive(GeometricPrimitive(shape, ...), transform) handed to Scene::Add
+ * (Primitive.hpp:34-49, Primitive.cpp:32-73): the shape is intersected in its own space, the hit comes back
+ * through `transform` (column-major glm::mat4), its AreaLight becomes a TransformedLight (Light.cpp:296-336). */
+PT_API int pt_scene_add_shape_xf(pt_scene*, const pt_shape_desc*, const float* transform16);
+/* AnimatedPrimitive(primitive, direction, timeBounds) (Primitive.hpp:52-66, Primitive.cpp:77-96; main.cpp:189)
+ * around the top-level primitive `prim_id` (any id returned by pt_scene_add_instance / _shape / _shape_xf):
+ * per ray, the primitive is seen under translate(direction * t), t = clamp(ray.time - tb.x, tb.x, tb.y) /
+ * (tb.y - tb.x); its lights become AnimatedLights (Light.cpp:338-365).  One wrapper per primitive.            */
+PT_API int pt_scene_animate(pt_scene*, int prim_id, const float direction[3], const float time_bounds[2]);
 PT_API int pt_scene_add_light(pt_scene*, const pt_light_desc*);
 PT_API int pt_scene_set_medium(pt_scene*, int medium_id); /* Scene::SetMedium  */
 

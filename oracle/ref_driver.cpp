@@ -43,7 +43,10 @@ struct RefMesh {
 };
 
 struct RefBlasDesc { std::vector<int> meshes; };
-struct RefInstDesc { int blas; bool has_xf; glm::mat4 xf; pt_shape_desc shape; };   // blas < 0: an analytic shape
+struct RefInstDesc {   // blas < 0: an analytic shape
+    int blas; bool has_xf; glm::mat4 xf; pt_shape_desc shape;
+    bool animated = false; glm::vec3 adir { 0 }; glm::vec2 atb { 0, 1 };   // AnimatedPrimitive around it
+};
 
 struct RefScene {
     std::vector<std::shared_ptr<Texture>> textures;
@@ -283,13 +286,23 @@ PT_API int ref_scene_add_instance(void* p, int blas, const float* xf){
 }
 
 // GeometricPrimitive(shape, material, areaLight, medium) handed to Scene::Add (examples/example_1.cpp:37-66)
-PT_API int ref_scene_add_shape(void* p, const pt_shape_desc* d){
+PT_API int ref_scene_add_shape(void* p, const pt_shape_desc* d, const float* xf){
     RefScene* s = static_cast<RefScene*>(p);
     RefInstDesc i;
-    i.blas = -1; i.has_xf = false; i.shape = *d;
+    i.blas = -1; i.has_xf = xf != nullptr; i.shape = *d;
+    if(xf)memcpy(&i.xf[0][0], xf, 16 * sizeof(float));
     s->instDescs.push_back(i);
     s->hasShapes = true;
     return (int)s->instDescs.size() - 1;
+}
+
+// AnimatedPrimitive(primitive, direction, timeBounds) around top-level primitive `id` (main.cpp:189)
+PT_API int ref_scene_animate(void* p, int id, const float* dir, const float* tb){
+    RefScene* s = static_cast<RefScene*>(p);
+    if(id < 0 || id >= (int)s->instDescs.size())return PT_ERR_INVALID;
+    RefInstDesc& i = s->instDescs[id];
+    i.animated = true; i.adir = glm::vec3(dir[0], dir[1], dir[2]); i.atb = glm::vec2(tb[0], tb[1]);
+    return PT_OK;
 }
 
 PT_API int ref_scene_add_light(void* p, const pt_light_desc* d){
@@ -349,12 +362,16 @@ PT_API int ref_scene_commit(void* p, int bvh_width, int light_sampler, int id_mo
             if(d.kind == PT_SHAPE_SPHERE)shape = std::make_shared<SphereShape>(glm::vec3(d.p[0], d.p[1], d.p[2]), d.radius);
             else shape = std::make_shared<QuadShape>(glm::vec3(d.p[0], d.p[1], d.p[2]), glm::vec3(d.u[0], d.u[1], d.u[2]), glm::vec3(d.v[0], d.v[1], d.v[2]));
             std::shared_ptr<AreaLight> area = d.emissive_tex >= 0 ? std::make_shared<AreaLight>(shape, s->textures.at(d.emissive_tex), d.one_sided != 0) : nullptr;
-            s->topLevel.push_back(std::make_shared<GeometricPrimitive>(shape, d.material >= 0 ? s->materials.at(d.material) : nullptr, area,
-                                                                       d.medium >= 0 ? s->media.at(d.medium) : nullptr));
+            std::shared_ptr<Primitive> gp = std::make_shared<GeometricPrimitive>(shape, d.material >= 0 ? s->materials.at(d.material) : nullptr, area,
+                                                                                 d.medium >= 0 ? s->media.at(d.medium) : nullptr);
+            if(i.has_xf)gp = std::make_shared<TransformedPrimitive>(gp, i.xf);
+            if(i.animated)gp = std::make_shared<AnimatedPrimitive>(gp, i.adir, i.atb);
+            s->topLevel.push_back(gp);
             continue;
         }
         std::shared_ptr<Primitive> prim = s->blas.at(i.blas);
         if(i.has_xf)prim = std::make_shared<TransformedPrimitive>(prim, i.xf);
+        if(i.animated)prim = std::make_shared<AnimatedPrimitive>(prim, i.adir, i.atb);
         s->topLevel.push_back(prim);
     }
     if(count_rays){

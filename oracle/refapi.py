@@ -45,10 +45,14 @@ def load(flavour="strict") -> C.CDLL:
     lib.ref_hardware_threads.restype = i
     for name, desc in (("ref_scene_add_texture", pt_texture_desc), ("ref_scene_add_material", pt_material_desc),
                        ("ref_scene_add_medium", pt_medium_desc), ("ref_scene_add_mesh", pt_mesh_desc),
-                       ("ref_scene_add_light", pt_light_desc), ("ref_scene_add_shape", pt_shape_desc)):
+                       ("ref_scene_add_light", pt_light_desc)):
         f = getattr(lib, name)
         f.restype = i
         f.argtypes = [vp, C.POINTER(desc)]
+    lib.ref_scene_add_shape.restype = i
+    lib.ref_scene_add_shape.argtypes = [vp, C.POINTER(pt_shape_desc), C.POINTER(C.c_float)]
+    lib.ref_scene_animate.restype = i
+    lib.ref_scene_animate.argtypes = [vp, i, C.POINTER(C.c_float), C.POINTER(C.c_float)]
     lib.ref_scene_add_blas.restype = i
     lib.ref_scene_add_blas.argtypes = [vp, C.POINTER(C.c_int32), i]
     lib.ref_scene_add_instance.restype = i
@@ -111,8 +115,12 @@ class RefScene:
         p = xf.ctypes.data_as(C.POINTER(C.c_float)) if xf is not None else None
         return self._ck(self.lib.ref_scene_add_instance(self.h, blas_id, p))
 
-    def add_shape(self, d):
-        return self._ck(self.lib.ref_scene_add_shape(self.h, C.byref(d)))
+    def add_shape(self, d, xf=None):
+        p = xf.ctypes.data_as(C.POINTER(C.c_float)) if xf is not None else None
+        return self._ck(self.lib.ref_scene_add_shape(self.h, C.byref(d), p))
+
+    def animate(self, prim_id, direction, time_bounds):
+        return self._ck(self.lib.ref_scene_animate(self.h, prim_id, (C.c_float * 3)(*direction), (C.c_float * 2)(*time_bounds)))
 
     def add_light(self, d):
         return self._ck(self.lib.ref_scene_add_light(self.h, C.byref(d)))

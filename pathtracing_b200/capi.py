@@ -112,7 +112,7 @@ FILTER_BOX, FILTER_GAUSSIAN, FILTER_MITCHELL, FILTER_LANCZOS = range(4)
 EXPORTS = [
     "pt_device_count", "pt_scene_create", "pt_scene_destroy", "pt_last_error",
     "pt_scene_add_texture", "pt_scene_add_material", "pt_scene_add_medium", "pt_scene_add_mesh",
-    "pt_scene_add_blas", "pt_scene_add_instance", "pt_scene_add_shape", "pt_scene_add_light", "pt_scene_set_medium",
+    "pt_scene_add_blas", "pt_scene_add_instance", "pt_scene_add_shape", "pt_scene_add_shape_xf", "pt_scene_animate", "pt_scene_add_light", "pt_scene_set_medium",
     "pt_scene_commit", "pt_scene_set_builder", "pt_scene_set_allreduce", "pt_scene_build_stats", "pt_build_bvh2", "pt_scene_bounds", "pt_trace_closest", "pt_trace_any",
     "pt_trace_closest_dev", "pt_trace_any_dev", "pt_trace_closest_stats", "pt_render",
     "pt_film_device_ptr", "pt_film_download", "pt_film_download_sumsq", "pt_film_upload",
@@ -147,6 +147,10 @@ def load_library(path: os.PathLike | None = None) -> C.CDLL:
         f = getattr(lib, name)
         f.restype = i
         f.argtypes = [vp, C.POINTER(desc)]
+    lib.pt_scene_add_shape_xf.restype = i
+    lib.pt_scene_add_shape_xf.argtypes = [vp, C.POINTER(pt_shape_desc), C.POINTER(C.c_float)]
+    lib.pt_scene_animate.restype = i
+    lib.pt_scene_animate.argtypes = [vp, i, C.POINTER(C.c_float), C.POINTER(C.c_float)]
     lib.pt_scene_add_blas.restype = i
     lib.pt_scene_add_blas.argtypes = [vp, C.POINTER(C.c_int32), i]
     lib.pt_scene_add_instance.restype = i

@@ -18,6 +18,7 @@ PT_HDI float alpha_uniform(uint64_t salt, uint64_t ray, uint32_t prim, uint32_t 
 }
 
 struct AlphaTex {
+    static constexpr bool kWrap = true;      // the general traversal variant (trace.cuh NoAlpha)
     ShadeScene S;
     uint64_t salt;
     PT_HDI bool operator()(uint32_t mesh, uint32_t prim, uint32_t inst_rec, float bu, float bv, size_t ray) const{

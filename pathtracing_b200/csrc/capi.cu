@@ -147,6 +147,17 @@ int pt_scene_add_shape(pt_scene* s, const pt_shape_desc* d){
     return scene_add_shape(s, d);
 }
 
+int pt_scene_add_shape_xf(pt_scene* s, const pt_shape_desc* d, const float* xf){
+    PT_CHECK_OPEN(s);
+    if(!xf){ set_error("null transform"); return PT_ERR_INVALID; }
+    return scene_add_shape(s, d, xf);
+}
+
+int pt_scene_animate(pt_scene* s, int prim_id, const float* dir, const float* tb){
+    PT_CHECK_OPEN(s);
+    return scene_animate(s, prim_id, dir, tb);
+}
+
 int pt_scene_add_light(pt_scene* s, const pt_light_desc* d){
     PT_CHECK_OPEN(s);
     return scene_add_light(s, d);
@@ -278,6 +289,7 @@ int pt_trace_closest_stats(pt_scene* s, const void* d_rays, size_t n, pt_trace_s
 int pt_render(pt_scene* s, const pt_camera_desc* cam, const pt_render_params* rp, int clear, pt_render_stats* stats){
     PT_CHECK_READY(s);
     if(!cam || !rp){ set_error("null desc"); return PT_ERR_INVALID; }
+    if(s->has_wrappers){ set_error("pt_render: AnimatedPrimitive / TransformedPrimitive-over-shape wrappers are ray-cast only so far"); return PT_ERR_INVALID; }
     return render_passes(s, cam, rp, clear, stats);
 }
 

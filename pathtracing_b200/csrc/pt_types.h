@@ -91,6 +91,14 @@ constexpr uint32_t INST_LAST = 1u;
 constexpr uint32_t INST_XF = 2u;         // TransformedPrimitive (Primitive.cpp:41-66)
 constexpr uint32_t INST_SPHERE = 4u;     // not a BLAS: GeometricPrimitive(SphereShape), constants packed in the record (scene_build.cpp pack_shape)
 constexpr uint32_t INST_QUAD = 8u;       // GeometricPrimitive(QuadShape)
+// Wrapper records.  A top-level primitive is a chain of 1-3 consecutive records
+//   [INST_ANIM]? [INST_WRAP | INST_XF]? (BLAS instance | sphere | quad)
+// whose head carries INST_LAST, the primitive's id and, in bits 8-9 (INST_EXTRA_*), how many records
+// follow it; the next leaf item is head + 1 + extra.
+constexpr uint32_t INST_ANIM = 16u;      // AnimatedPrimitive (Primitive.cpp:77-96): inv[0..2] direction, inv[3..4] timeBounds; the child follows
+constexpr uint32_t INST_WRAP = 32u;      // TransformedPrimitive over an analytic shape: inv[] = inverse transform; the shape record follows
+constexpr uint32_t INST_EXTRA_SHIFT = 8u;
+constexpr uint32_t INST_EXTRA_MASK = 3u;
 
 // Everything a traversal kernel needs, passed by value as a kernel argument.
 struct DevScene {

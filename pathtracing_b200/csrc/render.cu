@@ -707,7 +707,7 @@ int render_passes(pt_scene* s, const pt_camera_desc* cam, const pt_render_params
             log.mark(4);
             const uint32_t n_next = h_counters[0], n_sh = h_counters[1], n_done = h_counters[2];
             if(n_sh > 0 && tr_walk){
-                if(s->has_alpha_tex)launch_shadow_tr(A, s, n_sh, st, AlphaTex { s->shade, s->alpha_salt += 0x9E3779B97F4A7C15ull });
+                if(s->has_alpha_tex || s->has_wrappers)launch_shadow_tr(A, s, n_sh, st, AlphaTex { s->shade, s->alpha_salt += 0x9E3779B97F4A7C15ull });
                 else launch_shadow_tr(A, s, n_sh, st, NoAlpha());
                 R.shadow_rays += n_sh; R.kernel_launches++;
                 log.mark(5);

@@ -105,17 +105,31 @@ int scene_add_instance(pt_scene* s, int blas_id, const float* xf){
     return (int)s->instances.size() - 1;
 }
 
-int scene_add_shape(pt_scene* s, const pt_shape_desc* d){
+int scene_add_shape(pt_scene* s, const pt_shape_desc* d, const float* xf){
     if(!d || (d->kind != PT_SHAPE_SPHERE && d->kind != PT_SHAPE_QUAD)){ set_error("bad shape"); return PT_ERR_INVALID; }
     if(d->material >= (int)s->materials.size() || d->emissive_tex >= (int)s->textures.size() || d->medium >= (int)s->media.size()){ set_error("shape material/texture/medium id out of range"); return PT_ERR_INVALID; }
     if(d->kind == PT_SHAPE_SPHERE && !(d->radius > 0.0f)){ set_error("sphere radius must be positive"); return PT_ERR_INVALID; }
     HostInstance i;
-    i.blas = -1; i.has_xf = false;
+    i.blas = -1; i.has_xf = xf != nullptr;       // xf: TransformedPrimitive(GeometricPrimitive(shape), M)
     memset(i.xf, 0, sizeof i.xf);
-    i.xf[0] = i.xf[5] = i.xf[10] = i.xf[15] = 1.0f;
+    if(xf)memcpy(i.xf, xf, sizeof i.xf);
+    else i.xf[0] = i.xf[5] = i.xf[10] = i.xf[15] = 1.0f;
     i.shape = *d;
     s->instances.push_back(i);
     return (int)s->instances.size() - 1;
+}
+
+// AnimatedPrimitive(primitive, direction, timeBounds) around an already added top-level primitive
+// (Primitive.hpp:52-66; main.cpp:189 wraps a sphere GeometricPrimitive).
+int scene_animate(pt_scene* s, int prim_id, const float* dir, const float* tb){
+    if(prim_id < 0 || prim_id >= (int)s->instances.size()){ set_error("primitive id out of range"); return PT_ERR_INVALID; }
+    if(!dir || !tb){ set_error("null direction / timeBounds"); return PT_ERR_INVALID; }
+    HostInstance& i = s->instances[prim_id];
+    if(i.animated){ set_error("nested AnimatedPrimitive wrappers are not supported"); return PT_ERR_INVALID; }
+    i.animated = true;
+    for(int k = 0; k < 3; k++)i.adir[k] = dir[k];
+    i.atb[0] = tb[0]; i.atb[1] = tb[1];
+    return PT_OK;
 }
 
 int scene_add_light(pt_scene* s, const pt_light_desc* d){
@@ -260,11 +274,19 @@ int pack_traversal(pt_scene* s, int width, PackedTraversal& P, BvhBuilder builde
         if(hi.blas < 0){
             if(material_alpha_flags(s, hi.shape.material) & TRI_ALPHA_TEX){ set_error("alpha-tested materials on sphere / quad shapes are not supported"); return PT_ERR_INVALID; }
             if(hi.shape.material < 0)s->has_boundary = true;
-            iboxes[i] = shape_box(hi.shape); continue;
+            iboxes[i] = shape_box(hi.shape);
+            if(hi.has_xf)iboxes[i] = transform_box(hi.xf, iboxes[i]);    // TransformedPrimitive::BoundingBox, Primitive.cpp:32-40
+        } else{
+            if(hi.blas >= (int)s->blas.size()){ set_error("instance refers to an unknown BLAS"); return PT_ERR_INVALID; }
+            const Box& bb = s->blas[hi.blas].bounds;
+            iboxes[i] = hi.has_xf ? transform_box(hi.xf, bb) : bb;
         }
-        if(hi.blas >= (int)s->blas.size()){ set_error("instance refers to an unknown BLAS"); return PT_ERR_INVALID; }
-        const Box& bb = s->blas[hi.blas].bounds;
-        iboxes[i] = hi.has_xf ? transform_box(hi.xf, bb) : bb;
+        if(hi.animated){
+            // AnimatedPrimitive::BoundingBox (Primitive.cpp:77-81): the child's box and the same box under translate(dir)
+            float tr[16] = { 1, 0, 0, 0, 0, 1, 0, 0, 0, 0, 1, 0, hi.adir[0], hi.adir[1], hi.adir[2], 1 };
+            const Box moved = transform_box(tr, iboxes[i]);
+            box_grow(iboxes[i], moved);
+        }
     }
     const auto tt0 = std::chrono::steady_clock::now();
     BinaryBvh tb;
@@ -287,34 +309,64 @@ int pack_traversal(pt_scene* s, int width, PackedTraversal& P, BvhBuilder builde
     } else{
         for(Bvh8Node nd : tf.n8){ for(int k = 0; k < 8; k++)nd.ref[k] = trebase(nd.ref[k]); P.n8.push_back(nd); }
     }
+    // One chain of 1-3 records per top-level primitive (pt_types.h): [ANIM]? [WRAP|XF]? (BLAS instance | shape)
     std::vector<Instance>& insts = P.insts;
-    insts.assign(ni, Instance());
+    insts.clear();
+    std::vector<uint32_t> rec_of(ni);
     for(uint32_t k = 0; k < ni; k++){
         const uint32_t id = tf.order[k];
         const HostInstance& hi = s->instances[id];
-        Instance& I = insts[k];
-        memset(&I, 0, sizeof I);
-        if(hi.blas < 0){
-            pack_shape(hi.shape, I);
-            I.flags |= tf.leaf_last[k] ? INST_LAST : 0u;
-            I.id = id;
-            continue;
-        }
-        const HostBlas& hb = s->blas[hi.blas];
+        const uint32_t head = (uint32_t)insts.size();
+        rec_of[k] = head;
         float inv[16];
         if(hi.has_xf)mat4_inverse(hi.xf, inv);   // TransformedPrimitive ctor, Primitive.hpp:40
         else{ memset(inv, 0, sizeof inv); inv[0] = inv[5] = inv[10] = inv[15] = 1.0f; }
-        for(int c = 0; c < 4; c++)for(int r = 0; r < 3; r++)I.inv[c * 3 + r] = inv[c * 4 + r];
-        I.root = hb.root;
-        I.flags = (hi.has_xf ? INST_XF : 0u) | (tf.leaf_last[k] ? INST_LAST : 0u);
-        I.id = id;
-        I.blas = (uint32_t)hi.blas;
-        for(int a = 0; a < 3; a++)I.blo[a] = hb.bounds.lo[a];
-        I.bhi0 = hb.bounds.hi[0]; I.bhi12[0] = hb.bounds.hi[1]; I.bhi12[1] = hb.bounds.hi[2];
+        if(hi.animated){
+            Instance A;
+            memset(&A, 0, sizeof A);
+            for(int a = 0; a < 3; a++)A.inv[a] = hi.adir[a];
+            A.inv[3] = hi.atb[0]; A.inv[4] = hi.atb[1];
+            A.flags = INST_ANIM; A.id = id;
+            insts.push_back(A);
+        }
+        if(hi.blas < 0 && hi.has_xf){
+            Instance W;
+            memset(&W, 0, sizeof W);
+            for(int c = 0; c < 4; c++)for(int r = 0; r < 3; r++)W.inv[c * 3 + r] = inv[c * 4 + r];
+            W.flags = INST_WRAP | INST_XF; W.id = id;
+            insts.push_back(W);
+        }
+        Instance I;
+        memset(&I, 0, sizeof I);
+        if(hi.blas < 0){
+            pack_shape(hi.shape, I);
+            I.id = id;
+        } else{
+            const HostBlas& hb = s->blas[hi.blas];
+            for(int c = 0; c < 4; c++)for(int r = 0; r < 3; r++)I.inv[c * 3 + r] = inv[c * 4 + r];
+            I.root = hb.root;
+            I.flags = hi.has_xf ? INST_XF : 0u;
+            I.id = id;
+            I.blas = (uint32_t)hi.blas;
+            for(int a = 0; a < 3; a++)I.blo[a] = hb.bounds.lo[a];
+            I.bhi0 = hb.bounds.hi[0]; I.bhi12[0] = hb.bounds.hi[1]; I.bhi12[1] = hb.bounds.hi[2];
+        }
+        insts.push_back(I);
+        const uint32_t extra = (uint32_t)insts.size() - head - 1;
+        if(extra)s->has_wrappers = true;
+        insts[head].flags |= (tf.leaf_last[k] ? INST_LAST : 0u) | (extra << INST_EXTRA_SHIFT);
     }
+    // TLAS leaf refs: leaf position -> head record
+    auto leaf_fix = [&](uint32_t ref) -> uint32_t{
+        if(ref == REF_EMPTY || !(ref & REF_LEAF))return ref;
+        return REF_LEAF | rec_of[ref & ~REF_LEAF];
+    };
+    if(width == 2){ for(size_t q = tnode_base; q < n2.size(); q++){ n2[q].ref0 = leaf_fix(n2[q].ref0); n2[q].ref1 = leaf_fix(n2[q].ref1); } }
+    else if(width == 4){ for(size_t q = tnode_base; q < n4.size(); q++)for(int k = 0; k < 4; k++)n4[q].ref[k] = leaf_fix(n4[q].ref[k]); }
+    else{ for(size_t q = tnode_base; q < P.n8.size(); q++)for(int k = 0; k < 8; k++)P.n8[q].ref[k] = leaf_fix(P.n8[q].ref[k]); }
 
-    if(ni == 1 && !s->instances[0].has_xf && s->instances[0].blas >= 0){ P.single_root = s->blas[s->instances[0].blas].root; P.single_id = 0; }
-    P.tlas_root = trebase(tf.root);
+    if(ni == 1 && !s->instances[0].has_xf && !s->instances[0].animated && s->instances[0].blas >= 0){ P.single_root = s->blas[s->instances[0].blas].root; P.single_id = 0; }
+    P.tlas_root = leaf_fix(trebase(tf.root));
     P.bounds = tf.bounds;
     P.inst_order = tf.order;
     return PT_OK;

@@ -41,6 +41,9 @@ struct HostInstance {        // one top-level primitive (Scene::Add order)
     bool has_xf;
     float xf[16];
     pt_shape_desc shape;     // blas < 0
+    bool animated = false;   // wrapped in an AnimatedPrimitive (pt_scene_animate)
+    float adir[3] = { 0, 0, 0 };
+    float atb[2] = { 0, 1 };
 };
 
 struct DeviceBuffers {
@@ -102,6 +105,7 @@ struct pt_scene {
     void* stream3 = nullptr;      // D2H stage
     std::vector<void*> events;    // cudaEvent_t pool of the pipeline (no timing)
     unsigned cursor_next = 0;
+    bool has_wrappers = false;    // some top-level primitive is a wrapper chain (INST_ANIM / INST_WRAP): kWrap kernel variants
     bool has_alpha_tex = false;   // some triangle carries TRI_ALPHA_TEX: traversal must evaluate Material::Alpha
     bool has_boundary = false;    // some primitive has no material (a medium boundary): VolPath shadow rays walk through it
     uint64_t alpha_salt = 0;      // advances per launch (AlphaTester Blend draws)
@@ -132,7 +136,8 @@ int scene_add_medium(pt_scene* s, const pt_medium_desc* d);
 int scene_add_mesh(pt_scene* s, const pt_mesh_desc* d);
 int scene_add_blas(pt_scene* s, const int32_t* mesh_ids, int n);
 int scene_add_instance(pt_scene* s, int blas_id, const float* xf);
-int scene_add_shape(pt_scene* s, const pt_shape_desc* d);
+int scene_add_shape(pt_scene* s, const pt_shape_desc* d, const float* xf = nullptr);
+int scene_animate(pt_scene* s, int prim_id, const float* dir, const float* tb);
 int scene_add_light(pt_scene* s, const pt_light_desc* d);
 // builder: binary build used for every BLAS and the TLAS (null = build_binary_bvh on the host); returns PT_OK or an error
 using BvhBuilder = int (*)(const Box* boxes, uint32_t n, BinaryBvh& out, void* user);

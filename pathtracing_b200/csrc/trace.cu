@@ -152,8 +152,9 @@ static int launch(pt_scene* sc, const void* d_rays, size_t n, void* d_hits, void
     if constexpr(STATS)return launch_ks<WIDTH, ANY, STATS, 0>(sc, d_rays, n, d_hits, d_inst, d_occ, d_stats, stream, NoAlpha());
     else{
     const int ks = stack_rows();
-    if(sc->has_alpha_tex){
-        // some triangle's material can reject a hit: the kernel variant that evaluates Material::Alpha
+    if(sc->has_alpha_tex || sc->has_wrappers){
+        // some triangle's material can reject a hit, or some top-level primitive is a wrapper chain: the
+        // general kernel variant (evaluates Material::Alpha where a triangle asks for it, AlphaTex::kWrap)
         const AlphaTex at = { sc->shade, sc->alpha_salt += 0x9E3779B97F4A7C15ull };
         if(ks >= 16)return launch_ks<WIDTH, ANY, STATS, 16>(sc, d_rays, n, d_hits, d_inst, d_occ, d_stats, stream, at);
         return launch_ks<WIDTH, ANY, STATS, 0>(sc, d_rays, n, d_hits, d_inst, d_occ, d_stats, stream, at);

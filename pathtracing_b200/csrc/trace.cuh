@@ -163,9 +163,15 @@ __device__ __forceinline__ bool tri_any(const RayCtx& r, const TriData& T, float
 // Primitive.cpp:6-26).  The ray-cast entry points pass NoAlpha; the integrator
 // passes a functor that evaluates the material's alpha texture.
 // operator()(mesh, prim, inst_record, u, v, ray index) -> accept the hit?
+// kWrap: does this kernel variant understand wrapper chains (AnimatedPrimitive, TransformedPrimitive over a
+// shape; pt_types.h)?  The plain ray-cast variant does not carry that code (64 registers instead of 78:
+// 8 instead of 6 CTAs per SM); a scene that holds a wrapper runs the general (AlphaTex) variant.
 struct NoAlpha {
+    static constexpr bool kWrap = false;
     __device__ __forceinline__ bool operator()(uint32_t, uint32_t, uint32_t, float, float, size_t) const{ return true; }
 };
+
+struct NoAlphaWrap : NoAlpha { static constexpr bool kWrap = true; };   // whole-ray walks: host emulation, tiny scenes
 
 struct InstData { float4 m0, m1, m2; uint4 meta; float4 b0; float4 b1; };
 
@@ -222,6 +228,31 @@ __device__ __forceinline__ void xf_apply(const InstData& d, float x, float y, fl
     oz = f_add(f_add(f_mul(d.m0.z, x), f_mul(d.m1.y, y)), f_add(f_mul(d.m2.x, z), f_mul(d.m2.w, w)));
 }
 
+// TransformedPrimitive::Intersect[Pred] head (Primitive.cpp:41-52): ray into the primitive's space,
+// direction renormalised, max scaled by the length.
+__device__ __forceinline__ void xf_ray(const InstData& d, RayCtx& r, float& tmax, float& len){
+    float ddx, ddy, ddz, oox, ooy, ooz;
+    xf_apply(d, r.dx, r.dy, r.dz, 0.0f, ddx, ddy, ddz);
+    len = f_sqrt(f_add(f_add(f_mul(ddx, ddx), f_mul(ddy, ddy)), f_mul(ddz, ddz)));
+    xf_apply(d, r.ox, r.oy, r.oz, 1.0f, oox, ooy, ooz);
+    make_ray(r, oox, ooy, ooz, f_div(ddx, len), f_div(ddy, len), f_div(ddz, len));
+    tmax = f_mul(tmax, len);
+}
+
+// AnimatedPrimitive::Intersect[Pred] (Primitive.cpp:82-89): a TransformedPrimitive with
+// glm::translate(mat4(1), dir * t), t = clamp(time - tb.x, tb.x, tb.y) / (tb.y - tb.x).  glm::inverse of
+// that matrix is the identity with column 3 = -dir*t (tests/test_raycast_emul.py checks it bit for bit);
+// it goes through the same mat4 * vec4 arithmetic as every other transform.
+__device__ __forceinline__ void anim_ray(const InstData& a, float time, RayCtx& r, float& tmax, float& len){
+    const float lo = a.m0.w, hi = a.m1.x;
+    const float tt = f_div(fminf(fmaxf(f_sub(time, lo), lo), hi), f_sub(hi, lo));
+    InstData T;
+    T.m0 = make_float4(1.0f, 0.0f, 0.0f, 0.0f);
+    T.m1 = make_float4(1.0f, 0.0f, 0.0f, 0.0f);
+    T.m2 = make_float4(1.0f, -f_mul(a.m0.x, tt), -f_mul(a.m0.y, tt), -f_mul(a.m0.z, tt));
+    xf_ray(T, r, tmax, len);
+}
+
 // ---- per-ray traversal state ------------------------------------------------------------
 
 enum : uint32_t {
@@ -229,7 +260,8 @@ enum : uint32_t {
     TF_XF = 2u,          // the current instance is a TransformedPrimitive: r/tmax are object space
     TF_FOUND_LOCAL = 4u, // a hit was accepted inside the current instance
     TF_DONE = 8u,
-    TF_OCCLUDED = 16u    // any-hit result
+    TF_OCCLUDED = 16u,   // any-hit result
+    TF_ANIM2 = 32u       // AnimatedPrimitive over a TransformedPrimitive: the outer |dir| sits on the stack under REF_LEAVE
 };
 
 struct TravState {
@@ -461,9 +493,15 @@ __device__ __forceinline__ void trav_step(TravState& s, const DevScene& S, const
                 fetch_ray(rays, ray_idx, a, b);
                 make_ray(s.r, a.x, a.y, a.z, b.x, b.y, b.z);
                 s.octant = ray_octant(s.r);
-                s.tmax = (s.flags & TF_FOUND_LOCAL) ? f_div(s.tmax, s.len) : s.wtmax;
+                float t = f_div(s.tmax, s.len);
+                if((Alpha::kWrap || STATS) && (s.flags & TF_ANIM2)){
+                    // the outer TransformedPrimitive(translate) divides once more by its own length
+                    const uint2 e = stack.ld(--s.sp);
+                    t = f_div(t, __uint_as_float(e.y));
+                }
+                s.tmax = (s.flags & TF_FOUND_LOCAL) ? t : s.wtmax;
             }
-            s.flags &= ~(TF_IN_INST | TF_XF | TF_FOUND_LOCAL);
+            s.flags &= ~(TF_IN_INST | TF_XF | TF_FOUND_LOCAL | TF_ANIM2);
             s.cur = REF_EMPTY;
         } else if(!(s.flags & TF_IN_INST)){
             // TLAS leaf item: BVHBase::intersectPrimitives over shared_ptr<Primitive> (BVH.hpp:107-135),
@@ -471,6 +509,51 @@ __device__ __forceinline__ void trav_step(TravState& s, const DevScene& S, const
             const uint32_t i = s.cur & ~REF_LEAF;
             const InstData d = load_inst(S.inst, i);
             if(STATS)cnt->instances++;
+            const uint32_t nxt = i + 1 + ((d.meta.y >> INST_EXTRA_SHIFT) & INST_EXTRA_MASK);
+            if((Alpha::kWrap || STATS) && (d.meta.y & (INST_ANIM | INST_WRAP))){
+                // wrapper chain (pt_types.h): [AnimatedPrimitive]? [TransformedPrimitive]? (BLAS | sphere | quad)
+                RayCtx r = s.r;
+                float tm = s.tmax, len_a = 1.0f, len_b = 1.0f;
+                uint32_t j = i;
+                InstData c = d;
+                const bool anim = (d.meta.y & INST_ANIM) != 0;
+                if(anim){
+                    float4 a, b;
+                    fetch_ray(rays, ray_idx, a, b);
+                    anim_ray(d, b.w, r, tm, len_a);
+                    c = load_inst(S.inst, ++j);
+                }
+                const bool xf = (c.meta.y & INST_XF) != 0;
+                if(xf)xf_ray(c, r, tm, len_b);
+                if(c.meta.y & INST_WRAP)c = load_inst(S.inst, ++j);
+                if(c.meta.y & (INST_SPHERE | INST_QUAD)){
+                    float t, u = 0.0f, v = 0.0f;
+                    const bool hit = (c.meta.y & INST_SPHERE) ? sphere_hit(r, c, tm, t) : quad_hit(r, c, tm, t, u, v);
+                    if(hit){
+                        if(ANY){ s.flags |= TF_OCCLUDED | TF_DONE; return; }
+                        if(xf)t = f_div(t, len_b);
+                        if(anim)t = f_div(t, len_a);
+                        s.tmax = t; s.hu = u; s.hv = v; s.hprim = 0u; s.hinst = d.meta.z;
+                    }
+                    s.cur = (d.meta.y & INST_LAST) ? REF_EMPTY : (REF_LEAF | nxt);
+                    return;
+                }
+                // AnimatedPrimitive over a BLAS instance
+                if(!(d.meta.y & INST_LAST))trav_push(stack, s.sp, REF_LEAF | nxt, -CUDART_INF_F);
+                if(xf){ trav_push(stack, s.sp, REF_EMPTY, len_a); s.flags |= TF_ANIM2; }
+                trav_push(stack, s.sp, REF_LEAVE, -CUDART_INF_F);
+                s.flags |= TF_IN_INST | TF_XF;
+                s.inst_rec = i; s.inst_id = d.meta.z;
+                s.wtmax = s.tmax; s.len = xf ? len_b : len_a;
+                s.r = r; s.tmax = tm;
+                s.octant = ray_octant(s.r);
+                s.cur = c.meta.x;
+                if(WIDTH == 2){
+                    const float rlo[3] = { c.b0.x, c.b0.y, c.b0.z }, rhi[3] = { c.b0.w, c.b1.x, c.b1.y };
+                    if(!box_hit2(s.r, rlo, rhi, s.tmax))s.cur = REF_EMPTY;
+                }
+                return;
+            }
             if(d.meta.y & (INST_SPHERE | INST_QUAD)){
                 // GeometricPrimitive over an analytic shape sitting directly in the TLAS leaf
                 float t, u = 0.0f, v = 0.0f;
@@ -479,22 +562,17 @@ __device__ __forceinline__ void trav_step(TravState& s, const DevScene& S, const
                     if(ANY){ s.flags |= TF_OCCLUDED | TF_DONE; return; }
                     s.tmax = t; s.hu = u; s.hv = v; s.hprim = 0u; s.hinst = d.meta.z;
                 }
-                s.cur = (d.meta.y & INST_LAST) ? REF_EMPTY : (REF_LEAF | (i + 1));
+                s.cur = (d.meta.y & INST_LAST) ? REF_EMPTY : (REF_LEAF | nxt);
                 return;
             }
-            if(!(d.meta.y & INST_LAST))trav_push(stack, s.sp, REF_LEAF | (i + 1), -CUDART_INF_F);
+            if(!(d.meta.y & INST_LAST))trav_push(stack, s.sp, REF_LEAF | nxt, -CUDART_INF_F);
             trav_push(stack, s.sp, REF_LEAVE, -CUDART_INF_F);
             s.flags |= TF_IN_INST;
             s.inst_rec = i; s.inst_id = d.meta.z;
             if(d.meta.y & INST_XF){
-                float ddx, ddy, ddz, oox, ooy, ooz;
-                xf_apply(d, s.r.dx, s.r.dy, s.r.dz, 0.0f, ddx, ddy, ddz);
-                const float len = f_sqrt(f_add(f_add(f_mul(ddx, ddx), f_mul(ddy, ddy)), f_mul(ddz, ddz)));
-                xf_apply(d, s.r.ox, s.r.oy, s.r.oz, 1.0f, oox, ooy, ooz);
-                make_ray(s.r, oox, ooy, ooz, f_div(ddx, len), f_div(ddy, len), f_div(ddz, len));
+                s.wtmax = s.tmax;
+                xf_ray(d, s.r, s.tmax, s.len);
                 s.octant = ray_octant(s.r);
-                s.wtmax = s.tmax; s.len = len;
-                s.tmax = f_mul(s.tmax, len);
                 s.flags |= TF_XF;
             }
             s.cur = d.meta.x;

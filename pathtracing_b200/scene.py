@@ -32,6 +32,8 @@ class SceneDesc:
     meshes: list = field(default_factory=list)
     blas: list = field(default_factory=list)
     instances: list = field(default_factory=list)
+    shape_xf: dict = field(default_factory=dict)    # instance index -> column-major transform of a TransformedPrimitive over a shape
+    animated: dict = field(default_factory=dict)    # instance index -> (direction, timeBounds) of its AnimatedPrimitive
     lights: list = field(default_factory=list)
     scene_medium: int = -1
     _keep: list = field(default_factory=list)   # numpy arrays referenced by descriptors
@@ -146,7 +148,15 @@ class SceneDesc:
         self.instances.append((blas_id, transform))
         return len(self.instances) - 1
 
-    def _shape(self, kind, p, u, v, radius, material, medium, emissive_tex, one_sided):
+    def animate(self, prim_id, direction, time_bounds=(0.0, 1.0)):
+        """AnimatedPrimitive(primitive, direction, timeBounds) around an already added top-level primitive"""
+        self.animated[prim_id] = (tuple(float(x) for x in direction), tuple(float(x) for x in time_bounds))
+        return prim_id
+
+    def _shape(self, kind, p, u, v, radius, material, medium, emissive_tex, one_sided, transform=None):
+        if transform is not None:   # TransformedPrimitive(GeometricPrimitive(shape), M)
+            m = np.asarray(transform, dtype=np.float32).reshape(4, 4)
+            self.shape_xf[len(self.instances)] = np.ascontiguousarray(m.T).reshape(16)
         d = pt_shape_desc()
         d.kind = kind
         _f3(d.p, p)
@@ -156,13 +166,14 @@ class SceneDesc:
         self.instances.append((-1, d))
         return len(self.instances) - 1
 
-    def sphere(self, center, radius, material=-1, medium=-1, emissive_tex=-1, one_sided=False):
-        """GeometricPrimitive(SphereShape(center, radius), material, AreaLight(shape, emissive_tex, one_sided), medium)"""
-        return self._shape(capi.SHAPE_SPHERE, center, (0, 0, 0), (0, 0, 0), radius, material, medium, emissive_tex, one_sided)
+    def sphere(self, center, radius, material=-1, medium=-1, emissive_tex=-1, one_sided=False, transform=None):
+        """GeometricPrimitive(SphereShape(center, radius), material, AreaLight(shape, emissive_tex, one_sided), medium),
+        inside a TransformedPrimitive when `transform` (4x4, row-major numpy) is given"""
+        return self._shape(capi.SHAPE_SPHERE, center, (0, 0, 0), (0, 0, 0), radius, material, medium, emissive_tex, one_sided, transform)
 
-    def quad(self, q, u, v, material=-1, medium=-1, emissive_tex=-1, one_sided=False):
+    def quad(self, q, u, v, material=-1, medium=-1, emissive_tex=-1, one_sided=False, transform=None):
         """GeometricPrimitive(QuadShape(Q, u, v), ...)"""
-        return self._shape(capi.SHAPE_QUAD, q, u, v, 0.0, material, medium, emissive_tex, one_sided)
+        return self._shape(capi.SHAPE_QUAD, q, u, v, 0.0, material, medium, emissive_tex, one_sided, transform)
 
     # -- lights -----------------------------------------------------------------------
     def light(self, kind, color=(0, 0, 0), color_b=(0, 0, 0), scale=1.0, v=(0, 0, 0), tex=-1, power_func=0):
@@ -187,11 +198,13 @@ class SceneDesc:
             b.add_mesh(d)
         for ids in self.blas:
             b.add_blas(ids)
-        for blas_id, xf in self.instances:
+        for k, (blas_id, xf) in enumerate(self.instances):
             if blas_id < 0:
-                b.add_shape(xf)
+                b.add_shape(xf, self.shape_xf.get(k))
             else:
                 b.add_instance(blas_id, xf)
+            if k in self.animated:
+                b.animate(k, *self.animated[k])
         for d in self.lights:
             b.add_light(d)
         if self.scene_medium >= 0:
@@ -279,8 +292,14 @@ class GpuScene:
         p = xf.ctypes.data_as(C.POINTER(C.c_float)) if xf is not None else None
         return self._ck(self.lib.pt_scene_add_instance(self.h, blas_id, p))
 
-    def add_shape(self, d):
-        return self._ck(self.lib.pt_scene_add_shape(self.h, C.byref(d)))
+    def add_shape(self, d, xf=None):
+        if xf is None:
+            return self._ck(self.lib.pt_scene_add_shape(self.h, C.byref(d)))
+        return self._ck(self.lib.pt_scene_add_shape_xf(self.h, C.byref(d), xf.ctypes.data_as(C.POINTER(C.c_float))))
+
+    def animate(self, prim_id, direction, time_bounds):
+        a, b = (C.c_float * 3)(*direction), (C.c_float * 2)(*time_bounds)
+        return self._ck(self.lib.pt_scene_animate(self.h, prim_id, a, b))
 
     def add_light(self, d):
         return self._ck(self.lib.pt_scene_add_light(self.h, C.byref(d)))

@@ -557,3 +557,46 @@ def shapes_scene(mesh=True, quad_light=True, sphere_light=True, one_sided=True, 
         d.light(capi.LIGHT_GRADIENT_INFINITE, color=(1.0, 1.0, 1.0), color_b=(0.5, 0.7, 1.0), scale=0.4)
     cam = camera_desc((0.0, 1.1, 4.0), (0.0, 0.3, 0.0), fov=0.9)
     return d, cam
+
+
+def wrapped_scene(boundary=False, lights=True, seed=12):
+    """shapes_scene plus every wrapper the reference can put around a top-level primitive: a
+    TransformedPrimitive over a sphere and over a quad GeometricPrimitive (Primitive.cpp:32-73), an
+    AnimatedPrimitive (Primitive.cpp:77-96; main.cpp:189) over a plain sphere, over a transformed sphere,
+    over a BLAS and over a TransformedPrimitive(BLAS), emissive wrapped shapes (TransformedLight /
+    AnimatedLight, Light.cpp:296-365).  Rays need a `time` for the animated ones."""
+    d, cam = shapes_scene(boundary=boundary, sphere_light=lights, quad_light=lights)
+    blue = d.diffuse(d.solid((0.1, 0.2, 0.5)))
+    gold = d.conductor((0.8, 0.6, 0.2))
+    red = d.diffuse(d.solid((0.7, 0.15, 0.1)))
+    # main.cpp:187-190: a diffuse sphere moving up by 0.2 over the shutter interval
+    d.animate(d.sphere((0.0, 0.1, -1.2), 0.5, material=blue), (0.0, 0.2, 0.0), (0.0, 1.0))
+    # an ellipsoid (non-uniformly scaled, rotated sphere) and a sheared, rotated quad
+    m = trs((1.4, 0.35, -0.9), 1.0, (0.3, 1, 0.2), 0.7) @ np.diag([1.0, 0.45, 0.7, 1.0]).astype(np.float32)
+    d.sphere((0.1, 0.0, -0.1), 0.6, material=gold, transform=m)
+    d.quad((-0.5, 0.0, -0.5), (1.0, 0, 0), (0.2, 0, 1.0), material=red, transform=trs((-1.3, 0.6, 0.4), 0.8, (1, 0.2, 0.1), 1.1))
+    # animated ellipsoid, time bounds that do not start at 0 (the reference clamps time - tb.x to [tb.x, tb.y])
+    m2 = trs((-0.4, 1.2, -0.4), 0.6, (0, 0, 1), 0.5) @ np.diag([1.0, 0.5, 1.0, 1.0]).astype(np.float32)
+    d.animate(d.sphere((0.0, 0.0, 0.0), 0.5, material=blue, transform=m2), (0.3, -0.1, 0.2), (0.25, 0.75))
+    # animated BLAS, with and without its own transform
+    pos, idx, nrm, uv = icosphere(1, 1.0)
+    b = d.add_blas([d.mesh(pos, idx, nrm, uv, material=red)])
+    d.animate(d.instance(b, trs((2.0, 0.5, 0.3), 0.35, (0.1, 1, 0.3), 2.0)), (-0.2, 0.3, 0.1), (0.0, 1.0))
+    pos2, idx2, nrm2, uv2 = icosphere(1, 0.3)
+    b2 = d.add_blas([d.mesh(pos2 + np.float32((-2.2, 0.4, 0.6)), idx2, nrm2, uv2, material=gold)])
+    d.animate(d.instance(b2), (0.0, 0.25, 0.0), (0.0, 0.5))
+    if lights:
+        warm = d.solid((1.0, 0.8, 0.5), scale=(9, 9, 9))
+        black = d.diffuse(d.solid((0, 0, 0)))
+        d.quad((-0.3, 0.0, -0.3), (0.6, 0, 0), (0, 0, 0.6), material=black, emissive_tex=warm, one_sided=False,
+               transform=trs((1.2, 1.7, -0.3), 1.2, (1, 0, 0.2), 2.8))
+        d.animate(d.sphere((-0.9, 1.5, 0.5), 0.12, material=black, emissive_tex=d.solid((0.5, 0.8, 1.0), scale=(12, 12, 12))), (0.4, 0.0, 0.0), (0.0, 1.0))
+    return d, cam
+
+
+def with_times(rays, seed=3, lo=-0.25, hi=1.25):
+    """random ray times (the camera's Get1D() shutter sample lives in [0, 1); tests go a little outside)"""
+    rng = np.random.default_rng(seed)
+    rays = rays.copy()
+    rays["time"] = (lo + (hi - lo) * rng.random(len(rays))).astype(np.float32)
+    return rays

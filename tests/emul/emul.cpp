@@ -52,7 +52,9 @@ PT_API int emul_scene_add_medium(void* p, const pt_medium_desc* d){ return scene
 PT_API int emul_scene_add_mesh(void* p, const pt_mesh_desc* d){ return scene_add_mesh(&((EmulScene*)p)->s, d); }
 PT_API int emul_scene_add_blas(void* p, const int32_t* ids, int n){ return scene_add_blas(&((EmulScene*)p)->s, ids, n); }
 PT_API int emul_scene_add_instance(void* p, int b, const float* xf){ return scene_add_instance(&((EmulScene*)p)->s, b, xf); }
-PT_API int emul_scene_add_shape(void* p, const pt_shape_desc* d){ return scene_add_shape(&((EmulScene*)p)->s, d); }
+PT_API int emul_scene_add_shape(void* p, const pt_shape_desc* d, const float* xf){ return scene_add_shape(&((EmulScene*)p)->s, d, xf); }
+PT_API int emul_scene_animate(void* p, int id, const float* dir, const float* tb){ return scene_animate(&((EmulScene*)p)->s, id, dir, tb); }
+PT_API void emul_mat4_inverse(const float* m, float* out){ mat4_inverse(m, out); }
 PT_API int emul_scene_add_light(void* p, const pt_light_desc* d){ return scene_add_light(&((EmulScene*)p)->s, d); }
 
 PT_API int emul_scene_commit(void* p, int width){
@@ -83,9 +85,9 @@ PT_API int emul_trace_closest(void* p, const pt_ray* rays, size_t n, pt_hit* hit
         for(size_t i = tid; i < n; i += nt){
             HitRec h;
             const float4* rb = reinterpret_cast<const float4*>(rays);
-            if(D.width == 2)trace_scene<2, false, true>(D, rb, i, h, &cs[tid], NoAlpha());
-            else if(D.width == 4)trace_scene<4, false, true>(D, rb, i, h, &cs[tid], NoAlpha());
-            else trace_scene<8, false, true>(D, rb, i, h, &cs[tid], NoAlpha());
+            if(D.width == 2)trace_scene<2, false, true>(D, rb, i, h, &cs[tid], NoAlphaWrap());
+            else if(D.width == 4)trace_scene<4, false, true>(D, rb, i, h, &cs[tid], NoAlphaWrap());
+            else trace_scene<8, false, true>(D, rb, i, h, &cs[tid], NoAlphaWrap());
             hits[i].t = h.t; hits[i].u = h.u; hits[i].v = h.v; hits[i].prim = h.prim;
             if(inst)inst[i] = h.inst;
         }
@@ -108,9 +110,9 @@ PT_API int emul_trace_any(void* p, const pt_ray* rays, size_t n, uint8_t* occ){
         for(size_t i = tid; i < n; i += nt){
             HitRec h;
             const float4* rb = reinterpret_cast<const float4*>(rays);
-            bool o = D.width == 2 ? trace_scene<2, true, false>(D, rb, i, h, nullptr, NoAlpha())
-                   : D.width == 4 ? trace_scene<4, true, false>(D, rb, i, h, nullptr, NoAlpha())
-                                  : trace_scene<8, true, false>(D, rb, i, h, nullptr, NoAlpha());
+            bool o = D.width == 2 ? trace_scene<2, true, false>(D, rb, i, h, nullptr, NoAlphaWrap())
+                   : D.width == 4 ? trace_scene<4, true, false>(D, rb, i, h, nullptr, NoAlphaWrap())
+                                  : trace_scene<8, true, false>(D, rb, i, h, nullptr, NoAlphaWrap());
             occ[i] = o ? 1 : 0;
         }
     };
@@ -144,9 +146,9 @@ PT_API int emul_unit_shade(void* p, const pt_ray* rays, size_t n, const float* i
         float* o = out + i * (size_t)stride;
         for(int k = 0; k < stride; k++)o[k] = 0.0f;
         HitRec h;
-        const bool hit = e->D.width == 2 ? trace_scene<2, false, false>(e->D, rb, i, h, nullptr, NoAlpha())
-                       : e->D.width == 4 ? trace_scene<4, false, false>(e->D, rb, i, h, nullptr, NoAlpha())
-                                         : trace_scene<8, false, false>(e->D, rb, i, h, nullptr, NoAlpha());
+        const bool hit = e->D.width == 2 ? trace_scene<2, false, false>(e->D, rb, i, h, nullptr, NoAlphaWrap())
+                       : e->D.width == 4 ? trace_scene<4, false, false>(e->D, rb, i, h, nullptr, NoAlphaWrap())
+                                         : trace_scene<8, false, false>(e->D, rb, i, h, nullptr, NoAlphaWrap());
         if(!hit)continue;
         const V3 ro = v3(rays[i].ox, rays[i].oy, rays[i].oz), rd = v3(rays[i].dx, rays[i].dy, rays[i].dz);
         SurfInt si;

@@ -27,10 +27,15 @@ def load():
     lib.emul_last_error.restype = C.c_char_p
     for name, desc in (("emul_scene_add_texture", pt_texture_desc), ("emul_scene_add_material", pt_material_desc),
                        ("emul_scene_add_medium", pt_medium_desc), ("emul_scene_add_mesh", pt_mesh_desc),
-                       ("emul_scene_add_light", pt_light_desc), ("emul_scene_add_shape", pt_shape_desc)):
+                       ("emul_scene_add_light", pt_light_desc)):
         f = getattr(lib, name)
         f.restype = i
         f.argtypes = [vp, C.POINTER(desc)]
+    lib.emul_scene_add_shape.restype = i
+    lib.emul_scene_add_shape.argtypes = [vp, C.POINTER(pt_shape_desc), C.POINTER(C.c_float)]
+    lib.emul_scene_animate.restype = i
+    lib.emul_scene_animate.argtypes = [vp, i, C.POINTER(C.c_float), C.POINTER(C.c_float)]
+    lib.emul_mat4_inverse.argtypes = [C.POINTER(C.c_float), C.POINTER(C.c_float)]
     lib.emul_scene_add_blas.restype = i
     lib.emul_scene_add_blas.argtypes = [vp, C.POINTER(C.c_int32), i]
     lib.emul_scene_add_instance.restype = i
@@ -79,8 +84,12 @@ class EmulScene:
         p = xf.ctypes.data_as(C.POINTER(C.c_float)) if xf is not None else None
         return self._ck(self.lib.emul_scene_add_instance(self.h, blas_id, p))
 
-    def add_shape(self, d):
-        return self._ck(self.lib.emul_scene_add_shape(self.h, C.byref(d)))
+    def add_shape(self, d, xf=None):
+        p = xf.ctypes.data_as(C.POINTER(C.c_float)) if xf is not None else None
+        return self._ck(self.lib.emul_scene_add_shape(self.h, C.byref(d), p))
+
+    def animate(self, prim_id, direction, time_bounds):
+        return self._ck(self.lib.emul_scene_animate(self.h, prim_id, (C.c_float * 3)(*direction), (C.c_float * 2)(*time_bounds)))
 
     def add_light(self, d):
         return self._ck(self.lib.emul_scene_add_light(self.h, C.byref(d)))

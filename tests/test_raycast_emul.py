@@ -123,3 +123,51 @@ def test_shapes_only_scene():
             eh, ei = em.trace_closest(rays)
             assert np.array_equal(ri, ei) and np.array_equal(rh["t"].view(np.uint32), eh["t"].view(np.uint32))
             assert np.array_equal(ref.trace_any(rays), em.trace_any(rays))
+
+
+@needs_ref
+def test_translation_inverse_is_exact():
+    """AnimatedPrimitive builds TransformedPrimitive(translate(dir * t)) per ray (Primitive.cpp:82-89); trace.cuh
+    assumes glm::inverse of that matrix is the identity with column 3 = -dir*t, bit for bit"""
+    import ctypes as C
+    from emulapi import load
+    lib = load()
+    rng = np.random.default_rng(0)
+    for _ in range(2000):
+        v = (rng.standard_normal(3) * 10.0 ** rng.integers(-6, 4)).astype(np.float32)
+        m = np.eye(4, dtype=np.float32)
+        m[3, :3] = v                      # column-major storage: column 3
+        out = np.zeros(16, np.float32)
+        lib.emul_mat4_inverse(m.reshape(16).ctypes.data_as(C.POINTER(C.c_float)), out.ctypes.data_as(C.POINTER(C.c_float)))
+        want = np.eye(4, dtype=np.float32)
+        want[3, :3] = -v
+        assert np.array_equal(out.reshape(4, 4), want)      # == treats -0 and +0 alike, as every use of the matrix does
+
+
+@needs_ref
+@pytest.mark.parametrize("width", [2, 4, 8])
+def test_wrapped_primitives_bit_exact(width):
+    """TransformedPrimitive over sphere / quad GeometricPrimitives and AnimatedPrimitive over shapes, transformed
+    shapes, BLASes and transformed BLASes (Primitive.cpp:32-96), rays carrying a time"""
+    d, _ = synth.wrapped_scene()
+    from emulapi import EmulScene
+    from oracle.refapi import RefScene
+    ref, em = RefScene(d, width, id_mode=True), EmulScene(d, width)
+    lo, hi = ref.bounds()
+    elo, ehi = em.bounds()
+    assert np.array_equal(lo, elo) and np.array_equal(hi, ehi)
+    wrapped = sorted(set(d.shape_xf) | set(d.animated))
+    seen = set()
+    for seed, tmax, box in ((7, np.inf, ((-3, -0.3, -2.5), (3, 2.2, 1.5))), (9, 2.0, ((-3, -0.3, -2.5), (3, 2.2, 1.5))), (11, np.inf, (lo, hi))):
+        rays = synth.with_times(synth.random_rays(40000, box[0], box[1], seed=seed, tmax=tmax), seed=seed)
+        rh, ri = ref.trace_closest(rays, want_inst=True)
+        eh, ei = em.trace_closest(rays)
+        assert np.array_equal(ri, ei)
+        assert np.array_equal(rh["prim"], eh["prim"])
+        assert np.array_equal(rh["t"].view(np.uint32), eh["t"].view(np.uint32))
+        shape_hit = np.isin(ri, [k for k, (b, _) in enumerate(d.instances) if b < 0])
+        assert np.array_equal(rh["u"][shape_hit].view(np.uint32), eh["u"][shape_hit].view(np.uint32))
+        assert np.array_equal(rh["v"][shape_hit].view(np.uint32), eh["v"][shape_hit].view(np.uint32))
+        assert np.array_equal(ref.trace_any(rays), em.trace_any(rays))
+        seen |= set(np.unique(ri[np.isin(ri, wrapped)]).tolist())
+    assert seen == set(wrapped), (seen, wrapped)      # every wrapped primitive was actually hit

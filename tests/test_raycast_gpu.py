@@ -232,3 +232,32 @@ def test_sphere_and_quad_shapes_bit_exact(width, mesh):
         assert np.array_equal(rh["v"][sh].view(np.uint32), gh["v"][sh].view(np.uint32))
         assert np.array_equal(ref.trace_any(rays), gpu.trace_any(rays))
     gpu.close()
+
+
+@needs_ref
+@pytest.mark.parametrize("width", [2, 4, 8])
+def test_wrapped_primitives_bit_exact(width):
+    """TransformedPrimitive over sphere / quad GeometricPrimitives, AnimatedPrimitive over shapes, transformed shapes,
+    BLASes and transformed BLASes (Primitive.cpp:32-96), rays carrying a time: ids, t, (alpha, beta), any-hit."""
+    from oracle.refapi import RefScene
+    d, _ = synth.wrapped_scene()
+    ref, gpu = RefScene(d, width, id_mode=True), GpuScene(d, width)
+    lo, hi = ref.bounds()
+    glo, ghi = gpu.bounds()
+    assert np.array_equal(lo, glo) and np.array_equal(hi, ghi)
+    shapes = [k for k, (b, _) in enumerate(d.instances) if b < 0]
+    wrapped = sorted(set(d.shape_xf) | set(d.animated))
+    seen = set()
+    for seed, tmax, box in ((7, np.inf, ((-3, -0.3, -2.5), (3, 2.2, 1.5))), (9, 2.0, ((-3, -0.3, -2.5), (3, 2.2, 1.5))), (11, np.inf, (lo, hi))):
+        rays = synth.with_times(synth.random_rays(100000, box[0], box[1], seed=seed, tmax=tmax), seed=seed)
+        rh, ri = ref.trace_closest(rays, want_inst=True)
+        gh, gi = gpu.trace_closest(rays)
+        assert np.array_equal(ri, gi) and np.array_equal(rh["prim"], gh["prim"])
+        assert np.array_equal(rh["t"].view(np.uint32), gh["t"].view(np.uint32))
+        sh = np.isin(ri, shapes)
+        assert np.array_equal(rh["u"][sh].view(np.uint32), gh["u"][sh].view(np.uint32))
+        assert np.array_equal(rh["v"][sh].view(np.uint32), gh["v"][sh].view(np.uint32))
+        assert np.array_equal(ref.trace_any(rays), gpu.trace_any(rays))
+        seen |= set(np.unique(ri[np.isin(ri, wrapped)]).tolist())
+    assert seen == set(wrapped)
+    gpu.close()
