@@ -701,18 +701,18 @@ PT_API int ref_unit_lights(void* p, float* out){
 
 // Light::sample(uv) of light k and what SampleLd evaluates next for a shading point ip (Integrators.cpp:260-294):
 // in: ux, uy, ip.xyz | out: 0-2 sample.L | 3-5 p | 6-8 n | 9-10 uv | 11-13 dir | 14-16 shadow dir | 17 t | 18 PDF(sample, shadow ray) | 19-21 L(sample, shadow ray)
-PT_API int ref_unit_light_sample(void* p, int k, size_t n, const float* in, float* out, int stride){
+PT_API int ref_unit_light_sample(void* p, int k, size_t n, const float* in, float* out, int stride, float time){
     RefScene* s = static_cast<RefScene*>(p);
     if(k < 0 || k >= (int)s->allLights.size() || stride < 22)return PT_ERR_INVALID;
     const std::shared_ptr<Light>& light = s->allLights[k];
     for(size_t i = 0;i < n;i++){
         const float* q = in + 5 * i;
         float* o = out + i * (size_t)stride;
-        LightSample ls = light->sample(glm::vec2(q[0], q[1]), 0.0f);
+        LightSample ls = light->sample(glm::vec2(q[0], q[1]), time);
         glm::vec3 ip(q[2], q[3], q[4]), lightDir; float t;
         if(ls.isDeltaInteraction()){ lightDir = ls.dir; t = std::numeric_limits<float>::infinity(); }
         else{ lightDir = ls.interaction.p - ip; t = glm::length(lightDir) - shadowEpsilon; }
-        Ray shadow(ip, glm::normalize(lightDir), 0.0f);
+        Ray shadow(ip, glm::normalize(lightDir), time);
         for(int c = 0;c < 3;c++){ o[c] = ls.L[c]; o[3 + c] = ls.interaction.p[c]; o[6 + c] = ls.interaction.n[c]; o[11 + c] = ls.dir[c]; o[14 + c] = shadow.dir[c]; }
         o[9] = ls.interaction.uv.x; o[10] = ls.interaction.uv.y; o[17] = t;
         o[18] = light->PDF(ls.interaction, shadow);

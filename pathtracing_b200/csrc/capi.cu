@@ -289,7 +289,6 @@ int pt_trace_closest_stats(pt_scene* s, const void* d_rays, size_t n, pt_trace_s
 int pt_render(pt_scene* s, const pt_camera_desc* cam, const pt_render_params* rp, int clear, pt_render_stats* stats){
     PT_CHECK_READY(s);
     if(!cam || !rp){ set_error("null desc"); return PT_ERR_INVALID; }
-    if(s->has_wrappers){ set_error("pt_render: AnimatedPrimitive / TransformedPrimitive-over-shape wrappers are ray-cast only so far"); return PT_ERR_INVALID; }
     return render_passes(s, cam, rp, clear, stats);
 }
 

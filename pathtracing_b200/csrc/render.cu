@@ -168,7 +168,7 @@ __global__ void __launch_bounds__(128) k_shadow_tr(Arena A, DevScene D, ShadeSce
         if(med >= 0)tr *= medium_Tr(S.media[med], h.t);
         SurfInt si;
         const V3 o = v3(ray.a.x, ray.a.y, ray.a.z);
-        build_interaction(S, o, d, h.t, h.u, h.v, h.prim, h.inst, si);
+        build_interaction(S, o, d, ray.b.w, h.t, h.u, h.v, h.prim, h.inst, si);
         if(si.mat >= 0){ blocked = true; break; }
         const V3 q = o + h.t * d;
         med = dot(d, si.n) < 0.0f ? si.medium : -1;                   // interaction.getMedium(ray.dir)
@@ -307,14 +307,14 @@ struct NeeOut { bool want; V3 o, d; float tmax; V3 contrib; int medium; };
 // PathIntegrator::SampleLd (Integrators.cpp:260-294) / VolPathIntegrator::SampleLd (:426-479) up to the
 // visibility test, which the connect stage resolves.  `medium_pt`: the interaction is a medium event.
 template <int INTEG>
-__device__ inline void sample_ld(const ShadeScene& S, const SurfInt& si, const MatCtx& mc, bool medium_pt, V3 ip, V3 rd, float hg_g, int cur_medium,
+__device__ inline void sample_ld(const ShadeScene& S, const SurfInt& si, const MatCtx& mc, bool medium_pt, V3 ip, V3 rd, float time, float hg_g, int cur_medium,
                                  float u_sel, float ux, float uy, Pcg& rng, bool tr_walk, NeeOut& out){
     out.want = false; out.medium = cur_medium;
     const int li = pick_light(S, u_sel);
     if(li < 0)return;
     const DevLight& L = S.lights[li];
     LightSmp ls;
-    light_sample(S, L, ux, uy, rng, ls);
+    light_sample(S, L, ux, uy, time, rng, ls);
     V3 ldir; float t;
     if(is_zero(ls.n)){ ldir = ls.dir; t = CUDART_INF_F; }
     else{
@@ -339,7 +339,7 @@ __device__ inline void sample_ld(const ShadeScene& S, const SurfInt& si, const M
     V3 c;
     if(light_is_delta(L))c = ls.L * f / pmf;
     else{
-        pmf *= light_pdf_sampled(S, L, ls.p, ls.n, ip, sd);
+        pmf *= light_pdf_sampled(S, L, ls.p, ls.n, ip, sd, time);
         if(pmf <= 0.0f)return;
         const float w2 = pmf * pmf, w1 = spdf * spdf;
         c = light_L_sampled(S, L, ls, sd) * f * (w2 / (w1 + w2)) / pmf;
@@ -382,13 +382,13 @@ __global__ void __launch_bounds__(128) k_shade(Arena A, ShadeScene S, BatchInfo 
                 const V3 le = inf_Le(S, L, rd);
                 if(INTEG == PT_INTEGRATOR_SIMPLE || spec)outp += att * le;
                 else if(prev_pdf > 0.0f){
-                    const float lp = L.pmf_sample * light_pdf_sampled(S, L, v3(0.0f), v3(0.0f), ro, rd);
+                    const float lp = L.pmf_sample * light_pdf_sampled(S, L, v3(0.0f), v3(0.0f), ro, rd, ntime);
                     outp += att * le * (prev_pdf * prev_pdf / (prev_pdf * prev_pdf + lp * lp));
                 }
             }
         } else{
             SurfInt si;
-            build_interaction(S, ro, rd, h.x, h.y, h.z, prim, A.hinst[j], si);
+            build_interaction(S, ro, rd, ntime, h.x, h.y, h.z, prim, A.hinst[j], si);
             bool med_event = false; float med_dist = 0.0f;
             int ray_medium = -1;        // ray.medium while this bounce is evaluated (the shadow ray inherits it)
             if(INTEG == PT_INTEGRATOR_VOLPATH){
@@ -411,7 +411,7 @@ __global__ void __launch_bounds__(128) k_shade(Arena A, ShadeScene S, BatchInfo 
                 // medium event (Integrators.cpp:356-362)
                 const DevMedium& M = S.media[medium];
                 const V3 mp = ro + med_dist * rd;
-                sample_ld<INTEG>(S, si, mc, true, mp, rd, M.g, medium, r[5], r[2], r[3], g, B.tr_walk != 0, ne);
+                sample_ld<INTEG>(S, si, mc, true, mp, rd, ntime, M.g, medium, r[5], r[2], r[3], g, B.tr_walk != 0, ne);
                 if(ne.want)ne.contrib = att * ne.contrib;
                 outp += att * ld3(M.Le);
                 no = mp; nd = hg_sample(M.g, rd, r[6], r[7]);
@@ -451,7 +451,7 @@ __global__ void __launch_bounds__(128) k_shade(Arena A, ShadeScene S, BatchInfo 
                         if(INTEG != PT_INTEGRATOR_SIMPLE){
                             spec = (sc.flags & BX_SPECULAR) != 0;
                             if(!spec){
-                                sample_ld<INTEG>(S, si, mc, false, si.p, rd, 0.0f, ray_medium, r[5], r[2], r[3], g, B.tr_walk != 0, ne);
+                                sample_ld<INTEG>(S, si, mc, false, si.p, rd, ntime, 0.0f, ray_medium, r[5], r[2], r[3], g, B.tr_walk != 0, ne);
                                 if(ne.want)ne.contrib = att * ne.contrib;
                                 prev_pdf = mat_pdf(mc, si, rd, sc.d);
                             }

@@ -43,25 +43,57 @@ PT_HDI V3 sample_normal_map(const ShadeScene& S, int mat, V3 ns, V3 tangent, flo
     return to_world(onb_from_frame(ns, tangent), nn);
 }
 
+// AnimatedPrimitive / AnimatedLight offset at a ray time (Primitive.cpp:82-89, Light.cpp:341-356):
+// dir * (clamp(time - tb.x, tb.x, tb.y) / (tb.y - tb.x))
+PT_HDI V3 anim_offset(const DevInstShade& I, float time){
+    const float tt = fminf(fmaxf(time - I.atb[0], I.atb[0]), I.atb[1]) / (I.atb[1] - I.atb[0]);
+    return ld3(I.adir) * tt;
+}
+
 // TriangleShape::Intersect's shading frame (Shape.cpp:205-243) + GeometricPrimitive::Intersect's
-// stamping (Primitive.cpp:20-24) + TransformedPrimitive::Intersect's world transform (Primitive.cpp:54-63)
-PT_HDN void build_interaction(const ShadeScene& S, V3 ro, V3 rd, float t, float bu, float bv, uint32_t prim, uint32_t inst, SurfInt& si){
+// stamping (Primitive.cpp:20-24) + TransformedPrimitive::Intersect's world transform (Primitive.cpp:54-63),
+// applied once more with translate(dir * t) for an AnimatedPrimitive (Primitive.cpp:86-89)
+PT_HDN void build_interaction(const ShadeScene& S, V3 ro, V3 rd, float time, float t, float bu, float bv, uint32_t prim, uint32_t inst, SurfInt& si){
     const DevInstShade& I = S.inst[inst];
+    const float t_world = t;
+    V3 off = v3(0.0f);
+    if(I.animated){
+        // the outer TransformedPrimitive(translate): origin back by the offset, direction renormalised
+        off = anim_offset(I, time);
+        ro = ro - off;
+        const float la = length(rd);
+        rd = rd / la; t = t * la;
+    }
     if(I.shape >= 0){
-        // SphereShape::Intersect (Shape.cpp:11-20) / QuadShape::Intersect (Shape.cpp:333-340)
-        const V3 at = ro + t * rd;
+        // SphereShape::Intersect (Shape.cpp:11-20) / QuadShape::Intersect (Shape.cpp:333-340), in the shape's space
+        V3 o = ro, d = rd;
+        float tl = t;
+        if(I.has_xf){
+            const V3 dd = xf_vec(I.inv, rd);
+            const float len = length(dd);
+            o = xf_point(I.inv, ro); d = dd / len; tl = t * len;
+        }
+        const V3 at = o + tl * d;
         V3 ns, n;
         if(I.shape == PT_SHAPE_SPHERE){
-            ns = normalize(at - ld3(I.fwd)); n = ns;
+            ns = normalize(at - ld3(I.shp)); n = ns;
             sphere_uv(n, si.u, si.v);
         } else{
-            n = ld3(I.fwd + 9);
-            ns = dot(rd, n) > 0.0f ? -n : n;
+            n = ld3(I.shp + 9);
+            ns = dot(d, n) > 0.0f ? -n : n;
             si.u = bu; si.v = bv;
         }
         const V3 up = fabsf(ns.x) > 0.9999f ? v3(0, 1, 0) : v3(1, 0, 0);
-        si.tangent = normalize(cross(up, ns));
-        si.p = at + kEps * ns; si.n = n; si.ns = ns; si.t = t;
+        V3 tangent = normalize(cross(up, ns));
+        V3 p = at + kEps * ns;
+        if(I.has_xf){
+            p = xf_point(I.fwd, p);
+            n = normalize(m3_mul(I.nrm, n));
+            ns = normalize(m3_mul(I.nrm, ns));
+            tangent = normalize(xf_vec(I.fwd, tangent));
+        }
+        si.tangent = tangent;
+        si.p = p + off; si.n = n; si.ns = ns; si.t = t_world;
         si.mat = I.material; si.medium = I.medium; si.emis_tex = -1;
         si.light = I.light_base;
         return;
@@ -102,7 +134,7 @@ PT_HDN void build_interaction(const ShadeScene& S, V3 ro, V3 rd, float t, float 
         ns = normalize(m3_mul(I.nrm, ns));
         tangent = normalize(xf_vec(I.fwd, tangent));
     }
-    si.p = p; si.n = n; si.ns = ns; si.tangent = tangent; si.t = t;
+    si.p = p + off; si.n = n; si.ns = ns; si.tangent = tangent; si.t = t_world;
     si.mat = m.material; si.medium = m.medium; si.emis_tex = m.emissive_tex;
     si.light = -1;
     if(m.emissive_tex >= 0 && I.light_base >= 0){

@@ -41,8 +41,17 @@ __host__ __device__ inline void tri_vertices(const ShadeScene& S, const DevLight
     v0 = ld3(S.pos + 3 * (size_t)i0); v1 = ld3(S.pos + 3 * (size_t)i1); v2 = ld3(S.pos + 3 * (size_t)i2);
 }
 
+// TransformedLight::sample (Light.cpp:306-312) of the light on instance I, then AnimatedLight::sample (:345-348)
+PT_HDI void light_to_world(const DevInstShade& I, float time, LightSmp& o){
+    if(I.has_xf){
+        o.p = xf_point(I.fwd, o.p);
+        o.n = m3_mul(I.nrm, o.n);
+    }
+    if(I.animated)o.p = o.p + anim_offset(I, time);
+}
+
 // Light::sample(uv, time).  `rng` feeds TextureInfiniteLight::sample's extra random_float (Light.cpp:120).
-PT_HDN void light_sample(const ShadeScene& S, const DevLight& L, float ux, float uy, Pcg& rng, LightSmp& o){
+PT_HDN void light_sample(const ShadeScene& S, const DevLight& L, float ux, float uy, float time, Pcg& rng, LightSmp& o){
     o.L = v3(0.0f); o.p = v3(0.0f); o.n = v3(0.0f); o.dir = v3(0.0f); o.u = 0.0f; o.v = 0.0f;
     switch(L.kind){
     case DL_UNIFORM_INF: o.dir = sphere_dir(ux, uy); o.L = ld3(L.color); break;                  // Light.cpp:35-42
@@ -59,7 +68,7 @@ PT_HDN void light_sample(const ShadeScene& S, const DevLight& L, float ux, float
     case DL_DISTANT: o.dir = normalize(ld3(L.v) + sphere_dir(ux, uy) * 0.02f); o.L = ld3(L.color); o.u = ux; o.v = uy; break;   // Light.cpp:208-215
     case DL_POINT: o.p = ld3(L.v); o.n = v3(1.0f); o.L = ld3(L.color); o.u = ux; o.v = uy; break;                             // Light.cpp:235-237
     case DL_SPHERE: {                                                                            // SphereShape::Sample, Shape.cpp:73-81
-        const float* g = S.inst[L.inst].fwd;
+        const float* g = S.inst[L.inst].shp;
         const float z = 1.0f - 2.0f * ux;
         const float r = sqrtf(1.0f - z * z);
         const float phi = 2.0f * kPi * uy;
@@ -67,12 +76,14 @@ PT_HDN void light_sample(const ShadeScene& S, const DevLight& L, float ux, float
         o.p = c + g[3] * v3(r * cosf(phi), r * sinf(phi), z);
         o.n = normalize(o.p - c);
         sphere_uv(o.p, o.u, o.v);                      // GetSphereUV of the point, not of the normal
+        light_to_world(S.inst[L.inst], time, o);
         break;
     }
     case DL_QUAD: {                                                                              // QuadShape::Sample, Shape.hpp:139-141: uv stays (0,0)
-        const float* g = S.inst[L.inst].fwd;
+        const float* g = S.inst[L.inst].shp;
         o.p = ld3(g) + ux * ld3(g + 3) + uy * ld3(g + 6);
         o.n = ld3(g + 9);
+        light_to_world(S.inst[L.inst], time, o);
         break;
     }
     default: {
@@ -85,11 +96,7 @@ PT_HDN void light_sample(const ShadeScene& S, const DevLight& L, float ux, float
         o.p = ux * v1 + uy * v2 + w * v0; o.n = n;
         o.u = ux * S.uv[2 * (size_t)i1] + uy * S.uv[2 * (size_t)i2] + w * S.uv[2 * (size_t)i0];
         o.v = ux * S.uv[2 * (size_t)i1 + 1] + uy * S.uv[2 * (size_t)i2 + 1] + w * S.uv[2 * (size_t)i0 + 1];
-        const DevInstShade& I = S.inst[L.inst];
-        if(I.has_xf){                                   // TransformedLight::sample (Light.cpp:306-312)
-            o.p = xf_point(I.fwd, o.p);
-            o.n = m3_mul(I.nrm, o.n);
-        }
+        light_to_world(S.inst[L.inst], time, o);
         break;
     }
     }
@@ -124,8 +131,10 @@ PT_HDI V3 area_L(const ShadeScene& S, const DevLight& L, V3 n, V3 ns, float u, f
     return tex_eval(S, L.tex, u, v, ns);
 }
 
-// Light::PDF(interaction, ray) of the light object the sampler holds (TransformedLight for xf instances)
-PT_HDN float light_pdf_sampled(const ShadeScene& S, const DevLight& L, V3 p, V3 n, V3 ro, V3 rd){
+// Light::PDF(interaction, ray) of the light object the sampler holds: AnimatedLight::PDF (Light.cpp:353-356) ->
+// TransformedLight::PDF (:318-325) -> AreaLight::PDF (:267-272), each wrapper taking p, n and the ray into its
+// child's space
+PT_HDN float light_pdf_sampled(const ShadeScene& S, const DevLight& L, V3 p, V3 n, V3 ro, V3 rd, float time){
     switch(L.kind){
     case DL_UNIFORM_INF: case DL_GRADIENT_INF: return 1.0f / (4.0f * kPi);
     case DL_TEXTURE_INF: {                                                                       // Light.cpp:146-150
@@ -133,15 +142,17 @@ PT_HDN float light_pdf_sampled(const ShadeScene& S, const DevLight& L, V3 p, V3 
         return (lum(inf_Le(S, L, rd)) / L.total_weight) * (1.0f / cell);
     }
     case DL_DISTANT: case DL_POINT: return 0.0f;
-    case DL_SPHERE: case DL_QUAD: return area_pdf(L, p, n, ro, rd);
     default: {
         const DevInstShade& I = S.inst[L.inst];
-        if(I.has_xf){                                    // TransformedLight::PDF (Light.cpp:318-325)
-            const V3 pl = xf_point(I.inv, p);
-            const V3 nl = normalize(xf_vec(I.inv, n));
-            return tri_pdf(pl, nl, xf_point(I.inv, ro), normalize(xf_vec(I.inv, rd)), L.area);
+        if(I.animated){
+            const V3 off = anim_offset(I, time);
+            p = p - off; n = normalize(n); ro = ro - off; rd = normalize(rd);
         }
-        return tri_pdf(p, n, ro, rd, L.area);
+        if(I.has_xf){
+            p = xf_point(I.inv, p); n = normalize(xf_vec(I.inv, n));
+            ro = xf_point(I.inv, ro); rd = normalize(xf_vec(I.inv, rd));
+        }
+        return L.kind == DL_AREA ? tri_pdf(p, n, ro, rd, L.area) : area_pdf(L, p, n, ro, rd);
     }
     }
 }
@@ -149,11 +160,14 @@ PT_HDN float light_pdf_sampled(const ShadeScene& S, const DevLight& L, V3 p, V3 
 // Light::L(lightSample.interaction, shadow_ray) as SampleLd calls it on the sampled light
 __host__ __device__ inline V3 light_L_sampled(const ShadeScene& S, const DevLight& L, const LightSmp& ls, V3 rd){
     if(L.kind <= DL_TEXTURE_INF)return inf_Le(S, L, rd);
-    if(L.kind >= DL_SPHERE)return area_L(S, L, ls.n, v3(0.0f), ls.u, ls.v, rd);
-    if(L.kind != DL_AREA)return v3(0.0f);
-    // TransformedLight::L builds a fresh SurfaceInteraction: its uv is (0,0) (Light.cpp:300-305)
-    if(S.inst[L.inst].has_xf)return tex_eval(S, L.tex, 0.0f, 0.0f, v3(0.0f));
-    return tex_eval(S, L.tex, ls.u, ls.v, v3(0.0f));
+    if(L.kind != DL_AREA && L.kind < DL_SPHERE)return v3(0.0f);
+    const DevInstShade& I = S.inst[L.inst];
+    // TransformedLight::L / AnimatedLight::L build a fresh SurfaceInteraction (Light.cpp:300-305, 341-344): its
+    // uv is (0,0) and its normal the wrapper's normal matrix applied to the (already world-space) sample normal
+    const bool wrapped = I.has_xf || I.animated;
+    const V3 n = I.has_xf ? m3_mul(I.nrm, ls.n) : ls.n;
+    if(L.kind >= DL_SPHERE)return area_L(S, L, n, v3(0.0f), wrapped ? 0.0f : ls.u, wrapped ? 0.0f : ls.v, rd);
+    return tex_eval(S, L.tex, wrapped ? 0.0f : ls.u, wrapped ? 0.0f : ls.v, v3(0.0f));
 }
 
 // ---- media (Medium.hpp:14-61, PhaseFunction.cpp:4-26) ---------------------------------------

@@ -77,30 +77,29 @@ static void build_geometry(pt_scene* s, ShadeTables& T){
     }
     for(const HostInstance& hi : s->instances){
         DevInstShade d {};
-        d.shape = -1; d.material = -1; d.medium = -1;
-        if(hi.blas < 0){
-            const pt_shape_desc& sd = hi.shape;
-            d.shape = sd.kind; d.material = sd.material; d.medium = sd.medium; d.light_base = -1;
-            for(int k = 0; k < 3; k++)d.fwd[k] = sd.p[k];
-            if(sd.kind == PT_SHAPE_SPHERE)d.fwd[3] = sd.radius;
-            else{
-                const V3 u = ld3(sd.u), v = ld3(sd.v);
-                const V3 n = normalize(cross(u, v));                      // QuadShape ctor, Shape.hpp:121-122
-                for(int k = 0; k < 3; k++){ d.fwd[3 + k] = sd.u[k]; d.fwd[6 + k] = sd.v[k]; }
-                d.fwd[9] = n.x; d.fwd[10] = n.y; d.fwd[11] = n.z;
-            }
-            T.inst.push_back(d);
-            continue;
-        }
+        d.shape = -1; d.material = -1; d.medium = -1; d.light_base = -1;
+        d.animated = hi.animated ? 1u : 0u;
+        for(int k = 0; k < 3; k++)d.adir[k] = hi.adir[k];
+        d.atb[0] = hi.atb[0]; d.atb[1] = hi.atb[1];
         float inv[16], nm[9];
         mat4_inverse(hi.xf, inv);
         mat3_normal_matrix(hi.xf, nm);
         for(int c = 0; c < 4; c++)for(int r = 0; r < 3; r++){ d.fwd[c * 3 + r] = hi.xf[c * 4 + r]; d.inv[c * 3 + r] = inv[c * 4 + r]; }
         for(int k = 0; k < 9; k++)d.nrm[k] = nm[k];
         d.det = mat4_det(hi.xf);
-        d.blas = (uint32_t)hi.blas;
         d.has_xf = hi.has_xf ? 1u : 0u;
-        d.light_base = -1;
+        if(hi.blas < 0){
+            const pt_shape_desc& sd = hi.shape;
+            d.shape = sd.kind; d.material = sd.material; d.medium = sd.medium;
+            for(int k = 0; k < 3; k++)d.shp[k] = sd.p[k];
+            if(sd.kind == PT_SHAPE_SPHERE)d.shp[3] = sd.radius;
+            else{
+                const V3 u = ld3(sd.u), v = ld3(sd.v);
+                const V3 n = normalize(cross(u, v));                      // QuadShape ctor, Shape.hpp:121-122
+                for(int k = 0; k < 3; k++){ d.shp[3 + k] = sd.u[k]; d.shp[6 + k] = sd.v[k]; }
+                d.shp[9] = n.x; d.shp[10] = n.y; d.shp[11] = n.z;
+            }
+        } else d.blas = (uint32_t)hi.blas;
         T.inst.push_back(d);
     }
 }
@@ -163,7 +162,7 @@ static float area_light_power(const ShadeTables& T, const DevMesh& m, uint32_t t
 
 // AreaLight::PreProcess for a sphere / quad light: (oneSided ? 1 : 2) * Area * luminance(mean emissive)
 static float shape_light_power(const ShadeTables& T, const DevLight& L, float& area_out){
-    const float* g = T.inst[L.inst].fwd;
+    const float* g = T.inst[L.inst].shp;
     const float area = L.kind == DL_SPHERE ? 4.0f * kPi * g[3] * g[3]                     // Shape.cpp:58-60
                                            : length(cross(ld3(g + 3), ld3(g + 6)));       // Shape.hpp:143-145
     area_out = area;
@@ -171,7 +170,7 @@ static float shape_light_power(const ShadeTables& T, const DevLight& L, float& a
     Pcg unused {};
     for(int j = 0; j < 16; j++)for(int i = 0; i < 16; i++){
         LightSmp ls;
-        light_sample(T.view, L, (i + 0.5f) / 16.0f, (j + 0.5f) / 16.0f, unused, ls);
+        light_sample(T.view, L, (i + 0.5f) / 16.0f, (j + 0.5f) / 16.0f, 0.0f, unused, ls);   // texcoords are the inner shape's
         const V3 e = tex_eval(T.view, L.tex, ls.u, ls.v, v3(0.0f));
         acc[0] += e.x; acc[1] += e.y; acc[2] += e.z;
     }
@@ -225,7 +224,8 @@ static int build_lights(pt_scene* s, ShadeTables& T, const std::vector<uint32_t>
             const float p = shape_light_power(T, L, L.area);
             T.inst[id].light_base = (int32_t)T.lights.size();
             T.lights.push_back(L);
-            power.push_back(p); power_inner.push_back(p);
+            // TransformedLight::Power = inner * det(transform) (Light.cpp:334-336); AnimatedLight::Power = inner (:362-364)
+            power.push_back(hinst.has_xf ? p * T.inst[id].det : p); power_inner.push_back(p);
             continue;
         }
         const HostBlas& hb = s->blas[hinst.blas];

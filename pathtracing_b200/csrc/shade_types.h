@@ -29,13 +29,18 @@ struct DevInstShade {
     uint32_t blas;
     uint32_t has_xf;
     int32_t light_base;      // first DevLight of this instance's emissive triangles (shape: its AreaLight), or -1
-    // GeometricPrimitive over an analytic shape (shape >= 0): no BLAS, no transform; fwd[] then holds the
-    // shape constants in the layout of the traversal record (scene_build.cpp pack_shape):
-    //   sphere: fwd[0..2] center, fwd[3] radius        quad: fwd[0..2] Q, [3..5] u, [6..8] v, [9..11] normal
+    // GeometricPrimitive over an analytic shape (shape >= 0): no BLAS; shp[] holds the shape constants in the
+    // layout of the traversal record (scene_build.cpp pack_shape):
+    //   sphere: shp[0..2] center, shp[3] radius        quad: shp[0..2] Q, [3..5] u, [6..8] v, [9..11] normal
+    // has_xf then means TransformedPrimitive(GeometricPrimitive(shape), M) and fwd / nrm / inv / det are M's.
     int32_t shape;           // -1 | pt_shape_kind
     int32_t material;        // shape: material id or -1 (medium boundary)
     int32_t medium;          // shape: medium id or -1
-    uint32_t pad;
+    uint32_t animated;       // inside an AnimatedPrimitive (Primitive.cpp:77-96): translate(adir * t(time)) on top
+    float shp[12];
+    float adir[3];
+    float atb[2];
+    uint32_t pad[3];
 };
 
 struct DevTexture {
@@ -64,7 +69,7 @@ struct DevMedium {
 
 enum DevLightKind : int32_t {
     DL_UNIFORM_INF = 0, DL_GRADIENT_INF = 1, DL_TEXTURE_INF = 2, DL_DISTANT = 3, DL_POINT = 4, DL_AREA = 5,
-    DL_SPHERE = 6, DL_QUAD = 7      // AreaLight over a SphereShape / QuadShape (geometry in S.inst[L.inst].fwd)
+    DL_SPHERE = 6, DL_QUAD = 7      // AreaLight over a SphereShape / QuadShape (geometry in S.inst[L.inst].shp)
 };
 
 struct DevLight {

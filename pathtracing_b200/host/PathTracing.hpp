@@ -504,8 +504,8 @@ struct TLAS8 { static constexpr int width = 8; };
 class Primitive {
 public:
     virtual ~Primitive() = default;
-    // adds this primitive's instance(s) to the scene being assembled; transform = column-major mat4 or null
-    virtual void Lower(ptb_host::Builder& b, const glm::mat4* transform) const = 0;
+    // adds this primitive to the scene being assembled and returns its top-level id; transform = column-major mat4 or null
+    virtual int Lower(ptb_host::Builder& b, const glm::mat4* transform) const = 0;
     virtual int RequiredWidth() const{ return 0; }     // BLAS width this primitive was built with (0: any)
 };
 
@@ -519,8 +519,7 @@ public:
         if(!shape)throw std::invalid_argument("GeometricPrimitive: null shape");
         if(areaLight && areaLight->getShape() != shape)throw std::invalid_argument("GeometricPrimitive: the AreaLight must be built over the primitive's own shape");
     }
-    void Lower(ptb_host::Builder& b, const glm::mat4* transform) const override{
-        if(transform)throw std::logic_error("TransformedPrimitive over a sphere / quad GeometricPrimitive is not supported: transform the shape's constants instead");
+    int Lower(ptb_host::Builder& b, const glm::mat4* transform) const override{
         pt_shape_desc d;
         std::memset(&d, 0, sizeof d);
         shape->Describe(d);
@@ -528,7 +527,10 @@ public:
         d.medium = medium ? medium->Emit(b) : -1;
         d.emissive_tex = areaLight ? areaLight->EmissiveTexture()->Emit(b) : -1;
         d.one_sided = areaLight && areaLight->OneSided() ? 1 : 0;
-        ptb_host::check(pt_scene_add_shape(b.scene, &d), "pt_scene_add_shape");
+        // inside a TransformedPrimitive (Primitive.cpp:32-73) the shape keeps its own space and the wrapper's matrix travels with it
+        const int id = transform ? pt_scene_add_shape_xf(b.scene, &d, &(*transform)[0][0]) : pt_scene_add_shape(b.scene, &d);
+        ptb_host::check(id, "pt_scene_add_shape");
+        return id;
     }
 private:
     std::shared_ptr<Shape> shape;
@@ -552,7 +554,7 @@ public:
         width = T::width; overridden = true; matOverride = material; medOverride = medium;
     }
     int RequiredWidth() const override{ return width; }
-    void Lower(ptb_host::Builder& b, const glm::mat4* transform) const override{
+    int Lower(ptb_host::Builder& b, const glm::mat4* transform) const override{
         if(width == 0)throw std::logic_error("Model::BuildBlas<BLAS2|BLAS4|BLAS8>() was not called");
         int blas = b.lookup(this);
         if(blas < 0){
@@ -562,7 +564,9 @@ public:
             ptb_host::check(blas, "pt_scene_add_blas");
             b.ids[this] = blas;
         }
-        ptb_host::check(pt_scene_add_instance(b.scene, blas, transform ? &(*transform)[0][0] : nullptr), "pt_scene_add_instance");
+        const int id = pt_scene_add_instance(b.scene, blas, transform ? &(*transform)[0][0] : nullptr);
+        ptb_host::check(id, "pt_scene_add_instance");
+        return id;
     }
 private:
     std::vector<std::shared_ptr<Mesh>> meshes;
@@ -576,15 +580,37 @@ class TransformedPrimitive : public Primitive {
 public:
     TransformedPrimitive(const std::shared_ptr<Primitive>& primitive, const glm::mat4& transform) : primitive(primitive), transform(transform){}
     int RequiredWidth() const override{ return primitive->RequiredWidth(); }
-    void Lower(ptb_host::Builder& b, const glm::mat4* outer) const override{
+    int Lower(ptb_host::Builder& b, const glm::mat4* outer) const override{
         // the reference nests TransformedPrimitives by composing ray transforms; the GPU TLAS holds one
         // transform per instance, and the per-level renormalisation of the ray direction is not associative
         if(outer)throw std::logic_error("nested TransformedPrimitive is not supported");
-        primitive->Lower(b, &transform);
+        return primitive->Lower(b, &transform);
     }
 private:
     std::shared_ptr<Primitive> primitive;
     glm::mat4 transform;
+};
+
+// Primitive.hpp:52-66, Primitive.cpp:77-96 (main.cpp:187-190): motion blur.  Per ray the child is seen under
+// translate(direction * t), t = clamp(ray.time - timeBounds.x, timeBounds.x, timeBounds.y) / (timeBounds.y -
+// timeBounds.x); its lights become AnimatedLights.  The child may be a Model, a GeometricPrimitive or a
+// TransformedPrimitive over either.
+class AnimatedPrimitive : public Primitive {
+public:
+    AnimatedPrimitive(const std::shared_ptr<Primitive>& primitive, const glm::vec3& direction, const glm::vec2& timeBounds)
+        : primitive(primitive), dir(direction), timeBounds(timeBounds){}
+    int RequiredWidth() const override{ return primitive->RequiredWidth(); }
+    int Lower(ptb_host::Builder& b, const glm::mat4* outer) const override{
+        if(outer)throw std::logic_error("TransformedPrimitive over an AnimatedPrimitive is not supported: animate the TransformedPrimitive instead");
+        const int id = primitive->Lower(b, nullptr);
+        const float d[3] = { dir.x, dir.y, dir.z }, tb[2] = { timeBounds.x, timeBounds.y };
+        ptb_host::check(pt_scene_animate(b.scene, id, d, tb), "pt_scene_animate");
+        return id;
+    }
+private:
+    std::shared_ptr<Primitive> primitive;
+    glm::vec3 dir;
+    glm::vec2 timeBounds;
 };
 
 // ---- LightSampler.hpp:5-60 ----------------------------------------------------------------------------

@@ -152,7 +152,7 @@ PT_API int emul_unit_shade(void* p, const pt_ray* rays, size_t n, const float* i
         if(!hit)continue;
         const V3 ro = v3(rays[i].ox, rays[i].oy, rays[i].oz), rd = v3(rays[i].dx, rays[i].dy, rays[i].dz);
         SurfInt si;
-        build_interaction(S, ro, rd, h.t, h.u, h.v, h.prim, h.inst, si);
+        build_interaction(S, ro, rd, rays[i].time, h.t, h.u, h.v, h.prim, h.inst, si);
         o[0] = 1.0f;
         const V3 vs[4] = { si.p, si.n, si.ns, si.tangent };
         for(int k = 0; k < 4; k++){ o[1 + 3 * k] = vs[k].x; o[2 + 3 * k] = vs[k].y; o[3 + 3 * k] = vs[k].z; }
@@ -194,7 +194,7 @@ PT_API int emul_unit_lights(void* p, float* out){
     return PT_OK;
 }
 
-PT_API int emul_unit_light_sample(void* p, int k, size_t n, const float* in, float* out, int stride){
+PT_API int emul_unit_light_sample(void* p, int k, size_t n, const float* in, float* out, int stride, float time){
     EmulScene* e = (EmulScene*)p;
     if(k < 0 || k >= (int)e->T.lights.size() || stride < 22)return PT_ERR_INVALID;
     const ShadeScene& S = e->T.view;
@@ -204,7 +204,7 @@ PT_API int emul_unit_light_sample(void* p, int k, size_t n, const float* in, flo
         const float* q = in + 5 * i;
         float* o = out + i * (size_t)stride;
         LightSmp ls;
-        light_sample(S, L, q[0], q[1], rng, ls);
+        light_sample(S, L, q[0], q[1], time, rng, ls);
         const V3 ip = v3(q[2], q[3], q[4]);
         V3 ldir; float t;
         if(is_zero(ls.n)){ ldir = ls.dir; t = INFINITY; }
@@ -212,7 +212,7 @@ PT_API int emul_unit_light_sample(void* p, int k, size_t n, const float* in, flo
         const V3 sd = normalize(ldir);
         o[0] = ls.L.x; o[1] = ls.L.y; o[2] = ls.L.z; o[3] = ls.p.x; o[4] = ls.p.y; o[5] = ls.p.z; o[6] = ls.n.x; o[7] = ls.n.y; o[8] = ls.n.z;
         o[9] = ls.u; o[10] = ls.v; o[11] = ls.dir.x; o[12] = ls.dir.y; o[13] = ls.dir.z; o[14] = sd.x; o[15] = sd.y; o[16] = sd.z; o[17] = t;
-        o[18] = light_pdf_sampled(S, L, ls.p, ls.n, ip, sd);
+        o[18] = light_pdf_sampled(S, L, ls.p, ls.n, ip, sd, time);
         const V3 Lv = light_L_sampled(S, L, ls, sd);
         o[19] = Lv.x; o[20] = Lv.y; o[21] = Lv.z;
     }
@@ -228,7 +228,7 @@ PT_API int emul_unit_escape(void* p, size_t n, const float* dirs, float* out){
         for(int k = 0; k < S.n_inf_lights; k++){
             const DevLight& L = S.lights[S.inf_lights[k]];
             le += inf_Le(S, L, rd);
-            pp += L.pmf_sample * light_pdf_sampled(S, L, v3(0.0f), v3(0.0f), v3(0.0f), rd);
+            pp += L.pmf_sample * light_pdf_sampled(S, L, v3(0.0f), v3(0.0f), v3(0.0f), rd, 0.0f);
         }
         out[4 * i] = le.x; out[4 * i + 1] = le.y; out[4 * i + 2] = le.z; out[4 * i + 3] = pp;
     }

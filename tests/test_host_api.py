@@ -143,6 +143,31 @@ int main(){
     assert png[:, 0, 0].max() == 0 and png[:, -1, 0].min() > 250 and "no JPEG encoder" in r.stderr
 
 
+@pytest.mark.parametrize("glm", ["bundled", "reference"])
+def test_motion_blur_example_compiles(tmp_path, glm):
+    """AnimatedPrimitive and TransformedPrimitive over GeometricPrimitives (Primitive.hpp:34-66) in the host API"""
+    if glm == "reference" and not Path("/root/reference/glm/glm.hpp").exists():
+        pytest.skip("reference tree (real glm) not present")
+    _compile(tmp_path / "motion_blur", HOST / "glm_min" if glm == "bundled" else "/root/reference", ROOT / "examples" / "motion_blur.cpp")
+
+
+@pytest.mark.gpu
+def test_motion_blur_example_renders_on_the_gpu(tmp_path):
+    """examples/motion_blur.cpp: the moving sphere of main.cpp:187-190, an ellipsoid (TransformedPrimitive over a
+    sphere) and a transformed quad light"""
+    _compile(tmp_path / "motion_blur", HOST / "glm_min", ROOT / "examples" / "motion_blur.cpp")
+    r = subprocess.run([str(tmp_path / "motion_blur"), "160", "90", "64", "8"], capture_output=True, text=True, cwd=tmp_path, timeout=300)
+    assert r.returncode == 0, r.stderr[-2000:]
+    out = json.loads(r.stdout.strip().splitlines()[-1])
+    assert out["samples"] == 160 * 90 * 64 and out["shadow_rays"] > 0
+    # the sphere's top: y = 0.6 at shutter open, 0.8 at shutter close, seen from y = 3
+    assert out["hit0"] == 1 and abs(out["t0"] - 2.4) < 1e-5 and out["hit1"] == 1 and abs(out["t1"] - 2.2) < 1e-5
+    # the ellipsoid's long semi-axis is 0.6: a ray from 3 away along it enters at 2.4
+    assert out["hit2"] == 1 and abs(out["t2"] - 2.4) < 1e-4 and out["inst2"] == 2
+    img = _read_png(tmp_path / "motion_blur.png")
+    assert img.shape == (90, 160, 3) and 10 < img.mean() < 240
+
+
 @pytest.mark.gpu
 def test_shapes_example_renders_on_the_gpu(tmp_path):
     """examples/shapes.cpp = the scene of the reference's example_1.cpp: three integrators over spheres, quads,

@@ -264,6 +264,21 @@ def test_medium_boundary_sphere_path_integrator():
 
 
 @needs_ref
+def test_wrapped_primitives_path_motion_blur():
+    """TransformedPrimitive over sphere / quad GeometricPrimitives and AnimatedPrimitives (motion blur over the
+    camera's shutter sample, main.cpp:187-190) incl. a transformed quad light and an animated sphere light
+    (TransformedLight / AnimatedLight, Light.cpp:296-365)."""
+    desc, cam = synth.wrapped_scene()
+    compare(desc, cam, 64, 48, 1024, 10)
+
+
+@needs_ref
+def test_wrapped_primitives_volpath_boundary_bvh2():
+    desc, cam = synth.wrapped_scene(boundary=True)
+    compare(desc, cam, 48, 36, 1024, 8, integrator=capi.INTEGRATOR_VOLPATH, bvh=2)
+
+
+@needs_ref
 def test_volpath_without_medium_equals_reference():
     desc, cam = synth.cornell_scene()
     compare(desc, cam, 40, 40, 1024, 6, integrator=capi.INTEGRATOR_VOLPATH)

@@ -17,7 +17,7 @@ vp, sz, i32, f32 = C.c_void_p, C.c_size_t, C.c_int, C.c_float
 
 def _sig(lib, prefix):
     for name, args in (("unit_shade", [vp, vp, sz, vp, vp, i32]), ("unit_light_count", [vp]), ("unit_lights", [vp, vp]),
-                       ("unit_light_sample", [vp, i32, sz, vp, vp, i32]), ("unit_escape", [vp, sz, vp, vp]),
+                       ("unit_light_sample", [vp, i32, sz, vp, vp, i32, f32]), ("unit_escape", [vp, sz, vp, vp]),
                        ("unit_camera", [vp, i32, i32, sz, vp, vp]), ("unit_hg", [f32, sz, vp, vp])):
         f = getattr(lib, f"{prefix}_{name}")
         f.restype, f.argtypes = i32, args
@@ -144,8 +144,8 @@ def test_lights_power_pmf_sample_pdf(libs, sampler):
     for k in range(n):
         inp = np.ascontiguousarray(np.concatenate([rng.random((m, 2)), rng.uniform(-2, 2, (m, 3))], 1).astype(np.float32))
         a, b = np.zeros((m, 22), np.float32), np.zeros((m, 22), np.float32)
-        assert ref.ref_unit_light_sample(r.h, k, m, inp.ctypes.data, a.ctypes.data, 22) == 0
-        assert emu.emul_unit_light_sample(e.h, k, m, inp.ctypes.data, b.ctypes.data, 22) == 0
+        assert ref.ref_unit_light_sample(r.h, k, m, inp.ctypes.data, a.ctypes.data, 22, 0.0) == 0
+        assert emu.emul_unit_light_sample(e.h, k, m, inp.ctypes.data, b.ctypes.data, 22, 0.0) == 0
         if not a[:, 6:9].any():
             a[:, 9:11] = b[:, 9:11] = 0     # a direction sample's uv (GetSphereUV(dir) in the reference) is never read
         _close(a[:, :18], b[:, :18], 1e-4, 1e-5, f"light {k}: sample, shadow ray")
@@ -275,10 +275,73 @@ def test_sphere_and_quad_shapes(libs, one_sided):
     for k in range(n):
         inp = np.ascontiguousarray(np.concatenate([rng.random((m, 2)), rng.uniform(-2, 3, (m, 3))], 1).astype(np.float32))
         a, b = np.zeros((m, 22), np.float32), np.zeros((m, 22), np.float32)
-        assert ref.ref_unit_light_sample(r.h, k, m, inp.ctypes.data, a.ctypes.data, 22) == 0
-        assert emu.emul_unit_light_sample(e.h, k, m, inp.ctypes.data, b.ctypes.data, 22) == 0
+        assert ref.ref_unit_light_sample(r.h, k, m, inp.ctypes.data, a.ctypes.data, 22, 0.0) == 0
+        assert emu.emul_unit_light_sample(e.h, k, m, inp.ctypes.data, b.ctypes.data, 22, 0.0) == 0
         if not a[:, 6:9].any():
             a[:, 9:11] = b[:, 9:11] = 0
         _close(a[:, :18], b[:, :18], 1e-4, 1e-5, f"light {k}: sample, shadow ray", frac=1e-3)
         _close(a[:, 18:22], b[:, 18:22], 2e-3, 1e-6, f"light {k}: PDF and L along the shadow ray", frac=2e-3)
+    r.close(); e.close()
+
+
+@needs_ref
+def test_wrapped_primitives_shading(libs):
+    """TransformedPrimitive over sphere / quad GeometricPrimitives and AnimatedPrimitive wrappers (Primitive.cpp:32-96):
+    the interaction that comes back through the wrappers at the ray's time, the inner AreaLight seen by a hit, and
+    TransformedLight / AnimatedLight::{sample, PDF, L, Power} (Light.cpp:296-365) at several shutter times."""
+    ref, emu = libs
+    desc, cam = synth.wrapped_scene()
+    r, e = _scenes(desc, 4)
+    rng = np.random.default_rng(6)
+    rays = synth.with_times(_camera_rays(cam, 64, 48, 20000, 5), seed=1)
+    lo, hi = r.bounds()
+    r2 = synth.with_times(synth.random_rays(30000, (-3, -0.3, -2.5), (3, 2.2, 1.5), seed=8), seed=2)
+    # rays aimed at the two wrapped lights (a transformed two-sided quad, an animated sphere)
+    tgt = np.where(rng.random((8000, 1)) < 0.5, np.array([[1.2, 1.7, -0.3]]), np.array([[-0.7, 1.5, 0.5]])) + rng.normal(size=(8000, 3)) * 0.2
+    o3 = rng.uniform((-3, 0, -3), (3, 4, 3), (8000, 3))
+    d3 = tgt - o3
+    d3 /= np.linalg.norm(d3, axis=1, keepdims=True)
+    r3 = np.zeros(8000, capi.RAY_DTYPE)
+    r3["o"], r3["d"], r3["tmax"] = o3.astype(np.float32), d3.astype(np.float32), np.inf
+    r3 = synth.with_times(r3, seed=3)
+    wrapped = sorted(set(desc.shape_xf) | set(desc.animated))
+    seen_lights = 0
+    for rr in (rays, r2, r3):
+        a, b = _shade(libs, r, e, rr)
+        assert np.array_equal(a[:, 0], b[:, 0])
+        h = a[:, 0] == 1
+        assert np.array_equal(a[h, 16], b[h, 16]) and np.array_equal(a[h, 17], b[h, 17])
+        assert np.array_equal(a[h, 15].view(np.uint32), b[h, 15].view(np.uint32))
+        _close(a[h, 1:16], b[h, 1:16], 3e-5, 3e-6, "interaction", frac=2e-4)
+        ok = h & (a[:, 16] >= 0)
+        assert np.array_equal(a[ok, 18], b[ok, 18])
+        s = ok & (a[:, 18] == 1)
+        _close(a[s, 24:30], b[s, 24:30], 1e-4, 1e-5, "scattered ray", frac=2e-3)
+        _close(a[s, 19:23], b[s, 19:23], 2e-3, 1e-6, "f, pdf", frac=5e-3)
+        em = h & (a[:, 17] == 1)
+        seen_lights += int(em.sum())
+        if em.any():
+            _close(a[em, 38:43], b[em, 38:43], 1e-4, 1e-7, "emission, PMF, PDF of the hit light")
+    assert seen_lights > 500
+    # the hits above did land on the wrapped primitives
+    _, inst = e.trace_closest(r2)
+    assert set(wrapped) <= set(np.unique(inst).tolist())
+    n = ref.ref_unit_light_count(r.h)
+    assert n == emu.emul_unit_light_count(e.h) == 5      # quad, sphere, transformed quad, animated sphere, sky
+    ra, eb = np.zeros((n, 3), np.float32), np.zeros((n, 4), np.float32)
+    ref.ref_unit_lights(r.h, ra.ctypes.data)
+    emu.emul_unit_lights(e.h, eb.ctypes.data)
+    assert np.array_equal(ra[:, 2], eb[:, 2])
+    _close(ra[:, 1], eb[:, 0], 2e-3, 1e-6, "sampler PMF per light (the reference jitters its 256 power samples)")
+    m = 3000
+    for time in (0.0, 0.37, 0.9, 1.4):
+        for k in range(n):
+            inp = np.ascontiguousarray(np.concatenate([rng.random((m, 2)), rng.uniform(-2, 3, (m, 3))], 1).astype(np.float32))
+            a, b = np.zeros((m, 22), np.float32), np.zeros((m, 22), np.float32)
+            assert ref.ref_unit_light_sample(r.h, k, m, inp.ctypes.data, a.ctypes.data, 22, time) == 0
+            assert emu.emul_unit_light_sample(e.h, k, m, inp.ctypes.data, b.ctypes.data, 22, time) == 0
+            if not a[:, 6:9].any():
+                a[:, 9:11] = b[:, 9:11] = 0
+            _close(a[:, :18], b[:, :18], 1e-4, 1e-5, f"light {k} at time {time}: sample, shadow ray", frac=1e-3)
+            _close(a[:, 18:22], b[:, 18:22], 2e-3, 1e-6, f"light {k} at time {time}: PDF and L along the shadow ray", frac=2e-3)
     r.close(); e.close()
