@@ -55,14 +55,20 @@ template <class Launch, class CopyOut>
 static int trace_pipelined(pt_scene* s, const pt_ray* rays, size_t n, Launch launch, CopyOut copy_out){
     int rc = ensure_stage(s, n);
     if(rc != PT_OK)return rc;
-    cudaStream_t compute = (cudaStream_t)s->stream, in = (cudaStream_t)s->stream2, out = (cudaStream_t)s->stream3;
+    // Chunks alternate between two trace streams: the persistent kernel of chunk k+1 moves onto the SMs that
+    // chunk k's tail (its longest rays) leaves idle.  PTB_TRACE_STREAMS=1 serialises them again.
+    static const int n_cs = []{ const char* e = getenv("PTB_TRACE_STREAMS"); return e && atoi(e) == 1 ? 1 : 2; }();
+    cudaStream_t cs[2] = { (cudaStream_t)s->stream, n_cs == 2 ? (cudaStream_t)s->stream4 : (cudaStream_t)s->stream };
+    cudaStream_t in = (cudaStream_t)s->stream2, out = (cudaStream_t)s->stream3;
     pt_ray* d_rays = (pt_ray*)s->buf.stage_rays;
     const size_t full = chunk_rays();
     size_t k = 0;
     for(size_t off = 0; off < n; k++){
         size_t m = k == 0 ? full / 8 : k == 1 ? full / 2 : full;      // ramp up: 1/8, 1/2, then full chunks
         if(m < 1024)m = 1024;
-        if(m > n - off)m = n - off;
+        const size_t left = n - off;
+        if(m >= left)m = left > full / 2 ? left - full / 4 : left;    // ramp down: the last D2H is a quarter chunk at most
+        cudaStream_t compute = cs[k & 1];
         cudaEvent_t landed = pipeline_event(s, 2 * k), traced = pipeline_event(s, 2 * k + 1);
         if(!landed || !traced)return PT_ERR_CUDA;
         if(!cuda_ok(cudaMemcpyAsync(d_rays + off, rays + off, m * sizeof(pt_ray), cudaMemcpyHostToDevice, in), "H2D rays") ||
@@ -74,7 +80,8 @@ static int trace_pipelined(pt_scene* s, const pt_ray* rays, size_t n, Launch lau
         if(rc != PT_OK)return rc;
         off += m;
     }
-    if(!cuda_ok(cudaStreamSynchronize(out), "sync") || !cuda_ok(cudaStreamSynchronize(compute), "sync") || !cuda_ok(cudaStreamSynchronize(in), "sync"))return PT_ERR_CUDA;
+    if(!cuda_ok(cudaStreamSynchronize(out), "sync") || !cuda_ok(cudaStreamSynchronize(cs[0]), "sync") || !cuda_ok(cudaStreamSynchronize(cs[1]), "sync") ||
+       !cuda_ok(cudaStreamSynchronize(in), "sync"))return PT_ERR_CUDA;
     return PT_OK;
 }
 
@@ -105,6 +112,7 @@ void pt_scene_destroy(pt_scene* s){
         if(s->stream)cudaStreamDestroy((cudaStream_t)s->stream);
         if(s->stream2)cudaStreamDestroy((cudaStream_t)s->stream2);
         if(s->stream3)cudaStreamDestroy((cudaStream_t)s->stream3);
+        if(s->stream4)cudaStreamDestroy((cudaStream_t)s->stream4);
         for(void* e : s->events)cudaEventDestroy((cudaEvent_t)e);
     }
     delete s;

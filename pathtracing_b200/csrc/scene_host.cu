@@ -85,11 +85,12 @@ int scene_commit(pt_scene* s, int width, int light_sampler){
     int rc = build_shade_tables(s, P.inst_order);
     if(rc != PT_OK){ scene_free_device(s); return rc; }
 
-    cudaStream_t st, st2, st3;
+    cudaStream_t st, st2, st3, st4;
     if(!cuda_ok(cudaStreamCreateWithFlags(&st, cudaStreamNonBlocking), "cudaStreamCreate") ||
        !cuda_ok(cudaStreamCreateWithFlags(&st2, cudaStreamNonBlocking), "cudaStreamCreate") ||
-       !cuda_ok(cudaStreamCreateWithFlags(&st3, cudaStreamNonBlocking), "cudaStreamCreate")){ scene_free_device(s); return PT_ERR_CUDA; }
-    s->stream = st; s->stream2 = st2; s->stream3 = st3;
+       !cuda_ok(cudaStreamCreateWithFlags(&st3, cudaStreamNonBlocking), "cudaStreamCreate") ||
+       !cuda_ok(cudaStreamCreateWithFlags(&st4, cudaStreamNonBlocking), "cudaStreamCreate")){ scene_free_device(s); return PT_ERR_CUDA; }
+    s->stream = st; s->stream2 = st2; s->stream3 = st3; s->stream4 = st4;
     if(!cuda_ok(cudaMalloc(&b.stats, 64), "cudaMalloc stats") ||
        !cuda_ok(cudaMalloc(&b.cursors, kCursorRing * sizeof(unsigned long long)), "cudaMalloc cursors")){ scene_free_device(s); return PT_ERR_CUDA; }
     s->committed = true;

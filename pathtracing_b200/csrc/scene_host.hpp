@@ -103,6 +103,7 @@ struct pt_scene {
     void* stream = nullptr;       // internal stream for the host-buffer entry points
     void* stream2 = nullptr;      // H2D stage of the host-buffer pipeline
     void* stream3 = nullptr;      // D2H stage
+    void* stream4 = nullptr;      // second trace stream of the host-buffer pipeline (odd chunks): chunk tails overlap
     std::vector<void*> events;    // cudaEvent_t pool of the pipeline (no timing)
     unsigned cursor_next = 0;
     bool has_wrappers = false;    // some top-level primitive is a wrapper chain (INST_ANIM / INST_WRAP): kWrap kernel variants
