@@ -35,7 +35,7 @@ static int ensure_stage(pt_scene* s, size_t n){
 static size_t chunk_rays(){
     static size_t v = 0;
     if(!v){
-        v = 4u << 20;
+        v = 2u << 20;      // 2 Mi rays: best of the 0.75-8 Mi sweep with two trace streams (scratch/e2e_sweep.py)
         if(const char* e = getenv("PTB_CHUNK")){ const long long x = atoll(e); if(x >= 1024)v = (size_t)x; }
     }
     return v;
