@@ -353,7 +353,7 @@ int pack_traversal(pt_scene* s, int width, PackedTraversal& P, BvhBuilder builde
         }
         insts.push_back(I);
         const uint32_t extra = (uint32_t)insts.size() - head - 1;
-        if(extra)s->has_wrappers = true;
+        if(extra || hi.blas < 0)s->has_wrappers = true;
         insts[head].flags |= (tf.leaf_last[k] ? INST_LAST : 0u) | (extra << INST_EXTRA_SHIFT);
     }
     // TLAS leaf refs: leaf position -> head record

@@ -106,7 +106,7 @@ struct pt_scene {
     void* stream4 = nullptr;      // second trace stream of the host-buffer pipeline (odd chunks): chunk tails overlap
     std::vector<void*> events;    // cudaEvent_t pool of the pipeline (no timing)
     unsigned cursor_next = 0;
-    bool has_wrappers = false;    // some top-level primitive is a wrapper chain (INST_ANIM / INST_WRAP): kWrap kernel variants
+    bool has_wrappers = false;    // some top-level primitive is an analytic shape or a wrapper chain (INST_SPHERE / QUAD / ANIM / WRAP): kWrap kernel variants
     bool has_alpha_tex = false;   // some triangle carries TRI_ALPHA_TEX: traversal must evaluate Material::Alpha
     bool has_boundary = false;    // some primitive has no material (a medium boundary): VolPath shadow rays walk through it
     uint64_t alpha_salt = 0;      // advances per launch (AlphaTester Blend draws)

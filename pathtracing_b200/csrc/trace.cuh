@@ -163,9 +163,12 @@ __device__ __forceinline__ bool tri_any(const RayCtx& r, const TriData& T, float
 // Primitive.cpp:6-26).  The ray-cast entry points pass NoAlpha; the integrator
 // passes a functor that evaluates the material's alpha texture.
 // operator()(mesh, prim, inst_record, u, v, ray index) -> accept the hit?
-// kWrap: does this kernel variant understand wrapper chains (AnimatedPrimitive, TransformedPrimitive over a
-// shape; pt_types.h)?  The plain ray-cast variant does not carry that code (64 registers instead of 78:
-// 8 instead of 6 CTAs per SM); a scene that holds a wrapper runs the general (AlphaTex) variant.
+// kWrap: does this kernel variant understand analytic shapes and wrapper chains (sphere / quad GeometricPrimitives,
+// AnimatedPrimitive, TransformedPrimitive over a shape; pt_types.h)?  The plain variant -- TLAS of BLAS instances,
+// the C2-C5 case -- does not carry that code: with the wrappers compiled in it needs 78 registers instead of 64
+// (6 instead of 8 CTAs per SM), and the shape branch alone costs the BVH2 kernel 7 % (63 registers instead of 55,
+// 940 instead of 1008 Mrays/s on the C2 soup, scratch/bvh2_bisect.py).  A scene that holds a shape or a wrapper
+// runs the general (AlphaTex) variant.
 struct NoAlpha {
     static constexpr bool kWrap = false;
     __device__ __forceinline__ bool operator()(uint32_t, uint32_t, uint32_t, float, float, size_t) const{ return true; }
@@ -554,7 +557,7 @@ __device__ __forceinline__ void trav_step(TravState& s, const DevScene& S, const
                 }
                 return;
             }
-            if(d.meta.y & (INST_SPHERE | INST_QUAD)){
+            if((Alpha::kWrap || STATS) && (d.meta.y & (INST_SPHERE | INST_QUAD))){
                 // GeometricPrimitive over an analytic shape sitting directly in the TLAS leaf
                 float t, u = 0.0f, v = 0.0f;
                 const bool hit = (d.meta.y & INST_SPHERE) ? sphere_hit(s.r, d, s.tmax, t) : quad_hit(s.r, d, s.tmax, t, u, v);

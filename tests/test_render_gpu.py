@@ -306,9 +306,13 @@ def test_adaptive_sampling_loop(integrator, spp):
     assert np.allclose(gn, np.round(gn)) and gn.min() >= 1 and gn.max() <= 128
     assert g_stats["samples"] == int(round(g_rgbw[..., 3].sum())) and r_stats["samples"] == int(round(r_rgbw[..., 3].sum()))
     assert rn.max() > 4, "scene too easy: the reference never iterates"
-    # the total is dominated by the few pixels that run to the 128-round cap: loose; the rule itself is
-    # compared through the distribution of rounds per pixel
-    assert abs(g_stats["samples"] / r_stats["samples"] - 1.0) < 0.3, (g_stats["samples"], r_stats["samples"])
+    # the raw total is dominated by the two or three dozen pixels that run to the 128-round cap (512 samples each;
+    # their count is Poisson-like, and the reference is seeded from random_device: 25144 vs 16704 was seen once),
+    # so the totals are compared with the rounds per pixel clipped at 16; the rule itself is compared through
+    # the distribution of rounds per pixel
+    cr, cg = float(np.minimum(rn, 16).sum()), float(np.minimum(gn, 16).sum())
+    assert abs(cg / cr - 1.0) < 0.15, (cg, cr, g_stats["samples"], r_stats["samples"])
+    assert abs(g_stats["samples"] / r_stats["samples"] - 1.0) < 0.6, (g_stats["samples"], r_stats["samples"])
     npx = W * H
     for lo, hi in ((1, 1), (2, 3), (4, 11), (12, 128)):
         cr, cg = int(((rn >= lo) & (rn <= hi)).sum()), int(((gn >= lo) & (gn <= hi)).sum())
