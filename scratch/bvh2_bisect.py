@@ -19,7 +19,7 @@ from pathtracing_b200 import synth
 from pathtracing_b200.scene import GpuScene
 desc = synth.soup_scene(1000000)
 n = 1 << 24
-for width in (2, 4):
+for width in tuple(int(x) for x in os.environ.get("PTB_WIDTHS", "2,4").split(",")):
     scene = GpuScene(desc, width)
     lo, hi = scene.bounds()
     rays = torch.from_numpy(synth.random_rays(n, lo, hi, seed=7).view(np.uint8).reshape(-1)).cuda()
