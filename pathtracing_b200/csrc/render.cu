@@ -35,20 +35,31 @@ struct FilterParams {   // Filter.hpp:29-144
     double p0, p1, gx, gy, inv_integral;
 };
 
+// Path state of one slot: four 16 B quarters
+//   0 thr   throughput rgb, prevPDF           1 rad   radiance rgb
+//   2 rng (pcg state, 8 B; inc is rebuilt from the sample id), depth (low 16) | rr_depth (high 16), mflag (bit0 spec, bits 1..: medium id + 1)
+//   3 gid (which camera sample lives in the slot, 8 B), spos (fractional sample position inside the pixel)
+// laid out one of two ways (ps_at):
+//  * records (quarter k of slot i at 4 i + k): a call whose samples outnumber the pool regenerates finished slots,
+//    and after a few rounds queue order is a random order over the pool: every access is a gather / scatter.  As
+//    seven arrays that cost seven partial-sector writes per regenerated sample (DRAM read-modify-write each:
+//    k_generate ran at a tenth of its sequential speed, 7 % of a C3 frame); a record is two whole sectors.
+//    C3 335 -> 371, C4 285 -> 307 Msamples/s.
+//  * planes (quarter k of slot i at k cap + i): a call that fits the pool (C1) keeps queue order == slot order, and
+//    planes keep a warp's access to one quarter on 4 cache lines instead of 16 (records cost C1 8 %).
 struct Arena {
     float4* rays[2]; uint32_t* qslot[2];
     float4* hits; uint32_t* hinst;
     float4* srays; uint32_t* sslot; float4* scontrib; uint8_t* socc;
-    float4* thr;        // throughput rgb, prevPDF
-    float4* rad;        // radiance rgb
-    uint32_t* depth;    // depth (low 16) | rr_depth (high 16)
-    uint32_t* mflag;    // bit0 spec, bits 1..: medium id + 1
-    uint64_t* rng;      // pcg state (inc is rebuilt from the sample id)
-    float2* spos;       // fractional sample position inside the pixel
-    uint64_t* gid;      // which camera sample lives in the slot (index into this call's sample sequence)
+    float4* ps;         // per-slot path state, 4 quarters per slot (see above)
+    uint32_t ps_slot, ps_quarter;   // index strides: (4, 1) records | (1, cap) planes
     uint32_t* done;     // slots whose path ended in the last shade pass: splatted, then handed to new samples
     uint32_t* counters; // [0] next-queue size, [1] shadow-queue size, [2] done-list size, [3] non-finite samples of the call
 };
+
+__device__ __forceinline__ float4* ps_at(const Arena& A, uint32_t slot, uint32_t k){
+    return A.ps + ((size_t)slot * A.ps_slot + (size_t)k * A.ps_quarter);
+}
 
 struct BatchInfo {     // how a sample id maps to (pixel, sample index): id = pass_k * W*H + pixel
     int W, H, pass_begin, pass_stride, max_depth;
@@ -123,13 +134,12 @@ __global__ void __launch_bounds__(256) k_generate(Arena A, BatchInfo B, CamParam
     A.rays[cur][2 * q] = make_float4(org.x, org.y, org.z, CUDART_INF_F);
     A.rays[cur][2 * q + 1] = make_float4(dir.x, dir.y, dir.z, t);
     A.qslot[cur][q] = slot;
-    A.gid[slot] = gid;
-    A.thr[slot] = make_float4(1.0f, 1.0f, 1.0f, 1.0f);
-    A.rad[slot] = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
-    A.depth[slot] = 1u;                                          // `depth++ < maxDepth` already taken for bounce 1
-    A.mflag[slot] = 1u | ((uint32_t)(C.medium + 1) << 1);
-    A.rng[slot] = g.state;
-    A.spos[slot] = make_float2((float)jx, (float)jy);
+    *ps_at(A, slot, 0) = make_float4(1.0f, 1.0f, 1.0f, 1.0f);
+    *ps_at(A, slot, 1) = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+    // depth 1: `depth++ < maxDepth` already taken for bounce 1
+    *ps_at(A, slot, 2) = make_float4(__uint_as_float((uint32_t)g.state), __uint_as_float((uint32_t)(g.state >> 32)), __uint_as_float(1u),
+                       __uint_as_float(1u | ((uint32_t)(C.medium + 1) << 1)));
+    *ps_at(A, slot, 3) = make_float4(__uint_as_float((uint32_t)gid), __uint_as_float((uint32_t)(gid >> 32)), (float)jx, (float)jy);
 }
 
 // ---- connect: add the unoccluded NEE contributions (Integrators.cpp:243-244, 356, 398) ------
@@ -138,9 +148,9 @@ __global__ void __launch_bounds__(256) k_connect(Arena A, uint32_t n){
     if(k >= n || A.socc[k])return;
     const uint32_t slot = A.sslot[k];
     const float4 c = A.scontrib[k];
-    float4 r = A.rad[slot];
+    float4 r = *ps_at(A, slot, 1);
     r.x += c.x; r.y += c.y; r.z += c.z;
-    A.rad[slot] = r;
+    *ps_at(A, slot, 1) = r;
 }
 
 // ---- connect through medium boundaries: Scene::IntersectTr (Scene.cpp:8-29) ---------------------------
@@ -176,9 +186,9 @@ __global__ void __launch_bounds__(128) k_shadow_tr(Arena A, DevScene D, ShadeSce
     }
     if(blocked)return;
     const uint32_t slot = A.sslot[k];
-    float4 r = A.rad[slot];
+    float4 r = *ps_at(A, slot, 1);
     r.x += c.x * tr.x; r.y += c.y * tr.y; r.z += c.z * tr.z;
-    A.rad[slot] = r;
+    *ps_at(A, slot, 1) = r;
 }
 
 template <class Alpha>
@@ -242,10 +252,11 @@ __global__ void __launch_bounds__(256) k_film(Arena A, BatchInfo B, FilterParams
     if(i >= n_done)return;
     const uint32_t slot = done ? done[i] : i;
     uint32_t pixel, sample;
-    stream_of(B, A.gid[slot], pixel, sample);
+    const float4 q3 = *ps_at(A, slot, 3);
+    stream_of(B, (uint64_t)__float_as_uint(q3.x) | ((uint64_t)__float_as_uint(q3.y) << 32), pixel, sample);
     const int x = (int)(pixel % (uint32_t)B.W), y = (int)(pixel / (uint32_t)B.W);
-    const float4 r = A.rad[slot];
-    const float2 sp = A.spos[slot];
+    const float4 r = *ps_at(A, slot, 1);
+    const float2 sp = make_float2(q3.z, q3.w);
     if(!(fabsf(r.x) <= 3.0e38f && fabsf(r.y) <= 3.0e38f && fabsf(r.z) <= 3.0e38f)){
         atomicAdd(A.counters + 3, 1u);       // non-finite radiance: counted, not splatted (one NaN would own the pixel)
         return;
@@ -363,17 +374,19 @@ __global__ void __launch_bounds__(128) k_shade(Arena A, ShadeScene S, BatchInfo 
         ntime = rb.w;
         const float4 h = A.hits[j];
         const uint32_t prim = __float_as_uint(h.w);
-        float4 thr4 = A.thr[slot];
+        float4 thr4 = *ps_at(A, slot, 0);
         V3 att = v3(thr4.x, thr4.y, thr4.z);
         float prev_pdf = thr4.w;
-        float4 rad4 = A.rad[slot];
+        float4 rad4 = *ps_at(A, slot, 1);
         V3 outp = v3(rad4.x, rad4.y, rad4.z);
-        uint32_t dw = A.depth[slot], mf = A.mflag[slot];
+        const uint4 st4 = *reinterpret_cast<const uint4*>(ps_at(A, slot, 2));     // rng, depth, mflag
+        const float4 q3 = *ps_at(A, slot, 3);                                    // gid, spos
+        uint32_t dw = st4.z, mf = st4.w;
         uint32_t depth = dw & 0xFFFFu, rr_depth = dw >> 16;
         bool spec = (mf & 1u) != 0;
         int medium = (int)(mf >> 1) - 1;
         uint32_t pixel, sample;
-        Pcg g; g.inc = pcg_inc(B.seed, stream_of(B, A.gid[slot], pixel, sample)); g.state = A.rng[slot];
+        Pcg g; g.inc = pcg_inc(B.seed, stream_of(B, (uint64_t)__float_as_uint(q3.x) | ((uint64_t)__float_as_uint(q3.y) << 32), pixel, sample)); g.state = (uint64_t)st4.x | ((uint64_t)st4.y << 32);
 
         if(prim == 0xFFFFFFFFu){
             // miss: infinite lights (Integrators.cpp:136-141, 197-207, 308-330)
@@ -473,11 +486,10 @@ __global__ void __launch_bounds__(128) k_shade(Arena A, ShadeScene S, BatchInfo 
             if(alive && (int)depth < B.max_depth && (att.x + att.y + att.z) > 0.0f){ cont = true; depth++; }
         }
         nee = ne.want;
-        A.thr[slot] = make_float4(att.x, att.y, att.z, prev_pdf);
-        A.rad[slot] = make_float4(outp.x, outp.y, outp.z, 0.0f);
-        A.depth[slot] = depth | (rr_depth << 16);
-        A.mflag[slot] = (spec ? 1u : 0u) | ((uint32_t)(medium + 1) << 1);
-        A.rng[slot] = g.state;
+        *ps_at(A, slot, 0) = make_float4(att.x, att.y, att.z, prev_pdf);
+        *ps_at(A, slot, 1) = make_float4(outp.x, outp.y, outp.z, 0.0f);
+        *ps_at(A, slot, 2) = make_float4(__uint_as_float((uint32_t)g.state), __uint_as_float((uint32_t)(g.state >> 32)), __uint_as_float(depth | (rr_depth << 16)),
+                            __uint_as_float((spec ? 1u : 0u) | ((uint32_t)(medium + 1) << 1)));
     }
     const uint32_t qn = queue_slot(A.counters + 0, cont);
     if(cont){
@@ -546,8 +558,7 @@ static size_t arena_layout(char* base, Arena& A, size_t cap){
     carve(p, (void**)&A.qslot[0], cap * 4); carve(p, (void**)&A.qslot[1], cap * 4);
     carve(p, (void**)&A.hits, cap * 16); carve(p, (void**)&A.hinst, cap * 4);
     carve(p, (void**)&A.srays, cap * 32); carve(p, (void**)&A.sslot, cap * 4); carve(p, (void**)&A.scontrib, cap * 16); carve(p, (void**)&A.socc, cap);
-    carve(p, (void**)&A.thr, cap * 16); carve(p, (void**)&A.rad, cap * 16); carve(p, (void**)&A.depth, cap * 4); carve(p, (void**)&A.mflag, cap * 4);
-    carve(p, (void**)&A.rng, cap * 8); carve(p, (void**)&A.spos, cap * 8); carve(p, (void**)&A.gid, cap * 8); carve(p, (void**)&A.done, cap * 4);
+    carve(p, (void**)&A.ps, cap * 64); carve(p, (void**)&A.done, cap * 4);
     carve(p, (void**)&A.counters, 256);
     return (size_t)(p - base);
 }
@@ -670,6 +681,8 @@ int render_passes(pt_scene* s, const pt_camera_desc* cam, const pt_render_params
         B.tr_walk = tr_walk ? 1 : 0;
         uint64_t next_gid = 0;
         if(count == 0)return PT_OK;                   // more ranks than samples per round
+        // a run that fits the pool never regenerates a slot: queue order stays slot order -> planes; else records
+        if(count <= cap){ A.ps_slot = 1; A.ps_quarter = (uint32_t)cap; } else{ A.ps_slot = 4; A.ps_quarter = 1; }
         if(rp->max_depth <= 0){
             // `depth++ < maxDepth` fails at once: black samples that still carry their filter weight
             while(next_gid < count){
