@@ -53,6 +53,7 @@ struct Arena {
     float4* srays; uint32_t* sslot; float4* scontrib; uint8_t* socc;
     float4* ps;         // per-slot path state, 4 quarters per slot (see above)
     uint32_t ps_slot, ps_quarter;   // index strides: (4, 1) records | (1, cap) planes
+    uint8_t* skey; uint32_t* perm; uint32_t* shist;   // shade-order sort: class per queue entry, sorted order, per-block histograms
     uint32_t* done;     // slots whose path ended in the last shade pass: splatted, then handed to new samples
     uint32_t* counters; // [0] next-queue size, [1] shadow-queue size, [2] done-list size, [3] non-finite samples of the call
 };
@@ -311,6 +312,78 @@ __global__ void __launch_bounds__(256) k_est_merge(double* __restrict__ est, dou
     if(i < n){ est[i] += round[i]; round[i] = 0.0; }
 }
 
+// ---- shade order: queue entries grouped by what k_shade will do with them -----------------------------------
+// A warp of k_shade that holds a miss, a medium boundary, a Lambertian, a rough dielectric and a mirror runs all
+// five code paths one after the other (profiles/r01_shade.md: 10.9 of 32 lanes per instruction).  A stable
+// counting sort of the queue by class -- key pass with per-block histograms, one scan, one scatter pass --
+// gives k_shade an order in which neighbouring lanes take the same branch; it reads its entry through `perm`.
+constexpr int kSortBlock = 256;
+constexpr int kSortKeys = 8;       // 0 miss | 1 medium boundary | 2.. material kind (+4 when the hit carries an area light)
+
+__device__ __forceinline__ uint32_t shade_class(const Arena& A, const ShadeScene& S, uint32_t j){
+    const uint32_t prim = __float_as_uint(A.hits[j].w);
+    if(prim == 0xFFFFFFFFu)return 0u;
+    const DevInstShade& I = S.inst[A.hinst[j]];
+    int mat;
+    if(I.shape >= 0)mat = I.material;
+    else mat = S.meshes[S.tri_mesh[S.blas[I.blas].tri_base + prim]].material;
+    if(mat < 0)return 1u;
+    return 2u + (uint32_t)S.materials[mat].kind;      // pt_mat_kind 0..3
+}
+
+__global__ void __launch_bounds__(kSortBlock) k_sort_count(Arena A, ShadeScene S, uint32_t n, uint32_t nb){
+    __shared__ uint32_t h[kSortKeys];
+    if(threadIdx.x < kSortKeys)h[threadIdx.x] = 0u;
+    __syncthreads();
+    const uint32_t j = blockIdx.x * kSortBlock + threadIdx.x;
+    if(j < n){
+        const uint32_t k = shade_class(A, S, j);
+        A.skey[j] = (uint8_t)k;
+        atomicAdd(&h[k], 1u);
+    }
+    __syncthreads();
+    if(threadIdx.x < kSortKeys)A.shist[threadIdx.x * nb + blockIdx.x] = h[threadIdx.x];   // key-major: one scan gives final offsets
+}
+
+// exclusive scan of `m` counters in place, one block
+__global__ void __launch_bounds__(1024) k_sort_scan(uint32_t* __restrict__ v, uint32_t m){
+    __shared__ uint32_t part[1024];
+    const uint32_t per = (m + 1023u) / 1024u;
+    const uint32_t lo = threadIdx.x * per, hi = min(lo + per, m);
+    uint32_t sum = 0;
+    for(uint32_t i = lo; i < hi; i++)sum += v[i];
+    part[threadIdx.x] = sum;
+    __syncthreads();
+    for(int o = 1; o < 1024; o <<= 1){
+        const uint32_t x = threadIdx.x >= (unsigned)o ? part[threadIdx.x - o] : 0u;
+        __syncthreads();
+        part[threadIdx.x] += x;
+        __syncthreads();
+    }
+    uint32_t run = part[threadIdx.x] - sum;
+    for(uint32_t i = lo; i < hi; i++){ const uint32_t c = v[i]; v[i] = run; run += c; }
+}
+
+__global__ void __launch_bounds__(kSortBlock) k_sort_scatter(Arena A, uint32_t n, uint32_t nb){
+    __shared__ uint32_t wc[kSortBlock / 32][kSortKeys];
+    const uint32_t j = blockIdx.x * kSortBlock + threadIdx.x;
+    const unsigned lane = threadIdx.x & 31u, w = threadIdx.x >> 5;
+    const uint32_t k = j < n ? (uint32_t)A.skey[j] : 0xFFu;
+    uint32_t rank = 0;
+#pragma unroll
+    for(uint32_t c = 0; c < (uint32_t)kSortKeys; c++){
+        const unsigned m = __ballot_sync(0xffffffffu, k == c);
+        if(k == c)rank = __popc(m & ((1u << lane) - 1u));
+        if(lane == 0)wc[w][c] = __popc(m);
+    }
+    __syncthreads();
+    if(j < n){
+        uint32_t off = A.shist[k * nb + blockIdx.x] + rank;
+        for(unsigned q = 0; q < w; q++)off += wc[q][k];
+        A.perm[off] = j;
+    }
+}
+
 // ---- shade: one bounce of Li() for every queue entry ------------------------------------------
 
 struct NeeOut { bool want; V3 o, d; float tmax; V3 contrib; int medium; };
@@ -361,8 +434,9 @@ __device__ inline void sample_ld(const ShadeScene& S, const SurfInt& si, const M
 
 // 96 registers: forcing 6 or 8 resident CTAs (80 / 64 registers, spills) measured slower
 template <int INTEG>
-__global__ void __launch_bounds__(128) k_shade(Arena A, ShadeScene S, BatchInfo B, uint32_t n, int cur){
-    const uint32_t j = blockIdx.x * blockDim.x + threadIdx.x;
+__global__ void __launch_bounds__(128) k_shade(Arena A, ShadeScene S, BatchInfo B, uint32_t n, int cur, const uint32_t* __restrict__ perm){
+    const uint32_t tid = blockIdx.x * blockDim.x + threadIdx.x;
+    const uint32_t j = (perm && tid < n) ? perm[tid] : tid;      // shade order (k_sort_*) or queue order
     bool cont = false, nee = false;
     V3 no = v3(0.0f), nd = v3(0.0f); float ntime = 0.0f;
     NeeOut ne; ne.want = false;
@@ -559,6 +633,7 @@ static size_t arena_layout(char* base, Arena& A, size_t cap){
     carve(p, (void**)&A.hits, cap * 16); carve(p, (void**)&A.hinst, cap * 4);
     carve(p, (void**)&A.srays, cap * 32); carve(p, (void**)&A.sslot, cap * 4); carve(p, (void**)&A.scontrib, cap * 16); carve(p, (void**)&A.socc, cap);
     carve(p, (void**)&A.ps, cap * 64); carve(p, (void**)&A.done, cap * 4);
+    carve(p, (void**)&A.skey, cap); carve(p, (void**)&A.perm, cap * 4); carve(p, (void**)&A.shist, ((cap + kSortBlock - 1) / kSortBlock) * kSortKeys * 4 + 4096);
     carve(p, (void**)&A.counters, 256);
     return (size_t)(p - base);
 }
@@ -670,6 +745,13 @@ int render_passes(pt_scene* s, const pt_camera_desc* cam, const pt_render_params
     // long tail of deep paths is paid once per call and not once per batch.
     double host_wait_s = 0.0; unsigned iterations = 0;
     const bool tr_walk = rp->integrator == PT_INTEGRATOR_VOLPATH && s->has_boundary;
+    // shade-order sort (k_sort_*).  Measured on one B200 (scratch/stage_prof.py, shade stage incl. the sort): C4
+    // (VolPath: medium events, textured materials) 218.8 -> 178.7 ms, C3 (PathIntegrator, four material kinds)
+    // 59.2 -> 58.1 ms, C1 (one material) 1.89 -> 2.82 ms.  So: on for VolPathIntegrator, off otherwise;
+    // PTB_SORT=0 / 1 forces it, PTB_SORT_MIN sets the smallest queue worth sorting.
+    static const int sort_env = []{ const char* e = getenv("PTB_SORT"); return e ? (atoi(e) != 0 ? 1 : 0) : -1; }();
+    const bool sort_shade = sort_env >= 0 ? sort_env == 1 : rp->integrator == PT_INTEGRATOR_VOLPATH;
+    static const uint32_t sort_min = []{ const char* e = getenv("PTB_SORT_MIN"); return e ? (uint32_t)atoll(e) : 65536u; }();
     StageLog log; log.on = getenv("PTB_PROFILE") != nullptr; log.st = st;
     log.mark(0);
     const auto t_host0 = std::chrono::steady_clock::now();
@@ -705,10 +787,19 @@ int render_passes(pt_scene* s, const pt_camera_desc* cam, const pt_render_params
             log.mark(2);
             if(!cuda_ok(cudaMemsetAsync(A.counters, 0, 12, st), "counter reset"))return PT_ERR_CUDA;
             const unsigned grid = (n + 127) / 128;
+            const uint32_t* perm = nullptr;
+            if(sort_shade && n >= sort_min){
+                const uint32_t nb = (n + kSortBlock - 1) / kSortBlock;
+                k_sort_count<<<nb, kSortBlock, 0, st>>>(A, s->shade, n, nb);
+                k_sort_scan<<<1, 1024, 0, st>>>(A.shist, nb * kSortKeys);
+                k_sort_scatter<<<nb, kSortBlock, 0, st>>>(A, n, nb);
+                R.kernel_launches += 3;
+                perm = A.perm;
+            }
             switch(rp->integrator){
-            case PT_INTEGRATOR_SIMPLE: k_shade<PT_INTEGRATOR_SIMPLE><<<grid, 128, 0, st>>>(A, s->shade, B, n, cur); break;
-            case PT_INTEGRATOR_PATH: k_shade<PT_INTEGRATOR_PATH><<<grid, 128, 0, st>>>(A, s->shade, B, n, cur); break;
-            default: k_shade<PT_INTEGRATOR_VOLPATH><<<grid, 128, 0, st>>>(A, s->shade, B, n, cur); break;
+            case PT_INTEGRATOR_SIMPLE: k_shade<PT_INTEGRATOR_SIMPLE><<<grid, 128, 0, st>>>(A, s->shade, B, n, cur, perm); break;
+            case PT_INTEGRATOR_PATH: k_shade<PT_INTEGRATOR_PATH><<<grid, 128, 0, st>>>(A, s->shade, B, n, cur, perm); break;
+            default: k_shade<PT_INTEGRATOR_VOLPATH><<<grid, 128, 0, st>>>(A, s->shade, B, n, cur, perm); break;
             }
             R.kernel_launches++;
             log.mark(3);
