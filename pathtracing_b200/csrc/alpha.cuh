@@ -21,6 +21,22 @@ struct AlphaTex {
     static constexpr bool kWrap = true;      // the general traversal variant (trace.cuh NoAlpha)
     ShadeScene S;
     uint64_t salt;
+    // Material::Alpha(uv) (Material.hpp:336-342, 572-578) through AlphaTester (:181-198)
+    PT_HDI bool test(const DevMaterial& M, float u, float v, uint32_t prim, uint32_t inst_rec, size_t ray) const{
+        const float a = M.alpha >= 0 ? tex_eval(S, M.alpha, u, v, v3(0.0f)).x : tex_alpha(S, M.tex, u, v);
+        switch(M.alpha_mode){
+        case PT_ALPHA_BLEND: return alpha_uniform(salt, (uint64_t)ray, prim, inst_rec) < a;
+        case PT_ALPHA_MASK: return a > M.alpha_cutoff;
+        default: return true;
+        }
+    }
+    // a sphere / quad GeometricPrimitive: (a, b, c) = hit point - center (SphereShape::Intersect: uv = GetSphereUV of the
+    // normal, Shape.cpp:11-17) or (a, b) = the quad's (alpha, beta) (Shape.cpp:333-340)
+    PT_HDI bool shape(uint32_t material, bool sphere, float a, float b, float c, uint32_t inst_rec, size_t ray) const{
+        float u = a, v = b;
+        if(sphere)sphere_uv(v3(a, b, c), u, v);
+        return test(S.materials[material], u, v, 0u, inst_rec, ray);
+    }
     PT_HDI bool operator()(uint32_t mesh, uint32_t prim, uint32_t inst_rec, float bu, float bv, size_t ray) const{
         const DevMesh m = S.meshes[mesh];
         if(m.material < 0)return true;
@@ -31,12 +47,7 @@ struct AlphaTex {
         const float w = 1.0f - bu - bv;
         const float u = bu * S.uv[2 * (size_t)i1] + bv * S.uv[2 * (size_t)i2] + w * S.uv[2 * (size_t)i0];
         const float v = bu * S.uv[2 * (size_t)i1 + 1] + bv * S.uv[2 * (size_t)i2 + 1] + w * S.uv[2 * (size_t)i0 + 1];
-        const float a = M.alpha >= 0 ? tex_eval(S, M.alpha, u, v, v3(0.0f)).x : tex_alpha(S, M.tex, u, v);
-        switch(M.alpha_mode){
-        case PT_ALPHA_BLEND: return alpha_uniform(salt, (uint64_t)ray, prim, inst_rec) < a;
-        case PT_ALPHA_MASK: return a > M.alpha_cutoff;
-        default: return true;
-        }
+        return test(M, u, v, prim, inst_rec, ray);
     }
 };
 

@@ -272,7 +272,7 @@ int pack_traversal(pt_scene* s, int width, PackedTraversal& P, BvhBuilder builde
     for(uint32_t i = 0; i < ni; i++){
         const HostInstance& hi = s->instances[i];
         if(hi.blas < 0){
-            if(material_alpha_flags(s, hi.shape.material) & TRI_ALPHA_TEX){ set_error("alpha-tested materials on sphere / quad shapes are not supported"); return PT_ERR_INVALID; }
+            if(material_alpha_flags(s, hi.shape.material) & TRI_ALPHA_TEX)s->has_alpha_tex = true;
             if(hi.shape.material < 0)s->has_boundary = true;
             iboxes[i] = shape_box(hi.shape);
             if(hi.has_xf)iboxes[i] = transform_box(hi.xf, iboxes[i]);    // TransformedPrimitive::BoundingBox, Primitive.cpp:32-40
@@ -341,6 +341,7 @@ int pack_traversal(pt_scene* s, int width, PackedTraversal& P, BvhBuilder builde
         if(hi.blas < 0){
             pack_shape(hi.shape, I);
             I.id = id;
+            if(material_alpha_flags(s, hi.shape.material) & TRI_ALPHA_TEX){ I.flags |= INST_ALPHA; I.root = (uint32_t)hi.shape.material; }
         } else{
             const HostBlas& hb = s->blas[hi.blas];
             for(int c = 0; c < 4; c++)for(int r = 0; r < 3; r++)I.inv[c * 3 + r] = inv[c * 4 + r];

@@ -172,6 +172,7 @@ __device__ __forceinline__ bool tri_any(const RayCtx& r, const TriData& T, float
 struct NoAlpha {
     static constexpr bool kWrap = false;
     __device__ __forceinline__ bool operator()(uint32_t, uint32_t, uint32_t, float, float, size_t) const{ return true; }
+    __device__ __forceinline__ bool shape(uint32_t, bool, float, float, float, uint32_t, size_t) const{ return true; }
 };
 
 struct NoAlphaWrap : NoAlpha { static constexpr bool kWrap = true; };   // whole-ray walks: host emulation, tiny scenes
@@ -185,6 +186,16 @@ __device__ __forceinline__ InstData load_inst(const Instance* inst, uint32_t i){
     d.meta = __ldg(reinterpret_cast<const uint4*>(p + 3));
     d.b0 = __ldg(p + 4); d.b1 = __ldg(p + 5);
     return d;
+}
+
+// Material::Alpha on a candidate hit of a sphere / quad record flagged INST_ALPHA
+template <class Alpha>
+__device__ __forceinline__ bool shape_alpha(const Alpha& alpha, const RayCtx& r, const InstData& c, float t, float u, float v, uint32_t inst_rec, size_t ray_idx){
+    if(c.meta.y & INST_SPHERE){
+        const float ax = f_sub(f_add(r.ox, f_mul(r.dx, t)), c.m0.x), ay = f_sub(f_add(r.oy, f_mul(r.dy, t)), c.m0.y), az = f_sub(f_add(r.oz, f_mul(r.dz, t)), c.m0.z);
+        return alpha.shape(c.meta.x, true, ax, ay, az, inst_rec, ray_idx);
+    }
+    return alpha.shape(c.meta.x, false, u, v, 0.0f, inst_rec, ray_idx);
 }
 
 // SphereShape::Intersect / IntersectPred (Shape.cpp:3-56): both roots, strict `eps < t < max`.
@@ -531,7 +542,8 @@ __device__ __forceinline__ void trav_step(TravState& s, const DevScene& S, const
                 if(c.meta.y & INST_WRAP)c = load_inst(S.inst, ++j);
                 if(c.meta.y & (INST_SPHERE | INST_QUAD)){
                     float t, u = 0.0f, v = 0.0f;
-                    const bool hit = (c.meta.y & INST_SPHERE) ? sphere_hit(r, c, tm, t) : quad_hit(r, c, tm, t, u, v);
+                    bool hit = (c.meta.y & INST_SPHERE) ? sphere_hit(r, c, tm, t) : quad_hit(r, c, tm, t, u, v);
+                    if(hit && (c.meta.y & INST_ALPHA))hit = shape_alpha(alpha, r, c, t, u, v, i, ray_idx);
                     if(hit){
                         if(ANY){ s.flags |= TF_OCCLUDED | TF_DONE; return; }
                         if(xf)t = f_div(t, len_b);
@@ -560,7 +572,8 @@ __device__ __forceinline__ void trav_step(TravState& s, const DevScene& S, const
             if((Alpha::kWrap || STATS) && (d.meta.y & (INST_SPHERE | INST_QUAD))){
                 // GeometricPrimitive over an analytic shape sitting directly in the TLAS leaf
                 float t, u = 0.0f, v = 0.0f;
-                const bool hit = (d.meta.y & INST_SPHERE) ? sphere_hit(s.r, d, s.tmax, t) : quad_hit(s.r, d, s.tmax, t, u, v);
+                bool hit = (d.meta.y & INST_SPHERE) ? sphere_hit(s.r, d, s.tmax, t) : quad_hit(s.r, d, s.tmax, t, u, v);
+                if(hit && (d.meta.y & INST_ALPHA))hit = shape_alpha(alpha, s.r, d, t, u, v, i, ray_idx);
                 if(hit){
                     if(ANY){ s.flags |= TF_OCCLUDED | TF_DONE; return; }
                     s.tmax = t; s.hu = u; s.hv = v; s.hprim = 0u; s.hinst = d.meta.z;

@@ -600,3 +600,23 @@ def with_times(rays, seed=3, lo=-0.25, hi=1.25):
     rays = rays.copy()
     rays["time"] = (lo + (hi - lo) * rng.random(len(rays))).astype(np.float32)
     return rays
+
+
+def alpha_shapes_scene(mode=capi.ALPHA_MASK, wrapped=True):
+    """alpha_scene plus alpha-tested analytic shapes (GeometricPrimitive::Intersect[Pred] runs Material::Alpha on the
+    shape's own uv, Primitive.cpp:6-26): a sphere whose opacity comes from a checker over GetSphereUV, a quad card with
+    a smooth opacity image over (alpha, beta), and -- wrapped -- the same kind of card inside a TransformedPrimitive."""
+    d, cam = alpha_scene(mode)
+    n = 32
+    y, x = np.mgrid[0:n, 0:n].astype(np.float32) / n
+    opacity = np.clip(0.5 + 0.5 * np.sin(6.28 * 3 * x) * np.cos(6.28 * 2 * y), 0.0, 1.0)
+    to8 = lambda a: np.ascontiguousarray(np.clip(np.round(a * 255), 0, 255).astype(np.uint8))
+    a_img = d.image_u8(to8(np.repeat(opacity[..., None], 3, -1)))
+    holes = d.checker(d.solid((1, 1, 1)), d.solid((0.2, 0.2, 0.2)), (0.125, 0.125))
+    ball = d.diffuse(d.solid((0.8, 0.3, 0.2)), alpha=holes, alpha_mode=mode, alpha_cutoff=0.5)
+    card = d.diffuse(d.solid((0.2, 0.4, 0.8)), alpha=a_img, alpha_mode=mode, alpha_cutoff=0.5)
+    d.sphere((0.3, 0.6, 1.25), 0.18, material=ball)
+    d.quad((0.55, 0.1, 1.3), (0.35, 0, 0.05), (0, 0.45, 0), material=card)
+    if wrapped:
+        d.quad((-0.5, -0.5, 0.0), (1, 0, 0), (0, 1, 0), material=card, transform=trs((0.2, 0.3, 1.45), 0.3, (0, 1, 0), 0.4))
+    return d, cam

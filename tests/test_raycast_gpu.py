@@ -261,3 +261,37 @@ def test_wrapped_primitives_bit_exact(width):
         seen |= set(np.unique(ri[np.isin(ri, wrapped)]).tolist())
     assert seen == set(wrapped)
     gpu.close()
+
+
+@needs_ref
+@pytest.mark.parametrize("width", [2, 4, 8])
+def test_alpha_mask_on_shapes(width):
+    """Alpha-tested materials on sphere / quad GeometricPrimitives (Primitive.cpp:6-26), plain and inside a
+    TransformedPrimitive.  Quads are bit-exact (their uv is the hit's (alpha, beta)); a sphere's uv goes through
+    acos / atan2, whose last bit differs between libm and CUDA, so a candidate within an ulp of a checker edge may
+    fall on the other side: a handful of rays in 10^5."""
+    from oracle.refapi import RefScene
+    from pathtracing_b200 import capi
+    desc, _ = synth.alpha_shapes_scene(capi.ALPHA_MASK)
+    ref, gpu = RefScene(desc, width), GpuScene(desc, width)      # not id mode: the cards' alpha needs their real texcoords
+    rays = _alpha_rays(100000)
+    rays["o"][:, 2] = 2.4
+    rh, ri = ref.trace_closest(rays, want_inst=True)
+    gh, gi = gpu.trace_closest(rays)
+    same = (rh["t"].view(np.uint32) == gh["t"].view(np.uint32)) & (ri == gi)
+    shapes = [k for k, (b, _) in enumerate(desc.instances) if b < 0]
+    spheres = [k for k in shapes if desc.instances[k][1].kind == capi.SHAPE_SPHERE]
+    assert (~same).mean() < 2e-4, (~same).mean()
+    for k in shapes:
+        hit_k = (gi == k).mean()
+        assert 0.005 < hit_k, (k, hit_k)                           # every alpha-tested shape stops some rays ...
+    # ... and lets others through: rays aimed at the sphere's disc that end up behind it
+    c, r = np.array([0.3, 0.6, 1.25]), 0.18
+    oc = rays["o"] - c
+    b = (oc * rays["d"]).sum(1)
+    disc = b * b - ((oc * oc).sum(1) - r * r) > 0
+    assert 0.2 < (gi[disc] == spheres[0]).mean() < 0.95
+    rays["tmax"] = 1.6
+    ra, ga = ref.trace_any(rays), gpu.trace_any(rays)
+    assert (ra != ga).mean() < 2e-4
+    gpu.close(); ref.close()

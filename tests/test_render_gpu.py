@@ -279,6 +279,14 @@ def test_wrapped_primitives_volpath_boundary_bvh2():
 
 
 @needs_ref
+@pytest.mark.parametrize("mode", [capi.ALPHA_MASK, capi.ALPHA_BLEND])
+def test_alpha_tested_shapes(mode):
+    """alpha-tested sphere / quad GeometricPrimitives (plain and transformed) next to the alpha-tested cards"""
+    desc, cam = synth.alpha_shapes_scene(mode)
+    compare(desc, cam, 48, 48, 1024, 6)
+
+
+@needs_ref
 def test_volpath_without_medium_equals_reference():
     desc, cam = synth.cornell_scene()
     compare(desc, cam, 40, 40, 1024, 6, integrator=capi.INTEGRATOR_VOLPATH)
