@@ -379,9 +379,9 @@ def run_ours(a):
     # dram__bytes_read 1.77 GB + dram__bytes_write 0.094 GB for a 4,194,304-ray launch of this workload), per ray
     # times the rays of one bench launch.  Only the default workload was captured.
     default_workload = a.bvh == 4 and a.mesh == "soup" and a.tris == 1_000_000
-    traffic = (1.77e9 + 0.094e9) / 4194304 * n if default_workload else None
+    traffic = (7.105e9 + 0.375e9) / 16777216 * n if default_workload else None   # dram__bytes_read.sum + dram__bytes_write.sum of one 16 Mi-ray launch
     roofline = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": traffic,
-                "traffic_source": "profiles/r01_trace4_v5.md (ncu --set full of a 4 Mi-ray launch, scaled per ray)" if default_workload else None,
+                "traffic_source": "profiles/r01_trace4_v7.md (ncu --set full of the timed 16 Mi-ray launch)" if default_workload else None,
                 "algorithmic_bytes": n * b_ray,
                 "peak_source": peak_src, "kernel": f"k_trace<{a.bvh},false,false>", "bytes_per_ray": b_ray,
                 "nodes_per_ray": nodes_per_ray, "tris_per_ray": tris_per_ray, "instances_per_ray": inst_per_ray,
