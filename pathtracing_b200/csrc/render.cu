@@ -27,6 +27,9 @@
 #include "trace.cuh"
 #include "alpha.cuh"
 
+#ifndef PTB_SHADE_MINB
+#define PTB_SHADE_MINB 6      // 80 registers, 24 warps / SM: shade stage 5-10 % faster than at 96 registers (C1 2.14 -> 1.94, C3 66.2 -> 59.7, C4 191 -> 182 ms); 8 (64 registers) spills more and gains nothing further
+#endif
 namespace ptb {
 
 struct FilterParams {   // Filter.hpp:29-144
@@ -434,7 +437,7 @@ __device__ inline void sample_ld(const ShadeScene& S, const SurfInt& si, const M
 
 // 96 registers: forcing 6 or 8 resident CTAs (80 / 64 registers, spills) measured slower
 template <int INTEG>
-__global__ void __launch_bounds__(128) k_shade(Arena A, ShadeScene S, BatchInfo B, uint32_t n, int cur, const uint32_t* __restrict__ perm){
+__global__ void __launch_bounds__(128, PTB_SHADE_MINB) k_shade(Arena A, ShadeScene S, BatchInfo B, uint32_t n, int cur, const uint32_t* __restrict__ perm){
     const uint32_t tid = blockIdx.x * blockDim.x + threadIdx.x;
     const uint32_t j = (perm && tid < n) ? perm[tid] : tid;      // shade order (k_sort_*) or queue order
     bool cont = false, nee = false;
