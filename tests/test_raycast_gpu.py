@@ -295,3 +295,30 @@ def test_alpha_mask_on_shapes(width):
     ra, ga = ref.trace_any(rays), gpu.trace_any(rays)
     assert (ra != ga).mean() < 2e-4
     gpu.close(); ref.close()
+
+
+def test_wrapper_entry_points_reject_bad_arguments():
+    """pt_scene_animate / pt_scene_add_shape_xf: error codes + pt_last_error instead of undefined behaviour"""
+    import ctypes as C
+    from pathtracing_b200 import capi
+    lib = capi.load_library()
+    h = lib.pt_scene_create(0)
+    assert h
+    d = SceneDesc()
+    d.sphere((0, 0, 0), 1.0, material=d.diffuse(d.solid((1, 1, 1))))
+    for t in d.textures:
+        assert lib.pt_scene_add_texture(h, C.byref(t)) >= 0
+    for m in d.materials:
+        assert lib.pt_scene_add_material(h, C.byref(m)) >= 0
+    shape = d.instances[0][1]
+    assert lib.pt_scene_add_shape_xf(h, C.byref(shape), None) < 0 and b"transform" in lib.pt_last_error()
+    pid = lib.pt_scene_add_shape(h, C.byref(shape))
+    assert pid == 0
+    v, tb = (C.c_float * 3)(0, 1, 0), (C.c_float * 2)(0, 1)
+    assert lib.pt_scene_animate(h, 5, v, tb) < 0 and b"out of range" in lib.pt_last_error()
+    assert lib.pt_scene_animate(h, pid, None, tb) < 0
+    assert lib.pt_scene_animate(h, pid, v, tb) == 0
+    assert lib.pt_scene_animate(h, pid, v, tb) < 0 and b"nested" in lib.pt_last_error()
+    assert lib.pt_scene_commit(h, 4, 1) == 0
+    assert lib.pt_scene_animate(h, pid, v, tb) < 0 and b"committed" in lib.pt_last_error()
+    lib.pt_scene_destroy(h)
