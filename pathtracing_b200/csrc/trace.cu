@@ -19,7 +19,6 @@ namespace ptb {
 
 constexpr int kTraceBlock = 128;
 constexpr unsigned kChunk = 64;        // rays per cursor grab (one atomic per 64 rays)
-constexpr uint32_t kNoRay = 0xFFFFFFFFu;
 
 // Warp-level ray dispenser.  base/avail are warp-uniform.
 struct RayFeed {
