@@ -1,5 +1,9 @@
 // capi.cu — the extern "C" surface declared in include/pt_b200.h.
 #include <cuda_runtime.h>
+#include <algorithm>
+#include <chrono>
+#include <cstdint>
+#include <cstdio>
 #include <cstdlib>
 #include <cstring>
 #include <new>
@@ -83,6 +87,117 @@ static int trace_pipelined(pt_scene* s, const pt_ray* rays, size_t n, Launch lau
     if(!cuda_ok(cudaStreamSynchronize(out), "sync") || !cuda_ok(cudaStreamSynchronize(cs[0]), "sync") || !cuda_ok(cudaStreamSynchronize(cs[1]), "sync") ||
        !cuda_ok(cudaStreamSynchronize(in), "sync"))return PT_ERR_CUDA;
     return PT_OK;
+}
+
+constexpr int kStreamGaveUp = 1000;    // internal: the streamed kernel timed out waiting for rays -> the caller runs the chunked pipeline
+
+// Streamed form of the same pipeline, for plain scenes and large batches: ONE persistent kernel over the whole
+// batch, launched before the first ray has arrived.  The H2D stream copies the rays in chunks and moves a watermark
+// in device memory after each; a warp that grabs rays beyond the watermark waits for it (trace.cu feed_grab<true>).
+// Every retired ray bumps the counter of its 256 Ki-ray granule (after a fence), the host polls the counters and
+// sends the finished prefix back on the D2H stream.  Against one kernel per chunk this removes every chunk's tail
+// (a 2 Mi-ray launch runs at 0.91 Grays/s, the 16 Mi-ray one at 1.06: profiles/r01_trace4_v7.md).
+// copy_out(off, m, stream) queues the D2H copies of rays [off, off + m).
+template <class CopyOut>
+static int trace_streamed(pt_scene* s, const pt_ray* rays, size_t n, bool any, CopyOut copy_out){
+    int rc = ensure_stage(s, n);
+    if(rc != PT_OK)return rc;
+    DeviceBuffers& b = s->buf;
+    const unsigned shift = 18;
+    const size_t ng = (n + ((size_t)1 << shift) - 1) >> shift;
+    const size_t aux_bytes = 64 + 1024 * ng;       // per granule 32 sub-counters, 32 B apart
+    const size_t chunk = (size_t)1 << 20;
+    const size_t n_chunks = (n + chunk - 1) / chunk + 2;
+    if(aux_bytes > b.stream_aux_bytes){
+        if(b.stream_aux){ cudaFree(b.stream_aux); b.stream_aux = nullptr; b.stream_aux_bytes = 0; }
+        if(!cuda_ok(cudaMalloc(&b.stream_aux, aux_bytes), "cudaMalloc stream ctl"))return PT_ERR_CUDA;
+        b.stream_aux_bytes = aux_bytes;
+    }
+    const size_t h_bytes = 8 * n_chunks + aux_bytes + 64;
+    if(h_bytes > b.h_stream_bytes){
+        if(b.h_stream){ cudaFreeHost(b.h_stream); b.h_stream = nullptr; b.h_stream_bytes = 0; }
+        if(!cuda_ok(cudaMallocHost(&b.h_stream, h_bytes), "pinned stream ctl"))return PT_ERR_CUDA;
+        b.h_stream_bytes = h_bytes;
+    }
+    unsigned long long* h_wm = (unsigned long long*)b.h_stream;
+    unsigned char* h_poll = (unsigned char*)b.h_stream + 8 * n_chunks;
+    h_poll += (64 - ((uintptr_t)h_poll & 63)) & 63;
+    cudaStream_t compute = (cudaStream_t)s->stream, in = (cudaStream_t)s->stream2, out = (cudaStream_t)s->stream3, poll = (cudaStream_t)s->stream4;
+    cudaEvent_t ready = pipeline_event(s, 0);
+    if(!ready)return PT_ERR_CUDA;
+    StreamCtl ctl;
+    ctl.landed = (const unsigned long long*)b.stream_aux;
+    ctl.abort = (unsigned*)((char*)b.stream_aux + 8);
+    ctl.done = (unsigned*)((char*)b.stream_aux + 64);
+    ctl.shift = shift;
+    if(!cuda_ok(cudaMemsetAsync(b.stream_aux, 0, aux_bytes, compute), "stream ctl reset") || !cuda_ok(cudaEventRecord(ready, compute), "event"))return PT_ERR_CUDA;
+    static const bool prof = getenv("PTB_PROFILE") != nullptr;
+    cudaEvent_t pe0 = nullptr, pe1 = nullptr, pe2 = nullptr, pe3 = nullptr;
+    if(prof){ cudaEventCreate(&pe0); cudaEventCreate(&pe1); cudaEventCreate(&pe2); cudaEventCreate(&pe3); cudaEventRecord(pe0, compute); }
+    rc = launch_trace_streamed(s, any, b.stage_rays, n, b.stage_hits, b.stage_inst, b.stage_occ, ctl, compute);
+    if(rc != PT_OK)return rc;
+    if(prof)cudaEventRecord(pe1, compute);
+    // rays in: a small first chunk so that the kernel has work at once, then 1 Mi-ray chunks, the watermark after each
+    if(!cuda_ok(cudaStreamWaitEvent(in, ready, 0), "wait") || !cuda_ok(cudaStreamWaitEvent(poll, ready, 0), "wait"))return PT_ERR_CUDA;
+    pt_ray* d_rays = (pt_ray*)b.stage_rays;
+    size_t k = 0;
+    bool enqueue_failed = false;
+    for(size_t off = 0; off < n && !enqueue_failed; k++){
+        size_t m = k == 0 ? chunk / 16 : k == 1 ? chunk / 4 : chunk;
+        if(m > n - off)m = n - off;
+        h_wm[k] = (unsigned long long)(off + m);
+        if(!cuda_ok(cudaMemcpyAsync(d_rays + off, rays + off, m * sizeof(pt_ray), cudaMemcpyHostToDevice, in), "H2D rays") ||
+           !cuda_ok(cudaMemcpyAsync(b.stream_aux, h_wm + k, 8, cudaMemcpyHostToDevice, in), "H2D watermark"))enqueue_failed = true;
+        off += m;
+    }
+    if(prof)cudaEventRecord(pe3, in);
+    // results out: poll the granule counters, send every finished prefix
+    const unsigned* h_done = (const unsigned*)(h_poll + 64);
+    const unsigned* h_abort = (const unsigned*)(h_poll + 8);
+    size_t sent = 0, g_ready = 0;
+    bool failed = enqueue_failed, gave_up = false;
+    const auto t0 = std::chrono::steady_clock::now();
+    while(sent < n && !failed){
+        if(!cuda_ok(cudaMemcpyAsync(h_poll, b.stream_aux, aux_bytes, cudaMemcpyDeviceToHost, poll), "poll") || !cuda_ok(cudaStreamSynchronize(poll), "poll")){ failed = true; break; }
+        if(*h_abort){ set_error("streamed ray cast: the kernel gave up waiting for its rays"); failed = true; gave_up = true; break; }
+        while(g_ready < ng){
+            const size_t g_lo = g_ready << shift, g_n = std::min(n - g_lo, (size_t)1 << shift);
+            unsigned long long got = 0;
+            for(int q = 0; q < 32; q++)got += h_done[(g_ready * 32 + q) * 8];
+            if(got != (unsigned long long)g_n)break;
+            g_ready++;
+        }
+        const size_t upto = std::min(n, g_ready << shift);
+        if(upto > sent){
+            if(copy_out(sent, upto - sent, out) != PT_OK){ failed = true; break; }
+            sent = upto;
+        } else if(std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count() > 20.0){
+            set_error("streamed ray cast: timed out"); failed = true; break;
+        }
+    }
+    if(failed){
+        // make sure the kernel ends: raise the abort flag it polls while waiting
+        static const unsigned one = 1u;
+        cudaMemcpyAsync((char*)b.stream_aux + 8, &one, 4, cudaMemcpyHostToDevice, poll);
+        cudaStreamSynchronize(poll); cudaStreamSynchronize(in); cudaStreamSynchronize(compute); cudaStreamSynchronize(out);
+        return gave_up ? kStreamGaveUp : (int)PT_ERR_CUDA;
+    }
+    if(prof)cudaEventRecord(pe2, out);
+    if(!cuda_ok(cudaStreamSynchronize(out), "sync") || !cuda_ok(cudaStreamSynchronize(compute), "sync") || !cuda_ok(cudaStreamSynchronize(in), "sync"))return PT_ERR_CUDA;
+    if(prof){
+        float k = 0, t = 0, h = 0; cudaEventElapsedTime(&k, pe0, pe1); cudaEventElapsedTime(&t, pe0, pe2); cudaEventElapsedTime(&h, pe0, pe3);
+        cudaEventDestroy(pe3);
+        fprintf(stderr, "[ptb] streamed: H2D done at %.3f ms, kernel %.3f ms, last D2H done at %.3f ms, host %.3f ms\n", h, k, t,
+                std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count() * 1e3);
+        cudaEventDestroy(pe0); cudaEventDestroy(pe1); cudaEventDestroy(pe2);
+    }
+    return PT_OK;
+}
+
+// which form a host-buffer call takes: PTB_E2E_STREAMED=0 keeps one kernel per chunk everywhere
+static bool use_streamed(const pt_scene* s, size_t n){
+    static const bool on = []{ const char* e = getenv("PTB_E2E_STREAMED"); return !(e && atoi(e) == 0); }();
+    return on && !s->streamed_off && n >= ((size_t)1 << 20) && !s->has_alpha_tex && !s->has_wrappers;
 }
 
 extern "C" {
@@ -244,6 +359,16 @@ int pt_trace_closest(pt_scene* s, const pt_ray* rays, size_t n, pt_hit* hits, ui
     if(n == 0)return PT_OK;
     if(!rays || !hits){ set_error("null buffer"); return PT_ERR_INVALID; }
     DeviceBuffers& b = s->buf;
+    auto out_hits = [&](size_t off, size_t m, cudaStream_t st){
+        if(!cuda_ok(cudaMemcpyAsync(hits + off, (pt_hit*)b.stage_hits + off, m * sizeof(pt_hit), cudaMemcpyDeviceToHost, st), "D2H hits"))return (int)PT_ERR_CUDA;
+        if(inst && !cuda_ok(cudaMemcpyAsync(inst + off, (uint32_t*)b.stage_inst + off, m * sizeof(uint32_t), cudaMemcpyDeviceToHost, st), "D2H inst"))return (int)PT_ERR_CUDA;
+        return (int)PT_OK;
+    };
+    if(use_streamed(s, n)){
+        const int rc = trace_streamed(s, rays, n, false, out_hits);
+        if(rc != kStreamGaveUp)return rc;
+        s->streamed_off = true;      // this process blocks in kernel launches: stay with one kernel per chunk
+    }
     return trace_pipelined(s, rays, n,
         [&](size_t off, size_t m, cudaStream_t st){
             return launch_trace_closest(s, (pt_ray*)b.stage_rays + off, m, (pt_hit*)b.stage_hits + off, inst ? (uint32_t*)b.stage_inst + off : nullptr, st);
@@ -260,6 +385,12 @@ int pt_trace_any(pt_scene* s, const pt_ray* rays, size_t n, uint8_t* occluded){
     if(n == 0)return PT_OK;
     if(!rays || !occluded){ set_error("null buffer"); return PT_ERR_INVALID; }
     DeviceBuffers& b = s->buf;
+    if(use_streamed(s, n)){
+        const int rc = trace_streamed(s, rays, n, true, [&](size_t off, size_t m, cudaStream_t st){
+            return cuda_ok(cudaMemcpyAsync(occluded + off, (uint8_t*)b.stage_occ + off, m, cudaMemcpyDeviceToHost, st), "D2H occ") ? (int)PT_OK : (int)PT_ERR_CUDA; });
+        if(rc != kStreamGaveUp)return rc;
+        s->streamed_off = true;      // this process blocks in kernel launches: stay with one kernel per chunk
+    }
     return trace_pipelined(s, rays, n,
         [&](size_t off, size_t m, cudaStream_t st){ return launch_trace_any(s, (pt_ray*)b.stage_rays + off, m, (uint8_t*)b.stage_occ + off, st); },
         [&](size_t off, size_t m, cudaStream_t st){

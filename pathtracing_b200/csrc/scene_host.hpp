@@ -64,6 +64,8 @@ struct DeviceBuffers {
     // staging for the host-buffer ray-cast entry points
     void* stage_rays = nullptr; void* stage_hits = nullptr; void* stage_inst = nullptr; void* stage_occ = nullptr;
     size_t stage_cap = 0;
+    void* stream_aux = nullptr; size_t stream_aux_bytes = 0;   // device: landed watermark, abort flag, per-granule counters
+    void* h_stream = nullptr; size_t h_stream_bytes = 0;       // pinned: watermark values + polled copy of stream_aux
     void* stats = nullptr;
     void* cursors = nullptr;      // ring of ray-dispenser cursors for the persistent kernels
 };
@@ -106,6 +108,7 @@ struct pt_scene {
     void* stream4 = nullptr;      // second trace stream of the host-buffer pipeline (odd chunks): chunk tails overlap
     std::vector<void*> events;    // cudaEvent_t pool of the pipeline (no timing)
     unsigned cursor_next = 0;
+    bool streamed_off = false;    // the streamed host-buffer ray cast gave up once (capi.cu): do not try again
     bool has_wrappers = false;    // some top-level primitive is an analytic shape or a wrapper chain (INST_SPHERE / QUAD / ANIM / WRAP): kWrap kernel variants
     bool has_alpha_tex = false;   // some triangle carries TRI_ALPHA_TEX: traversal must evaluate Material::Alpha
     bool has_boundary = false;    // some primitive has no material (a medium boundary): VolPath shadow rays walk through it
@@ -137,6 +140,15 @@ int scene_add_medium(pt_scene* s, const pt_medium_desc* d);
 int scene_add_mesh(pt_scene* s, const pt_mesh_desc* d);
 int scene_add_blas(pt_scene* s, const int32_t* mesh_ids, int n);
 int scene_add_instance(pt_scene* s, int blas_id, const float* xf);
+// Streamed ray cast: what the persistent kernel shares with the host while the rays are still being copied in
+struct StreamCtl {
+    const unsigned long long* landed = nullptr;   // rays [0, *landed) have arrived (written on the H2D stream after each chunk)
+    unsigned* done = nullptr;                     // per granule of 2^shift rays: how many are retired
+    unsigned* abort = nullptr;                    // raised by the kernel when a wait timed out, or by the host
+    unsigned shift = 18;
+};
+int launch_trace_streamed(pt_scene* sc, bool any, const void* d_rays, size_t n, void* d_hits, void* d_inst, void* d_occ, const StreamCtl& ctl, void* stream);
+
 int scene_add_shape(pt_scene* s, const pt_shape_desc* d, const float* xf = nullptr);
 int scene_animate(pt_scene* s, int prim_id, const float* dir, const float* tb);
 int scene_add_light(pt_scene* s, const pt_light_desc* d);

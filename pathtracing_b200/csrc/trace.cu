@@ -27,9 +27,25 @@ struct RayFeed {
     bool exhausted;
 };
 
-__device__ __forceinline__ void feed_grab(RayFeed& f, unsigned long long* cursor, size_t n, unsigned lane){
+// FEED: the rays are still arriving (host-buffer pipeline, StreamCtl in scene_host.hpp): a grabbed chunk is waited
+// for until the H2D watermark covers it.  A wait of about a second means the copy is not coming (a host that blocks in the launch call, e.g. under a
+// profiler or CUDA_LAUNCH_BLOCKING; the caller then falls back to one kernel per chunk): raise the abort flag
+// and let every warp run dry instead of hanging the device.
+template <bool FEED>
+__device__ __forceinline__ void feed_grab(RayFeed& f, unsigned long long* cursor, size_t n, unsigned lane, const StreamCtl& ctl){
     unsigned long long b = 0;
-    if(lane == 0)b = atomicAdd(cursor, (unsigned long long)kChunk);
+    if(lane == 0){
+        b = atomicAdd(cursor, (unsigned long long)kChunk);
+        if(FEED && b < n){
+            const unsigned long long need = b + kChunk < n ? b + kChunk : (unsigned long long)n;
+            const long long t0 = clock64();
+            while(*(volatile const unsigned long long*)ctl.landed < need){
+                if(*(volatile const unsigned*)ctl.abort != 0u || clock64() - t0 > 2000000000LL){ atomicExch(ctl.abort, 1u); b = n; break; }
+                __nanosleep(100);
+            }
+            __threadfence();
+        }
+    }
     b = __shfl_sync(0xffffffffu, b, 0);
     if(b >= n){ f.exhausted = true; f.avail = 0; return; }
     f.base = b;
@@ -37,11 +53,11 @@ __device__ __forceinline__ void feed_grab(RayFeed& f, unsigned long long* cursor
     f.avail = left < kChunk ? (unsigned)left : kChunk;
 }
 
-template <int WIDTH, bool ANY, bool STATS, int KS, class Alpha>
+template <int WIDTH, bool ANY, bool STATS, int KS, class Alpha, bool FEED = false>
 __global__ void __launch_bounds__(kTraceBlock) k_trace(DevScene S, const float4* __restrict__ rays, size_t n,
                                                        float4* __restrict__ hits, uint32_t* __restrict__ inst, uint8_t* __restrict__ occ,
                                                        unsigned long long* __restrict__ cursor, unsigned long long* __restrict__ stats,
-                                                       unsigned refill_min, const Alpha alpha){
+                                                       unsigned refill_min, const Alpha alpha, const StreamCtl ctl){
     extern __shared__ uint2 smem_stack[];            // KS rows of kTraceBlock entries
     uint2 spill[kStack - KS];
     TravStack<KS, KS ? kTraceBlock : 1> stack;
@@ -71,10 +87,19 @@ __global__ void __launch_bounds__(kTraceBlock) k_trace(DevScene S, const float4*
                         if(inst)inst[idx] = s.hinst;
                         if(STATS && found)hitc++;
                     }
+                    if(FEED){
+                        // release: this ray's result is written before its granule's count says so
+                        // 32 sub-counters per granule, one sector each: every SM works on the same one or two granules
+                        // at any time, a single counter would serialise all retirements on one L2 atomic unit
+                        unsigned* c = ctl.done + ((((idx >> ctl.shift) << 5) | (blockIdx.x & 31u)) << 3);
+#if defined(__CUDA_ARCH__)
+                        asm volatile("red.release.gpu.global.add.u32 [%0], 1;" :: "l"(c) : "memory");
+#endif
+                    }
                     idx = (size_t)-1;
                 }
             }
-            if(feed.avail == 0 && !feed.exhausted)feed_grab(feed, cursor, n, lane);
+            if(feed.avail == 0 && !feed.exhausted)feed_grab<FEED>(feed, cursor, n, lane, ctl);
             const unsigned rank = __popc(need & lt);
             if((s.flags & TF_DONE) && rank < feed.avail){
                 idx = (size_t)(feed.base + rank);
@@ -142,7 +167,7 @@ static int launch_ks(pt_scene* sc, const void* d_rays, size_t n, void* d_hits, v
     unsigned long long* cursor = (unsigned long long*)sc->buf.cursors + (sc->cursor_next++ % kCursorRing);
     if(!cuda_ok(cudaMemsetAsync(cursor, 0, sizeof(unsigned long long), st), "cursor reset"))return PT_ERR_CUDA;
     kernel<<<grid, kTraceBlock, smem, st>>>(sc->dev, (const float4*)d_rays, n, (float4*)d_hits, (uint32_t*)d_inst, (uint8_t*)d_occ,
-                                            cursor, (unsigned long long*)d_stats, refill_min(), alpha);
+                                            cursor, (unsigned long long*)d_stats, refill_min(), alpha, StreamCtl());
     return check_launch("k_trace");
 }
 
@@ -168,6 +193,34 @@ static int launch(pt_scene* sc, const void* d_rays, size_t n, void* d_hits, void
     if(ks >= 8)return launch_ks<WIDTH, ANY, STATS, 8>(sc, d_rays, n, d_hits, d_inst, d_occ, d_stats, stream, na);
     return launch_ks<WIDTH, ANY, STATS, 0>(sc, d_rays, n, d_hits, d_inst, d_occ, d_stats, stream, na);
     }
+}
+
+// One launch over a ray buffer that is still being filled (capi.cu trace_streamed): plain scenes only
+template <int WIDTH, bool ANY>
+static int launch_feed(pt_scene* sc, const void* d_rays, size_t n, void* d_hits, void* d_inst, void* d_occ, const StreamCtl& ctl, void* stream){
+    static int cache[8] = { 0, 0, 0, 0, 0, 0, 0, 0 };
+    cudaStream_t st = (cudaStream_t)stream;
+    auto kernel = k_trace<WIDTH, ANY, false, 16, NoAlpha, true>;
+    const size_t smem = (size_t)16 * kTraceBlock * sizeof(uint2);
+    unsigned grid = persistent_grid(kernel, sc->device, smem, cache[sc->device & 7]);
+    const size_t need_ctas = (n + kTraceBlock - 1) / kTraceBlock;
+    if(need_ctas < grid)grid = (unsigned)need_ctas;
+    unsigned long long* cursor = (unsigned long long*)sc->buf.cursors + (sc->cursor_next++ % kCursorRing);
+    if(!cuda_ok(cudaMemsetAsync(cursor, 0, sizeof(unsigned long long), st), "cursor reset"))return PT_ERR_CUDA;
+    kernel<<<grid, kTraceBlock, smem, st>>>(sc->dev, (const float4*)d_rays, n, (float4*)d_hits, (uint32_t*)d_inst, (uint8_t*)d_occ,
+                                            cursor, nullptr, refill_min(), NoAlpha(), ctl);
+    return check_launch("k_trace (streamed)");
+}
+
+int launch_trace_streamed(pt_scene* sc, bool any, const void* d_rays, size_t n, void* d_hits, void* d_inst, void* d_occ, const StreamCtl& ctl, void* stream){
+    if(n == 0)return PT_OK;
+    const int w = sc->dev.width;
+    if(any)return w == 2 ? launch_feed<2, true>(sc, d_rays, n, nullptr, nullptr, d_occ, ctl, stream)
+                : w == 4 ? launch_feed<4, true>(sc, d_rays, n, nullptr, nullptr, d_occ, ctl, stream)
+                         : launch_feed<8, true>(sc, d_rays, n, nullptr, nullptr, d_occ, ctl, stream);
+    return w == 2 ? launch_feed<2, false>(sc, d_rays, n, d_hits, d_inst, nullptr, ctl, stream)
+         : w == 4 ? launch_feed<4, false>(sc, d_rays, n, d_hits, d_inst, nullptr, ctl, stream)
+                  : launch_feed<8, false>(sc, d_rays, n, d_hits, d_inst, nullptr, ctl, stream);
 }
 
 int launch_trace_closest(pt_scene* sc, const void* d_rays, size_t n, void* d_hits, void* d_inst, void* stream){
