@@ -195,9 +195,15 @@ static int trace_streamed(pt_scene* s, const pt_ray* rays, size_t n, bool any, C
 }
 
 // which form a host-buffer call takes: PTB_E2E_STREAMED=0 keeps one kernel per chunk everywhere
-static bool use_streamed(const pt_scene* s, size_t n){
+static bool use_streamed(pt_scene* s, size_t n){
     static const bool on = []{ const char* e = getenv("PTB_E2E_STREAMED"); return !(e && atoi(e) == 0); }();
-    return on && !s->streamed_off && n >= ((size_t)1 << 20) && !s->has_alpha_tex && !s->has_wrappers;
+    if(!on || s->streamed_off || n < ((size_t)1 << 20) || s->has_alpha_tex || s->has_wrappers)return false;
+    if(!s->streamed_probed){
+        // once per scene: a process whose launch calls block (profiler, CUDA_LAUNCH_BLOCKING) cannot feed a running kernel
+        s->streamed_probed = true;
+        if(!probe_async_launch(s, s->buf.stats, s->stream, s->stream2)){ cudaGetLastError(); s->streamed_off = true; return false; }
+    }
+    return true;
 }
 
 extern "C" {

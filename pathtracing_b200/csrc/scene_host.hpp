@@ -108,6 +108,7 @@ struct pt_scene {
     void* stream4 = nullptr;      // second trace stream of the host-buffer pipeline (odd chunks): chunk tails overlap
     std::vector<void*> events;    // cudaEvent_t pool of the pipeline (no timing)
     unsigned cursor_next = 0;
+    bool streamed_probed = false; // probe_async_launch ran for this scene
     bool streamed_off = false;    // the streamed host-buffer ray cast gave up once (capi.cu): do not try again
     bool has_wrappers = false;    // some top-level primitive is an analytic shape or a wrapper chain (INST_SPHERE / QUAD / ANIM / WRAP): kWrap kernel variants
     bool has_alpha_tex = false;   // some triangle carries TRI_ALPHA_TEX: traversal must evaluate Material::Alpha
@@ -147,6 +148,7 @@ struct StreamCtl {
     unsigned* abort = nullptr;                    // raised by the kernel when a wait timed out, or by the host
     unsigned shift = 18;
 };
+bool probe_async_launch(pt_scene* sc, void* d_words, void* compute_stream, void* copy_stream);
 int launch_trace_streamed(pt_scene* sc, bool any, const void* d_rays, size_t n, void* d_hits, void* d_inst, void* d_occ, const StreamCtl& ctl, void* stream);
 
 int scene_add_shape(pt_scene* s, const pt_shape_desc* d, const float* xf = nullptr);

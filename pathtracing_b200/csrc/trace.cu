@@ -212,6 +212,30 @@ static int launch_feed(pt_scene* sc, const void* d_rays, size_t n, void* d_hits,
     return check_launch("k_trace (streamed)");
 }
 
+// Can the host enqueue work while a kernel runs?  (Not under a profiler that serialises launches, not with
+// CUDA_LAUNCH_BLOCKING.)  A one-thread kernel waits up to ~2 ms for a flag that the host sets right after the launch call
+// returns; it reports whether the flag came.
+__global__ void k_probe_async(volatile const unsigned* flag, unsigned* seen){
+    const long long t0 = clock64();
+    unsigned ok = 0u;
+    while(clock64() - t0 < 4000000LL){ if(*flag != 0u){ ok = 1u; break; } }
+    *seen = ok;
+}
+
+bool probe_async_launch(pt_scene* sc, void* d_words, void* compute_stream, void* copy_stream){
+    unsigned* w = (unsigned*)d_words;          // w[0] flag, w[1] result
+    cudaStream_t cs = (cudaStream_t)compute_stream, xs = (cudaStream_t)copy_stream;
+    static const unsigned one = 1u;
+    unsigned seen = 0u;
+    if(cudaMemsetAsync(w, 0, 8, cs) != cudaSuccess || cudaStreamSynchronize(cs) != cudaSuccess)return false;
+    k_probe_async<<<1, 1, 0, cs>>>(w, w + 1);
+    if(cudaMemcpyAsync(w, &one, 4, cudaMemcpyHostToDevice, xs) != cudaSuccess)return false;
+    if(cudaStreamSynchronize(cs) != cudaSuccess || cudaStreamSynchronize(xs) != cudaSuccess)return false;
+    if(cudaMemcpy(&seen, w + 1, 4, cudaMemcpyDeviceToHost) != cudaSuccess)return false;
+    (void)sc;
+    return seen == 1u;
+}
+
 int launch_trace_streamed(pt_scene* sc, bool any, const void* d_rays, size_t n, void* d_hits, void* d_inst, void* d_occ, const StreamCtl& ctl, void* stream){
     if(n == 0)return PT_OK;
     const int w = sc->dev.width;
