@@ -101,6 +101,18 @@ def test_cornell_path_nee_mis():
 
 
 @needs_ref
+@pytest.mark.parametrize("integrator", [capi.INTEGRATOR_PATH, capi.INTEGRATOR_VOLPATH])
+def test_small_slot_pool_regenerates_slots(monkeypatch, integrator):
+    """A pool much smaller than the call (PTB_BATCH): finished slots are splatted and handed to new camera samples
+    mid-flight, path state lives in 64 B records, the queue order becomes a random order over the pool
+    (render.cu: PathState layout, done list, k_generate into free slots).  The default pool holds these test frames whole."""
+    monkeypatch.setenv("PTB_BATCH", "98304")
+    desc, cam = synth.materials_scene(subdiv=2, sky=True)
+    out = compare(desc, cam, 64, 48, 512, 8, integrator=integrator)
+    assert out["gpu_rays"][0] > 64 * 48 * 512
+
+
+@needs_ref
 def test_cornell_bvh2_uniform_light_sampler():
     desc, cam = synth.cornell_scene()
     compare(desc, cam, 48, 48, 1024, 5, bvh=2, light_sampler=0)
