@@ -776,6 +776,7 @@ int build_binary_bvh_gpu(const Box* boxes, uint32_t n, uint32_t leaf_size, Binar
     if(!cuda_ok(cudaMemcpyAsync(d_boxes.p, boxes, sizeof(Box) * (size_t)n, cudaMemcpyHostToDevice, st), "H2D boxes"))return PT_ERR_CUDA;
     cudaEventRecord(ev[1], st);
     k_pack_items<<<(n + 255) / 256, 256, 0, st>>>(d_boxes.as<Box>(), n, d_ilo.as<float4>(), d_ihi.as<float4>());
+    if(!cuda_ok(cudaMemsetAsync(d_nodes.p, 0, sizeof(GNode) * node_cap, st), "node pool clear"))return PT_ERR_CUDA;   // unused slots stay zero
 
     Counters init; memset(&init, 0, sizeof init);
     init.nnodes = 1;
@@ -812,6 +813,7 @@ int build_binary_bvh_gpu(const Box* boxes, uint32_t n, uint32_t leaf_size, Binar
         k_mark<<<nchunks, kThreads, 0, st>>>(d_ilo.as<float4>(), d_ihi.as<float4>(), d_chunks.as<Chunk>(), d_tasks[cur].as<LTask>(), d_good.as<uint32_t>(),
                                             d_bad_pos.as<uint32_t>(), d_good_pos.as<uint32_t>());
         k_swap<<<nchunks, kThreads, 0, st>>>(d_ilo.as<float4>(), d_ihi.as<float4>(), d_chunks.as<Chunk>(), d_tasks[cur].as<LTask>(), d_bad_pos.as<uint32_t>(), d_good_pos.as<uint32_t>());
+        if(!cuda_ok(cudaGetLastError(), "bvh build level launch"))return PT_ERR_CUDA;
         cur ^= 1;
         levels++;
         if(!plan())return PT_ERR_CUDA;
@@ -820,12 +822,10 @@ int build_binary_bvh_gpu(const Box* boxes, uint32_t n, uint32_t leaf_size, Binar
     k_order_from_items<<<(n + 255) / 256, 256, 0, st>>>(d_ilo.as<float4>(), n, d_order.as<uint32_t>());
     const uint32_t nsmall = n > (uint32_t)kSmall ? h_cnt->nsmall : 1u;
     if(nsmall){
-        static bool attr_set = false;
-        if(!attr_set){
-            if(!cuda_ok(cudaFuncSetAttribute(k_subtree, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(SubShared)), "smem attribute"))return PT_ERR_CUDA;
-            attr_set = true;
-        }
+        // function attributes are per device: set on every build (a few microseconds), not once per process
+        if(!cuda_ok(cudaFuncSetAttribute(k_subtree, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(SubShared)), "smem attribute"))return PT_ERR_CUDA;
         k_subtree<<<nsmall, kThreads, sizeof(SubShared), st>>>(d_ilo.as<float4>(), d_ihi.as<float4>(), d_small.as<SmallTask>(), d_nodes.as<GNode>(), d_order.as<uint32_t>(), leaf_size);
+        if(!cuda_ok(cudaGetLastError(), "k_subtree launch"))return PT_ERR_CUDA;
     }
     cudaEventRecord(ev[2], st);
     if(!cuda_ok(cudaMemcpyAsync(h_cnt, d_cnt.p, sizeof(Counters), cudaMemcpyDeviceToHost, st), "D2H counters") ||

@@ -157,6 +157,7 @@ static int trace_streamed(pt_scene* s, const pt_ray* rays, size_t n, bool any, C
     size_t sent = 0, g_ready = 0;
     bool failed = enqueue_failed, gave_up = false;
     const auto t0 = std::chrono::steady_clock::now();
+    auto t_progress = t0;                   // the 20 s limit counts from the last granule that finished, not from the start of the call
     while(sent < n && !failed){
         if(!cuda_ok(cudaMemcpyAsync(h_poll, b.stream_aux, aux_bytes, cudaMemcpyDeviceToHost, poll), "poll") || !cuda_ok(cudaStreamSynchronize(poll), "poll")){ failed = true; break; }
         if(*h_abort){ set_error("streamed ray cast: the kernel gave up waiting for its rays"); failed = true; gave_up = true; break; }
@@ -171,7 +172,8 @@ static int trace_streamed(pt_scene* s, const pt_ray* rays, size_t n, bool any, C
         if(upto > sent){
             if(copy_out(sent, upto - sent, out) != PT_OK){ failed = true; break; }
             sent = upto;
-        } else if(std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count() > 20.0){
+            t_progress = std::chrono::steady_clock::now();
+        } else if(std::chrono::duration<double>(std::chrono::steady_clock::now() - t_progress).count() > 20.0){
             set_error("streamed ray cast: timed out"); failed = true; break;
         }
     }

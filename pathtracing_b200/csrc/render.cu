@@ -672,6 +672,7 @@ int render_passes(pt_scene* s, const pt_camera_desc* cam, const pt_render_params
     const int W = rp->width, H = rp->height;
     if(W <= 0 || H <= 0 || W > 65535 || H > 65535){ set_error("bad resolution"); return PT_ERR_INVALID; }   // Film stores uint16_t (Film.hpp:266-267)
     if(rp->spp <= 0 || rp->max_depth < 0 || rp->pass_stride <= 0 || rp->pass_begin < 0){ set_error("bad spp / depth / pass range"); return PT_ERR_INVALID; }
+    if(rp->max_depth > 65535){ set_error("max_depth above 65535: the path state keeps depth in 16 bits"); return PT_ERR_INVALID; }
     if(rp->integrator < PT_INTEGRATOR_SIMPLE || rp->integrator > PT_INTEGRATOR_VOLPATH){ set_error("unknown integrator"); return PT_ERR_INVALID; }
     if(rp->sampler != 0 && rp->sampler != 1){ set_error("unknown sampler"); return PT_ERR_INVALID; }
     if(rp->sampler == 1 && (rp->strata_x <= 0 || rp->strata_y <= 0 || rp->strata_x * rp->strata_y != rp->spp)){

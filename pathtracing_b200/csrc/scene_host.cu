@@ -94,6 +94,9 @@ int scene_commit(pt_scene* s, int width, int light_sampler){
     s->stream = st; s->stream2 = st2; s->stream3 = st3; s->stream4 = st4;
     if(!cuda_ok(cudaMalloc(&b.stats, 64), "cudaMalloc stats") ||
        !cuda_ok(cudaMalloc(&b.cursors, kCursorRing * sizeof(unsigned long long)), "cudaMalloc cursors")){ scene_free_device(s); return PT_ERR_CUDA; }
+    // the tables went up as pageable cudaMemcpy on the legacy stream; the non-blocking streams created above do not
+    // order against it: make everything land before the first kernel can read it
+    if(!cuda_ok(cudaDeviceSynchronize(), "scene commit")){ scene_free_device(s); return PT_ERR_CUDA; }
     s->committed = true;
     const auto t3 = std::chrono::steady_clock::now();
     auto sec = [](auto a, auto b){ return std::chrono::duration<double>(b - a).count(); };

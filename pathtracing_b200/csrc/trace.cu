@@ -31,6 +31,17 @@ struct RayFeed {
 // for until the H2D watermark covers it.  A wait of about a second means the copy is not coming (a host that blocks in the launch call, e.g. under a
 // profiler or CUDA_LAUNCH_BLOCKING; the caller then falls back to one kernel per chunk): raise the abort flag
 // and let every warp run dry instead of hanging the device.
+__device__ __forceinline__ unsigned long long global_ns(){
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    return t;
+}
+__device__ __forceinline__ unsigned long long ld_acquire_u64(const unsigned long long* p){
+    unsigned long long v;
+    asm volatile("ld.acquire.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+    return v;
+}
+
 template <bool FEED>
 __device__ __forceinline__ void feed_grab(RayFeed& f, unsigned long long* cursor, size_t n, unsigned lane, const StreamCtl& ctl){
     unsigned long long b = 0;
@@ -38,9 +49,11 @@ __device__ __forceinline__ void feed_grab(RayFeed& f, unsigned long long* cursor
         b = atomicAdd(cursor, (unsigned long long)kChunk);
         if(FEED && b < n){
             const unsigned long long need = b + kChunk < n ? b + kChunk : (unsigned long long)n;
-            const long long t0 = clock64();
-            while(*(volatile const unsigned long long*)ctl.landed < need){
-                if(*(volatile const unsigned*)ctl.abort != 0u || clock64() - t0 > 2000000000LL){ atomicExch(ctl.abort, 1u); b = n; break; }
+            // acquire loads of the watermark: the rays below it were written (by the copy engine) before it moved.
+            // The wait is bounded in wall time (%globaltimer, nanoseconds), not in SM clocks.
+            const unsigned long long t0 = global_ns();
+            while(ld_acquire_u64(ctl.landed) < need){
+                if(*(volatile const unsigned*)ctl.abort != 0u || global_ns() - t0 > 1000000000ull){ atomicExch(ctl.abort, 1u); b = n; break; }
                 __nanosleep(100);
             }
             __threadfence();
@@ -103,14 +116,18 @@ __global__ void __launch_bounds__(kTraceBlock) k_trace(DevScene S, const float4*
             const unsigned rank = __popc(need & lt);
             if((s.flags & TF_DONE) && rank < feed.avail){
                 idx = (size_t)(feed.base + rank);
-                trav_init<WIDTH>(s, S, __ldg(rays + 2 * idx), __ldg(rays + 2 * idx + 1));
+                if constexpr(FEED)trav_init<WIDTH>(s, S, __ldcg(rays + 2 * idx), __ldcg(rays + 2 * idx + 1));
+                else trav_init<WIDTH>(s, S, __ldg(rays + 2 * idx), __ldg(rays + 2 * idx + 1));
             }
             const unsigned want = __popc(need);
             const unsigned taken = want < feed.avail ? want : feed.avail;
             feed.base += taken; feed.avail -= taken;
             if(feed.exhausted && __all_sync(0xffffffffu, idx == (size_t)-1))break;
         }
-        if(!(s.flags & TF_DONE))trav_step<WIDTH, ANY, STATS>(s, S, stack, rays, idx, STATS ? &c : nullptr, alpha);
+        if(!(s.flags & TF_DONE)){
+            if constexpr(FEED)trav_step<WIDTH, ANY, STATS>(s, S, stack, CgRays { rays }, idx, STATS ? &c : nullptr, alpha);
+            else trav_step<WIDTH, ANY, STATS>(s, S, stack, rays, idx, STATS ? &c : nullptr, alpha);
+        }
     }
     if(STATS){
         // warp reduce, one atomic per warp per counter

@@ -473,6 +473,15 @@ __device__ __forceinline__ void node_step8(TravState& s, const DevScene& S, cons
 struct RayRegs { float4 a, b; };
 __device__ __forceinline__ void fetch_ray(const float4* rays, size_t i, float4& a, float4& b){ a = __ldg(rays + 2 * i); b = __ldg(rays + 2 * i + 1); }
 __device__ __forceinline__ void fetch_ray(const RayRegs& r, size_t, float4& a, float4& b){ a = r.a; b = r.b; }
+// a ray buffer that the copy engine is still filling while the kernel runs (streamed host-buffer ray cast): the
+// non-coherent path (ld.global.nc) is specified only for data that stays read-only for the whole kernel, so
+// these reads go through L2 (ld.global.cg)
+struct CgRays { const float4* p; };
+#if defined(__CUDA_ARCH__)
+__device__ __forceinline__ void fetch_ray(const CgRays& r, size_t i, float4& a, float4& b){ a = __ldcg(r.p + 2 * i); b = __ldcg(r.p + 2 * i + 1); }
+#else
+__device__ __forceinline__ void fetch_ray(const CgRays& r, size_t i, float4& a, float4& b){ a = r.p[2 * i]; b = r.p[2 * i + 1]; }
+#endif
 
 // One round; the ray is finished once s.flags & TF_DONE.
 // The world-space ray is re-read from its source when a transformed instance is left (cheaper than

@@ -286,15 +286,6 @@ def test_sphere_and_quad_shapes(libs, one_sided):
 
 @needs_ref
 def test_wrapped_primitives_shading(libs):
-    try:
-        _wrapped_primitives_shading(libs)
-    except AssertionError:
-        # seen failing once in ~25 runs and never when repeated; the reference draws its light-power samples from
-        # an unseeded generator, everything else here is seeded: a real difference fails again
-        _wrapped_primitives_shading(libs)
-
-
-def _wrapped_primitives_shading(libs):
     """TransformedPrimitive over sphere / quad GeometricPrimitives and AnimatedPrimitive wrappers (Primitive.cpp:32-96):
     the interaction that comes back through the wrappers at the ray's time, the inner AreaLight seen by a hit, and
     TransformedLight / AnimatedLight::{sample, PDF, L, Power} (Light.cpp:296-365) at several shutter times."""
@@ -341,7 +332,19 @@ def _wrapped_primitives_shading(libs):
     ref.ref_unit_lights(r.h, ra.ctypes.data)
     emu.emul_unit_lights(e.h, eb.ctypes.data)
     assert np.array_equal(ra[:, 2], eb[:, 2])
-    _close(ra[:, 1], eb[:, 0], 2e-3, 1e-6, "sampler PMF per light (the reference jitters its 256 power samples)")
+    try:
+        _close(ra[:, 1], eb[:, 0], 2e-3, 1e-6, "sampler PMF per light (the reference jitters its 256 power samples)")
+    except AssertionError as err:
+        # the only comparison here that depends on the reference's unseeded generator (AreaLight::PreProcess draws its 256
+        # power samples from random_device-seeded PCG): repeat THIS comparison once against a fresh reference scene and say so.
+        # Every other assert of this test is seeded and single-shot.
+        import warnings
+        warnings.warn(f"sampler PMF comparison failed once, repeating against a fresh reference scene: {err}")
+        r_b, _e_b = _scenes(desc, 4)
+        ra2 = np.zeros((n, 3), np.float32)
+        ref.ref_unit_lights(r_b.h, ra2.ctypes.data)
+        r_b.close(); _e_b.close()
+        _close(ra2[:, 1], eb[:, 0], 2e-3, 1e-6, "sampler PMF per light, second reference scene")
     m = 3000
     for time in (0.0, 0.37, 0.9, 1.4):
         for k in range(n):
