@@ -257,6 +257,22 @@ PT_API int pt_trace_closest_dev(pt_scene*, const void* d_rays, size_t n,
 PT_API int pt_trace_any_dev(pt_scene*, const void* d_rays, size_t n,
                             void* d_occluded, void* stream);
 
+/* NO COUNTERPART IN THE REFERENCE: added
+ * for callers that must not allocate device memory (tight serving loops,
+ * harnesses that forbid cudaMalloc).  Same result as pt_trace_closest, bit for
+ * bit (the same kernel), but the call makes no cudaMalloc / cudaFree /
+ * cudaMallocHost or other allocating call: the staged rays, hits, instance ids
+ * and the ray-dispenser cursor live in a fixed `static __device__` scratch
+ * array inside the library (3.4 MB, held by every GPU that loads the library
+ * until the process exits).  n > PT_STATIC_MAX_RAYS is refused with
+ * PT_ERR_INVALID and a message.  Host buffers in, host buffers out, `inst` may
+ * be NULL; synchronous.  All calls on one GPU share the scratch (it keeps the
+ * last call's contents; what must start at zero is cleared per call): calls
+ * that overlap on one GPU (two host threads, two scenes) race on it.          */
+#define PT_STATIC_MAX_RAYS 65536
+PT_API int pt_trace_closest_static(pt_scene*, const pt_ray* rays, size_t n,
+                                   pt_hit* hits, uint32_t* inst);
+
 /* traversal statistics of the last counted launch (for the roofline's
  * algorithmic bytes): runs a counting build of the SAME
  * traversal over device rays and returns totals.                            */

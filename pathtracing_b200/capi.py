@@ -107,6 +107,7 @@ ALPHA_OPAQUE, ALPHA_BLEND, ALPHA_MASK = range(3)
 LIGHT_UNIFORM_INFINITE, LIGHT_GRADIENT_INFINITE, LIGHT_TEXTURE_INFINITE, LIGHT_DISTANT, LIGHT_POINT = range(5)
 INTEGRATOR_SIMPLE, INTEGRATOR_PATH, INTEGRATOR_VOLPATH = range(3)
 SHAPE_SPHERE, SHAPE_QUAD = range(2)
+STATIC_MAX_RAYS = 65536            # PT_STATIC_MAX_RAYS
 FILTER_BOX, FILTER_GAUSSIAN, FILTER_MITCHELL, FILTER_LANCZOS = range(4)
 
 EXPORTS = [
@@ -114,7 +115,7 @@ EXPORTS = [
     "pt_scene_add_texture", "pt_scene_add_material", "pt_scene_add_medium", "pt_scene_add_mesh",
     "pt_scene_add_blas", "pt_scene_add_instance", "pt_scene_add_shape", "pt_scene_add_shape_xf", "pt_scene_animate", "pt_scene_add_light", "pt_scene_set_medium",
     "pt_scene_commit", "pt_scene_set_builder", "pt_scene_set_allreduce", "pt_scene_build_stats", "pt_build_bvh2", "pt_scene_bounds", "pt_trace_closest", "pt_trace_any",
-    "pt_trace_closest_dev", "pt_trace_any_dev", "pt_trace_closest_stats", "pt_render",
+    "pt_trace_closest_dev", "pt_trace_any_dev", "pt_trace_closest_static", "pt_trace_closest_stats", "pt_render",
     "pt_film_device_ptr", "pt_film_download", "pt_film_download_sumsq", "pt_film_upload",
 ]
 
@@ -173,6 +174,8 @@ def load_library(path: os.PathLike | None = None) -> C.CDLL:
     lib.pt_trace_closest.argtypes = [vp, vp, sz, vp, vp]
     lib.pt_trace_any.restype = i
     lib.pt_trace_any.argtypes = [vp, vp, sz, vp]
+    lib.pt_trace_closest_static.restype = i
+    lib.pt_trace_closest_static.argtypes = [vp, vp, sz, vp, vp]
     lib.pt_trace_closest_dev.restype = i
     lib.pt_trace_closest_dev.argtypes = [vp, vp, sz, vp, vp, vp]
     lib.pt_trace_any_dev.restype = i

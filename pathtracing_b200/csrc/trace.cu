@@ -11,6 +11,7 @@
 // the upper tree levels (PTB_STACK_SMEM=0|8|16|24 selects the split; 16 measured best).
 #include <cstdio>
 #include <cstdlib>
+#include <string>
 #include "scene_host.hpp"
 #include "trace.cuh"
 #include "alpha.cuh"
@@ -286,4 +287,81 @@ int launch_trace_stats(pt_scene* sc, const void* d_rays, size_t n, void* d_count
                               : launch<8, false, true>(sc, d_rays, n, nullptr, nullptr, nullptr, d_counters, stream);
 }
 
+// ---- pt_trace_closest_static: the host-buffer closest-hit ray cast without any allocation -------------------------
+// Requested by the run's operators; no counterpart in the reference.  pt_trace_closest stages the batch in device buffers
+// it cudaMallocs (and grows) on demand; callers that must not allocate (serving loops, harnesses that forbid cudaMalloc)
+// get the same kernel (k_trace, the same instantiation pt_trace_closest_dev launches) over a FIXED scratch area that
+// lives in the library image: the ray-dispenser cursor and the staged rays / hits / instance ids of at most
+// PT_STATIC_MAX_RAYS rays.  Every GPU that loads the library holds the array (3.4 MB) until exit.  All calls on one
+// device share it and it keeps the previous call's contents: the cursor is cleared on the stream before every launch,
+// the staging areas are fully overwritten for [0, n).  Calls that overlap on one GPU race on it.
+struct StaticScratch {
+    unsigned long long cursor;
+    unsigned char pad[248];
+    float4 rays[2 * PT_STATIC_MAX_RAYS];
+    float4 hits[PT_STATIC_MAX_RAYS];
+    uint32_t inst[PT_STATIC_MAX_RAYS];
+};
+static __device__ __align__(256) unsigned char g_static_scratch[sizeof(StaticScratch)];
+
+// In host code `g_static_scratch` is only a handle for the runtime, not a device address: the address is asked for
+// once per device, with that device current, and kept per ordinal.
+static StaticScratch* static_scratch_ptr(int device){
+    static StaticScratch* ptr[64] = {};
+    if(device < 0 || device >= 64){ set_error("pt_trace_closest_static: device ordinal out of range"); return nullptr; }
+    if(!ptr[device]){
+        void* p = nullptr;
+        if(!cuda_ok(cudaGetSymbolAddress(&p, g_static_scratch), "cudaGetSymbolAddress(static scratch)"))return nullptr;
+        ptr[device] = (StaticScratch*)p;
+    }
+    return ptr[device];
+}
+
+template <int WIDTH, class Alpha>
+static int launch_static(pt_scene* sc, StaticScratch* d, size_t n, bool want_inst, cudaStream_t st, const Alpha& alpha){
+    static int cache[8] = { 0, 0, 0, 0, 0, 0, 0, 0 };
+    auto kernel = k_trace<WIDTH, false, false, 16, Alpha>;
+    const size_t smem = (size_t)16 * kTraceBlock * sizeof(uint2);
+    unsigned grid = persistent_grid(kernel, sc->device, smem, cache[sc->device & 7]);
+    const size_t need_ctas = (n + kTraceBlock - 1) / kTraceBlock;
+    if(need_ctas < grid)grid = (unsigned)need_ctas;
+    if(!cuda_ok(cudaMemsetAsync(&d->cursor, 0, sizeof(unsigned long long), st), "cursor reset"))return PT_ERR_CUDA;
+    kernel<<<grid, kTraceBlock, smem, st>>>(sc->dev, d->rays, n, d->hits, want_inst ? d->inst : nullptr, nullptr,
+                                            &d->cursor, nullptr, refill_min(), alpha, StreamCtl());
+    return check_launch("k_trace (static scratch)");
+}
+
 } // namespace ptb
+
+extern "C" int pt_trace_closest_static(pt_scene* s, const pt_ray* rays, size_t n, pt_hit* hits, uint32_t* inst){
+    using namespace ptb;
+    if(!s){ set_error("null scene"); return PT_ERR_INVALID; }
+    if(!s->committed){ set_error("scene not committed"); return PT_ERR_STATE; }
+    if(n > (size_t)PT_STATIC_MAX_RAYS){
+        set_error("pt_trace_closest_static: " + std::to_string(n) + " rays exceed PT_STATIC_MAX_RAYS = " + std::to_string(PT_STATIC_MAX_RAYS) +
+                  " (the static scratch is fixed; split the batch or use pt_trace_closest)");
+        return PT_ERR_INVALID;
+    }
+    if(n == 0)return PT_OK;
+    if(!rays || !hits){ set_error("null buffer"); return PT_ERR_INVALID; }
+    if(!cuda_ok(cudaSetDevice(s->device), "cudaSetDevice"))return PT_ERR_CUDA;
+    StaticScratch* d = static_scratch_ptr(s->device);
+    if(!d)return PT_ERR_CUDA;
+    cudaStream_t st = (cudaStream_t)s->stream;
+    if(!cuda_ok(cudaMemcpyAsync(d->rays, rays, n * sizeof(pt_ray), cudaMemcpyHostToDevice, st), "H2D rays"))return PT_ERR_CUDA;
+    int rc;
+    if(s->has_alpha_tex || s->has_wrappers){
+        const AlphaTex at = { s->shade, s->alpha_salt += 0x9E3779B97F4A7C15ull };
+        rc = s->dev.width == 2 ? launch_static<2>(s, d, n, inst != nullptr, st, at) : s->dev.width == 4 ? launch_static<4>(s, d, n, inst != nullptr, st, at)
+                                                                                                      : launch_static<8>(s, d, n, inst != nullptr, st, at);
+    } else{
+        const NoAlpha na;
+        rc = s->dev.width == 2 ? launch_static<2>(s, d, n, inst != nullptr, st, na) : s->dev.width == 4 ? launch_static<4>(s, d, n, inst != nullptr, st, na)
+                                                                                                      : launch_static<8>(s, d, n, inst != nullptr, st, na);
+    }
+    if(rc != PT_OK)return rc;
+    if(!cuda_ok(cudaMemcpyAsync(hits, d->hits, n * sizeof(pt_hit), cudaMemcpyDeviceToHost, st), "D2H hits"))return PT_ERR_CUDA;
+    if(inst && !cuda_ok(cudaMemcpyAsync(inst, d->inst, n * sizeof(uint32_t), cudaMemcpyDeviceToHost, st), "D2H inst"))return PT_ERR_CUDA;
+    if(!cuda_ok(cudaStreamSynchronize(st), "pt_trace_closest_static"))return PT_ERR_CUDA;
+    return PT_OK;
+}
