@@ -33,7 +33,8 @@ typedef enum pt_status {
     PT_ERR_CUDA = -2,     /* CUDA runtime error (message in pt_last_error)  */
     PT_ERR_NO_DEVICE = -3,/* no CUDA device: there is NO CPU fallback       */
     PT_ERR_STATE = -4,    /* scene not committed / already committed        */
-    PT_ERR_NOMEM = -5
+    PT_ERR_NOMEM = -5,
+    PT_ERR_OVERFLOW = -6  /* some ray needed more traversal-stack entries than the kernel has (96): results unreliable */
 } pt_status;
 
 /* ---- ray casting ------------------------------------------------------------
@@ -215,6 +216,20 @@ PT_API int pt_scene_commit(pt_scene*, int bvh_width, int light_sampler);
 typedef enum pt_builder { PT_BUILDER_HOST = 0, PT_BUILDER_GPU = 1 } pt_builder;
 PT_API int pt_scene_set_builder(pt_scene*, int builder);
 
+/* Node layout the traversal kernels walk (before pt_scene_commit; bvh_width 4 only).
+ * PT_LAYOUT_EXACT (default): the reference's BVH4_CLUSTER content (BVH.hpp:45-60) in
+ * 128 B, box tests in the reference's own arithmetic: the same nodes are visited in
+ * the same order, exact ties resolve to the same triangle.
+ * PT_LAYOUT_FAST: the SAME tree and visit order with the child boxes quantised to
+ * 8 bits per plane around a per-cluster origin (64 B per cluster, 64 B per triangle
+ * record), rounded outwards, so every box contains the exact one.  Triangle tests are
+ * unchanged, so the closest hit (primitive / instance id, bits of t) is the
+ * reference's except where two candidates tie exactly or the reference's own box
+ * test rounds a grazing hit away.  Half the 32 B sectors per cluster visit: the
+ * traversal is bound by L1 wavefronts, not bytes.               */
+typedef enum pt_layout { PT_LAYOUT_EXACT = 0, PT_LAYOUT_FAST = 1 } pt_layout;
+PT_API int pt_scene_set_layout(pt_scene*, int layout);
+
 typedef struct pt_build_stats {   /* wall-clock split of the last pt_scene_commit */
     double total_s;
     double pack_s;          /* triangle records + BVH builds + flattening (includes bvh2_s, flatten_s) */
@@ -257,6 +272,14 @@ PT_API int pt_trace_closest_dev(pt_scene*, const void* d_rays, size_t n,
 PT_API int pt_trace_any_dev(pt_scene*, const void* d_rays, size_t n,
                             void* d_occluded, void* stream);
 
+/* The reference's traversal stacks are 32 entries and unchecked (BVH.hpp:478,505,
+ * 1035,1128: overflow is undefined behaviour there).  Here the unified TLAS+BLAS
+ * stack holds 96 entries and a push that finds it full is COUNTED: the
+ * synchronous entry points (pt_trace_closest / pt_trace_any / pt_render) return
+ * PT_ERR_OVERFLOW when one of their rays overflowed; after asynchronous *_dev
+ * launches read the scene's running total here (synchronises the device).     */
+PT_API int pt_scene_stack_overflows(pt_scene*, uint64_t* count);
+
 /* NO COUNTERPART IN THE REFERENCE: added
  * for callers that must not allocate device memory (tight serving loops,
  * harnesses that forbid cudaMalloc).  Same result as pt_trace_closest, bit for
@@ -286,6 +309,14 @@ typedef struct pt_trace_stats {
 } pt_trace_stats;
 PT_API int pt_trace_closest_stats(pt_scene*, const void* d_rays, size_t n,
                                   pt_trace_stats* out);
+
+/* Counted renders (per-sample algorithmic bytes): while counting is on, pt_render
+ * launches the counting build of the same traversal kernels (slower) and the scene sums the
+ * cluster / instance / triangle visits of its closest-hit and shadow rays.
+ * pt_scene_render_counts returns the totals since the last call and clears them; `rays`
+ * is left 0 (pt_render_stats has the ray counts).  bvh_width 4 (either layout) only.      */
+PT_API int pt_scene_set_counting(pt_scene*, int on);
+PT_API int pt_scene_render_counts(pt_scene*, pt_trace_stats* closest, pt_trace_stats* shadow);
 
 /* ---- rendering ---------------------------------------------------------------- */
 
@@ -358,6 +389,60 @@ PT_API int pt_film_download(pt_scene*, double* rgbw);
  * VarianceEstimator (Util.hpp:8-43) accumulates per pixel in Integrators.cpp:78-81.             */
 PT_API int pt_film_download_sumsq(pt_scene*, double* sumsq);
 PT_API int pt_film_upload(pt_scene*, const double* rgbw, int width, int height);
+
+/* ---- multi-GPU rendering -----------------------------------------
+ * replaces the worker threads of Integrator::Render(threadCount) (Integrators.hpp:13,
+ * Integrators.cpp:23-41,117-123) and their merge into one film (Film::Merge,
+ * Film.hpp:125-132): a worker is a GPU.  The committed scene is replicated device
+ * to device, rank r of G renders the sample passes r, r+G, ... of the frame into its
+ * own film, and ONE reduce(sum) of the fp64 accumulators (NCCL over NVLink) brings
+ * the frame to rank 0; adaptive renders add one all-reduce of the per-pixel
+ * estimator sums per round.  Sample streams are keyed by sample id, so the frame
+ * equals the single-GPU frame up to the order of the fp64 sums.  NCCL is bound at
+ * run time (libnccl.so.2, the copy already in the process if there is one).        */
+
+/* a second committed copy of `src` on `device` (tables copied GPU to GPU, no build)  */
+PT_API int pt_scene_replicate(pt_scene* src, int device, pt_scene** out);
+
+/* one process, G GPUs, one host thread per GPU.  devices[0] must be the primary's
+ * device; devices == NULL: every visible GPU.  All entries different (NCCL), or all
+ * equal ("virtual ranks" sharing one GPU: the sharding logic without NCCL, reduced
+ * by an add kernel).  The primary stays owned by the caller and must outlive the
+ * pt_multi; replicas are owned by it.                                              */
+typedef struct pt_multi pt_multi;
+PT_API pt_multi* pt_multi_create(pt_scene* primary, const int* devices, int n_devices);
+PT_API void pt_multi_destroy(pt_multi*);
+PT_API int pt_multi_gpus(const pt_multi*);
+PT_API pt_scene* pt_multi_scene(pt_multi*, int rank);     /* rank 0 = the primary   */
+/* Integrator::Render over all ranks; the frame is the primary scene's film
+ * (pt_film_download(primary)).  stats: sums over the ranks, gpu_ms = the slowest.  */
+PT_API int pt_multi_render(pt_multi*, const pt_camera_desc*, const pt_render_params*,
+                           int clear, pt_render_stats* stats);
+
+/* one process per GPU (torchrun, mpirun): rank 0 calls pt_dist_unique_id and the
+ * launcher carries the 128 bytes to the other ranks; every rank then calls
+ * pt_dist_init on its committed scene (collective) and pt_dist_render per frame
+ * (collective; the frame is rank 0's film).  world == 1 needs no id and no NCCL.   */
+PT_API int pt_dist_unique_id(void* id128);
+PT_API int pt_dist_init(pt_scene*, const void* id128, int rank, int world);
+PT_API int pt_dist_render(pt_scene*, const pt_camera_desc*, const pt_render_params*,
+                          int clear, pt_render_stats* stats);
+PT_API int pt_dist_finalize(pt_scene*);
+
+/* ---- diagnostic probes of the device build of the shading code (csrc/unit.cu) ------
+ * One record per thread through the SAME device functions k_shade calls, compiled with
+ * the same flags (fast math): the interaction Shape::Intersect + Primitive::Intersect
+ * build (Shape.cpp:205-243, Primitive.cpp:20-24,54-63), Material::{scatter,
+ * calc_attenuation, PDF} (Material.hpp:200-673), the AreaLight seen by a hit
+ * (Light.cpp:254-291), Light::{sample, PDF, L} (Light.cpp:9-365) and
+ * HenyeyGreenstein::{Sample, PDF} (PhaseFunction.cpp:4-26).  Host buffers, synchronous.
+ * Record layouts: csrc/unit.cu (those of oracle/ref_driver.cpp ref_unit_*).             */
+PT_API int pt_unit_shade(pt_scene*, const pt_ray* rays, size_t n, const float* in6,
+                         float* out, int stride /* >= 43 */);
+PT_API int pt_unit_light_count(pt_scene*);
+PT_API int pt_unit_light_sample(pt_scene*, int light, size_t n, const float* in5,
+                                float* out, int stride /* >= 22 */, float time);
+PT_API int pt_unit_hg(int device, float g, size_t n, const float* in5, float* out5);
 
 #ifdef __cplusplus
 }

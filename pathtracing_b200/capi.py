@@ -95,6 +95,7 @@ ALLREDUCE_FN = C.CFUNCTYPE(C.c_int, C.c_void_p, C.c_void_p, C.c_size_t, C.c_void
 BVH2_NODE_DTYPE = np.dtype([("lo", "<f4", 3), ("hi", "<f4", 3), ("left", "<u4"), ("right", "<u4"), ("count", "<u4"), ("axis", "<u4")])
 assert BVH2_NODE_DTYPE.itemsize == 40
 BUILDER_HOST, BUILDER_GPU = range(2)
+LAYOUT_EXACT, LAYOUT_FAST = range(2)
 
 RAY_DTYPE = np.dtype([("o", "<f4", 3), ("tmax", "<f4"), ("d", "<f4", 3), ("time", "<f4")])
 HIT_DTYPE = np.dtype([("t", "<f4"), ("u", "<f4"), ("v", "<f4"), ("prim", "<u4")])
@@ -114,9 +115,12 @@ EXPORTS = [
     "pt_device_count", "pt_scene_create", "pt_scene_destroy", "pt_last_error",
     "pt_scene_add_texture", "pt_scene_add_material", "pt_scene_add_medium", "pt_scene_add_mesh",
     "pt_scene_add_blas", "pt_scene_add_instance", "pt_scene_add_shape", "pt_scene_add_shape_xf", "pt_scene_animate", "pt_scene_add_light", "pt_scene_set_medium",
-    "pt_scene_commit", "pt_scene_set_builder", "pt_scene_set_allreduce", "pt_scene_build_stats", "pt_build_bvh2", "pt_scene_bounds", "pt_trace_closest", "pt_trace_any",
-    "pt_trace_closest_dev", "pt_trace_any_dev", "pt_trace_closest_static", "pt_trace_closest_stats", "pt_render",
+    "pt_scene_commit", "pt_scene_set_builder", "pt_scene_set_layout", "pt_scene_set_allreduce", "pt_scene_build_stats", "pt_build_bvh2", "pt_scene_bounds", "pt_trace_closest", "pt_trace_any",
+    "pt_trace_closest_dev", "pt_trace_any_dev", "pt_trace_closest_static", "pt_scene_stack_overflows", "pt_trace_closest_stats", "pt_scene_set_counting", "pt_scene_render_counts", "pt_render",
     "pt_film_device_ptr", "pt_film_download", "pt_film_download_sumsq", "pt_film_upload",
+    "pt_scene_replicate", "pt_multi_create", "pt_multi_destroy", "pt_multi_gpus", "pt_multi_scene", "pt_multi_render",
+    "pt_dist_unique_id", "pt_dist_init", "pt_dist_render", "pt_dist_finalize",
+    "pt_unit_shade", "pt_unit_light_count", "pt_unit_light_sample", "pt_unit_hg",
 ]
 
 _lib = None
@@ -162,6 +166,8 @@ def load_library(path: os.PathLike | None = None) -> C.CDLL:
     lib.pt_scene_commit.argtypes = [vp, i, i]
     lib.pt_scene_set_builder.restype = i
     lib.pt_scene_set_builder.argtypes = [vp, i]
+    lib.pt_scene_set_layout.restype = i
+    lib.pt_scene_set_layout.argtypes = [vp, i]
     lib.pt_scene_set_allreduce.restype = i
     lib.pt_scene_set_allreduce.argtypes = [vp, ALLREDUCE_FN, vp]
     lib.pt_scene_build_stats.restype = i
@@ -174,12 +180,18 @@ def load_library(path: os.PathLike | None = None) -> C.CDLL:
     lib.pt_trace_closest.argtypes = [vp, vp, sz, vp, vp]
     lib.pt_trace_any.restype = i
     lib.pt_trace_any.argtypes = [vp, vp, sz, vp]
+    lib.pt_scene_stack_overflows.restype = i
+    lib.pt_scene_stack_overflows.argtypes = [vp, C.POINTER(C.c_uint64)]
     lib.pt_trace_closest_static.restype = i
     lib.pt_trace_closest_static.argtypes = [vp, vp, sz, vp, vp]
     lib.pt_trace_closest_dev.restype = i
     lib.pt_trace_closest_dev.argtypes = [vp, vp, sz, vp, vp, vp]
     lib.pt_trace_any_dev.restype = i
     lib.pt_trace_any_dev.argtypes = [vp, vp, sz, vp, vp]
+    lib.pt_scene_set_counting.restype = i
+    lib.pt_scene_set_counting.argtypes = [vp, i]
+    lib.pt_scene_render_counts.restype = i
+    lib.pt_scene_render_counts.argtypes = [vp, C.POINTER(pt_trace_stats), C.POINTER(pt_trace_stats)]
     lib.pt_trace_closest_stats.restype = i
     lib.pt_trace_closest_stats.argtypes = [vp, vp, sz, C.POINTER(pt_trace_stats)]
     lib.pt_render.restype = i
@@ -192,6 +204,34 @@ def load_library(path: os.PathLike | None = None) -> C.CDLL:
     lib.pt_film_download_sumsq.argtypes = [vp, vp]
     lib.pt_film_upload.restype = i
     lib.pt_film_upload.argtypes = [vp, vp, i, i]
+    lib.pt_scene_replicate.restype = i
+    lib.pt_scene_replicate.argtypes = [vp, i, C.POINTER(vp)]
+    lib.pt_multi_create.restype = vp
+    lib.pt_multi_create.argtypes = [vp, C.POINTER(C.c_int), i]
+    lib.pt_multi_destroy.restype = None
+    lib.pt_multi_destroy.argtypes = [vp]
+    lib.pt_multi_gpus.restype = i
+    lib.pt_multi_gpus.argtypes = [vp]
+    lib.pt_multi_scene.restype = vp
+    lib.pt_multi_scene.argtypes = [vp, i]
+    lib.pt_multi_render.restype = i
+    lib.pt_multi_render.argtypes = [vp, C.POINTER(pt_camera_desc), C.POINTER(pt_render_params), i, C.POINTER(pt_render_stats)]
+    lib.pt_dist_unique_id.restype = i
+    lib.pt_dist_unique_id.argtypes = [vp]
+    lib.pt_dist_init.restype = i
+    lib.pt_dist_init.argtypes = [vp, vp, i, i]
+    lib.pt_dist_render.restype = i
+    lib.pt_dist_render.argtypes = [vp, C.POINTER(pt_camera_desc), C.POINTER(pt_render_params), i, C.POINTER(pt_render_stats)]
+    lib.pt_dist_finalize.restype = i
+    lib.pt_dist_finalize.argtypes = [vp]
+    lib.pt_unit_shade.restype = i
+    lib.pt_unit_shade.argtypes = [vp, vp, sz, vp, vp, i]
+    lib.pt_unit_light_count.restype = i
+    lib.pt_unit_light_count.argtypes = [vp]
+    lib.pt_unit_light_sample.restype = i
+    lib.pt_unit_light_sample.argtypes = [vp, i, sz, vp, vp, i, C.c_float]
+    lib.pt_unit_hg.restype = i
+    lib.pt_unit_hg.argtypes = [i, C.c_float, sz, vp, vp]
     if path is None:
         _lib = lib
     return lib

@@ -2,6 +2,7 @@
 // costs decide the topology and must not depend on FMA contraction.
 #include "bvh_build.hpp"
 #include "scene_host.hpp"
+#include <algorithm>
 #include <cstring>
 
 #include <atomic>
@@ -484,6 +485,72 @@ Box transform_box(const float m[16], const Box& b){
         box_grow(out, p);
     }
     return out;
+}
+
+
+// ---- PT_LAYOUT_FAST: Bvh4Node -> Bvh4QNode -----------------------------------------------------------------------------
+// Per cluster and axis: step = 2^e with (extent + margins) / step <= 255 and step >= 2^-20 of the largest coordinate
+// (so that a quarter step stays far above the float rounding of the traversal's plane distances), origin a quarter
+// step below the cluster's lower corner.  Child planes: lower ones rounded down, upper ones up, each by at least a
+// quarter step; the result is checked in float arithmetic (origin + q * step) against the exact box and widened if
+// a rounding ever went the wrong way.
+void encode_bvh4q(const std::vector<Bvh4Node>& n4, std::vector<Bvh4QNode>& out){
+    out.resize(n4.size());
+    const size_t n = n4.size();
+    unsigned nt = std::thread::hardware_concurrency();
+    if(nt == 0)nt = 1;
+    if(nt > 16)nt = 16;
+    if(n < 65536)nt = 1;
+    auto work = [&](size_t lo_i, size_t hi_i){
+        for(size_t i = lo_i; i < hi_i; i++){
+            const Bvh4Node& a = n4[i];
+            Bvh4QNode q;
+            memset(&q, 0, sizeof q);
+            const float* mins[3] = { a.xmin, a.ymin, a.zmin };
+            const float* maxs[3] = { a.xmax, a.ymax, a.zmax };
+            uint32_t words[6] = { 0, 0, 0, 0, 0, 0 };
+            for(int ax = 0; ax < 3; ax++){
+                float lo = std::numeric_limits<float>::infinity(), hi = -lo;
+                for(int c = 0; c < 4; c++)if(a.ref[c] != REF_EMPTY){ lo = std::min(lo, mins[ax][c]); hi = std::max(hi, maxs[ax][c]); }
+                if(!(lo <= hi)){ lo = 0.0f; hi = 0.0f; }              // no child at all: never visited
+                const double mag = std::max(std::max((double)std::fabs(lo), (double)std::fabs(hi)), 1e-30);
+                int e = (int)std::ceil(std::log2(std::max((double)hi - (double)lo, 1e-300) / 254.0));
+                e = std::max(e, (int)std::floor(std::log2(mag)) - 20);
+                e = std::max(e, -120);
+                for(;; e++){
+                    const float step = std::ldexp(1.0f, e);
+                    const float org = lo - 0.25f * step;
+                    bool ok = e <= 120;
+                    uint32_t wl = 0, wh = 0;
+                    for(int c = 0; c < 4 && ok; c++){
+                        if(a.ref[c] == REF_EMPTY){ wl |= 255u << (8 * c); continue; }      // lo planes at 255, hi planes at 0 steps: whichever of the two is the near plane for a ray, the slab interval comes out empty
+                        long ql = (long)std::floor(((double)mins[ax][c] - (double)org) / (double)step - 0.25);
+                        long qh = (long)std::ceil(((double)maxs[ax][c] - (double)org) / (double)step + 0.25);
+                        if(ql < 0)ql = 0;
+                        // float check, the way a decoder would form the planes
+                        while(ql > 0 && !(org + (float)ql * step <= mins[ax][c]))ql--;
+                        while(qh < 256 && !(org + (float)qh * step >= maxs[ax][c]))qh++;
+                        if(!(org + (float)ql * step <= mins[ax][c]) || qh > 255){ ok = false; break; }
+                        wl |= (uint32_t)ql << (8 * c); wh |= (uint32_t)qh << (8 * c);
+                    }
+                    if(ok){
+                        q.org[ax] = org; q.ex[ax] = (uint8_t)(e + 127);
+                        words[ax] = wl; words[3 + ax] = wh;
+                        break;
+                    }
+                    if(e > 120){ q.org[ax] = lo; q.ex[ax] = 254; words[ax] = 0; words[3 + ax] = 0xFFFFFFFFu; break; }   // absurd extents: boxes that always pass
+                }
+            }
+            for(int k = 0; k < 6; k++)q.q[k] = words[k];
+            for(int c = 0; c < 4; c++)q.ref[c] = a.ref[c];
+            for(int k = 0; k < 8; k++)q.order[k] = a.order[k];
+            out[i] = q;
+        }
+    };
+    if(nt == 1){ work(0, n); return; }
+    std::vector<std::thread> th;
+    for(unsigned t = 0; t < nt; t++)th.emplace_back(work, n * t / nt, n * (t + 1) / nt);
+    for(auto& t : th)t.join();
 }
 
 } // namespace ptb

@@ -7,6 +7,7 @@
 #include <cstdlib>
 #include <cstring>
 #include <new>
+#include <string>
 
 #include "scene_host.hpp"
 
@@ -86,6 +87,20 @@ static int trace_pipelined(pt_scene* s, const pt_ray* rays, size_t n, Launch lau
     }
     if(!cuda_ok(cudaStreamSynchronize(out), "sync") || !cuda_ok(cudaStreamSynchronize(cs[0]), "sync") || !cuda_ok(cudaStreamSynchronize(cs[1]), "sync") ||
        !cuda_ok(cudaStreamSynchronize(in), "sync"))return PT_ERR_CUDA;
+    return PT_OK;
+}
+
+// Traversal-stack overflow (trace.cuh TF_OVERFLOW) is counted on the device; the synchronous entry points fail the call
+// whose rays moved the counter (the asynchronous *_dev ones cannot: pt_scene_stack_overflows reads it).
+static int check_overflow(pt_scene* s, const char* what){
+    unsigned long long now = 0;
+    const int rc = scene_overflow_count(s, &now);
+    if(rc != PT_OK)return rc;
+    if(now != s->overflow_seen){
+        set_error(std::string(what) + ": traversal stack overflow on " + std::to_string(now - s->overflow_seen) + " rays (more than 96 stack entries needed); their hits may be wrong");
+        s->overflow_seen = now;
+        return PT_ERR_OVERFLOW;
+    }
     return PT_OK;
 }
 
@@ -228,6 +243,7 @@ pt_scene* pt_scene_create(int device){
 
 void pt_scene_destroy(pt_scene* s){
     if(!s)return;
+    pt_dist_finalize(s);
     if(s->committed || s->buf.n2 || s->buf.n4){
         cudaSetDevice(s->device);
         cudaDeviceSynchronize();
@@ -313,6 +329,13 @@ int pt_scene_set_builder(pt_scene* s, int builder){
     return PT_OK;
 }
 
+int pt_scene_set_layout(pt_scene* s, int layout){
+    PT_CHECK_OPEN(s);
+    if(layout != PT_LAYOUT_EXACT && layout != PT_LAYOUT_FAST){ set_error("unknown layout"); return PT_ERR_INVALID; }
+    s->layout = layout;
+    return PT_OK;
+}
+
 int pt_scene_set_allreduce(pt_scene* s, pt_allreduce_fn sum, void* user){
     PT_CHECK_SCENE(s);
     s->allreduce = sum; s->allreduce_user = user;
@@ -374,10 +397,10 @@ int pt_trace_closest(pt_scene* s, const pt_ray* rays, size_t n, pt_hit* hits, ui
     };
     if(use_streamed(s, n)){
         const int rc = trace_streamed(s, rays, n, false, out_hits);
-        if(rc != kStreamGaveUp)return rc;
+        if(rc != kStreamGaveUp)return rc != PT_OK ? rc : check_overflow(s, "pt_trace_closest");
         s->streamed_off = true;      // this process blocks in kernel launches: stay with one kernel per chunk
     }
-    return trace_pipelined(s, rays, n,
+    const int prc = trace_pipelined(s, rays, n,
         [&](size_t off, size_t m, cudaStream_t st){
             return launch_trace_closest(s, (pt_ray*)b.stage_rays + off, m, (pt_hit*)b.stage_hits + off, inst ? (uint32_t*)b.stage_inst + off : nullptr, st);
         },
@@ -386,6 +409,7 @@ int pt_trace_closest(pt_scene* s, const pt_ray* rays, size_t n, pt_hit* hits, ui
             if(inst && !cuda_ok(cudaMemcpyAsync(inst + off, (uint32_t*)b.stage_inst + off, m * sizeof(uint32_t), cudaMemcpyDeviceToHost, st), "D2H inst"))return (int)PT_ERR_CUDA;
             return (int)PT_OK;
         });
+    return prc != PT_OK ? prc : check_overflow(s, "pt_trace_closest");
 }
 
 int pt_trace_any(pt_scene* s, const pt_ray* rays, size_t n, uint8_t* occluded){
@@ -396,14 +420,15 @@ int pt_trace_any(pt_scene* s, const pt_ray* rays, size_t n, uint8_t* occluded){
     if(use_streamed(s, n)){
         const int rc = trace_streamed(s, rays, n, true, [&](size_t off, size_t m, cudaStream_t st){
             return cuda_ok(cudaMemcpyAsync(occluded + off, (uint8_t*)b.stage_occ + off, m, cudaMemcpyDeviceToHost, st), "D2H occ") ? (int)PT_OK : (int)PT_ERR_CUDA; });
-        if(rc != kStreamGaveUp)return rc;
+        if(rc != kStreamGaveUp)return rc != PT_OK ? rc : check_overflow(s, "pt_trace_any");
         s->streamed_off = true;      // this process blocks in kernel launches: stay with one kernel per chunk
     }
-    return trace_pipelined(s, rays, n,
+    const int prc = trace_pipelined(s, rays, n,
         [&](size_t off, size_t m, cudaStream_t st){ return launch_trace_any(s, (pt_ray*)b.stage_rays + off, m, (uint8_t*)b.stage_occ + off, st); },
         [&](size_t off, size_t m, cudaStream_t st){
             return cuda_ok(cudaMemcpyAsync(occluded + off, (uint8_t*)b.stage_occ + off, m, cudaMemcpyDeviceToHost, st), "D2H occ") ? (int)PT_OK : (int)PT_ERR_CUDA;
         });
+    return prc != PT_OK ? prc : check_overflow(s, "pt_trace_any");
 }
 
 int pt_trace_closest_dev(pt_scene* s, const void* d_rays, size_t n, void* d_hits, void* d_inst, void* stream){
@@ -416,6 +441,37 @@ int pt_trace_any_dev(pt_scene* s, const void* d_rays, size_t n, void* d_occ, voi
     PT_CHECK_READY(s);
     if(n && (!d_rays || !d_occ)){ set_error("null buffer"); return PT_ERR_INVALID; }
     return launch_trace_any(s, d_rays, n, d_occ, stream);
+}
+
+int pt_scene_stack_overflows(pt_scene* s, uint64_t* count){
+    PT_CHECK_READY(s);
+    if(!count){ set_error("null count"); return PT_ERR_INVALID; }
+    unsigned long long now = 0;
+    const int rc = scene_overflow_count(s, &now);
+    if(rc == PT_OK)*count = now;
+    return rc;
+}
+
+int pt_scene_set_counting(pt_scene* s, int on){
+    PT_CHECK_READY(s);
+    if(on && s->dev.width != 4){ set_error("counted renders need bvh_width 4"); return PT_ERR_INVALID; }
+    s->counting = on != 0;
+    if(!cuda_ok(cudaDeviceSynchronize(), "sync") || !cuda_ok(cudaMemset((unsigned long long*)s->buf.stats + 16, 0, 128), "counters clear"))return PT_ERR_CUDA;
+    return PT_OK;
+}
+
+int pt_scene_render_counts(pt_scene* s, pt_trace_stats* closest, pt_trace_stats* shadow){
+    PT_CHECK_READY(s);
+    if(!closest || !shadow){ set_error("null stats"); return PT_ERR_INVALID; }
+    unsigned long long h[16];
+    if(!cuda_ok(cudaDeviceSynchronize(), "sync") || !cuda_ok(cudaMemcpy(h, (unsigned long long*)s->buf.stats + 16, 128, cudaMemcpyDeviceToHost), "D2H counters") ||
+       !cuda_ok(cudaMemset((unsigned long long*)s->buf.stats + 16, 0, 128), "counters clear"))return PT_ERR_CUDA;
+    pt_trace_stats* out[2] = { closest, shadow };
+    for(int k = 0; k < 2; k++){
+        const unsigned long long* c = h + 8 * k;
+        out[k]->rays = 0; out[k]->tlas_nodes = c[0]; out[k]->blas_nodes = c[1]; out[k]->instances = c[2]; out[k]->triangles = c[3]; out[k]->hits = c[4];
+    }
+    return PT_OK;
 }
 
 int pt_trace_closest_stats(pt_scene* s, const void* d_rays, size_t n, pt_trace_stats* out){

@@ -47,6 +47,26 @@ struct alignas(16) Bvh4Node {
 };
 static_assert(sizeof(Bvh4Node) == 128, "Bvh4Node must be 128 B");
 
+// "Fast" BVH4 cluster, 64 B = two 32 B sectors (pt_scene_set_layout(PT_LAYOUT_FAST)).  The same tree, child
+// order and visit-order bytes as Bvh4Node -- only the child boxes are stored as 8-bit offsets from a per-cluster
+// origin in power-of-two steps per axis (after Ylitie et al. 2017, "Efficient Incoherent Ray Traversal on GPUs Through
+// Compressed Wide BVHs"), rounded outwards by at least a quarter step, so every decoded box CONTAINS the exact one:
+// the traversal visits a superset of the nodes the reference visits, in the same order, and the closest hit (exact
+// triangle arithmetic, unchanged) is the same.  Why: k_trace is bound by L1 data-pipe wavefronts -- one per 32 B
+// sector per lane for incoherent rays (profiles/r01_trace4_v7.md: 92 % of peak) -- and this halves the sectors per
+// cluster visit (2 x LDG.256 instead of 4).
+//   word[p], p = 0..5 (lo x, lo y, lo z, hi x, hi y, hi z): byte c = child c's plane p in steps from `org`
+struct alignas(32) Bvh4QNode {
+    float org[3];
+    uint8_t ex[3];          // biased exponent of the step per axis: step = 2^(ex - 127)
+    uint8_t pad0;
+    uint32_t ref[4];
+    uint32_t q[6];
+    uint8_t order[8];
+};
+static_assert(sizeof(Bvh4QNode) == 64, "Bvh4QNode must be 64 B");
+constexpr int kWidthFast4 = 44;          // template "width" of the kernels that walk Bvh4QNode + Tri64
+
 // BVH8 cluster, 256 B = eight 32 B sectors.  Same content as BVH8_CLUSTER (BVH.hpp:1241-1257) with the child
 // boxes stored as two 4-lane halves (half h holds lanes 4h..4h+3: xmin[4] xmax[4] ymin[4] ymax[4] zmin[4]
 // zmax[4]) so that a half is three 256-bit loads and eight slab tests never hold 48 box floats at once.
@@ -68,6 +88,9 @@ struct alignas(16) Tri {
     float e2[3]; uint32_t flags;
 };
 static_assert(sizeof(Tri) == 48, "Tri must be 48 B");
+// fast layout: the same record padded to 64 B, so that it is two aligned 256-bit loads (2 wavefronts) instead of three 128-bit ones
+struct alignas(32) Tri64 { Tri t; uint32_t pad[4]; };
+static_assert(sizeof(Tri64) == 64, "Tri64 must be 64 B");
 constexpr uint32_t TRI_LAST = 1u;        // last triangle of its leaf
 constexpr uint32_t TRI_ALPHA_PATH = 2u;  // material->HasAlpha(): any-hit goes through
                                          // shape->Intersect (Primitive.cpp:6-14)
@@ -108,8 +131,11 @@ struct DevScene {
     const Bvh8Node* n8;      // BVH8 clusters: all BLASes, then the TLAS
     const Tri* tris;         // all BLAS triangles in leaf order
     const Instance* inst;    // instances in TLAS leaf order
+    const Bvh4QNode* n4q;    // fast layout (width == 4 only): quantised copy of n4, same indices
+    const Tri64* tris64;     // fast layout: tris padded to 64 B, same indices
     uint32_t tlas_root;      // ref into n2/n4 (or a leaf ref into inst)
     int width;               // 2 | 4 | 8
+    int fast;                // 1: the kernels walk n4q / tris64 (kWidthFast4)
     float tlo[3], thi[3];    // TLAS root box (BVH2::Intersect tests it first)
     uint32_t single_root;    // scene = one untransformed instance: its BLAS root ref (traversal starts
                              // inside it, no TLAS leaf / instance record round trip); else REF_EMPTY

@@ -19,6 +19,7 @@
 #include <algorithm>
 #include <cmath>
 #include <cstdlib>
+#include <string>
 
 #include "scene_host.hpp"
 #include "shade_mat.cuh"
@@ -58,7 +59,27 @@ struct Arena {
     uint32_t ps_slot, ps_quarter;   // index strides: (4, 1) records | (1, cap) planes
     uint8_t* skey; uint32_t* perm; uint32_t* shist;   // shade-order sort: class per queue entry, sorted order, per-block histograms
     uint32_t* done;     // slots whose path ended in the last shade pass: splatted, then handed to new samples
-    uint32_t* counters; // [0] next-queue size, [1] shadow-queue size, [2] done-list size, [3] non-finite samples of the call
+    struct WaveCtl* ctl; // queue sizes and everything else the loop decides per bounce: on the device, never read by the host inside the loop
+};
+
+// Control block of the wavefront loop.  The host enqueues whole bounces without knowing any queue size: every kernel
+// is a persistent grid that reads its batch from here, the last block of k_finish closes a bounce (which camera samples refill the slots
+// that ended, which queue is current next, cursors back to zero).  The host only watches n_cur a few bounces late to
+// find out when to stop (render_passes).  Round 1 read three counters back and synchronised the stream every bounce:
+// 18 us x 1250 bounces on C5, and most of a C1 frame on 8 GPUs.
+struct WaveCtl {
+    uint32_t n_cur;        // rays in the current queue
+    uint32_t n_next;       // continuation rays appended by k_shade: the next current queue
+    uint32_t n_sh;         // shadow rays of this bounce
+    uint32_t n_done;       // paths that ended in this bounce
+    uint32_t cur;          // which of the two ray queues is current
+    uint32_t n_gen;        // camera samples k_generate starts after this bounce
+    uint32_t q_off;        // where they go in the (new) current queue
+    uint32_t nonfinite;    // non-finite samples of the call (counted, not splatted)
+    unsigned long long gen_first, next_gid, count;
+    unsigned long long cursor[2];                         // ray dispensers of the closest-hit / any-hit launches
+    unsigned long long closest_rays, shadow_rays, samples, bounces;   // totals of the call
+    uint32_t ticket;       // blocks of k_finish that have ended (the last one plans the next bounce)
 };
 
 __device__ __forceinline__ float4* ps_at(const Arena& A, uint32_t slot, uint32_t k){
@@ -102,12 +123,8 @@ __device__ __forceinline__ uint32_t queue_slot(uint32_t* counter, bool want){
 
 // ---- generate: StartPixelSample / getPixel2D / get1D / get2D / Camera::GenerateRay (Integrators.cpp:61-64) ----
 // n_new camera samples gid_first.. go into the slots free[i] (or free_base + i) and onto the end of queue `cur`
-__global__ void __launch_bounds__(256) k_generate(Arena A, BatchInfo B, CamParams C, uint32_t n_new, uint64_t gid_first,
-                                                  const uint32_t* __restrict__ free, uint32_t q_off, int cur){
-    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
-    if(i >= n_new)return;
-    const uint32_t slot = free ? free[i] : i;
-    const uint64_t gid = gid_first + i;
+// one camera sample: gid -> slot `slot`, ray -> position q of queue `cur`
+__device__ __forceinline__ void generate_one(const Arena& A, const BatchInfo& B, const CamParams& C, uint64_t gid, uint32_t slot, size_t q, int cur){
     uint32_t pixel, sample;
     const uint64_t stream = stream_of(B, gid, pixel, sample);
     Pcg g = pcg_seed(B.seed, stream);
@@ -134,10 +151,10 @@ __global__ void __launch_bounds__(256) k_generate(Arena A, BatchInfo B, CamParam
     const float px = (float)((double)x + jx), py = (float)((double)y + jy);   // GenerateRay takes a glm::vec2
     V3 org, dir; float t;
     camera_ray(C, B.W, B.H, px, py, time, lx, ly, org, dir, t);
-    const size_t q = (size_t)q_off + i;
-    A.rays[cur][2 * q] = make_float4(org.x, org.y, org.z, CUDART_INF_F);
-    A.rays[cur][2 * q + 1] = make_float4(dir.x, dir.y, dir.z, t);
-    A.qslot[cur][q] = slot;
+    float4* __restrict__ qr = cur ? A.rays[1] : A.rays[0];
+    qr[2 * q] = make_float4(org.x, org.y, org.z, CUDART_INF_F);
+    qr[2 * q + 1] = make_float4(dir.x, dir.y, dir.z, t);
+    (cur ? A.qslot[1] : A.qslot[0])[q] = slot;
     *ps_at(A, slot, 0) = make_float4(1.0f, 1.0f, 1.0f, 1.0f);
     *ps_at(A, slot, 1) = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
     // depth 1: `depth++ < maxDepth` already taken for bounce 1
@@ -146,27 +163,53 @@ __global__ void __launch_bounds__(256) k_generate(Arena A, BatchInfo B, CamParam
     *ps_at(A, slot, 3) = make_float4(__uint_as_float((uint32_t)gid), __uint_as_float((uint32_t)(gid >> 32)), (float)jx, (float)jy);
 }
 
-// ---- connect: add the unoccluded NEE contributions (Integrators.cpp:243-244, 356, 398) ------
-__global__ void __launch_bounds__(256) k_connect(Arena A, uint32_t n){
-    const uint32_t k = blockIdx.x * blockDim.x + threadIdx.x;
-    if(k >= n || A.socc[k])return;
-    const uint32_t slot = A.sslot[k];
-    const float4 c = A.scontrib[k];
-    float4 r = *ps_at(A, slot, 1);
-    r.x += c.x; r.y += c.y; r.z += c.z;
-    *ps_at(A, slot, 1) = r;
+// the first samples of a run: slots 0 .. n_gen - 1, queue 0 (k_wave_init)
+__global__ void __launch_bounds__(256) k_generate(Arena A, BatchInfo B, CamParams C){
+    const WaveCtl& W = *A.ctl;
+    const uint32_t n_new = W.n_gen;
+    const uint64_t gid_first = W.gen_first;
+    for(uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n_new; i += gridDim.x * blockDim.x)
+        generate_one(A, B, C, gid_first + i, i, (size_t)i, 0);
 }
+
+// ---- plan: close one bounce on the device (run by ONE thread, after every other block of k_finish has ended) ----
+__device__ __forceinline__ void plan_bounce(WaveCtl& W){
+    const unsigned long long left = W.count - W.next_gid;
+    const uint32_t m = (uint32_t)(left < (unsigned long long)W.n_done ? left : (unsigned long long)W.n_done);
+    W.closest_rays += W.n_cur; W.shadow_rays += W.n_sh; W.samples += m; W.bounces += W.n_cur ? 1ull : 0ull;
+    W.n_gen = m; W.gen_first = W.next_gid; W.next_gid += m;
+    W.q_off = W.n_next;
+    W.cur ^= 1u;
+    W.n_cur = W.n_next + m;
+    W.n_next = 0u; W.n_sh = 0u; W.n_done = 0u;
+    W.cursor[0] = 0ull; W.cursor[1] = 0ull;
+    W.ticket = 0u;
+}
+
+// start of a run of `count` camera samples: the first min(cap, count) go straight into slots 0.. of queue 0
+__global__ void k_wave_init(Arena A, unsigned long long gid_base, unsigned long long count, unsigned long long cap, int reset_totals){
+    WaveCtl& W = *A.ctl;
+    const uint32_t n = (uint32_t)(count - gid_base < cap ? count - gid_base : cap);
+    W.n_cur = n; W.n_next = 0u; W.n_sh = 0u; W.n_done = 0u; W.cur = 0u;
+    W.n_gen = n; W.q_off = 0u; W.gen_first = gid_base; W.next_gid = gid_base + n; W.count = count;
+    W.cursor[0] = 0ull; W.cursor[1] = 0ull; W.ticket = 0u;
+    if(reset_totals){ W.nonfinite = 0u; W.closest_rays = 0ull; W.shadow_rays = 0ull; W.samples = 0ull; W.bounces = 0ull; }
+    W.samples += n;
+}
+
+// ---- connect: the unoccluded NEE contributions (Integrators.cpp:243-244, 356, 398) are added by the any-hit kernel
+// itself when a shadow ray retires (trace.cu, ConnectAcc): no separate pass, no occlusion flags in memory.
 
 // ---- connect through medium boundaries: Scene::IntersectTr (Scene.cpp:8-29) ---------------------------
 // VolPathIntegrator::SampleLd (Integrators.cpp:466) does not ask "is anything in the way" but walks the
 // shadow ray with closest hits: a primitive without a material (a medium boundary) lets it through and
 // switches the medium, transmittance is collected per segment, the first primitive WITH a material blocks.
 // One lane walks one shadow ray start to end (whole-ray traversal, local stack): only scenes that hold
-// such boundaries take this path, everything else keeps the any-hit kernel + k_connect.
+// such boundaries take this path, everything else keeps the any-hit kernel (which adds the contribution itself).
 template <int WIDTH, class Alpha>
-__global__ void __launch_bounds__(128) k_shadow_tr(Arena A, DevScene D, ShadeScene S, uint32_t n, Alpha alpha){
-    const uint32_t k = blockIdx.x * blockDim.x + threadIdx.x;
-    if(k >= n)return;
+__global__ void __launch_bounds__(128) k_shadow_tr(Arena A, DevScene D, ShadeScene S, Alpha alpha, unsigned long long* __restrict__ overflow){
+    const uint32_t n = A.ctl->n_sh;
+    for(uint32_t k = blockIdx.x * blockDim.x + threadIdx.x; k < n; k += gridDim.x * blockDim.x){
     RayRegs ray; ray.a = A.srays[2 * (size_t)k]; ray.b = A.srays[2 * (size_t)k + 1];
     const float4 c = A.scontrib[k];
     int med = __float_as_int(c.w);
@@ -175,7 +218,9 @@ __global__ void __launch_bounds__(128) k_shadow_tr(Arena A, DevScene D, ShadeSce
     bool blocked = false;
     for(int seg = 0; seg < 256 && ray.a.w > 0.0f; seg++){
         HitRec h;
-        if(!trace_scene<WIDTH, false, false>(D, ray, k, h, nullptr, alpha)){
+        const bool found = trace_scene<WIDTH, false, false>(D, ray, k, h, nullptr, alpha);
+        if(h.overflow)atomicAdd(overflow, 1ull);
+        if(!found){
             if(med >= 0)tr *= medium_Tr(S.media[med], ray.a.w);
             break;
         }
@@ -188,20 +233,22 @@ __global__ void __launch_bounds__(128) k_shadow_tr(Arena A, DevScene D, ShadeSce
         med = dot(d, si.n) < 0.0f ? si.medium : -1;                   // interaction.getMedium(ray.dir)
         ray.a = make_float4(q.x, q.y, q.z, ray.a.w - h.t);
     }
-    if(blocked)return;
+    if(blocked)continue;
     const uint32_t slot = A.sslot[k];
     float4 r = *ps_at(A, slot, 1);
     r.x += c.x * tr.x; r.y += c.y * tr.y; r.z += c.z * tr.z;
     *ps_at(A, slot, 1) = r;
+    }
 }
 
 template <class Alpha>
-static void launch_shadow_tr(const Arena& A, const pt_scene* s, uint32_t n, cudaStream_t st, const Alpha& alpha){
-    const unsigned grid = (n + 127) / 128;
+static void launch_shadow_tr(const Arena& A, const pt_scene* s, unsigned grid, cudaStream_t st, const Alpha& alpha){
+    unsigned long long* ovf = (unsigned long long*)s->buf.stats + 8;
+    if(s->dev.fast){ k_shadow_tr<kWidthFast4><<<grid, 128, 0, st>>>(A, s->dev, s->shade, alpha, ovf); return; }
     switch(s->dev.width){
-    case 2: k_shadow_tr<2><<<grid, 128, 0, st>>>(A, s->dev, s->shade, n, alpha); break;
-    case 4: k_shadow_tr<4><<<grid, 128, 0, st>>>(A, s->dev, s->shade, n, alpha); break;
-    default: k_shadow_tr<8><<<grid, 128, 0, st>>>(A, s->dev, s->shade, n, alpha); break;
+    case 2: k_shadow_tr<2><<<grid, 128, 0, st>>>(A, s->dev, s->shade, alpha, ovf); break;
+    case 4: k_shadow_tr<4><<<grid, 128, 0, st>>>(A, s->dev, s->shade, alpha, ovf); break;
+    default: k_shadow_tr<8><<<grid, 128, 0, st>>>(A, s->dev, s->shade, alpha, ovf); break;
     }
 }
 
@@ -250,10 +297,24 @@ __device__ inline double filter_eval(const FilterParams& F, float x, float y){
 }
 
 // est: this call's per-pixel estimator sums for the adaptive loop, 6 doubles per pixel {sum rgb, sum of squares rgb}, or null
-__global__ void __launch_bounds__(256) k_film(Arena A, BatchInfo B, FilterParams F, double* __restrict__ film, double* __restrict__ film_sq, double* __restrict__ est,
-                                              const uint32_t* __restrict__ done, uint32_t n_done){
-    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
-    if(i >= n_done)return;
+// ---- finish a bounce: film + regeneration + plan in one launch ---------------------------------------------------------
+// Thread i takes done[i]: splats that slot's finished sample (FilmTile::Add + Film::Merge), and -- while camera samples are
+// left -- starts the next one in the same slot, its ray appended behind the continuation rays k_shade queued.  The block
+// that ends last (a ticket in WaveCtl) then closes the bounce for everybody (plan_bounce).  Round 1 ran these as
+// k_film, a counters read-back on the host and k_generate; as three launches they cost a C1 shard a third of its frame.
+// whole_pool: splat slots 0 .. n_cur - 1 instead (max_depth == 0: black samples, nothing else runs).
+// est: this call's per-pixel estimator sums for the adaptive loop, 6 doubles per pixel {sum rgb, sum of squares rgb}, or null
+__global__ void __launch_bounds__(256) k_finish(Arena A, BatchInfo B, FilterParams F, CamParams C, double* __restrict__ film, double* __restrict__ film_sq,
+                                                double* __restrict__ est, int whole_pool){
+    WaveCtl& W = *A.ctl;
+    const uint32_t n_done = whole_pool ? W.n_cur : W.n_done;
+    const uint32_t* __restrict__ done = whole_pool ? nullptr : A.done;
+    const unsigned long long left = W.count - W.next_gid;
+    const uint32_t m = whole_pool ? 0u : (uint32_t)(left < (unsigned long long)n_done ? left : (unsigned long long)n_done);
+    const uint64_t gid_first = W.next_gid;
+    const uint32_t q_off = W.n_next;
+    const int ncur = (int)(W.cur ^ 1u);
+    for(uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n_done; i += gridDim.x * blockDim.x){
     const uint32_t slot = done ? done[i] : i;
     uint32_t pixel, sample;
     const float4 q3 = *ps_at(A, slot, 3);
@@ -262,27 +323,39 @@ __global__ void __launch_bounds__(256) k_film(Arena A, BatchInfo B, FilterParams
     const float4 r = *ps_at(A, slot, 1);
     const float2 sp = make_float2(q3.z, q3.w);
     if(!(fabsf(r.x) <= 3.0e38f && fabsf(r.y) <= 3.0e38f && fabsf(r.z) <= 3.0e38f)){
-        atomicAdd(A.counters + 3, 1u);       // non-finite radiance: counted, not splatted (one NaN would own the pixel)
-        return;
-    }
-    {   // per-pixel sum of squared sample radiance (owner pixel): the variance the 3-sigma parity test
-        // and VarianceEstimator (Util.hpp:8-43) need
-        double* q = film_sq + 3 * ((size_t)y * B.W + x);
-        atomicAdd(q, (double)r.x * r.x); atomicAdd(q + 1, (double)r.y * r.y); atomicAdd(q + 2, (double)r.z * r.z);
-        if(est){
-            double* e = est + 6 * ((size_t)y * B.W + x);
-            atomicAdd(e, (double)r.x); atomicAdd(e + 1, (double)r.y); atomicAdd(e + 2, (double)r.z);
-            atomicAdd(e + 3, (double)r.x * r.x); atomicAdd(e + 4, (double)r.y * r.y); atomicAdd(e + 5, (double)r.z * r.z);
+        atomicAdd(&W.nonfinite, 1u);         // non-finite radiance: counted, not splatted (one NaN would own the pixel)
+    } else{
+        {   // per-pixel sum of squared sample radiance (owner pixel): the variance the 3-sigma parity test
+            // and VarianceEstimator (Util.hpp:8-43) need
+            double* q = film_sq + 3 * ((size_t)y * B.W + x);
+            atomicAdd(q, (double)r.x * r.x); atomicAdd(q + 1, (double)r.y * r.y); atomicAdd(q + 2, (double)r.z * r.z);
+            if(est){
+                double* e = est + 6 * ((size_t)y * B.W + x);
+                atomicAdd(e, (double)r.x); atomicAdd(e + 1, (double)r.y); atomicAdd(e + 2, (double)r.z);
+                atomicAdd(e + 3, (double)r.x * r.x); atomicAdd(e + 4, (double)r.y * r.y); atomicAdd(e + 5, (double)r.z * r.z);
+            }
+        }
+        for(int dy = -F.ry; dy <= F.ry; dy++)for(int dx = -F.rx; dx <= F.rx; dx++){
+            const float fx = (float)((double)dx + 0.5 - (double)sp.x), fy = (float)((double)dy + 0.5 - (double)sp.y);   // Filter::Evaluate takes a glm::vec2
+            const double w = filter_eval(F, fx, fy) * F.inv_integral;
+            const int qx = x + dx, qy = y + dy;
+            if(w <= 0.0 || qx < 0 || qy < 0 || qx >= B.W || qy >= B.H)continue;
+            double* q = film + 4 * ((size_t)qy * B.W + qx);
+            atomicAdd(q, (double)r.x * w); atomicAdd(q + 1, (double)r.y * w); atomicAdd(q + 2, (double)r.z * w); atomicAdd(q + 3, w);
         }
     }
-    for(int dy = -F.ry; dy <= F.ry; dy++)for(int dx = -F.rx; dx <= F.rx; dx++){
-        const float fx = (float)((double)dx + 0.5 - (double)sp.x), fy = (float)((double)dy + 0.5 - (double)sp.y);   // Filter::Evaluate takes a glm::vec2
-        const double w = filter_eval(F, fx, fy) * F.inv_integral;
-        const int qx = x + dx, qy = y + dy;
-        if(w <= 0.0 || qx < 0 || qy < 0 || qx >= B.W || qy >= B.H)continue;
-        double* q = film + 4 * ((size_t)qy * B.W + qx);
-        atomicAdd(q, (double)r.x * w); atomicAdd(q + 1, (double)r.y * w); atomicAdd(q + 2, (double)r.z * w); atomicAdd(q + 3, w);
+    if(i < m)generate_one(A, B, C, gid_first + i, slot, (size_t)q_off + i, ncur);
     }
+    if(whole_pool)return;
+    // last block out plans the next bounce: every other block has finished reading WaveCtl by then
+    __shared__ bool last;
+    __syncthreads();
+    if(threadIdx.x == 0){
+        __threadfence();
+        last = atomicAdd(&W.ticket, 1u) == gridDim.x - 1;
+    }
+    __syncthreads();
+    if(last && threadIdx.x == 0){ __threadfence(); plan_bounce(W); }
 }
 
 // ---- adaptive loop: the per-pixel stopping rule of TileIntegrator::Render (Integrators.cpp:59-86) ----
@@ -334,22 +407,36 @@ __device__ __forceinline__ uint32_t shade_class(const Arena& A, const ShadeScene
     return 2u + (uint32_t)S.materials[mat].kind;      // pt_mat_kind 0..3
 }
 
-__global__ void __launch_bounds__(kSortBlock) k_sort_count(Arena A, ShadeScene S, uint32_t n, uint32_t nb){
+// The batch size lives on the device: a fixed grid of kSortGrid blocks, block b owns the contiguous range
+// [b * per, (b + 1) * per) of the queue (per = a multiple of kSortBlock), so block order == queue order and the sort stays stable.
+constexpr unsigned kSortGrid = 1184;      // 148 SMs x 8
+
+__device__ __forceinline__ uint32_t sort_per(uint32_t n){
+    const uint32_t per = (n + kSortGrid - 1) / kSortGrid;
+    return (per + kSortBlock - 1) / kSortBlock * kSortBlock;
+}
+
+__global__ void __launch_bounds__(kSortBlock) k_sort_count(Arena A, ShadeScene S, uint32_t sort_min){
+    const uint32_t n = A.ctl->n_cur;
+    if(n < sort_min)return;
     __shared__ uint32_t h[kSortKeys];
     if(threadIdx.x < kSortKeys)h[threadIdx.x] = 0u;
     __syncthreads();
-    const uint32_t j = blockIdx.x * kSortBlock + threadIdx.x;
-    if(j < n){
+    const uint32_t per = sort_per(n), lo = blockIdx.x * per, hi = min(n, lo + per);
+    for(uint32_t j = lo + threadIdx.x; j < hi; j += kSortBlock){
         const uint32_t k = shade_class(A, S, j);
         A.skey[j] = (uint8_t)k;
         atomicAdd(&h[k], 1u);
     }
     __syncthreads();
-    if(threadIdx.x < kSortKeys)A.shist[threadIdx.x * nb + blockIdx.x] = h[threadIdx.x];   // key-major: one scan gives final offsets
+    if(threadIdx.x < kSortKeys)A.shist[threadIdx.x * kSortGrid + blockIdx.x] = h[threadIdx.x];   // key-major: one scan gives final offsets
 }
 
-// exclusive scan of `m` counters in place, one block
-__global__ void __launch_bounds__(1024) k_sort_scan(uint32_t* __restrict__ v, uint32_t m){
+// exclusive scan of the kSortKeys x kSortGrid counters in place, one block
+__global__ void __launch_bounds__(1024) k_sort_scan(Arena A, uint32_t sort_min){
+    if(A.ctl->n_cur < sort_min)return;
+    uint32_t* __restrict__ v = A.shist;
+    const uint32_t m = kSortGrid * kSortKeys;
     __shared__ uint32_t part[1024];
     const uint32_t per = (m + 1023u) / 1024u;
     const uint32_t lo = threadIdx.x * per, hi = min(lo + per, m);
@@ -367,23 +454,37 @@ __global__ void __launch_bounds__(1024) k_sort_scan(uint32_t* __restrict__ v, ui
     for(uint32_t i = lo; i < hi; i++){ const uint32_t c = v[i]; v[i] = run; run += c; }
 }
 
-__global__ void __launch_bounds__(kSortBlock) k_sort_scatter(Arena A, uint32_t n, uint32_t nb){
+__global__ void __launch_bounds__(kSortBlock) k_sort_scatter(Arena A, uint32_t sort_min){
+    const uint32_t n = A.ctl->n_cur;
+    if(n < sort_min)return;
     __shared__ uint32_t wc[kSortBlock / 32][kSortKeys];
-    const uint32_t j = blockIdx.x * kSortBlock + threadIdx.x;
+    __shared__ uint32_t base[kSortKeys];
     const unsigned lane = threadIdx.x & 31u, w = threadIdx.x >> 5;
-    const uint32_t k = j < n ? (uint32_t)A.skey[j] : 0xFFu;
-    uint32_t rank = 0;
+    if(threadIdx.x < kSortKeys)base[threadIdx.x] = A.shist[threadIdx.x * kSortGrid + blockIdx.x];
+    const uint32_t per = sort_per(n), lo = blockIdx.x * per, hi = min(n, lo + per);
+    for(uint32_t j0 = lo; j0 < hi; j0 += kSortBlock){
+        const uint32_t j = j0 + threadIdx.x;
+        const uint32_t k = j < hi ? (uint32_t)A.skey[j] : 0xFFu;
+        uint32_t rank = 0;
 #pragma unroll
-    for(uint32_t c = 0; c < (uint32_t)kSortKeys; c++){
-        const unsigned m = __ballot_sync(0xffffffffu, k == c);
-        if(k == c)rank = __popc(m & ((1u << lane) - 1u));
-        if(lane == 0)wc[w][c] = __popc(m);
-    }
-    __syncthreads();
-    if(j < n){
-        uint32_t off = A.shist[k * nb + blockIdx.x] + rank;
-        for(unsigned q = 0; q < w; q++)off += wc[q][k];
-        A.perm[off] = j;
+        for(uint32_t c = 0; c < (uint32_t)kSortKeys; c++){
+            const unsigned m = __ballot_sync(0xffffffffu, k == c);
+            if(k == c)rank = __popc(m & ((1u << lane) - 1u));
+            if(lane == 0)wc[w][c] = __popc(m);
+        }
+        __syncthreads();
+        if(j < hi){
+            uint32_t off = base[k] + rank;
+            for(unsigned q = 0; q < w; q++)off += wc[q][k];
+            A.perm[off] = j;
+        }
+        __syncthreads();
+        if(threadIdx.x < kSortKeys){
+            uint32_t t = 0;
+            for(unsigned q = 0; q < kSortBlock / 32; q++)t += wc[q][threadIdx.x];
+            base[threadIdx.x] += t;
+        }
+        __syncthreads();
     }
 }
 
@@ -437,16 +538,27 @@ __device__ inline void sample_ld(const ShadeScene& S, const SurfInt& si, const M
 
 // 96 registers: forcing 6 or 8 resident CTAs (80 / 64 registers, spills) measured slower
 template <int INTEG>
-__global__ void __launch_bounds__(128, PTB_SHADE_MINB) k_shade(Arena A, ShadeScene S, BatchInfo B, uint32_t n, int cur, const uint32_t* __restrict__ perm){
-    const uint32_t tid = blockIdx.x * blockDim.x + threadIdx.x;
-    const uint32_t j = (perm && tid < n) ? perm[tid] : tid;      // shade order (k_sort_*) or queue order
+__global__ void __launch_bounds__(128, PTB_SHADE_MINB) k_shade(Arena A, ShadeScene S, BatchInfo B, uint32_t sort_min){
+    WaveCtl& W = *A.ctl;
+    const uint32_t n = W.n_cur;
+    const int cur = (int)W.cur;
+    const uint32_t* __restrict__ perm = n >= sort_min ? A.perm : nullptr;     // shade order (k_sort_*) or queue order
+    const float4* __restrict__ q_rays = cur ? A.rays[1] : A.rays[0];
+    const uint32_t* __restrict__ q_slot = cur ? A.qslot[1] : A.qslot[0];
+    float4* __restrict__ nq_rays = cur ? A.rays[0] : A.rays[1];
+    uint32_t* __restrict__ nq_slot = cur ? A.qslot[0] : A.qslot[1];
+    // persistent: the block walks the queue in strides of the grid (the loop bound is block-uniform: every lane of a
+    // warp takes part in the ballots of queue_slot)
+    for(uint32_t tile = blockIdx.x * blockDim.x; tile < n; tile += gridDim.x * blockDim.x){
+    const uint32_t tid = tile + threadIdx.x;
+    const uint32_t j = (perm && tid < n) ? perm[tid] : tid;
     bool cont = false, nee = false;
     V3 no = v3(0.0f), nd = v3(0.0f); float ntime = 0.0f;
     NeeOut ne; ne.want = false;
     uint32_t slot = 0;
     if(j < n){
-        slot = A.qslot[cur][j];
-        const float4 ra = A.rays[cur][2 * (size_t)j], rb = A.rays[cur][2 * (size_t)j + 1];
+        slot = q_slot[j];
+        const float4 ra = q_rays[2 * (size_t)j], rb = q_rays[2 * (size_t)j + 1];
         const V3 ro = v3(ra.x, ra.y, ra.z), rd = v3(rb.x, rb.y, rb.z);
         ntime = rb.w;
         const float4 h = A.hits[j];
@@ -568,21 +680,22 @@ __global__ void __launch_bounds__(128, PTB_SHADE_MINB) k_shade(Arena A, ShadeSce
         *ps_at(A, slot, 2) = make_float4(__uint_as_float((uint32_t)g.state), __uint_as_float((uint32_t)(g.state >> 32)), __uint_as_float(depth | (rr_depth << 16)),
                             __uint_as_float((spec ? 1u : 0u) | ((uint32_t)(medium + 1) << 1)));
     }
-    const uint32_t qn = queue_slot(A.counters + 0, cont);
+    const uint32_t qn = queue_slot(&W.n_next, cont);
     if(cont){
-        A.rays[cur ^ 1][2 * (size_t)qn] = make_float4(no.x, no.y, no.z, CUDART_INF_F);
-        A.rays[cur ^ 1][2 * (size_t)qn + 1] = make_float4(nd.x, nd.y, nd.z, ntime);
-        A.qslot[cur ^ 1][qn] = slot;
+        nq_rays[2 * (size_t)qn] = make_float4(no.x, no.y, no.z, CUDART_INF_F);
+        nq_rays[2 * (size_t)qn + 1] = make_float4(nd.x, nd.y, nd.z, ntime);
+        nq_slot[qn] = slot;
     }
     const bool ended = j < n && !cont;
-    const uint32_t qd = queue_slot(A.counters + 2, ended);
+    const uint32_t qd = queue_slot(&W.n_done, ended);
     if(ended)A.done[qd] = slot;
-    const uint32_t qs = queue_slot(A.counters + 1, nee);
+    const uint32_t qs = queue_slot(&W.n_sh, nee);
     if(nee){
         A.srays[2 * (size_t)qs] = make_float4(ne.o.x, ne.o.y, ne.o.z, ne.tmax);
         A.srays[2 * (size_t)qs + 1] = make_float4(ne.d.x, ne.d.y, ne.d.z, ntime);
         A.sslot[qs] = slot;
         A.scontrib[qs] = make_float4(ne.contrib.x, ne.contrib.y, ne.contrib.z, __int_as_float(ne.medium));
+    }
     }
 }
 
@@ -636,8 +749,9 @@ static size_t arena_layout(char* base, Arena& A, size_t cap){
     carve(p, (void**)&A.hits, cap * 16); carve(p, (void**)&A.hinst, cap * 4);
     carve(p, (void**)&A.srays, cap * 32); carve(p, (void**)&A.sslot, cap * 4); carve(p, (void**)&A.scontrib, cap * 16); carve(p, (void**)&A.socc, cap);
     carve(p, (void**)&A.ps, cap * 64); carve(p, (void**)&A.done, cap * 4);
-    carve(p, (void**)&A.skey, cap); carve(p, (void**)&A.perm, cap * 4); carve(p, (void**)&A.shist, ((cap + kSortBlock - 1) / kSortBlock) * kSortKeys * 4 + 4096);
-    carve(p, (void**)&A.counters, 256);
+    carve(p, (void**)&A.skey, cap); carve(p, (void**)&A.perm, cap * 4); carve(p, (void**)&A.shist, (size_t)kSortGrid * kSortKeys * 4 + 4096);
+    carve(p, (void**)&A.ctl, 256);
+    static_assert(sizeof(WaveCtl) <= 256, "WaveCtl outgrew its arena slot");
     return (size_t)(p - base);
 }
 
@@ -744,14 +858,25 @@ int render_passes(pt_scene* s, const pt_camera_desc* cam, const pt_render_params
     }
     // pinned once per scene: cudaMallocHost / cudaFreeHost per frame cost milliseconds (more with other
     // large pinned buffers mapped in the process) and synchronise the device
-    if(!b.h_counters && !cuda_ok(cudaMallocHost(&b.h_counters, 64), "pinned counters"))return PT_ERR_CUDA;
-    uint32_t* h_counters = (uint32_t*)b.h_counters;
-    cudaEvent_t e0, e1;
-    cudaEventCreate(&e0); cudaEventCreate(&e1);
-    cudaEventRecord(e0, st);
-    if(!cuda_ok(cudaMemsetAsync(A.counters, 0, 16, st), "counter reset"))return PT_ERR_CUDA;
-    pt_render_stats R {};
+    constexpr int kRing = 8;                 // watch slots: copies of WaveCtl the host reads a few bounces late
+    if(!b.h_counters && !cuda_ok(cudaMallocHost(&b.h_counters, 256 * (kRing + 2)), "pinned counters"))return PT_ERR_CUDA;
+    WaveCtl* h_ring = (WaveCtl*)b.h_counters;                            // slot k at byte 256 k
+    auto h_slot = [&](int k){ return (WaveCtl*)((char*)b.h_counters + 256 * k); };
+    uint32_t* h_words = (uint32_t*)((char*)b.h_counters + 256 * kRing);  // adaptive list size
+    (void)h_ring;
+    for(int k = 0; k < kRing; k++)if(!b.wave_events[k] && !cuda_ok(cudaEventCreateWithFlags((cudaEvent_t*)&b.wave_events[k], cudaEventDisableTiming), "cudaEventCreate"))return PT_ERR_CUDA;
+    cudaEvent_t e0 = nullptr, e1 = nullptr;
+    if(!cuda_ok(cudaEventCreate(&e0), "cudaEventCreate"))return PT_ERR_CUDA;
+    if(!cuda_ok(cudaEventCreate(&e1), "cudaEventCreate")){ cudaEventDestroy(e0); return PT_ERR_CUDA; }
     auto fail = [&](int code){ cudaEventDestroy(e0); cudaEventDestroy(e1); return code; };
+    cudaEventRecord(e0, st);
+    pt_render_stats R {};
+    const unsigned long long overflow0 = s->overflow_seen;   // traversal-stack overflows are counted per scene; this call fails if the count moves
+
+    // persistent grids: every kernel of the loop reads its batch size from WaveCtl
+    int sms = 148;
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, s->device);
+    const unsigned g_shade = (unsigned)sms * PTB_SHADE_MINB, g_256 = (unsigned)sms * 8, g_tr = (unsigned)sms * 8;
 
     // one set of `count` camera samples through the wavefront.  The slot pool stays full: the slots whose
     // paths ended in a shade pass are splatted and handed to the next camera samples straight away, so the
@@ -764,89 +889,95 @@ int render_passes(pt_scene* s, const pt_camera_desc* cam, const pt_render_params
     // PTB_SORT=0 / 1 forces it, PTB_SORT_MIN sets the smallest queue worth sorting.
     static const int sort_env = []{ const char* e = getenv("PTB_SORT"); return e ? (atoi(e) != 0 ? 1 : 0) : -1; }();
     const bool sort_shade = sort_env >= 0 ? sort_env == 1 : rp->integrator == PT_INTEGRATOR_VOLPATH;
-    static const uint32_t sort_min = []{ const char* e = getenv("PTB_SORT_MIN"); return e ? (uint32_t)atoll(e) : 65536u; }();
+    static const uint32_t sort_min_env = []{ const char* e = getenv("PTB_SORT_MIN"); return e ? (uint32_t)atoll(e) : 65536u; }();
+    const uint32_t sort_min = sort_shade ? sort_min_env : 0xFFFFFFFFu;      // the kernels compare the device-side queue size with it
+    // how many bounces the host may enqueue beyond the last queue size it has seen (PTB_LOOKAHEAD)
+    static const int lookahead = []{ const char* e = getenv("PTB_LOOKAHEAD"); const int v = e ? atoi(e) : 2; return v < 1 ? 1 : (v > kRing - 2 ? kRing - 2 : v); }();
     StageLog log; log.on = getenv("PTB_PROFILE") != nullptr; log.st = st;
     log.mark(0);
     const auto t_host0 = std::chrono::steady_clock::now();
+    bool first_run = true;
+    auto launch_ok = [&](const char* what){ return cuda_ok(cudaGetLastError(), what); };
     auto run = [&](uint64_t count, const uint32_t* list, uint32_t n_list, uint32_t sample_base) -> int {
         BatchInfo B;
         B.W = W; B.H = H; B.pass_begin = rp->pass_begin; B.pass_stride = rp->pass_stride; B.max_depth = rp->max_depth; B.seed = rp->seed;
         B.sampler = rp->sampler; B.sx = rp->strata_x; B.sy = rp->strata_y;
         B.list = list; B.n_list = n_list; B.sample_base = sample_base;
         B.tr_walk = tr_walk ? 1 : 0;
-        uint64_t next_gid = 0;
         if(count == 0)return PT_OK;                   // more ranks than samples per round
         // a run that fits the pool never regenerates a slot: queue order stays slot order -> planes; else records
         if(count <= cap){ A.ps_slot = 1; A.ps_quarter = (uint32_t)cap; } else{ A.ps_slot = 4; A.ps_quarter = 1; }
+        double* est_now = est_round ? est_round : est;
         if(rp->max_depth <= 0){
             // `depth++ < maxDepth` fails at once: black samples that still carry their filter weight
-            while(next_gid < count){
-                const uint32_t m = (uint32_t)std::min<uint64_t>(cap, count - next_gid);
-                k_generate<<<(m + 255) / 256, 256, 0, st>>>(A, B, C, m, next_gid, nullptr, 0, 0);
-                k_film<<<(m + 255) / 256, 256, 0, st>>>(A, B, F, (double*)b.film, (double*)b.film_sq, est_round ? est_round : est, nullptr, m);
-                R.kernel_launches += 2; R.samples += m; next_gid += m;
-            }
-            return PT_OK;
-        }
-        uint32_t n = (uint32_t)std::min<uint64_t>(cap, count);
-        int cur = 0;
-        k_generate<<<(n + 255) / 256, 256, 0, st>>>(A, B, C, n, 0, nullptr, 0, cur);
-        R.kernel_launches++; R.samples += n; next_gid = n;
-        log.mark(1);
-        while(n > 0){
-            int rc = launch_trace_closest(s, A.rays[cur], n, A.hits, A.hinst, st);
-            if(rc != PT_OK)return rc;
-            R.closest_rays += n; R.kernel_launches++;
-            log.mark(2);
-            if(!cuda_ok(cudaMemsetAsync(A.counters, 0, 12, st), "counter reset"))return PT_ERR_CUDA;
-            const unsigned grid = (n + 127) / 128;
-            const uint32_t* perm = nullptr;
-            if(sort_shade && n >= sort_min){
-                const uint32_t nb = (n + kSortBlock - 1) / kSortBlock;
-                k_sort_count<<<nb, kSortBlock, 0, st>>>(A, s->shade, n, nb);
-                k_sort_scan<<<1, 1024, 0, st>>>(A.shist, nb * kSortKeys);
-                k_sort_scatter<<<nb, kSortBlock, 0, st>>>(A, n, nb);
+            for(uint64_t gid = 0; gid < count; gid += cap){
+                k_wave_init<<<1, 1, 0, st>>>(A, gid, count, cap, first_run ? 1 : 0);
+                first_run = false;
+                k_generate<<<g_256, 256, 0, st>>>(A, B, C);
+                k_finish<<<g_256, 256, 0, st>>>(A, B, F, C, (double*)b.film, (double*)b.film_sq, est_now, 1);
                 R.kernel_launches += 3;
-                perm = A.perm;
+            }
+            return launch_ok("black frame") ? PT_OK : PT_ERR_CUDA;
+        }
+        k_wave_init<<<1, 1, 0, st>>>(A, 0, count, cap, first_run ? 1 : 0);
+        first_run = false;
+        k_generate<<<g_256, 256, 0, st>>>(A, B, C);
+        R.kernel_launches += 2;
+        log.mark(1);
+        DynBatch dq; dq.n_dev = &A.ctl->n_cur; dq.sel_dev = &A.ctl->cur; dq.sel_stride = (size_t)(A.rays[1] - A.rays[0]);
+        DynBatch ds; ds.n_dev = &A.ctl->n_sh;
+        ConnectAcc acc; acc.slot = A.sslot; acc.contrib = A.scontrib; acc.ps = A.ps; acc.ps_slot = A.ps_slot; acc.ps_off = A.ps_quarter;
+        // A batch that fits the pool ends after max_depth bounces at the latest and that is all the host needs to know
+        // when the depth is small; otherwise the host watches n_cur `lookahead` bounces late and stops once it reads 0.
+        const bool blind = count <= cap && rp->max_depth <= 12;
+        for(unsigned it = 0;; it++){
+            if(blind && it >= (unsigned)rp->max_depth)break;
+            int rc = launch_trace_closest_dyn(s, A.rays[0], dq, A.hits, A.hinst, &A.ctl->cursor[0], st);
+            if(rc != PT_OK)return rc;
+            R.kernel_launches++;
+            log.mark(2);
+            if(sort_shade){
+                k_sort_count<<<kSortGrid, kSortBlock, 0, st>>>(A, s->shade, sort_min);
+                k_sort_scan<<<1, 1024, 0, st>>>(A, sort_min);
+                k_sort_scatter<<<kSortGrid, kSortBlock, 0, st>>>(A, sort_min);
+                R.kernel_launches += 3;
             }
             switch(rp->integrator){
-            case PT_INTEGRATOR_SIMPLE: k_shade<PT_INTEGRATOR_SIMPLE><<<grid, 128, 0, st>>>(A, s->shade, B, n, cur, perm); break;
-            case PT_INTEGRATOR_PATH: k_shade<PT_INTEGRATOR_PATH><<<grid, 128, 0, st>>>(A, s->shade, B, n, cur, perm); break;
-            default: k_shade<PT_INTEGRATOR_VOLPATH><<<grid, 128, 0, st>>>(A, s->shade, B, n, cur, perm); break;
+            case PT_INTEGRATOR_SIMPLE: k_shade<PT_INTEGRATOR_SIMPLE><<<g_shade, 128, 0, st>>>(A, s->shade, B, sort_min); break;
+            case PT_INTEGRATOR_PATH: k_shade<PT_INTEGRATOR_PATH><<<g_shade, 128, 0, st>>>(A, s->shade, B, sort_min); break;
+            default: k_shade<PT_INTEGRATOR_VOLPATH><<<g_shade, 128, 0, st>>>(A, s->shade, B, sort_min); break;
             }
             R.kernel_launches++;
             log.mark(3);
-            const auto tw0 = std::chrono::steady_clock::now();
-            if(!cuda_ok(cudaMemcpyAsync(h_counters, A.counters, 12, cudaMemcpyDeviceToHost, st), "counters D2H") ||
-               !cuda_ok(cudaStreamSynchronize(st), "shade"))return PT_ERR_CUDA;
-            host_wait_s += std::chrono::duration<double>(std::chrono::steady_clock::now() - tw0).count();
+            if(rp->integrator != PT_INTEGRATOR_SIMPLE){
+                if(tr_walk){
+                    if(s->has_alpha_tex || s->has_wrappers)launch_shadow_tr(A, s, g_tr, st, AlphaTex { s->shade, s->alpha_salt += 0x9E3779B97F4A7C15ull });
+                    else launch_shadow_tr(A, s, g_tr, st, NoAlpha());
+                    R.kernel_launches++;
+                } else{
+                    rc = launch_trace_any_dyn(s, A.srays, ds, nullptr, acc, &A.ctl->cursor[1], st);
+                    if(rc != PT_OK)return rc;
+                    R.kernel_launches++;
+                }
+                log.mark(5);
+            }
+            // after the shadow rays: a path may end in the very pass that queued its last one
+            k_finish<<<g_256, 256, 0, st>>>(A, B, F, C, (double*)b.film, (double*)b.film_sq, est_now, 0);
+            R.kernel_launches++;
+            log.mark(6);
+            if(!launch_ok("wavefront bounce"))return PT_ERR_CUDA;
             iterations++;
-            log.mark(4);
-            const uint32_t n_next = h_counters[0], n_sh = h_counters[1], n_done = h_counters[2];
-            if(n_sh > 0 && tr_walk){
-                if(s->has_alpha_tex || s->has_wrappers)launch_shadow_tr(A, s, n_sh, st, AlphaTex { s->shade, s->alpha_salt += 0x9E3779B97F4A7C15ull });
-                else launch_shadow_tr(A, s, n_sh, st, NoAlpha());
-                R.shadow_rays += n_sh; R.kernel_launches++;
-                log.mark(5);
-            } else if(n_sh > 0){
-                rc = launch_trace_any(s, A.srays, n_sh, A.socc, st);
-                if(rc != PT_OK)return rc;
-                k_connect<<<(n_sh + 255) / 256, 256, 0, st>>>(A, n_sh);
-                R.shadow_rays += n_sh; R.kernel_launches += 2;
-                log.mark(5);
-            }
-            if(n_done > 0){
-                // after k_connect: a path may end in the very pass that queued its last shadow ray
-                k_film<<<(n_done + 255) / 256, 256, 0, st>>>(A, B, F, (double*)b.film, (double*)b.film_sq, est_round ? est_round : est, A.done, n_done);
-                R.kernel_launches++;
-                log.mark(6);
-            }
-            n = n_next; cur ^= 1;
-            if(n_done > 0 && next_gid < count){
-                const uint32_t m = (uint32_t)std::min<uint64_t>(n_done, count - next_gid);
-                k_generate<<<(m + 255) / 256, 256, 0, st>>>(A, B, C, m, next_gid, A.done, n, cur);
-                R.kernel_launches++; R.samples += m; next_gid += m; n += m;
-                log.mark(1);
+            if(blind)continue;
+            // watch slot of this bounce: WaveCtl as k_finish left it, and an event behind the copy
+            const int k = (int)(it % kRing);
+            if(!cuda_ok(cudaMemcpyAsync(h_slot(k), A.ctl, sizeof(WaveCtl), cudaMemcpyDeviceToHost, st), "WaveCtl D2H") ||
+               !cuda_ok(cudaEventRecord((cudaEvent_t)b.wave_events[k], st), "event"))return PT_ERR_CUDA;
+            if(it >= (unsigned)lookahead){
+                const int w = (int)((it - lookahead) % kRing);
+                const auto tw0 = std::chrono::steady_clock::now();
+                if(!cuda_ok(cudaEventSynchronize((cudaEvent_t)b.wave_events[w]), "wavefront watch"))return PT_ERR_CUDA;
+                host_wait_s += std::chrono::duration<double>(std::chrono::steady_clock::now() - tw0).count();
+                if(h_slot(w)->n_cur == 0)break;       // the queue ran dry `lookahead` bounces ago: what was enqueued since found nothing to do
             }
         }
         return PT_OK;
@@ -874,27 +1005,36 @@ int render_passes(pt_scene* s, const pt_camera_desc* cam, const pt_render_params
             if(rc != PT_OK)return fail(rc);
             k_adapt<<<(n_in + 255) / 256, 256, 0, st>>>(est, in, n_in, out, list_n, (double)round * rp->spp);
             R.kernel_launches++;
-            if(!cuda_ok(cudaMemcpyAsync(h_counters + 8, list_n, 4, cudaMemcpyDeviceToHost, st), "list size D2H") ||
+            if(!cuda_ok(cudaMemcpyAsync(h_words, list_n, 4, cudaMemcpyDeviceToHost, st), "list size D2H") ||
                !cuda_ok(cudaStreamSynchronize(st), "adapt"))return fail(PT_ERR_CUDA);
-            n_in = h_counters[8]; in = out;
+            n_in = h_words[0]; in = out;
             if(n_in == 0)break;
             rc = run((uint64_t)n_in * n_pass, in, n_in, (uint32_t)round * (uint32_t)rp->spp);
             if(rc != PT_OK)return fail(rc);
         }
     }
     cudaEventRecord(e1, st);
-    if(!cuda_ok(cudaMemcpyAsync(h_counters + 12, A.counters + 3, 4, cudaMemcpyDeviceToHost, st), "counters D2H"))return fail(PT_ERR_CUDA);
+    if(!cuda_ok(cudaMemcpyAsync(h_slot(kRing - 1), A.ctl, sizeof(WaveCtl), cudaMemcpyDeviceToHost, st), "WaveCtl D2H") ||
+       !cuda_ok(cudaMemcpyAsync(h_words + 8, (unsigned long long*)b.stats + 8, 8, cudaMemcpyDeviceToHost, st), "overflow counter"))return fail(PT_ERR_CUDA);
     if(!cuda_ok(cudaStreamSynchronize(st), "render"))return fail(PT_ERR_CUDA);
-    R.nonfinite_samples = h_counters[12];
+    const WaveCtl& end = *h_slot(kRing - 1);
+    R.nonfinite_samples = end.nonfinite;
+    R.samples = end.samples; R.closest_rays = end.closest_rays; R.shadow_rays = end.shadow_rays;
     float ms = 0; cudaEventElapsedTime(&ms, e0, e1);
     R.gpu_ms = ms;
     if(getenv("PTB_PROFILE")){
         const double host_s = std::chrono::duration<double>(std::chrono::steady_clock::now() - t_host0).count();
         log.report();
-        fprintf(stderr, "[ptb] render: %.3f ms on the stream, host %.3f ms of which %.3f ms waiting for counters, %u iterations, %llu launches\n",
-                ms, host_s * 1e3, host_wait_s * 1e3, iterations, (unsigned long long)R.kernel_launches);
+        fprintf(stderr, "[ptb] render: %.3f ms on the stream, host %.3f ms of which %.3f ms waiting for the watch slots, %u bounces enqueued (%llu ran), %llu launches\n",
+                ms, host_s * 1e3, host_wait_s * 1e3, iterations, (unsigned long long)end.bounces, (unsigned long long)R.kernel_launches);
     }
     if(stats)*stats = R;
+    s->overflow_seen = *(unsigned long long*)(h_words + 8);
+    if(s->overflow_seen != overflow0){
+        set_error("traversal stack overflow: " + std::to_string(*(unsigned long long*)(h_words + 8) - overflow0) + " rays needed more than " + std::to_string(kStack) +
+                  " stack entries; their hits may be wrong");
+        return fail(PT_ERR_OVERFLOW);
+    }
     return fail(PT_OK);
 }
 

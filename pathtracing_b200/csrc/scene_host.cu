@@ -18,13 +18,33 @@ bool cuda_ok(int err, const char* what){
     return false;
 }
 
+void note_upload(pt_scene* s, void** slot, size_t bytes){
+    s->uploads.push_back({ (size_t)((char*)slot - (char*)&s->buf), bytes });
+}
+
+void bind_device_pointers(pt_scene* s){
+    const DeviceBuffers& b = s->buf;
+    s->dev.n2 = (const Bvh2Node*)b.n2; s->dev.n4 = (const Bvh4Node*)b.n4; s->dev.n8 = (const Bvh8Node*)b.n8;
+    s->dev.tris = (const Tri*)b.tris; s->dev.inst = (const Instance*)b.inst;
+    s->dev.n4q = (const Bvh4QNode*)b.n4q; s->dev.tris64 = (const Tri64*)b.tris64;
+    ShadeScene& D = s->shade;
+    D.meshes = (const DevMesh*)b.meshes; D.blas = (const DevBlasInfo*)b.blas_info; D.inst = (const DevInstShade*)b.inst_shade;
+    D.pos = (const float*)b.vtx_pos; D.nrm = (const float*)b.vtx_nrm; D.uv = (const float*)b.vtx_uv; D.tan = (const float*)b.vtx_tan;
+    D.idx = (const uint32_t*)b.indices; D.tri_mesh = (const uint32_t*)b.tri_mesh; D.tri_emis = (const int32_t*)b.tri_light;
+    D.textures = (const DevTexture*)b.textures; D.texels = (const uint8_t*)b.texels;
+    D.materials = (const DevMaterial*)b.materials; D.media = (const DevMedium*)b.media;
+    D.lights = (const DevLight*)b.lights; D.sampler_lights = (const int32_t*)b.sampler_lights; D.sampler_cdf = (const float*)b.light_cdf;
+    D.inf_lights = (const int32_t*)b.inf_lights; D.env_cdf = (const float*)b.env_cdf;
+}
+
 template <class T>
-static bool upload(void** dst, const std::vector<T>& v, const char* what){
+static bool upload(pt_scene* s, void** dst, const std::vector<T>& v, const char* what){
     *dst = nullptr;
     size_t bytes = v.size() * sizeof(T);
     if(bytes == 0)bytes = 16;   // keep pointers valid
     if(!cuda_ok(cudaMalloc(dst, bytes), what))return false;
     if(!v.empty() && !cuda_ok(cudaMemcpy(*dst, v.data(), v.size() * sizeof(T), cudaMemcpyHostToDevice), what))return false;
+    note_upload(s, dst, bytes);
     return true;
 }
 
@@ -32,11 +52,12 @@ int build_shade_tables(pt_scene* s, const std::vector<uint32_t>& inst_order);   
 
 void scene_free_device(pt_scene* s){
     DeviceBuffers& b = s->buf;
-    void** ptrs[] = { &b.n2, &b.n4, &b.n8, &b.tris, &b.inst, &b.meshes, &b.blas_info, &b.inst_shade, &b.vtx_pos, &b.vtx_nrm, &b.vtx_uv, &b.vtx_tan,
+    void** ptrs[] = { &b.n2, &b.n4, &b.n8, &b.tris, &b.inst, &b.n4q, &b.tris64, &b.meshes, &b.blas_info, &b.inst_shade, &b.vtx_pos, &b.vtx_nrm, &b.vtx_uv, &b.vtx_tan,
         &b.indices, &b.tri_light, &b.textures, &b.texels, &b.materials, &b.media, &b.lights, &b.light_cdf, &b.env_cdf, &b.film, &b.work, &b.adapt,
         &b.stage_rays, &b.stage_hits, &b.stage_inst, &b.stage_occ, &b.stats, &b.tri_mesh, &b.inst_light_base, &b.sampler_lights, &b.inf_lights, &b.cursors, &b.film_sq, &b.stream_aux };
     for(void** p : ptrs){ if(*p){ cudaFree(*p); *p = nullptr; } }
     if(b.h_counters){ cudaFreeHost(b.h_counters); b.h_counters = nullptr; }
+    for(void*& e : b.wave_events)if(e){ cudaEventDestroy((cudaEvent_t)e); e = nullptr; }
     if(b.h_stream){ cudaFreeHost(b.h_stream); b.h_stream = nullptr; }
     b.work_bytes = 0; b.adapt_bytes = 0; b.stage_cap = 0; b.stream_aux_bytes = 0; b.h_stream_bytes = 0;
 }
@@ -68,13 +89,22 @@ int scene_commit(pt_scene* s, int width, int light_sampler){
 
     // ---- upload ---------------------------------------------------------------------
     DeviceBuffers& b = s->buf;
-    if(!upload(&b.n2, n2, "upload bvh2 nodes") || !upload(&b.n4, n4, "upload bvh4 clusters") || !upload(&b.n8, P.n8, "upload bvh8 clusters") ||
-       !upload(&b.tris, tris, "upload triangles") || !upload(&b.inst, insts, "upload instances")){
+    s->uploads.clear();
+    if(!upload(s, &b.n2, n2, "upload bvh2 nodes") || !upload(s, &b.n4, n4, "upload bvh4 clusters") || !upload(s, &b.n8, P.n8, "upload bvh8 clusters") ||
+       !upload(s, &b.tris, tris, "upload triangles") || !upload(s, &b.inst, insts, "upload instances")){
         scene_free_device(s);
         return PT_ERR_CUDA;
     }
-    s->dev.n2 = (const Bvh2Node*)b.n2; s->dev.n4 = (const Bvh4Node*)b.n4; s->dev.n8 = (const Bvh8Node*)b.n8;
-    s->dev.tris = (const Tri*)b.tris; s->dev.inst = (const Instance*)b.inst;
+    s->dev.fast = 0;
+    if(s->layout == PT_LAYOUT_FAST){
+        if(width != 4){ set_error("PT_LAYOUT_FAST needs bvh_width 4"); scene_free_device(s); return PT_ERR_INVALID; }
+        std::vector<Bvh4QNode> n4q;
+        encode_bvh4q(n4, n4q);
+        std::vector<Tri64> t64(tris.size());
+        for(size_t i = 0; i < tris.size(); i++){ t64[i].t = tris[i]; t64[i].pad[0] = t64[i].pad[1] = t64[i].pad[2] = t64[i].pad[3] = 0u; }
+        if(!upload(s, &b.n4q, n4q, "upload quantised bvh4 clusters") || !upload(s, &b.tris64, t64, "upload padded triangles")){ scene_free_device(s); return PT_ERR_CUDA; }
+        s->dev.fast = 1;
+    }
     s->dev.tlas_root = P.tlas_root;
     s->dev.width = width;
     s->dev.single_root = P.single_root; s->dev.single_id = P.single_id;
@@ -85,6 +115,7 @@ int scene_commit(pt_scene* s, int width, int light_sampler){
     const auto t2 = std::chrono::steady_clock::now();
     int rc = build_shade_tables(s, P.inst_order);
     if(rc != PT_OK){ scene_free_device(s); return rc; }
+    bind_device_pointers(s);
 
     cudaStream_t st, st2, st3, st4;
     if(!cuda_ok(cudaStreamCreateWithFlags(&st, cudaStreamNonBlocking), "cudaStreamCreate") ||
@@ -92,7 +123,7 @@ int scene_commit(pt_scene* s, int width, int light_sampler){
        !cuda_ok(cudaStreamCreateWithFlags(&st3, cudaStreamNonBlocking), "cudaStreamCreate") ||
        !cuda_ok(cudaStreamCreateWithFlags(&st4, cudaStreamNonBlocking), "cudaStreamCreate")){ scene_free_device(s); return PT_ERR_CUDA; }
     s->stream = st; s->stream2 = st2; s->stream3 = st3; s->stream4 = st4;
-    if(!cuda_ok(cudaMalloc(&b.stats, 64), "cudaMalloc stats") ||
+    if(!cuda_ok(cudaMalloc(&b.stats, 256), "cudaMalloc stats") || !cuda_ok(cudaMemset(b.stats, 0, 256), "stats clear") ||
        !cuda_ok(cudaMalloc(&b.cursors, kCursorRing * sizeof(unsigned long long)), "cudaMalloc cursors")){ scene_free_device(s); return PT_ERR_CUDA; }
     // the tables went up as pageable cudaMemcpy on the legacy stream; the non-blocking streams created above do not
     // order against it: make everything land before the first kernel can read it

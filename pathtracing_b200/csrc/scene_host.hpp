@@ -48,6 +48,7 @@ struct HostInstance {        // one top-level primitive (Scene::Add order)
 
 struct DeviceBuffers {
     void* n2 = nullptr; void* n4 = nullptr; void* n8 = nullptr; void* tris = nullptr; void* inst = nullptr;
+    void* n4q = nullptr; void* tris64 = nullptr;      // PT_LAYOUT_FAST
     // shading tables
     void* meshes = nullptr; void* blas_info = nullptr; void* inst_shade = nullptr;
     void* vtx_pos = nullptr; void* vtx_nrm = nullptr; void* vtx_uv = nullptr; void* vtx_tan = nullptr; void* indices = nullptr;
@@ -58,7 +59,8 @@ struct DeviceBuffers {
     void* film_sq = nullptr;      // per-pixel sum of squared sample radiance, double[3*W*H]
     void* work = nullptr;         // wavefront state arena
     size_t work_bytes = 0;
-    void* h_counters = nullptr;   // pinned host words the wavefront loop reads queue sizes into
+    void* h_counters = nullptr;   // pinned host memory: the watch slots of the wavefront loop (copies of its device control block)
+    void* wave_events[8] = {};    // one event per watch slot
     void* adapt = nullptr;        // adaptive loop: per-pixel estimator sums + pixel lists
     size_t adapt_bytes = 0;
     // staging for the host-buffer ray-cast entry points
@@ -114,9 +116,19 @@ struct pt_scene {
     bool has_alpha_tex = false;   // some triangle carries TRI_ALPHA_TEX: traversal must evaluate Material::Alpha
     bool has_boundary = false;    // some primitive has no material (a medium boundary): VolPath shadow rays walk through it
     uint64_t alpha_salt = 0;      // advances per launch (AlphaTester Blend draws)
+    unsigned long long overflow_seen = 0;  // device overflow counter (buf.stats + 64) as the last checked call left it
     pt_allreduce_fn allreduce = nullptr;   // sums a device buffer over the ranks that shard this scene's sample passes
     void* allreduce_user = nullptr;
     int builder = 0;              // pt_builder: where the binary SAH build runs
+    bool counting = false;        // pt_scene_set_counting: pt_render launches the counting build of the traversal kernels
+    int layout = 0;               // pt_layout: exact 128 B clusters, or the quantised 64 B ones (width 4)
+    // every device table of the committed scene as (byte offset of its pointer inside `buf`, bytes): what
+    // pt_scene_replicate copies to another GPU (multi.cu) without running the build again
+    std::vector<std::pair<size_t, size_t>> uploads;
+    // multi-GPU (multi.cu): this scene's rank in the communicator that shards its sample passes
+    void* comm = nullptr;         // ncclComm_t, or null
+    int comm_rank = 0, comm_world = 1;
+    bool comm_owned = false;      // created by pt_dist_init (destroyed with the scene / pt_dist_finalize)
     pt_build_stats build_stats {};
 };
 
@@ -148,6 +160,22 @@ struct StreamCtl {
     unsigned* abort = nullptr;                    // raised by the kernel when a wait timed out, or by the host
     unsigned shift = 18;
 };
+// A launch whose batch size and queue are decided on the device (the wavefront loop of render.cu): n = *n_dev rays,
+// read from rays + *sel_dev * sel_stride (float4 units).  All null / zero: the host-side arguments are used.
+struct DynBatch {
+    const uint32_t* n_dev = nullptr;
+    const uint32_t* sel_dev = nullptr;
+    size_t sel_stride = 0;
+};
+// Any-hit launches of the wavefront loop: a shadow ray that turns out unoccluded adds its contribution to its path's
+// radiance when it retires (the k_connect pass of round 1, fused into the kernel that produces the answer).
+// A slot has at most one shadow ray per bounce, so the read-modify-write needs no atomics.
+struct ConnectAcc {
+    const uint32_t* slot = nullptr;     // per shadow ray: the path slot
+    const void* contrib = nullptr;      // per shadow ray: rgb contribution (float4)
+    void* ps = nullptr;                 // path state (float4 units); radiance of slot i at ps[i * ps_slot + ps_off]
+    uint32_t ps_slot = 0, ps_off = 0;
+};
 bool probe_async_launch(pt_scene* sc, void* d_words, void* compute_stream, void* copy_stream);
 int launch_trace_streamed(pt_scene* sc, bool any, const void* d_rays, size_t n, void* d_hits, void* d_inst, void* d_occ, const StreamCtl& ctl, void* stream);
 
@@ -156,6 +184,8 @@ int scene_animate(pt_scene* s, int prim_id, const float* dir, const float* tb);
 int scene_add_light(pt_scene* s, const pt_light_desc* d);
 // builder: binary build used for every BLAS and the TLAS (null = build_binary_bvh on the host); returns PT_OK or an error
 using BvhBuilder = int (*)(const Box* boxes, uint32_t n, BinaryBvh& out, void* user);
+// PT_LAYOUT_FAST: quantised copy of the BVH4 clusters (pt_types.h Bvh4QNode); every decoded box contains the exact one
+void encode_bvh4q(const std::vector<Bvh4Node>& n4, std::vector<Bvh4QNode>& out);
 int pack_traversal(pt_scene* s, int width, PackedTraversal& out, BvhBuilder builder = nullptr, void* user = nullptr);
 int build_binary_bvh_gpu(const Box* boxes, uint32_t n, uint32_t leaf_size, BinaryBvh& out, GpuBuildTimes* times);   // bvh_build_gpu.cu
 // BinaryBvh with nodes renumbered in DFS preorder (left subtree first), the host builder's own numbering
@@ -167,12 +197,20 @@ const char* get_error();
 bool cuda_ok(int err, const char* what);     // records the message on failure
 
 int scene_commit(pt_scene* s, int width, int light_sampler);
+void note_upload(pt_scene* s, void** slot, size_t bytes);     // slot points into s->buf
+void bind_device_pointers(pt_scene* s);                      // s->dev / s->shade pointer fields from s->buf
+int scene_replicate(pt_scene* src, int device, pt_scene** out);   // multi.cu
 void scene_free_device(pt_scene* s);
 
 // trace.cu
 int launch_trace_closest(pt_scene* s, const void* d_rays, size_t n, void* d_hits, void* d_inst, void* stream);
 int launch_trace_any(pt_scene* s, const void* d_rays, size_t n, void* d_occ, void* stream);
 int launch_trace_stats(pt_scene* s, const void* d_rays, size_t n, void* d_counters /* 6 x u64 */, void* stream);
+// wavefront form: full persistent grid, batch described on the device, the caller owns (and clears) the cursor
+int launch_trace_closest_dyn(pt_scene* s, const void* d_rays, const DynBatch& dyn, void* d_hits, void* d_inst, unsigned long long* cursor, void* stream);
+int launch_trace_any_dyn(pt_scene* s, const void* d_rays, const DynBatch& dyn, void* d_occ, const ConnectAcc& acc, unsigned long long* cursor, void* stream);
+// traversal-stack overflows counted on this scene's device since commit (synchronises the device)
+int scene_overflow_count(pt_scene* s, unsigned long long* out);
 
 // render.cu
 int render_passes(pt_scene* s, const pt_camera_desc* cam, const pt_render_params* rp, int clear, pt_render_stats* stats);

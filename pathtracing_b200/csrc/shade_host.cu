@@ -8,6 +8,8 @@ namespace ptb {
 
 namespace {
 
+thread_local pt_scene* g_scene = nullptr;      // the scene build_shade_tables is uploading for (commit is not re-entrant)
+
 template <class T>
 bool up(void** dst, const std::vector<T>& v, const char* what){
     *dst = nullptr;
@@ -15,6 +17,7 @@ bool up(void** dst, const std::vector<T>& v, const char* what){
     if(bytes == 0)bytes = 16;
     if(!cuda_ok(cudaMalloc(dst, bytes), what))return false;
     if(!v.empty() && !cuda_ok(cudaMemcpy(*dst, v.data(), v.size() * sizeof(T), cudaMemcpyHostToDevice), what))return false;
+    note_upload(g_scene, dst, bytes);
     return true;
 }
 
@@ -25,6 +28,7 @@ int build_shade_tables(pt_scene* s, const std::vector<uint32_t>& inst_order){
     int rc = build_shade_tables_host(s, inst_order, T);
     if(rc != PT_OK)return rc;
     DeviceBuffers& b = s->buf;
+    g_scene = s;
     if(!up(&b.meshes, T.meshes, "meshes") || !up(&b.blas_info, T.blas, "blas info") || !up(&b.inst_shade, T.inst, "instances") ||
        !up(&b.vtx_pos, T.pos, "positions") || !up(&b.vtx_nrm, T.nrm, "normals") || !up(&b.vtx_uv, T.uv, "texcoords") ||
        !up(&b.vtx_tan, T.tan, "tangents") || !up(&b.indices, T.idx, "indices") || !up(&b.tri_mesh, T.tri_mesh, "tri_mesh") ||
@@ -32,14 +36,7 @@ int build_shade_tables(pt_scene* s, const std::vector<uint32_t>& inst_order){
        !up(&b.materials, T.materials, "materials") || !up(&b.media, T.media, "media") || !up(&b.lights, T.lights, "lights") ||
        !up(&b.sampler_lights, T.sampler_lights, "sampler lights") || !up(&b.light_cdf, T.sampler_cdf, "light cdf") ||
        !up(&b.inf_lights, T.inf_lights, "infinite lights") || !up(&b.env_cdf, T.env_cdf, "env cdf"))return PT_ERR_CUDA;
-    ShadeScene& D = s->shade;
-    D.meshes = (const DevMesh*)b.meshes; D.blas = (const DevBlasInfo*)b.blas_info; D.inst = (const DevInstShade*)b.inst_shade;
-    D.pos = (const float*)b.vtx_pos; D.nrm = (const float*)b.vtx_nrm; D.uv = (const float*)b.vtx_uv; D.tan = (const float*)b.vtx_tan;
-    D.idx = (const uint32_t*)b.indices; D.tri_mesh = (const uint32_t*)b.tri_mesh; D.tri_emis = (const int32_t*)b.tri_light;
-    D.textures = (const DevTexture*)b.textures; D.texels = (const uint8_t*)b.texels;
-    D.materials = (const DevMaterial*)b.materials; D.media = (const DevMedium*)b.media;
-    D.lights = (const DevLight*)b.lights; D.sampler_lights = (const int32_t*)b.sampler_lights; D.sampler_cdf = (const float*)b.light_cdf;
-    D.inf_lights = (const int32_t*)b.inf_lights; D.env_cdf = (const float*)b.env_cdf;
+    ShadeScene& D = s->shade;      // pointer fields: bind_device_pointers (scene_host.cu)
     D.n_lights = (int32_t)T.lights.size(); D.n_sampler_lights = (int32_t)T.sampler_lights.size(); D.n_inf_lights = (int32_t)T.inf_lights.size();
     D.sampler_kind = T.view.sampler_kind; D.total_power = T.view.total_power;
     D.scene_medium = T.view.scene_medium;

@@ -71,7 +71,14 @@ template <int WIDTH, bool ANY, bool STATS, int KS, class Alpha, bool FEED = fals
 __global__ void __launch_bounds__(kTraceBlock) k_trace(DevScene S, const float4* __restrict__ rays, size_t n,
                                                        float4* __restrict__ hits, uint32_t* __restrict__ inst, uint8_t* __restrict__ occ,
                                                        unsigned long long* __restrict__ cursor, unsigned long long* __restrict__ stats,
-                                                       unsigned refill_min, const Alpha alpha, const StreamCtl ctl){
+                                                       unsigned refill_min, const Alpha alpha, const StreamCtl ctl, const DynBatch dyn,
+                                                       unsigned long long* __restrict__ overflow, const ConnectAcc acc){
+    if(dyn.n_dev){
+        // wavefront loop: the batch size and which of the two ray queues is current live on the device
+        n = *dyn.n_dev;
+        if(dyn.sel_dev)rays += (size_t)(*dyn.sel_dev) * dyn.sel_stride;
+        if(n == 0)return;
+    }
     extern __shared__ uint2 smem_stack[];            // KS rows of kTraceBlock entries
     uint2 spill[kStack - KS];
     TravStack<KS, KS ? kTraceBlock : 1> stack;
@@ -94,8 +101,18 @@ __global__ void __launch_bounds__(kTraceBlock) k_trace(DevScene S, const float4*
             if(s.flags & TF_DONE){
                 if(idx != (size_t)-1){
                     // retire the finished ray
-                    if(ANY)occ[idx] = (s.flags & TF_OCCLUDED) ? 1 : 0;
-                    else{
+                    if(s.flags & TF_OVERFLOW)atomicAdd(overflow, 1ull);      // never on any scene seen so far: 96 entries
+                    if(ANY){
+                        if(acc.ps){
+                            if(!(s.flags & TF_OCCLUDED)){
+                                float4* d = (float4*)acc.ps + ((size_t)acc.slot[idx] * acc.ps_slot + acc.ps_off);
+                                const float4 c = ((const float4*)acc.contrib)[idx];
+                                float4 r = *d;
+                                r.x += c.x; r.y += c.y; r.z += c.z;
+                                *d = r;
+                            }
+                        } else occ[idx] = (s.flags & TF_OCCLUDED) ? 1 : 0;
+                    } else{
                         const bool found = s.hprim != 0xFFFFFFFFu;
                         if(!STATS || hits)hits[idx] = make_float4(found ? s.tmax : CUDART_INF_F, s.hu, s.hv, __uint_as_float(s.hprim));
                         if(inst)inst[idx] = s.hinst;
@@ -172,6 +189,73 @@ static unsigned refill_min(){ static int v = env_int("PTB_REFILL_MIN", 4, 1, 32)
 // shared-memory stack rows per lane: 0 (all local), 8, 16 or 24
 static int stack_rows(){ static int v = env_int("PTB_STACK_SMEM", 16, 0, 24); return v; }
 
+// s->buf.stats: 8 x u64 of the counting build, then the scene's traversal-stack overflow counter
+static unsigned long long* overflow_counter(pt_scene* sc){ return (unsigned long long*)sc->buf.stats + 8; }
+
+int scene_overflow_count(pt_scene* s, unsigned long long* out){
+    if(!cuda_ok(cudaDeviceSynchronize(), "sync") ||
+       !cuda_ok(cudaMemcpy(out, overflow_counter(s), sizeof(unsigned long long), cudaMemcpyDeviceToHost), "D2H overflow counter"))return PT_ERR_CUDA;
+    return PT_OK;
+}
+
+// wavefront form of launch_ks (render.cu): always the full persistent grid (the batch size is only known on the
+// device), the cursor belongs to the caller, who clears it between launches
+template <int WIDTH, bool ANY, int KS, class Alpha>
+static int launch_dyn_ks(pt_scene* sc, const void* d_rays, const DynBatch& dyn, void* d_hits, void* d_inst, void* d_occ, const ConnectAcc& acc, unsigned long long* cursor, void* stream, const Alpha& alpha){
+    static int cache[8] = { 0, 0, 0, 0, 0, 0, 0, 0 };
+    cudaStream_t st = (cudaStream_t)stream;
+    auto kernel = k_trace<WIDTH, ANY, false, KS, Alpha>;
+    const size_t smem = (size_t)KS * kTraceBlock * sizeof(uint2);
+    const unsigned grid = persistent_grid(kernel, sc->device, smem, cache[sc->device & 7]);
+    kernel<<<grid, kTraceBlock, smem, st>>>(sc->dev, (const float4*)d_rays, 0, (float4*)d_hits, (uint32_t*)d_inst, (uint8_t*)d_occ,
+                                            cursor, nullptr, refill_min(), alpha, StreamCtl(), dyn, overflow_counter(sc), acc);
+    return check_launch("k_trace (wavefront)");
+}
+
+// counting build of the wavefront launches (pt_scene_set_counting): node / triangle / instance visits of a render's
+// closest-hit and shadow rays, for the per-sample algorithmic bytes of SURVEY.md section 8d.  BVH4 layouts only.
+template <int WIDTH, bool ANY, class Alpha>
+static int launch_dyn_count(pt_scene* sc, const void* d_rays, const DynBatch& dyn, void* d_hits, void* d_inst, void* d_occ, const ConnectAcc& acc, unsigned long long* cursor, void* stream, const Alpha& alpha){
+    static int cache[8] = { 0, 0, 0, 0, 0, 0, 0, 0 };
+    auto kernel = k_trace<WIDTH, ANY, true, 16, Alpha>;
+    const size_t smem = (size_t)16 * kTraceBlock * sizeof(uint2);
+    const unsigned grid = persistent_grid(kernel, sc->device, smem, cache[sc->device & 7]);
+    unsigned long long* stats = (unsigned long long*)sc->buf.stats + (ANY ? 24 : 16);
+    kernel<<<grid, kTraceBlock, smem, (cudaStream_t)stream>>>(sc->dev, (const float4*)d_rays, 0, (float4*)d_hits, (uint32_t*)d_inst, (uint8_t*)d_occ,
+                                                             cursor, stats, refill_min(), alpha, StreamCtl(), dyn, overflow_counter(sc), acc);
+    return check_launch("k_trace (wavefront, counting)");
+}
+
+template <int WIDTH, bool ANY>
+static int launch_dyn(pt_scene* sc, const void* d_rays, const DynBatch& dyn, void* d_hits, void* d_inst, void* d_occ, const ConnectAcc& acc, unsigned long long* cursor, void* stream){
+    if constexpr(WIDTH == 4 || WIDTH == kWidthFast4){
+        if(sc->counting){
+            if(sc->has_alpha_tex || sc->has_wrappers)
+                return launch_dyn_count<WIDTH, ANY>(sc, d_rays, dyn, d_hits, d_inst, d_occ, acc, cursor, stream, AlphaTex { sc->shade, sc->alpha_salt += 0x9E3779B97F4A7C15ull });
+            return launch_dyn_count<WIDTH, ANY>(sc, d_rays, dyn, d_hits, d_inst, d_occ, acc, cursor, stream, NoAlpha());
+        }
+    }
+    if(sc->has_alpha_tex || sc->has_wrappers){
+        const AlphaTex at = { sc->shade, sc->alpha_salt += 0x9E3779B97F4A7C15ull };
+        return launch_dyn_ks<WIDTH, ANY, 16>(sc, d_rays, dyn, d_hits, d_inst, d_occ, acc, cursor, stream, at);
+    }
+    return launch_dyn_ks<WIDTH, ANY, 16>(sc, d_rays, dyn, d_hits, d_inst, d_occ, acc, cursor, stream, NoAlpha());
+}
+
+int launch_trace_closest_dyn(pt_scene* sc, const void* d_rays, const DynBatch& dyn, void* d_hits, void* d_inst, unsigned long long* cursor, void* stream){
+    if(sc->dev.fast)return launch_dyn<kWidthFast4, false>(sc, d_rays, dyn, d_hits, d_inst, nullptr, ConnectAcc(), cursor, stream);
+    return sc->dev.width == 2 ? launch_dyn<2, false>(sc, d_rays, dyn, d_hits, d_inst, nullptr, ConnectAcc(), cursor, stream)
+         : sc->dev.width == 4 ? launch_dyn<4, false>(sc, d_rays, dyn, d_hits, d_inst, nullptr, ConnectAcc(), cursor, stream)
+                              : launch_dyn<8, false>(sc, d_rays, dyn, d_hits, d_inst, nullptr, ConnectAcc(), cursor, stream);
+}
+
+int launch_trace_any_dyn(pt_scene* sc, const void* d_rays, const DynBatch& dyn, void* d_occ, const ConnectAcc& acc, unsigned long long* cursor, void* stream){
+    if(sc->dev.fast)return launch_dyn<kWidthFast4, true>(sc, d_rays, dyn, nullptr, nullptr, d_occ, acc, cursor, stream);
+    return sc->dev.width == 2 ? launch_dyn<2, true>(sc, d_rays, dyn, nullptr, nullptr, d_occ, acc, cursor, stream)
+         : sc->dev.width == 4 ? launch_dyn<4, true>(sc, d_rays, dyn, nullptr, nullptr, d_occ, acc, cursor, stream)
+                              : launch_dyn<8, true>(sc, d_rays, dyn, nullptr, nullptr, d_occ, acc, cursor, stream);
+}
+
 template <int WIDTH, bool ANY, bool STATS, int KS, class Alpha>
 static int launch_ks(pt_scene* sc, const void* d_rays, size_t n, void* d_hits, void* d_inst, void* d_occ, void* d_stats, void* stream, const Alpha& alpha){
     static int cache[8] = { 0, 0, 0, 0, 0, 0, 0, 0 };   // per device ordinal (one process drives at most 8 GPUs)
@@ -185,7 +269,7 @@ static int launch_ks(pt_scene* sc, const void* d_rays, size_t n, void* d_hits, v
     unsigned long long* cursor = (unsigned long long*)sc->buf.cursors + (sc->cursor_next++ % kCursorRing);
     if(!cuda_ok(cudaMemsetAsync(cursor, 0, sizeof(unsigned long long), st), "cursor reset"))return PT_ERR_CUDA;
     kernel<<<grid, kTraceBlock, smem, st>>>(sc->dev, (const float4*)d_rays, n, (float4*)d_hits, (uint32_t*)d_inst, (uint8_t*)d_occ,
-                                            cursor, (unsigned long long*)d_stats, refill_min(), alpha, StreamCtl());
+                                            cursor, (unsigned long long*)d_stats, refill_min(), alpha, StreamCtl(), DynBatch(), overflow_counter(sc), ConnectAcc());
     return check_launch("k_trace");
 }
 
@@ -202,7 +286,7 @@ static int launch(pt_scene* sc, const void* d_rays, size_t n, void* d_hits, void
         return launch_ks<WIDTH, ANY, STATS, 0>(sc, d_rays, n, d_hits, d_inst, d_occ, d_stats, stream, at);
     }
     const NoAlpha na;
-    if constexpr(WIDTH == 8){
+    if constexpr(WIDTH == 8 || WIDTH == kWidthFast4){
         if(ks >= 16)return launch_ks<WIDTH, ANY, STATS, 16>(sc, d_rays, n, d_hits, d_inst, d_occ, d_stats, stream, na);
         return launch_ks<WIDTH, ANY, STATS, 0>(sc, d_rays, n, d_hits, d_inst, d_occ, d_stats, stream, na);
     }
@@ -226,7 +310,7 @@ static int launch_feed(pt_scene* sc, const void* d_rays, size_t n, void* d_hits,
     unsigned long long* cursor = (unsigned long long*)sc->buf.cursors + (sc->cursor_next++ % kCursorRing);
     if(!cuda_ok(cudaMemsetAsync(cursor, 0, sizeof(unsigned long long), st), "cursor reset"))return PT_ERR_CUDA;
     kernel<<<grid, kTraceBlock, smem, st>>>(sc->dev, (const float4*)d_rays, n, (float4*)d_hits, (uint32_t*)d_inst, (uint8_t*)d_occ,
-                                            cursor, nullptr, refill_min(), NoAlpha(), ctl);
+                                            cursor, nullptr, refill_min(), NoAlpha(), ctl, DynBatch(), overflow_counter(sc), ConnectAcc());
     return check_launch("k_trace (streamed)");
 }
 
@@ -257,6 +341,8 @@ bool probe_async_launch(pt_scene* sc, void* d_words, void* compute_stream, void*
 int launch_trace_streamed(pt_scene* sc, bool any, const void* d_rays, size_t n, void* d_hits, void* d_inst, void* d_occ, const StreamCtl& ctl, void* stream){
     if(n == 0)return PT_OK;
     const int w = sc->dev.width;
+    if(sc->dev.fast)return any ? launch_feed<kWidthFast4, true>(sc, d_rays, n, nullptr, nullptr, d_occ, ctl, stream)
+                               : launch_feed<kWidthFast4, false>(sc, d_rays, n, d_hits, d_inst, nullptr, ctl, stream);
     if(any)return w == 2 ? launch_feed<2, true>(sc, d_rays, n, nullptr, nullptr, d_occ, ctl, stream)
                 : w == 4 ? launch_feed<4, true>(sc, d_rays, n, nullptr, nullptr, d_occ, ctl, stream)
                          : launch_feed<8, true>(sc, d_rays, n, nullptr, nullptr, d_occ, ctl, stream);
@@ -267,6 +353,7 @@ int launch_trace_streamed(pt_scene* sc, bool any, const void* d_rays, size_t n, 
 
 int launch_trace_closest(pt_scene* sc, const void* d_rays, size_t n, void* d_hits, void* d_inst, void* stream){
     if(n == 0)return PT_OK;
+    if(sc->dev.fast)return launch<kWidthFast4, false, false>(sc, d_rays, n, d_hits, d_inst, nullptr, nullptr, stream);
     return sc->dev.width == 2 ? launch<2, false, false>(sc, d_rays, n, d_hits, d_inst, nullptr, nullptr, stream)
          : sc->dev.width == 4 ? launch<4, false, false>(sc, d_rays, n, d_hits, d_inst, nullptr, nullptr, stream)
                               : launch<8, false, false>(sc, d_rays, n, d_hits, d_inst, nullptr, nullptr, stream);
@@ -274,6 +361,7 @@ int launch_trace_closest(pt_scene* sc, const void* d_rays, size_t n, void* d_hit
 
 int launch_trace_any(pt_scene* sc, const void* d_rays, size_t n, void* d_occ, void* stream){
     if(n == 0)return PT_OK;
+    if(sc->dev.fast)return launch<kWidthFast4, true, false>(sc, d_rays, n, nullptr, nullptr, d_occ, nullptr, stream);
     return sc->dev.width == 2 ? launch<2, true, false>(sc, d_rays, n, nullptr, nullptr, d_occ, nullptr, stream)
          : sc->dev.width == 4 ? launch<4, true, false>(sc, d_rays, n, nullptr, nullptr, d_occ, nullptr, stream)
                               : launch<8, true, false>(sc, d_rays, n, nullptr, nullptr, d_occ, nullptr, stream);
@@ -282,6 +370,7 @@ int launch_trace_any(pt_scene* sc, const void* d_rays, size_t n, void* d_occ, vo
 // counting build of the same closest-hit traversal
 int launch_trace_stats(pt_scene* sc, const void* d_rays, size_t n, void* d_counters, void* stream){
     if(n == 0)return PT_OK;
+    if(sc->dev.fast)return launch<kWidthFast4, false, true>(sc, d_rays, n, nullptr, nullptr, nullptr, d_counters, stream);
     return sc->dev.width == 2 ? launch<2, false, true>(sc, d_rays, n, nullptr, nullptr, nullptr, d_counters, stream)
          : sc->dev.width == 4 ? launch<4, false, true>(sc, d_rays, n, nullptr, nullptr, nullptr, d_counters, stream)
                               : launch<8, false, true>(sc, d_rays, n, nullptr, nullptr, nullptr, d_counters, stream);
@@ -327,7 +416,7 @@ static int launch_static(pt_scene* sc, StaticScratch* d, size_t n, bool want_ins
     if(need_ctas < grid)grid = (unsigned)need_ctas;
     if(!cuda_ok(cudaMemsetAsync(&d->cursor, 0, sizeof(unsigned long long), st), "cursor reset"))return PT_ERR_CUDA;
     kernel<<<grid, kTraceBlock, smem, st>>>(sc->dev, d->rays, n, d->hits, want_inst ? d->inst : nullptr, nullptr,
-                                            &d->cursor, nullptr, refill_min(), alpha, StreamCtl());
+                                            &d->cursor, nullptr, refill_min(), alpha, StreamCtl(), DynBatch(), overflow_counter(sc), ConnectAcc());
     return check_launch("k_trace (static scratch)");
 }
 
@@ -350,7 +439,10 @@ extern "C" int pt_trace_closest_static(pt_scene* s, const pt_ray* rays, size_t n
     cudaStream_t st = (cudaStream_t)s->stream;
     if(!cuda_ok(cudaMemcpyAsync(d->rays, rays, n * sizeof(pt_ray), cudaMemcpyHostToDevice, st), "H2D rays"))return PT_ERR_CUDA;
     int rc;
-    if(s->has_alpha_tex || s->has_wrappers){
+    if(s->dev.fast){
+        if(s->has_alpha_tex || s->has_wrappers)rc = launch_static<kWidthFast4>(s, d, n, inst != nullptr, st, AlphaTex { s->shade, s->alpha_salt += 0x9E3779B97F4A7C15ull });
+        else rc = launch_static<kWidthFast4>(s, d, n, inst != nullptr, st, NoAlpha());
+    } else if(s->has_alpha_tex || s->has_wrappers){
         const AlphaTex at = { s->shade, s->alpha_salt += 0x9E3779B97F4A7C15ull };
         rc = s->dev.width == 2 ? launch_static<2>(s, d, n, inst != nullptr, st, at) : s->dev.width == 4 ? launch_static<4>(s, d, n, inst != nullptr, st, at)
                                                                                                       : launch_static<8>(s, d, n, inst != nullptr, st, at);

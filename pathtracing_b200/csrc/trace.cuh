@@ -40,6 +40,7 @@ struct RayCtx {
 struct HitRec {
     float t, u, v;
     uint32_t prim, inst;
+    uint32_t overflow;   // the traversal stack overflowed on this ray (TF_OVERFLOW)
 };
 
 struct TraceCounters {
@@ -97,6 +98,14 @@ __device__ __forceinline__ F8 ldg256(const void* p){
     r.lo = reinterpret_cast<const float4*>(p)[0]; r.hi = reinterpret_cast<const float4*>(p)[1];
 #endif
     return r;
+}
+
+__device__ __forceinline__ TriData load_tri64(const Tri64* tris, uint32_t i){
+    const float4* p = reinterpret_cast<const float4*>(tris + i);
+    const F8 w0 = ldg256(p), w1 = ldg256(p + 2);
+    TriData t;
+    t.a = w0.lo; t.b = w0.hi; t.c = w1.lo;
+    return t;
 }
 
 __device__ __forceinline__ TriData load_tri(const Tri* tris, uint32_t i){
@@ -275,7 +284,8 @@ enum : uint32_t {
     TF_FOUND_LOCAL = 4u, // a hit was accepted inside the current instance
     TF_DONE = 8u,
     TF_OCCLUDED = 16u,   // any-hit result
-    TF_ANIM2 = 32u       // AnimatedPrimitive over a TransformedPrimitive: the outer |dir| sits on the stack under REF_LEAVE
+    TF_ANIM2 = 32u,      // AnimatedPrimitive over a TransformedPrimitive: the outer |dir| sits on the stack under REF_LEAVE
+    TF_OVERFLOW = 64u    // a push found the traversal stack full and was dropped: the result may be wrong, the caller counts it and fails the call
 };
 
 struct TravState {
@@ -317,8 +327,9 @@ struct TravStack<0, 1> {    // all local (host emulation, tiny launches)
 using LocalStack = TravStack<0, 1>;
 
 template <class STK>
-__device__ __forceinline__ void trav_push(const STK& stack, int& sp, uint32_t ref, float entry){
+__device__ __forceinline__ void trav_push(const STK& stack, int& sp, uint32_t& flags, uint32_t ref, float entry){
     if(sp < kStack){ stack.st(sp, make_uint2(ref, __float_as_uint(entry))); ++sp; }
+    else flags |= TF_OVERFLOW;
 }
 
 // Scene::Intersect / IntersectPred entry (Scene.cpp:4-6,31-33).
@@ -363,7 +374,7 @@ __device__ __forceinline__ void node_step2(TravState& s, const DevScene& S, cons
     const uint32_t nref = near0 ? q3.x : q3.y, fref = near0 ? q3.y : q3.x;
     const bool hn = near0 ? h0 : h1, hf = near0 ? h1 : h0;
     if(hn){
-        if(hf)trav_push(stack, s.sp, fref, 0.0f);
+        if(hf)trav_push(stack, s.sp, s.flags, fref, 0.0f);
         s.cur = nref;
     } else s.cur = hf ? fref : REF_EMPTY;
 }
@@ -396,18 +407,29 @@ __device__ __forceinline__ void node_step4(TravState& s, const DevScene& S, cons
     uint32_t cur = REF_EMPTY;
     float cure = 0.0f;
     int sp = s.sp;
+    bool ovf = false;
     const unsigned word = s.octant < 4 ? ord.x : ord.y;
     const unsigned code = (word >> ((s.octant & 3u) * 8u)) & 0xFFu;
 #pragma unroll
     for(int k = 0; k < 4; k++){
-        const unsigned lane = (code >> (2 * k)) & 3u;   // k = 0 is the LAST visited lane
-        const bool hit = ((mask >> lane) & 1u) != 0;
-        const bool hi = (lane & 2u) != 0, lo = (lane & 1u) != 0;
-        const uint32_t ra = lo ? refs.y : refs.x, rb = lo ? refs.w : refs.z;
-        const float ea = lo ? e1 : e0, eb = lo ? e3 : e2;
-        const uint32_t r = hi ? rb : ra;
-        const float e = hi ? eb : ea;
-        const bool push = hit && cur != REF_EMPTY && sp < kStack;
+        uint32_t r; float e; bool hit;
+        if(ANY){
+            // any-hit: the answer does not depend on the visit order; BVH4::IntersectPred pushes unordered too (BVH.hpp:1019-1109)
+            hit = ((mask >> k) & 1u) != 0;
+            r = k == 0 ? refs.x : k == 1 ? refs.y : k == 2 ? refs.z : refs.w;
+            e = k == 0 ? e0 : k == 1 ? e1 : k == 2 ? e2 : e3;
+        } else{
+            const unsigned lane = (code >> (2 * k)) & 3u;   // k = 0 is the LAST visited lane
+            hit = ((mask >> lane) & 1u) != 0;
+            const bool hi = (lane & 2u) != 0, lo = (lane & 1u) != 0;
+            const uint32_t ra = lo ? refs.y : refs.x, rb = lo ? refs.w : refs.z;
+            const float ea = lo ? e1 : e0, eb = lo ? e3 : e2;
+            r = hi ? rb : ra;
+            e = hi ? eb : ea;
+        }
+        const bool want = hit && cur != REF_EMPTY;
+        const bool push = want && sp < kStack;
+        ovf |= want && !push;
         if(push)stack.st(sp, make_uint2(cur, __float_as_uint(cure)));
         sp += push ? 1 : 0;
         cur = hit ? r : cur;
@@ -415,6 +437,98 @@ __device__ __forceinline__ void node_step4(TravState& s, const DevScene& S, cons
     }
     s.sp = sp;
     s.cur = cur;
+    if(ovf)s.flags |= TF_OVERFLOW;
+}
+
+// Fast BVH4 cluster (pt_types.h Bvh4QNode): two 256-bit loads.  The slab planes of child c along x are
+// org.x + q * step.x; with a = step.x * inv.x and b = (org.x - o.x) * inv.x every plane distance is one FMA
+// q * a + b.  The boxes were rounded outwards by at least a quarter step at build time, far more than the rounding
+// of these FMAs, so no exact box is ever missed; `e <= tmax` (not the reference's strict `<`) keeps the superset
+// property for candidates at exactly tmax.  Visit order and pop-time cull as in node_step4.
+__device__ __forceinline__ float qbyte(uint32_t w, int c){ return __uint2float_rn((w >> (8 * c)) & 0xFFu); }
+
+// Up to three pushes of one cluster visit.  Common case (all of them land in the shared-memory rows): predicated
+// stores, no branch per push; the generic path (rows spilling to local memory, overflow) only near the row limit.
+// profiles/r02_trace44_v1.md: with one smem-or-local branch inside each of the four unrolled pushes the push code was
+// 12 % of all instructions of the kernel.
+template <int KS, int STRIDE>
+__device__ __forceinline__ bool stack_fast(const TravStack<KS, STRIDE>&, int sp){ return KS >= 4 && sp + 3 <= KS; }
+__device__ __forceinline__ bool stack_fast(const LocalStack&, int){ return false; }
+template <int KS, int STRIDE>
+__device__ __forceinline__ void stack_st_sm(const TravStack<KS, STRIDE>& k, int i, uint2 v){ k.sm[i * STRIDE] = v; }
+__device__ __forceinline__ void stack_st_sm(const LocalStack& k, int i, uint2 v){ k.lm[i] = v; }
+
+// pop: rows below KS come straight from shared memory (no branch in the common case of a shallow stack)
+template <int KS, int STRIDE>
+__device__ __forceinline__ uint2 stack_ld(const TravStack<KS, STRIDE>& k, int i){ return k.ld(i); }
+__device__ __forceinline__ uint2 stack_ld(const LocalStack& k, int i){ return k.lm[i]; }
+
+template <bool ANY, class STK>
+__device__ __forceinline__ void node_step4q(TravState& s, const DevScene& S, const STK& stack){
+    const float4* p = reinterpret_cast<const float4*>(S.n4q + s.cur);
+    const F8 w0 = ldg256(p), w1 = ldg256(p + 2);
+    const uint32_t exw = __float_as_uint(w0.lo.w);
+    const uint4 refs = make_uint4(__float_as_uint(w0.hi.x), __float_as_uint(w0.hi.y), __float_as_uint(w0.hi.z), __float_as_uint(w0.hi.w));
+    const uint2 ord = make_uint2(__float_as_uint(w1.hi.z), __float_as_uint(w1.hi.w));
+    const float ax = __uint_as_float((exw & 0xFFu) << 23) * s.r.ix, ay = __uint_as_float(((exw >> 8) & 0xFFu) << 23) * s.r.iy,
+                az = __uint_as_float(((exw >> 16) & 0xFFu) << 23) * s.r.iz;
+    const float bx = (w0.lo.x - s.r.ox) * s.r.ix, by = (w0.lo.y - s.r.oy) * s.r.iy, bz = (w0.lo.z - s.r.oz) * s.r.iz;
+    // near / far plane words per axis by the sign of the ray's reciprocal direction: the slab interval needs no min / max
+    const bool nx = s.r.ix < 0.0f, ny = s.r.iy < 0.0f, nz = s.r.iz < 0.0f;
+    const uint32_t qnx = nx ? __float_as_uint(w1.lo.w) : __float_as_uint(w1.lo.x), qfx = nx ? __float_as_uint(w1.lo.x) : __float_as_uint(w1.lo.w);
+    const uint32_t qny = ny ? __float_as_uint(w1.hi.x) : __float_as_uint(w1.lo.y), qfy = ny ? __float_as_uint(w1.lo.y) : __float_as_uint(w1.hi.x);
+    const uint32_t qnz = nz ? __float_as_uint(w1.hi.y) : __float_as_uint(w1.lo.z), qfz = nz ? __float_as_uint(w1.lo.z) : __float_as_uint(w1.hi.y);
+    const float tmax = s.tmax;
+    float e[4];
+    unsigned mask = 0;
+#pragma unroll
+    for(int c = 0; c < 4; c++){
+        const float en = fmaxf(fmaxf(fmaf(qbyte(qnx, c), ax, bx), fmaf(qbyte(qny, c), ay, by)), fmaf(qbyte(qnz, c), az, bz));
+        const float ex = fminf(fminf(fmaf(qbyte(qfx, c), ax, bx), fmaf(qbyte(qfy, c), ay, by)), fmaf(qbyte(qfz, c), az, bz));
+        e[c] = en;
+        if(ex >= kShadowEps && en <= fminf(tmax, ex))mask |= 1u << c;
+    }
+    // (an absent child is stored with its near planes at 255 and its far planes at 0 steps: it never passes, whatever the ray)
+    uint32_t cur = REF_EMPTY;
+    float cure = 0.0f;
+    int sp = s.sp;
+    const unsigned word = s.octant < 4 ? ord.x : ord.y;
+    const unsigned code = (word >> ((s.octant & 3u) * 8u)) & 0xFFu;
+    const bool fast = stack_fast(stack, sp);
+    bool ovf = false;
+#pragma unroll
+    for(int k = 0; k < 4; k++){
+        uint32_t r; float en; bool hit;
+        if(ANY){
+            // any-hit: the answer does not depend on the visit order (the reference pushes unordered too, BVH.hpp:1019-1109)
+            hit = ((mask >> k) & 1u) != 0;
+            r = k == 0 ? refs.x : k == 1 ? refs.y : k == 2 ? refs.z : refs.w;
+            en = e[k];
+        } else{
+            const unsigned lane = (code >> (2 * k)) & 3u;   // k = 0 is the LAST visited lane
+            hit = ((mask >> lane) & 1u) != 0;
+            const bool hi = (lane & 2u) != 0, lo = (lane & 1u) != 0;
+            const uint32_t ra = lo ? refs.y : refs.x, rb = lo ? refs.w : refs.z;
+            const float ea = lo ? e[1] : e[0], eb = lo ? e[3] : e[2];
+            r = hi ? rb : ra;
+            en = hi ? eb : ea;
+        }
+        const bool want = hit && cur != REF_EMPTY;
+        if(fast){
+            if(want)stack_st_sm(stack, sp, make_uint2(cur, __float_as_uint(cure)));
+            sp += want ? 1 : 0;
+        } else{
+            const bool push = want && sp < kStack;
+            ovf |= want && !push;
+            if(push)stack.st(sp, make_uint2(cur, __float_as_uint(cure)));
+            sp += push ? 1 : 0;
+        }
+        cur = hit ? r : cur;
+        cure = hit ? en : cure;
+    }
+    s.sp = sp;
+    s.cur = cur;
+    if(ovf)s.flags |= TF_OVERFLOW;
 }
 
 // BVH8 cluster (BVH8::Intersect / IntersectPred, BVH.hpp:1374-1540): the same slab test and strict
@@ -450,13 +564,16 @@ __device__ __forceinline__ void node_step8(TravState& s, const DevScene& S, cons
     uint32_t cur = REF_EMPTY;
     float cure = 0.0f;
     int sp = s.sp;
+    bool ovf = false;
 #pragma unroll
     for(int k = 7; k >= 0; k--){                 // far to near: the nearest hit lane ends up in `cur`
         const unsigned lane = (code >> (3 * k)) & 7u;
         const uint32_t r = sel8(refs, lane);
         const float en = sel8(e, lane);
         const bool hit = ((mask >> lane) & 1u) != 0 && r != REF_EMPTY;   // absent lanes have zero boxes, never children
-        const bool push = hit && cur != REF_EMPTY && sp < kStack;
+        const bool want = hit && cur != REF_EMPTY;
+        const bool push = want && sp < kStack;
+        ovf |= want && !push;
         if(push)stack.st(sp, make_uint2(cur, __float_as_uint(cure)));
         sp += push ? 1 : 0;
         cur = hit ? r : cur;
@@ -464,6 +581,7 @@ __device__ __forceinline__ void node_step8(TravState& s, const DevScene& S, cons
     }
     s.sp = sp;
     s.cur = cur;
+    if(ovf)s.flags |= TF_OVERFLOW;
 }
 
 // ---- one round of the state machine -------------------------------------------------------
@@ -492,7 +610,7 @@ __device__ __forceinline__ void trav_step(TravState& s, const DevScene& S, const
     // -- pop (BVH4 closest: cull by entry distance, BVH.hpp:1135) --
     if(s.cur == REF_EMPTY){
         while(s.sp > 0){
-            const uint2 e = stack.ld(--s.sp);
+            const uint2 e = stack_ld(stack, --s.sp);
             if(WIDTH >= 4 && !ANY && __uint_as_float(e.y) > s.tmax)continue;
             if(e.x == REF_EMPTY)continue;      // empty lane of a cluster (BVH.hpp:38-43)
             s.cur = e.x;
@@ -505,6 +623,7 @@ __device__ __forceinline__ void trav_step(TravState& s, const DevScene& S, const
         if(STATS){ if(s.flags & TF_IN_INST)cnt->blas_nodes++; else cnt->tlas_nodes++; }
         if(WIDTH == 2)node_step2<ANY>(s, S, stack);
         else if(WIDTH == 4)node_step4<ANY>(s, S, stack);
+        else if(WIDTH == kWidthFast4)node_step4q<ANY>(s, S, stack);
         else node_step8<ANY>(s, S, stack);
     }
     // -- leaf items --
@@ -563,9 +682,9 @@ __device__ __forceinline__ void trav_step(TravState& s, const DevScene& S, const
                     return;
                 }
                 // AnimatedPrimitive over a BLAS instance
-                if(!(d.meta.y & INST_LAST))trav_push(stack, s.sp, REF_LEAF | nxt, -CUDART_INF_F);
-                if(xf){ trav_push(stack, s.sp, REF_EMPTY, len_a); s.flags |= TF_ANIM2; }
-                trav_push(stack, s.sp, REF_LEAVE, -CUDART_INF_F);
+                if(!(d.meta.y & INST_LAST))trav_push(stack, s.sp, s.flags, REF_LEAF | nxt, -CUDART_INF_F);
+                if(xf){ trav_push(stack, s.sp, s.flags, REF_EMPTY, len_a); s.flags |= TF_ANIM2; }
+                trav_push(stack, s.sp, s.flags, REF_LEAVE, -CUDART_INF_F);
                 s.flags |= TF_IN_INST | TF_XF;
                 s.inst_rec = i; s.inst_id = d.meta.z;
                 s.wtmax = s.tmax; s.len = xf ? len_b : len_a;
@@ -590,8 +709,8 @@ __device__ __forceinline__ void trav_step(TravState& s, const DevScene& S, const
                 s.cur = (d.meta.y & INST_LAST) ? REF_EMPTY : (REF_LEAF | nxt);
                 return;
             }
-            if(!(d.meta.y & INST_LAST))trav_push(stack, s.sp, REF_LEAF | nxt, -CUDART_INF_F);
-            trav_push(stack, s.sp, REF_LEAVE, -CUDART_INF_F);
+            if(!(d.meta.y & INST_LAST))trav_push(stack, s.sp, s.flags, REF_LEAF | nxt, -CUDART_INF_F);
+            trav_push(stack, s.sp, s.flags, REF_LEAVE, -CUDART_INF_F);
             s.flags |= TF_IN_INST;
             s.inst_rec = i; s.inst_id = d.meta.z;
             if(d.meta.y & INST_XF){
@@ -608,7 +727,7 @@ __device__ __forceinline__ void trav_step(TravState& s, const DevScene& S, const
         } else{
             // BLAS leaf item: one triangle of BVHBase::intersectPrimitives[Pred] (BVH.hpp:107-135)
             const uint32_t i = s.cur & ~REF_LEAF;
-            const TriData T = load_tri(S.tris, i);
+            const TriData T = WIDTH == kWidthFast4 ? load_tri64(S.tris64, i) : load_tri(S.tris, i);
             const uint32_t tf = __float_as_uint(T.c.w);
             if(STATS)cnt->triangles++;
             float t, u, v;
@@ -645,6 +764,7 @@ __device__ __forceinline__ bool trace_scene(const DevScene& S, const RAYS& rays,
     while(!(s.flags & TF_DONE))trav_step<WIDTH, ANY, STATS>(s, S, stack, rays, ray_idx, cnt, alpha);
     const bool found = s.hprim != 0xFFFFFFFFu;
     hit.t = found ? s.tmax : CUDART_INF_F; hit.u = s.hu; hit.v = s.hv; hit.prim = s.hprim; hit.inst = s.hinst;
+    hit.overflow = (s.flags & TF_OVERFLOW) ? 1u : 0u;
     return ANY ? (s.flags & TF_OCCLUDED) != 0 : found;
 }
 

@@ -8,6 +8,8 @@
 // What has no GPU counterpart yet is a compile-time absence (SphereShape / QuadShape, BVH8, file-loading
 // texture ctors, per-triangle GeometricPrimitive lists), not a silent approximation.
 #pragma once
+#include <algorithm>
+#include <cstdlib>
 #include <cmath>
 #include <cstdint>
 #include <cstdio>
@@ -641,7 +643,7 @@ public:
     Scene(const std::shared_ptr<Medium>& medium) : sceneMedium(medium){}
     Scene(const Scene&) = delete;
     Scene& operator=(const Scene&) = delete;
-    ~Scene(){ if(gpu)pt_scene_destroy(gpu); }
+    ~Scene(){ DropGpu(); }
 
     void Add(const std::shared_ptr<Primitive>& ptr){ primitives.push_back(ptr); Invalidate(); }
     std::vector<std::shared_ptr<Light>> GetLights() const{ return { std::make_shared<SceneLights>() }; }
@@ -692,7 +694,7 @@ public:
         if(sampler && !sampler->HasSceneLights())throw std::logic_error("LightSampler::Add(scene->GetLights()) was not called");
         const bool newMedium = cameraMedium && MediumId(cameraMedium.get()) < 0;
         if(gpu && !newMedium && (sampler == nullptr || (kind == committedKind && key == committedKey)))return gpu;
-        if(gpu){ pt_scene_destroy(gpu); gpu = nullptr; }
+        DropGpu();
         ptb_host::Builder b;
         b.scene = pt_scene_create(device);
         if(!b.scene)throw std::runtime_error(std::string("pt_scene_create: ") + pt_last_error());
@@ -716,8 +718,30 @@ public:
     }
     // id of a medium object in the committed scene (camera medium), -1 if it is not part of it
     int MediumId(const Medium* m) const{ auto it = media.find(m); return it == media.end() ? -1 : it->second; }
+    // The committed scene on `gpus` GPUs (the primary's device first, then the other visible ones): replicas, an NCCL
+    // communicator and one host thread per GPU inside libptb200.so (pt_multi_create), cached like the scene itself.
+    // gpus <= 1 or a single visible GPU: nullptr (Render then calls pt_render on the primary).
+    pt_multi* Multi(pt_scene* committed, int gpus){
+        const int visible = pt_device_count();
+        if(gpus > visible)gpus = visible;
+        if(gpus <= 1)return nullptr;
+        if(multi && multiGpus == gpus)return multi;
+        if(multi){ pt_multi_destroy(multi); multi = nullptr; }
+        std::vector<int> devs { device };
+        for(int d = 0; d < visible && (int)devs.size() < gpus; d++)if(d != device)devs.push_back(d);
+        multi = pt_multi_create(committed, devs.data(), (int)devs.size());
+        if(!multi)throw std::runtime_error(std::string("pt_multi_create: ") + pt_last_error());
+        multiGpus = gpus;
+        return multi;
+    }
 private:
-    void Invalidate(){ if(gpu){ pt_scene_destroy(gpu); gpu = nullptr; } }
+    void DropGpu(){
+        if(multi){ pt_multi_destroy(multi); multi = nullptr; }       // before the primary it refers to
+        if(gpu){ pt_scene_destroy(gpu); gpu = nullptr; }
+    }
+    void Invalidate(){ DropGpu(); }
+    pt_multi* multi = nullptr;
+    int multiGpus = 0;
     std::vector<std::shared_ptr<Primitive>> primitives;
     std::shared_ptr<Medium> sceneMedium;
     int tlasWidth = 0, device = 0;
@@ -946,8 +970,9 @@ public:
     Integrator(const std::shared_ptr<Scene>& scene, const std::shared_ptr<Camera>& camera, const std::shared_ptr<Sampler>& sampler)
         : scene(scene), camera(camera), sampler(sampler){}
     virtual ~Integrator() = default;
-    // Runs the whole frame on the GPU and merges it into the camera's Film.  threadCount is accepted for
-    // source compatibility; the wavefront kernels size themselves to the device.
+    // Runs the whole frame on the GPUs and merges it into the camera's Film.  The reference's workers are host threads
+    // (Integrators.cpp:23-41); here a worker is a GPU: threadCount = 0 (the default) uses every visible GPU, a smaller
+    // number that many (PTB_GPUS in the environment overrides both); the wavefront kernels size themselves to each device.
     virtual void Render(unsigned int threadCount = 0) const = 0;
     bool Intersect(const Ray& ray, SurfaceInteraction& interaction, float max = std::numeric_limits<float>::infinity()) const{ return scene->Intersect(ray, interaction, max); }
     bool Unoccluded(const Ray& ray, float t) const{ return !scene->IntersectPred(ray, t); }
@@ -961,9 +986,12 @@ class TileIntegrator : public Integrator {
 public:
     TileIntegrator(const std::shared_ptr<Scene>& scene, const std::shared_ptr<Camera>& camera, const std::shared_ptr<Sampler>& sampler)
         : Integrator(scene, camera, sampler){}
-    void Render(unsigned int = 0) const override{
+    void Render(unsigned int threadCount = 0) const override{
         const std::shared_ptr<Film> film = camera->GetFilm();
         pt_scene* s = scene->Commit(Sampler_(), camera->GetMedium());
+        int gpus = threadCount == 0 ? pt_device_count() : (int)std::min<unsigned int>(threadCount, (unsigned int)pt_device_count());
+        if(const char* e = std::getenv("PTB_GPUS"))gpus = std::max(1, std::atoi(e));
+        pt_multi* multi = scene->Multi(s, gpus);
         pt_render_params rp;
         std::memset(&rp, 0, sizeof rp);
         const glm::ivec2 res = film->Resolution();
@@ -975,7 +1003,8 @@ public:
         rp.adaptive = adaptive ? 1 : 0;
         const pt_camera_desc cd = camera->Describe(camera->GetMedium() ? scene->MediumId(camera->GetMedium().get()) : -1);
         pt_render_stats st;
-        ptb_host::check(pt_render(s, &cd, &rp, 1, &st), "pt_render");
+        if(multi)ptb_host::check(pt_multi_render(multi, &cd, &rp, 1, &st), "pt_multi_render");   // sample passes sharded over the GPUs, one NCCL reduce of the film
+        else ptb_host::check(pt_render(s, &cd, &rp, 1, &st), "pt_render");
         std::vector<double> rgbw(4 * (size_t)res.x * res.y);
         ptb_host::check(pt_film_download(s, rgbw.data()), "pt_film_download");
         film->Merge(rgbw);

@@ -1,8 +1,10 @@
 """Multi-GPU plumbing: scene replicated per rank, sample passes sharded
 (rank r renders passes r, r+G, ...), ONE reduce(sum) of the film accumulators to rank 0.
 
-torch.distributed is plumbing only: NCCL over NVLink for device films, gloo for the CPU-side
-tests of the same logic.  The reference has no counterpart: its only shared state is the
+The product path is csrc/multi.cu (pt_multi_* in one process, pt_dist_* with one process per GPU: NCCL inside
+libptb200.so).  What is left here: render_sharded (the call bench.py makes under torchrun), a torch view of the
+device film, and the same sharding / reduce / all-reduce glue over torch.distributed for the gloo tests that run
+without a GPU.  The reference has no counterpart: its only shared state is the
 atomic<double> film that worker threads merge into (Film.hpp:125-132, 244-249).
 """
 from __future__ import annotations
@@ -75,22 +77,14 @@ def make_allreduce(dist, cuda: bool = True):
 
 
 def render_sharded(scene, cam, params, dist=None):
-    """Render this rank's passes and reduce the film to rank 0.  Returns (stats, film tensor);
-    the tensor holds the complete image on rank 0 only."""
-    world = dist.get_world_size() if dist is not None and dist.is_initialized() else 1
-    rank = dist.get_rank() if world > 1 else 0
-    if world > 1 and params.adaptive and getattr(scene, "_allreduce", None) is None:
-        scene._allreduce = make_allreduce(dist)
-        scene._ck(scene.lib.pt_scene_set_allreduce(scene.h, scene._allreduce, None))
-    stats = scene.render(cam, pass_range(params, world, rank), clear=True)
-    film = film_tensor(scene)
-    reduce_film(film, dist)
-    if world > 1:
-        # the scene renders on its own stream: the reduce (queued behind torch's current stream) has to
-        # finish before the next pt_render clears or accumulates into the same film
-        import torch
-        torch.cuda.synchronize()
-    return stats, film
+    """Render this rank's passes and reduce the film to rank 0 -- all inside libptb200.so (pt_dist_render: NCCL
+    communicator, pass sharding, the film reduce and the per-round all-reduce of adaptive renders live behind the
+    C-ABI; `dist` only carries the 128-byte NCCL id once, GpuScene.dist_init).  Returns (stats, film tensor);
+    the tensor is a view of the device film and holds the complete image on rank 0 only."""
+    if getattr(scene, "world", None) is None:
+        scene.dist_init(dist)
+    stats = scene.dist_render(cam, params, clear=True)
+    return stats, film_tensor(scene)
 
 
 def resolve(rgbw: np.ndarray):

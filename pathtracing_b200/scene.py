@@ -9,6 +9,7 @@ them through any object exposing the add_* entry points: the product's C-ABI
 from __future__ import annotations
 
 import ctypes as C
+import os
 from dataclasses import dataclass, field
 
 import numpy as np
@@ -248,7 +249,7 @@ def render_params(width, height, spp, max_depth, integrator=capi.INTEGRATOR_PATH
 class GpuScene:
     """A committed scene on one B200, through the C-ABI only."""
 
-    def __init__(self, desc: SceneDesc, bvh_width=4, light_sampler=1, device=0, builder=capi.BUILDER_HOST):
+    def __init__(self, desc: SceneDesc, bvh_width=4, light_sampler=1, device=0, builder=capi.BUILDER_HOST, layout=None):
         self.lib = capi.load_library()
         self.h = self.lib.pt_scene_create(device)
         if not self.h:
@@ -256,6 +257,10 @@ class GpuScene:
         self.desc = desc
         desc.replay(self)
         self._ck(self.lib.pt_scene_set_builder(self.h, builder))
+        if layout is None:      # experiments: PTB_LAYOUT=fast turns the quantised layout on for every width-4 scene
+            layout = capi.LAYOUT_FAST if (os.environ.get("PTB_LAYOUT") == "fast" and bvh_width == 4) else capi.LAYOUT_EXACT
+        self.layout = layout
+        self._ck(self.lib.pt_scene_set_layout(self.h, layout))
         self._ck(self.lib.pt_scene_commit(self.h, bvh_width, light_sampler))
         self.bvh_width = bvh_width
 
@@ -364,9 +369,89 @@ class GpuScene:
         self._ck(self.lib.pt_film_device_ptr(self.h, C.byref(p), C.byref(n)))
         return p.value, n.value
 
+    def counted_render(self, cam, params):
+        """One frame with the counting build of the traversal kernels: (render stats, closest-ray visits, shadow-ray visits)."""
+        self._ck(self.lib.pt_scene_set_counting(self.h, 1))
+        try:
+            st = self.render(cam, params)
+            c, s = pt_trace_stats(), pt_trace_stats()
+            self._ck(self.lib.pt_scene_render_counts(self.h, C.byref(c), C.byref(s)))
+        finally:
+            self._ck(self.lib.pt_scene_set_counting(self.h, 0))
+        d = lambda x: {k: int(getattr(x, k)) for k, _ in pt_trace_stats._fields_}
+        return st, d(c), d(s)
+
+    def stack_overflows(self) -> int:
+        n = C.c_uint64(0)
+        self._ck(self.lib.pt_scene_stack_overflows(self.h, C.byref(n)))
+        return int(n.value)
+
+    # one process per GPU (pt_dist_*): the NCCL communicator lives inside libptb200.so; `dist` (torch.distributed,
+    # any backend) only carries the 128-byte id from rank 0 to the others
+    def dist_init(self, dist=None):
+        world = dist.get_world_size() if dist is not None and dist.is_initialized() else 1
+        rank = dist.get_rank() if world > 1 else 0
+        ident = None
+        if world > 1:
+            import torch  # noqa: F401  (loads PyTorch's NCCL before ours is looked for: one NCCL per process)
+            box = [None]
+            if rank == 0:
+                buf = (C.c_ubyte * 128)()
+                self._ck(self.lib.pt_dist_unique_id(buf))
+                box[0] = bytes(buf)
+            dist.broadcast_object_list(box, src=0)
+            ident = (C.c_ubyte * 128).from_buffer_copy(box[0])
+        self._ck(self.lib.pt_dist_init(self.h, ident, rank, world))
+        self.rank, self.world = rank, world
+
+    def dist_render(self, cam, params, clear=True):
+        """This rank's passes of the frame + the one film reduce to rank 0 (pt_dist_render)."""
+        st = pt_render_stats()
+        self._ck(self.lib.pt_dist_render(self.h, C.byref(cam), C.byref(params), 1 if clear else 0, C.byref(st)))
+        self._film_shape = (params.height, params.width)
+        return {k: getattr(st, k) for k, _ in pt_render_stats._fields_}
+
     def close(self):
         if self.h:
             self.lib.pt_scene_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+class MultiGpu:
+    """pt_multi_*: one process, one host thread per GPU inside libptb200.so, the frame in the primary scene's film.
+    devices=None: every visible GPU; [0, 0, ...]: virtual ranks on one GPU (the sharding logic without NCCL)."""
+
+    def __init__(self, primary: GpuScene, devices=None):
+        self.primary, self.lib = primary, primary.lib
+        if devices is None:
+            self.h = self.lib.pt_multi_create(primary.h, None, 0)
+        else:
+            arr = (C.c_int * len(devices))(*devices)
+            self.h = self.lib.pt_multi_create(primary.h, arr, len(devices))
+        if not self.h:
+            raise PtError(primary._err())
+
+    @property
+    def gpus(self) -> int:
+        return self.lib.pt_multi_gpus(self.h)
+
+    def render(self, cam, params, clear=True):
+        st = pt_render_stats()
+        rc = self.lib.pt_multi_render(self.h, C.byref(cam), C.byref(params), 1 if clear else 0, C.byref(st))
+        if rc < 0:
+            raise PtError(f"pt error {rc}: {self.primary._err()}")
+        self.primary._film_shape = (params.height, params.width)
+        return {k: getattr(st, k) for k, _ in pt_render_stats._fields_}
+
+    def close(self):
+        if self.h:
+            self.lib.pt_multi_destroy(self.h)
             self.h = None
 
     def __del__(self):

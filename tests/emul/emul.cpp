@@ -22,6 +22,7 @@ static inline unsigned __float_as_uint(float f){ unsigned u; memcpy(&u, &f, 4); 
 static inline float __uint_as_float(unsigned u){ float f; memcpy(&f, &u, 4); return f; }
 static inline float __int_as_float(unsigned u){ float f; memcpy(&f, &u, 4); return f; }
 template <class T> static inline T __ldg(const T* p){ return *p; }
+static inline float __uint2float_rn(unsigned u){ return (float)u; }
 #endif
 
 #include "../../pathtracing_b200/csrc/scene_host.hpp"
@@ -36,6 +37,8 @@ using namespace ptb;
 struct EmulScene {
     pt_scene s;
     PackedTraversal P;
+    std::vector<Bvh4QNode> n4q;      // width 44: the fast layout (PT_LAYOUT_FAST)
+    std::vector<Tri64> tris64;
     DevScene D;
     ShadeTables T;          // host copies of the shading tables (emul_shade_tables)
     bool shaded = false;
@@ -59,13 +62,52 @@ PT_API int emul_scene_add_light(void* p, const pt_light_desc* d){ return scene_a
 
 PT_API int emul_scene_commit(void* p, int width){
     EmulScene* e = (EmulScene*)p;
+    const bool fast = width == kWidthFast4;
+    if(fast)width = 4;
     int rc = pack_traversal(&e->s, width, e->P);
     if(rc != PT_OK)return rc;
+    e->D.fast = fast ? 1 : 0; e->D.n4q = nullptr; e->D.tris64 = nullptr;
+    if(fast){
+        encode_bvh4q(e->P.n4, e->n4q);
+        e->tris64.resize(e->P.tris.size());
+        for(size_t i = 0; i < e->P.tris.size(); i++){ memset(&e->tris64[i], 0, sizeof(Tri64)); e->tris64[i].t = e->P.tris[i]; }
+        e->D.n4q = e->n4q.data(); e->D.tris64 = e->tris64.data();
+    }
     e->D.n2 = e->P.n2.data(); e->D.n4 = e->P.n4.data(); e->D.n8 = e->P.n8.data(); e->D.tris = e->P.tris.data(); e->D.inst = e->P.insts.data();
     e->D.tlas_root = e->P.tlas_root; e->D.width = width;
     e->D.single_root = e->P.single_root; e->D.single_id = e->P.single_id;
     for(int a = 0; a < 3; a++){ e->D.tlo[a] = e->P.bounds.lo[a]; e->D.thi[a] = e->P.bounds.hi[a]; }
     return PT_OK;
+}
+
+// fast layout: every decoded child box contains the exact one; returns the number of violations, the clusters
+// checked and the largest growth of a child box relative to its cluster's extent (per side, any axis)
+PT_API int emul_bvh4q_check(void* p, int* n_nodes, float* worst_growth){
+    EmulScene* e = (EmulScene*)p;
+    int bad = 0;
+    float worst = 0.0f;
+    for(size_t i = 0; i < e->n4q.size(); i++){
+        const Bvh4Node& a = e->P.n4[i];
+        const Bvh4QNode& q = e->n4q[i];
+        const float* mins[3] = { a.xmin, a.ymin, a.zmin };
+        const float* maxs[3] = { a.xmax, a.ymax, a.zmax };
+        for(int ax = 0; ax < 3; ax++){
+            const float step = __uint_as_float((unsigned)q.ex[ax] << 23);
+            float lo = INFINITY, hi = -INFINITY;
+            for(int c = 0; c < 4; c++)if(a.ref[c] != REF_EMPTY){ lo = std::min(lo, mins[ax][c]); hi = std::max(hi, maxs[ax][c]); }
+            for(int c = 0; c < 4; c++){
+                if(a.ref[c] == REF_EMPTY)continue;
+                const float dl = q.org[ax] + (float)((q.q[ax] >> (8 * c)) & 255u) * step, dh = q.org[ax] + (float)((q.q[3 + ax] >> (8 * c)) & 255u) * step;
+                if(!(dl <= mins[ax][c]) || !(dh >= maxs[ax][c]) || !(mins[ax][c] - dl >= 0.2f * step) || !(dh - maxs[ax][c] >= 0.2f * step))bad++;
+                if(hi > lo){
+                    const float ext = std::max(hi - lo, 1e-30f);
+                    if(step <= ext){ worst = std::max(worst, (mins[ax][c] - dl) / ext); worst = std::max(worst, (dh - maxs[ax][c]) / ext); }
+                }
+            }
+        }
+    }
+    *n_nodes = (int)e->n4q.size(); *worst_growth = worst;
+    return bad;
 }
 
 PT_API int emul_scene_bounds(void* p, float lo[3], float hi[3]){
@@ -85,7 +127,8 @@ PT_API int emul_trace_closest(void* p, const pt_ray* rays, size_t n, pt_hit* hit
         for(size_t i = tid; i < n; i += nt){
             HitRec h;
             const float4* rb = reinterpret_cast<const float4*>(rays);
-            if(D.width == 2)trace_scene<2, false, true>(D, rb, i, h, &cs[tid], NoAlphaWrap());
+            if(D.fast)trace_scene<kWidthFast4, false, true>(D, rb, i, h, &cs[tid], NoAlphaWrap());
+            else if(D.width == 2)trace_scene<2, false, true>(D, rb, i, h, &cs[tid], NoAlphaWrap());
             else if(D.width == 4)trace_scene<4, false, true>(D, rb, i, h, &cs[tid], NoAlphaWrap());
             else trace_scene<8, false, true>(D, rb, i, h, &cs[tid], NoAlphaWrap());
             hits[i].t = h.t; hits[i].u = h.u; hits[i].v = h.v; hits[i].prim = h.prim;
@@ -110,7 +153,8 @@ PT_API int emul_trace_any(void* p, const pt_ray* rays, size_t n, uint8_t* occ){
         for(size_t i = tid; i < n; i += nt){
             HitRec h;
             const float4* rb = reinterpret_cast<const float4*>(rays);
-            bool o = D.width == 2 ? trace_scene<2, true, false>(D, rb, i, h, nullptr, NoAlphaWrap())
+            bool o = D.fast ? trace_scene<kWidthFast4, true, false>(D, rb, i, h, nullptr, NoAlphaWrap())
+                   : D.width == 2 ? trace_scene<2, true, false>(D, rb, i, h, nullptr, NoAlphaWrap())
                    : D.width == 4 ? trace_scene<4, true, false>(D, rb, i, h, nullptr, NoAlphaWrap())
                                   : trace_scene<8, true, false>(D, rb, i, h, nullptr, NoAlphaWrap());
             occ[i] = o ? 1 : 0;

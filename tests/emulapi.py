@@ -44,6 +44,8 @@ def load():
     lib.emul_scene_commit.argtypes = [vp, i]
     lib.emul_scene_bounds.argtypes = [vp, C.POINTER(C.c_float), C.POINTER(C.c_float)]
     lib.emul_node_count.argtypes = [vp]
+    lib.emul_bvh4q_check.restype = i
+    lib.emul_bvh4q_check.argtypes = [vp, C.POINTER(C.c_int), C.POINTER(C.c_float)]
     lib.emul_trace_closest.restype = i
     lib.emul_trace_closest.argtypes = [vp, vp, sz, vp, vp, vp]
     lib.emul_trace_any.restype = i
@@ -104,6 +106,11 @@ class EmulScene:
 
     def node_count(self):
         return self.lib.emul_node_count(self.h)
+
+    def bvh4q_check(self):
+        n, worst = C.c_int(0), C.c_float(0)
+        bad = self.lib.emul_bvh4q_check(self.h, C.byref(n), C.byref(worst))
+        return bad, n.value, worst.value
 
     def trace_closest(self, rays, want_inst=True):
         rays = np.ascontiguousarray(rays, dtype=capi.RAY_DTYPE)

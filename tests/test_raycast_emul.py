@@ -171,3 +171,76 @@ def test_wrapped_primitives_bit_exact(width):
         assert np.array_equal(ref.trace_any(rays), em.trace_any(rays))
         seen |= set(np.unique(ri[np.isin(ri, wrapped)]).tolist())
     assert seen == set(wrapped), (seen, wrapped)      # every wrapped primitive was actually hit
+
+
+# ---- PT_LAYOUT_FAST (quantised 64 B clusters, csrc/trace.cuh node_step4q) ---------------------------------------------
+
+def _cmp_fast(desc, n_rays=60000, tmax=np.inf, seed=7, allow=0):
+    """The fast layout walks the reference's BVH4 tree with boxes that CONTAIN the exact ones: it may test more
+    candidates than the reference, never fewer.  Same closest hit (ids and the bits of t) except where candidates tie
+    or the reference's own box test rounds a grazing hit away -- `allow` bounds those, and each one must be a hit the
+    fast layout found IN FRONT of (or instead of a miss of) the reference's."""
+    from emulapi import EmulScene
+    from oracle.refapi import RefScene
+    ref = RefScene(desc, 4, id_mode=True)
+    exact = EmulScene(desc, 4)
+    fast = EmulScene(desc, 44)
+    lo, hi = ref.bounds()
+    rays = synth.random_rays(n_rays, lo, hi, seed=seed, tmax=tmax)
+    rh, ri = ref.trace_closest(rays, want_inst=True)
+    fh, fi = fast.trace_closest(rays)
+    diff = (rh["prim"] != fh["prim"]) | (rh["t"].view(np.uint32) != fh["t"].view(np.uint32)) | (ri != fi)
+    assert diff.sum() <= allow, (int(diff.sum()), rh[diff][:5], fh[diff][:5])
+    if diff.any():
+        assert (fh["t"][diff] <= rh["t"][diff]).all()
+    occ_r, occ_f = ref.trace_any(rays), fast.trace_any(rays)
+    d2 = occ_r != occ_f
+    assert d2.sum() <= allow and (occ_f[d2] == 1).all()
+    # and it does visit a superset: never fewer node / triangle visits than the exact layout, and not many more
+    exact.trace_closest(rays)
+    se, sf = exact.last_stats, fast.last_stats
+    for k in ("tlas_nodes", "blas_nodes", "triangles"):
+        assert sf[k] >= se[k], (k, se, sf)
+    assert sf["blas_nodes"] <= 1.15 * se["blas_nodes"] + 100 and sf["triangles"] <= 1.15 * se["triangles"] + 100, (se, sf)
+    return (rh["prim"] != 0xFFFFFFFF).mean()
+
+
+@needs_ref
+@pytest.mark.parametrize("opaque", [False, True])
+def test_fast_layout_soup(opaque):
+    assert _cmp_fast(synth.soup_scene(20000, opaque=opaque)) > 0.05
+
+
+@needs_ref
+def test_fast_layout_terrain_instances_tiny():
+    assert _cmp_fast(synth.terrain_scene(101, 81)) > 0.2
+    d = synth.instanced_scene(2, 16)
+    assert _cmp_fast(d) > 0.1
+    _cmp_fast(d, tmax=1.5, seed=11)
+    for n in (1, 2, 3, 5):
+        _cmp_fast(synth.soup_scene(n, seed=5), n_rays=2000)
+
+
+@needs_ref
+def test_fast_layout_shapes_and_wrappers():
+    _cmp_fast(synth.shapes_scene()[0], n_rays=30000)
+    d, _ = synth.wrapped_scene()
+    lo, hi = (-3, -0.3, -2.5), (3, 2.2, 1.5)
+    from emulapi import EmulScene
+    from oracle.refapi import RefScene
+    ref, fast = RefScene(d, 4, id_mode=True), EmulScene(d, 44)
+    rays = synth.with_times(synth.random_rays(30000, lo, hi, seed=8), seed=2)
+    rh, ri = ref.trace_closest(rays, want_inst=True)
+    fh, fi = fast.trace_closest(rays)
+    assert np.array_equal(rh["prim"], fh["prim"]) and np.array_equal(ri, fi) and np.array_equal(rh["t"].view(np.uint32), fh["t"].view(np.uint32))
+
+
+def test_fast_layout_boxes_contain_the_exact_ones():
+    """Decode every quantised cluster the way a reader of the format would (org + q * 2^(ex-127), float arithmetic)
+    and check containment with at least a quarter step of margin on the low side (emul_bvh4q_check)."""
+    from emulapi import EmulScene
+    for desc in (synth.soup_scene(30000), synth.terrain_scene(121, 91), synth.instanced_scene(3, 24)):
+        e = EmulScene(desc, 44)
+        bad, nodes, worst = e.bvh4q_check()
+        assert nodes > 0 and bad == 0, (bad, nodes)
+        assert worst <= 1.25 / 127.0 * 1.05, worst         # a box grows by at most 1.25 steps per side, a step is at most 1/127 of the cluster extent (power-of-two steps)

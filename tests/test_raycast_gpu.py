@@ -6,7 +6,7 @@ import numpy as np
 import pytest
 
 from conftest import needs_ref
-from pathtracing_b200 import synth
+from pathtracing_b200 import capi, synth
 from pathtracing_b200.scene import GpuScene, SceneDesc
 
 pytestmark = pytest.mark.gpu
@@ -128,6 +128,94 @@ def test_bvh2_and_bvh4_agree_at_full_size():
     assert (p >= lo - 1e-4).all() and (p <= hi + 1e-4).all()
     g2.close()
     g4.close()
+
+
+# ---- BASELINE.json C2 at its real size, against the reference itself (oracle/_ref), not GPU-vs-GPU ----------------------
+# 1 000 000 triangles, the two meshes SURVEY.md section 8d names (triangle soup, displaced-grid "surface"), 2 Mi incoherent rays
+# (a prefix-sized sample of the 16 Mi-ray set the bench times: the reference does ~3.5 Mrays/s on the box's host threads),
+# BVH2 / BVH4 / BVH8: primitive ids, the bits of t and the any-hit flags.  Reference side: BVH.hpp:503-548, 1111-1211.
+
+def _full_size_scene(mesh):
+    return synth.soup_scene(1_000_000) if mesh == "soup" else synth.terrain_scene(1001, 501)      # 1000 x 500 x 2 triangles
+
+
+@needs_ref
+@pytest.mark.parametrize("mesh", ["soup", "surface"])
+@pytest.mark.parametrize("width", [4, 2, 8])
+def test_c2_full_size_against_the_reference(mesh, width):
+    from oracle.refapi import RefScene
+    d = _full_size_scene(mesh)
+    ref = RefScene(d, width, id_mode=True)
+    gpu = GpuScene(d, width, layout=capi.LAYOUT_EXACT)
+    lo, hi = ref.bounds()
+    rays = synth.random_rays(1 << 21, lo, hi, seed=7)
+    rh, _ = ref.trace_closest(rays)
+    gh, _ = gpu.trace_closest(rays, want_inst=False)
+    assert np.array_equal(rh["prim"], gh["prim"])
+    assert np.array_equal(rh["t"].view(np.uint32), gh["t"].view(np.uint32))
+    assert (rh["prim"] != 0xFFFFFFFF).mean() > 0.2
+    k = 1 << 20                                        # any-hit on half of them, with finite and infinite tmax
+    sh = rays[:k].copy()
+    sh["tmax"][: k // 2] = 0.35
+    assert np.array_equal(ref.trace_any(sh), gpu.trace_any(sh))
+    assert gpu.stack_overflows() == 0
+    gpu.close(); ref.close()
+
+
+# ---- PT_LAYOUT_FAST: quantised clusters, same tree ------------------------------------------------------------------------
+
+def _cmp_fast(desc, n_rays=200000, tmax=np.inf, seed=7, allow=0):
+    """Same closest hit as the reference (ids, bits of t, any-hit flag); `allow` bounds the rays where the fast layout,
+    whose boxes contain the reference's, finds a hit that the reference's box arithmetic rounds away (never the reverse)."""
+    from oracle.refapi import RefScene
+    ref = RefScene(desc, 4, id_mode=True)
+    gpu = GpuScene(desc, 4, layout=capi.LAYOUT_FAST)
+    lo, hi = ref.bounds()
+    rays = synth.random_rays(n_rays, lo, hi, seed=seed, tmax=tmax)
+    rh, ri = ref.trace_closest(rays, want_inst=True)
+    gh, gi = gpu.trace_closest(rays)
+    diff = (rh["prim"] != gh["prim"]) | (rh["t"].view(np.uint32) != gh["t"].view(np.uint32)) | (ri != gi)
+    assert diff.sum() <= allow, (int(diff.sum()), rh[diff][:4], gh[diff][:4])
+    assert (gh["t"][diff] <= rh["t"][diff]).all()
+    ro, go = ref.trace_any(rays), gpu.trace_any(rays)
+    d2 = ro != go
+    assert d2.sum() <= allow and (go[d2] == 1).all()
+    gpu.close(); ref.close()
+    return rh
+
+
+@needs_ref
+def test_fast_layout_small_scenes():
+    rh = _cmp_fast(synth.soup_scene(100000))
+    assert (rh["prim"] != 0xFFFFFFFF).mean() > 0.2
+    _cmp_fast(synth.soup_scene(100000, opaque=True))
+    _cmp_fast(synth.terrain_scene(301, 201))
+    d = synth.instanced_scene(3, 24)
+    _cmp_fast(d, n_rays=100000)
+    _cmp_fast(d, n_rays=50000, tmax=2.0, seed=11)
+    for n in (1, 2, 3, 5):
+        _cmp_fast(synth.soup_scene(n, seed=5), n_rays=3000)
+    _cmp_fast(synth.shapes_scene()[0], n_rays=50000)
+
+
+@needs_ref
+@pytest.mark.parametrize("mesh", ["soup", "surface"])
+def test_fast_layout_c2_full_size_against_the_reference(mesh):
+    _cmp_fast(_full_size_scene(mesh), n_rays=1 << 21, allow=2)
+
+
+def test_fast_layout_needs_width_4_and_streams_like_the_exact_one():
+    d = synth.soup_scene(20000)
+    with pytest.raises(capi.PtError):
+        GpuScene(d, 8, layout=capi.LAYOUT_FAST)
+    fast, exact = GpuScene(d, 4, layout=capi.LAYOUT_FAST), GpuScene(d, 4)
+    lo, hi = fast.bounds()
+    rays = synth.random_rays((1 << 21) + 777, lo, hi)          # large enough for the streamed host-buffer path
+    hf, i_f = fast.trace_closest(rays)
+    he, ie = exact.trace_closest(rays)
+    assert np.array_equal(hf.view(np.uint8), he.view(np.uint8)) and np.array_equal(i_f, ie)
+    assert np.array_equal(fast.trace_any(rays), exact.trace_any(rays))
+    fast.close(); exact.close()
 
 
 def test_error_paths():
