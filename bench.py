@@ -270,8 +270,10 @@ def bench_render(a, key, torch, dist, world, rank, local, peak, peak_src):
     heavy = total > (1 << 25)
     very_heavy = total > (1 << 30)
     steps = 1 if very_heavy else 2 if heavy else max(2, min(a.steps, 5))
-    # warm-up: whole frames for the light configs, a 16-spp frame of the same scene for the heavy ones (allocates the arena, pages the scene in)
-    warm = params if not heavy else render_params(W, H, min(spp, 16 * world), depth, integrator=integ, seed=2)
+    # warm-up: whole frames, except for the very heavy config (C5: 2 G samples), which warms up on a 64-spp frame of the same
+    # scene -- enough samples per rank to size the wavefront arena as the full frame does (64 Mi slots), so that the timed
+    # frame does not pay a 16 GB cudaMalloc
+    warm = params if not very_heavy else render_params(W, H, min(spp, 64 * world), depth, integrator=integ, seed=2)
     for _ in range(1 if heavy else 3):
         multi.render_sharded(scene, cam, warm, dist if world > 1 else None)
     torch.cuda.synchronize()

@@ -79,6 +79,8 @@ __global__ void __launch_bounds__(kTraceBlock) k_trace(DevScene S, const float4*
         if(dyn.sel_dev)rays += (size_t)(*dyn.sel_dev) * dyn.sel_stride;
         if(n == 0)return;
     }
+    const unsigned leaf_min = refill_min >> 8;       // packed by the launchers: leaf_min << 8 | refill_min
+    refill_min &= 0xFFu;
     extern __shared__ uint2 smem_stack[];            // KS rows of kTraceBlock entries
     uint2 spill[kStack - KS];
     TravStack<KS, KS ? kTraceBlock : 1> stack;
@@ -142,9 +144,18 @@ __global__ void __launch_bounds__(kTraceBlock) k_trace(DevScene S, const float4*
             feed.base += taken; feed.avail -= taken;
             if(feed.exhausted && __all_sync(0xffffffffu, idx == (size_t)-1))break;
         }
+        // postponed leaf processing: the leaf code (triangle test, instance entry / exit) runs in a round only when at least
+        // leaf_min lanes hold a leaf item, or when no live lane has anything else to do
+        bool do_leaf = true;
+        if(leaf_min > 1u){
+            const bool live = !(s.flags & TF_DONE);
+            const bool at_leaf = live && (s.cur & REF_LEAF) && s.cur != REF_EMPTY;
+            const unsigned nl = __popc(__ballot_sync(0xffffffffu, at_leaf)), nv = __popc(__ballot_sync(0xffffffffu, live));
+            do_leaf = nl >= leaf_min || nl == nv;
+        }
         if(!(s.flags & TF_DONE)){
-            if constexpr(FEED)trav_step<WIDTH, ANY, STATS>(s, S, stack, CgRays { rays }, idx, STATS ? &c : nullptr, alpha);
-            else trav_step<WIDTH, ANY, STATS>(s, S, stack, rays, idx, STATS ? &c : nullptr, alpha);
+            if constexpr(FEED)trav_step<WIDTH, ANY, STATS>(s, S, stack, CgRays { rays }, idx, STATS ? &c : nullptr, alpha, do_leaf);
+            else trav_step<WIDTH, ANY, STATS>(s, S, stack, rays, idx, STATS ? &c : nullptr, alpha, do_leaf);
         }
     }
     if(STATS){
@@ -185,7 +196,8 @@ static int env_int(const char* name, int dflt, int lo, int hi){
     int v = e ? atoi(e) : dflt;
     return v < lo ? lo : (v > hi ? hi : v);
 }
-static unsigned refill_min(){ static int v = env_int("PTB_REFILL_MIN", 4, 1, 32); return (unsigned)v; }
+// refill threshold in the low byte, postponed-leaf threshold (PTB_LEAF_MIN, 1 = leaf items are never postponed) above it
+static unsigned refill_min(){ static int v = env_int("PTB_REFILL_MIN", 4, 1, 32) | (env_int("PTB_LEAF_MIN", 1, 1, 32) << 8); return (unsigned)v; }
 // shared-memory stack rows per lane: 0 (all local), 8, 16 or 24
 static int stack_rows(){ static int v = env_int("PTB_STACK_SMEM", 16, 0, 24); return v; }
 

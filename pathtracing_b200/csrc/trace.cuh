@@ -606,7 +606,10 @@ __device__ __forceinline__ void fetch_ray(const CgRays& r, size_t i, float4& a, 
 // holding 9 more registers).
 template <int WIDTH, bool ANY, bool STATS, class STK, class Alpha, class RAYS>
 __device__ __forceinline__ void trav_step(TravState& s, const DevScene& S, const STK& stack, const RAYS& rays, size_t ray_idx,
-                                          TraceCounters* cnt, const Alpha& alpha){
+                                          TraceCounters* cnt, const Alpha& alpha, bool do_leaf = true){
+    // do_leaf == false (decided per warp by the caller, k_trace): a lane that holds a leaf item keeps it for a later
+    // round, so that the leaf code runs when enough lanes of the warp have one (postponed leaf processing)
+    if(!do_leaf && (s.cur & REF_LEAF) && s.cur != REF_EMPTY)return;
     // -- pop (BVH4 closest: cull by entry distance, BVH.hpp:1135) --
     if(s.cur == REF_EMPTY){
         while(s.sp > 0){
@@ -627,7 +630,7 @@ __device__ __forceinline__ void trav_step(TravState& s, const DevScene& S, const
         else node_step8<ANY>(s, S, stack);
     }
     // -- leaf items --
-    if((s.cur & REF_LEAF) && s.cur != REF_EMPTY){
+    if(do_leaf && (s.cur & REF_LEAF) && s.cur != REF_EMPTY){
         if(s.cur == REF_LEAVE){
             // end of TransformedPrimitive::Intersect (Primitive.cpp:54-63): t back to world space
             if(s.flags & TF_XF){

@@ -37,6 +37,7 @@ def run(name, desc, n=1 << 24, widths=((4, 0), (4, 1), (2, 0), (8, 0))):
 
 which = sys.argv[1:] or ["soup", "terrain"]
 if "soup" in which: run("soup 1M", synth.soup_scene(1_000_000))
+if "soup4" in which: run("soup 1M", synth.soup_scene(1_000_000), widths=((4, 0), (4, 1)))
 if "terrain" in which: run("terrain 1M", synth.terrain_scene(1001, 501), widths=((4, 0), (4, 1)))
 if "c5" in which:
     desc, cam = synth.c5_scene()

@@ -55,6 +55,32 @@ def render_case():
     return desc, cam, render_params(24, 24, 4096, 6, seed=11)
 
 
+def c1_case():
+    """BASELINE.json configs[0] as it stands: Cornell box 512x512, depth 8, NEE + MIS (PathIntegrator, PowerLightSampler);
+    the test renders it at the config's 16 spp, the stored reference film is converged further (C1_REF_SPP)."""
+    desc, cam = synth.cornell_scene()
+    return desc, cam, render_params(512, 512, 16, 8, seed=21)
+
+
+C1_REF_SPP = 256
+
+
+def make_c1():
+    """The reference's film of C1 at 256 spp, stored as per-pixel mean and per-sample variance in float16 (3 MB: the rounding,
+    5e-4 relative, is far below the Monte-Carlo noise of the 16-spp frame it is compared with)."""
+    from oracle.refapi import RefScene
+    desc, cam, p = c1_case()
+    q = render_params(p.width, p.height, C1_REF_SPP, p.max_depth, seed=5)
+    ref = RefScene(desc, 4, flavour="fast" if __import__("oracle.refapi").refapi.available("fast") else "strict")
+    rgbw, sq, stats = ref.render(cam, q)
+    ref.close()
+    mean = rgbw[..., :3] / rgbw[..., 3:4]
+    var = np.maximum(sq / C1_REF_SPP - mean ** 2, 0.0) * C1_REF_SPP / (C1_REF_SPP - 1)
+    np.savez_compressed(OUT / "render_c1_512_depth8.npz", mean=mean.astype(np.float16), var=var.astype(np.float16), spp=C1_REF_SPP,
+                        digest=scene_digest(desc))
+    print("c1", stats, "mean radiance", float(mean.mean()))
+
+
 def main():
     from oracle.refapi import RefScene
     for name, desc, box, timed in raycast_cases():
@@ -80,7 +106,11 @@ def main():
     ref.close()
     np.savez_compressed(OUT / "render_cornell_path.npz", rgbw=rgbw, sumsq=sq, spp=p.spp, digest=scene_digest(desc))
     print("render", stats)
+    make_c1()
 
 
 if __name__ == "__main__":
-    main()
+    if len(sys.argv) > 1 and sys.argv[1] == "c1":
+        make_c1()           # only the C1 film (the other fixtures stay as they are)
+    else:
+        main()

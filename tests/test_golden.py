@@ -117,3 +117,91 @@ def _render_vs_golden(g, desc, cam, p, spp):
     assert mse <= 1e-3 + 2.0 * floor, (mse, floor)
     assert (np.abs(z) > 3).mean() <= 0.01 and abs(z.mean()) <= 0.08 and z.std() <= 1.12, ((np.abs(z) > 3).mean(), z.mean(), z.std())
     assert np.allclose(a.mean(axis=(0, 1)), b.mean(axis=(0, 1)), rtol=0.01)
+
+
+# ---- BASELINE.json configs[0] at its real size: Cornell 512 x 512, 16 spp, depth 8, NEE + MIS ------------------------------
+def _c1_stats(a, va, na, b, vb, nb):
+    """per-pixel z between two films with per-sample variances va / vb at na / nb samples per pixel"""
+    sigma = np.sqrt(va / na + vb / nb)
+    ok = sigma > 1e-12
+    z = (a - b)[ok] / sigma[ok]
+    floor = float((sigma ** 2).sum() / (b ** 2).sum())
+    mse = float(((a - b) ** 2).sum() / (b ** 2).sum())
+    return z, mse, floor
+
+
+def _c1_gpu(p):
+    from pathtracing_b200.scene import GpuScene
+    desc, cam, _ = make_golden.c1_case()
+    gpu = GpuScene(desc, 4)
+    st = gpu.render(cam, p)
+    rgbw, sq = gpu.film(), gpu.film_sumsq()
+    gpu.close()
+    assert st["samples"] == p.width * p.height * p.spp
+    a = rgbw[..., :3] / rgbw[..., 3:4]
+    va = np.maximum(sq / p.spp - a ** 2, 0.0) * p.spp / (p.spp - 1)
+    return a, va, st
+
+
+@pytest.mark.gpu
+def test_c1_full_config_against_the_stored_reference_film():
+    """The config as BASELINE.json states it (512 x 512, 16 spp, depth 8) against the reference's stored 256-spp film of the
+    same scene: relMSE above the noise floor <= 1e-3, per-pixel means within 3 sigma as a normal law allows, no bias, channel
+    means within 1 %.  A first failure is reported (not swallowed) and must reproduce with independent samples to count."""
+    g = np.load(GOLDEN / "render_c1_512_depth8.npz")
+    desc, cam, p = make_golden.c1_case()
+    if str(g["digest"]) != make_golden.scene_digest(desc):
+        pytest.fail("golden C1 film was made from a different Cornell scene: regenerate it (python tests/golden/make_golden.py c1)")
+    b, vb, nb = g["mean"].astype(np.float64), g["var"].astype(np.float64), int(g["spp"])
+
+    def once(seed):
+        p.seed = seed
+        a, va, st = _c1_gpu(p)
+        z, mse, floor = _c1_stats(a, va, p.spp, b, vb, nb)
+        out = {"rel_mse": mse, "noise_floor": floor, "z_frac": float((np.abs(z) > 3).mean()), "z_bias": float(z.mean()), "z_std": float(z.std()),
+               "gpu_mean": a.mean(axis=(0, 1)), "ref_mean": b.mean(axis=(0, 1)), "rays_per_sample": (st["closest_rays"] + st["shadow_rays"]) / st["samples"]}
+        assert mse <= 1e-3 + 2.0 * floor, out
+        # a 16-spp estimate of a skewed integrand is not normal: 3-sigma outliers run a little above 0.27 % (calibrated on
+        # reference-vs-reference renders of this scene, scratch/calib.py); a lobe or stream error moves all three numbers
+        assert out["z_frac"] <= 0.012 and abs(out["z_bias"]) <= 0.05 and out["z_std"] <= 1.12, out
+        assert np.allclose(out["gpu_mean"], out["ref_mean"], rtol=0.01), out
+        return out
+
+    try:
+        once(21)
+    except AssertionError as first:
+        import warnings
+        warnings.warn(f"C1 comparison failed once, repeating with independent samples: {str(first)[:400]}")
+        once(22)
+
+
+@needs_ref
+@pytest.mark.gpu
+def test_c1_full_config_against_the_live_reference():
+    """The same frame against the reference itself rendering it now (oracle/_ref, all host threads, 16 spp like the config)."""
+    from oracle.refapi import RefScene
+    from oracle import refapi
+    desc, cam, p = make_golden.c1_case()
+    ref = RefScene(desc, 4, count_rays=True, flavour="fast" if refapi.available("fast") else "strict")
+    r_rgbw, r_sq, r_st = ref.render(cam, p)
+    ref.close()
+    b = r_rgbw[..., :3] / r_rgbw[..., 3:4]
+    vb = np.maximum(r_sq / p.spp - b ** 2, 0.0) * p.spp / (p.spp - 1)
+
+    def once(seed):
+        p.seed = seed
+        a, va, st = _c1_gpu(p)
+        z, mse, floor = _c1_stats(a, va, p.spp, b, vb, p.spp)
+        out = {"rel_mse": mse, "noise_floor": floor, "z_frac": float((np.abs(z) > 3).mean()), "z_bias": float(z.mean()), "z_std": float(z.std())}
+        assert r_st["samples"] == st["samples"]
+        assert mse <= 1e-3 + 2.0 * floor and out["z_frac"] <= 0.012 and abs(out["z_bias"]) <= 0.05 and out["z_std"] <= 1.12, out
+        assert np.allclose(a.mean(axis=(0, 1)), b.mean(axis=(0, 1)), rtol=0.01), out
+        # and the two trace the same number of rays per sample (path lengths, NEE decisions)
+        assert abs((st["closest_rays"] + st["shadow_rays"]) / st["samples"] - (r_st["closest_rays"] + r_st["shadow_rays"]) / r_st["samples"]) < 0.02
+
+    try:
+        once(31)
+    except AssertionError as first:
+        import warnings
+        warnings.warn(f"C1 live comparison failed once, repeating with independent samples: {str(first)[:400]}")
+        once(32)
