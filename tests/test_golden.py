@@ -120,14 +120,38 @@ def _render_vs_golden(g, desc, cam, p, spp):
 
 
 # ---- BASELINE.json configs[0] at its real size: Cornell 512 x 512, 16 spp, depth 8, NEE + MIS ------------------------------
-def _c1_stats(a, va, na, b, vb, nb):
-    """per-pixel z between two films with per-sample variances va / vb at na / nb samples per pixel"""
-    sigma = np.sqrt(va / na + vb / nb)
-    ok = sigma > 1e-12
-    z = (a - b)[ok] / sigma[ok]
-    floor = float((sigma ** 2).sum() / (b ** 2).sum())
+# A 16-spp estimate of this integrand is heavy-tailed (rare bright paths), and a pixel's sample variance is correlated with
+# its own mean error, so a z-score built from the frame's OWN 16-sample variance is neither normal nor centred: the reference
+# rendering the config against its own stored 256-spp film gives 3.3 % of pixels beyond 3 sigma and a mean z of -0.33 that way.
+# The statistics below were therefore calibrated on exactly that experiment (reference at 16 spp vs the stored film, three
+# draws; numbers in brackets), and the thresholds leave the usual margin:
+#   pixel level, variance = mean of the two films' per-sample variances:  beyond 3 sigma [0.21-0.23 %] <= 0.6 %, std(z) [0.966-0.968] <= 1.06
+#   16 x 16 blocks (256 px x 16 spp: near normal), variance from the stored film:  mean z [-0.012..0.000] within 0.05, std(z) [1.02-1.07] <= 1.15,
+#                                                                                 beyond 3 sigma [0.8-1.0 %] <= 2 %
+#   relative MSE [0.0014-0.0015, all of it Monte-Carlo noise: floor 0.0015] <= 1e-3 + 2 x floor;  channel means within 1 %
+def _blocks(x, k=16):
+    h, w, c = x.shape
+    return x.reshape(h // k, k, w // k, k, c).mean(axis=(1, 3))
+
+
+def _c1_compare(a, va, na, b, vb, nb):
+    """GPU film (mean a, per-sample variance va, na spp) against a reference film (b, vb, nb spp) of C1"""
+    s2 = 0.5 * (va + vb) / na + vb / nb
+    ok = s2 > 1e-24
+    z = (a - b)[ok] / np.sqrt(s2[ok])
+    floor = float((vb * (1.0 / na + 1.0 / nb)).sum() / (b ** 2).sum())
     mse = float(((a - b) ** 2).sum() / (b ** 2).sum())
-    return z, mse, floor
+    k = 16
+    sb = _blocks(vb, k) / (k * k) * (1.0 / na + 1.0 / nb)
+    zb = ((_blocks(a, k) - _blocks(b, k)) / np.sqrt(np.maximum(sb, 1e-30)))[sb > 1e-24]
+    out = {"rel_mse": mse, "noise_floor": floor, "pixel_z_frac": float((np.abs(z) > 3).mean()), "pixel_z_std": float(z.std()),
+           "block_z_bias": float(zb.mean()), "block_z_std": float(zb.std()), "block_z_frac": float((np.abs(zb) > 3).mean()),
+           "gpu_mean": a.mean(axis=(0, 1)), "ref_mean": b.mean(axis=(0, 1))}
+    assert mse <= 1e-3 + 2.0 * floor, out
+    assert out["pixel_z_frac"] <= 0.006 and out["pixel_z_std"] <= 1.06, out
+    assert abs(out["block_z_bias"]) <= 0.05 and out["block_z_std"] <= 1.15 and out["block_z_frac"] <= 0.02, out
+    assert np.allclose(out["gpu_mean"], out["ref_mean"], rtol=0.01), out
+    return out
 
 
 def _c1_gpu(p):
@@ -143,11 +167,20 @@ def _c1_gpu(p):
     return a, va, st
 
 
+def _twice(fn, what, seeds):
+    """a failed statistical comparison is REPORTED and has to reproduce with independent samples before it counts"""
+    try:
+        return fn(seeds[0])
+    except AssertionError as first:
+        import warnings
+        warnings.warn(f"{what} failed once, repeating with independent samples: {str(first)[:600]}")
+        return fn(seeds[1])
+
+
 @pytest.mark.gpu
 def test_c1_full_config_against_the_stored_reference_film():
     """The config as BASELINE.json states it (512 x 512, 16 spp, depth 8) against the reference's stored 256-spp film of the
-    same scene: relMSE above the noise floor <= 1e-3, per-pixel means within 3 sigma as a normal law allows, no bias, channel
-    means within 1 %.  A first failure is reported (not swallowed) and must reproduce with independent samples to count."""
+    same scene (tests/golden/render_c1_512_depth8.npz, made by make_golden.py c1)."""
     g = np.load(GOLDEN / "render_c1_512_depth8.npz")
     desc, cam, p = make_golden.c1_case()
     if str(g["digest"]) != make_golden.scene_digest(desc):
@@ -157,28 +190,16 @@ def test_c1_full_config_against_the_stored_reference_film():
     def once(seed):
         p.seed = seed
         a, va, st = _c1_gpu(p)
-        z, mse, floor = _c1_stats(a, va, p.spp, b, vb, nb)
-        out = {"rel_mse": mse, "noise_floor": floor, "z_frac": float((np.abs(z) > 3).mean()), "z_bias": float(z.mean()), "z_std": float(z.std()),
-               "gpu_mean": a.mean(axis=(0, 1)), "ref_mean": b.mean(axis=(0, 1)), "rays_per_sample": (st["closest_rays"] + st["shadow_rays"]) / st["samples"]}
-        assert mse <= 1e-3 + 2.0 * floor, out
-        # a 16-spp estimate of a skewed integrand is not normal: 3-sigma outliers run a little above 0.27 % (calibrated on
-        # reference-vs-reference renders of this scene, scratch/calib.py); a lobe or stream error moves all three numbers
-        assert out["z_frac"] <= 0.012 and abs(out["z_bias"]) <= 0.05 and out["z_std"] <= 1.12, out
-        assert np.allclose(out["gpu_mean"], out["ref_mean"], rtol=0.01), out
-        return out
+        return _c1_compare(a, va, p.spp, b, vb, nb)
 
-    try:
-        once(21)
-    except AssertionError as first:
-        import warnings
-        warnings.warn(f"C1 comparison failed once, repeating with independent samples: {str(first)[:400]}")
-        once(22)
+    _twice(once, "C1 against the stored film", (21, 22))
 
 
 @needs_ref
 @pytest.mark.gpu
 def test_c1_full_config_against_the_live_reference():
-    """The same frame against the reference itself rendering it now (oracle/_ref, all host threads, 16 spp like the config)."""
+    """The same frame against the reference itself rendering the config now (oracle/_ref, all host threads, 16 spp): the criteria
+    of tests/test_render_gpu.py (symmetric: both films carry 16 samples per pixel), plus the rays traced per sample."""
     from oracle.refapi import RefScene
     from oracle import refapi
     desc, cam, p = make_golden.c1_case()
@@ -191,17 +212,16 @@ def test_c1_full_config_against_the_live_reference():
     def once(seed):
         p.seed = seed
         a, va, st = _c1_gpu(p)
-        z, mse, floor = _c1_stats(a, va, p.spp, b, vb, p.spp)
+        s2 = (va + vb) / p.spp
+        ok = s2 > 1e-24
+        z = (a - b)[ok] / np.sqrt(s2[ok])
+        floor = float(s2.sum() / (b ** 2).sum())
+        mse = float(((a - b) ** 2).sum() / (b ** 2).sum())
         out = {"rel_mse": mse, "noise_floor": floor, "z_frac": float((np.abs(z) > 3).mean()), "z_bias": float(z.mean()), "z_std": float(z.std())}
         assert r_st["samples"] == st["samples"]
-        assert mse <= 1e-3 + 2.0 * floor and out["z_frac"] <= 0.012 and abs(out["z_bias"]) <= 0.05 and out["z_std"] <= 1.12, out
+        assert mse <= 1e-3 + 2.0 * floor and out["z_frac"] <= 0.01 and abs(out["z_bias"]) <= 0.08 and out["z_std"] <= 1.12, out
         assert np.allclose(a.mean(axis=(0, 1)), b.mean(axis=(0, 1)), rtol=0.01), out
         # and the two trace the same number of rays per sample (path lengths, NEE decisions)
         assert abs((st["closest_rays"] + st["shadow_rays"]) / st["samples"] - (r_st["closest_rays"] + r_st["shadow_rays"]) / r_st["samples"]) < 0.02
 
-    try:
-        once(31)
-    except AssertionError as first:
-        import warnings
-        warnings.warn(f"C1 live comparison failed once, repeating with independent samples: {str(first)[:400]}")
-        once(32)
+    _twice(once, "C1 against the live reference", (31, 32))
