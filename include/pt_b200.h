@@ -154,7 +154,11 @@ typedef enum pt_light_kind {
     PT_LIGHT_GRADIENT_INFINITE = 1,/* FunctionInfiniteLight Light.cpp:53-108 with
                                       the gradient sky every reference scene uses
                                       (main.cpp:108-111):
-                                      scale*((1-a)*color + a*color_b), a=.5*(d.y+1) */
+                                      scale*((1-a)*color + a*color_b), a=.5*(d.y+1);
+                                      tex >= 0 instead: any other sky function, baked
+                                      by the host into a lat-long float texture
+                                      (GetSphereUV parametrisation) that Le reads;
+                                      sampling and pdf stay uniform on the sphere   */
     PT_LIGHT_TEXTURE_INFINITE = 2, /* TextureInfiniteLight  Light.cpp:110-200 */
     PT_LIGHT_DISTANT = 3,          /* DistantLight          Light.cpp:202-227 */
     PT_LIGHT_POINT = 4             /* PointLight            Light.cpp:229-251 */

@@ -765,3 +765,23 @@ PT_API int ref_unit_hg(float g, size_t n, const float* in, float* out){
 }
 
 } // extern "C"
+
+// ---- the reference's own film writers (Film.hpp:154-217) on caller-chosen pixel values -------------------------------
+// rgb: W*H*3 floats, row 0 = the film's row 0 (bottom row of the written image).  Every pixel receives ONE sample of that
+// radiance through the reference's FilmTile::Add / Film::Merge with a box filter (weight 1), so the film holds exactly
+// these values; then Film::WritePPM / WritePNG / WriteJPG with the reference's default tone mapper write
+// <path_noext>.ppm / .png / .jpg.  fmt: 0 ppm, 1 png, 2 jpg.
+extern "C" int ref_film_write(const float* rgb, int W, int H, const char* path_noext, int fmt, int quality){
+    auto film = std::make_shared<Film>(glm::ivec2 { W, H }, std::make_shared<BoxFilter>());
+    FilmTile tile = film->GetFilmTile({ {0,0},{W,H} });
+    for(int y = 0;y < H;y++)for(int x = 0;x < W;x++){
+        const float* c = rgb + 3 * ((size_t)y * W + x);
+        tile.Add(glm::dvec2 { x + 0.5, y + 0.5 }, glm::dvec3 { c[0], c[1], c[2] });
+    }
+    film->Merge(tile);
+    film->setOutputPath(std::filesystem::path(path_noext));
+    if(fmt == 0)film->WritePPM("unused");
+    else if(fmt == 1)film->WritePNG("unused");
+    else film->WriteJPG("unused", quality);
+    return 0;
+}

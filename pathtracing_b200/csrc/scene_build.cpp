@@ -135,6 +135,7 @@ int scene_animate(pt_scene* s, int prim_id, const float* dir, const float* tb){
 int scene_add_light(pt_scene* s, const pt_light_desc* d){
     if(!d || d->kind < 0 || d->kind > PT_LIGHT_POINT){ set_error("bad light"); return PT_ERR_INVALID; }
     if(d->kind == PT_LIGHT_TEXTURE_INFINITE && (d->tex < 0 || d->tex >= (int)s->textures.size())){ set_error("light texture id out of range"); return PT_ERR_INVALID; }
+    if(d->kind == PT_LIGHT_GRADIENT_INFINITE && d->tex >= (int)s->textures.size()){ set_error("light texture id out of range"); return PT_ERR_INVALID; }
     s->lights.push_back(*d);
     return (int)s->lights.size() - 1;
 }

@@ -240,6 +240,11 @@ PT_HDI V3 sphere_dir(float ux, float uy){
 PT_HDI V3 inf_Le(const ShadeScene& S, const DevLight& L, V3 dir){
     if(L.kind == DL_UNIFORM_INF)return ld3(L.color);
     if(L.kind == DL_GRADIENT_INF){
+        if(L.tex >= 0){     // a FunctionInfiniteLight whose sky function the host baked into a lat-long table (host/PathTracing.hpp)
+            float u, v;
+            sphere_uv(dir, u, v);
+            return tex_eval(S, L.tex, u, v, v3(0.0f));
+        }
         const float a = 0.5f * (dir.y + 1.0f);
         return L.scale * ((1.0f - a) * ld3(L.color) + a * ld3(L.color_b));
     }

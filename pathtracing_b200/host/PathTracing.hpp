@@ -26,6 +26,7 @@
 #include <glm/glm.hpp>
 
 #include "pt_b200.h"
+#include "ImageIO.hpp"
 
 namespace ptb_host {
 
@@ -107,11 +108,25 @@ private:
     glm::vec3 color;
 };
 
-// The reference builds image textures from a file name (stb_image, Texture.cpp:4-36).  Decoding is host
-// I/O outside the hot path: here the caller hands over the decoded texels (row 0 first, 1-4 channels,
-// sRGB->linear already applied if the reference would have loaded with gammaCorrection).
+// The reference builds image textures from a file name (Texture.hpp:139, Image::Image Texture.cpp:4-19: stbi_load, then the
+// sRGB -> linear LUT of Texture.hpp:26-34 on the colour channels when gammaCorrection is set).  Same constructor here, decoding
+// through ImageIO.hpp (PNG / PPM / BMP / TGA); a second constructor takes texels that are already decoded (row 0 first, 1-4
+// channels).  `invertTex` is accepted and, as in the reference (Texture.hpp:110-119: stored, never read by Evaluate), has no effect.
 class ImageTexture : public Texture {
 public:
+    ImageTexture(const std::string& filename, bool gammaCorrection = false, const glm::vec3& colorScale = glm::vec3(1), bool /*invertTex*/ = false)
+        : Texture(colorScale){
+        ptb_io::ImageU8 img = ptb_io::load_u8(filename);        // throws where the reference aborts (Texture.cpp:6-9)
+        width = img.width; height = img.height; channels = img.channels; texels = std::move(img.data);
+        if(gammaCorrection){
+            uint8_t lut[256];
+            for(int i = 0; i < 256; i++){
+                const double srgb = i / 255.0, lin = srgb <= 0.04045 ? srgb / 12.92 : std::pow((srgb + 0.055) / 1.055, 2.4);
+                lut[i] = (uint8_t)std::lround(std::min(1.0, std::max(0.0, lin)) * 255.0);
+            }
+            for(size_t i = 0; i < texels.size(); i++)if((int)(i % (size_t)channels) < std::min(channels, 3))texels[i] = lut[texels[i]];
+        }
+    }
     ImageTexture(std::vector<uint8_t> texels, int width, int height, int channels, const glm::vec3& colorScale = glm::vec3(1))
         : Texture(colorScale), texels(std::move(texels)), width(width), height(height), channels(channels){
         if((size_t)width * height * channels != this->texels.size())throw std::invalid_argument("ImageTexture: texel count");
@@ -128,6 +143,11 @@ private:
 
 class FloatImageTexture : public Texture {
 public:
+    // Texture.hpp:170 / FloatImage::FloatImage (Texture.cpp:26-32: stbi_loadf): Radiance .hdr and PFM natively, LDR files as (v / 255)^2.2
+    FloatImageTexture(const std::string& filename, const glm::vec3& colorScale = glm::vec3(1), bool /*invertTex*/ = false) : Texture(colorScale){
+        ptb_io::ImageF32 img = ptb_io::load_f32(filename);
+        width = img.width; height = img.height; channels = img.channels; texels = std::move(img.data);
+    }
     FloatImageTexture(std::vector<float> texels, int width, int height, int channels, const glm::vec3& colorScale = glm::vec3(1))
         : Texture(colorScale), texels(std::move(texels)), width(width), height(height), channels(channels){
         if((size_t)width * height * channels != this->texels.size())throw std::invalid_argument("FloatImageTexture: texel count");
@@ -398,14 +418,64 @@ struct GradientSky {
         return scale * ((1.0f - a) * horizon + a * zenith);
     }
 };
+// FunctionInfiniteLight (Light.hpp:70-93, Light.cpp:53-108) holds a host closure.  The GradientSky functor is evaluated on
+// the device in closed form.  Any other std::function<glm::vec3(const Ray&)> cannot run on the GPU: it is BAKED, once, into a
+// lat-long float table (kBakeW x kBakeH texels at the centres of GetSphereUV cells) that the device reads bilinearly; sampling
+// stays the reference's (uniform on the sphere, pdf 1 / 4 pi), Power() is the reference's mean luminance over the sphere.
+// BakeError() reports what the table costs: the largest and the mean absolute difference between the function and the
+// table's bilinear value at 20 000 directions, relative to the function's mean luminance.
 class FunctionInfiniteLight : public InfiniteLight {
 public:
+    static constexpr int kBakeW = 1024, kBakeH = 512;
+    struct Error { double max_rel = 0, mean_rel = 0; };
     FunctionInfiniteLight(const GradientSky& lightFunc, PowerFunction powerFunc = PowerFunction::SqrtR) : sky(lightFunc), pf(powerFunc){}
-    void Describe(ptb_host::Builder&, pt_light_desc& d) const override{
-        d.kind = PT_LIGHT_GRADIENT_INFINITE; set3(d.color, sky.horizon); set3(d.color_b, sky.zenith); d.scale = sky.scale; d.power_func = (int)pf;
+    FunctionInfiniteLight(const std::function<glm::vec3(const Ray&)>& lightFunc, PowerFunction powerFunc = PowerFunction::SqrtR) : pf(powerFunc){ Bake(lightFunc); }
+    void Describe(ptb_host::Builder& b, pt_light_desc& d) const override{
+        d.kind = PT_LIGHT_GRADIENT_INFINITE; d.power_func = (int)pf;
+        if(table){ d.tex = table->Emit(b); d.scale = 1.0f; }
+        else{ set3(d.color, sky.horizon); set3(d.color_b, sky.zenith); d.scale = sky.scale; }
     }
+    bool Baked() const{ return table != nullptr; }
+    Error BakeError() const{ return err; }
 private:
+    static glm::vec3 Dir(double u, double v){          // inverse of SphereShape::GetSphereUV (Shape.hpp): u = phi / 2 pi, v = theta / pi, y up
+        const double phi = 2.0 * 3.14159265358979323846 * u, theta = 3.14159265358979323846 * v;
+        return glm::vec3((float)(std::sin(theta) * std::cos(phi)), (float)std::cos(theta), (float)(std::sin(theta) * std::sin(phi)));
+    }
+    void Bake(const std::function<glm::vec3(const Ray&)>& f){
+        std::vector<float> tex((size_t)kBakeW * kBakeH * 3);
+        for(int y = 0; y < kBakeH; y++)for(int x = 0; x < kBakeW; x++){
+            const glm::vec3 c = f(Ray(glm::vec3(0, 0, 0), Dir((x + 0.5) / kBakeW, (y + 0.5) / kBakeH)));
+            float* t = &tex[((size_t)y * kBakeW + x) * 3];
+            t[0] = c.x; t[1] = c.y; t[2] = c.z;
+        }
+        // error of the bilinear read-back (repeat wrap in u, clamp in v as the device texture fetch does near the poles)
+        auto fetch = [&](double u, double v, int ch){
+            const double fx = u * kBakeW - 0.5, fy = v * kBakeH - 0.5;
+            const int x0 = (int)std::floor(fx), y0 = (int)std::floor(fy);
+            const double ax = fx - x0, ay = fy - y0;
+            auto at = [&](int x, int y){ x = ((x % kBakeW) + kBakeW) % kBakeW; y = ((y % kBakeH) + kBakeH) % kBakeH; return (double)tex[((size_t)y * kBakeW + x) * 3 + ch]; };
+            return (1 - ay) * ((1 - ax) * at(x0, y0) + ax * at(x0 + 1, y0)) + ay * ((1 - ax) * at(x0, y0 + 1) + ax * at(x0 + 1, y0 + 1));
+        };
+        double lum = 0;
+        for(size_t i = 0; i < tex.size(); i += 3)lum += 0.2126 * tex[i] + 0.7152 * tex[i + 1] + 0.0722 * tex[i + 2];
+        lum = std::max(lum / ((double)kBakeW * kBakeH), 1e-30);
+        uint64_t st = 0x9E3779B97F4A7C15ull;
+        auto rnd = [&](){ st ^= st << 13; st ^= st >> 7; st ^= st << 17; return (double)(st >> 11) / 9007199254740992.0; };
+        double worst = 0, sum = 0; const int n = 20000;
+        for(int k = 0; k < n; k++){
+            const double u = rnd(), v = std::acos(1.0 - 2.0 * rnd()) / 3.14159265358979323846;
+            const glm::vec3 c = f(Ray(glm::vec3(0, 0, 0), Dir(u, v)));
+            double e = 0;
+            for(int ch = 0; ch < 3; ch++)e = std::max(e, std::fabs(fetch(u, v, ch) - (double)c[ch]));
+            worst = std::max(worst, e / lum); sum += e / lum;
+        }
+        err.max_rel = worst; err.mean_rel = sum / n;
+        table = std::make_shared<FloatImageTexture>(std::move(tex), kBakeW, kBakeH, 3);
+    }
     GradientSky sky; PowerFunction pf;
+    std::shared_ptr<FloatImageTexture> table;
+    Error err;
 };
 
 class TextureInfiniteLight : public InfiniteLight {
@@ -897,12 +967,21 @@ public:
         chunk("IDAT", z);
         chunk("IEND", {});
     }
-    // The reference encodes JPEG through stb_image_write (Film.hpp:196-217), a third-party encoder outside
-    // this path: the same tone-mapped image is written losslessly as <filename>.png instead.
-    void WriteJPG(const std::string& filename, int /*quality*/, const std::function<glm::vec3(glm::vec3)>& toneMapper = reinhard_jodie) const{
-        static bool told = false;
-        if(!told){ told = true; std::fprintf(stderr, "Film::WriteJPG: no JPEG encoder on this path, writing %s.png\n", filename.c_str()); }
-        WritePNG(filename, toneMapper);
+    // JPEG, quality 1..100 (Film.hpp:196-217): the same tone-mapped, sRGB-encoded 8-bit image as WritePNG, through the baseline
+    // encoder of ImageIO.hpp (the reference calls stb_image_write; the bytes differ, the decoded image agrees to JPEG accuracy)
+    void WriteJPG(const std::string& filename, int quality, const std::function<glm::vec3(glm::vec3)>& toneMapper = reinhard_jodie) const{
+        const std::vector<uint8_t> rgb = ToneMapped8(toneMapper);
+        ptb_io::write_jpg((outputPath.empty() ? filename : outputPath) + ".jpg", xResolution, yResolution, rgb.data(), quality);
+    }
+    // the 8-bit image every writer encodes: top row first, tone-mapped, sRGB-encoded, 255.999 * clamp (Film.hpp:160-168)
+    std::vector<uint8_t> ToneMapped8(const std::function<glm::vec3(glm::vec3)>& toneMapper = reinhard_jodie) const{
+        std::vector<uint8_t> rgb((size_t)xResolution * yResolution * 3);
+        size_t k = 0;
+        for(int i = yResolution - 1; i >= 0; i--)for(int j = 0; j < xResolution; j++){
+            const glm::vec3 c = toneMapper(glm::vec3(Pixel(j, i)));
+            for(int a = 0; a < 3; a++)rgb[k++] = (uint8_t)(255.999 * std::max(0.0, std::min(1.0, linear_to_sRGB((double)c[a]))));
+        }
+        return rgb;
     }
 private:
     int xResolution, yResolution;

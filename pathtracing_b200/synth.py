@@ -242,7 +242,16 @@ def procedural_textures(size=64, seed=11):
     return to8(albedo), to8(orm), to8(nm)
 
 
-def materials_scene(subdiv=3, sky=True, point_light=False, distant_light=False):
+def baked_gradient_table(horizon, zenith, scale, w=1024, h=512):
+    """The gradient sky evaluated the way the host API bakes ANY FunctionInfiniteLight sky function (host/PathTracing.hpp):
+    a lat-long float table at the centres of SphereShape::GetSphereUV cells (u = phi / 2 pi, v = theta / pi, y up)."""
+    v = (np.arange(h, dtype=np.float64) + 0.5) / h
+    a = 0.5 * (np.cos(np.pi * v) + 1.0)
+    col = scale * ((1.0 - a)[:, None] * np.asarray(horizon, np.float64)[None] + a[:, None] * np.asarray(zenith, np.float64)[None])
+    return np.ascontiguousarray(np.broadcast_to(col[:, None, :], (h, w, 3)).astype(np.float32))
+
+
+def materials_scene(subdiv=3, sky=True, point_light=False, distant_light=False, baked_sky=False):
     """C3-style: instanced icospheres (TransformedPrimitive) with the four README materials +
     ThinDielectric on a textured ground, a transformed emissive quad (TransformedLight) and a gradient sky."""
     d = SceneDesc()
@@ -277,7 +286,10 @@ def materials_scene(subdiv=3, sky=True, point_light=False, distant_light=False):
     lb = d.add_blas([d.mesh(lp, li, ln, lu, material=d.diffuse(d.solid((0, 0, 0))), emissive_tex=emit)])
     d.instance(lb, trs((0.3, 2.6, 0.2), 1.4, (1, 0, 0.3), 0.5))
     if sky:
-        d.light(capi.LIGHT_GRADIENT_INFINITE, color=(1.0, 1.0, 1.0), color_b=(0.5, 0.7, 1.0), scale=0.6)
+        # baked_sky: the device reads the sky from the baked table (tex >= 0); the colours stay in the descriptor for the reference,
+        # whose FunctionInfiniteLight evaluates the same function in closed form
+        tex = d.image_f32(baked_gradient_table((1.0, 1.0, 1.0), (0.5, 0.7, 1.0), 0.6)) if baked_sky else -1
+        d.light(capi.LIGHT_GRADIENT_INFINITE, color=(1.0, 1.0, 1.0), color_b=(0.5, 0.7, 1.0), scale=0.6, tex=tex)
     if point_light:
         d.light(capi.LIGHT_POINT, color=(6, 5, 4), v=(-1.5, 2.0, 1.0), power_func=1)
     if distant_light:

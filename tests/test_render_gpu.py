@@ -215,6 +215,15 @@ def test_materials_instances_sky():
 
 
 @needs_ref
+def test_function_infinite_light_baked_into_a_table():
+    """Any sky function other than the GradientSky functor reaches the device as a baked lat-long table (FunctionInfiniteLight,
+    Light.hpp:74; host/PathTracing.hpp).  Here the table holds the gradient sky itself, so the reference (closed form) renders
+    the same scene: same image within the usual criteria, uniform-sphere sampling and its pdf unchanged."""
+    desc, cam = synth.materials_scene(baked_sky=True)
+    compare(desc, cam, 64, 48, 1024, 12)
+
+
+@needs_ref
 def test_materials_point_and_distant_lights():
     desc, cam = synth.materials_scene(sky=False, point_light=True, distant_light=True)
     compare(desc, cam, 48, 36, 1024, 8)
