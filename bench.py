@@ -452,6 +452,25 @@ def run_ours(a):
         torch.cuda.synchronize()
         pcie[name] = 3 * src.numel() * src.element_size() / (e0.elapsed_time(e1) * 1e-3) / 1e9
     e2e_floor_ms = max(n * 32 / pcie["h2d"], n * 16 / pcie["d2h"]) / 1e6
+    # what the host memory system gives a rank while ALL ranks use it at once (one NUMA node feeds every GPU's copy engines):
+    # a plain host-to-host copy of the ray buffer, every rank at the same time.  The e2e figure at N >= 4 is bound by this, not
+    # by a kernel or a link (per-rank PCIe rates fall with N, SCALE_r01.json).
+    scratch = np.empty(n * 32, np.uint8)
+    src_np = host_rays.numpy()
+    np.copyto(scratch, src_np)
+    if world > 1:
+        dist.barrier()
+    t0 = time.perf_counter()
+    for _ in range(2):
+        np.copyto(scratch, src_np)
+    host_copy_gbs = 2 * 2 * n * 32 / (time.perf_counter() - t0) / 1e9       # bytes read + written
+    del scratch
+    if world > 1:
+        t = torch.tensor([host_copy_gbs, pcie["h2d"], pcie["d2h"]], device="cuda", dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MIN)
+        host_copy_gbs, pcie_min = float(t[0].item()), (float(t[1].item()), float(t[2].item()))
+    else:
+        pcie_min = (pcie["h2d"], pcie["d2h"])
     # the result really came back: hit count of the host buffer
     hits_np = host_hits.numpy().view(np.dtype([("t", "<f4"), ("u", "<f4"), ("v", "<f4"), ("prim", "<u4")]))
     hit_rate = float((hits_np["prim"] != 0xFFFFFFFF).mean())
@@ -566,6 +585,10 @@ def run_ours(a):
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": n * 32, "d2h_bytes_per_step": n * 16,
                     "ms_per_step": e2e_ms, "api": e2e_api,
                     "pcie_h2d_gbs": pcie["h2d"], "pcie_d2h_gbs": pcie["d2h"], "pcie_floor_ms": e2e_floor_ms,
+                    "pcie_h2d_gbs_min_over_ranks": pcie_min[0], "pcie_d2h_gbs_min_over_ranks": pcie_min[1],
+                    "host_copy_gbs_per_rank_all_ranks_at_once": host_copy_gbs,
+                    "limiter": ("the kernel (PCIe floor of the same buffers is below the step time)" if world == 1 else
+                                "host memory: every rank moves 48 B per ray through one NUMA node's DRAM; per-rank pinned-copy and host-copy rates fall with the rank count"),
                     "note": "floor = the slower of the two plain pinned copies of one step's buffers on this box"},
             "gpu_launches": a.steps, "gpu_launches_e2e": e2e_steps * chunks,
             "clocks": clocks, "roofline": roofline, "cpu_baseline": cpu, "extras": extras}

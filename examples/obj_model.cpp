@@ -1,5 +1,6 @@
 // obj_model.cpp — Model(path) / ResourceManager::CacheModel<BLAS4>(name, path) as the reference's model scenes use
-// them (main.cpp:290,376-381,483), over the Wavefront OBJ / MTL importer of the host API (ObjImport.hpp).
+// them (main.cpp:290,376-381,483), over the importers of the host API: Wavefront OBJ / MTL (ObjImport.hpp) and glTF 2.0
+// .gltf / .glb (GltfImport.hpp), picked by the file extension.
 //
 //   ./obj_model file.obj                 -> one JSON line with the imported meshes (no device needed)
 //   ./obj_model file.obj width height spp -> also renders it under a gradient sky + its own emitters (GPU)
@@ -8,6 +9,7 @@
 #include <memory>
 
 #include "Model.hpp"
+#include "Material.hpp"
 #include "ResourceManager.hpp"
 #include "Light.hpp"
 #include "LightSampler.hpp"
@@ -34,6 +36,19 @@ int main(int argc, char** argv){
     }
     printf("{\"meshes\": %zu, \"triangles\": %zu, \"vertices\": %zu, \"emissive_meshes\": %zu, \"meshes_with_tangents\": %zu, \"lo\": [%g, %g, %g], \"hi\": [%g, %g, %g]",
            model->GetMeshes().size(), tris, verts, emissive, tangents, lo.x, lo.y, lo.z, hi.x, hi.y, hi.z);
+    // per mesh: material class, medium, the first vertex as imported (position, normal, uv)
+    printf(", \"per_mesh\": [");
+    bool first = true;
+    for(const std::shared_ptr<Mesh>& m : model->GetMeshes()){
+        const char* kind = std::dynamic_pointer_cast<MicrofacetDiffuse>(m->GetMaterial()) ? "diffuse" : std::dynamic_pointer_cast<MicrofacetDielectric>(m->GetMaterial()) ? "dielectric"
+                         : std::dynamic_pointer_cast<ThinDielectric>(m->GetMaterial()) ? "thin" : std::dynamic_pointer_cast<SpecularConductor>(m->GetMaterial()) ? "conductor" : "other";
+        const glm::vec3 p = m->GetVertices()[0], n = m->GetNormals()[0];
+        const glm::vec2 t = m->GetTexCoords()[0];
+        printf("%s{\"material\": \"%s\", \"medium\": %d, \"emissive\": %d, \"triangles\": %u, \"p0\": [%g, %g, %g], \"n0\": [%g, %g, %g], \"uv0\": [%g, %g]}", first ? "" : ", ", kind,
+               m->GetMedium() ? 1 : 0, m->GetEmissiveTexture() ? 1 : 0, m->GetTriangleCount(), p.x, p.y, p.z, n.x, n.y, n.z, t.x, t.y);
+        first = false;
+    }
+    printf("]");
     if(argc < 5){ printf("}\n"); return 0; }
 
     const int width = atoi(argv[2]), height = atoi(argv[3]);

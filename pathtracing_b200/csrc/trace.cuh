@@ -379,6 +379,22 @@ __device__ __forceinline__ void node_step2(TravState& s, const DevScene& S, cons
     } else s.cur = hf ? fref : REF_EMPTY;
 }
 
+// Up to three pushes of one cluster visit.  Common case (all of them land in the shared-memory rows): predicated
+// stores, no branch per push; the generic path (rows spilling to local memory, overflow) only near the row limit.
+// profiles/r02_trace44_v1.md: with one smem-or-local branch inside each of the four unrolled pushes the push code was
+// 12 % of all instructions of the kernel.
+template <int KS, int STRIDE>
+__device__ __forceinline__ bool stack_fast(const TravStack<KS, STRIDE>&, int sp){ return KS >= 4 && sp + 3 <= KS; }
+__device__ __forceinline__ bool stack_fast(const LocalStack&, int){ return false; }
+template <int KS, int STRIDE>
+__device__ __forceinline__ void stack_st_sm(const TravStack<KS, STRIDE>& k, int i, uint2 v){ k.sm[i * STRIDE] = v; }
+__device__ __forceinline__ void stack_st_sm(const LocalStack& k, int i, uint2 v){ k.lm[i] = v; }
+
+// pop: rows below KS come straight from shared memory (no branch in the common case of a shallow stack)
+template <int KS, int STRIDE>
+__device__ __forceinline__ uint2 stack_ld(const TravStack<KS, STRIDE>& k, int i){ return k.ld(i); }
+__device__ __forceinline__ uint2 stack_ld(const LocalStack& k, int i){ return k.lm[i]; }
+
 __device__ __forceinline__ uint32_t pick4(const uint4& v, unsigned k){
     return k == 0 ? v.x : (k == 1 ? v.y : (k == 2 ? v.z : v.w));
 }
@@ -410,6 +426,7 @@ __device__ __forceinline__ void node_step4(TravState& s, const DevScene& S, cons
     bool ovf = false;
     const unsigned word = s.octant < 4 ? ord.x : ord.y;
     const unsigned code = (word >> ((s.octant & 3u) * 8u)) & 0xFFu;
+    const bool fast = stack_fast(stack, sp);
 #pragma unroll
     for(int k = 0; k < 4; k++){
         uint32_t r; float e; bool hit;
@@ -428,10 +445,15 @@ __device__ __forceinline__ void node_step4(TravState& s, const DevScene& S, cons
             e = hi ? eb : ea;
         }
         const bool want = hit && cur != REF_EMPTY;
-        const bool push = want && sp < kStack;
-        ovf |= want && !push;
-        if(push)stack.st(sp, make_uint2(cur, __float_as_uint(cure)));
-        sp += push ? 1 : 0;
+        if(fast){
+            if(want)stack_st_sm(stack, sp, make_uint2(cur, __float_as_uint(cure)));
+            sp += want ? 1 : 0;
+        } else{
+            const bool push = want && sp < kStack;
+            ovf |= want && !push;
+            if(push)stack.st(sp, make_uint2(cur, __float_as_uint(cure)));
+            sp += push ? 1 : 0;
+        }
         cur = hit ? r : cur;
         cure = hit ? e : cure;
     }
@@ -446,22 +468,6 @@ __device__ __forceinline__ void node_step4(TravState& s, const DevScene& S, cons
 // of these FMAs, so no exact box is ever missed; `e <= tmax` (not the reference's strict `<`) keeps the superset
 // property for candidates at exactly tmax.  Visit order and pop-time cull as in node_step4.
 __device__ __forceinline__ float qbyte(uint32_t w, int c){ return __uint2float_rn((w >> (8 * c)) & 0xFFu); }
-
-// Up to three pushes of one cluster visit.  Common case (all of them land in the shared-memory rows): predicated
-// stores, no branch per push; the generic path (rows spilling to local memory, overflow) only near the row limit.
-// profiles/r02_trace44_v1.md: with one smem-or-local branch inside each of the four unrolled pushes the push code was
-// 12 % of all instructions of the kernel.
-template <int KS, int STRIDE>
-__device__ __forceinline__ bool stack_fast(const TravStack<KS, STRIDE>&, int sp){ return KS >= 4 && sp + 3 <= KS; }
-__device__ __forceinline__ bool stack_fast(const LocalStack&, int){ return false; }
-template <int KS, int STRIDE>
-__device__ __forceinline__ void stack_st_sm(const TravStack<KS, STRIDE>& k, int i, uint2 v){ k.sm[i * STRIDE] = v; }
-__device__ __forceinline__ void stack_st_sm(const LocalStack& k, int i, uint2 v){ k.lm[i] = v; }
-
-// pop: rows below KS come straight from shared memory (no branch in the common case of a shallow stack)
-template <int KS, int STRIDE>
-__device__ __forceinline__ uint2 stack_ld(const TravStack<KS, STRIDE>& k, int i){ return k.ld(i); }
-__device__ __forceinline__ uint2 stack_ld(const LocalStack& k, int i){ return k.lm[i]; }
 
 template <bool ANY, class STK>
 __device__ __forceinline__ void node_step4q(TravState& s, const DevScene& S, const STK& stack){

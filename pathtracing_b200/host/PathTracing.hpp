@@ -617,7 +617,7 @@ private:
 class Model : public Primitive {
 public:
     Model(std::vector<std::shared_ptr<Mesh>> meshes) : meshes(std::move(meshes)){}
-    // Model(path) (Model.cpp:14-18): the reference imports through assimp; here Wavefront OBJ / MTL (ObjImport.hpp).
+    // Model(path) (Model.cpp:14-18): the reference imports through assimp; here Wavefront OBJ / MTL (ObjImport.hpp) and glTF 2.0 (GltfImport.hpp).
     // Throws where the reference prints "Failed to load model" and carries on with an empty model.
     explicit Model(const std::string& path);
     std::vector<std::shared_ptr<Mesh>> GetMeshes() const{ return meshes; }
@@ -1199,4 +1199,5 @@ private:
 };
 
 #include "ObjImport.hpp"
-inline Model::Model(const std::string& path) : meshes(ptb_host::load_obj(path)){}
+#include "GltfImport.hpp"
+inline Model::Model(const std::string& path) : meshes(ptb_host::load_model(path)){}

@@ -270,6 +270,97 @@ def test_obj_import_model_from_path(tmp_path):
     assert r.returncode != 0 and "cannot open" in r.stderr
 
 
+def _write_gltf(d, glb=False):
+    """A two-node glTF 2.0 scene: a quad with normals / uv / u16 indices under a translated + scaled node, and a non-indexed
+    triangle without normals under a rotated child node; three materials (textured metallic-roughness with MASK alpha and an
+    emitter, a transmissive one with a volume -> dielectric + medium, a thin transmissive one)."""
+    import base64
+    import struct
+    import numpy as np
+    from PIL import Image
+    Image.fromarray((np.arange(8 * 8 * 3).reshape(8, 8, 3) % 256).astype(np.uint8), "RGB").save(d / "base.png")
+    quad_p = np.array([[0, 0, 0], [1, 0, 0], [1, 0, 1], [0, 0, 1]], np.float32)
+    quad_n = np.array([[0, 1, 0]] * 4, np.float32)
+    quad_uv = np.array([[0, 0], [1, 0], [1, 1], [0, 0.25]], np.float32)
+    quad_i = np.array([0, 2, 1, 0, 3, 2], np.uint16)
+    tri_p = np.array([[0, 0, 0], [1, 0, 0], [0, 1, 0]], np.float32)
+    blob = b""
+    views, accessors = [], []
+
+    def add(arr, ctype, atype, target=None):
+        nonlocal blob
+        while len(blob) % 4:
+            blob += b"\0"
+        views.append({"buffer": 0, "byteOffset": len(blob), "byteLength": arr.nbytes})
+        acc = {"bufferView": len(views) - 1, "componentType": ctype, "count": len(arr), "type": atype}
+        if atype == "VEC3" and ctype == 5126:
+            acc["min"], acc["max"] = arr.min(0).tolist(), arr.max(0).tolist()
+        accessors.append(acc)
+        blob += arr.tobytes()
+        return len(accessors) - 1
+    a_qp, a_qn, a_quv, a_qi, a_tp = add(quad_p, 5126, "VEC3"), add(quad_n, 5126, "VEC3"), add(quad_uv, 5126, "VEC2"), add(quad_i, 5123, "SCALAR"), add(tri_p, 5126, "VEC3")
+    doc = {
+        "asset": {"version": "2.0"}, "scene": 0, "scenes": [{"nodes": [0]}],
+        "nodes": [{"mesh": 0, "translation": [10, 0, 0], "scale": [2, 1, 3], "children": [1]},
+                  {"mesh": 1, "rotation": [0, 0, 0.70710678, 0.70710678], "translation": [0, 5, 0]}],       # +90 degrees about z
+        "meshes": [{"primitives": [{"attributes": {"POSITION": a_qp, "NORMAL": a_qn, "TEXCOORD_0": a_quv}, "indices": a_qi, "material": 0},
+                                   {"attributes": {"POSITION": a_tp}, "material": 2}]},
+                   {"primitives": [{"attributes": {"POSITION": a_tp}, "material": 1}]}],
+        "materials": [
+            {"pbrMetallicRoughness": {"baseColorFactor": [0.5, 1.0, 0.25, 1.0], "baseColorTexture": {"index": 0}}, "alphaMode": "MASK", "alphaCutoff": 0.3,
+             "emissiveFactor": [1.0, 0.5, 0.0], "extensions": {"KHR_materials_emissive_strength": {"emissiveStrength": 4.0}}},
+            {"extensions": {"KHR_materials_transmission": {"transmissionFactor": 1.0}, "KHR_materials_ior": {"ior": 1.33},
+                            "KHR_materials_volume": {"thicknessFactor": 0.5, "attenuationColor": [0.5, 0.8, 0.9], "attenuationDistance": 2.0}}},
+            {"extensions": {"KHR_materials_transmission": {"transmissionFactor": 1.0}, "KHR_materials_volume": {"thicknessFactor": 0.0}}}],
+        "textures": [{"source": 0}], "images": [{"uri": "base.png"}],
+        "accessors": accessors, "bufferViews": views,
+    }
+    if glb:
+        doc["buffers"] = [{"byteLength": len(blob)}]
+        js = json.dumps(doc).encode()
+        js += b" " * (-len(js) % 4)
+        bin_ = blob + b"\0" * (-len(blob) % 4)
+        out = struct.pack("<III", 0x46546C67, 2, 12 + 8 + len(js) + 8 + len(bin_)) + struct.pack("<II", len(js), 0x4E4F534A) + js + struct.pack("<II", len(bin_), 0x004E4942) + bin_
+        (d / "scene.glb").write_bytes(out)
+        return d / "scene.glb"
+    doc["buffers"] = [{"byteLength": len(blob), "uri": "data:application/octet-stream;base64," + base64.b64encode(blob).decode()}]
+    (d / "scene.gltf").write_text(json.dumps(doc))
+    return d / "scene.gltf"
+
+
+@pytest.mark.parametrize("glb", [False, True])
+def test_gltf_import_model_from_path(tmp_path, glb):
+    """Model(path) over the glTF 2.0 reader (GltfImport.hpp): node transforms baked into the vertices (TRS and nested nodes),
+    flipped V, generated normals, indexed and non-indexed primitives, .gltf with a data-URI buffer and .glb, the material
+    mapping of Model::SetupMaterial for the glTF material model (Model.cpp:123-190) and the volume medium (:343-351)."""
+    path = _write_gltf(tmp_path, glb)
+    _compile(tmp_path / "obj_model", HOST / "glm_min", ROOT / "examples" / "obj_model.cpp")
+    r = subprocess.run([str(tmp_path / "obj_model"), str(path)], capture_output=True, text=True, cwd=tmp_path)
+    assert r.returncode == 0, r.stderr
+    out = json.loads(r.stdout)
+    assert out["meshes"] == 3 and out["triangles"] == 2 + 1 + 1 and out["vertices"] == 4 + 3 + 3
+    quad, tri_root, tri_child = out["per_mesh"]
+    # node 0: translate (10, 0, 0) * scale (2, 1, 3)
+    assert quad["material"] == "diffuse" and quad["emissive"] == 1 and quad["medium"] == 0 and quad["p0"] == [10, 0, 0] and quad["n0"] == [0, 1, 0]
+    assert quad["uv0"] == [0, 1]                                   # V flipped
+    assert tri_root["material"] == "thin" and tri_root["p0"] == [10, 0, 0]
+    assert tri_root["n0"] == [0, 0, 1]                             # generated: the triangle lies in the xy plane
+    # node 1 under node 0: rotate 90 degrees about z, translate (0, 5, 0), then the parent's scale and translation
+    assert tri_child["material"] == "dielectric" and tri_child["medium"] == 1 and tri_child["p0"] == [10, 5, 0]
+    assert out["lo"][0] == pytest.approx(8.0, abs=1e-5) and out["hi"][1] == pytest.approx(6.0, abs=1e-5)    # (0,1,0) -> rotated (-1,0,0) -> scaled (-2,..) + 10
+    assert out["emissive_meshes"] == 1 and out["meshes_with_tangents"] == 1
+
+
+@pytest.mark.gpu
+def test_gltf_import_renders_on_the_gpu(tmp_path):
+    path = _write_gltf(tmp_path)
+    _compile(tmp_path / "obj_model", HOST / "glm_min", ROOT / "examples" / "obj_model.cpp")
+    r = subprocess.run([str(tmp_path / "obj_model"), str(path), "64", "64", "16"], capture_output=True, text=True, cwd=tmp_path, timeout=300)
+    assert r.returncode == 0, r.stderr
+    out = json.loads(r.stdout)
+    assert out["samples"] == 64 * 64 * 16 and all(0.01 < v < 50.0 for v in out["mean"])
+
+
 @pytest.mark.gpu
 def test_obj_import_renders_on_the_gpu(tmp_path):
     _write_obj(tmp_path)
