@@ -328,6 +328,12 @@ private:
 };
 
 // ---- Mesh.hpp:14-95 ---------------------------------------------------------------------------------
+// Shape.hpp:60-116: one triangle of a Mesh.  The reference's Mesh owns a vector of them and hands them out through
+// GetShape(j) + GetControlPtr() (Mesh.hpp:64-69) so that user code can build GeometricPrimitive lists by hand (the recipe of
+// Model::BuildBlas, Model.hpp:47-59).  Defined after Shape below; here only what Mesh needs.
+class Mesh;
+class TriangleShape;
+
 class Mesh {
 public:
     Mesh(const std::vector<uint32_t>& indices, const std::vector<glm::vec3>& vertices, const std::vector<glm::vec3>& tangents,
@@ -348,6 +354,17 @@ public:
     std::shared_ptr<Material> GetMaterial() const{ return material; }
     std::shared_ptr<Texture> GetEmissiveTexture() const{ return emissiveTexture; }
     std::shared_ptr<Medium> GetMedium() const{ return medium; }
+    // Mesh.hpp:64-69: the triangle shapes of this mesh and the control block that keeps them alive (aliasing shared_ptr recipe)
+    inline const std::shared_ptr<std::vector<TriangleShape>>& GetControlPtr() const;
+    inline TriangleShape* GetShape(std::size_t index) const;
+    // the triangles [first, first + count) as a mesh of their own with this mesh's vertex arrays (BLAS lists, below)
+    std::shared_ptr<Mesh> Slice(const std::vector<uint32_t>& tris, const std::shared_ptr<Material>& mat, const std::shared_ptr<Texture>& emissive,
+                                const std::shared_ptr<Medium>& med) const{
+        std::vector<uint32_t> idx;
+        idx.reserve(tris.size() * 3);
+        for(uint32_t t : tris){ idx.push_back(indices[3 * t]); idx.push_back(indices[3 * t + 1]); idx.push_back(indices[3 * t + 2]); }
+        return std::make_shared<Mesh>(idx, vertices, tangents, normals, texCoords, mat, emissive, med);
+    }
 
     // material / medium overrides as Model::BuildBlas(material, medium) applies them (Model.hpp:62-80)
     int Emit(ptb_host::Builder& b, const std::shared_ptr<Material>& matOverride, const std::shared_ptr<Medium>& medOverride, bool overridden) const{
@@ -367,6 +384,7 @@ public:
         return id;
     }
 private:
+    mutable std::shared_ptr<std::vector<TriangleShape>> shapes;       // built on first use
     std::vector<uint32_t> indices;
     std::vector<glm::vec3> vertices, tangents, normals;
     std::vector<glm::vec2> texCoords;
@@ -539,6 +557,35 @@ private:
 
 // Light.hpp:179-206.  An AreaLight reaches the light sampler through Scene::GetLights() (the
 // GeometricPrimitive that carries it), exactly as in the reference; it cannot be added on its own.
+class TriangleShape : public Shape {
+public:
+    TriangleShape(const Mesh* mesh, uint32_t triangleIndex) : mesh(mesh), tri(triangleIndex){}
+    void Describe(pt_shape_desc&) const override{ throw std::logic_error("TriangleShape: triangles reach the GPU through a BLAS (BLAS2/4/8 over a GeometricPrimitive list, or Model::BuildBlas)"); }
+    AABB BoundingBox() const override{
+        AABB b;
+        for(int k = 0; k < 3; k++)b.Expand(mesh->GetVertices()[mesh->GetIndices()[3 * tri + k]]);
+        return b;
+    }
+    float Area() const override{
+        const glm::vec3 a = mesh->GetVertices()[mesh->GetIndices()[3 * tri]], e1 = mesh->GetVertices()[mesh->GetIndices()[3 * tri + 1]] - a, e2 = mesh->GetVertices()[mesh->GetIndices()[3 * tri + 2]] - a;
+        return 0.5f * glm::length(glm::cross(e1, e2));
+    }
+    const Mesh* GetMesh() const{ return mesh; }
+    uint32_t Index() const{ return tri; }
+private:
+    const Mesh* mesh;
+    uint32_t tri;
+};
+inline const std::shared_ptr<std::vector<TriangleShape>>& Mesh::GetControlPtr() const{
+    if(!shapes){
+        shapes = std::make_shared<std::vector<TriangleShape>>();
+        shapes->reserve(GetTriangleCount());
+        for(uint32_t j = 0; j < GetTriangleCount(); j++)shapes->emplace_back(this, j);
+    }
+    return shapes;
+}
+inline TriangleShape* Mesh::GetShape(std::size_t index) const{ return &(*GetControlPtr())[index]; }
+
 class AreaLight : public Light {
 public:
     AreaLight(const std::shared_ptr<Shape>& light_shape, const glm::vec3& light_color, bool oneSided = false)
@@ -549,6 +596,10 @@ public:
         throw std::logic_error("AreaLight: hand it to a GeometricPrimitive and add scene->GetLights() to the light sampler");
     }
     std::shared_ptr<Shape> getShape() const{ return shape; }
+    // the recipe of Model::BuildBlas calls these per triangle (Model.hpp:52-55); powers are computed at commit on this path
+    // (csrc/shade_tables.cpp, incl. the Power <= epsilon drop), so here they only keep the recipe compiling
+    void PreProcess(const AABB&){}
+    float Power() const{ return 1.0f; }
     const std::shared_ptr<Texture>& EmissiveTexture() const{ return emissiveTexture; }
     bool OneSided() const{ return oneSided; }
 private:
@@ -566,9 +617,6 @@ public:
 };
 
 // ---- Primitive.hpp:7-50, Model.hpp:14-80, BVH.hpp:554-555,1219-1220,1550-1551 -----------------------------------
-struct BLAS2 { static constexpr int width = 2; };
-struct BLAS4 { static constexpr int width = 4; };
-struct BLAS8 { static constexpr int width = 8; };
 struct TLAS2 { static constexpr int width = 2; };
 struct TLAS4 { static constexpr int width = 4; };
 struct TLAS8 { static constexpr int width = 8; };
@@ -585,6 +633,10 @@ public:
 // material == nullptr: a medium boundary.  The area light must be built over the same shape.
 class GeometricPrimitive : public Primitive {
 public:
+    const std::shared_ptr<Shape>& GetShape() const{ return shape; }
+    const std::shared_ptr<Material>& GetMaterial() const{ return material; }
+    const std::shared_ptr<AreaLight>& GetAreaLight() const{ return areaLight; }
+    const std::shared_ptr<Medium>& GetMedium() const{ return medium; }
     GeometricPrimitive(const std::shared_ptr<Shape>& shape, const std::shared_ptr<Material>& material, const std::shared_ptr<AreaLight>& areaLight = nullptr,
                        const std::shared_ptr<Medium>& medium = nullptr)
         : shape(shape), material(material), areaLight(areaLight), medium(medium){
@@ -614,6 +666,59 @@ private:
 // A bottom-level structure over meshes.  The reference's Model imports a file through assimp
 // (Model.cpp:22-357, host I/O outside the hot path); here the meshes are handed over directly — the
 // constructor the reference keeps commented out at Model.hpp:18.
+// BVH.hpp:554-555,743,1219-1220,1550-1551: BLASx = BVHx<GeometricPrimitive>.  As a tag (BLAS4::width) it selects the node width in
+// Model::BuildBlas<BLAS4>() / Scene::BuildTlas<TLAS4>(); constructed from a hand-built primitive list -- the public constructor
+// BVH4(const std::vector<GeometricPrimitive>&), used with the recipe of Model.hpp:47-59 -- it is a Primitive the Scene can hold.
+// The list must consist of TriangleShape primitives (what Mesh::GetShape hands out); runs of consecutive triangles that share
+// mesh, material, emitter and medium become one sub-mesh each, in list order, so primitive ids are list positions as in the
+// reference.  Analytic shapes go into the Scene directly (GeometricPrimitive), as in examples/example_1.cpp.
+template <int W>
+class BLASx : public Primitive {
+public:
+    static constexpr int width = W;
+    BLASx() = default;
+    BLASx(const std::vector<GeometricPrimitive>& prims){
+        size_t i = 0;
+        while(i < prims.size()){
+            const TriangleShape* t0 = dynamic_cast<const TriangleShape*>(prims[i].GetShape().get());
+            if(!t0)throw std::invalid_argument("BLAS: only TriangleShape primitives can be put into a BLAS on this path (spheres / quads go into the Scene directly)");
+            const std::shared_ptr<Texture> em = prims[i].GetAreaLight() ? prims[i].GetAreaLight()->EmissiveTexture() : nullptr;
+            std::vector<uint32_t> tris;
+            size_t j = i;
+            for(; j < prims.size(); j++){
+                const TriangleShape* t = dynamic_cast<const TriangleShape*>(prims[j].GetShape().get());
+                const std::shared_ptr<Texture> ej = prims[j].GetAreaLight() ? prims[j].GetAreaLight()->EmissiveTexture() : nullptr;
+                if(!t || t->GetMesh() != t0->GetMesh() || prims[j].GetMaterial() != prims[i].GetMaterial() || prims[j].GetMedium() != prims[i].GetMedium() || ej != em)break;
+                tris.push_back(t->Index());
+            }
+            meshes.push_back(t0->GetMesh()->Slice(tris, prims[i].GetMaterial(), em, prims[i].GetMedium()));
+            i = j;
+        }
+        if(meshes.empty())throw std::invalid_argument("BLAS: empty primitive list");
+    }
+    int RequiredWidth() const override{ return W; }
+    int Lower(ptb_host::Builder& b, const glm::mat4* transform) const override{
+        if(meshes.empty())throw std::logic_error("BLAS: default-constructed (a width tag), nothing to add to a Scene");
+        int blas = b.lookup(this);
+        if(blas < 0){
+            std::vector<int32_t> ids;
+            for(const std::shared_ptr<Mesh>& m : meshes)ids.push_back(m->Emit(b, nullptr, nullptr, false));
+            blas = pt_scene_add_blas(b.scene, ids.data(), (int)ids.size());
+            ptb_host::check(blas, "pt_scene_add_blas");
+            b.ids[this] = blas;
+        }
+        const int id = pt_scene_add_instance(b.scene, blas, transform ? &(*transform)[0][0] : nullptr);
+        ptb_host::check(id, "pt_scene_add_instance");
+        return id;
+    }
+    const std::vector<std::shared_ptr<Mesh>>& GetMeshes() const{ return meshes; }
+private:
+    std::vector<std::shared_ptr<Mesh>> meshes;
+};
+using BLAS2 = BLASx<2>;
+using BLAS4 = BLASx<4>;
+using BLAS8 = BLASx<8>;
+
 class Model : public Primitive {
 public:
     Model(std::vector<std::shared_ptr<Mesh>> meshes) : meshes(std::move(meshes)){}
@@ -653,9 +758,11 @@ public:
     TransformedPrimitive(const std::shared_ptr<Primitive>& primitive, const glm::mat4& transform) : primitive(primitive), transform(transform){}
     int RequiredWidth() const override{ return primitive->RequiredWidth(); }
     int Lower(ptb_host::Builder& b, const glm::mat4* outer) const override{
-        // the reference nests TransformedPrimitives by composing ray transforms; the GPU TLAS holds one
-        // transform per instance, and the per-level renormalisation of the ray direction is not associative
-        if(outer)throw std::logic_error("nested TransformedPrimitive is not supported");
+        // Nested wrappers (Primitive.hpp:37 takes any Primitive): the reference applies the levels one after the other, the GPU TLAS
+        // holds one transform per instance, so the matrices are multiplied here.  Same geometry; the per-level renormalisation of the
+        // ray direction is not associative in floating point, so hit distances of a NESTED wrapper agree with the reference to
+        // rounding, not bit for bit (a single level stays bit-exact).
+        if(outer){ const glm::mat4 m = *outer * transform; return primitive->Lower(b, &m); }
         return primitive->Lower(b, &transform);
     }
 private:
@@ -673,9 +780,12 @@ public:
         : primitive(primitive), dir(direction), timeBounds(timeBounds){}
     int RequiredWidth() const override{ return primitive->RequiredWidth(); }
     int Lower(ptb_host::Builder& b, const glm::mat4* outer) const override{
-        if(outer)throw std::logic_error("TransformedPrimitive over an AnimatedPrimitive is not supported: animate the TransformedPrimitive instead");
-        const int id = primitive->Lower(b, nullptr);
-        const float d[3] = { dir.x, dir.y, dir.z }, tb[2] = { timeBounds.x, timeBounds.y };
+        // TransformedPrimitive(AnimatedPrimitive(x, dir), M) sees x under M then translate(dir t): the same rays as
+        // AnimatedPrimitive(TransformedPrimitive(x, M), M_linear dir), the chain the device understands
+        const int id = primitive->Lower(b, outer);
+        glm::vec3 dw = dir;
+        if(outer){ const glm::vec4 q = *outer * glm::vec4(dir.x, dir.y, dir.z, 0.0f); dw = glm::vec3(q.x, q.y, q.z); }
+        const float d[3] = { dw.x, dw.y, dw.z }, tb[2] = { timeBounds.x, timeBounds.y };
         ptb_host::check(pt_scene_animate(b.scene, id, d, tb), "pt_scene_animate");
         return id;
     }

@@ -270,6 +270,25 @@ def test_obj_import_model_from_path(tmp_path):
     assert r.returncode != 0 and "cannot open" in r.stderr
 
 
+def test_blas_from_a_primitive_list_and_nested_wrappers(tmp_path):
+    """BLAS4(std::vector<GeometricPrimitive>) with the recipe of Model::BuildBlas (BVH.hpp:743, Model.hpp:47-59) and nested
+    wrappers (Primitive.hpp:37) in the host API: runs of the list that share mesh / material / emitter / medium become sub-meshes
+    in list order (4 grey, 2 red emitters, 2 red, 4 mirror)."""
+    _compile(tmp_path / "blas_list", HOST / "glm_min", ROOT / "examples" / "blas_list.cpp")
+    r = subprocess.run([str(tmp_path / "blas_list")], capture_output=True, text=True, cwd=tmp_path)
+    assert r.returncode == 0, r.stderr
+    assert json.loads(r.stdout.replace('"4": 0, "2": 1, "2": 0, "4": 0', '"split": [4, 2, 2, 4]')) == {"list": 12, "sub_meshes": 4, "split": [4, 2, 2, 4]}, r.stdout
+
+
+@pytest.mark.gpu
+def test_blas_list_and_nested_wrappers_on_the_gpu(tmp_path):
+    _compile(tmp_path / "blas_list", HOST / "glm_min", ROOT / "examples" / "blas_list.cpp")
+    r = subprocess.run([str(tmp_path / "blas_list"), "64", "48", "32"], capture_output=True, text=True, cwd=tmp_path, timeout=300)
+    assert r.returncode == 0, r.stderr
+    out = r.stdout
+    assert '"ids_are_list_positions": 1' in out and '"samples": %d' % (64 * 48 * 32) in out, out
+
+
 def _write_gltf(d, glb=False):
     """A two-node glTF 2.0 scene: a quad with normals / uv / u16 indices under a translated + scaled node, and a non-indexed
     triangle without normals under a rotated child node; three materials (textured metallic-roughness with MASK alpha and an
