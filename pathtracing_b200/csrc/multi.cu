@@ -20,6 +20,7 @@
 #include <dlfcn.h>
 
 #include <condition_variable>
+#include <cstdlib>
 #include <cstring>
 #include <functional>
 #include <mutex>
@@ -112,6 +113,28 @@ pt_render_params shard_params(const pt_render_params& rp, int rank, int world){
     q.pass_begin = rp.pass_begin + rank * rp.pass_stride;
     q.pass_stride = rp.pass_stride * world;
     return q;
+}
+
+// Passes are the unit of sharding while there are enough of them: every rank traces whole frames, perfectly balanced.  A frame
+// with fewer passes than ranks would leave GPUs idle; it is split by interleaved 32 x 32 tiles instead.
+// PTB_SHARD=tiles|passes forces one.  Adaptive frames always shard passes (the stopping rule needs every pixel on every rank).
+bool shard_by_tiles(const pt_render_params& rp, int world){
+    if(world <= 1 || rp.adaptive)return false;
+    if(const char* e = getenv("PTB_SHARD"))return e[0] == 't';
+    const int passes = rp.pass_begin >= rp.spp ? 0 : (rp.spp - rp.pass_begin + rp.pass_stride - 1) / rp.pass_stride;
+    return passes < world;
+}
+
+// one rank's share of a frame, by passes or by tiles
+int render_share(pt_scene* s, const pt_camera_desc* cam, const pt_render_params* rp, int rank, int world, int clear, pt_render_stats* st){
+    if(shard_by_tiles(*rp, world)){
+        s->tile_rank = rank; s->tile_world = world;
+        const int rc = render_passes(s, cam, rp, clear, st);
+        s->tile_rank = 0; s->tile_world = 1;
+        return rc;
+    }
+    const pt_render_params q = shard_params(*rp, rank, world);
+    return render_passes(s, cam, &q, clear, st);
 }
 
 } // namespace
@@ -298,9 +321,8 @@ int pt_multi_render(pt_multi* m, const pt_camera_desc* cam, const pt_render_para
         pt_scene* s = m->ranks[r];
         if(!cuda_ok(cudaSetDevice(s->device), "cudaSetDevice"))return PT_ERR_CUDA;
         if(sharded_adaptive){ s->allreduce = nccl_allreduce_cb; s->allreduce_user = s; }
-        const pt_render_params q = shard_params(*rp, r, G);
         // every rank but the primary starts from an empty film: the reduce adds them onto whatever the primary keeps
-        int rc = render_passes(s, cam, &q, r == 0 ? clear : 1, &st[r]);
+        int rc = render_share(s, cam, rp, r, G, r == 0 ? clear : 1, &st[r]);
         if(rc != PT_OK)return rc;
         if(G > 1 && !m->virtual_ranks){
             rc = reduce_film_nccl(s, 0);
@@ -381,8 +403,7 @@ int pt_dist_render(pt_scene* s, const pt_camera_desc* cam, const pt_render_param
     const int G = s->comm_world, r = s->comm_rank;
     if(G > 1 && !s->comm){ set_error("pt_dist_render: call pt_dist_init first"); return PT_ERR_STATE; }
     if(G > 1 && rp->adaptive){ s->allreduce = nccl_allreduce_cb; s->allreduce_user = s; }
-    const pt_render_params q = shard_params(*rp, r, G);
-    int rc = render_passes(s, cam, &q, (r == 0 ? clear : 1), stats);
+    int rc = render_share(s, cam, rp, r, G, (r == 0 ? clear : 1), stats);
     if(rc != PT_OK)return rc;
     if(G > 1){
         rc = reduce_film_nccl(s, 0);

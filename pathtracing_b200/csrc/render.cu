@@ -983,7 +983,23 @@ int render_passes(pt_scene* s, const pt_camera_desc* cam, const pt_render_params
         return PT_OK;
     };
 
-    rc = run(total, nullptr, 0, 0);
+    if(s->tile_world > 1 && !rp->adaptive){
+        // Interleaved tile sharding (the split for frames with fewer passes than GPUs): this rank renders ALL the
+        // passes of the 32 x 32 tiles whose index is congruent to its rank; the film reduce adds the disjoint tile sets.
+        // The pixel list rides the mechanism of the adaptive rounds (BatchInfo::list).
+        const int tw = (W + 31) / 32;
+        std::vector<uint32_t> mine;
+        for(int y = 0; y < H; y++)for(int x = 0; x < W; x++)if(((y / 32) * tw + x / 32) % s->tile_world == s->tile_rank)mine.push_back((uint32_t)(y * W + x));
+        if(mine.size() * 4 > b.tile_list_bytes){
+            if(b.tile_list){ cudaFree(b.tile_list); b.tile_list = nullptr; b.tile_list_bytes = 0; }
+            if(!mine.empty() && !cuda_ok(cudaMalloc(&b.tile_list, mine.size() * 4), "cudaMalloc tile list"))return fail(PT_ERR_NOMEM);
+            b.tile_list_bytes = mine.size() * 4;
+        }
+        if(!mine.empty()){
+            if(!cuda_ok(cudaMemcpyAsync(b.tile_list, mine.data(), mine.size() * 4, cudaMemcpyHostToDevice, st), "tile list") || !cuda_ok(cudaStreamSynchronize(st), "tile list"))return fail(PT_ERR_CUDA);
+            rc = run((uint64_t)mine.size() * n_pass, (const uint32_t*)b.tile_list, (uint32_t)mine.size(), 0);
+        } else rc = PT_OK;
+    } else rc = run(total, nullptr, 0, 0);
     if(rc != PT_OK)return fail(rc);
     // sharded adaptive rounds: sum this round's statistics over the ranks, fold them into the totals
     auto merge_round = [&]() -> int{

@@ -61,6 +61,7 @@ struct DeviceBuffers {
     size_t work_bytes = 0;
     void* h_counters = nullptr;   // pinned host memory: the watch slots of the wavefront loop (copies of its device control block)
     void* wave_events[8] = {};    // one event per watch slot
+    void* tile_list = nullptr; size_t tile_list_bytes = 0;   // tile-sharded frames: this rank's pixels
     void* adapt = nullptr;        // adaptive loop: per-pixel estimator sums + pixel lists
     size_t adapt_bytes = 0;
     // staging for the host-buffer ray-cast entry points
@@ -129,6 +130,7 @@ struct pt_scene {
     void* comm = nullptr;         // ncclComm_t, or null
     int comm_rank = 0, comm_world = 1;
     bool comm_owned = false;      // created by pt_dist_init (destroyed with the scene / pt_dist_finalize)
+    int tile_rank = 0, tile_world = 1;   // set by multi.cu around a frame that is sharded by tiles instead of passes (render.cu)
     pt_build_stats build_stats {};
 };
 

@@ -54,6 +54,22 @@ def test_virtual_ranks_on_one_gpu_equal_the_single_gpu_film(ranks):
     gpu.close()
 
 
+@pytest.mark.parametrize("ranks,spp", [(4, 2), (3, 5)])
+def test_tile_sharding_for_frames_with_fewer_passes_than_ranks(ranks, spp, monkeypatch):
+    """with fewer sample passes than ranks the frame is split by interleaved 32 x 32 tiles (rank = tile index mod G)
+    and the film reduce adds the disjoint tile sets: same film as one GPU.  (3 ranks, 5 spp: forced with PTB_SHARD=tiles.)"""
+    desc, cam = synth.cornell_scene()
+    p = render_params(100, 70, spp, 5, seed=6)        # 4 x 3 tiles, the last column / row partial
+    one = _single(desc, cam, p)
+    if spp >= ranks:
+        monkeypatch.setenv("PTB_SHARD", "tiles")
+    gpu = GpuScene(desc, 4)
+    m = MultiGpu(gpu, devices=[0] * ranks)
+    st = m.render(cam, p)
+    _check_equal(one, (st, gpu.film(), gpu.film_sumsq()))
+    m.close(); gpu.close()
+
+
 def test_replica_traces_and_renders_like_the_original():
     """pt_scene_replicate: device-to-device copy of every table (here onto the same GPU), no second build."""
     desc = synth.instanced_scene(3, 24)
