@@ -181,7 +181,46 @@ namespace {
 inline uint32_t leaf_ref(uint32_t first){ return REF_LEAF | first; }
 
 void mark_leaf(FlatBvh& f, const BuildNode& n){
-    f.leaf_last[n.right + n.count - 1] = 1;
+    f.last_out[n.right + n.count - 1] = 1;
+}
+
+// Items below binary node ni: the build partitions `order` in place, so a subtree owns one contiguous range of
+// it, from the first item of its leftmost leaf to the end of its rightmost one (O(depth); used for load balancing only).
+uint32_t subtree_items(const BinaryBvh& b, uint32_t ni){
+    uint32_t l = ni, r = ni;
+    while(b.nodes[l].count == 0)l = b.nodes[l].left;
+    while(b.nodes[r].count == 0)r = b.nodes[r].right;
+    const uint32_t lo = std::min(b.nodes[l].right, b.nodes[r].right);
+    const uint32_t hi = std::max(b.nodes[l].right + b.nodes[l].count, b.nodes[r].right + b.nodes[r].count);
+    return hi - lo;
+}
+
+constexpr uint32_t REF_JOB = 0x40000000u;     // top pass only: placeholder for the root of a deferred subtree
+
+} // namespace
+
+// Threaded flatten: the top pass runs the usual recursion but hands every subtree of at most `threshold` items to a
+// worker, which flattens it into arrays of its own.  Node numbering is DFS preorder, so a deferred subtree occupies
+// one contiguous index range whose start is known once the sizes of everything before it are: the stitch below
+// reproduces the arrays of the one-thread recursion exactly.
+struct FlattenDefer {
+    uint32_t threshold = 0;
+    struct Job { uint32_t node, after_top; };   // after_top: top nodes allocated before the subtree was met
+    std::vector<Job> jobs;
+};
+
+namespace {
+
+template <class F> inline void each_ref(Bvh2Node& n, F fn){ fn(n.ref0); fn(n.ref1); }
+template <class F> inline void each_ref(Bvh4Node& n, F fn){ for(int k = 0; k < 4; k++)fn(n.ref[k]); }
+template <class F> inline void each_ref(Bvh8Node& n, F fn){ for(int k = 0; k < 8; k++)fn(n.ref[k]); }
+
+// true (and *ref set) if ni was handed to a worker
+inline bool deferred(FlatBvh& f, const BinaryBvh& b, uint32_t ni, size_t top_nodes, uint32_t* ref){
+    if(!f.defer || subtree_items(b, ni) > f.defer->threshold)return false;
+    *ref = REF_JOB | (uint32_t)f.defer->jobs.size();
+    f.defer->jobs.push_back({ ni, (uint32_t)top_nodes });
+    return true;
 }
 
 // BVH2: DFS preorder over inner nodes; node k holds the boxes + refs of its two
@@ -189,6 +228,7 @@ void mark_leaf(FlatBvh& f, const BuildNode& n){
 uint32_t flatten2(FlatBvh& f, const BinaryBvh& b, uint32_t ni){
     const BuildNode& n = b.nodes[ni];
     if(n.count != 0){ mark_leaf(f, n); return leaf_ref(n.right); }
+    { uint32_t job; if(deferred(f, b, ni, f.n2.size(), &job))return job; }
     const uint32_t me = (uint32_t)f.n2.size();
     f.n2.emplace_back();
     const BuildNode& l = b.nodes[n.left];
@@ -235,6 +275,7 @@ void visit(const ClusterPlan& p, int e, unsigned octant, int* out, int& n){
 uint32_t flatten4(FlatBvh& f, const BinaryBvh& b, uint32_t ni){
     const BuildNode& n = b.nodes[ni];
     if(n.count != 0){ mark_leaf(f, n); return leaf_ref(n.right); }
+    { uint32_t job; if(deferred(f, b, ni, f.n4.size(), &job))return job; }
     const uint32_t me = (uint32_t)f.n4.size();
     f.n4.emplace_back();
 
@@ -328,6 +369,7 @@ void perm8(const BinaryBvh& b, const uint32_t* lanes, int end, uint32_t curr, un
 uint32_t flatten8(FlatBvh& f, const BinaryBvh& b, uint32_t ni){
     const BuildNode& n = b.nodes[ni];
     if(n.count != 0){ mark_leaf(f, n); return leaf_ref(n.right); }
+    { uint32_t job; if(deferred(f, b, ni, f.n8.size(), &job))return job; }
     const uint32_t me = (uint32_t)f.n8.size();
     f.n8.emplace_back();
     uint32_t lanes[8] = { ni, 0, 0, 0, 0, 0, 0, 0 };
@@ -372,13 +414,88 @@ uint32_t flatten8(FlatBvh& f, const BinaryBvh& b, uint32_t ni){
 
 } // namespace
 
-FlatBvh flatten_bvh(const BinaryBvh& b, int width){
+namespace {
+
+template <class Node, class Fn>
+void flatten_threaded(FlatBvh& f, const BinaryBvh& b, std::vector<Node> FlatBvh::* arr, Fn flatten, unsigned threads){
+    FlattenDefer D;
+    D.threshold = std::max<uint32_t>(4096u, (uint32_t)(b.order.size() / (8 * (size_t)threads)));
+    f.defer = &D;
+    f.root = flatten(f, b, 0u);                 // the root holds more than `threshold` items: never a job itself
+    f.defer = nullptr;
+    std::vector<Node>& top = f.*arr;
+    const size_t nj = D.jobs.size();
+    std::vector<FlatBvh> part(nj);
+    std::atomic<size_t> next { 0 };
+    auto work = [&]{
+        for(size_t j; (j = next.fetch_add(1)) < nj; ){
+            part[j].last_out = f.last_out;
+            flatten(part[j], b, D.jobs[j].node);  // an inner node: becomes node 0 of its part
+        }
+    };
+    std::vector<std::thread> th;
+    for(unsigned t = 1; t < threads; t++)th.emplace_back(work);
+    work();
+    for(std::thread& t : th)t.join();
+    // final index of top node t = t + sizes of the jobs met before it; of job j = after_top + sizes of the jobs before j
+    std::vector<uint32_t> before(nj + 1, 0), start(nj);
+    for(size_t j = 0; j < nj; j++){ before[j + 1] = before[j] + (uint32_t)(part[j].*arr).size(); start[j] = D.jobs[j].after_top + before[j]; }
+    auto top_final = [&](uint32_t t){
+        size_t lo = 0, hi = nj;                   // jobs with after_top <= t
+        while(lo < hi){ const size_t mid = (lo + hi) / 2; if(D.jobs[mid].after_top <= t)lo = mid + 1; else hi = mid; }
+        return t + before[lo];
+    };
+    std::vector<Node> out(top.size() + before[nj]);
+    for(size_t t = 0; t < top.size(); t++){
+        Node nd = top[t];
+        each_ref(nd, [&](uint32_t& r){
+            if(r & REF_LEAF)return;               // leaves and REF_EMPTY
+            r = (r & REF_JOB) ? start[r & ~REF_JOB] : top_final(r);
+        });
+        out[top_final((uint32_t)t)] = nd;
+    }
+    next = 0;
+    auto copy = [&]{
+        for(size_t j; (j = next.fetch_add(1)) < nj; ){
+            const std::vector<Node>& src = part[j].*arr;
+            const uint32_t off = start[j];
+            for(size_t q = 0; q < src.size(); q++){
+                Node nd = src[q];
+                each_ref(nd, [&](uint32_t& r){ if(!(r & REF_LEAF))r += off; });
+                out[off + q] = nd;
+            }
+        }
+    };
+    th.clear();
+    for(unsigned t = 1; t < threads; t++)th.emplace_back(copy);
+    copy();
+    for(std::thread& t : th)t.join();
+    if(f.root & REF_JOB)f.root = start[f.root & ~REF_JOB]; else if(!(f.root & REF_LEAF))f.root = top_final(f.root);
+    top.swap(out);
+}
+
+} // namespace
+
+FlatBvh flatten_bvh(const BinaryBvh& b, int width, unsigned threads){
     FlatBvh f;
     f.width = width;
     f.order = b.order;
     f.leaf_last.assign(b.order.size(), 0);
+    f.last_out = f.leaf_last.data();
     if(b.nodes.empty())return f;
     f.bounds = b.nodes[0].box;
+    if(threads == 0){
+        threads = std::min(16u, std::max(1u, std::thread::hardware_concurrency()));
+        if(b.order.size() < ((size_t)1 << 17))threads = 1;
+    }
+    if(b.nodes.size() >= REF_JOB)threads = 1;     // the placeholder bit must stay clear of node indices
+    if(threads > 1 && b.nodes[0].count == 0){
+        if(width == 2)flatten_threaded<Bvh2Node>(f, b, &FlatBvh::n2, flatten2, threads);
+        else if(width == 4)flatten_threaded<Bvh4Node>(f, b, &FlatBvh::n4, flatten4, threads);
+        else flatten_threaded<Bvh8Node>(f, b, &FlatBvh::n8, flatten8, threads);
+        f.last_out = nullptr;
+        return f;
+    }
     if(width == 2){
         f.n2.reserve(b.nodes.size() / 2 + 1);
         f.root = flatten2(f, b, 0);
@@ -389,6 +506,7 @@ FlatBvh flatten_bvh(const BinaryBvh& b, int width){
         f.n8.reserve(b.nodes.size() / 5 + 1);
         f.root = flatten8(f, b, 0);
     }
+    f.last_out = nullptr;
     return f;
 }
 

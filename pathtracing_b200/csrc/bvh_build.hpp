@@ -50,9 +50,14 @@ struct FlatBvh {
     Box bounds = box_empty();
     std::vector<uint32_t> order;   // leaf order -> original item index
     std::vector<uint32_t> leaf_last; // per item in leaf order: 1 if last of its leaf
+    // transient, used while flattening on several threads (bvh_build.cpp): where leaf marks go, and the top pass's
+    // list of subtrees handed to worker threads
+    uint32_t* last_out = nullptr;
+    struct FlattenDefer* defer = nullptr;
 };
 
-FlatBvh flatten_bvh(const BinaryBvh& b, int width);
+// threads: 0 = pick (one thread under 128 Ki items, else up to 16); the arrays do not depend on it
+FlatBvh flatten_bvh(const BinaryBvh& b, int width, unsigned threads = 0);
 
 // glm::inverse(mat4) restated (glm/detail/func_matrix.inl:347-404), column-major.
 void mat4_inverse(const float m[16], float out[16]);

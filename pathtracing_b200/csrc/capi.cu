@@ -238,6 +238,7 @@ pt_scene* pt_scene_create(int device){
     pt_scene* s = new (std::nothrow) pt_scene();
     if(!s){ set_error("out of memory"); return nullptr; }
     s->device = device;
+    if(const char* e = getenv("PTB_BUILDER"))s->builder = e[0] == 'h' ? PT_BUILDER_HOST : PT_BUILDER_GPU;
     return s;
 }
 

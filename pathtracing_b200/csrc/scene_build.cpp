@@ -4,6 +4,7 @@
 #include <chrono>
 #include <cmath>
 #include <cstring>
+#include <thread>
 
 #include "scene_host.hpp"
 
@@ -200,6 +201,19 @@ static void pack_shape(const pt_shape_desc& d, Instance& I){
     I.bhi0 = I.inv[9] * d.p[0] + I.inv[10] * d.p[1] + I.inv[11] * d.p[2];
 }
 
+// the per-triangle loops of a 10 M-triangle commit (boxes, edge records, the gather into leaf order, ref rebasing) took
+// 1.3 s on one thread: split them over the host threads
+template <class F>
+static void parallel_for(size_t n, F fn){
+    unsigned nt = std::thread::hardware_concurrency();
+    if(nt == 0)nt = 1;
+    if(nt > 16)nt = 16;
+    if(n < (size_t)1 << 16 || nt == 1){ fn((size_t)0, n); return; }
+    std::vector<std::thread> th;
+    for(unsigned t = 0; t < nt; t++)th.emplace_back([=]{ fn(n * t / nt, n * (t + 1) / nt); });
+    for(std::thread& t : th)t.join();
+}
+
 int pack_traversal(pt_scene* s, int width, PackedTraversal& P, BvhBuilder builder, void* user){
     if(width != 2 && width != 4 && width != 8){ set_error("bvh_width must be 2, 4 or 8"); return PT_ERR_INVALID; }
     if(s->instances.empty()){ set_error("scene has no instances"); return PT_ERR_INVALID; }
@@ -224,16 +238,21 @@ int pack_traversal(pt_scene* s, int width, PackedTraversal& P, BvhBuilder builde
             const uint32_t flags = material_alpha_flags(s, m.d.material);
             if(m.d.material < 0)s->has_boundary = true;
             if(flags & TRI_ALPHA_TEX)s->has_alpha_tex = true;
-            for(uint32_t t = 0; t < m.d.n_triangles; t++, g++){
-                const uint32_t i0 = m.idx[3 * (size_t)t], i1 = m.idx[3 * (size_t)t + 1], i2 = m.idx[3 * (size_t)t + 2];
-                const float* p0 = &m.pos[3 * (size_t)i0]; const float* p1 = &m.pos[3 * (size_t)i1]; const float* p2 = &m.pos[3 * (size_t)i2];
-                Box bx = box_empty();
-                box_grow(bx, p0); box_grow(bx, p1); box_grow(bx, p2);   // TriangleShape::BoundingBox, Shape.cpp:270-276
-                boxes[g] = bx;
-                Tri& T = src[g];
-                for(int a = 0; a < 3; a++){ T.v0[a] = p0[a]; T.e1[a] = p1[a] - p0[a]; T.e2[a] = p2[a] - p0[a]; }
-                T.prim = g; T.mesh = (uint32_t)mi; T.flags = flags;
-            }
+            const uint32_t g0 = g;
+            parallel_for(m.d.n_triangles, [&, g0, mi, flags](size_t lo, size_t hi){
+                for(size_t t = lo; t < hi; t++){
+                    const uint32_t gg = g0 + (uint32_t)t;
+                    const uint32_t i0 = m.idx[3 * t], i1 = m.idx[3 * t + 1], i2 = m.idx[3 * t + 2];
+                    const float* p0 = &m.pos[3 * (size_t)i0]; const float* p1 = &m.pos[3 * (size_t)i1]; const float* p2 = &m.pos[3 * (size_t)i2];
+                    Box bx = box_empty();
+                    box_grow(bx, p0); box_grow(bx, p1); box_grow(bx, p2);   // TriangleShape::BoundingBox, Shape.cpp:270-276
+                    boxes[gg] = bx;
+                    Tri& T = src[gg];
+                    for(int a = 0; a < 3; a++){ T.v0[a] = p0[a]; T.e1[a] = p1[a] - p0[a]; T.e2[a] = p2[a] - p0[a]; }
+                    T.prim = gg; T.mesh = (uint32_t)mi; T.flags = flags;
+                }
+            });
+            g += m.d.n_triangles;
         }
         const auto tb0 = std::chrono::steady_clock::now();
         BinaryBvh bb;
@@ -254,17 +273,23 @@ int pack_traversal(pt_scene* s, int width, PackedTraversal& P, BvhBuilder builde
         };
         hb.root = rebase(fb.root);
         if(width == 2){
-            for(Bvh2Node nd : fb.n2){ nd.ref0 = rebase(nd.ref0); nd.ref1 = rebase(nd.ref1); n2.push_back(nd); }
+            n2.resize(node_base + fb.n2.size());
+            parallel_for(fb.n2.size(), [&](size_t lo, size_t hi){ for(size_t q = lo; q < hi; q++){ Bvh2Node nd = fb.n2[q]; nd.ref0 = rebase(nd.ref0); nd.ref1 = rebase(nd.ref1); n2[node_base + q] = nd; } });
         } else if(width == 4){
-            for(Bvh4Node nd : fb.n4){ for(int k = 0; k < 4; k++)nd.ref[k] = rebase(nd.ref[k]); n4.push_back(nd); }
+            n4.resize(node_base + fb.n4.size());
+            parallel_for(fb.n4.size(), [&](size_t lo, size_t hi){ for(size_t q = lo; q < hi; q++){ Bvh4Node nd = fb.n4[q]; for(int k = 0; k < 4; k++)nd.ref[k] = rebase(nd.ref[k]); n4[node_base + q] = nd; } });
         } else{
-            for(Bvh8Node nd : fb.n8){ for(int k = 0; k < 8; k++)nd.ref[k] = rebase(nd.ref[k]); P.n8.push_back(nd); }
+            P.n8.resize(node_base + fb.n8.size());
+            parallel_for(fb.n8.size(), [&](size_t lo, size_t hi){ for(size_t q = lo; q < hi; q++){ Bvh8Node nd = fb.n8[q]; for(int k = 0; k < 8; k++)nd.ref[k] = rebase(nd.ref[k]); P.n8[node_base + q] = nd; } });
         }
-        for(uint32_t i = 0; i < hb.n_tris; i++){
-            Tri T = src[fb.order[i]];
-            if(fb.leaf_last[i])T.flags |= TRI_LAST;
-            tris.push_back(T);
-        }
+        tris.resize((size_t)hb.tri_base + hb.n_tris);
+        parallel_for(hb.n_tris, [&](size_t lo, size_t hi){
+            for(size_t i = lo; i < hi; i++){
+                Tri T = src[fb.order[i]];
+                if(fb.leaf_last[i])T.flags |= TRI_LAST;
+                tris[(size_t)hb.tri_base + i] = T;
+            }
+        });
     }
 
     // ---- TLAS -----------------------------------------------------------------------

@@ -120,7 +120,7 @@ struct pt_scene {
     unsigned long long overflow_seen = 0;  // device overflow counter (buf.stats + 64) as the last checked call left it
     pt_allreduce_fn allreduce = nullptr;   // sums a device buffer over the ranks that shard this scene's sample passes
     void* allreduce_user = nullptr;
-    int builder = 0;              // pt_builder: where the binary SAH build runs
+    int builder = 1;              // pt_builder: where the binary SAH build runs (default: on the GPU, same tree; PTB_BUILDER=host in the environment or pt_scene_set_builder)
     bool counting = false;        // pt_scene_set_counting: pt_render launches the counting build of the traversal kernels
     int layout = 0;               // pt_layout: exact 128 B clusters, or the quantised 64 B ones (width 4)
     // every device table of the committed scene as (byte offset of its pointer inside `buf`, bytes): what

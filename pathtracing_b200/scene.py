@@ -249,14 +249,15 @@ def render_params(width, height, spp, max_depth, integrator=capi.INTEGRATOR_PATH
 class GpuScene:
     """A committed scene on one B200, through the C-ABI only."""
 
-    def __init__(self, desc: SceneDesc, bvh_width=4, light_sampler=1, device=0, builder=capi.BUILDER_HOST, layout=None):
+    def __init__(self, desc: SceneDesc, bvh_width=4, light_sampler=1, device=0, builder=None, layout=None):
         self.lib = capi.load_library()
         self.h = self.lib.pt_scene_create(device)
         if not self.h:
             raise PtError(self._err())
         self.desc = desc
         desc.replay(self)
-        self._ck(self.lib.pt_scene_set_builder(self.h, builder))
+        if builder is not None:                      # library default: GPU builder (PTB_BUILDER=host overrides)
+            self._ck(self.lib.pt_scene_set_builder(self.h, builder))
         if layout is None:      # experiments: PTB_LAYOUT=fast turns the quantised layout on for every width-4 scene
             layout = capi.LAYOUT_FAST if (os.environ.get("PTB_LAYOUT") == "fast" and bvh_width == 4) else capi.LAYOUT_EXACT
         self.layout = layout

@@ -110,6 +110,37 @@ PT_API int emul_bvh4q_check(void* p, int* n_nodes, float* worst_growth){
     return bad;
 }
 
+// flatten_bvh on `threads` threads against the one-thread recursion, over n random item boxes: number of differing
+// bytes in the node arrays + differing entries of order / leaf_last / root (0 = identical)
+PT_API long long emul_flatten_check(unsigned n, unsigned seed, int width, unsigned threads, int clustered, int* n_nodes){
+    std::vector<Box> boxes(n);
+    uint64_t st = seed * 0x9E3779B97F4A7C15ull + 1;
+    auto rnd = [&]{ st = st * 6364136223846793005ull + 1442695040888963407ull; return (float)((st >> 40) & 0xFFFFFF) / 16777216.0f; };
+    for(unsigned i = 0; i < n; i++){
+        float c[3] = { rnd(), rnd(), rnd() };
+        if(clustered && (i & 3))for(int k = 0; k < 3; k++)c[k] = 0.5f + 0.01f * c[k];     // a dense clump: a lopsided tree
+        Box b = box_empty();
+        for(int v = 0; v < 3; v++){ float p[3]; for(int k = 0; k < 3; k++)p[k] = c[k] + 0.01f * (rnd() - 0.5f); box_grow(b, p); }
+        boxes[i] = b;
+    }
+    const BinaryBvh bb = build_binary_bvh(boxes.data(), n);
+    const FlatBvh a = flatten_bvh(bb, width, 1), t = flatten_bvh(bb, width, threads);
+    long long bad = 0;
+    auto cmp = [&](const void* x, size_t nx, const void* y, size_t ny){
+        if(nx != ny){ bad += 1 + (long long)(nx > ny ? nx - ny : ny - nx); return; }
+        const unsigned char* p = (const unsigned char*)x; const unsigned char* q = (const unsigned char*)y;
+        for(size_t i = 0; i < nx; i++)bad += p[i] != q[i];
+    };
+    cmp(a.n2.data(), a.n2.size() * sizeof(Bvh2Node), t.n2.data(), t.n2.size() * sizeof(Bvh2Node));
+    cmp(a.n4.data(), a.n4.size() * sizeof(Bvh4Node), t.n4.data(), t.n4.size() * sizeof(Bvh4Node));
+    cmp(a.n8.data(), a.n8.size() * sizeof(Bvh8Node), t.n8.data(), t.n8.size() * sizeof(Bvh8Node));
+    cmp(a.order.data(), a.order.size() * 4, t.order.data(), t.order.size() * 4);
+    cmp(a.leaf_last.data(), a.leaf_last.size() * 4, t.leaf_last.data(), t.leaf_last.size() * 4);
+    bad += a.root != t.root;
+    *n_nodes = (int)(a.n2.size() + a.n4.size() + a.n8.size());
+    return bad;
+}
+
 PT_API int emul_scene_bounds(void* p, float lo[3], float hi[3]){
     EmulScene* e = (EmulScene*)p;
     for(int a = 0; a < 3; a++){ lo[a] = e->P.bounds.lo[a]; hi[a] = e->P.bounds.hi[a]; }

@@ -44,6 +44,8 @@ def load():
     lib.emul_scene_commit.argtypes = [vp, i]
     lib.emul_scene_bounds.argtypes = [vp, C.POINTER(C.c_float), C.POINTER(C.c_float)]
     lib.emul_node_count.argtypes = [vp]
+    lib.emul_flatten_check.restype = C.c_longlong
+    lib.emul_flatten_check.argtypes = [C.c_uint, C.c_uint, i, C.c_uint, i, C.POINTER(C.c_int)]
     lib.emul_bvh4q_check.restype = i
     lib.emul_bvh4q_check.argtypes = [vp, C.POINTER(C.c_int), C.POINTER(C.c_float)]
     lib.emul_trace_closest.restype = i

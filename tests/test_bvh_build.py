@@ -112,3 +112,15 @@ def test_scene_committed_with_gpu_builder_traces_identically(width):
         assert np.array_equal(ah.view(np.uint8), bh.view(np.uint8)) and np.array_equal(ai, bi)
         assert np.array_equal(a.trace_any(rays), b.trace_any(rays))
         a.close(); b.close()
+
+
+@pytest.mark.parametrize("width", [2, 4, 8])
+@pytest.mark.parametrize("n,threads,clustered", [(5000, 3, 0), (200000, 7, 0), (150000, 16, 1)])
+def test_threaded_flatten_gives_the_one_thread_arrays(width, n, threads, clustered):
+    """flatten_bvh hands subtrees to worker threads and stitches their arrays back into DFS preorder
+    (csrc/bvh_build.cpp flatten_threaded): byte-identical BVH2 / BVH4 / BVH8 node arrays, leaf marks and root."""
+    import ctypes as C
+    import emulapi
+    nodes = C.c_int(0)
+    bad = emulapi.load().emul_flatten_check(n, 11 + width, width, threads, clustered, C.byref(nodes))
+    assert bad == 0 and nodes.value > n // 8, (bad, nodes.value)
