@@ -13,6 +13,7 @@ from pathlib import Path
 import numpy as np
 
 _PKG = Path(__file__).resolve().parent
+LIB_PATH_SMALL_STACK = Path(__file__).resolve().parent / "libptb200_stack20.so"    # test-only twin, csrc/Makefile
 LIB_PATH = _PKG / "libptb200.so"
 if os.environ.get("PTB_LIB"):            # kernel experiments: an alternative build of the same C-ABI
     LIB_PATH = Path(os.environ["PTB_LIB"])

@@ -82,7 +82,7 @@ __global__ void __launch_bounds__(kTraceBlock) k_trace(DevScene S, const float4*
     const unsigned leaf_min = refill_min >> 8;       // packed by the launchers: leaf_min << 8 | refill_min
     refill_min &= 0xFFu;
     extern __shared__ uint2 smem_stack[];            // KS rows of kTraceBlock entries
-    uint2 spill[kStack - KS];
+    uint2 spill[kStack > KS ? kStack - KS : 1];
     TravStack<KS, KS ? kTraceBlock : 1> stack;
     if constexpr(KS > 0)stack.sm = smem_stack + threadIdx.x;
     stack.lm = spill;

@@ -30,7 +30,10 @@ namespace ptb {
 
 constexpr float kShadowEps = 0.00001f;          // shadowEpsilon, AABB.hpp:6
 constexpr float kFltEps = 1.1920928955078125e-7f;
-constexpr int kStack = 96;                      // unified TLAS+BLAS stack (the reference: 32 + 32, unchecked)
+#ifndef PTB_STACK
+#define PTB_STACK 96                            // tests build a second library with a small stack to exercise the overflow error (Makefile)
+#endif
+constexpr int kStack = PTB_STACK;               // unified TLAS+BLAS stack (the reference: 32 + 32, unchecked)
 constexpr uint32_t REF_LEAVE = 0xFFFFFFFEu;     // stack sentinel: end of the current instance
 
 struct RayCtx {

@@ -249,8 +249,8 @@ def render_params(width, height, spp, max_depth, integrator=capi.INTEGRATOR_PATH
 class GpuScene:
     """A committed scene on one B200, through the C-ABI only."""
 
-    def __init__(self, desc: SceneDesc, bvh_width=4, light_sampler=1, device=0, builder=None, layout=None):
-        self.lib = capi.load_library()
+    def __init__(self, desc: SceneDesc, bvh_width=4, light_sampler=1, device=0, builder=None, layout=None, lib=None):
+        self.lib = lib if lib is not None else capi.load_library()      # lib: a second build of the library (tests: the small-stack twin)
         self.h = self.lib.pt_scene_create(device)
         if not self.h:
             raise PtError(self._err())

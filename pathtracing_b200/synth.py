@@ -140,6 +140,21 @@ def soup_scene(n_tris: int, seed: int = 42, opaque: bool = False):
     return d
 
 
+def deep_chain_scene(n: int = 230, ratio: float = 2.0 ** -0.25):
+    """n self-similar triangles: triangle k lies in the plane x = ratio^k and spans about ratio^k in y and z.  Binned SAH peels the big outer
+    ones off a shrinking inner group, so the tree is a chain tens of clusters deep, and a ray along +x through the origin finds every
+    peeled child farther than the inner group it descends into: all of them wait on the traversal stack before the first triangle is
+    tested.  n = 230 needs more than the 96 stack rows of k_trace (PT_ERR_OVERFLOW); n = 60 does not."""
+    d = SceneDesc()
+    m = d.diffuse(d.solid((0.7, 0.7, 0.7)), alpha_mode=capi.ALPHA_OPAQUE)
+    sc = (ratio ** np.arange(n)).astype(np.float32)
+    base = np.array([[1, -1, -1], [1, 2, -1], [1, -1, 2]], np.float32)
+    pos = sc[:, None, None] * base[None]
+    me = d.mesh(pos.reshape(-1, 3), np.arange(3 * n, dtype=np.uint32), material=m)
+    d.instance(d.add_blas([me]))
+    return d
+
+
 def terrain_scene(nx: int, nz: int, seed: int = 42, opaque: bool = False):
     d = SceneDesc()
     t = d.solid((0.7, 0.7, 0.7))

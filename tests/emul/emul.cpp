@@ -42,6 +42,7 @@ struct EmulScene {
     DevScene D;
     ShadeTables T;          // host copies of the shading tables (emul_shade_tables)
     bool shaded = false;
+    unsigned long long overflows = 0;
 };
 
 extern "C" {
@@ -141,6 +142,9 @@ PT_API long long emul_flatten_check(unsigned n, unsigned seed, int width, unsign
     return bad;
 }
 
+// rays of the last emul_trace_closest whose traversal needed more than the 96 stack rows (the product counts them and fails the call)
+PT_API unsigned long long emul_stack_overflows(void* p){ return ((EmulScene*)p)->overflows; }
+
 PT_API int emul_scene_bounds(void* p, float lo[3], float hi[3]){
     EmulScene* e = (EmulScene*)p;
     for(int a = 0; a < 3; a++){ lo[a] = e->P.bounds.lo[a]; hi[a] = e->P.bounds.hi[a]; }
@@ -154,6 +158,7 @@ PT_API int emul_trace_closest(void* p, const pt_ray* rays, size_t n, pt_hit* hit
     const DevScene& D = e->D;
     int nt = (int)std::thread::hardware_concurrency(); if(nt < 1)nt = 1;
     std::vector<TraceCounters> cs(nt, TraceCounters{0, 0, 0, 0});
+    std::vector<unsigned long long> over(nt, 0);
     auto work = [&](int tid){
         for(size_t i = tid; i < n; i += nt){
             HitRec h;
@@ -164,6 +169,7 @@ PT_API int emul_trace_closest(void* p, const pt_ray* rays, size_t n, pt_hit* hit
             else trace_scene<8, false, true>(D, rb, i, h, &cs[tid], NoAlphaWrap());
             hits[i].t = h.t; hits[i].u = h.u; hits[i].v = h.v; hits[i].prim = h.prim;
             if(inst)inst[i] = h.inst;
+            over[tid] += h.overflow;
         }
     };
     std::vector<std::thread> pool;
@@ -173,6 +179,8 @@ PT_API int emul_trace_closest(void* p, const pt_ray* rays, size_t n, pt_hit* hit
         stats[0] = stats[1] = stats[2] = stats[3] = 0;
         for(auto& c : cs){ stats[0] += c.tlas_nodes; stats[1] += c.blas_nodes; stats[2] += c.instances; stats[3] += c.triangles; }
     }
+    e->overflows = 0;
+    for(unsigned long long o : over)e->overflows += o;
     return PT_OK;
 }
 

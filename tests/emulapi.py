@@ -13,14 +13,16 @@ from pathtracing_b200.capi import pt_light_desc, pt_material_desc, pt_medium_des
 
 _DIR = Path(__file__).resolve().parent / "emul"
 _lib = None
+_libs = {}
 
 
-def load():
+def load(name="libptemul.so"):
+    """name: libptemul.so, or libptemul_stack20.so (the same code with a 20-row traversal stack)."""
     global _lib
-    if _lib is not None:
-        return _lib
+    if name in _libs:
+        return _libs[name]
     subprocess.run(["make", "-s", "-C", str(_DIR)], check=True)
-    lib = C.CDLL(str(_DIR / "libptemul.so"))
+    lib = C.CDLL(str(_DIR / name))
     vp, i, sz = C.c_void_p, C.c_int, C.c_size_t
     lib.emul_scene_create.restype = vp
     lib.emul_scene_destroy.argtypes = [vp]
@@ -46,19 +48,23 @@ def load():
     lib.emul_node_count.argtypes = [vp]
     lib.emul_flatten_check.restype = C.c_longlong
     lib.emul_flatten_check.argtypes = [C.c_uint, C.c_uint, i, C.c_uint, i, C.POINTER(C.c_int)]
+    lib.emul_stack_overflows.restype = C.c_ulonglong
+    lib.emul_stack_overflows.argtypes = [vp]
     lib.emul_bvh4q_check.restype = i
     lib.emul_bvh4q_check.argtypes = [vp, C.POINTER(C.c_int), C.POINTER(C.c_float)]
     lib.emul_trace_closest.restype = i
     lib.emul_trace_closest.argtypes = [vp, vp, sz, vp, vp, vp]
     lib.emul_trace_any.restype = i
     lib.emul_trace_any.argtypes = [vp, vp, sz, vp]
-    _lib = lib
+    _libs[name] = lib
+    if name == "libptemul.so":
+        _lib = lib
     return lib
 
 
 class EmulScene:
-    def __init__(self, desc, bvh_width=4):
-        self.lib = load()
+    def __init__(self, desc, bvh_width=4, lib_name="libptemul.so"):
+        self.lib = load(lib_name)
         self.h = self.lib.emul_scene_create()
         self.desc = desc
         desc.replay(self)
@@ -108,6 +114,9 @@ class EmulScene:
 
     def node_count(self):
         return self.lib.emul_node_count(self.h)
+
+    def stack_overflows(self):
+        return int(self.lib.emul_stack_overflows(self.h))
 
     def bvh4q_check(self):
         n, worst = C.c_int(0), C.c_float(0)

@@ -244,3 +244,25 @@ def test_fast_layout_boxes_contain_the_exact_ones():
         bad, nodes, worst = e.bvh4q_check()
         assert nodes > 0 and bad == 0, (bad, nodes)
         assert worst <= 1.25 / 127.0 * 1.05, worst         # a box grows by at most 1.25 steps per side, a step is at most 1/127 of the cluster extent (power-of-two steps)
+
+
+def test_stack_overflow_flag_on_a_small_stack():
+    """The host build of the traversal with a 20-row stack (libptemul_stack20.so): the deep-chain scene in BVH8 overflows on the two
+    rays along +x and they come back wrong -- and flagged; the 96-row build answers all four like the reference.  GPU twin:
+    test_raycast_gpu.py::test_stack_overflow_is_a_counted_error."""
+    from emulapi import EmulScene
+    from test_raycast_gpu import _deep_rays
+    desc, rays = synth.deep_chain_scene(230), _deep_rays()
+    full, small = EmulScene(desc, 8), EmulScene(desc, 8, lib_name="libptemul_stack20.so")
+    want, _ = full.trace_closest(rays)
+    assert full.stack_overflows() == 0 and (want["prim"] != 0xFFFFFFFF).all()
+    got, _ = small.trace_closest(rays)
+    assert small.stack_overflows() == 2
+    assert np.array_equal(got[2:], want[2:]) and not np.array_equal(got[:2]["prim"], want[:2]["prim"])
+    from oracle import refapi
+    if refapi.available("strict"):
+        from oracle.refapi import RefScene
+        r = RefScene(desc, 8, id_mode=True)
+        rh, _ = r.trace_closest(rays, want_inst=True)
+        assert np.array_equal(rh["prim"], want["prim"]) and np.array_equal(rh["t"].view(np.uint32), want["t"].view(np.uint32))
+        r.close()

@@ -232,6 +232,43 @@ def test_error_paths():
     g.close()
 
 
+def _deep_rays():
+    r = np.zeros(4, dtype=capi.RAY_DTYPE)
+    r["tmax"] = np.inf
+    r["o"][:2], r["o"][2:] = (-1, 0, 0), (2, 0, 0)
+    for k, d in enumerate(((1, 0, 0), (1, 1e-3, 1e-3), (-1, 0, 0), (-1, 1e-3, 0))):
+        r["d"][k] = np.asarray(d, np.float32) / np.linalg.norm(d)
+    return r
+
+
+def test_stack_overflow_is_a_counted_error():
+    """A ray that needs more traversal-stack rows than there are used to lose a push silently (a possibly wrong hit, no error).
+    Now the ray is flagged, counted, and every entry point that traced it returns PT_ERR_OVERFLOW.  No scene a SAH builder makes
+    comes near the product's 96 rows (the deepest test scene needs 22), so the error path runs against the library's test-only twin
+    built with 20 rows (csrc/Makefile, PTB_STACK=20): synth.deep_chain_scene in BVH8 needs more for rays along +x."""
+    from pathtracing_b200 import capi
+    small = capi.load_library(capi.LIB_PATH_SMALL_STACK)
+    desc, rays = synth.deep_chain_scene(230), _deep_rays()
+    good = GpuScene(desc, 8)
+    want, _ = good.trace_closest(rays)
+    assert good.stack_overflows() == 0
+    g = GpuScene(desc, 8, lib=small)
+    hits = np.empty(len(rays), capi.HIT_DTYPE)
+    rc = small.pt_trace_closest(g.h, rays.ctypes.data, len(rays), hits.ctypes.data, None)
+    assert rc == -6 and b"stack overflow on 2 rays" in small.pt_last_error(), (rc, small.pt_last_error())      # PT_ERR_OVERFLOW
+    assert g.stack_overflows() == 2
+    assert np.array_equal(hits[2:], want[2:]) and not np.array_equal(hits[:2]["prim"], want[:2]["prim"])        # the two flagged rays are the ones that went wrong
+    occ = np.empty(len(rays), np.uint8)
+    assert small.pt_trace_any(g.h, rays.ctypes.data, len(rays), occ.ctypes.data) in (0, -6)                     # any-hit stops at the first hit: may or may not get that deep
+    # the same rays in BVH4 fit in 20 rows: no error, right answer, and the count does not move
+    g4 = GpuScene(desc, 4, lib=small)
+    h4 = np.empty(len(rays), capi.HIT_DTYPE)
+    assert small.pt_trace_closest(g4.h, rays.ctypes.data, len(rays), h4.ctypes.data, None) == 0
+    assert np.array_equal(h4["prim"], want["prim"]) and g4.stack_overflows() == 0
+    for s in (good, g, g4):
+        s.close()
+
+
 def _alpha_rays(n, seed=3):
     """Rays from in front of the Cornell opening towards the cards (most of them hit a card first)."""
     rng = np.random.default_rng(seed)
