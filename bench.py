@@ -439,6 +439,35 @@ def run_ours(a):
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         e2e_ms = float(t.item())
     e2e_value = world * n / (e2e_ms * 1e-3) / 1e6
+    # the same rays through the compact transfer form (pt_trace_closest_compact: 24 B in, 8 B out per ray; every C2 ray has
+    # tmax = inf and time = 0).  Reported next to the full-format number, which stays the headline.
+    host_rays24 = torch.empty(n * 24, dtype=torch.uint8).pin_memory()
+    r24 = host_rays24.numpy().view(capi.RAY24_DTYPE)
+    r24["o"], r24["d"] = rays_np["o"], rays_np["d"]
+    host_hits8 = torch.empty(n * 8, dtype=torch.uint8).pin_memory()
+    hp24, hh8 = host_rays24.data_ptr(), host_hits8.data_ptr()
+
+    def compact_step():
+        rc = lib.pt_trace_closest_compact(scene.h, hp24, n, hh8, None)
+        assert rc == 0, lib.pt_last_error()
+
+    for _ in range(max(1, min(a.warmup, 2))):
+        compact_step()
+    if world > 1:
+        dist.barrier()
+    t0 = time.perf_counter()
+    for _ in range(e2e_steps):
+        compact_step()
+    compact_ms = (time.perf_counter() - t0) * 1e3 / e2e_steps
+    if world > 1:
+        t = torch.tensor([compact_ms], device="cuda", dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        compact_ms = float(t.item())
+    compact_value = world * n / (compact_ms * 1e-3) / 1e6
+    h8 = host_hits8.numpy().view(capi.HIT8_DTYPE)
+    h16 = host_hits.numpy().view(capi.HIT_DTYPE)
+    compact_equal = bool(np.array_equal(h8["t"].view(np.uint32), h16["t"].view(np.uint32)) and np.array_equal(h8["prim"], h16["prim"]))
+    del host_rays24, host_hits8, r24, h8, h16
     # what the PCIe link of this box gives the same pinned buffers (plain copies, CUDA events): the floor of e2e
     pcie = {}
     for name, dst, src in (("h2d", d_rays, host_rays), ("d2h", host_hits, d_hits)):
@@ -589,7 +618,10 @@ def run_ours(a):
                     "host_copy_gbs_per_rank_all_ranks_at_once": host_copy_gbs,
                     "limiter": ("the kernel (PCIe floor of the same buffers is below the step time)" if world == 1 else
                                 "host memory: every rank moves 48 B per ray through one NUMA node's DRAM; per-rank pinned-copy and host-copy rates fall with the rank count"),
-                    "note": "floor = the slower of the two plain pinned copies of one step's buffers on this box"},
+                    "note": "floor = the slower of the two plain pinned copies of one step's buffers on this box",
+                    "compact": {"value": compact_value, "unit": UNIT, "ms_per_step": compact_ms, "h2d_bytes_per_step": n * 24, "d2h_bytes_per_step": n * 8,
+                                "api": "pt_trace_closest_compact (pt_ray24 in, pt_hit8 out; same kernel family, same pipeline)",
+                                "same_t_bits_and_ids_as_the_full_form": compact_equal}},
             "gpu_launches": a.steps, "gpu_launches_e2e": e2e_steps * chunks,
             "clocks": clocks, "roofline": roofline, "cpu_baseline": cpu, "extras": extras}
     print(json.dumps(line), flush=True)

@@ -100,7 +100,9 @@ LAYOUT_EXACT, LAYOUT_FAST = range(2)
 
 RAY_DTYPE = np.dtype([("o", "<f4", 3), ("tmax", "<f4"), ("d", "<f4", 3), ("time", "<f4")])
 HIT_DTYPE = np.dtype([("t", "<f4"), ("u", "<f4"), ("v", "<f4"), ("prim", "<u4")])
-assert RAY_DTYPE.itemsize == 32 and HIT_DTYPE.itemsize == 16
+RAY24_DTYPE = np.dtype([("o", "<f4", 3), ("d", "<f4", 3)])       # pt_ray24: tmax = inf, time = 0 implied
+HIT8_DTYPE = np.dtype([("t", "<f4"), ("prim", "<u4")])              # pt_hit8
+assert RAY_DTYPE.itemsize == 32 and HIT_DTYPE.itemsize == 16 and RAY24_DTYPE.itemsize == 24 and HIT8_DTYPE.itemsize == 8
 
 # enums
 TEX_SOLID, TEX_IMAGE_U8, TEX_IMAGE_F32, TEX_CHECKER, TEX_UV, TEX_NORMAL = range(6)
@@ -116,7 +118,7 @@ EXPORTS = [
     "pt_device_count", "pt_scene_create", "pt_scene_destroy", "pt_last_error",
     "pt_scene_add_texture", "pt_scene_add_material", "pt_scene_add_medium", "pt_scene_add_mesh",
     "pt_scene_add_blas", "pt_scene_add_instance", "pt_scene_add_shape", "pt_scene_add_shape_xf", "pt_scene_animate", "pt_scene_add_light", "pt_scene_set_medium",
-    "pt_scene_commit", "pt_scene_set_builder", "pt_scene_set_layout", "pt_scene_set_allreduce", "pt_scene_build_stats", "pt_build_bvh2", "pt_scene_bounds", "pt_trace_closest", "pt_trace_any",
+    "pt_scene_commit", "pt_scene_set_builder", "pt_scene_set_layout", "pt_scene_set_allreduce", "pt_scene_build_stats", "pt_build_bvh2", "pt_scene_bounds", "pt_trace_closest", "pt_trace_closest_compact", "pt_trace_any",
     "pt_trace_closest_dev", "pt_trace_any_dev", "pt_trace_closest_static", "pt_scene_stack_overflows", "pt_trace_closest_stats", "pt_scene_set_counting", "pt_scene_render_counts", "pt_render",
     "pt_film_device_ptr", "pt_film_download", "pt_film_download_sumsq", "pt_film_upload",
     "pt_scene_replicate", "pt_multi_create", "pt_multi_destroy", "pt_multi_gpus", "pt_multi_scene", "pt_multi_render",
@@ -225,6 +227,8 @@ def load_library(path: os.PathLike | None = None) -> C.CDLL:
     lib.pt_dist_render.argtypes = [vp, C.POINTER(pt_camera_desc), C.POINTER(pt_render_params), i, C.POINTER(pt_render_stats)]
     lib.pt_dist_finalize.restype = i
     lib.pt_dist_finalize.argtypes = [vp]
+    lib.pt_trace_closest_compact.restype = i
+    lib.pt_trace_closest_compact.argtypes = [vp, vp, sz, vp, vp]
     lib.pt_unit_shade.restype = i
     lib.pt_unit_shade.argtypes = [vp, vp, sz, vp, vp, i]
     lib.pt_unit_light_count.restype = i

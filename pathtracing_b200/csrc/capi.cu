@@ -32,6 +32,18 @@ static int ensure_stage(pt_scene* s, size_t n){
     return PT_OK;
 }
 
+static int ensure_stage24(pt_scene* s, size_t n){
+    DeviceBuffers& b = s->buf;
+    if(n <= b.stage24_cap)return PT_OK;
+    void** ptrs[] = { &b.stage_rays24, &b.stage_hits8 };
+    for(void** p : ptrs){ if(*p){ cudaFree(*p); *p = nullptr; } }
+    b.stage24_cap = 0;
+    if(!cuda_ok(cudaMalloc(&b.stage_rays24, n * sizeof(pt_ray24)), "cudaMalloc compact rays") ||
+       !cuda_ok(cudaMalloc(&b.stage_hits8, n * sizeof(pt_hit8)), "cudaMalloc compact hits"))return PT_ERR_CUDA;
+    b.stage24_cap = n;
+    return PT_OK;
+}
+
 // Host-buffer entry points: a three-stage pipeline over three streams.  Chunk k is copied in on the H2D
 // stream, traced on the compute stream once its copy has landed, and copied out on the D2H stream once its
 // kernel is done — so the kernels run back to back while both PCIe directions stay busy (full duplex).  The
@@ -56,8 +68,9 @@ static cudaEvent_t pipeline_event(pt_scene* s, size_t i){
 }
 
 // launch(off, m, stream) queues the kernel for rays [off, off+m); copy_out(off, m, stream) queues its D2H copies
+// rays / ray_bytes / d_in: the host records, their size and where they are staged (pt_ray into stage_rays, or pt_ray24 into stage_rays24)
 template <class Launch, class CopyOut>
-static int trace_pipelined(pt_scene* s, const pt_ray* rays, size_t n, Launch launch, CopyOut copy_out){
+static int trace_pipelined(pt_scene* s, const void* rays, size_t n, Launch launch, CopyOut copy_out, size_t ray_bytes = sizeof(pt_ray), void* d_in = nullptr){
     int rc = ensure_stage(s, n);
     if(rc != PT_OK)return rc;
     // Chunks alternate between two trace streams: the persistent kernel of chunk k+1 moves onto the SMs that
@@ -65,7 +78,7 @@ static int trace_pipelined(pt_scene* s, const pt_ray* rays, size_t n, Launch lau
     static const int n_cs = []{ const char* e = getenv("PTB_TRACE_STREAMS"); return e && atoi(e) == 1 ? 1 : 2; }();
     cudaStream_t cs[2] = { (cudaStream_t)s->stream, n_cs == 2 ? (cudaStream_t)s->stream4 : (cudaStream_t)s->stream };
     cudaStream_t in = (cudaStream_t)s->stream2, out = (cudaStream_t)s->stream3;
-    pt_ray* d_rays = (pt_ray*)s->buf.stage_rays;
+    char* d_rays = (char*)(d_in ? d_in : s->buf.stage_rays);
     const size_t full = chunk_rays();
     size_t k = 0;
     for(size_t off = 0; off < n; k++){
@@ -76,7 +89,7 @@ static int trace_pipelined(pt_scene* s, const pt_ray* rays, size_t n, Launch lau
         cudaStream_t compute = cs[k & 1];
         cudaEvent_t landed = pipeline_event(s, 2 * k), traced = pipeline_event(s, 2 * k + 1);
         if(!landed || !traced)return PT_ERR_CUDA;
-        if(!cuda_ok(cudaMemcpyAsync(d_rays + off, rays + off, m * sizeof(pt_ray), cudaMemcpyHostToDevice, in), "H2D rays") ||
+        if(!cuda_ok(cudaMemcpyAsync(d_rays + off * ray_bytes, (const char*)rays + off * ray_bytes, m * ray_bytes, cudaMemcpyHostToDevice, in), "H2D rays") ||
            !cuda_ok(cudaEventRecord(landed, in), "event") || !cuda_ok(cudaStreamWaitEvent(compute, landed, 0), "wait"))return PT_ERR_CUDA;
         rc = launch(off, m, compute);
         if(rc != PT_OK)return rc;
@@ -113,10 +126,12 @@ constexpr int kStreamGaveUp = 1000;    // internal: the streamed kernel timed ou
 // sends the finished prefix back on the D2H stream.  Against one kernel per chunk this removes every chunk's tail
 // (a 2 Mi-ray launch runs at 0.91 Grays/s, the 16 Mi-ray one at 1.06: profiles/r01_trace4_v7.md).
 // copy_out(off, m, stream) queues the D2H copies of rays [off, off + m).
+// compact: the rays are pt_ray24 records staged in stage_rays24, the kernel writes pt_hit8 into stage_hits8
 template <class CopyOut>
-static int trace_streamed(pt_scene* s, const pt_ray* rays, size_t n, bool any, CopyOut copy_out){
+static int trace_streamed(pt_scene* s, const void* rays, size_t n, bool any, CopyOut copy_out, bool compact = false){
     int rc = ensure_stage(s, n);
     if(rc != PT_OK)return rc;
+    const size_t ray_bytes = compact ? sizeof(pt_ray24) : sizeof(pt_ray);
     DeviceBuffers& b = s->buf;
     const unsigned shift = 18;
     const size_t ng = (n + ((size_t)1 << shift) - 1) >> shift;
@@ -149,19 +164,20 @@ static int trace_streamed(pt_scene* s, const pt_ray* rays, size_t n, bool any, C
     static const bool prof = getenv("PTB_PROFILE") != nullptr;
     cudaEvent_t pe0 = nullptr, pe1 = nullptr, pe2 = nullptr, pe3 = nullptr;
     if(prof){ cudaEventCreate(&pe0); cudaEventCreate(&pe1); cudaEventCreate(&pe2); cudaEventCreate(&pe3); cudaEventRecord(pe0, compute); }
-    rc = launch_trace_streamed(s, any, b.stage_rays, n, b.stage_hits, b.stage_inst, b.stage_occ, ctl, compute);
+    rc = compact ? launch_trace_streamed(s, false, b.stage_rays24, n, b.stage_hits8, b.stage_inst, nullptr, ctl, compute, true)
+                 : launch_trace_streamed(s, any, b.stage_rays, n, b.stage_hits, b.stage_inst, b.stage_occ, ctl, compute);
     if(rc != PT_OK)return rc;
     if(prof)cudaEventRecord(pe1, compute);
     // rays in: a small first chunk so that the kernel has work at once, then 1 Mi-ray chunks, the watermark after each
     if(!cuda_ok(cudaStreamWaitEvent(in, ready, 0), "wait") || !cuda_ok(cudaStreamWaitEvent(poll, ready, 0), "wait"))return PT_ERR_CUDA;
-    pt_ray* d_rays = (pt_ray*)b.stage_rays;
+    char* d_rays = (char*)(compact ? b.stage_rays24 : b.stage_rays);
     size_t k = 0;
     bool enqueue_failed = false;
     for(size_t off = 0; off < n && !enqueue_failed; k++){
         size_t m = k == 0 ? chunk / 16 : k == 1 ? chunk / 4 : chunk;
         if(m > n - off)m = n - off;
         h_wm[k] = (unsigned long long)(off + m);
-        if(!cuda_ok(cudaMemcpyAsync(d_rays + off, rays + off, m * sizeof(pt_ray), cudaMemcpyHostToDevice, in), "H2D rays") ||
+        if(!cuda_ok(cudaMemcpyAsync(d_rays + off * ray_bytes, (const char*)rays + off * ray_bytes, m * ray_bytes, cudaMemcpyHostToDevice, in), "H2D rays") ||
            !cuda_ok(cudaMemcpyAsync(b.stream_aux, h_wm + k, 8, cudaMemcpyHostToDevice, in), "H2D watermark"))enqueue_failed = true;
         off += m;
     }
@@ -411,6 +427,34 @@ int pt_trace_closest(pt_scene* s, const pt_ray* rays, size_t n, pt_hit* hits, ui
             return (int)PT_OK;
         });
     return prc != PT_OK ? prc : check_overflow(s, "pt_trace_closest");
+}
+
+int pt_trace_closest_compact(pt_scene* s, const pt_ray24* rays, size_t n, pt_hit8* hits, uint32_t* inst){
+    PT_CHECK_READY(s);
+    if(n == 0)return PT_OK;
+    if(!rays || !hits){ set_error("null buffer"); return PT_ERR_INVALID; }
+    int rc = ensure_stage24(s, n);
+    if(rc != PT_OK)return rc;
+    DeviceBuffers& b = s->buf;
+    auto out_hits = [&](size_t off, size_t m, cudaStream_t st){
+        if(!cuda_ok(cudaMemcpyAsync(hits + off, (pt_hit8*)b.stage_hits8 + off, m * sizeof(pt_hit8), cudaMemcpyDeviceToHost, st), "D2H hits"))return (int)PT_ERR_CUDA;
+        if(inst && !cuda_ok(cudaMemcpyAsync(inst + off, (uint32_t*)b.stage_inst + off, m * sizeof(uint32_t), cudaMemcpyDeviceToHost, st), "D2H inst"))return (int)PT_ERR_CUDA;
+        return (int)PT_OK;
+    };
+    if(use_streamed(s, n)){
+        rc = trace_streamed(s, rays, n, false, out_hits, true);
+        if(rc != kStreamGaveUp)return rc != PT_OK ? rc : check_overflow(s, "pt_trace_closest_compact");
+        s->streamed_off = true;
+    }
+    // one kernel per chunk: expand the chunk to pt_ray on the device, the ordinary kernel, pack its hits to 8 B
+    const int prc = trace_pipelined(s, rays, n,
+        [&](size_t off, size_t m, cudaStream_t st){
+            int r = launch_expand_rays24((pt_ray24*)b.stage_rays24 + off, (pt_ray*)b.stage_rays + off, m, st);
+            if(r == PT_OK)r = launch_trace_closest(s, (pt_ray*)b.stage_rays + off, m, (pt_hit*)b.stage_hits + off, inst ? (uint32_t*)b.stage_inst + off : nullptr, st);
+            if(r == PT_OK)r = launch_pack_hits8((pt_hit*)b.stage_hits + off, (pt_hit8*)b.stage_hits8 + off, m, st);
+            return r;
+        }, out_hits, sizeof(pt_ray24), b.stage_rays24);
+    return prc != PT_OK ? prc : check_overflow(s, "pt_trace_closest_compact");
 }
 
 int pt_trace_any(pt_scene* s, const pt_ray* rays, size_t n, uint8_t* occluded){

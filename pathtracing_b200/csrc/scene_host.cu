@@ -54,12 +54,12 @@ void scene_free_device(pt_scene* s){
     DeviceBuffers& b = s->buf;
     void** ptrs[] = { &b.n2, &b.n4, &b.n8, &b.tris, &b.inst, &b.n4q, &b.tris64, &b.tile_list, &b.meshes, &b.blas_info, &b.inst_shade, &b.vtx_pos, &b.vtx_nrm, &b.vtx_uv, &b.vtx_tan,
         &b.indices, &b.tri_light, &b.textures, &b.texels, &b.materials, &b.media, &b.lights, &b.light_cdf, &b.env_cdf, &b.film, &b.work, &b.adapt,
-        &b.stage_rays, &b.stage_hits, &b.stage_inst, &b.stage_occ, &b.stats, &b.tri_mesh, &b.inst_light_base, &b.sampler_lights, &b.inf_lights, &b.cursors, &b.film_sq, &b.stream_aux };
+        &b.stage_rays, &b.stage_hits, &b.stage_inst, &b.stage_occ, &b.stage_rays24, &b.stage_hits8, &b.stats, &b.tri_mesh, &b.inst_light_base, &b.sampler_lights, &b.inf_lights, &b.cursors, &b.film_sq, &b.stream_aux };
     for(void** p : ptrs){ if(*p){ cudaFree(*p); *p = nullptr; } }
     if(b.h_counters){ cudaFreeHost(b.h_counters); b.h_counters = nullptr; }
     for(void*& e : b.wave_events)if(e){ cudaEventDestroy((cudaEvent_t)e); e = nullptr; }
     if(b.h_stream){ cudaFreeHost(b.h_stream); b.h_stream = nullptr; }
-    b.work_bytes = 0; b.adapt_bytes = 0; b.tile_list_bytes = 0; b.stage_cap = 0; b.stream_aux_bytes = 0; b.h_stream_bytes = 0;
+    b.work_bytes = 0; b.adapt_bytes = 0; b.tile_list_bytes = 0; b.stage_cap = 0; b.stage24_cap = 0; b.stream_aux_bytes = 0; b.h_stream_bytes = 0;
 }
 
 int scene_commit(pt_scene* s, int width, int light_sampler){

@@ -66,6 +66,7 @@ struct DeviceBuffers {
     size_t adapt_bytes = 0;
     // staging for the host-buffer ray-cast entry points
     void* stage_rays = nullptr; void* stage_hits = nullptr; void* stage_inst = nullptr; void* stage_occ = nullptr;
+    void* stage_rays24 = nullptr; void* stage_hits8 = nullptr; size_t stage24_cap = 0;   // pt_trace_closest_compact
     size_t stage_cap = 0;
     void* stream_aux = nullptr; size_t stream_aux_bytes = 0;   // device: landed watermark, abort flag, per-granule counters
     void* h_stream = nullptr; size_t h_stream_bytes = 0;       // pinned: watermark values + polled copy of stream_aux
@@ -179,7 +180,9 @@ struct ConnectAcc {
     uint32_t ps_slot = 0, ps_off = 0;
 };
 bool probe_async_launch(pt_scene* sc, void* d_words, void* compute_stream, void* copy_stream);
-int launch_trace_streamed(pt_scene* sc, bool any, const void* d_rays, size_t n, void* d_hits, void* d_inst, void* d_occ, const StreamCtl& ctl, void* stream);
+int launch_trace_streamed(pt_scene* sc, bool any, const void* d_rays, size_t n, void* d_hits, void* d_inst, void* d_occ, const StreamCtl& ctl, void* stream, bool compact = false);
+int launch_expand_rays24(const void* d_rays24, void* d_rays, size_t n, void* stream);
+int launch_pack_hits8(const void* d_hits, void* d_hits8, size_t n, void* stream);
 
 int scene_add_shape(pt_scene* s, const pt_shape_desc* d, const float* xf = nullptr);
 int scene_animate(pt_scene* s, int prim_id, const float* dir, const float* tb);

@@ -67,7 +67,8 @@ __device__ __forceinline__ void feed_grab(RayFeed& f, unsigned long long* cursor
     f.avail = left < kChunk ? (unsigned)left : kChunk;
 }
 
-template <int WIDTH, bool ANY, bool STATS, int KS, class Alpha, bool FEED = false>
+// COMPACT (with FEED, closest hit only): rays are 24 B {o, d} records, results 8 B {t, prim} (pt_trace_closest_compact)
+template <int WIDTH, bool ANY, bool STATS, int KS, class Alpha, bool FEED = false, bool COMPACT = false>
 __global__ void __launch_bounds__(kTraceBlock) k_trace(DevScene S, const float4* __restrict__ rays, size_t n,
                                                        float4* __restrict__ hits, uint32_t* __restrict__ inst, uint8_t* __restrict__ occ,
                                                        unsigned long long* __restrict__ cursor, unsigned long long* __restrict__ stats,
@@ -116,7 +117,8 @@ __global__ void __launch_bounds__(kTraceBlock) k_trace(DevScene S, const float4*
                         } else occ[idx] = (s.flags & TF_OCCLUDED) ? 1 : 0;
                     } else{
                         const bool found = s.hprim != 0xFFFFFFFFu;
-                        if(!STATS || hits)hits[idx] = make_float4(found ? s.tmax : CUDART_INF_F, s.hu, s.hv, __uint_as_float(s.hprim));
+                        if constexpr(COMPACT)((float2*)hits)[idx] = make_float2(found ? s.tmax : CUDART_INF_F, __uint_as_float(s.hprim));
+                        else if(!STATS || hits)hits[idx] = make_float4(found ? s.tmax : CUDART_INF_F, s.hu, s.hv, __uint_as_float(s.hprim));
                         if(inst)inst[idx] = s.hinst;
                         if(STATS && found)hitc++;
                     }
@@ -136,7 +138,11 @@ __global__ void __launch_bounds__(kTraceBlock) k_trace(DevScene S, const float4*
             const unsigned rank = __popc(need & lt);
             if((s.flags & TF_DONE) && rank < feed.avail){
                 idx = (size_t)(feed.base + rank);
-                if constexpr(FEED)trav_init<WIDTH>(s, S, __ldcg(rays + 2 * idx), __ldcg(rays + 2 * idx + 1));
+                if constexpr(COMPACT){
+                    float4 ra, rb;
+                    fetch_ray(CgRays24 { (const float2*)rays }, idx, ra, rb);
+                    trav_init<WIDTH>(s, S, ra, rb);
+                } else if constexpr(FEED)trav_init<WIDTH>(s, S, __ldcg(rays + 2 * idx), __ldcg(rays + 2 * idx + 1));
                 else trav_init<WIDTH>(s, S, __ldg(rays + 2 * idx), __ldg(rays + 2 * idx + 1));
             }
             const unsigned want = __popc(need);
@@ -154,7 +160,8 @@ __global__ void __launch_bounds__(kTraceBlock) k_trace(DevScene S, const float4*
             do_leaf = nl >= leaf_min || nl == nv;
         }
         if(!(s.flags & TF_DONE)){
-            if constexpr(FEED)trav_step<WIDTH, ANY, STATS>(s, S, stack, CgRays { rays }, idx, STATS ? &c : nullptr, alpha, do_leaf);
+            if constexpr(COMPACT)trav_step<WIDTH, ANY, STATS>(s, S, stack, CgRays24 { (const float2*)rays }, idx, STATS ? &c : nullptr, alpha, do_leaf);
+            else if constexpr(FEED)trav_step<WIDTH, ANY, STATS>(s, S, stack, CgRays { rays }, idx, STATS ? &c : nullptr, alpha, do_leaf);
             else trav_step<WIDTH, ANY, STATS>(s, S, stack, rays, idx, STATS ? &c : nullptr, alpha, do_leaf);
         }
     }
@@ -310,11 +317,11 @@ static int launch(pt_scene* sc, const void* d_rays, size_t n, void* d_hits, void
 }
 
 // One launch over a ray buffer that is still being filled (capi.cu trace_streamed): plain scenes only
-template <int WIDTH, bool ANY>
+template <int WIDTH, bool ANY, bool COMPACT = false>
 static int launch_feed(pt_scene* sc, const void* d_rays, size_t n, void* d_hits, void* d_inst, void* d_occ, const StreamCtl& ctl, void* stream){
     static int cache[8] = { 0, 0, 0, 0, 0, 0, 0, 0 };
     cudaStream_t st = (cudaStream_t)stream;
-    auto kernel = k_trace<WIDTH, ANY, false, 16, NoAlpha, true>;
+    auto kernel = k_trace<WIDTH, ANY, false, 16, NoAlpha, true, COMPACT>;
     const size_t smem = (size_t)16 * kTraceBlock * sizeof(uint2);
     unsigned grid = persistent_grid(kernel, sc->device, smem, cache[sc->device & 7]);
     const size_t need_ctas = (n + kTraceBlock - 1) / kTraceBlock;
@@ -350,9 +357,16 @@ bool probe_async_launch(pt_scene* sc, void* d_words, void* compute_stream, void*
     return seen == 1u;
 }
 
-int launch_trace_streamed(pt_scene* sc, bool any, const void* d_rays, size_t n, void* d_hits, void* d_inst, void* d_occ, const StreamCtl& ctl, void* stream){
+int launch_trace_streamed(pt_scene* sc, bool any, const void* d_rays, size_t n, void* d_hits, void* d_inst, void* d_occ, const StreamCtl& ctl, void* stream, bool compact){
     if(n == 0)return PT_OK;
     const int w = sc->dev.width;
+    if(compact){
+        // 24 B rays in, 8 B hits out (pt_trace_closest_compact): closest hit only
+        if(sc->dev.fast)return launch_feed<kWidthFast4, false, true>(sc, d_rays, n, d_hits, d_inst, nullptr, ctl, stream);
+        return w == 2 ? launch_feed<2, false, true>(sc, d_rays, n, d_hits, d_inst, nullptr, ctl, stream)
+             : w == 4 ? launch_feed<4, false, true>(sc, d_rays, n, d_hits, d_inst, nullptr, ctl, stream)
+                      : launch_feed<8, false, true>(sc, d_rays, n, d_hits, d_inst, nullptr, ctl, stream);
+    }
     if(sc->dev.fast)return any ? launch_feed<kWidthFast4, true>(sc, d_rays, n, nullptr, nullptr, d_occ, ctl, stream)
                                : launch_feed<kWidthFast4, false>(sc, d_rays, n, d_hits, d_inst, nullptr, ctl, stream);
     if(any)return w == 2 ? launch_feed<2, true>(sc, d_rays, n, nullptr, nullptr, d_occ, ctl, stream)
@@ -361,6 +375,32 @@ int launch_trace_streamed(pt_scene* sc, bool any, const void* d_rays, size_t n, 
     return w == 2 ? launch_feed<2, false>(sc, d_rays, n, d_hits, d_inst, nullptr, ctl, stream)
          : w == 4 ? launch_feed<4, false>(sc, d_rays, n, d_hits, d_inst, nullptr, ctl, stream)
                   : launch_feed<8, false>(sc, d_rays, n, d_hits, d_inst, nullptr, ctl, stream);
+}
+
+// chunked form of pt_trace_closest_compact (small batches, scenes with alpha / wrappers, processes that cannot feed a
+// running kernel): the 24 B rays are expanded to pt_ray on the device, the hits packed to 8 B after the ordinary kernel
+__global__ void k_expand_rays24(const float2* __restrict__ in, float4* __restrict__ out, size_t n){
+    const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if(i >= n)return;
+    const float2 x = in[3 * i], y = in[3 * i + 1], z = in[3 * i + 2];
+    out[2 * i] = make_float4(x.x, x.y, y.x, CUDART_INF_F);
+    out[2 * i + 1] = make_float4(y.y, z.x, z.y, 0.0f);
+}
+__global__ void k_pack_hits8(const float4* __restrict__ in, float2* __restrict__ out, size_t n){
+    const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if(i >= n)return;
+    const float4 h = in[i];
+    out[i] = make_float2(h.x, h.w);
+}
+int launch_expand_rays24(const void* d_rays24, void* d_rays, size_t n, void* stream){
+    if(n == 0)return PT_OK;
+    k_expand_rays24<<<(unsigned)((n + 255) / 256), 256, 0, (cudaStream_t)stream>>>((const float2*)d_rays24, (float4*)d_rays, n);
+    return check_launch("k_expand_rays24");
+}
+int launch_pack_hits8(const void* d_hits, void* d_hits8, size_t n, void* stream){
+    if(n == 0)return PT_OK;
+    k_pack_hits8<<<(unsigned)((n + 255) / 256), 256, 0, (cudaStream_t)stream>>>((const float4*)d_hits, (float2*)d_hits8, n);
+    return check_launch("k_pack_hits8");
 }
 
 int launch_trace_closest(pt_scene* sc, const void* d_rays, size_t n, void* d_hits, void* d_inst, void* stream){

@@ -610,6 +610,20 @@ __device__ __forceinline__ void fetch_ray(const CgRays& r, size_t i, float4& a, 
 __device__ __forceinline__ void fetch_ray(const CgRays& r, size_t i, float4& a, float4& b){ a = r.p[2 * i]; b = r.p[2 * i + 1]; }
 #endif
 
+// compact rays of the host-buffer pipeline (pt_trace_closest_compact): {o, d} in 24 B, tmax = inf, time = 0; 8-byte aligned
+struct CgRays24 { const float2* p; };
+#if defined(__CUDA_ARCH__)
+__device__ __forceinline__ void fetch_ray(const CgRays24& r, size_t i, float4& a, float4& b){
+    const float2 x = __ldcg(r.p + 3 * i), y = __ldcg(r.p + 3 * i + 1), z = __ldcg(r.p + 3 * i + 2);
+    a = make_float4(x.x, x.y, y.x, CUDART_INF_F); b = make_float4(y.y, z.x, z.y, 0.0f);
+}
+#else
+inline void fetch_ray(const CgRays24& r, size_t i, float4& a, float4& b){
+    const float2 x = r.p[3 * i], y = r.p[3 * i + 1], z = r.p[3 * i + 2];
+    a = make_float4(x.x, x.y, y.x, INFINITY); b = make_float4(y.y, z.x, z.y, 0.0f);
+}
+#endif
+
 // One round; the ray is finished once s.flags & TF_DONE.
 // The world-space ray is re-read from its source when a transformed instance is left (cheaper than
 // holding 9 more registers).

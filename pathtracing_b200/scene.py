@@ -328,6 +328,15 @@ class GpuScene:
                                            inst.ctypes.data if want_inst else None))
         return hits, inst
 
+    def trace_closest_compact(self, rays24, want_inst=True):
+        """pt_trace_closest_compact: 24 B rays {o, d} in (tmax = inf, time = 0), 8 B hits {t, prim} out."""
+        rays24 = np.ascontiguousarray(rays24, dtype=capi.RAY24_DTYPE)
+        hits = np.empty(len(rays24), dtype=capi.HIT8_DTYPE)
+        inst = np.empty(len(rays24), dtype=np.uint32) if want_inst else None
+        self._ck(self.lib.pt_trace_closest_compact(self.h, rays24.ctypes.data, len(rays24), hits.ctypes.data,
+                                                   inst.ctypes.data if want_inst else None))
+        return hits, inst
+
     def trace_any(self, rays):
         rays = np.ascontiguousarray(rays, dtype=capi.RAY_DTYPE)
         occ = np.empty(len(rays), dtype=np.uint8)

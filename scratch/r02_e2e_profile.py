@@ -33,3 +33,19 @@ for layout in (capi.LAYOUT_FAST, capi.LAYOUT_EXACT):
         torch.cuda.synchronize()
         print("  device buffers %.3f ms" % ((time.perf_counter() - t0) * 1e3), file=sys.stderr, flush=True)
     gpu.close()
+
+# compact transfer form on the same workload
+for layout in (capi.LAYOUT_FAST,):
+    gpu = GpuScene(synth.soup_scene(1_000_000), 4, layout=layout)
+    lo, hi = gpu.bounds()
+    rays = synth.random_rays(n, lo, hi, seed=1)
+    r24 = np.zeros(n, capi.RAY24_DTYPE); r24["o"], r24["d"] = rays["o"], rays["d"]
+    h24 = torch.from_numpy(r24.view(np.uint8).reshape(-1)).pin_memory()
+    hh8 = torch.empty(n * 8, dtype=torch.uint8).pin_memory()
+    for it in range(5):
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        rc = gpu.lib.pt_trace_closest_compact(gpu.h, h24.data_ptr(), n, hh8.data_ptr(), None)
+        assert rc == 0
+        print("  compact host buffers %.3f ms" % ((time.perf_counter() - t0) * 1e3), file=sys.stderr, flush=True)
+    gpu.close()

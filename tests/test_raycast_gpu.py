@@ -232,6 +232,31 @@ def test_error_paths():
     g.close()
 
 
+@pytest.mark.parametrize("width,layout", [(4, 0), (4, 1), (2, 0), (8, 0)])
+def test_compact_transfer_form_equals_the_full_one(width, layout):
+    """pt_trace_closest_compact (24 B rays in, 8 B hits out): same t bits, primitive and instance ids as pt_trace_closest on the
+    expanded rays -- in the chunked form (small batch; a scene with wrappers) and in the streamed one (>= 1 Mi rays, plain scene)."""
+    for desc, n in ((synth.instanced_scene(3, 24), 3000), (synth.instanced_scene(3, 24), (1 << 20) + 12345), (synth.wrapped_scene()[0], 50000)):
+        g = GpuScene(desc, width, layout=layout)
+        lo, hi = g.bounds()
+        rays = synth.random_rays(n, lo, hi, seed=width + n)
+        r24 = np.zeros(n, capi.RAY24_DTYPE)
+        r24["o"], r24["d"] = rays["o"], rays["d"]
+        want_h, want_i = g.trace_closest(rays)
+        got_h, got_i = g.trace_closest_compact(r24)
+        assert np.array_equal(got_h["t"].view(np.uint32), want_h["t"].view(np.uint32)) and np.array_equal(got_h["prim"], want_h["prim"])
+        assert np.array_equal(got_i, want_i) and (want_h["prim"] != 0xFFFFFFFF).mean() > 0.05
+        got_h2, none = g.trace_closest_compact(r24, want_inst=False)
+        assert none is None and np.array_equal(got_h2, got_h)
+        g.close()
+    with pytest.raises(capi.PtError):
+        g2 = GpuScene(synth.soup_scene(10), 4)
+        try:
+            g2._ck(g2.lib.pt_trace_closest_compact(g2.h, None, 5, None, None))
+        finally:
+            g2.close()
+
+
 def _deep_rays():
     r = np.zeros(4, dtype=capi.RAY_DTYPE)
     r["tmax"] = np.inf
