@@ -123,7 +123,7 @@ EXPORTS = [
     "pt_film_device_ptr", "pt_film_download", "pt_film_download_sumsq", "pt_film_upload",
     "pt_scene_replicate", "pt_multi_create", "pt_multi_destroy", "pt_multi_gpus", "pt_multi_scene", "pt_multi_render",
     "pt_dist_unique_id", "pt_dist_init", "pt_dist_render", "pt_dist_finalize",
-    "pt_unit_shade", "pt_unit_light_count", "pt_unit_light_sample", "pt_unit_hg",
+    "pt_unit_shade", "pt_unit_light_count", "pt_unit_light_sample", "pt_unit_hg", "pt_unit_table",
 ]
 
 _lib = None
@@ -235,6 +235,8 @@ def load_library(path: os.PathLike | None = None) -> C.CDLL:
     lib.pt_unit_light_count.argtypes = [vp]
     lib.pt_unit_light_sample.restype = i
     lib.pt_unit_light_sample.argtypes = [vp, i, sz, vp, vp, i, C.c_float]
+    lib.pt_unit_table.restype = i
+    lib.pt_unit_table.argtypes = [vp, i, vp, sz, C.POINTER(sz)]
     lib.pt_unit_hg.restype = i
     lib.pt_unit_hg.argtypes = [i, C.c_float, sz, vp, vp]
     if path is None:

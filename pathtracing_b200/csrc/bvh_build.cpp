@@ -1,6 +1,8 @@
 // bvh_build.cpp — see bvh_build.hpp.  Compiled with -ffp-contract=off: the SAH
 // costs decide the topology and must not depend on FMA contraction.
 #include "bvh_build.hpp"
+#include "bvh_flatten4.hpp"
+#include "bvh4q_encode.hpp"
 #include "scene_host.hpp"
 #include <algorithm>
 #include <cstring>
@@ -244,114 +246,22 @@ uint32_t flatten2(FlatBvh& f, const BinaryBvh& b, uint32_t ni){
     return me;
 }
 
-// BVH4 collapse.  A cluster is described by a tiny expression tree over the
-// original binary nodes: Leafs of that tree become the cluster's lanes.
-struct Expr {
-    int lane = -1;          // >= 0: a lane holding binary node `node`
-    uint32_t node = 0;
-    uint32_t axis = 0;      // split axis (inner expr)
-    int l = -1, r = -1;     // children (indices into the per-cluster pool)
-};
-
-struct ClusterPlan {
-    Expr pool[7];
-    int used = 0;
-    int root = -1;
-    int add_lane(uint32_t node){ pool[used].node = node; pool[used].lane = 0; return used++; }
-    int add_split(uint32_t axis, int l, int r){ pool[used].axis = axis; pool[used].l = l; pool[used].r = r; pool[used].lane = -1; return used++; }
-};
-
-// Visit order for one octant: at every binary split the near side comes
-// first; a negative direction on the split axis makes the right side near
-// (this is what the 5x27x8 LUT of BVH.hpp:562-718 enumerates).
-void visit(const ClusterPlan& p, int e, unsigned octant, int* out, int& n){
-    const Expr& x = p.pool[e];
-    if(x.lane >= 0){ out[n++] = x.lane; return; }
-    const bool neg = (octant >> x.axis) & 1u;
-    visit(p, neg ? x.r : x.l, octant, out, n);
-    visit(p, neg ? x.l : x.r, octant, out, n);
-}
-
+// BVH4 collapse: the per-cluster logic (which binary nodes become lanes, visit orders) lives in bvh_flatten4.hpp,
+// shared with the device flatten.  Children are emitted lane by lane in increasing lane order, as the reference recursion does.
 uint32_t flatten4(FlatBvh& f, const BinaryBvh& b, uint32_t ni){
     const BuildNode& n = b.nodes[ni];
     if(n.count != 0){ mark_leaf(f, n); return leaf_ref(n.right); }
     { uint32_t job; if(deferred(f, b, ni, f.n4.size(), &job))return job; }
     const uint32_t me = (uint32_t)f.n4.size();
     f.n4.emplace_back();
-
-    const BuildNode& L = b.nodes[n.left];
-    const BuildNode& R = b.nodes[n.right];
-    const bool lleaf = L.count != 0, rleaf = R.count != 0;
     ClusterPlan p;
-    // lane numbers follow BVH4::buildBVH4's slot choices (BVH.hpp:801-1015)
-    auto lane = [&](uint32_t node, int slot){ int e = p.add_lane(node); p.pool[e].lane = slot; return e; };
-    if(lleaf && rleaf){
-        p.root = p.add_split(n.axis, lane(n.left, 0), lane(n.right, 2));
-    } else if(lleaf){
-        const BuildNode& RL = b.nodes[R.left];
-        const BuildNode& RR = b.nodes[R.right];
-        if(RL.count != 0 && RR.count != 0){
-            int sub = p.add_split(R.axis, lane(R.left, 2), lane(R.right, 3));
-            p.root = p.add_split(n.axis, lane(n.left, 0), sub);
-        } else if(RL.count != 0){
-            int low = p.add_split(RR.axis, lane(RR.left, 2), lane(RR.right, 3));
-            int sub = p.add_split(R.axis, lane(R.left, 1), low);
-            p.root = p.add_split(n.axis, lane(n.left, 0), sub);
-        } else{
-            int low = p.add_split(RL.axis, lane(RL.left, 1), lane(RL.right, 2));
-            int sub = p.add_split(R.axis, low, lane(R.right, 3));
-            p.root = p.add_split(n.axis, lane(n.left, 0), sub);
-        }
-    } else if(rleaf){
-        const BuildNode& LL = b.nodes[L.left];
-        const BuildNode& LR = b.nodes[L.right];
-        if(LL.count != 0 && LR.count != 0){
-            int sub = p.add_split(L.axis, lane(L.left, 0), lane(L.right, 1));
-            p.root = p.add_split(n.axis, sub, lane(n.right, 2));
-        } else if(LL.count != 0){
-            int low = p.add_split(LR.axis, lane(LR.left, 1), lane(LR.right, 2));
-            int sub = p.add_split(L.axis, lane(L.left, 0), low);
-            p.root = p.add_split(n.axis, sub, lane(n.right, 3));
-        } else{
-            int low = p.add_split(LL.axis, lane(LL.left, 0), lane(LL.right, 1));
-            int sub = p.add_split(L.axis, low, lane(L.right, 2));
-            p.root = p.add_split(n.axis, sub, lane(n.right, 3));
-        }
-    } else{
-        int a = p.add_split(L.axis, lane(L.left, 0), lane(L.right, 1));
-        int c = p.add_split(R.axis, lane(R.left, 2), lane(R.right, 3));
-        p.root = p.add_split(n.axis, a, c);
-    }
-
-    uint32_t refs[4] = { REF_EMPTY, REF_EMPTY, REF_EMPTY, REF_EMPTY };
-    Box boxes[4];
-    for(int k = 0; k < 4; k++)for(int a = 0; a < 3; a++){ boxes[k].lo[a] = 0.0f; boxes[k].hi[a] = 0.0f; } // inactive lanes: zero boxes (BVH.hpp:46-48)
-    // children are emitted lane by lane in increasing lane order, as the
-    // reference recursion does
-    int by_lane[4] = { -1, -1, -1, -1 };
-    for(int e = 0; e < p.used; e++)if(p.pool[e].lane >= 0)by_lane[p.pool[e].lane] = e;
-    for(int k = 0; k < 4; k++){
-        if(by_lane[k] < 0)continue;
-        const uint32_t child = p.pool[by_lane[k]].node;
-        boxes[k] = b.nodes[child].box;
-        refs[k] = flatten4(f, b, child);
-    }
-    Bvh4Node& o = f.n4[me];
-    for(int k = 0; k < 4; k++){
-        o.xmin[k] = boxes[k].lo[0]; o.xmax[k] = boxes[k].hi[0];
-        o.ymin[k] = boxes[k].lo[1]; o.ymax[k] = boxes[k].hi[1];
-        o.zmin[k] = boxes[k].lo[2]; o.zmax[k] = boxes[k].hi[2];
-        o.ref[k] = refs[k];
-    }
-    for(unsigned oct = 0; oct < 8; oct++){
-        int seq[4], cnt = 0;
-        visit(p, p.root, oct, seq, cnt);
-        bool seen[4] = { false, false, false, false };
-        for(int k = 0; k < cnt; k++)seen[seq[k]] = true;
-        for(int k = 0; k < 4; k++)if(!seen[k])seq[cnt++] = k;   // absent lanes last; never pushed
-        o.order[oct] = (uint8_t)((seq[0] << 6) | (seq[1] << 4) | (seq[2] << 2) | seq[3]);
-    }
-    o.pad[0] = o.pad[1] = 0;
+    plan_cluster4(b.nodes.data(), ni, p);
+    Bvh4Node o;
+    uint32_t lane_node[4];
+    bool lane_used[4];
+    fill_cluster4(b.nodes.data(), p, o, lane_node, lane_used);
+    for(int k = 0; k < 4; k++)if(lane_used[k])o.ref[k] = flatten4(f, b, lane_node[k]);
+    f.n4[me] = o;
     return me;
 }
 
@@ -619,52 +529,7 @@ void encode_bvh4q(const std::vector<Bvh4Node>& n4, std::vector<Bvh4QNode>& out){
     if(nt == 0)nt = 1;
     if(nt > 16)nt = 16;
     if(n < 65536)nt = 1;
-    auto work = [&](size_t lo_i, size_t hi_i){
-        for(size_t i = lo_i; i < hi_i; i++){
-            const Bvh4Node& a = n4[i];
-            Bvh4QNode q;
-            memset(&q, 0, sizeof q);
-            const float* mins[3] = { a.xmin, a.ymin, a.zmin };
-            const float* maxs[3] = { a.xmax, a.ymax, a.zmax };
-            uint32_t words[6] = { 0, 0, 0, 0, 0, 0 };
-            for(int ax = 0; ax < 3; ax++){
-                float lo = std::numeric_limits<float>::infinity(), hi = -lo;
-                for(int c = 0; c < 4; c++)if(a.ref[c] != REF_EMPTY){ lo = std::min(lo, mins[ax][c]); hi = std::max(hi, maxs[ax][c]); }
-                if(!(lo <= hi)){ lo = 0.0f; hi = 0.0f; }              // no child at all: never visited
-                const double mag = std::max(std::max((double)std::fabs(lo), (double)std::fabs(hi)), 1e-30);
-                int e = (int)std::ceil(std::log2(std::max((double)hi - (double)lo, 1e-300) / 254.0));
-                e = std::max(e, (int)std::floor(std::log2(mag)) - 20);
-                e = std::max(e, -120);
-                for(;; e++){
-                    const float step = std::ldexp(1.0f, e);
-                    const float org = lo - 0.25f * step;
-                    bool ok = e <= 120;
-                    uint32_t wl = 0, wh = 0;
-                    for(int c = 0; c < 4 && ok; c++){
-                        if(a.ref[c] == REF_EMPTY){ wl |= 255u << (8 * c); continue; }      // lo planes at 255, hi planes at 0 steps: whichever of the two is the near plane for a ray, the slab interval comes out empty
-                        long ql = (long)std::floor(((double)mins[ax][c] - (double)org) / (double)step - 0.25);
-                        long qh = (long)std::ceil(((double)maxs[ax][c] - (double)org) / (double)step + 0.25);
-                        if(ql < 0)ql = 0;
-                        // float check, the way a decoder would form the planes
-                        while(ql > 0 && !(org + (float)ql * step <= mins[ax][c]))ql--;
-                        while(qh < 256 && !(org + (float)qh * step >= maxs[ax][c]))qh++;
-                        if(!(org + (float)ql * step <= mins[ax][c]) || qh > 255){ ok = false; break; }
-                        wl |= (uint32_t)ql << (8 * c); wh |= (uint32_t)qh << (8 * c);
-                    }
-                    if(ok){
-                        q.org[ax] = org; q.ex[ax] = (uint8_t)(e + 127);
-                        words[ax] = wl; words[3 + ax] = wh;
-                        break;
-                    }
-                    if(e > 120){ q.org[ax] = lo; q.ex[ax] = 254; words[ax] = 0; words[3 + ax] = 0xFFFFFFFFu; break; }   // absurd extents: boxes that always pass
-                }
-            }
-            for(int k = 0; k < 6; k++)q.q[k] = words[k];
-            for(int c = 0; c < 4; c++)q.ref[c] = a.ref[c];
-            for(int k = 0; k < 8; k++)q.order[k] = a.order[k];
-            out[i] = q;
-        }
-    };
+    auto work = [&](size_t lo_i, size_t hi_i){ for(size_t i = lo_i; i < hi_i; i++)encode_node4q(n4[i], out[i]); };     // bvh4q_encode.hpp
     if(nt == 1){ work(0, n); return; }
     std::vector<std::thread> th;
     for(unsigned t = 0; t < nt; t++)th.emplace_back(work, n * t / nt, n * (t + 1) / nt);

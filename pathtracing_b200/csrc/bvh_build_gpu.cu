@@ -750,7 +750,15 @@ struct DevMem {
 // Build on the current device.  On success `out` is what build_binary_bvh() returns for the same boxes
 // (node numbering aside: nodes are reached through left / right, and unused slots stay zero).
 int build_binary_bvh_gpu(const Box* boxes, uint32_t n, uint32_t leaf_size, BinaryBvh& out, GpuBuildTimes* times){
-    out.nodes.clear(); out.order.clear();
+    return build_binary_bvh_gpu_ex(boxes, nullptr, n, leaf_size, &out, nullptr, times);
+}
+
+DeviceBvh2::~DeviceBvh2(){ if(nodes)cudaFree(nodes); if(order)cudaFree(order); }
+
+// The general form: the item boxes come from the host (boxes) or are on the device already (d_boxes_in); the tree goes
+// back to the host (out) and / or stays on the device for the device flatten (keep: scene_pack_gpu.cu).
+int build_binary_bvh_gpu_ex(const Box* boxes, const Box* d_boxes_in, uint32_t n, uint32_t leaf_size, BinaryBvh* out, DeviceBvh2* keep, GpuBuildTimes* times){
+    if(out){ out->nodes.clear(); out->order.clear(); }
     if(n == 0)return PT_OK;
     cudaEvent_t ev[4];
     for(auto& e : ev)if(!cuda_ok(cudaEventCreate(&e), "cudaEventCreate"))return PT_ERR_CUDA;
@@ -760,7 +768,7 @@ int build_binary_bvh_gpu(const Box* boxes, uint32_t n, uint32_t leaf_size, Binar
     const uint32_t max_chunks = n / kChunk + max_tasks + 2;
     const size_t node_cap = 4 * (size_t)n + 16;     // <= 2 per large inner node (< n of them) + 2 * span per subtree
     DevMem d_boxes, d_ilo, d_ihi, d_nodes, d_order, d_tasks[2], d_bins, d_chunks, d_small, d_good, d_bad_pos, d_good_pos, d_cnt;
-    if(!d_boxes.alloc(sizeof(Box) * (size_t)n, "cudaMalloc boxes") || !d_ilo.alloc(16 * (size_t)n, "cudaMalloc items") || !d_ihi.alloc(16 * (size_t)n, "cudaMalloc items") ||
+    if((!d_boxes_in && !d_boxes.alloc(sizeof(Box) * (size_t)n, "cudaMalloc boxes")) || !d_ilo.alloc(16 * (size_t)n, "cudaMalloc items") || !d_ihi.alloc(16 * (size_t)n, "cudaMalloc items") ||
        !d_nodes.alloc(sizeof(GNode) * node_cap, "cudaMalloc nodes") || !d_order.alloc(4 * (size_t)n, "cudaMalloc order") ||
        !d_tasks[0].alloc(sizeof(LTask) * max_tasks, "cudaMalloc tasks") || !d_tasks[1].alloc(sizeof(LTask) * max_tasks, "cudaMalloc tasks") ||
        !d_bins.alloc(sizeof(Bin) * 96 * (size_t)max_tasks, "cudaMalloc bins") || !d_chunks.alloc(sizeof(Chunk) * max_chunks, "cudaMalloc chunks") ||
@@ -773,9 +781,9 @@ int build_binary_bvh_gpu(const Box* boxes, uint32_t n, uint32_t leaf_size, Binar
 
     cudaStream_t st = 0;
     cudaEventRecord(ev[0], st);
-    if(!cuda_ok(cudaMemcpyAsync(d_boxes.p, boxes, sizeof(Box) * (size_t)n, cudaMemcpyHostToDevice, st), "H2D boxes"))return PT_ERR_CUDA;
+    if(!d_boxes_in && !cuda_ok(cudaMemcpyAsync(d_boxes.p, boxes, sizeof(Box) * (size_t)n, cudaMemcpyHostToDevice, st), "H2D boxes"))return PT_ERR_CUDA;
     cudaEventRecord(ev[1], st);
-    k_pack_items<<<(n + 255) / 256, 256, 0, st>>>(d_boxes.as<Box>(), n, d_ilo.as<float4>(), d_ihi.as<float4>());
+    k_pack_items<<<(n + 255) / 256, 256, 0, st>>>(d_boxes_in ? d_boxes_in : d_boxes.as<Box>(), n, d_ilo.as<float4>(), d_ihi.as<float4>());
     if(!cuda_ok(cudaMemsetAsync(d_nodes.p, 0, sizeof(GNode) * node_cap, st), "node pool clear"))return PT_ERR_CUDA;   // unused slots stay zero
 
     Counters init; memset(&init, 0, sizeof init);
@@ -832,16 +840,25 @@ int build_binary_bvh_gpu(const Box* boxes, uint32_t n, uint32_t leaf_size, Binar
        !cuda_ok(cudaStreamSynchronize(st), "bvh subtree build"))return PT_ERR_CUDA;
     const uint32_t nnodes = h_cnt->nnodes;
     if(nnodes > node_cap){ set_error("gpu bvh build: node pool overflow"); return PT_ERR_CUDA; }
-    out.nodes.resize(nnodes);
-    out.order.resize(n);
-    if(!cuda_ok(cudaMemcpyAsync(out.nodes.data(), d_nodes.p, sizeof(GNode) * (size_t)nnodes, cudaMemcpyDeviceToHost, st), "D2H nodes") ||
-       !cuda_ok(cudaMemcpyAsync(out.order.data(), d_order.p, 4 * (size_t)n, cudaMemcpyDeviceToHost, st), "D2H order"))return PT_ERR_CUDA;
+    if(out){
+        out->nodes.resize(nnodes);
+        out->order.resize(n);
+        if(!cuda_ok(cudaMemcpyAsync(out->nodes.data(), d_nodes.p, sizeof(GNode) * (size_t)nnodes, cudaMemcpyDeviceToHost, st), "D2H nodes") ||
+           !cuda_ok(cudaMemcpyAsync(out->order.data(), d_order.p, 4 * (size_t)n, cudaMemcpyDeviceToHost, st), "D2H order"))return PT_ERR_CUDA;
+    }
     cudaEventRecord(ev[3], st);
     if(!cuda_ok(cudaStreamSynchronize(st), "bvh download"))return PT_ERR_CUDA;
     if(times){
         float a = 0, b = 0, c = 0;
         cudaEventElapsedTime(&a, ev[0], ev[1]); cudaEventElapsedTime(&b, ev[1], ev[2]); cudaEventElapsedTime(&c, ev[2], ev[3]);
         times->upload_ms += a; times->build_ms += b; times->download_ms += c; times->levels += levels; times->subtrees += nsmall; times->items += n;
+    }
+    if(keep){
+        if(keep->nodes)cudaFree(keep->nodes);
+        if(keep->order)cudaFree(keep->order);
+        keep->nodes = d_nodes.p; d_nodes.p = nullptr;
+        keep->order = d_order.p; d_order.p = nullptr;
+        keep->n_nodes = nnodes; keep->n = n;
     }
     return PT_OK;
 }

@@ -164,6 +164,8 @@ static uint32_t material_alpha_flags(const pt_scene* s, int mat){
     return TRI_ALPHA_PATH | (can_be_transparent ? TRI_ALPHA_TEX : 0u);
 }
 
+uint32_t mesh_tri_flags(const pt_scene* s, int mesh){ return material_alpha_flags(s, s->meshes[mesh].d.material); }
+
 // SphereShape ctor (Shape.hpp:23-27) / QuadShape ctor (Shape.hpp:120-130): AABB::Expand over the same points
 static Box shape_box(const pt_shape_desc& d){
     Box b = box_empty();
@@ -201,6 +203,12 @@ static void pack_shape(const pt_shape_desc& d, Instance& I){
     I.bhi0 = I.inv[9] * d.p[0] + I.inv[10] * d.p[1] + I.inv[11] * d.p[2];
 }
 
+void (*g_dev_free)(void*) = nullptr;
+void DevBlasPiece::release(){
+    if(g_dev_free){ if(d_nodes)g_dev_free(d_nodes); if(d_tris)g_dev_free(d_tris); }
+    d_nodes = d_tris = nullptr;
+}
+
 // the per-triangle loops of a 10 M-triangle commit (boxes, edge records, the gather into leaf order, ref rebasing) took
 // 1.3 s on one thread: split them over the host threads
 template <class F>
@@ -214,12 +222,15 @@ static void parallel_for(size_t n, F fn){
     for(std::thread& t : th)t.join();
 }
 
-int pack_traversal(pt_scene* s, int width, PackedTraversal& P, BvhBuilder builder, void* user){
+int pack_traversal(pt_scene* s, int width, PackedTraversal& P, BvhBuilder builder, void* user, BlasPacker packer){
     if(width != 2 && width != 4 && width != 8){ set_error("bvh_width must be 2, 4 or 8"); return PT_ERR_INVALID; }
     if(s->instances.empty()){ set_error("scene has no instances"); return PT_ERR_INVALID; }
     std::vector<Bvh2Node>& n2 = P.n2;
     std::vector<Bvh4Node>& n4 = P.n4;
     std::vector<Tri>& tris = P.tris;
+    // scene-wide counts so far: host vectors hold only what was packed on the host (P.node_segs / P.tri_segs say where it goes)
+    size_t g_nodes = 0, g_tris = 0;
+    auto host_nodes = [&]() -> size_t{ return width == 2 ? n2.size() : width == 4 ? n4.size() : P.n8.size(); };
 
     // ---- BLASes ---------------------------------------------------------------------
     for(HostBlas& hb : s->blas){
@@ -227,7 +238,26 @@ int pack_traversal(pt_scene* s, int width, PackedTraversal& P, BvhBuilder builde
         hb.tri_mesh_base.clear();
         for(int mi : hb.meshes){ hb.tri_mesh_base.push_back(hb.n_tris); hb.n_tris += s->meshes[mi].d.n_triangles; }
         if(hb.n_tris == 0){ set_error("empty BLAS"); return PT_ERR_INVALID; }
-        if((uint64_t)tris.size() + hb.n_tris >= 0x7FFFFFFFull){ set_error("too many triangles"); return PT_ERR_INVALID; }
+        if((uint64_t)g_tris + hb.n_tris >= 0x7FFFFFFFull){ set_error("too many triangles"); return PT_ERR_INVALID; }
+        if(packer && width == 4){
+            // the whole BLAS on the device: boxes, binary build, collapse, triangle records (scene_pack_gpu.cu)
+            for(int mi : hb.meshes){
+                const HostMesh& m = s->meshes[mi];
+                if(m.d.material < 0)s->has_boundary = true;
+                if(material_alpha_flags(s, m.d.material) & TRI_ALPHA_TEX)s->has_alpha_tex = true;
+            }
+            DevBlasPiece piece;
+            Box bounds = box_empty();
+            const int prc = packer(s, hb, piece, bounds, user);
+            if(prc < 0)return prc;
+            if(prc == PT_OK){
+                piece.node_base = (uint32_t)g_nodes; piece.tri_base = (uint32_t)g_tris;
+                hb.tri_base = piece.tri_base; hb.bounds = bounds; hb.root = piece.node_base;     // the root cluster is node 0 of the piece
+                g_nodes += piece.n_nodes; g_tris += piece.n_tris;
+                P.dev_pieces.push_back(std::move(piece));
+                continue;
+            }
+        }
         // per-triangle data in original (BLAS-wide) order
         std::vector<Box> boxes(hb.n_tris);
         std::vector<Tri> src(hb.n_tris);
@@ -263,9 +293,14 @@ int pack_traversal(pt_scene* s, int width, PackedTraversal& P, BvhBuilder builde
         const auto tb2 = std::chrono::steady_clock::now();
         s->build_stats.bvh2_s += std::chrono::duration<double>(tb1 - tb0).count();
         s->build_stats.flatten_s += std::chrono::duration<double>(tb2 - tb1).count();
-        hb.tri_base = (uint32_t)tris.size();
+        hb.tri_base = (uint32_t)g_tris;
         hb.bounds = fb.bounds;
-        const uint32_t node_base = width == 2 ? (uint32_t)n2.size() : width == 4 ? (uint32_t)n4.size() : (uint32_t)P.n8.size();
+        const uint32_t node_base = (uint32_t)g_nodes;
+        const size_t h_nodes = host_nodes(), h_tris = tris.size();
+        const size_t fb_nodes = width == 2 ? fb.n2.size() : width == 4 ? fb.n4.size() : fb.n8.size();
+        P.node_segs.push_back({ h_nodes, fb_nodes, g_nodes });
+        P.tri_segs.push_back({ h_tris, hb.n_tris, g_tris });
+        g_nodes += fb_nodes; g_tris += hb.n_tris;
         auto rebase = [&](uint32_t ref) -> uint32_t{
             if(ref == REF_EMPTY)return ref;
             if(ref & REF_LEAF)return REF_LEAF | ((ref & ~REF_LEAF) + hb.tri_base);
@@ -273,21 +308,21 @@ int pack_traversal(pt_scene* s, int width, PackedTraversal& P, BvhBuilder builde
         };
         hb.root = rebase(fb.root);
         if(width == 2){
-            n2.resize(node_base + fb.n2.size());
-            parallel_for(fb.n2.size(), [&](size_t lo, size_t hi){ for(size_t q = lo; q < hi; q++){ Bvh2Node nd = fb.n2[q]; nd.ref0 = rebase(nd.ref0); nd.ref1 = rebase(nd.ref1); n2[node_base + q] = nd; } });
+            n2.resize(h_nodes + fb.n2.size());
+            parallel_for(fb.n2.size(), [&](size_t lo, size_t hi){ for(size_t q = lo; q < hi; q++){ Bvh2Node nd = fb.n2[q]; nd.ref0 = rebase(nd.ref0); nd.ref1 = rebase(nd.ref1); n2[h_nodes + q] = nd; } });
         } else if(width == 4){
-            n4.resize(node_base + fb.n4.size());
-            parallel_for(fb.n4.size(), [&](size_t lo, size_t hi){ for(size_t q = lo; q < hi; q++){ Bvh4Node nd = fb.n4[q]; for(int k = 0; k < 4; k++)nd.ref[k] = rebase(nd.ref[k]); n4[node_base + q] = nd; } });
+            n4.resize(h_nodes + fb.n4.size());
+            parallel_for(fb.n4.size(), [&](size_t lo, size_t hi){ for(size_t q = lo; q < hi; q++){ Bvh4Node nd = fb.n4[q]; for(int k = 0; k < 4; k++)nd.ref[k] = rebase(nd.ref[k]); n4[h_nodes + q] = nd; } });
         } else{
-            P.n8.resize(node_base + fb.n8.size());
-            parallel_for(fb.n8.size(), [&](size_t lo, size_t hi){ for(size_t q = lo; q < hi; q++){ Bvh8Node nd = fb.n8[q]; for(int k = 0; k < 8; k++)nd.ref[k] = rebase(nd.ref[k]); P.n8[node_base + q] = nd; } });
+            P.n8.resize(h_nodes + fb.n8.size());
+            parallel_for(fb.n8.size(), [&](size_t lo, size_t hi){ for(size_t q = lo; q < hi; q++){ Bvh8Node nd = fb.n8[q]; for(int k = 0; k < 8; k++)nd.ref[k] = rebase(nd.ref[k]); P.n8[h_nodes + q] = nd; } });
         }
-        tris.resize((size_t)hb.tri_base + hb.n_tris);
+        tris.resize(h_tris + hb.n_tris);
         parallel_for(hb.n_tris, [&](size_t lo, size_t hi){
             for(size_t i = lo; i < hi; i++){
                 Tri T = src[fb.order[i]];
                 if(fb.leaf_last[i])T.flags |= TRI_LAST;
-                tris[(size_t)hb.tri_base + i] = T;
+                tris[h_tris + i] = T;
             }
         });
     }
@@ -323,7 +358,14 @@ int pack_traversal(pt_scene* s, int width, PackedTraversal& P, BvhBuilder builde
     s->build_stats.bvh2_s += std::chrono::duration<double>(tt1 - tt0).count();
     s->build_stats.flatten_s += std::chrono::duration<double>(std::chrono::steady_clock::now() - tt1).count();
     s->bounds = tf.bounds;
-    const uint32_t tnode_base = width == 2 ? (uint32_t)n2.size() : width == 4 ? (uint32_t)n4.size() : (uint32_t)P.n8.size();
+    const uint32_t tnode_base = (uint32_t)g_nodes;
+    const size_t th_nodes = host_nodes();       // where the TLAS starts in the host vector
+    {
+        const size_t tf_nodes = width == 2 ? tf.n2.size() : width == 4 ? tf.n4.size() : tf.n8.size();
+        P.node_segs.push_back({ th_nodes, tf_nodes, g_nodes });
+        g_nodes += tf_nodes;
+    }
+    P.total_nodes = g_nodes; P.total_tris = g_tris;
     auto trebase = [&](uint32_t ref) -> uint32_t{
         if(ref == REF_EMPTY || (ref & REF_LEAF))return ref;
         return ref + tnode_base;
@@ -388,9 +430,9 @@ int pack_traversal(pt_scene* s, int width, PackedTraversal& P, BvhBuilder builde
         if(ref == REF_EMPTY || !(ref & REF_LEAF))return ref;
         return REF_LEAF | rec_of[ref & ~REF_LEAF];
     };
-    if(width == 2){ for(size_t q = tnode_base; q < n2.size(); q++){ n2[q].ref0 = leaf_fix(n2[q].ref0); n2[q].ref1 = leaf_fix(n2[q].ref1); } }
-    else if(width == 4){ for(size_t q = tnode_base; q < n4.size(); q++)for(int k = 0; k < 4; k++)n4[q].ref[k] = leaf_fix(n4[q].ref[k]); }
-    else{ for(size_t q = tnode_base; q < P.n8.size(); q++)for(int k = 0; k < 8; k++)P.n8[q].ref[k] = leaf_fix(P.n8[q].ref[k]); }
+    if(width == 2){ for(size_t q = th_nodes; q < n2.size(); q++){ n2[q].ref0 = leaf_fix(n2[q].ref0); n2[q].ref1 = leaf_fix(n2[q].ref1); } }
+    else if(width == 4){ for(size_t q = th_nodes; q < n4.size(); q++)for(int k = 0; k < 4; k++)n4[q].ref[k] = leaf_fix(n4[q].ref[k]); }
+    else{ for(size_t q = th_nodes; q < P.n8.size(); q++)for(int k = 0; k < 8; k++)P.n8[q].ref[k] = leaf_fix(P.n8[q].ref[k]); }
 
     if(ni == 1 && !s->instances[0].has_xf && !s->instances[0].animated && s->instances[0].blas >= 0){ P.single_root = s->blas[s->instances[0].blas].root; P.single_id = 0; }
     P.tlas_root = leaf_fix(trebase(tf.root));

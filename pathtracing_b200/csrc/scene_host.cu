@@ -37,6 +37,22 @@ void bind_device_pointers(pt_scene* s){
     D.inf_lights = (const int32_t*)b.inf_lights; D.env_cdf = (const float*)b.env_cdf;
 }
 
+// a scene-wide array of `total` records: the host segments go up here, the device pieces are placed by the caller
+template <class T>
+static bool upload_segs(pt_scene* s, void** dst, const std::vector<T>& v, const std::vector<HostSeg>& segs, size_t total, const char* what){
+    *dst = nullptr;
+    size_t bytes = total * sizeof(T);
+    if(bytes == 0)bytes = 16;
+    if(!cuda_ok(cudaMalloc(dst, bytes), what))return false;
+    for(const HostSeg& g : segs){
+        if(g.count == 0)continue;
+        if(g.host_off + g.count > v.size() || g.global_base + g.count > total){ set_error(std::string(what) + ": segment out of range"); return false; }
+        if(!cuda_ok(cudaMemcpy((T*)*dst + g.global_base, v.data() + g.host_off, g.count * sizeof(T), cudaMemcpyHostToDevice), what))return false;
+    }
+    note_upload(s, dst, bytes);
+    return true;
+}
+
 template <class T>
 static bool upload(pt_scene* s, void** dst, const std::vector<T>& v, const char* what){
     *dst = nullptr;
@@ -79,7 +95,9 @@ int scene_commit(pt_scene* s, int width, int light_sampler){
         return build_binary_bvh_gpu(boxes, n, 2, out, (GpuBuildTimes*)user);
     };
     PackedTraversal P;
-    int prc = s->builder == PT_BUILDER_GPU ? pack_traversal(s, width, P, gpu_builder, &gt) : pack_traversal(s, width, P);
+    // PT_BUILDER_GPU: large BVH4 BLASes are packed on the device from the mesh arrays (scene_pack_gpu.cu: no tree download, no host
+    // flatten, no per-triangle host array); everything else builds its binary tree on the device and flattens it on the host
+    int prc = s->builder == PT_BUILDER_GPU ? pack_traversal(s, width, P, gpu_builder, &gt, pack_blas_on_device) : pack_traversal(s, width, P);
     if(prc != PT_OK)return prc;
     const auto t1 = std::chrono::steady_clock::now();
     std::vector<Bvh2Node>& n2 = P.n2;
@@ -90,11 +108,14 @@ int scene_commit(pt_scene* s, int width, int light_sampler){
     // ---- upload ---------------------------------------------------------------------
     DeviceBuffers& b = s->buf;
     s->uploads.clear();
-    if(!upload(s, &b.n2, n2, "upload bvh2 nodes") || !upload(s, &b.n4, n4, "upload bvh4 clusters") || !upload(s, &b.n8, P.n8, "upload bvh8 clusters") ||
-       !upload(s, &b.tris, tris, "upload triangles") || !upload(s, &b.inst, insts, "upload instances")){
+    static const std::vector<HostSeg> no_segs;
+    if(!upload(s, &b.n2, n2, "upload bvh2 nodes") || !upload_segs(s, &b.n4, n4, width == 4 ? P.node_segs : no_segs, width == 4 ? P.total_nodes : 0, "upload bvh4 clusters") ||
+       !upload(s, &b.n8, P.n8, "upload bvh8 clusters") ||
+       !upload_segs(s, &b.tris, tris, P.tri_segs, P.total_tris, "upload triangles") || !upload(s, &b.inst, insts, "upload instances")){
         scene_free_device(s);
         return PT_ERR_CUDA;
     }
+    for(const DevBlasPiece& pc : P.dev_pieces)if(place_blas_piece(pc, b.n4, b.tris) != PT_OK){ scene_free_device(s); return PT_ERR_CUDA; }
     s->dev.fast = 0;
     if(s->layout == PT_LAYOUT_FAST){
         if(width != 4){ set_error("PT_LAYOUT_FAST needs bvh_width 4"); scene_free_device(s); return PT_ERR_INVALID; }
@@ -102,15 +123,20 @@ int scene_commit(pt_scene* s, int width, int light_sampler){
         encode_bvh4q(n4, n4q);
         std::vector<Tri64> t64(tris.size());
         for(size_t i = 0; i < tris.size(); i++){ t64[i].t = tris[i]; t64[i].pad[0] = t64[i].pad[1] = t64[i].pad[2] = t64[i].pad[3] = 0u; }
-        if(!upload(s, &b.n4q, n4q, "upload quantised bvh4 clusters") || !upload(s, &b.tris64, t64, "upload padded triangles")){ scene_free_device(s); return PT_ERR_CUDA; }
+        if(!upload_segs(s, &b.n4q, n4q, P.node_segs, P.total_nodes, "upload quantised bvh4 clusters") ||
+           !upload_segs(s, &b.tris64, t64, P.tri_segs, P.total_tris, "upload padded triangles")){ scene_free_device(s); return PT_ERR_CUDA; }
+        for(const DevBlasPiece& pc : P.dev_pieces)
+            if(encode_fast_range(b.n4, b.n4q, pc.node_base, pc.n_nodes, b.tris, b.tris64, pc.tri_base, pc.n_tris) != PT_OK){ scene_free_device(s); return PT_ERR_CUDA; }
         s->dev.fast = 1;
     }
+    P.dev_pieces.clear();       // the pieces are in place: their buffers go back
     s->dev.tlas_root = P.tlas_root;
     s->dev.width = width;
     s->dev.single_root = P.single_root; s->dev.single_id = P.single_id;
     for(int a = 0; a < 3; a++){ s->dev.tlo[a] = P.bounds.lo[a]; s->dev.thi[a] = P.bounds.hi[a]; }
-    s->total_tris = tris.size();
-    s->total_nodes = width == 2 ? n2.size() : width == 4 ? n4.size() : P.n8.size();
+    s->total_tris = P.total_tris;
+    s->total_nodes = P.total_nodes;
+    s->n_inst_records = insts.size();
 
     const auto t2 = std::chrono::steady_clock::now();
     int rc = build_shade_tables(s, P.inst_order);

@@ -6,6 +6,7 @@
 #pragma once
 #include <cstdint>
 #include <string>
+#include <utility>
 #include <vector>
 
 #include "../../include/pt_b200.h"
@@ -105,7 +106,7 @@ struct pt_scene {
     ptb::ShadeScene shade {};
     ptb::DeviceBuffers buf;
     int film_w = 0, film_h = 0;
-    uint64_t total_tris = 0, total_nodes = 0;
+    uint64_t total_tris = 0, total_nodes = 0, n_inst_records = 0;
     void* stream = nullptr;       // internal stream for the host-buffer entry points
     void* stream2 = nullptr;      // H2D stage of the host-buffer pipeline
     void* stream3 = nullptr;      // D2H stage
@@ -137,11 +138,37 @@ struct pt_scene {
 
 namespace ptb {
 
+// A BLAS packed on the device (scene_pack_gpu.cu): its clusters and triangle records sit in device buffers of their own, refs local
+// to the BLAS (inner refs index d_nodes, leaf refs index d_tris); pack_traversal gives it its place in the scene-wide arrays.
+struct DevBlasPiece {
+    void* d_nodes = nullptr;      // Bvh4Node[n_nodes], DFS preorder (the host flatten's numbering)
+    void* d_tris = nullptr;       // Tri[n_tris], leaf order
+    uint32_t n_nodes = 0, n_tris = 0;
+    uint32_t node_base = 0, tri_base = 0;     // where it goes in the scene-wide arrays
+    DevBlasPiece() = default;
+    DevBlasPiece(DevBlasPiece&& o) noexcept { *this = std::move(o); }
+    DevBlasPiece& operator=(DevBlasPiece&& o) noexcept {
+        release(); d_nodes = o.d_nodes; d_tris = o.d_tris; n_nodes = o.n_nodes; n_tris = o.n_tris; node_base = o.node_base; tri_base = o.tri_base;
+        o.d_nodes = o.d_tris = nullptr; return *this;
+    }
+    DevBlasPiece(const DevBlasPiece&) = delete;
+    DevBlasPiece& operator=(const DevBlasPiece&) = delete;
+    ~DevBlasPiece(){ release(); }
+    void release();               // through g_dev_free: scene_build.cpp is also linked into host-only test code, which never holds a piece
+};
+extern void (*g_dev_free)(void*);     // set by scene_pack_gpu.cu to a cudaFree wrapper
+// a run of the host vectors below and where it goes in the scene-wide arrays (everything, at offset 0, when no BLAS was packed on the device)
+struct HostSeg { size_t host_off, count, global_base; };
+
 struct PackedTraversal {
     std::vector<Bvh2Node> n2;
     std::vector<Bvh4Node> n4;
     std::vector<Bvh8Node> n8;
     std::vector<Tri> tris;
+    // scene-wide layout: node array = host segments + device pieces, likewise the triangles.  Refs are scene-wide indices.
+    std::vector<HostSeg> node_segs, tri_segs;
+    std::vector<DevBlasPiece> dev_pieces;
+    size_t total_nodes = 0, total_tris = 0;
     std::vector<Instance> insts;      // TLAS leaf order
     std::vector<uint32_t> inst_order; // leaf order -> instance id
     uint32_t tlas_root = REF_EMPTY;
@@ -189,10 +216,27 @@ int scene_animate(pt_scene* s, int prim_id, const float* dir, const float* tb);
 int scene_add_light(pt_scene* s, const pt_light_desc* d);
 // builder: binary build used for every BLAS and the TLAS (null = build_binary_bvh on the host); returns PT_OK or an error
 using BvhBuilder = int (*)(const Box* boxes, uint32_t n, BinaryBvh& out, void* user);
+// packs one BLAS on the device (width 4): PT_OK and `out` filled (bounds = its root box), or 1 = not taken (the host path packs it), or an error
+using BlasPacker = int (*)(pt_scene* s, const HostBlas& hb, DevBlasPiece& out, Box& bounds, void* user);
 // PT_LAYOUT_FAST: quantised copy of the BVH4 clusters (pt_types.h Bvh4QNode); every decoded box contains the exact one
 void encode_bvh4q(const std::vector<Bvh4Node>& n4, std::vector<Bvh4QNode>& out);
-int pack_traversal(pt_scene* s, int width, PackedTraversal& out, BvhBuilder builder = nullptr, void* user = nullptr);
+int pack_traversal(pt_scene* s, int width, PackedTraversal& out, BvhBuilder builder = nullptr, void* user = nullptr, BlasPacker packer = nullptr);
+uint32_t mesh_tri_flags(const pt_scene* s, int mesh);      // TRI_ALPHA_* flags of the mesh's material (scene_build.cpp)
+// scene_pack_gpu.cu
+int pack_blas_on_device(pt_scene* s, const HostBlas& hb, DevBlasPiece& out, Box& bounds, void* user);
+int place_blas_piece(const DevBlasPiece& p, void* d_n4, void* d_tris);
+int encode_fast_range(const void* d_n4, void* d_n4q, uint32_t node_base, uint32_t n_nodes, const void* d_tris, void* d_tris64, uint32_t tri_base, uint32_t n_tris);
 int build_binary_bvh_gpu(const Box* boxes, uint32_t n, uint32_t leaf_size, BinaryBvh& out, GpuBuildTimes* times);   // bvh_build_gpu.cu
+// a binary tree left on the device by the GPU builder: BuildNode[n_nodes] (node 0 = root, unused pool slots zero) and the item order
+struct DeviceBvh2 {
+    void* nodes = nullptr; void* order = nullptr;
+    uint32_t n_nodes = 0, n = 0;
+    DeviceBvh2() = default;
+    DeviceBvh2(const DeviceBvh2&) = delete;
+    DeviceBvh2& operator=(const DeviceBvh2&) = delete;
+    ~DeviceBvh2();
+};
+int build_binary_bvh_gpu_ex(const Box* boxes, const Box* d_boxes_in, uint32_t n, uint32_t leaf_size, BinaryBvh* out, DeviceBvh2* keep, GpuBuildTimes* times);
 // BinaryBvh with nodes renumbered in DFS preorder (left subtree first), the host builder's own numbering
 // below 256 Ki items; makes trees from different builders comparable array by array
 BinaryBvh canonical_bvh(const BinaryBvh& b);

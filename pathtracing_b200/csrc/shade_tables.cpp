@@ -5,6 +5,9 @@
 #include <cfloat>
 #include <cmath>
 #include <cstring>
+#include <cstdlib>
+#include <cstdio>
+#include <chrono>
 #include <thread>
 
 #include "shade_tables.hpp"
@@ -307,8 +310,12 @@ static int build_lights(pt_scene* s, ShadeTables& T, const std::vector<uint32_t>
 }
 
 int build_shade_tables_host(pt_scene* s, const std::vector<uint32_t>& inst_order, ShadeTables& T){
+    static const bool prof = getenv("PTB_PROFILE") != nullptr;
+    const auto t0 = std::chrono::steady_clock::now();
     build_geometry(s, T);
+    const auto t1 = std::chrono::steady_clock::now();
     build_appearance(s, T);
+    const auto t2 = std::chrono::steady_clock::now();
     ShadeScene& V = T.view;
     V.meshes = T.meshes.data(); V.blas = T.blas.data(); V.inst = T.inst.data();
     V.pos = T.pos.data(); V.nrm = T.nrm.data(); V.uv = T.uv.data(); V.tan = T.tan.data(); V.idx = T.idx.data();
@@ -317,6 +324,10 @@ int build_shade_tables_host(pt_scene* s, const std::vector<uint32_t>& inst_order
     V.env_w = 1920; V.env_h = 1080;
     int rc = build_lights(s, T, inst_order);
     if(rc != PT_OK)return rc;
+    if(prof){
+        auto ms = [](auto a, auto b){ return std::chrono::duration<double, std::milli>(b - a).count(); };
+        fprintf(stderr, "[ptb] shade tables (host): geometry %.1f ms, appearance %.1f ms, lights %.1f ms\n", ms(t0, t1), ms(t1, t2), ms(t2, std::chrono::steady_clock::now()));
+    }
     V.inst = T.inst.data();          // light_base was filled in
     V.lights = T.lights.data(); V.sampler_lights = T.sampler_lights.data(); V.sampler_cdf = T.sampler_cdf.data();
     V.inf_lights = T.inf_lights.data(); V.env_cdf = T.env_cdf.data();

@@ -151,4 +151,24 @@ int pt_unit_hg(int device, float g, size_t n, const float* in5, float* out5){
     return PT_OK;
 }
 
+int pt_unit_table(pt_scene* s, int table, void* dst, size_t cap_bytes, size_t* bytes){
+    if(!s || !s->committed || !bytes){ set_error("pt_unit_table: needs a committed scene"); return PT_ERR_INVALID; }
+    if(!cuda_ok(cudaSetDevice(s->device), "cudaSetDevice"))return PT_ERR_CUDA;
+    const DeviceBuffers& b = s->buf;
+    const bool four = s->dev.width == 4;
+    const void* src = nullptr;
+    size_t n = 0;
+    switch(table){
+        case 0: src = b.n4; n = four ? s->total_nodes * sizeof(Bvh4Node) : 0; break;
+        case 1: src = b.tris; n = s->total_tris * sizeof(Tri); break;
+        case 2: src = b.n4q; n = s->dev.fast ? s->total_nodes * sizeof(Bvh4QNode) : 0; break;
+        case 3: src = b.tris64; n = s->dev.fast ? s->total_tris * sizeof(Tri64) : 0; break;
+        case 4: src = b.inst; n = s->n_inst_records * sizeof(Instance); break;
+        default: set_error("pt_unit_table: unknown table"); return PT_ERR_INVALID;
+    }
+    *bytes = n;
+    if(n == 0 || !dst || cap_bytes < n)return PT_OK;
+    return cuda_ok(cudaMemcpy(dst, src, n, cudaMemcpyDeviceToHost), "table download") ? PT_OK : PT_ERR_CUDA;
+}
+
 } // extern "C"

@@ -328,6 +328,15 @@ class GpuScene:
                                            inst.ctypes.data if want_inst else None))
         return hits, inst
 
+    def table(self, which):
+        """pt_unit_table: one of the committed traversal tables as bytes (0 clusters, 1 triangles, 2 quantised clusters, 3 padded triangles, 4 instances)."""
+        n = C.c_size_t(0)
+        self._ck(self.lib.pt_unit_table(self.h, which, None, 0, C.byref(n)))
+        out = np.empty(n.value, np.uint8)
+        if n.value:
+            self._ck(self.lib.pt_unit_table(self.h, which, out.ctypes.data, n.value, C.byref(n)))
+        return out
+
     def trace_closest_compact(self, rays24, want_inst=True):
         """pt_trace_closest_compact: 24 B rays {o, d} in (tmax = inf, time = 0), 8 B hits {t, prim} out."""
         rays24 = np.ascontiguousarray(rays24, dtype=capi.RAY24_DTYPE)
