@@ -285,8 +285,11 @@ def bench_render(a, key, torch, dist, world, rank, local, peak, peak_src):
     rays = 0
     launches = 0
     gpu_ms = 0.0
+    frame_ms = []
     for _ in range(steps):
+        tf = time.perf_counter()
         st, film = multi.render_sharded(scene, cam, params, dist if world > 1 else None)
+        frame_ms.append((time.perf_counter() - tf) * 1e3)
         rays += st["closest_rays"] + st["shadow_rays"]
         launches += st["kernel_launches"]
         gpu_ms += st["gpu_ms"]
@@ -306,7 +309,7 @@ def bench_render(a, key, torch, dist, world, rank, local, peak, peak_src):
         out = {"workload": name, "msamples_per_s": total / (ms * 1e-3) / 1e6,
                "mrays_per_s": rays / steps / (ms * 1e-3) / 1e6, "rays_per_sample": rays / steps / total, "ms_per_frame": ms,
                "ms_render_rank0": gpu_ms / steps,
-               "n_gpus": world, "scaling": "strong", "frames_timed": steps, "scene_build_s": build_s, "scene_synth_s": synth_s,
+               "n_gpus": world, "scaling": "strong", "frames_timed": steps, "frame_ms_rank0": frame_ms, "scene_build_s": build_s, "scene_synth_s": synth_s,
                "collective": "one ncclReduce(sum) of the fp64 film (4*W*H) and sum-of-squares (3*W*H) accumulators inside libptb200.so" if world > 1 else "none",
                "kernel_launches_per_frame": int(launches // steps), "mean_weight": float(img[..., 3].mean()),
                "mean_radiance": float((img[..., :3] / np.maximum(img[..., 3:4], 1e-300)).mean())}

@@ -80,7 +80,8 @@ __global__ void __launch_bounds__(kTraceBlock) k_trace(DevScene S, const float4*
         if(dyn.sel_dev)rays += (size_t)(*dyn.sel_dev) * dyn.sel_stride;
         if(n == 0)return;
     }
-    const unsigned leaf_min = refill_min >> 8;       // packed by the launchers: leaf_min << 8 | refill_min
+    const unsigned leaf_min = (refill_min >> 8) & 0xFFu;       // packed by the launchers: rounds << 16 | leaf_min << 8 | refill_min
+    const int rounds = (int)(refill_min >> 16);                // traversal rounds between two looks at the refill condition
     refill_min &= 0xFFu;
     extern __shared__ uint2 smem_stack[];            // KS rows of kTraceBlock entries
     uint2 spill[kStack > KS ? kStack - KS : 1];
@@ -159,10 +160,13 @@ __global__ void __launch_bounds__(kTraceBlock) k_trace(DevScene S, const float4*
             const unsigned nl = __popc(__ballot_sync(0xffffffffu, at_leaf)), nv = __popc(__ballot_sync(0xffffffffu, live));
             do_leaf = nl >= leaf_min || nl == nv;
         }
+#pragma unroll 1
+        for(int rep = 0; rep < rounds; rep++){
         if(!(s.flags & TF_DONE)){
             if constexpr(COMPACT)trav_step<WIDTH, ANY, STATS>(s, S, stack, CgRays24 { (const float2*)rays }, idx, STATS ? &c : nullptr, alpha, do_leaf);
             else if constexpr(FEED)trav_step<WIDTH, ANY, STATS>(s, S, stack, CgRays { rays }, idx, STATS ? &c : nullptr, alpha, do_leaf);
             else trav_step<WIDTH, ANY, STATS>(s, S, stack, rays, idx, STATS ? &c : nullptr, alpha, do_leaf);
+        }
         }
     }
     if(STATS){
@@ -204,7 +208,8 @@ static int env_int(const char* name, int dflt, int lo, int hi){
     return v < lo ? lo : (v > hi ? hi : v);
 }
 // refill threshold in the low byte, postponed-leaf threshold (PTB_LEAF_MIN, 1 = leaf items are never postponed) above it
-static unsigned refill_min(){ static int v = env_int("PTB_REFILL_MIN", 4, 1, 32) | (env_int("PTB_LEAF_MIN", 1, 1, 32) << 8); return (unsigned)v; }
+// and the traversal rounds per refill check (PTB_ROUNDS: 1 looks every round; 4 measured best, profiles/r02_trace.md) above that
+static unsigned refill_min(){ static int v = env_int("PTB_REFILL_MIN", 4, 1, 32) | (env_int("PTB_LEAF_MIN", 1, 1, 32) << 8) | (env_int("PTB_ROUNDS", 4, 1, 16) << 16); return (unsigned)v; }
 // shared-memory stack rows per lane: 0 (all local), 8, 16 or 24
 static int stack_rows(){ static int v = env_int("PTB_STACK_SMEM", 16, 0, 24); return v; }
 

@@ -392,6 +392,18 @@ __device__ __forceinline__ bool stack_fast(const LocalStack&, int){ return false
 template <int KS, int STRIDE>
 __device__ __forceinline__ void stack_st_sm(const TravStack<KS, STRIDE>& k, int i, uint2 v){ k.sm[i * STRIDE] = v; }
 __device__ __forceinline__ void stack_st_sm(const LocalStack& k, int i, uint2 v){ k.lm[i] = v; }
+// the same store under a predicate, as ONE predicated instruction: written as `if(p)store`, the compiler turns each of a
+// cluster's three pushes into a divergent branch with its own convergence barrier (7 instructions around one STS)
+template <int KS, int STRIDE>
+__device__ __forceinline__ void stack_st_sm_if(const TravStack<KS, STRIDE>& k, int i, uint2 v, bool p){
+#if defined(__CUDA_ARCH__)
+    const unsigned addr = (unsigned)__cvta_generic_to_shared(k.sm + i * STRIDE);
+    asm volatile("{\n\t.reg .pred q;\n\tsetp.ne.u32 q, %3, 0;\n\t@q st.shared.v2.u32 [%0], {%1, %2};\n\t}" :: "r"(addr), "r"(v.x), "r"(v.y), "r"((unsigned)p) : "memory");
+#else
+    if(p)k.sm[i * STRIDE] = v;
+#endif
+}
+__device__ __forceinline__ void stack_st_sm_if(const LocalStack& k, int i, uint2 v, bool p){ if(p)k.lm[i] = v; }
 
 // pop: rows below KS come straight from shared memory (no branch in the common case of a shallow stack)
 template <int KS, int STRIDE>
@@ -429,10 +441,7 @@ __device__ __forceinline__ void node_step4(TravState& s, const DevScene& S, cons
     bool ovf = false;
     const unsigned word = s.octant < 4 ? ord.x : ord.y;
     const unsigned code = (word >> ((s.octant & 3u) * 8u)) & 0xFFu;
-    const bool fast = stack_fast(stack, sp);
-#pragma unroll
-    for(int k = 0; k < 4; k++){
-        uint32_t r; float e; bool hit;
+    auto child = [&](int k, uint32_t& r, float& e, bool& hit){
         if(ANY){
             // any-hit: the answer does not depend on the visit order; BVH4::IntersectPred pushes unordered too (BVH.hpp:1019-1109)
             hit = ((mask >> k) & 1u) != 0;
@@ -447,18 +456,32 @@ __device__ __forceinline__ void node_step4(TravState& s, const DevScene& S, cons
             r = hi ? rb : ra;
             e = hi ? eb : ea;
         }
-        const bool want = hit && cur != REF_EMPTY;
-        if(fast){
-            if(want)stack_st_sm(stack, sp, make_uint2(cur, __float_as_uint(cure)));
+    };
+    if(stack_fast(stack, sp)){
+        // the three possible pushes land in shared-memory rows: straight-line code, one predicated store each
+#pragma unroll
+        for(int k = 0; k < 4; k++){
+            uint32_t r; float e; bool hit;
+            child(k, r, e, hit);
+            const bool want = hit && cur != REF_EMPTY;
+            if(k > 0)stack_st_sm_if(stack, sp, make_uint2(cur, __float_as_uint(cure)), want);
             sp += want ? 1 : 0;
-        } else{
+            cur = hit ? r : cur;
+            cure = hit ? e : cure;
+        }
+    } else{
+#pragma unroll
+        for(int k = 0; k < 4; k++){
+            uint32_t r; float e; bool hit;
+            child(k, r, e, hit);
+            const bool want = hit && cur != REF_EMPTY;
             const bool push = want && sp < kStack;
             ovf |= want && !push;
             if(push)stack.st(sp, make_uint2(cur, __float_as_uint(cure)));
             sp += push ? 1 : 0;
+            cur = hit ? r : cur;
+            cure = hit ? e : cure;
         }
-        cur = hit ? r : cur;
-        cure = hit ? e : cure;
     }
     s.sp = sp;
     s.cur = cur;
@@ -472,6 +495,10 @@ __device__ __forceinline__ void node_step4(TravState& s, const DevScene& S, cons
 // property for candidates at exactly tmax.  Visit order and pop-time cull as in node_step4.
 __device__ __forceinline__ float qbyte(uint32_t w, int c){ return __uint2float_rn((w >> (8 * c)) & 0xFFu); }
 
+#ifndef PTB_SORTED_PUSH
+#define PTB_SORTED_PUSH 1
+#endif
+constexpr bool kSortedPush4q = PTB_SORTED_PUSH != 0;
 template <bool ANY, class STK>
 __device__ __forceinline__ void node_step4q(TravState& s, const DevScene& S, const STK& stack){
     const float4* p = reinterpret_cast<const float4*>(S.n4q + s.cur);
@@ -503,18 +530,16 @@ __device__ __forceinline__ void node_step4q(TravState& s, const DevScene& S, con
     int sp = s.sp;
     const unsigned word = s.octant < 4 ? ord.x : ord.y;
     const unsigned code = (word >> ((s.octant & 3u) * 8u)) & 0xFFu;
-    const bool fast = stack_fast(stack, sp);
     bool ovf = false;
-#pragma unroll
-    for(int k = 0; k < 4; k++){
-        uint32_t r; float en; bool hit;
+    // child k of the visit sequence (k = 0 is the LAST visited lane): its ref, entry distance, and whether the ray enters it
+    auto child = [&](int k, uint32_t& r, float& en, bool& hit){
         if(ANY){
             // any-hit: the answer does not depend on the visit order (the reference pushes unordered too, BVH.hpp:1019-1109)
             hit = ((mask >> k) & 1u) != 0;
             r = k == 0 ? refs.x : k == 1 ? refs.y : k == 2 ? refs.z : refs.w;
             en = e[k];
         } else{
-            const unsigned lane = (code >> (2 * k)) & 3u;   // k = 0 is the LAST visited lane
+            const unsigned lane = (code >> (2 * k)) & 3u;
             hit = ((mask >> lane) & 1u) != 0;
             const bool hi = (lane & 2u) != 0, lo = (lane & 1u) != 0;
             const uint32_t ra = lo ? refs.y : refs.x, rb = lo ? refs.w : refs.z;
@@ -522,18 +547,64 @@ __device__ __forceinline__ void node_step4q(TravState& s, const DevScene& S, con
             r = hi ? rb : ra;
             en = hi ? eb : ea;
         }
-        const bool want = hit && cur != REF_EMPTY;
-        if(fast){
-            if(want)stack_st_sm(stack, sp, make_uint2(cur, __float_as_uint(cure)));
-            sp += want ? 1 : 0;
+    };
+    if(!ANY && kSortedPush4q){
+        // closest hit, fast layout: children ordered by their entry distance with a 5-exchange network instead of the
+        // cluster's per-octant visit bytes (which the exact layout has to follow to reproduce the reference's tie-breaks):
+        // 25 instructions instead of 48 for the decode, and the nearest child really comes first.  Hits differ from the
+        // octant order only where two triangles are hit at bit-equal t (north_star: "ties excepted").
+        float k0 = (mask & 1u) ? e[0] : CUDART_INF_F, k1 = (mask & 2u) ? e[1] : CUDART_INF_F, k2 = (mask & 4u) ? e[2] : CUDART_INF_F, k3 = (mask & 8u) ? e[3] : CUDART_INF_F;
+        uint32_t r0 = refs.x, r1 = refs.y, r2 = refs.z, r3 = refs.w;
+#define PTB_CAS(ka, kb, ra, rb) { const bool sw = kb < ka; const float ta = sw ? kb : ka, tb = sw ? ka : kb; const uint32_t ua = sw ? rb : ra, ub = sw ? ra : rb; ka = ta; kb = tb; ra = ua; rb = ub; }
+        PTB_CAS(k0, k1, r0, r1) PTB_CAS(k2, k3, r2, r3) PTB_CAS(k0, k2, r0, r2) PTB_CAS(k1, k3, r1, r3) PTB_CAS(k1, k2, r1, r2)
+#undef PTB_CAS
+        const bool v0 = k0 < CUDART_INF_F, v1 = k1 < CUDART_INF_F, v2 = k2 < CUDART_INF_F, v3 = k3 < CUDART_INF_F;
+        if(stack_fast(stack, sp)){
+            // the three possible pushes land in shared-memory rows: one predicated store each
+            stack_st_sm_if(stack, sp, make_uint2(r3, __float_as_uint(k3)), v3);
+            sp += v3 ? 1 : 0;
+            stack_st_sm_if(stack, sp, make_uint2(r2, __float_as_uint(k2)), v2);
+            sp += v2 ? 1 : 0;
+            stack_st_sm_if(stack, sp, make_uint2(r1, __float_as_uint(k1)), v1);
+            sp += v1 ? 1 : 0;
         } else{
+            const uint32_t rr[3] = { r3, r2, r1 };
+            const float kk[3] = { k3, k2, k1 };
+            const bool vv[3] = { v3, v2, v1 };
+#pragma unroll
+            for(int q = 0; q < 3; q++){
+                const bool push = vv[q] && sp < kStack;
+                ovf |= vv[q] && !push;
+                if(push)stack.st(sp, make_uint2(rr[q], __float_as_uint(kk[q])));
+                sp += push ? 1 : 0;
+            }
+        }
+        cur = v0 ? r0 : REF_EMPTY;
+    } else if(stack_fast(stack, sp)){
+        // the three possible pushes land in shared-memory rows: straight-line code, one predicated store each
+#pragma unroll
+        for(int k = 0; k < 4; k++){
+            uint32_t r; float en; bool hit;
+            child(k, r, en, hit);
+            const bool want = hit && cur != REF_EMPTY;
+            if(k > 0)stack_st_sm_if(stack, sp, make_uint2(cur, __float_as_uint(cure)), want);
+            sp += want ? 1 : 0;
+            cur = hit ? r : cur;
+            cure = hit ? en : cure;
+        }
+    } else{
+#pragma unroll
+        for(int k = 0; k < 4; k++){
+            uint32_t r; float en; bool hit;
+            child(k, r, en, hit);
+            const bool want = hit && cur != REF_EMPTY;
             const bool push = want && sp < kStack;
             ovf |= want && !push;
             if(push)stack.st(sp, make_uint2(cur, __float_as_uint(cure)));
             sp += push ? 1 : 0;
+            cur = hit ? r : cur;
+            cure = hit ? en : cure;
         }
-        cur = hit ? r : cur;
-        cure = hit ? en : cure;
     }
     s.sp = sp;
     s.cur = cur;
@@ -635,6 +706,9 @@ __device__ __forceinline__ void trav_step(TravState& s, const DevScene& S, const
     if(!do_leaf && (s.cur & REF_LEAF) && s.cur != REF_EMPTY)return;
     // -- pop (BVH4 closest: cull by entry distance, BVH.hpp:1135) --
     if(s.cur == REF_EMPTY){
+        // (a tighter loop for the all-shared-memory case was tried: the compiler then drops the convergence point behind it and the
+        // lanes that leave early run the cluster step on their own, 10.8 -> 17 ms; with the pop hoisted to k_trace's converged loop
+        // plus __syncwarp it is 10.9 ms -- no gain, profiles/r02_trace.md)
         while(s.sp > 0){
             const uint2 e = stack_ld(stack, --s.sp);
             if(WIDTH >= 4 && !ANY && __uint_as_float(e.y) > s.tmax)continue;

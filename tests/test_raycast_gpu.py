@@ -165,8 +165,11 @@ def test_c2_full_size_against_the_reference(mesh, width):
 # ---- PT_LAYOUT_FAST: quantised clusters, same tree ------------------------------------------------------------------------
 
 def _cmp_fast(desc, n_rays=200000, tmax=np.inf, seed=7, allow=0):
-    """Same closest hit as the reference (ids, bits of t, any-hit flag); `allow` bounds the rays where the fast layout,
-    whose boxes contain the reference's, finds a hit that the reference's box arithmetic rounds away (never the reverse)."""
+    """Same closest hit as the reference (ids, bits of t, any-hit flag).  `allow` bounds the rays where the two may differ: ties (two
+    triangles hit at bit-equal t: the fast closest-hit kernel visits children by entry distance, not in the reference's per-octant
+    order, so the other one can win) and hits that the reference's own box arithmetic rounds away by an ulp or two and the fast layout,
+    whose boxes contain the reference's, finds -- never the reverse: the fast kernel's t is never larger.  Measured at full size
+    (scratch/r02_tie_check.py, 2 x 16 Mi rays): 12 rays, 10 ties and 2 hits that are 1 and 2 ulp closer."""
     from oracle.refapi import RefScene
     ref = RefScene(desc, 4, id_mode=True)
     gpu = GpuScene(desc, 4, layout=capi.LAYOUT_FAST)
@@ -201,7 +204,7 @@ def test_fast_layout_small_scenes():
 @needs_ref
 @pytest.mark.parametrize("mesh", ["soup", "surface"])
 def test_fast_layout_c2_full_size_against_the_reference(mesh):
-    _cmp_fast(_full_size_scene(mesh), n_rays=1 << 21, allow=2)
+    _cmp_fast(_full_size_scene(mesh), n_rays=1 << 21, allow=4)
 
 
 def test_fast_layout_needs_width_4_and_streams_like_the_exact_one():
