@@ -41,6 +41,8 @@ def parse():
     ap.add_argument("--rays", type=int, default=1 << 24)
     ap.add_argument("--mesh", default="soup", choices=["soup", "terrain"])
     ap.add_argument("--bvh", type=int, default=4, choices=[2, 4, 8])
+    ap.add_argument("--render-layout", default="auto", choices=["auto", "fast", "exact"],
+                    help="node layout of the render configs: auto = RENDER_LAYOUT per config (fast for C3 / C4 / C5, exact for C1)")
     ap.add_argument("--layout", default="fast", choices=["fast", "exact"],
                     help="BVH4 node layout of the headline: 'fast' = 64 B quantised clusters of the reference's tree (same hits, "
                          "tests/test_raycast_gpu.py), 'exact' = the reference's 128 B cluster content; the other one is reported in extras")
@@ -229,16 +231,18 @@ def render_configs():
 B_STATE_PER_BOUNCE = 2 * 64 + (32 + 4 + 16 + 4) + (32 + 4) + 144
 B_SHADOW_QUEUE = 2 * (32 + 4 + 16)        # a shadow ray, its slot and contribution: written by k_shade, read by the any-hit kernel
 B_SAMPLE_FIXED = 64 + 32 + 4 + 7 * 8      # generate writes state + first ray + slot; the film splat is a read-modify-write of 7 doubles (box filter)
+RENDER_LAYOUT = {"c1": "exact", "c3": "fast", "c4": "fast", "c5": "fast"}     # --render-layout auto
 TEX_LOOKUPS = {"c1": 0, "c3": 0, "c4": 3, "c5": 2}   # image textures evaluated per surface bounce (4 texels x 4 B each, bilinear)
 
 
-def sample_roofline(key, counted, ms, W, H, spp, peak, peak_src):
+def sample_roofline(key, counted, ms, W, H, spp, peak, peak_src, fast=False):
     """B_sample = sum over bounces [B_ray(closest) + B_ray(shadow) + path-state traffic + shading fetches] + film,
     with the visit counts MEASURED by the counting build of the same kernels on this scene (a counted frame at low spp)."""
     st, c, sh = counted
     n_c, n_s, n = max(st["closest_rays"], 1), max(st["shadow_rays"], 1), max(st["samples"], 1)
-    b_closest = 32 + 16 + 4 + ((c["tlas_nodes"] + c["blas_nodes"]) * 128 + c["triangles"] * 48 + c["instances"] * 96) / n_c
-    b_shadow = 32 + ((sh["tlas_nodes"] + sh["blas_nodes"]) * 128 + sh["triangles"] * 48 + sh["instances"] * 96) / n_s
+    s_node, s_tri = (64, 64) if fast else (128, 48)       # bytes of a cluster / a triangle record in the scene's node layout
+    b_closest = 32 + 16 + 4 + ((c["tlas_nodes"] + c["blas_nodes"]) * s_node + c["triangles"] * s_tri + c["instances"] * 96) / n_c
+    b_shadow = 32 + ((sh["tlas_nodes"] + sh["blas_nodes"]) * s_node + sh["triangles"] * s_tri + sh["instances"] * 96) / n_s
     bounces, shadows = n_c / n, st["shadow_rays"] / n
     b_sample = bounces * (b_closest + B_STATE_PER_BOUNCE + TEX_LOOKUPS[key] * 16) + shadows * (b_shadow + B_SHADOW_QUEUE) + B_SAMPLE_FIXED
     achieved = W * H * spp * b_sample / (ms * 1e-3) / 1e9
@@ -255,14 +259,17 @@ def bench_render(a, key, torch, dist, world, rank, local, peak, peak_src):
     """One render config: sample passes sharded over the ranks, one NCCL reduce of the film per frame, all inside
     libptb200.so (pt_dist_render; strong scaling: total work fixed).  Frame time = CUDA events around render + reduce,
     max over ranks."""
-    from pathtracing_b200 import multi
+    from pathtracing_b200 import capi, multi
     from pathtracing_b200.scene import GpuScene, render_params
     name, builder, W, H, spp, depth, integ = render_configs()[key]
     t0 = time.perf_counter()
     desc, cam = builder()
     synth_s = time.perf_counter() - t0
     t0 = time.perf_counter()
-    scene = GpuScene(desc, 4, device=local)
+    # node layout per config: the quantised 64 B clusters win wherever rays diverge (C3 +8 %, C4 +7 %, measured with this build); the
+    # 512 x 512 Cornell frame is all coherent rays over 36 triangles and is a few % faster on the exact clusters
+    fast = RENDER_LAYOUT.get(key, "exact") == "fast" if a.render_layout == "auto" else a.render_layout == "fast"
+    scene = GpuScene(desc, 4, device=local, layout=capi.LAYOUT_FAST if fast else capi.LAYOUT_EXACT)
     build_s = time.perf_counter() - t0
     scene.dist_init(dist if world > 1 else None)
     params = render_params(W, H, spp, depth, integrator=integ, seed=1)
@@ -280,6 +287,9 @@ def bench_render(a, key, torch, dist, world, rank, local, peak, peak_src):
     if world > 1:
         dist.barrier()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    import gc
+    gc.collect()
+    gc.disable()            # a generation-2 collection inside a 5 ms frame showed up as one 30-100 ms frame in five (frame_ms_rank0)
     t_wall = time.perf_counter()
     e0.record()
     rays = 0
@@ -298,6 +308,7 @@ def bench_render(a, key, torch, dist, world, rank, local, peak, peak_src):
     # pt_dist_render is synchronous and runs on the scene's own stream: the wall clock around it is the frame time
     # (torch's events bracket the same region on torch's stream and agree when the region is long)
     ms = (time.perf_counter() - t_wall) * 1e3 / steps
+    gc.enable()
     if world > 1:
         t = torch.tensor([ms, float(rays)], device="cuda", dtype=torch.float64)
         dist.all_reduce(t[:1], op=dist.ReduceOp.MAX)
@@ -309,14 +320,14 @@ def bench_render(a, key, torch, dist, world, rank, local, peak, peak_src):
         out = {"workload": name, "msamples_per_s": total / (ms * 1e-3) / 1e6,
                "mrays_per_s": rays / steps / (ms * 1e-3) / 1e6, "rays_per_sample": rays / steps / total, "ms_per_frame": ms,
                "ms_render_rank0": gpu_ms / steps,
-               "n_gpus": world, "scaling": "strong", "frames_timed": steps, "frame_ms_rank0": frame_ms, "scene_build_s": build_s, "scene_synth_s": synth_s,
+               "n_gpus": world, "scaling": "strong", "frames_timed": steps, "frame_ms_rank0": frame_ms, "node_layout": "fast" if fast else "exact", "scene_build_s": build_s, "scene_synth_s": synth_s,
                "collective": "one ncclReduce(sum) of the fp64 film (4*W*H) and sum-of-squares (3*W*H) accumulators inside libptb200.so" if world > 1 else "none",
                "kernel_launches_per_frame": int(launches // steps), "mean_weight": float(img[..., 3].mean()),
                "mean_radiance": float((img[..., :3] / np.maximum(img[..., 3:4], 1e-300)).mean())}
         if world == 1:
             cspp = max(1, min(spp, 4))
             counted = scene.counted_render(cam, render_params(W, H, cspp, depth, integrator=integ, seed=3))
-            out["roofline"] = sample_roofline(key, counted, ms, W, H, spp, peak, peak_src)
+            out["roofline"] = sample_roofline(key, counted, ms, W, H, spp, peak, peak_src, fast=fast)
     scene.close()
     return out
 

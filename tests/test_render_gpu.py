@@ -480,3 +480,30 @@ def test_film_tensor_view_and_single_rank_reduce():
     assert torch.equal(film.cpu(), torch.from_numpy(host.reshape(-1)))
     assert float(host[..., 3].min()) == 4.0 == float(host[..., 3].max())
     gpu.close()
+
+
+@pytest.mark.parametrize("case", ["c3", "c4", "materials", "wrapped", "boundary"])
+def test_render_on_the_fast_layout_gives_the_same_film(case):
+    """PT_LAYOUT_FAST under pt_render (what bench.py uses for C3 / C4 / C5): the quantised clusters only decide which triangles get
+    tested, the sample streams are keyed by sample id, so the film must be the exact layout's film up to the order of the fp64 sums --
+    except for the rare paths that meet a tie (two triangles at bit-equal t; the fast closest-hit kernel visits children by entry
+    distance).  Every integrator, textures, a medium, wrappers with motion blur, a medium boundary (k_shadow_tr on the fast layout)."""
+    desc, cam, integ = {
+        "c3": lambda: (*synth.c3_scene(subdiv=3, n_instances=20), capi.INTEGRATOR_PATH),
+        "c4": lambda: (*synth.c4_scene(tex_size=64, subdiv=3), capi.INTEGRATOR_VOLPATH),
+        "materials": lambda: (*synth.materials_scene(subdiv=3), capi.INTEGRATOR_SIMPLE),
+        "wrapped": lambda: (*synth.wrapped_scene(), capi.INTEGRATOR_PATH),
+        "boundary": lambda: (*synth.shapes_scene(boundary=True), capi.INTEGRATOR_VOLPATH),
+    }[case]()
+    p = render_params(96, 64, 8, 6, integrator=integ, seed=3)
+    films = []
+    for layout in (capi.LAYOUT_EXACT, capi.LAYOUT_FAST):
+        g = GpuScene(desc, 4, layout=layout)
+        st = g.render(cam, p)
+        films.append((st, g.film().copy()))
+        g.close()
+    (sa, fa), (sb, fb) = films
+    assert np.array_equal(fa[..., 3], fb[..., 3]) and sa["samples"] == sb["samples"]
+    same = np.isclose(fa[..., :3], fb[..., :3], rtol=1e-9, atol=1e-12).all(axis=-1)
+    assert same.mean() >= 0.999, float(same.mean())
+    assert abs(sa["closest_rays"] - sb["closest_rays"]) <= 1e-4 * sa["closest_rays"]
