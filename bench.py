@@ -320,6 +320,7 @@ def bench_render(a, key, torch, dist, world, rank, local, peak, peak_src):
         out = {"workload": name, "msamples_per_s": total / (ms * 1e-3) / 1e6,
                "mrays_per_s": rays / steps / (ms * 1e-3) / 1e6, "rays_per_sample": rays / steps / total, "ms_per_frame": ms,
                "ms_render_rank0": gpu_ms / steps,
+               "msamples_per_s_median_frame": total / (sorted(frame_ms)[len(frame_ms) // 2] * 1e-3) / 1e6,    # rank 0's median frame: the mean above carries every host hiccup of a 1-5 ms frame
                "n_gpus": world, "scaling": "strong", "frames_timed": steps, "frame_ms_rank0": frame_ms, "node_layout": "fast" if fast else "exact", "scene_build_s": build_s, "scene_synth_s": synth_s,
                "collective": "one ncclReduce(sum) of the fp64 film (4*W*H) and sum-of-squares (3*W*H) accumulators inside libptb200.so" if world > 1 else "none",
                "kernel_launches_per_frame": int(launches // steps), "mean_weight": float(img[..., 3].mean()),

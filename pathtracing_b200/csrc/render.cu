@@ -402,7 +402,7 @@ __device__ __forceinline__ uint32_t shade_class(const Arena& A, const ShadeScene
     const DevInstShade& I = S.inst[A.hinst[j]];
     int mat;
     if(I.shape >= 0)mat = I.material;
-    else mat = S.meshes[S.tri_mesh[S.blas[I.blas].tri_base + prim]].material;
+    else mat = S.meshes[S.stri[I.tri_base + prim].mesh].material;
     if(mat < 0)return 1u;
     return 2u + (uint32_t)S.materials[mat].kind;      // pt_mat_kind 0..3
 }

@@ -30,7 +30,7 @@ void bind_device_pointers(pt_scene* s){
     ShadeScene& D = s->shade;
     D.meshes = (const DevMesh*)b.meshes; D.blas = (const DevBlasInfo*)b.blas_info; D.inst = (const DevInstShade*)b.inst_shade;
     D.pos = (const float*)b.vtx_pos; D.nrm = (const float*)b.vtx_nrm; D.uv = (const float*)b.vtx_uv; D.tan = (const float*)b.vtx_tan;
-    D.idx = (const uint32_t*)b.indices; D.tri_mesh = (const uint32_t*)b.tri_mesh; D.tri_emis = (const int32_t*)b.tri_light;
+    D.idx = (const uint32_t*)b.indices; D.stri = (const ShadeTri*)b.tri_mesh; D.tri_emis = (const int32_t*)b.tri_light;
     D.textures = (const DevTexture*)b.textures; D.texels = (const uint8_t*)b.texels;
     D.materials = (const DevMaterial*)b.materials; D.media = (const DevMedium*)b.media;
     D.lights = (const DevLight*)b.lights; D.sampler_lights = (const int32_t*)b.sampler_lights; D.sampler_cdf = (const float*)b.light_cdf;

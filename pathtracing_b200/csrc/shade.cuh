@@ -98,11 +98,9 @@ PT_HDN void build_interaction(const ShadeScene& S, V3 ro, V3 rd, float time, flo
         si.light = I.light_base;
         return;
     }
-    const DevBlasInfo bi = S.blas[I.blas];
-    const uint32_t mesh = S.tri_mesh[bi.tri_base + prim];
-    const DevMesh m = S.meshes[mesh];
-    const uint32_t tri = prim - m.prim_base;
-    const uint32_t i0 = m.vtx_base + S.idx[m.idx_base + 3 * tri], i1 = m.vtx_base + S.idx[m.idx_base + 3 * tri + 1], i2 = m.vtx_base + S.idx[m.idx_base + 3 * tri + 2];
+    const ShadeTri st = S.stri[I.tri_base + prim];      // vertices and mesh in one load (shade_types.h)
+    const DevMesh m = S.meshes[st.mesh];
+    const uint32_t i0 = st.i0, i1 = st.i1, i2 = st.i2;
     const V3 v0 = ld3(S.pos + 3 * (size_t)i0), v1 = ld3(S.pos + 3 * (size_t)i1), v2 = ld3(S.pos + 3 * (size_t)i2);
     V3 o = ro, d = rd;
     float tl = t;
@@ -138,7 +136,7 @@ PT_HDN void build_interaction(const ShadeScene& S, V3 ro, V3 rd, float time, flo
     si.mat = m.material; si.medium = m.medium; si.emis_tex = m.emissive_tex;
     si.light = -1;
     if(m.emissive_tex >= 0 && I.light_base >= 0){
-        const int32_t k = S.tri_emis[bi.tri_base + prim];
+        const int32_t k = S.tri_emis[I.tri_base + prim];
         if(k >= 0){
             const int32_t li = I.light_base + k;
             if(S.lights[li].valid)si.light = li;

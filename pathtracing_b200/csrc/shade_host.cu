@@ -35,7 +35,7 @@ int build_shade_tables(pt_scene* s, const std::vector<uint32_t>& inst_order){
     const auto tu0 = std::chrono::steady_clock::now();
     if(!up(&b.meshes, T.meshes, "meshes") || !up(&b.blas_info, T.blas, "blas info") || !up(&b.inst_shade, T.inst, "instances") ||
        !up(&b.vtx_pos, T.pos, "positions") || !up(&b.vtx_nrm, T.nrm, "normals") || !up(&b.vtx_uv, T.uv, "texcoords") ||
-       !up(&b.vtx_tan, T.tan, "tangents") || !up(&b.indices, T.idx, "indices") || !up(&b.tri_mesh, T.tri_mesh, "tri_mesh") ||
+       !up(&b.vtx_tan, T.tan, "tangents") || !up(&b.indices, T.idx, "indices") || !up(&b.tri_mesh, T.stri, "shading triangles") ||
        !up(&b.tri_light, T.tri_emis, "tri_emis") || !up(&b.textures, T.textures, "textures") || !up(&b.texels, T.texels, "texels") ||
        !up(&b.materials, T.materials, "materials") || !up(&b.media, T.media, "media") || !up(&b.lights, T.lights, "lights") ||
        !up(&b.sampler_lights, T.sampler_lights, "sampler lights") || !up(&b.light_cdf, T.sampler_cdf, "light cdf") ||

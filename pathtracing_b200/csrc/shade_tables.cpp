@@ -50,7 +50,7 @@ static void build_geometry(pt_scene* s, ShadeTables& T){
         for(const HostMesh& m : s->meshes){ nv += m.pos.size() / 3; ni += m.idx.size(); }
         for(const HostBlas& hb : s->blas)nt += hb.n_tris;
         T.pos.reserve(3 * nv); T.nrm.reserve(3 * nv); T.uv.reserve(2 * nv); T.tan.reserve(3 * nv); T.idx.reserve(ni);
-        T.tri_mesh.reserve(nt); T.tri_emis.reserve(nt);
+        T.stri.reserve(nt); T.tri_emis.reserve(nt);
     }
     for(const HostMesh& m : s->meshes){
         DevMesh d {};
@@ -68,17 +68,22 @@ static void build_geometry(pt_scene* s, ShadeTables& T){
         T.meshes.push_back(d);
     }
     // per-BLAS triangle tables in original (BLAS-wide) order.  A mesh used by two BLASes keeps
-    // the prim_base of the last one; BLAS-wide ids are resolved through tri_mesh + the running base.
+    // the prim_base of the last one; shading resolves BLAS-wide ids through the ShadeTri table, which needs no prim_base.
     for(const HostBlas& hb : s->blas){
         DevBlasInfo bi {};
-        bi.tri_base = (uint32_t)T.tri_mesh.size();
+        bi.tri_base = (uint32_t)T.stri.size();
         bi.n_tris = hb.n_tris;
         int32_t emis = 0;
         for(size_t k = 0; k < hb.meshes.size(); k++){
             const int mi = hb.meshes[k];
             const HostMesh& m = s->meshes[mi];
             T.meshes[mi].prim_base = hb.tri_mesh_base[k];
-            T.tri_mesh.insert(T.tri_mesh.end(), m.d.n_triangles, (uint32_t)mi);
+            {
+                const uint32_t vb = T.meshes[mi].vtx_base;
+                const size_t at = T.stri.size();
+                T.stri.resize(at + m.d.n_triangles);
+                for(uint32_t t = 0; t < m.d.n_triangles; t++)T.stri[at + t] = { vb + m.idx[3 * (size_t)t], vb + m.idx[3 * (size_t)t + 1], vb + m.idx[3 * (size_t)t + 2], (uint32_t)mi };
+            }
             if(m.d.emissive_tex >= 0)for(uint32_t t = 0; t < m.d.n_triangles; t++)T.tri_emis.push_back(emis++);
             else T.tri_emis.insert(T.tri_emis.end(), m.d.n_triangles, -1);
         }
@@ -108,7 +113,10 @@ static void build_geometry(pt_scene* s, ShadeTables& T){
                 for(int k = 0; k < 3; k++){ d.shp[3 + k] = sd.u[k]; d.shp[6 + k] = sd.v[k]; }
                 d.shp[9] = n.x; d.shp[10] = n.y; d.shp[11] = n.z;
             }
-        } else d.blas = (uint32_t)hi.blas;
+        } else{
+            d.blas = (uint32_t)hi.blas;
+            d.tri_base = T.blas[hi.blas].tri_base;
+        }
         T.inst.push_back(d);
     }
 }
@@ -319,7 +327,7 @@ int build_shade_tables_host(pt_scene* s, const std::vector<uint32_t>& inst_order
     ShadeScene& V = T.view;
     V.meshes = T.meshes.data(); V.blas = T.blas.data(); V.inst = T.inst.data();
     V.pos = T.pos.data(); V.nrm = T.nrm.data(); V.uv = T.uv.data(); V.tan = T.tan.data(); V.idx = T.idx.data();
-    V.tri_mesh = T.tri_mesh.data(); V.tri_emis = T.tri_emis.data();
+    V.stri = T.stri.data(); V.tri_emis = T.tri_emis.data();
     V.textures = T.textures.data(); V.texels = T.texels.data(); V.materials = T.materials.data(); V.media = T.media.data();
     V.env_w = 1920; V.env_h = 1080;
     int rc = build_lights(s, T, inst_order);

@@ -11,7 +11,8 @@ struct ShadeTables {
     std::vector<DevBlasInfo> blas;
     std::vector<DevInstShade> inst;
     std::vector<float> pos, nrm, uv, tan;
-    std::vector<uint32_t> idx, tri_mesh;
+    std::vector<uint32_t> idx;
+    std::vector<ShadeTri> stri;
     std::vector<int32_t> tri_emis;
     std::vector<DevTexture> textures;
     std::vector<uint8_t> texels;

@@ -40,8 +40,14 @@ struct DevInstShade {
     float shp[12];
     float adir[3];
     float atb[2];
-    uint32_t pad[3];
+    uint32_t tri_base;       // BLAS instance: offset of its BLAS in the per-triangle tables (DevBlasInfo::tri_base, copied here: one dependent load less per shaded hit)
+    uint32_t pad[2];
 };
+
+// What shading needs to know about a triangle, one 16 B load at [instance.tri_base + prim]: its three vertices in the global
+// vertex arrays and its mesh.  (Round 1 walked instance -> BLAS info -> tri_mesh -> mesh -> 3 indices -> vertices: five dependent
+// loads before the first vertex arrives, in a kernel that is latency-bound at 24 warps per SM.)
+struct ShadeTri { uint32_t i0, i1, i2, mesh; };
 
 struct DevTexture {
     int32_t kind;            // pt_tex_kind
@@ -99,7 +105,7 @@ struct ShadeScene {
     const float* uv;         // 2 floats per vertex
     const float* tan;        // 3 floats per vertex (zeros if mesh has none)
     const uint32_t* idx;
-    const uint32_t* tri_mesh;  // per BLAS-wide triangle (original order): mesh id
+    const ShadeTri* stri;      // per BLAS-wide triangle (original order): global vertex ids + mesh id
     const int32_t* tri_emis;   // per BLAS-wide triangle: ordinal among the BLAS's emissive triangles, or -1
     const DevTexture* textures;
     const uint8_t* texels;
