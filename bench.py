@@ -281,11 +281,13 @@ def bench_render(a, key, torch, dist, world, rank, local, peak, peak_src):
     # scene -- enough samples per rank to size the wavefront arena as the full frame does (64 Mi slots), so that the timed
     # frame does not pay a 16 GB cudaMalloc
     warm = params if not very_heavy else render_params(W, H, min(spp, 64 * world), depth, integrator=integ, seed=2)
+    # the barrier comes BEFORE the warm-up frames: every frame ends in a collective of its own (the film reduce), which keeps the ranks
+    # together, and the first frame behind a torch NCCL barrier took 6.8 ms instead of 1.5 (C1 on 8 GPUs, r02_bench_n8_v3.json)
+    if world > 1:
+        dist.barrier()
     for _ in range(1 if heavy else 3):
         multi.render_sharded(scene, cam, warm, dist if world > 1 else None)
     torch.cuda.synchronize()
-    if world > 1:
-        dist.barrier()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     import gc
     gc.collect()

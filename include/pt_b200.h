@@ -216,8 +216,14 @@ PT_API int pt_scene_commit(pt_scene*, int bvh_width, int light_sampler);
  * TLAS runs.  PT_BUILDER_GPU takes the same decisions with the same float operations on the device
  * (csrc/bvh_build_gpu.cu) and yields the same tree and leaf order as PT_BUILDER_HOST, so the packed
  * BVH2 / BVH4 / BVH8 arrays are byte-identical; hierarchies under 4096 items stay on the host (launch
- * overhead).  Call before pt_scene_commit.  Default: PT_BUILDER_GPU (a 10 M-triangle commit 5.75 s -> 3.7 s,
- * profiles/r02_build_check.log); PTB_BUILDER=host in the environment selects the host builder at pt_scene_create.  */
+ * overhead).  With PT_BUILDER_GPU a BVH4 BLAS of 4096 triangles or more is packed on the device altogether
+ * (csrc/scene_pack_gpu.cu: triangle boxes from the mesh arrays, the binary build, the BVH4 collapse in the host
+ * flatten's DFS numbering, the triangle records, the quantised clusters): the same bytes as the host path
+ * (tests/test_bvh_build.py::test_blas_packed_on_the_device_gives_the_host_arrays), no tree download, no
+ * per-triangle host array.  Call before pt_scene_commit.  Default: PT_BUILDER_GPU (a 10 M-triangle commit
+ * 3.9 s on the host -> 0.44-0.62 s, profiles/r02_build_check_v3.log, r02_bench_v6.json); PTB_BUILDER=host in
+ * the environment selects the host builder at pt_scene_create, PTB_GPU_PACK=0 keeps the GPU builder but
+ * flattens on the host.                                                                                       */
 typedef enum pt_builder { PT_BUILDER_HOST = 0, PT_BUILDER_GPU = 1 } pt_builder;
 PT_API int pt_scene_set_builder(pt_scene*, int builder);
 
@@ -225,13 +231,15 @@ PT_API int pt_scene_set_builder(pt_scene*, int builder);
  * PT_LAYOUT_EXACT (default): the reference's BVH4_CLUSTER content (BVH.hpp:45-60) in
  * 128 B, box tests in the reference's own arithmetic: the same nodes are visited in
  * the same order, exact ties resolve to the same triangle.
- * PT_LAYOUT_FAST: the SAME tree and visit order with the child boxes quantised to
- * 8 bits per plane around a per-cluster origin (64 B per cluster, 64 B per triangle
- * record), rounded outwards, so every box contains the exact one.  Triangle tests are
- * unchanged, so the closest hit (primitive / instance id, bits of t) is the
- * reference's except where two candidates tie exactly or the reference's own box
- * test rounds a grazing hit away.  Half the 32 B sectors per cluster visit: the
- * traversal is bound by L1 wavefronts, not bytes.               */
+ * PT_LAYOUT_FAST: the SAME tree with the child boxes quantised to 8 bits per plane
+ * around a per-cluster origin (64 B per cluster, 64 B per triangle record), rounded
+ * outwards, so every box contains the exact one; the closest-hit kernel visits a
+ * cluster's children by entry distance instead of the reference's per-octant order.
+ * Triangle tests are unchanged, so the closest hit (primitive / instance id, bits of
+ * t) is the reference's except where two candidates tie exactly or the reference's
+ * own box test rounds a hit away that is an ulp or two closer (12 of 33.5 M rays,
+ * profiles/r02_tie_check.log); t is never larger.  Half the 32 B sectors per cluster
+ * visit and 15 % fewer instructions: 1.62 against 1.07 Grays/s.   */
 typedef enum pt_layout { PT_LAYOUT_EXACT = 0, PT_LAYOUT_FAST = 1 } pt_layout;
 PT_API int pt_scene_set_layout(pt_scene*, int layout);
 
