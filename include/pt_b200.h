@@ -468,7 +468,8 @@ PT_API int pt_unit_light_sample(pt_scene*, int light, size_t n, const float* in5
 PT_API int pt_unit_hg(int device, float g, size_t n, const float* in5, float* out5);
 /* A committed scene's traversal tables read back (tests compare the device-packed arrays with the host-packed ones byte for
  * byte): table 0 BVH4 clusters (128 B), 1 triangles (48 B), 2 quantised clusters (64 B, PT_LAYOUT_FAST), 3 padded triangles
- * (64 B), 4 instance records (96 B).  *bytes = the table's size; copied only if it fits cap_bytes.                        */
+ * (64 B), 4 instance records (96 B); the shading geometry: 5 positions, 6 normals, 7 texcoords, 8 tangents, 9 indices, 10 shading
+ * triangles (16 B), 11 emissive ordinals.  *bytes = the table's size; copied only if it fits cap_bytes.                     */
 PT_API int pt_unit_table(pt_scene*, int table, void* dst, size_t cap_bytes, size_t* bytes);
 
 #ifdef __cplusplus

@@ -151,7 +151,7 @@ int scene_replicate(pt_scene* src, int device, pt_scene** out){
     r->materials = src->materials; r->media = src->media; r->lights = src->lights;     // small POD lists the host-side checks look at
     r->scene_medium = src->scene_medium; r->bounds = src->bounds;
     r->dev = src->dev; r->shade = src->shade;                                          // scalars; pointers are re-bound below
-    r->total_tris = src->total_tris; r->total_nodes = src->total_nodes; r->n_inst_records = src->n_inst_records;
+    r->total_tris = src->total_tris; r->total_nodes = src->total_nodes; r->n_inst_records = src->n_inst_records; r->n_shade_vertices = src->n_shade_vertices; r->n_shade_indices = src->n_shade_indices; r->n_shade_tris = src->n_shade_tris;
     r->has_wrappers = src->has_wrappers; r->has_alpha_tex = src->has_alpha_tex; r->has_boundary = src->has_boundary;
     r->builder = src->builder; r->build_stats = src->build_stats;
     if(!cuda_ok(cudaSetDevice(device), "cudaSetDevice")){ delete r; return PT_ERR_CUDA; }

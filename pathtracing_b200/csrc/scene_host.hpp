@@ -107,6 +107,7 @@ struct pt_scene {
     ptb::DeviceBuffers buf;
     int film_w = 0, film_h = 0;
     uint64_t total_tris = 0, total_nodes = 0, n_inst_records = 0;
+    uint64_t n_shade_vertices = 0, n_shade_indices = 0, n_shade_tris = 0;     // sizes of the shading geometry tables
     void* stream = nullptr;       // internal stream for the host-buffer entry points
     void* stream2 = nullptr;      // H2D stage of the host-buffer pipeline
     void* stream3 = nullptr;      // D2H stage
@@ -222,6 +223,8 @@ using BlasPacker = int (*)(pt_scene* s, const HostBlas& hb, DevBlasPiece& out, B
 void encode_bvh4q(const std::vector<Bvh4Node>& n4, std::vector<Bvh4QNode>& out);
 int pack_traversal(pt_scene* s, int width, PackedTraversal& out, BvhBuilder builder = nullptr, void* user = nullptr, BlasPacker packer = nullptr);
 uint32_t mesh_tri_flags(const pt_scene* s, int mesh);      // TRI_ALPHA_* flags of the mesh's material (scene_build.cpp)
+// pageable host memory to the device through pinned staging buffers (shade_host.cu); synchronous
+bool h2d_staged(int device, void* dst, const void* src, size_t bytes, const char* what);
 // scene_pack_gpu.cu
 int pack_blas_on_device(pt_scene* s, const HostBlas& hb, DevBlasPiece& out, Box& bounds, void* user);
 int place_blas_piece(const DevBlasPiece& p, void* d_n4, void* d_tris);

@@ -196,8 +196,8 @@ int pack_blas_on_device(pt_scene* s, const HostBlas& hb, DevBlasPiece& out, Box&
         DevMem& dp = mesh_mem[2 * k];
         DevMem& di = mesh_mem[2 * k + 1];
         if(!dp.alloc(m.pos.size() * sizeof(float), "cudaMalloc positions") || !di.alloc(m.idx.size() * sizeof(uint32_t), "cudaMalloc indices") ||
-           !cuda_ok(cudaMemcpyAsync(dp.p, m.pos.data(), m.pos.size() * sizeof(float), cudaMemcpyHostToDevice, st), "H2D positions") ||
-           !cuda_ok(cudaMemcpyAsync(di.p, m.idx.data(), m.idx.size() * sizeof(uint32_t), cudaMemcpyHostToDevice, st), "H2D indices"))return PT_ERR_CUDA;
+           !h2d_staged(s->device, dp.p, m.pos.data(), m.pos.size() * sizeof(float), "H2D positions") ||
+           !h2d_staged(s->device, di.p, m.idx.data(), m.idx.size() * sizeof(uint32_t), "H2D indices"))return PT_ERR_CUDA;
         MeshRef r;
         r.pos = dp.as<float>(); r.idx = di.as<uint32_t>();
         r.first = hb.tri_mesh_base[k]; r.count = m.d.n_triangles; r.mesh = (uint32_t)mi; r.flags = mesh_tri_flags(s, mi);

@@ -45,7 +45,8 @@ float mat4_det(const float m[16]){
 } // namespace
 
 static void build_geometry(pt_scene* s, ShadeTables& T){
-    {   // one allocation per table (a 10 M-triangle scene spent most of its 0.9 s here growing the vectors)
+    const bool dev = T.geometry_on_device;
+    if(!dev){   // one allocation per table (a 10 M-triangle scene spent most of its 0.9 s here growing the vectors)
         size_t nv = 0, ni = 0, nt = 0;
         for(const HostMesh& m : s->meshes){ nv += m.pos.size() / 3; ni += m.idx.size(); }
         for(const HostBlas& hb : s->blas)nt += hb.n_tris;
@@ -54,30 +55,36 @@ static void build_geometry(pt_scene* s, ShadeTables& T){
     }
     for(const HostMesh& m : s->meshes){
         DevMesh d {};
-        d.vtx_base = (uint32_t)(T.pos.size() / 3);
-        d.idx_base = (uint32_t)T.idx.size();
+        d.vtx_base = (uint32_t)T.n_vertices;
+        d.idx_base = (uint32_t)T.n_indices;
         d.prim_base = 0;
         d.has_tangents = m.tan.empty() ? 0u : 1u;
         d.material = m.d.material; d.emissive_tex = m.d.emissive_tex; d.medium = m.d.medium;
-        T.pos.insert(T.pos.end(), m.pos.begin(), m.pos.end());
-        T.nrm.insert(T.nrm.end(), m.nrm.begin(), m.nrm.end());
-        T.uv.insert(T.uv.end(), m.uv.begin(), m.uv.end());
-        if(m.tan.empty())T.tan.insert(T.tan.end(), m.pos.size(), 0.0f);
-        else T.tan.insert(T.tan.end(), m.tan.begin(), m.tan.end());
-        T.idx.insert(T.idx.end(), m.idx.begin(), m.idx.end());
+        T.n_vertices += m.pos.size() / 3; T.n_indices += m.idx.size();
+        if(!dev){
+            T.pos.insert(T.pos.end(), m.pos.begin(), m.pos.end());
+            T.nrm.insert(T.nrm.end(), m.nrm.begin(), m.nrm.end());
+            T.uv.insert(T.uv.end(), m.uv.begin(), m.uv.end());
+            if(m.tan.empty())T.tan.insert(T.tan.end(), m.pos.size(), 0.0f);
+            else T.tan.insert(T.tan.end(), m.tan.begin(), m.tan.end());
+            T.idx.insert(T.idx.end(), m.idx.begin(), m.idx.end());
+        }
         T.meshes.push_back(d);
     }
     // per-BLAS triangle tables in original (BLAS-wide) order.  A mesh used by two BLASes keeps
     // the prim_base of the last one; shading resolves BLAS-wide ids through the ShadeTri table, which needs no prim_base.
     for(const HostBlas& hb : s->blas){
         DevBlasInfo bi {};
-        bi.tri_base = (uint32_t)T.stri.size();
+        bi.tri_base = (uint32_t)T.n_blas_tris;
         bi.n_tris = hb.n_tris;
         int32_t emis = 0;
         for(size_t k = 0; k < hb.meshes.size(); k++){
             const int mi = hb.meshes[k];
             const HostMesh& m = s->meshes[mi];
             T.meshes[mi].prim_base = hb.tri_mesh_base[k];
+            T.tri_runs.push_back({ mi, (uint32_t)T.n_blas_tris, m.d.n_triangles, m.d.emissive_tex >= 0 ? emis : -1 });
+            T.n_blas_tris += m.d.n_triangles;
+            if(dev){ if(m.d.emissive_tex >= 0)emis += (int32_t)m.d.n_triangles; continue; }
             {
                 const uint32_t vb = T.meshes[mi].vtx_base;
                 const size_t at = T.stri.size();
@@ -160,10 +167,11 @@ static void build_appearance(pt_scene* s, ShadeTables& T){
 // AreaLight::PreProcess (Light.cpp:277-287): 2 * Area * luminance(mean emissive over 16x16
 // strata of TriangleShape::Sample, which does not fold u+v>1, Shape.cpp:277-297).  The strata are
 // sampled at their centres here (the reference jitters them with an unseeded RNG).
-static float area_light_power(const ShadeTables& T, const DevMesh& m, uint32_t tri, float& area_out){
-    const uint32_t* ix = &T.idx[m.idx_base + 3 * (size_t)tri];
-    const V3 p0 = ld3(&T.pos[3 * (size_t)(m.vtx_base + ix[0])]), p1 = ld3(&T.pos[3 * (size_t)(m.vtx_base + ix[1])]), p2 = ld3(&T.pos[3 * (size_t)(m.vtx_base + ix[2])]);
-    const float* t0 = &T.uv[2 * (size_t)(m.vtx_base + ix[0])]; const float* t1 = &T.uv[2 * (size_t)(m.vtx_base + ix[1])]; const float* t2 = &T.uv[2 * (size_t)(m.vtx_base + ix[2])];
+static float area_light_power(const ShadeTables& T, const DevMesh& m, const HostMesh& hm, uint32_t tri, float& area_out){
+    // vertex data straight from the mesh (mesh-local indices): the staged copies may not exist (ShadeTables::geometry_on_device)
+    const uint32_t* ix = &hm.idx[3 * (size_t)tri];
+    const V3 p0 = ld3(&hm.pos[3 * (size_t)ix[0]]), p1 = ld3(&hm.pos[3 * (size_t)ix[1]]), p2 = ld3(&hm.pos[3 * (size_t)ix[2]]);
+    const float* t0 = &hm.uv[2 * (size_t)ix[0]]; const float* t1 = &hm.uv[2 * (size_t)ix[1]]; const float* t2 = &hm.uv[2 * (size_t)ix[2]];
     const float area = length(cross(p0 - p2, p1 - p2)) * 0.5f;           // TriangleShape::Area, Shape.cpp:298-301
     area_out = area;
     double acc[3] = { 0, 0, 0 };
@@ -256,7 +264,7 @@ static int build_lights(pt_scene* s, ShadeTables& T, const std::vector<uint32_t>
             for(uint32_t t = 0; t < s->meshes[mi].d.n_triangles; t++){
                 DevLight L {};
                 L.kind = DL_AREA; L.tex = m.emissive_tex; L.inst = id; L.mesh = (uint32_t)mi; L.tri = t;
-                const float p = area_light_power(T, m, t, L.area);
+                const float p = area_light_power(T, m, s->meshes[mi], t, L.area);
                 L.valid = p > FLT_EPSILON ? 1u : 0u;              // Model.hpp:53-56
                 T.lights.push_back(L);
                 power_inner.push_back(p);

@@ -164,6 +164,14 @@ int pt_unit_table(pt_scene* s, int table, void* dst, size_t cap_bytes, size_t* b
         case 2: src = b.n4q; n = s->dev.fast ? s->total_nodes * sizeof(Bvh4QNode) : 0; break;
         case 3: src = b.tris64; n = s->dev.fast ? s->total_tris * sizeof(Tri64) : 0; break;
         case 4: src = b.inst; n = s->n_inst_records * sizeof(Instance); break;
+        // shading geometry: positions, normals, texcoords, tangents, indices, shading triangles, emissive ordinals
+        case 5: src = b.vtx_pos; n = s->n_shade_vertices * 12; break;
+        case 6: src = b.vtx_nrm; n = s->n_shade_vertices * 12; break;
+        case 7: src = b.vtx_uv; n = s->n_shade_vertices * 8; break;
+        case 8: src = b.vtx_tan; n = s->n_shade_vertices * 12; break;
+        case 9: src = b.indices; n = s->n_shade_indices * 4; break;
+        case 10: src = b.tri_mesh; n = s->n_shade_tris * sizeof(ShadeTri); break;
+        case 11: src = b.tri_light; n = s->n_shade_tris * 4; break;
         default: set_error("pt_unit_table: unknown table"); return PT_ERR_INVALID;
     }
     *bytes = n;

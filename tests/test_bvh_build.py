@@ -140,7 +140,7 @@ def test_blas_packed_on_the_device_gives_the_host_arrays(layout):
         b = GpuScene(desc, 4, builder=capi.BUILDER_GPU, layout=layout)
         st = b.build_stats()
         assert st["gpu_items"] > 0 or k == 4          # the last scene is all small BLASes: everything stays on the host
-        for t in ((0, 1, 4) if layout == 0 else (0, 1, 2, 3, 4)):
+        for t in ((0, 1, 4) if layout == 0 else (0, 1, 2, 3, 4)) + (5, 6, 7, 8, 9, 10, 11):
             ta, tb = a.table(t), b.table(t)
             assert len(ta) == len(tb) and len(ta) > 0, (t, len(ta), len(tb))
             diff = int((ta != tb).sum())
