@@ -221,7 +221,7 @@ PT_API int pt_scene_commit(pt_scene*, int bvh_width, int light_sampler);
  * flatten's DFS numbering, the triangle records, the quantised clusters): the same bytes as the host path
  * (tests/test_bvh_build.py::test_blas_packed_on_the_device_gives_the_host_arrays), no tree download, no
  * per-triangle host array.  Call before pt_scene_commit.  Default: PT_BUILDER_GPU (a 10 M-triangle commit
- * 3.9 s on the host -> 0.44-0.62 s, profiles/r02_build_check_v3.log, r02_bench_v6.json); PTB_BUILDER=host in
+ * 4.05 s on the host -> 0.34 s, profiles/r02_build_check_v4.log); PTB_BUILDER=host in
  * the environment selects the host builder at pt_scene_create, PTB_GPU_PACK=0 keeps the GPU builder but
  * flattens on the host.                                                                                       */
 typedef enum pt_builder { PT_BUILDER_HOST = 0, PT_BUILDER_GPU = 1 } pt_builder;

@@ -883,12 +883,14 @@ int render_passes(pt_scene* s, const pt_camera_desc* cam, const pt_render_params
     // long tail of deep paths is paid once per call and not once per batch.
     double host_wait_s = 0.0; unsigned iterations = 0;
     const bool tr_walk = rp->integrator == PT_INTEGRATOR_VOLPATH && s->has_boundary;
-    // shade-order sort (k_sort_*).  Measured on one B200 (scratch/stage_prof.py, shade stage incl. the sort): C4
-    // (VolPath: medium events, textured materials) 218.8 -> 178.7 ms, C3 (PathIntegrator, four material kinds)
-    // 59.2 -> 58.1 ms, C1 (one material) 1.89 -> 2.82 ms.  So: on for VolPathIntegrator, off otherwise;
-    // PTB_SORT=0 / 1 forces it, PTB_SORT_MIN sets the smallest queue worth sorting.
+    // shade-order sort (k_sort_*).  Measured on one B200 (PTB_PROFILE, shade stage incl. the sort, round 2 build): C4 (VolPath: medium
+    // events, textured materials) 325 -> 170 ms, C3 (PathIntegrator, four material kinds) 67.9 -> 38.5 ms (frame 291 -> 260 ms); C1 (one
+    // material kind) 1.89 -> 2.82 ms (round 1).  So: on for VolPathIntegrator and for every scene whose materials are of more than one
+    // kind; PTB_SORT=0 / 1 forces it, PTB_SORT_MIN sets the smallest queue worth sorting.
     static const int sort_env = []{ const char* e = getenv("PTB_SORT"); return e ? (atoi(e) != 0 ? 1 : 0) : -1; }();
-    const bool sort_shade = sort_env >= 0 ? sort_env == 1 : rp->integrator == PT_INTEGRATOR_VOLPATH;
+    unsigned kinds = 0;
+    for(const pt_material_desc& md : s->materials)kinds |= 1u << (md.kind & 31);
+    const bool sort_shade = sort_env >= 0 ? sort_env == 1 : (rp->integrator == PT_INTEGRATOR_VOLPATH || (kinds & (kinds - 1)) != 0);
     static const uint32_t sort_min_env = []{ const char* e = getenv("PTB_SORT_MIN"); return e ? (uint32_t)atoll(e) : 65536u; }();
     const uint32_t sort_min = sort_shade ? sort_min_env : 0xFFFFFFFFu;      // the kernels compare the device-side queue size with it
     // how many bounces the host may enqueue beyond the last queue size it has seen (PTB_LOOKAHEAD)
