@@ -276,22 +276,22 @@ def bench_render(a, key, torch, dist, world, rank, local, peak, peak_src):
     total = W * H * spp
     heavy = total > (1 << 25)
     very_heavy = total > (1 << 30)
-    steps = 1 if very_heavy else 2 if heavy else max(2, min(a.steps, 5))
+    steps = 1 if very_heavy else 3 if heavy else max(2, min(a.steps, 5))
     # warm-up: whole frames, except for the very heavy config (C5: 2 G samples), which warms up on a 64-spp frame of the same
     # scene -- enough samples per rank to size the wavefront arena as the full frame does (64 Mi slots), so that the timed
     # frame does not pay a 16 GB cudaMalloc
     warm = params if not very_heavy else render_params(W, H, min(spp, 64 * world), depth, integrator=integ, seed=2)
     # the barrier comes BEFORE the warm-up frames: every frame ends in a collective of its own (the film reduce), which keeps the ranks
     # together, and the first frame behind a torch NCCL barrier took 6.8 ms instead of 1.5 (C1 on 8 GPUs, r02_bench_n8_v3.json)
-    if world > 1:
-        dist.barrier()
-    for _ in range(1 if heavy else 3):
-        multi.render_sharded(scene, cam, warm, dist if world > 1 else None)
-    torch.cuda.synchronize()
-    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     import gc
     gc.collect()
     gc.disable()            # a generation-2 collection inside a 5 ms frame showed up as one 30-100 ms frame in five (frame_ms_rank0)
+    if world > 1:
+        dist.barrier()
+    for _ in range(2 if heavy else 3):
+        multi.render_sharded(scene, cam, warm, dist if world > 1 else None)
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     t_wall = time.perf_counter()
     e0.record()
     rays = 0
