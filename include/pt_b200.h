@@ -216,8 +216,8 @@ PT_API int pt_scene_commit(pt_scene*, int bvh_width, int light_sampler);
  * TLAS runs.  PT_BUILDER_GPU takes the same decisions with the same float operations on the device
  * (csrc/bvh_build_gpu.cu) and yields the same tree and leaf order as PT_BUILDER_HOST, so the packed
  * BVH2 / BVH4 / BVH8 arrays are byte-identical; hierarchies under 4096 items stay on the host (launch
- * overhead).  With PT_BUILDER_GPU a BVH4 BLAS of 4096 triangles or more is packed on the device altogether
- * (csrc/scene_pack_gpu.cu: triangle boxes from the mesh arrays, the binary build, the BVH4 collapse in the host
+ * overhead).  With PT_BUILDER_GPU a BLAS of 4096 triangles or more (any width) is packed on the device altogether
+ * (csrc/scene_pack_gpu.cu: triangle boxes from the mesh arrays, the binary build, the BVH2 / BVH4 / BVH8 collapse in the host
  * flatten's DFS numbering, the triangle records, the quantised clusters): the same bytes as the host path
  * (tests/test_bvh_build.py::test_blas_packed_on_the_device_gives_the_host_arrays), no tree download, no
  * per-triangle host array.  Call before pt_scene_commit.  Default: PT_BUILDER_GPU (a 10 M-triangle commit
@@ -467,7 +467,7 @@ PT_API int pt_unit_light_sample(pt_scene*, int light, size_t n, const float* in5
                                 float* out, int stride /* >= 22 */, float time);
 PT_API int pt_unit_hg(int device, float g, size_t n, const float* in5, float* out5);
 /* A committed scene's traversal tables read back (tests compare the device-packed arrays with the host-packed ones byte for
- * byte): table 0 BVH4 clusters (128 B), 1 triangles (48 B), 2 quantised clusters (64 B, PT_LAYOUT_FAST), 3 padded triangles
+ * byte): table 0 the nodes of the commit's width (BVH2 64 B, BVH4 128 B, BVH8 256 B), 1 triangles (48 B), 2 quantised clusters (64 B, PT_LAYOUT_FAST), 3 padded triangles
  * (64 B), 4 instance records (96 B); the shading geometry: 5 positions, 6 normals, 7 texcoords, 8 tangents, 9 indices, 10 shading
  * triangles (16 B), 11 emissive ordinals.  *bytes = the table's size; copied only if it fits cap_bytes.                     */
 PT_API int pt_unit_table(pt_scene*, int table, void* dst, size_t cap_bytes, size_t* bytes);

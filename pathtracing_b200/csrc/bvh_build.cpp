@@ -2,6 +2,7 @@
 // costs decide the topology and must not depend on FMA contraction.
 #include "bvh_build.hpp"
 #include "bvh_flatten4.hpp"
+#include "bvh_flatten28.hpp"
 #include "bvh4q_encode.hpp"
 #include "scene_host.hpp"
 #include <algorithm>
@@ -233,16 +234,12 @@ uint32_t flatten2(FlatBvh& f, const BinaryBvh& b, uint32_t ni){
     { uint32_t job; if(deferred(f, b, ni, f.n2.size(), &job))return job; }
     const uint32_t me = (uint32_t)f.n2.size();
     f.n2.emplace_back();
-    const BuildNode& l = b.nodes[n.left];
-    const BuildNode& r = b.nodes[n.right];
-    const uint32_t r0 = flatten2(f, b, n.left);
-    const uint32_t r1 = flatten2(f, b, n.right);
-    Bvh2Node& o = f.n2[me];
-    for(int k = 0; k < 3; k++){
-        o.lo0[k] = l.box.lo[k]; o.hi0[k] = l.box.hi[k];
-        o.lo1[k] = r.box.lo[k]; o.hi1[k] = r.box.hi[k];
-    }
-    o.ref0 = r0; o.ref1 = r1; o.axis = n.axis; o.pad = 0;
+    Bvh2Node o;
+    uint32_t lane_node[2];
+    fill_cluster2(b.nodes.data(), ni, o, lane_node);        // bvh_flatten28.hpp, shared with the device flatten
+    o.ref0 = flatten2(f, b, lane_node[0]);
+    o.ref1 = flatten2(f, b, lane_node[1]);
+    f.n2[me] = o;
     return me;
 }
 
@@ -265,60 +262,18 @@ uint32_t flatten4(FlatBvh& f, const BinaryBvh& b, uint32_t ni){
     return me;
 }
 
-// BVH8 collapse (BVH8::buildBVH8, BVH.hpp:1312-1354): starting from the node itself, the open inner node
-// with the largest AABB::Area (ties: the later slot, `>=`) is replaced by its left child and its right
-// child is appended, until eight lanes exist or every lane is a leaf.
-void perm8(const BinaryBvh& b, const uint32_t* lanes, int end, uint32_t curr, unsigned octant, int* out, int& n){
-    for(int i = 0; i < end; i++)if(lanes[i] == curr){ out[n++] = i; return; }
-    const BuildNode& x = b.nodes[curr];
-    const bool neg = (octant >> x.axis) & 1u;
-    perm8(b, lanes, end, neg ? x.right : x.left, octant, out, n);
-    perm8(b, lanes, end, neg ? x.left : x.right, octant, out, n);
-}
-
+// BVH8 collapse: the per-cluster logic (lane choice by area, visit orders) lives in bvh_flatten28.hpp, shared with the device flatten.
 uint32_t flatten8(FlatBvh& f, const BinaryBvh& b, uint32_t ni){
     const BuildNode& n = b.nodes[ni];
     if(n.count != 0){ mark_leaf(f, n); return leaf_ref(n.right); }
     { uint32_t job; if(deferred(f, b, ni, f.n8.size(), &job))return job; }
     const uint32_t me = (uint32_t)f.n8.size();
     f.n8.emplace_back();
-    uint32_t lanes[8] = { ni, 0, 0, 0, 0, 0, 0, 0 };
-    int end = 1;
-    while(end < 8){
-        int k = -1;
-        float best = -1.0f;
-        for(int i = 0; i < end; i++){
-            const BuildNode& c = b.nodes[lanes[i]];
-            if(c.count == 0 && box_half_area(c.box) >= best){ k = i; best = box_half_area(c.box); }
-        }
-        if(k < 0)break;
-        const BuildNode& c = b.nodes[lanes[k]];
-        lanes[end++] = c.right;
-        lanes[k] = c.left;
-    }
-    uint32_t refs[8];
-    for(int i = 0; i < 8; i++)refs[i] = REF_EMPTY;
-    for(int i = 0; i < end; i++)refs[i] = flatten8(f, b, lanes[i]);     // children in lane order, as the reference recursion
-    Bvh8Node& o = f.n8[me];
-    memset(&o, 0, sizeof o);                                            // absent lanes: zero boxes (BVH.hpp:1242-1244)
-    for(int i = 0; i < end; i++){
-        const Box& bx = b.nodes[lanes[i]].box;
-        const int h = i >> 2, l = i & 3;
-        o.box[h][0][l] = bx.lo[0]; o.box[h][1][l] = bx.hi[0];
-        o.box[h][2][l] = bx.lo[1]; o.box[h][3][l] = bx.hi[1];
-        o.box[h][4][l] = bx.lo[2]; o.box[h][5][l] = bx.hi[2];
-    }
-    for(int i = 0; i < 8; i++)o.ref[i] = refs[i];
-    for(unsigned oct = 0; oct < 8; oct++){
-        int seq[8], cnt = 0;
-        perm8(b, lanes, end, ni, oct, seq, cnt);
-        bool seen[8] = { false, false, false, false, false, false, false, false };
-        for(int k = 0; k < cnt; k++)seen[seq[k]] = true;
-        for(int k = 0; k < 8; k++)if(!seen[k])seq[cnt++] = k;
-        uint32_t code = 0;
-        for(int k = 0; k < 8; k++)code |= (uint32_t)seq[k] << (3 * k);
-        o.order[oct] = code;
-    }
+    Bvh8Node o;
+    uint32_t lanes[8];
+    const int end = fill_cluster8(b.nodes.data(), ni, o, lanes);
+    for(int i = 0; i < end; i++)o.ref[i] = flatten8(f, b, lanes[i]);     // children in lane order, as the reference recursion
+    f.n8[me] = o;
     return me;
 }
 

@@ -239,7 +239,7 @@ int pack_traversal(pt_scene* s, int width, PackedTraversal& P, BvhBuilder builde
         for(int mi : hb.meshes){ hb.tri_mesh_base.push_back(hb.n_tris); hb.n_tris += s->meshes[mi].d.n_triangles; }
         if(hb.n_tris == 0){ set_error("empty BLAS"); return PT_ERR_INVALID; }
         if((uint64_t)g_tris + hb.n_tris >= 0x7FFFFFFFull){ set_error("too many triangles"); return PT_ERR_INVALID; }
-        if(packer && width == 4){
+        if(packer){
             // the whole BLAS on the device: boxes, binary build, collapse, triangle records (scene_pack_gpu.cu)
             for(int mi : hb.meshes){
                 const HostMesh& m = s->meshes[mi];
@@ -248,7 +248,7 @@ int pack_traversal(pt_scene* s, int width, PackedTraversal& P, BvhBuilder builde
             }
             DevBlasPiece piece;
             Box bounds = box_empty();
-            const int prc = packer(s, hb, piece, bounds, user);
+            const int prc = packer(s, hb, width, piece, bounds, user);
             if(prc < 0)return prc;
             if(prc == PT_OK){
                 piece.node_base = (uint32_t)g_nodes; piece.tri_base = (uint32_t)g_tris;

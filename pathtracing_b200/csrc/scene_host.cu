@@ -109,13 +109,15 @@ int scene_commit(pt_scene* s, int width, int light_sampler){
     DeviceBuffers& b = s->buf;
     s->uploads.clear();
     static const std::vector<HostSeg> no_segs;
-    if(!upload(s, &b.n2, n2, "upload bvh2 nodes") || !upload_segs(s, &b.n4, n4, width == 4 ? P.node_segs : no_segs, width == 4 ? P.total_nodes : 0, "upload bvh4 clusters") ||
-       !upload(s, &b.n8, P.n8, "upload bvh8 clusters") ||
+    if(!upload_segs(s, &b.n2, n2, width == 2 ? P.node_segs : no_segs, width == 2 ? P.total_nodes : 0, "upload bvh2 nodes") ||
+       !upload_segs(s, &b.n4, n4, width == 4 ? P.node_segs : no_segs, width == 4 ? P.total_nodes : 0, "upload bvh4 clusters") ||
+       !upload_segs(s, &b.n8, P.n8, width == 8 ? P.node_segs : no_segs, width == 8 ? P.total_nodes : 0, "upload bvh8 clusters") ||
        !upload_segs(s, &b.tris, tris, P.tri_segs, P.total_tris, "upload triangles") || !upload(s, &b.inst, insts, "upload instances")){
         scene_free_device(s);
         return PT_ERR_CUDA;
     }
-    for(const DevBlasPiece& pc : P.dev_pieces)if(place_blas_piece(pc, b.n4, b.tris) != PT_OK){ scene_free_device(s); return PT_ERR_CUDA; }
+    for(const DevBlasPiece& pc : P.dev_pieces)
+        if(place_blas_piece(pc, width, width == 2 ? b.n2 : width == 4 ? b.n4 : b.n8, b.tris) != PT_OK){ scene_free_device(s); return PT_ERR_CUDA; }
     s->dev.fast = 0;
     if(s->layout == PT_LAYOUT_FAST){
         if(width != 4){ set_error("PT_LAYOUT_FAST needs bvh_width 4"); scene_free_device(s); return PT_ERR_INVALID; }

@@ -142,7 +142,7 @@ namespace ptb {
 // A BLAS packed on the device (scene_pack_gpu.cu): its clusters and triangle records sit in device buffers of their own, refs local
 // to the BLAS (inner refs index d_nodes, leaf refs index d_tris); pack_traversal gives it its place in the scene-wide arrays.
 struct DevBlasPiece {
-    void* d_nodes = nullptr;      // Bvh4Node[n_nodes], DFS preorder (the host flatten's numbering)
+    void* d_nodes = nullptr;      // Bvh2Node / Bvh4Node / Bvh8Node[n_nodes] (the commit's width), DFS preorder (the host flatten's numbering)
     void* d_tris = nullptr;       // Tri[n_tris], leaf order
     uint32_t n_nodes = 0, n_tris = 0;
     uint32_t node_base = 0, tri_base = 0;     // where it goes in the scene-wide arrays
@@ -217,8 +217,8 @@ int scene_animate(pt_scene* s, int prim_id, const float* dir, const float* tb);
 int scene_add_light(pt_scene* s, const pt_light_desc* d);
 // builder: binary build used for every BLAS and the TLAS (null = build_binary_bvh on the host); returns PT_OK or an error
 using BvhBuilder = int (*)(const Box* boxes, uint32_t n, BinaryBvh& out, void* user);
-// packs one BLAS on the device (width 4): PT_OK and `out` filled (bounds = its root box), or 1 = not taken (the host path packs it), or an error
-using BlasPacker = int (*)(pt_scene* s, const HostBlas& hb, DevBlasPiece& out, Box& bounds, void* user);
+// packs one BLAS on the device: PT_OK and `out` filled (bounds = its root box), or 1 = not taken (the host path packs it), or an error
+using BlasPacker = int (*)(pt_scene* s, const HostBlas& hb, int width, DevBlasPiece& out, Box& bounds, void* user);
 // PT_LAYOUT_FAST: quantised copy of the BVH4 clusters (pt_types.h Bvh4QNode); every decoded box contains the exact one
 void encode_bvh4q(const std::vector<Bvh4Node>& n4, std::vector<Bvh4QNode>& out);
 int pack_traversal(pt_scene* s, int width, PackedTraversal& out, BvhBuilder builder = nullptr, void* user = nullptr, BlasPacker packer = nullptr);
@@ -226,8 +226,8 @@ uint32_t mesh_tri_flags(const pt_scene* s, int mesh);      // TRI_ALPHA_* flags 
 // pageable host memory to the device through pinned staging buffers (shade_host.cu); synchronous
 bool h2d_staged(int device, void* dst, const void* src, size_t bytes, const char* what);
 // scene_pack_gpu.cu
-int pack_blas_on_device(pt_scene* s, const HostBlas& hb, DevBlasPiece& out, Box& bounds, void* user);
-int place_blas_piece(const DevBlasPiece& p, void* d_n4, void* d_tris);
+int pack_blas_on_device(pt_scene* s, const HostBlas& hb, int width, DevBlasPiece& out, Box& bounds, void* user);
+int place_blas_piece(const DevBlasPiece& p, int width, void* d_nodes, void* d_tris);
 int encode_fast_range(const void* d_n4, void* d_n4q, uint32_t node_base, uint32_t n_nodes, const void* d_tris, void* d_tris64, uint32_t tri_base, uint32_t n_tris);
 int build_binary_bvh_gpu(const Box* boxes, uint32_t n, uint32_t leaf_size, BinaryBvh& out, GpuBuildTimes* times);   // bvh_build_gpu.cu
 // a binary tree left on the device by the GPU builder: BuildNode[n_nodes] (node 0 = root, unused pool slots zero) and the item order

@@ -1,6 +1,6 @@
 // scene_pack_gpu.cu — one BLAS packed entirely on the device: triangle boxes, the binned-SAH binary build
-// (bvh_build_gpu.cu), the BVH4 collapse (BVH4::buildBVH4, BVH.hpp:788-1017; per-cluster logic shared with the host
-// flatten through bvh_flatten4.hpp) and the triangle records in leaf order.  What the host path of scene_build.cpp
+// (bvh_build_gpu.cu), the collapse into BVH2 child-pair nodes / BVH4 / BVH8 clusters (BVH.hpp:461-473, 788-1017, 1312-1372; per-cluster
+// logic shared with the host flatten through bvh_flatten4.hpp / bvh_flatten28.hpp) and the triangle records in leaf order.  What the host path of scene_build.cpp
 // pack_traversal does for a BLAS, with the same decisions and the same numbering (DFS preorder, children in lane
 // order), so the arrays are the ones the host would have produced; the binary tree is never downloaded and the
 // host never touches a per-triangle array (a 10 M-triangle commit spent 0.33 s in that download, 0.2 s flattening
@@ -19,6 +19,7 @@
 
 #include "scene_host.hpp"
 #include "bvh_flatten4.hpp"
+#include "bvh_flatten28.hpp"
 #include "bvh4q_encode.hpp"
 
 namespace ptb {
@@ -64,61 +65,96 @@ __global__ void k_tri_boxes(const MeshRef m, Box* __restrict__ boxes){
 // A cluster while its final index is not known yet: refs of inner lanes hold the breadth-first index of the child
 struct Work { uint32_t root; uint32_t subtree; uint32_t final_index; uint32_t pad; };
 
+// The three widths behind one set of sweeps: the node type, its refs, and the cluster of one binary node (the shared
+// host / device functions of bvh_flatten4.hpp and bvh_flatten28.hpp).  make() leaves every ref REF_EMPTY and says which
+// binary node sits in which lane.
+template <int W> struct Wide;
+template <> struct Wide<2> {
+    using Node = Bvh2Node;
+    static constexpr int kLanes = 2;
+    __device__ static uint32_t& ref(Node& o, int k){ return k ? o.ref1 : o.ref0; }
+    __device__ static void make(const BuildNode* nodes, uint32_t root, Node& o, uint32_t lane_node[8], bool lane_used[8]){
+        fill_cluster2(nodes, root, o, lane_node);
+        lane_used[0] = lane_used[1] = true;
+    }
+};
+template <> struct Wide<4> {
+    using Node = Bvh4Node;
+    static constexpr int kLanes = 4;
+    __device__ static uint32_t& ref(Node& o, int k){ return o.ref[k]; }
+    __device__ static void make(const BuildNode* nodes, uint32_t root, Node& o, uint32_t lane_node[8], bool lane_used[8]){
+        ClusterPlan p;
+        plan_cluster4(nodes, root, p);
+        fill_cluster4(nodes, p, o, lane_node, lane_used);
+    }
+};
+template <> struct Wide<8> {
+    using Node = Bvh8Node;
+    static constexpr int kLanes = 8;
+    __device__ static uint32_t& ref(Node& o, int k){ return o.ref[k]; }
+    __device__ static void make(const BuildNode* nodes, uint32_t root, Node& o, uint32_t lane_node[8], bool lane_used[8]){
+        const int end = fill_cluster8(nodes, root, o, lane_node);
+        for(int k = 0; k < 8; k++)lane_used[k] = k < end;
+    }
+};
+
 // expand one level: bfs[lo .. hi) -> their clusters, children appended at bfs[hi + ...)
-__global__ void k_expand(const BuildNode* __restrict__ nodes, Work* __restrict__ work, Bvh4Node* __restrict__ tmp, uint32_t lo, uint32_t hi,
+template <int W>
+__global__ void k_expand(const BuildNode* __restrict__ nodes, Work* __restrict__ work, typename Wide<W>::Node* __restrict__ tmp, uint32_t lo, uint32_t hi,
                          uint32_t* __restrict__ next_count, uint32_t* __restrict__ leaf_last, uint32_t cap){
     const uint32_t i = lo + blockIdx.x * blockDim.x + threadIdx.x;
     if(i >= hi)return;
-    ClusterPlan p;
-    plan_cluster4(nodes, work[i].root, p);
-    Bvh4Node o;
-    uint32_t lane_node[4];
-    bool lane_used[4];
-    fill_cluster4(nodes, p, o, lane_node, lane_used);
+    typename Wide<W>::Node o;
+    uint32_t lane_node[8];
+    bool lane_used[8];
+    Wide<W>::make(nodes, work[i].root, o, lane_node, lane_used);
     uint32_t inner = 0;
-    for(int k = 0; k < 4; k++)if(lane_used[k] && nodes[lane_node[k]].count == 0)inner++;
+    for(int k = 0; k < Wide<W>::kLanes; k++)if(lane_used[k] && nodes[lane_node[k]].count == 0)inner++;
     uint32_t at = inner ? hi + atomicAdd(next_count, inner) : 0u;
-    for(int k = 0; k < 4; k++){
+    for(int k = 0; k < Wide<W>::kLanes; k++){
         if(!lane_used[k])continue;
         const BuildNode& c = nodes[lane_node[k]];
         if(c.count != 0){
-            o.ref[k] = REF_LEAF | c.right;                  // first item of the leaf, BLAS-local
+            Wide<W>::ref(o, k) = REF_LEAF | c.right;        // first item of the leaf, BLAS-local
             leaf_last[c.right + c.count - 1] = 1u;
         } else{
             if(at < cap){ work[at].root = lane_node[k]; work[at].subtree = 0; work[at].final_index = 0; work[at].pad = 0; }
-            o.ref[k] = at++;
+            Wide<W>::ref(o, k) = at++;
         }
     }
     tmp[i] = o;
 }
 
 // clusters in the subtree of each cluster of one level (its children's counts are final: deeper levels ran first)
-__global__ void k_count(Work* __restrict__ work, const Bvh4Node* __restrict__ tmp, uint32_t lo, uint32_t hi){
+template <int W>
+__global__ void k_count(Work* __restrict__ work, typename Wide<W>::Node* __restrict__ tmp, uint32_t lo, uint32_t hi){
     const uint32_t i = lo + blockIdx.x * blockDim.x + threadIdx.x;
     if(i >= hi)return;
     uint32_t c = 1;
-    for(int k = 0; k < 4; k++){ const uint32_t r = tmp[i].ref[k]; if(!(r & REF_LEAF))c += work[r].subtree; }
+    for(int k = 0; k < Wide<W>::kLanes; k++){ const uint32_t r = Wide<W>::ref(tmp[i], k); if(!(r & REF_LEAF))c += work[r].subtree; }
     work[i].subtree = c;
 }
 
 // preorder index of the children of each cluster of one level
-__global__ void k_assign(Work* __restrict__ work, const Bvh4Node* __restrict__ tmp, uint32_t lo, uint32_t hi){
+template <int W>
+__global__ void k_assign(Work* __restrict__ work, typename Wide<W>::Node* __restrict__ tmp, uint32_t lo, uint32_t hi){
     const uint32_t i = lo + blockIdx.x * blockDim.x + threadIdx.x;
     if(i >= hi)return;
     uint32_t run = work[i].final_index + 1;
-    for(int k = 0; k < 4; k++){
-        const uint32_t r = tmp[i].ref[k];
+    for(int k = 0; k < Wide<W>::kLanes; k++){
+        const uint32_t r = Wide<W>::ref(tmp[i], k);
         if(r & REF_LEAF)continue;                           // leaves and REF_EMPTY
         work[r].final_index = run;
         run += work[r].subtree;
     }
 }
 
-__global__ void k_emit(const Work* __restrict__ work, const Bvh4Node* __restrict__ tmp, Bvh4Node* __restrict__ out, uint32_t n){
+template <int W>
+__global__ void k_emit(const Work* __restrict__ work, const typename Wide<W>::Node* __restrict__ tmp, typename Wide<W>::Node* __restrict__ out, uint32_t n){
     const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     if(i >= n)return;
-    Bvh4Node o = tmp[i];
-    for(int k = 0; k < 4; k++)if(!(o.ref[k] & REF_LEAF))o.ref[k] = work[o.ref[k]].final_index;
+    typename Wide<W>::Node o = tmp[i];
+    for(int k = 0; k < Wide<W>::kLanes; k++){ uint32_t& r = Wide<W>::ref(o, k); if(!(r & REF_LEAF))r = work[r].final_index; }
     out[work[i].final_index] = o;
 }
 
@@ -142,14 +178,15 @@ __global__ void k_gather_tris(const MeshTable T, const uint32_t* __restrict__ or
 }
 
 // ---- assembling the scene-wide arrays (scene_host.cu) ----------------------------------------------------------------
-__global__ void k_place_nodes4(const Bvh4Node* __restrict__ in, Bvh4Node* __restrict__ out, uint32_t n, uint32_t node_base, uint32_t tri_base){
+template <int W>
+__global__ void k_place_nodes(const typename Wide<W>::Node* __restrict__ in, typename Wide<W>::Node* __restrict__ out, uint32_t n, uint32_t node_base, uint32_t tri_base){
     const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     if(i >= n)return;
-    Bvh4Node o = in[i];
-    for(int k = 0; k < 4; k++){
-        const uint32_t r = o.ref[k];
+    typename Wide<W>::Node o = in[i];
+    for(int k = 0; k < Wide<W>::kLanes; k++){
+        uint32_t& r = Wide<W>::ref(o, k);
         if(r == REF_EMPTY)continue;
-        o.ref[k] = (r & REF_LEAF) ? (REF_LEAF | ((r & ~REF_LEAF) + tri_base)) : r + node_base;
+        r = (r & REF_LEAF) ? (REF_LEAF | ((r & ~REF_LEAF) + tri_base)) : r + node_base;
     }
     out[i] = o;
 }
@@ -173,10 +210,54 @@ void dev_free(void* p){ cudaFree(p); }
 
 inline unsigned blocks(size_t n){ return (unsigned)((n + 255) / 256); }
 
+// collapse: breadth-first expand, then sizes, then preorder indices; then the clusters at their final places and the triangle records
+template <int W>
+static int collapse_on_device(const BuildNode* d_nodes, uint32_t n, const MeshTable& T, const uint32_t* d_order, cudaStream_t st,
+                              uint32_t& n_clusters_out, void*& d_out_nodes, DevMem& d_tris){
+    const uint32_t cap = n;                      // clusters <= inner binary nodes < items
+    DevMem d_work, d_tmp, d_last, d_cnt;
+    if(!d_work.alloc(sizeof(Work) * (size_t)cap, "cudaMalloc collapse work") || !d_tmp.alloc(sizeof(typename Wide<W>::Node) * (size_t)cap, "cudaMalloc clusters") ||
+       !d_last.alloc(4 * (size_t)n, "cudaMalloc leaf marks") || !d_cnt.alloc(4, "cudaMalloc counter"))return PT_ERR_CUDA;
+    if(!cuda_ok(cudaMemsetAsync(d_last.p, 0, 4 * (size_t)n, st), "leaf marks clear"))return PT_ERR_CUDA;
+    const Work w0 = { 0u, 0u, 0u, 0u };
+    if(!cuda_ok(cudaMemcpyAsync(d_work.p, &w0, sizeof w0, cudaMemcpyHostToDevice, st), "H2D root cluster"))return PT_ERR_CUDA;
+    std::vector<uint32_t> level_lo;              // level l = [level_lo[l], level_lo[l + 1])
+    level_lo.push_back(0);
+    uint32_t lo = 0, hi = 1;
+    while(hi > lo){
+        level_lo.push_back(hi);
+        if(!cuda_ok(cudaMemsetAsync(d_cnt.p, 0, 4, st), "counter clear"))return PT_ERR_CUDA;
+        k_expand<W><<<blocks(hi - lo), 256, 0, st>>>(d_nodes, d_work.as<Work>(), d_tmp.as<typename Wide<W>::Node>(), lo, hi, d_cnt.as<uint32_t>(), d_last.as<uint32_t>(), cap);
+        uint32_t next = 0;
+        if(!cuda_ok(cudaGetLastError(), "k_expand") || !cuda_ok(cudaMemcpyAsync(&next, d_cnt.p, 4, cudaMemcpyDeviceToHost, st), "D2H level size") ||
+           !cuda_ok(cudaStreamSynchronize(st), "collapse level"))return PT_ERR_CUDA;
+        if((uint64_t)hi + next > cap){ set_error("gpu collapse: more clusters than items"); return PT_ERR_CUDA; }
+        lo = hi; hi += next;
+    }
+    const uint32_t n_clusters = hi;
+    const int levels = (int)level_lo.size() - 1;
+    for(int l = levels - 1; l >= 0; l--){
+        const uint32_t a = level_lo[l], b = level_lo[l + 1];
+        k_count<W><<<blocks(b - a), 256, 0, st>>>(d_work.as<Work>(), d_tmp.as<typename Wide<W>::Node>(), a, b);
+    }
+    for(int l = 0; l < levels; l++){
+        const uint32_t a = level_lo[l], b = level_lo[l + 1];
+        k_assign<W><<<blocks(b - a), 256, 0, st>>>(d_work.as<Work>(), d_tmp.as<typename Wide<W>::Node>(), a, b);
+    }
+    DevMem d_out;
+    if(!d_out.alloc(sizeof(typename Wide<W>::Node) * (size_t)n_clusters, "cudaMalloc BLAS clusters") || !d_tris.alloc(sizeof(Tri) * (size_t)n, "cudaMalloc BLAS triangles"))return PT_ERR_CUDA;
+    k_emit<W><<<blocks(n_clusters), 256, 0, st>>>(d_work.as<Work>(), d_tmp.as<typename Wide<W>::Node>(), d_out.as<typename Wide<W>::Node>(), n_clusters);
+    k_gather_tris<<<blocks(n), 256, 0, st>>>(T, d_order, d_last.as<uint32_t>(), n, d_tris.as<Tri>());
+    if(!cuda_ok(cudaGetLastError(), "collapse kernels") || !cuda_ok(cudaStreamSynchronize(st), "gpu pack"))return PT_ERR_CUDA;
+    n_clusters_out = n_clusters;
+    d_out_nodes = d_out.take();
+    return PT_OK;
+}
+
 } // namespace
 
 // BlasPacker (scene_host.hpp).  user: GpuBuildTimes* of the commit.
-int pack_blas_on_device(pt_scene* s, const HostBlas& hb, DevBlasPiece& out, Box& bounds, void* user){
+int pack_blas_on_device(pt_scene* s, const HostBlas& hb, int width, DevBlasPiece& out, Box& bounds, void* user){
     static const uint32_t gpu_min = []{ const char* e = getenv("PTB_GPU_BUILD_MIN"); return e ? (uint32_t)atoll(e) : 4096u; }();
     static const bool off = []{ const char* e = getenv("PTB_GPU_PACK"); return e && atoi(e) == 0; }();
     if(off || hb.n_tris < gpu_min || hb.n_tris < 8)return 1;
@@ -221,53 +302,26 @@ int pack_blas_on_device(pt_scene* s, const HostBlas& hb, DevBlasPiece& out, Box&
     if(root.count != 0)return 1;                 // a single leaf: nothing to collapse (cannot happen above gpu_min)
     bounds = root.box;
 
-    // collapse: breadth-first expand, then sizes, then preorder indices
     const auto t0 = std::chrono::steady_clock::now();
-    const uint32_t cap = n;                      // clusters <= inner binary nodes < items
-    DevMem d_work, d_tmp, d_last, d_cnt;
-    if(!d_work.alloc(sizeof(Work) * (size_t)cap, "cudaMalloc collapse work") || !d_tmp.alloc(sizeof(Bvh4Node) * (size_t)cap, "cudaMalloc clusters") ||
-       !d_last.alloc(4 * (size_t)n, "cudaMalloc leaf marks") || !d_cnt.alloc(4, "cudaMalloc counter"))return PT_ERR_CUDA;
-    if(!cuda_ok(cudaMemsetAsync(d_last.p, 0, 4 * (size_t)n, st), "leaf marks clear"))return PT_ERR_CUDA;
-    const Work w0 = { 0u, 0u, 0u, 0u };
-    if(!cuda_ok(cudaMemcpyAsync(d_work.p, &w0, sizeof w0, cudaMemcpyHostToDevice, st), "H2D root cluster"))return PT_ERR_CUDA;
-    std::vector<uint32_t> level_lo;              // level l = [level_lo[l], level_lo[l + 1])
-    level_lo.push_back(0);
-    uint32_t lo = 0, hi = 1;
-    while(hi > lo){
-        level_lo.push_back(hi);
-        if(!cuda_ok(cudaMemsetAsync(d_cnt.p, 0, 4, st), "counter clear"))return PT_ERR_CUDA;
-        k_expand<<<blocks(hi - lo), 256, 0, st>>>(d_nodes, d_work.as<Work>(), d_tmp.as<Bvh4Node>(), lo, hi, d_cnt.as<uint32_t>(), d_last.as<uint32_t>(), cap);
-        uint32_t next = 0;
-        if(!cuda_ok(cudaGetLastError(), "k_expand") || !cuda_ok(cudaMemcpyAsync(&next, d_cnt.p, 4, cudaMemcpyDeviceToHost, st), "D2H level size") ||
-           !cuda_ok(cudaStreamSynchronize(st), "collapse level"))return PT_ERR_CUDA;
-        if((uint64_t)hi + next > cap){ set_error("gpu collapse: more clusters than items"); return PT_ERR_CUDA; }
-        lo = hi; hi += next;
-    }
-    const uint32_t n_clusters = hi;
-    const int levels = (int)level_lo.size() - 1;
-    for(int l = levels - 1; l >= 0; l--){
-        const uint32_t a = level_lo[l], b = level_lo[l + 1];
-        k_count<<<blocks(b - a), 256, 0, st>>>(d_work.as<Work>(), d_tmp.as<Bvh4Node>(), a, b);
-    }
-    for(int l = 0; l < levels; l++){
-        const uint32_t a = level_lo[l], b = level_lo[l + 1];
-        k_assign<<<blocks(b - a), 256, 0, st>>>(d_work.as<Work>(), d_tmp.as<Bvh4Node>(), a, b);
-    }
-    DevMem d_out, d_tris;
-    if(!d_out.alloc(sizeof(Bvh4Node) * (size_t)n_clusters, "cudaMalloc BLAS clusters") || !d_tris.alloc(sizeof(Tri) * (size_t)n, "cudaMalloc BLAS triangles"))return PT_ERR_CUDA;
-    k_emit<<<blocks(n_clusters), 256, 0, st>>>(d_work.as<Work>(), d_tmp.as<Bvh4Node>(), d_out.as<Bvh4Node>(), n_clusters);
-    k_gather_tris<<<blocks(n), 256, 0, st>>>(T, (const uint32_t*)tree.order, d_last.as<uint32_t>(), n, d_tris.as<Tri>());
-    if(!cuda_ok(cudaGetLastError(), "collapse kernels") || !cuda_ok(cudaStreamSynchronize(st), "gpu pack"))return PT_ERR_CUDA;
+    uint32_t n_clusters = 0;
+    void* d_out_nodes = nullptr;
+    DevMem d_tris;
+    rc = width == 2 ? collapse_on_device<2>(d_nodes, n, T, (const uint32_t*)tree.order, st, n_clusters, d_out_nodes, d_tris)
+       : width == 4 ? collapse_on_device<4>(d_nodes, n, T, (const uint32_t*)tree.order, st, n_clusters, d_out_nodes, d_tris)
+                    : collapse_on_device<8>(d_nodes, n, T, (const uint32_t*)tree.order, st, n_clusters, d_out_nodes, d_tris);
+    if(rc != PT_OK)return rc;
     s->build_stats.flatten_s += std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
-    out.d_nodes = d_out.take(); out.d_tris = d_tris.take();
+    out.d_nodes = d_out_nodes; out.d_tris = d_tris.take();
     out.n_nodes = n_clusters; out.n_tris = n;
     return PT_OK;
 }
 
 // the piece's clusters into the scene-wide array, refs rebased (scene_host.cu)
-int place_blas_piece(const DevBlasPiece& p, void* d_n4, void* d_tris){
-    k_place_nodes4<<<blocks(p.n_nodes), 256>>>((const Bvh4Node*)p.d_nodes, (Bvh4Node*)d_n4 + p.node_base, p.n_nodes, p.node_base, p.tri_base);
-    if(!cuda_ok(cudaGetLastError(), "k_place_nodes4") ||
+int place_blas_piece(const DevBlasPiece& p, int width, void* d_nodes, void* d_tris){
+    if(width == 2)k_place_nodes<2><<<blocks(p.n_nodes), 256>>>((const Bvh2Node*)p.d_nodes, (Bvh2Node*)d_nodes + p.node_base, p.n_nodes, p.node_base, p.tri_base);
+    else if(width == 4)k_place_nodes<4><<<blocks(p.n_nodes), 256>>>((const Bvh4Node*)p.d_nodes, (Bvh4Node*)d_nodes + p.node_base, p.n_nodes, p.node_base, p.tri_base);
+    else k_place_nodes<8><<<blocks(p.n_nodes), 256>>>((const Bvh8Node*)p.d_nodes, (Bvh8Node*)d_nodes + p.node_base, p.n_nodes, p.node_base, p.tri_base);
+    if(!cuda_ok(cudaGetLastError(), "k_place_nodes") ||
        !cuda_ok(cudaMemcpy((Tri*)d_tris + p.tri_base, p.d_tris, sizeof(Tri) * (size_t)p.n_tris, cudaMemcpyDeviceToDevice), "D2D triangles"))return PT_ERR_CUDA;
     return PT_OK;
 }

@@ -159,7 +159,7 @@ int pt_unit_table(pt_scene* s, int table, void* dst, size_t cap_bytes, size_t* b
     const void* src = nullptr;
     size_t n = 0;
     switch(table){
-        case 0: src = b.n4; n = four ? s->total_nodes * sizeof(Bvh4Node) : 0; break;
+        case 0: src = four ? b.n4 : s->dev.width == 2 ? b.n2 : b.n8; n = s->total_nodes * (four ? sizeof(Bvh4Node) : s->dev.width == 2 ? sizeof(Bvh2Node) : sizeof(Bvh8Node)); break;
         case 1: src = b.tris; n = s->total_tris * sizeof(Tri); break;
         case 2: src = b.n4q; n = s->dev.fast ? s->total_nodes * sizeof(Bvh4QNode) : 0; break;
         case 3: src = b.tris64; n = s->dev.fast ? s->total_tris * sizeof(Tri64) : 0; break;

@@ -127,17 +127,17 @@ def test_threaded_flatten_gives_the_one_thread_arrays(width, n, threads, cluster
 
 
 @pytest.mark.gpu
-@pytest.mark.parametrize("layout", [0, 1])
-def test_blas_packed_on_the_device_gives_the_host_arrays(layout):
-    """PT_BUILDER_GPU packs every large BVH4 BLAS on the device (csrc/scene_pack_gpu.cu: boxes, binary build, collapse, triangle records,
+@pytest.mark.parametrize("width,layout", [(4, 0), (4, 1), (2, 0), (8, 0)])
+def test_blas_packed_on_the_device_gives_the_host_arrays(width, layout):
+    """PT_BUILDER_GPU packs every large BLAS (BVH2, BVH4 or BVH8) on the device (csrc/scene_pack_gpu.cu: boxes, binary build, collapse, triangle records,
     quantised clusters): the scene-wide tables must be, byte for byte, the ones the host path packs (pt_unit_table) -- multi-mesh BLAS, several
     BLASes of which one is small enough to stay on the host, instances, and a material with an alpha test among them."""
     from pathtracing_b200.scene import GpuScene
     cases = [synth.soup_scene(150000), synth.instanced_scene(5, 48), synth.c3_scene(subdiv=4, n_instances=9)[0], synth.c5_scene(grid=300, n_objects=6)[0],
              synth.alpha_scene()[0] if hasattr(synth, "alpha_scene") else synth.terrain_scene(200, 150)]
     for k, desc in enumerate(cases):
-        a = GpuScene(desc, 4, builder=capi.BUILDER_HOST, layout=layout)
-        b = GpuScene(desc, 4, builder=capi.BUILDER_GPU, layout=layout)
+        a = GpuScene(desc, width, builder=capi.BUILDER_HOST, layout=layout)
+        b = GpuScene(desc, width, builder=capi.BUILDER_GPU, layout=layout)
         st = b.build_stats()
         assert st["gpu_items"] > 0 or k == 4          # the last scene is all small BLASes: everything stays on the host
         for t in ((0, 1, 4) if layout == 0 else (0, 1, 2, 3, 4)) + (5, 6, 7, 8, 9, 10, 11):
