@@ -67,6 +67,8 @@ __device__ __forceinline__ void feed_grab(RayFeed& f, unsigned long long* cursor
     f.avail = left < kChunk ? (unsigned)left : kChunk;
 }
 
+// dynamic shared memory of a k_trace CTA: KS stack rows of 8 B per lane + the nine world-ray rows of 4 B per lane (trace.cuh)
+static constexpr size_t trace_smem_bytes(int ks){ return ks > 0 ? (size_t)ks * kTraceBlock * sizeof(uint2) + (size_t)kWorldRayRows * kTraceBlock * sizeof(float) : 0; }
 // COMPACT (with FEED, closest hit only): rays are 24 B {o, d} records, results 8 B {t, prim} (pt_trace_closest_compact)
 template <int WIDTH, bool ANY, bool STATS, int KS, class Alpha, bool FEED = false, bool COMPACT = false>
 __global__ void __launch_bounds__(kTraceBlock) k_trace(DevScene S, const float4* __restrict__ rays, size_t n,
@@ -86,7 +88,10 @@ __global__ void __launch_bounds__(kTraceBlock) k_trace(DevScene S, const float4*
     extern __shared__ uint2 smem_stack[];            // KS rows of kTraceBlock entries
     uint2 spill[kStack > KS ? kStack - KS : 1];
     TravStack<KS, KS ? kTraceBlock : 1> stack;
-    if constexpr(KS > 0)stack.sm = smem_stack + threadIdx.x;
+    if constexpr(KS > 0){
+        stack.sm = smem_stack + threadIdx.x;
+        stack.wr = reinterpret_cast<float*>(smem_stack + KS * kTraceBlock) + threadIdx.x;     // nine rows of kTraceBlock floats behind the stack rows
+    }
     stack.lm = spill;
     TravState s;
     s.flags = TF_DONE;
@@ -229,7 +234,7 @@ static int launch_dyn_ks(pt_scene* sc, const void* d_rays, const DynBatch& dyn, 
     static int cache[8] = { 0, 0, 0, 0, 0, 0, 0, 0 };
     cudaStream_t st = (cudaStream_t)stream;
     auto kernel = k_trace<WIDTH, ANY, false, KS, Alpha>;
-    const size_t smem = (size_t)KS * kTraceBlock * sizeof(uint2);
+    const size_t smem = trace_smem_bytes(KS);
     const unsigned grid = persistent_grid(kernel, sc->device, smem, cache[sc->device & 7]);
     kernel<<<grid, kTraceBlock, smem, st>>>(sc->dev, (const float4*)d_rays, 0, (float4*)d_hits, (uint32_t*)d_inst, (uint8_t*)d_occ,
                                             cursor, nullptr, refill_min(), alpha, StreamCtl(), dyn, overflow_counter(sc), acc);
@@ -242,7 +247,7 @@ template <int WIDTH, bool ANY, class Alpha>
 static int launch_dyn_count(pt_scene* sc, const void* d_rays, const DynBatch& dyn, void* d_hits, void* d_inst, void* d_occ, const ConnectAcc& acc, unsigned long long* cursor, void* stream, const Alpha& alpha){
     static int cache[8] = { 0, 0, 0, 0, 0, 0, 0, 0 };
     auto kernel = k_trace<WIDTH, ANY, true, 16, Alpha>;
-    const size_t smem = (size_t)16 * kTraceBlock * sizeof(uint2);
+    const size_t smem = trace_smem_bytes(16);
     const unsigned grid = persistent_grid(kernel, sc->device, smem, cache[sc->device & 7]);
     unsigned long long* stats = (unsigned long long*)sc->buf.stats + (ANY ? 24 : 16);
     kernel<<<grid, kTraceBlock, smem, (cudaStream_t)stream>>>(sc->dev, (const float4*)d_rays, 0, (float4*)d_hits, (uint32_t*)d_inst, (uint8_t*)d_occ,
@@ -285,7 +290,7 @@ static int launch_ks(pt_scene* sc, const void* d_rays, size_t n, void* d_hits, v
     static int cache[8] = { 0, 0, 0, 0, 0, 0, 0, 0 };   // per device ordinal (one process drives at most 8 GPUs)
     cudaStream_t st = (cudaStream_t)stream;
     auto kernel = k_trace<WIDTH, ANY, STATS, KS, Alpha>;
-    const size_t smem = (size_t)KS * kTraceBlock * sizeof(uint2);
+    const size_t smem = trace_smem_bytes(KS);
     unsigned grid = persistent_grid(kernel, sc->device, smem, cache[sc->device & 7]);
     const size_t need_ctas = (n + kTraceBlock - 1) / kTraceBlock;
     if(need_ctas < grid)grid = (unsigned)need_ctas;
@@ -327,7 +332,7 @@ static int launch_feed(pt_scene* sc, const void* d_rays, size_t n, void* d_hits,
     static int cache[8] = { 0, 0, 0, 0, 0, 0, 0, 0 };
     cudaStream_t st = (cudaStream_t)stream;
     auto kernel = k_trace<WIDTH, ANY, false, 16, NoAlpha, true, COMPACT>;
-    const size_t smem = (size_t)16 * kTraceBlock * sizeof(uint2);
+    const size_t smem = trace_smem_bytes(16);
     unsigned grid = persistent_grid(kernel, sc->device, smem, cache[sc->device & 7]);
     const size_t need_ctas = (n + kTraceBlock - 1) / kTraceBlock;
     if(need_ctas < grid)grid = (unsigned)need_ctas;
@@ -467,7 +472,7 @@ template <int WIDTH, class Alpha>
 static int launch_static(pt_scene* sc, StaticScratch* d, size_t n, bool want_inst, cudaStream_t st, const Alpha& alpha){
     static int cache[8] = { 0, 0, 0, 0, 0, 0, 0, 0 };
     auto kernel = k_trace<WIDTH, false, false, 16, Alpha>;
-    const size_t smem = (size_t)16 * kTraceBlock * sizeof(uint2);
+    const size_t smem = trace_smem_bytes(16);
     unsigned grid = persistent_grid(kernel, sc->device, smem, cache[sc->device & 7]);
     const size_t need_ctas = (n + kTraceBlock - 1) / kTraceBlock;
     if(need_ctas < grid)grid = (unsigned)need_ctas;

@@ -318,6 +318,7 @@ template <int KS, int STRIDE>
 struct TravStack {
     uint2* sm;      // &smem[threadIdx.x]
     uint2* lm;      // kStack - KS local entries
+    float* wr;      // this lane's column of the nine world-ray rows behind the stack rows (stack_save_world_ray)
     __device__ __forceinline__ void st(int i, uint2 v) const{ if(i < KS)sm[i * STRIDE] = v; else lm[i - KS] = v; }
     __device__ __forceinline__ uint2 ld(int i) const{ return i < KS ? sm[i * STRIDE] : lm[i - KS]; }
 };
@@ -404,6 +405,25 @@ __device__ __forceinline__ void stack_st_sm_if(const TravStack<KS, STRIDE>& k, i
 #endif
 }
 __device__ __forceinline__ void stack_st_sm_if(const LocalStack& k, int i, uint2 v, bool p){ if(p)k.lm[i] = v; }
+
+// The world-space ray of a lane that is inside a transformed instance.  Leaving the instance used to re-read the ray from global
+// memory and rebuild its three exact reciprocals (about 40 instructions, run for 4 of 32 lanes in most rounds of an instanced scene:
+// 13 % of the instructions of a C3 frame's closest-hit kernel, profiles/r02_trace.md); nine shared-memory words per lane hold it instead.
+// The restored values are the ones make_ray would compute again, bit for bit.  Stacks without shared memory keep the re-read.
+constexpr int kWorldRayRows = 9;
+template <int KS, int STRIDE>
+__device__ __forceinline__ void stack_save_world_ray(const TravStack<KS, STRIDE>& k, const RayCtx& r){
+    k.wr[0] = r.ox; k.wr[STRIDE] = r.oy; k.wr[2 * STRIDE] = r.oz; k.wr[3 * STRIDE] = r.dx; k.wr[4 * STRIDE] = r.dy; k.wr[5 * STRIDE] = r.dz;
+    k.wr[6 * STRIDE] = r.ix; k.wr[7 * STRIDE] = r.iy; k.wr[8 * STRIDE] = r.iz;
+}
+template <int KS, int STRIDE>
+__device__ __forceinline__ bool stack_load_world_ray(const TravStack<KS, STRIDE>& k, RayCtx& r){
+    r.ox = k.wr[0]; r.oy = k.wr[STRIDE]; r.oz = k.wr[2 * STRIDE]; r.dx = k.wr[3 * STRIDE]; r.dy = k.wr[4 * STRIDE]; r.dz = k.wr[5 * STRIDE];
+    r.ix = k.wr[6 * STRIDE]; r.iy = k.wr[7 * STRIDE]; r.iz = k.wr[8 * STRIDE];
+    return true;
+}
+__device__ __forceinline__ void stack_save_world_ray(const LocalStack&, const RayCtx&){}
+__device__ __forceinline__ bool stack_load_world_ray(const LocalStack&, RayCtx&){ return false; }
 
 // pop: rows below KS come straight from shared memory (no branch in the common case of a shallow stack)
 template <int KS, int STRIDE>
@@ -731,9 +751,11 @@ __device__ __forceinline__ void trav_step(TravState& s, const DevScene& S, const
         if(s.cur == REF_LEAVE){
             // end of TransformedPrimitive::Intersect (Primitive.cpp:54-63): t back to world space
             if(s.flags & TF_XF){
-                float4 a, b;
-                fetch_ray(rays, ray_idx, a, b);
-                make_ray(s.r, a.x, a.y, a.z, b.x, b.y, b.z);
+                if(!stack_load_world_ray(stack, s.r)){
+                    float4 a, b;
+                    fetch_ray(rays, ray_idx, a, b);
+                    make_ray(s.r, a.x, a.y, a.z, b.x, b.y, b.z);
+                }
                 s.octant = ray_octant(s.r);
                 float t = f_div(s.tmax, s.len);
                 if((Alpha::kWrap || STATS) && (s.flags & TF_ANIM2)){
@@ -788,6 +810,7 @@ __device__ __forceinline__ void trav_step(TravState& s, const DevScene& S, const
                 s.flags |= TF_IN_INST | TF_XF;
                 s.inst_rec = i; s.inst_id = d.meta.z;
                 s.wtmax = s.tmax; s.len = xf ? len_b : len_a;
+                stack_save_world_ray(stack, s.r);
                 s.r = r; s.tmax = tm;
                 s.octant = ray_octant(s.r);
                 s.cur = c.meta.x;
@@ -815,6 +838,7 @@ __device__ __forceinline__ void trav_step(TravState& s, const DevScene& S, const
             s.inst_rec = i; s.inst_id = d.meta.z;
             if(d.meta.y & INST_XF){
                 s.wtmax = s.tmax;
+                stack_save_world_ray(stack, s.r);
                 xf_ray(d, s.r, s.tmax, s.len);
                 s.octant = ray_octant(s.r);
                 s.flags |= TF_XF;
