@@ -121,6 +121,7 @@ constexpr uint32_t INST_QUAD = 8u;       // GeometricPrimitive(QuadShape)
 constexpr uint32_t INST_ANIM = 16u;      // AnimatedPrimitive (Primitive.cpp:77-96): inv[0..2] direction, inv[3..4] timeBounds; the child follows
 constexpr uint32_t INST_WRAP = 32u;      // TransformedPrimitive over an analytic shape: inv[] = inverse transform; the shape record follows
 constexpr uint32_t INST_ALPHA = 64u;     // shape record: its material can reject a hit (Material::Alpha, Primitive.cpp:6-26); `root` = material id
+constexpr uint32_t INST_WBOX = 128u;     // BVH4 / BVH8, BLAS instance: blo / bhi hold the instance's WORLD box (slightly enlarged), tested before the ray is transformed
 constexpr uint32_t INST_EXTRA_SHIFT = 8u;
 constexpr uint32_t INST_EXTRA_MASK = 3u;
 

@@ -419,6 +419,22 @@ int pack_traversal(pt_scene* s, int width, PackedTraversal& P, BvhBuilder builde
             I.blas = (uint32_t)hi.blas;
             for(int a = 0; a < 3; a++)I.blo[a] = hb.bounds.lo[a];
             I.bhi0 = hb.bounds.hi[0]; I.bhi12[0] = hb.bounds.hi[1]; I.bhi12[1] = hb.bounds.hi[2];
+            if(width != 2 && !hi.animated){
+                // BVH4 / BVH8: the record carries the instance's WORLD box instead (the BLAS root box is only read by the BVH2 kernels).  A TLAS
+                // leaf holds up to two instances and its cluster box is their union: testing the ray against each one's own box before paying for
+                // the transform (about 250 instructions with the reference's arithmetic) skips the one it misses.  Enlarged by 1e-4 of its extent
+                // (+ 1e-6 of its magnitude) per side, so that a hit found in object space is never lost to the rounding of this test: an instance
+                // is skipped only when the ray cannot hit anything in it, so the hits stay the reference's bit for bit (ties included).
+                const Box& wb = iboxes[id];
+                float lo[3], hh[3];
+                for(int a = 0; a < 3; a++){
+                    const float m = 1e-4f * (wb.hi[a] - wb.lo[a]) + 1e-6f * std::fmax(std::fabs(wb.lo[a]), std::fabs(wb.hi[a])) + 1e-30f;
+                    lo[a] = wb.lo[a] - m; hh[a] = wb.hi[a] + m;
+                }
+                for(int a = 0; a < 3; a++)I.blo[a] = lo[a];
+                I.bhi0 = hh[0]; I.bhi12[0] = hh[1]; I.bhi12[1] = hh[2];
+                I.flags |= INST_WBOX;
+            }
         }
         insts.push_back(I);
         const uint32_t extra = (uint32_t)insts.size() - head - 1;

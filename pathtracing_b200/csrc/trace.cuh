@@ -832,6 +832,14 @@ __device__ __forceinline__ void trav_step(TravState& s, const DevScene& S, const
                 s.cur = (d.meta.y & INST_LAST) ? REF_EMPTY : (REF_LEAF | nxt);
                 return;
             }
+            if(WIDTH != 2 && (d.meta.y & INST_WBOX)){
+                // the instance's own world box first (pt_types.h INST_WBOX); a miss costs one slab test instead of the transform
+                const float wlo[3] = { d.b0.x, d.b0.y, d.b0.z }, whi[3] = { d.b0.w, d.b1.x, d.b1.y };
+                if(!box_hit2(s.r, wlo, whi, s.tmax)){
+                    s.cur = (d.meta.y & INST_LAST) ? REF_EMPTY : (REF_LEAF | nxt);
+                    return;
+                }
+            }
             if(!(d.meta.y & INST_LAST))trav_push(stack, s.sp, s.flags, REF_LEAF | nxt, -CUDART_INF_F);
             trav_push(stack, s.sp, s.flags, REF_LEAVE, -CUDART_INF_F);
             s.flags |= TF_IN_INST;
