@@ -19,6 +19,7 @@ PT_HDI float alpha_uniform(uint64_t salt, uint64_t ray, uint32_t prim, uint32_t 
 
 struct AlphaTex {
     static constexpr bool kWrap = true;      // the general traversal variant (trace.cuh NoAlpha)
+    static constexpr bool kSingle = false;
     ShadeScene S;
     uint64_t salt;
     // Material::Alpha(uv) (Material.hpp:336-342, 572-578) through AlphaTester (:181-198)

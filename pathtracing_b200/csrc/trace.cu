@@ -70,8 +70,16 @@ __device__ __forceinline__ void feed_grab(RayFeed& f, unsigned long long* cursor
 // dynamic shared memory of a k_trace CTA: KS stack rows of 8 B per lane + the nine world-ray rows of 4 B per lane (trace.cuh)
 static constexpr size_t trace_smem_bytes(int ks){ return ks > 0 ? (size_t)ks * kTraceBlock * sizeof(uint2) + (size_t)kWorldRayRows * kTraceBlock * sizeof(float) : 0; }
 // COMPACT (with FEED, closest hit only): rays are 24 B {o, d} records, results 8 B {t, prim} (pt_trace_closest_compact)
+// resident CTAs the register allocation has to leave room for: the plain fast-layout kernels ran at 56 registers (9 CTAs of 128 threads per SM)
+// until the instance world-box test took them to 64 (8 CTAs: C2 1631 -> 1516 Mrays/s); everything else takes what it needs
+#ifndef PTB_SINGLE_CTAS
+#define PTB_SINGLE_CTAS 9       // 10 (48 registers) compiles without spills and runs at 1000 instead of 1654 Mrays/s
+#endif
+template <int WIDTH, bool STATS, class Alpha>
+constexpr int trace_min_ctas(){ return (WIDTH == kWidthFast4 && !STATS && !Alpha::kWrap) ? (Alpha::kSingle ? PTB_SINGLE_CTAS : 9) : 1; }
+
 template <int WIDTH, bool ANY, bool STATS, int KS, class Alpha, bool FEED = false, bool COMPACT = false>
-__global__ void __launch_bounds__(kTraceBlock) k_trace(DevScene S, const float4* __restrict__ rays, size_t n,
+__global__ void __launch_bounds__(kTraceBlock, trace_min_ctas<WIDTH, STATS, Alpha>()) k_trace(DevScene S, const float4* __restrict__ rays, size_t n,
                                                        float4* __restrict__ hits, uint32_t* __restrict__ inst, uint8_t* __restrict__ occ,
                                                        unsigned long long* __restrict__ cursor, unsigned long long* __restrict__ stats,
                                                        unsigned refill_min, const Alpha alpha, const StreamCtl ctl, const DynBatch dyn,
@@ -268,6 +276,7 @@ static int launch_dyn(pt_scene* sc, const void* d_rays, const DynBatch& dyn, voi
         const AlphaTex at = { sc->shade, sc->alpha_salt += 0x9E3779B97F4A7C15ull };
         return launch_dyn_ks<WIDTH, ANY, 16>(sc, d_rays, dyn, d_hits, d_inst, d_occ, acc, cursor, stream, at);
     }
+    if(sc->dev.single_root != REF_EMPTY)return launch_dyn_ks<WIDTH, ANY, 16>(sc, d_rays, dyn, d_hits, d_inst, d_occ, acc, cursor, stream, NoAlphaSingle());
     return launch_dyn_ks<WIDTH, ANY, 16>(sc, d_rays, dyn, d_hits, d_inst, d_occ, acc, cursor, stream, NoAlpha());
 }
 
@@ -315,6 +324,7 @@ static int launch(pt_scene* sc, const void* d_rays, size_t n, void* d_hits, void
         return launch_ks<WIDTH, ANY, STATS, 0>(sc, d_rays, n, d_hits, d_inst, d_occ, d_stats, stream, at);
     }
     const NoAlpha na;
+    if(ks >= 16 && sc->dev.single_root != REF_EMPTY)return launch_ks<WIDTH, ANY, STATS, 16>(sc, d_rays, n, d_hits, d_inst, d_occ, d_stats, stream, NoAlphaSingle());
     if constexpr(WIDTH == 8 || WIDTH == kWidthFast4){
         if(ks >= 16)return launch_ks<WIDTH, ANY, STATS, 16>(sc, d_rays, n, d_hits, d_inst, d_occ, d_stats, stream, na);
         return launch_ks<WIDTH, ANY, STATS, 0>(sc, d_rays, n, d_hits, d_inst, d_occ, d_stats, stream, na);
@@ -327,11 +337,11 @@ static int launch(pt_scene* sc, const void* d_rays, size_t n, void* d_hits, void
 }
 
 // One launch over a ray buffer that is still being filled (capi.cu trace_streamed): plain scenes only
-template <int WIDTH, bool ANY, bool COMPACT = false>
-static int launch_feed(pt_scene* sc, const void* d_rays, size_t n, void* d_hits, void* d_inst, void* d_occ, const StreamCtl& ctl, void* stream){
+template <int WIDTH, bool ANY, bool COMPACT, class Alpha>
+static int launch_feed_as(pt_scene* sc, const void* d_rays, size_t n, void* d_hits, void* d_inst, void* d_occ, const StreamCtl& ctl, void* stream){
     static int cache[8] = { 0, 0, 0, 0, 0, 0, 0, 0 };
     cudaStream_t st = (cudaStream_t)stream;
-    auto kernel = k_trace<WIDTH, ANY, false, 16, NoAlpha, true, COMPACT>;
+    auto kernel = k_trace<WIDTH, ANY, false, 16, Alpha, true, COMPACT>;
     const size_t smem = trace_smem_bytes(16);
     unsigned grid = persistent_grid(kernel, sc->device, smem, cache[sc->device & 7]);
     const size_t need_ctas = (n + kTraceBlock - 1) / kTraceBlock;
@@ -339,8 +349,13 @@ static int launch_feed(pt_scene* sc, const void* d_rays, size_t n, void* d_hits,
     unsigned long long* cursor = (unsigned long long*)sc->buf.cursors + (sc->cursor_next++ % kCursorRing);
     if(!cuda_ok(cudaMemsetAsync(cursor, 0, sizeof(unsigned long long), st), "cursor reset"))return PT_ERR_CUDA;
     kernel<<<grid, kTraceBlock, smem, st>>>(sc->dev, (const float4*)d_rays, n, (float4*)d_hits, (uint32_t*)d_inst, (uint8_t*)d_occ,
-                                            cursor, nullptr, refill_min(), NoAlpha(), ctl, DynBatch(), overflow_counter(sc), ConnectAcc());
+                                            cursor, nullptr, refill_min(), Alpha(), ctl, DynBatch(), overflow_counter(sc), ConnectAcc());
     return check_launch("k_trace (streamed)");
+}
+template <int WIDTH, bool ANY, bool COMPACT = false>
+static int launch_feed(pt_scene* sc, const void* d_rays, size_t n, void* d_hits, void* d_inst, void* d_occ, const StreamCtl& ctl, void* stream){
+    if(sc->dev.single_root != REF_EMPTY)return launch_feed_as<WIDTH, ANY, COMPACT, NoAlphaSingle>(sc, d_rays, n, d_hits, d_inst, d_occ, ctl, stream);
+    return launch_feed_as<WIDTH, ANY, COMPACT, NoAlpha>(sc, d_rays, n, d_hits, d_inst, d_occ, ctl, stream);
 }
 
 // Can the host enqueue work while a kernel runs?  (Not under a profiler that serialises launches, not with

@@ -181,13 +181,18 @@ __device__ __forceinline__ bool tri_any(const RayCtx& r, const TriData& T, float
 // (6 instead of 8 CTAs per SM), and the shape branch alone costs the BVH2 kernel 7 % (63 registers instead of 55,
 // 940 instead of 1008 Mrays/s on the C2 soup, scratch/bvh2_bisect.py).  A scene that holds a shape or a wrapper
 // runs the general (AlphaTex) variant.
+// kSingle: the scene is ONE untransformed BLAS (DevScene::single_root: traversal starts inside it and never meets a TLAS leaf or an
+// instance exit), so that code is not compiled in -- the C2 case; the instance code costs the plain kernel registers and schedule
+// even when no lane ever runs it (1631 -> 1573 Mrays/s when the world-box test joined it, profiles/r02_trace.md).
 struct NoAlpha {
     static constexpr bool kWrap = false;
+    static constexpr bool kSingle = false;
     __device__ __forceinline__ bool operator()(uint32_t, uint32_t, uint32_t, float, float, size_t) const{ return true; }
     __device__ __forceinline__ bool shape(uint32_t, bool, float, float, float, uint32_t, size_t) const{ return true; }
 };
 
 struct NoAlphaWrap : NoAlpha { static constexpr bool kWrap = true; };   // whole-ray walks: host emulation, tiny scenes
+struct NoAlphaSingle : NoAlpha { static constexpr bool kSingle = true; };
 
 struct InstData { float4 m0, m1, m2; uint4 meta; float4 b0; float4 b1; };
 
@@ -748,7 +753,7 @@ __device__ __forceinline__ void trav_step(TravState& s, const DevScene& S, const
     }
     // -- leaf items --
     if(do_leaf && (s.cur & REF_LEAF) && s.cur != REF_EMPTY){
-        if(s.cur == REF_LEAVE){
+        if(!Alpha::kSingle && s.cur == REF_LEAVE){
             // end of TransformedPrimitive::Intersect (Primitive.cpp:54-63): t back to world space
             if(s.flags & TF_XF){
                 if(!stack_load_world_ray(stack, s.r)){
@@ -767,7 +772,7 @@ __device__ __forceinline__ void trav_step(TravState& s, const DevScene& S, const
             }
             s.flags &= ~(TF_IN_INST | TF_XF | TF_FOUND_LOCAL | TF_ANIM2);
             s.cur = REF_EMPTY;
-        } else if(!(s.flags & TF_IN_INST)){
+        } else if(!Alpha::kSingle && !(s.flags & TF_IN_INST)){
             // TLAS leaf item: BVHBase::intersectPrimitives over shared_ptr<Primitive> (BVH.hpp:107-135),
             // each either the BLAS itself or a TransformedPrimitive (Primitive.cpp:41-66)
             const uint32_t i = s.cur & ~REF_LEAF;
