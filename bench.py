@@ -545,7 +545,8 @@ def run_ours(a):
     inst_per_ray = st["instances"] / n
     b_ray = 32 + 16 + nodes_per_ray * s_node + tris_per_ray * s_tri + inst_per_ray * 96
     achieved = n * b_ray / (ms * 1e-3) / 1e9
-    kernel = f"k_trace<{'44' if fast else a.bvh},false,false,16,NoAlpha>"
+    # the soup and the surface mesh are ONE untransformed BLAS: the kernel variant without instance code (trace.cuh NoAlphaSingle)
+    kernel = f"k_trace<{'44' if fast else a.bvh},false,false,16,NoAlphaSingle>"
     # what ncu measured for this kernel on this workload (dram__bytes per ray, L1 wavefront and issue utilisation): read from
     # the tracked summary of the capture, never typed in here; absent for workloads that were not captured
     prof = (tracked_profile("r02_kernels.json") or {}).get(f"{kernel}|{a.mesh}|{a.tris}")
