@@ -136,8 +136,17 @@ static int trace_streamed(pt_scene* s, const void* rays, size_t n, bool any, Cop
     const unsigned shift = 18;
     const size_t ng = (n + ((size_t)1 << shift) - 1) >> shift;
     const size_t aux_bytes = 64 + 1024 * ng;       // per granule 32 sub-counters, 32 B apart
-    const size_t chunk = (size_t)1 << 20;
-    const size_t n_chunks = (n + chunk - 1) / chunk + 2;
+    // Chunk sizes of the H2D stream (measured on the C2 workload, scratch/r02_stream_sweep.py).  The 32 B form is bound by the
+    // link: 1 Mi-ray copies (every copy costs the stream about 18 us, smaller ones lose more than they smooth), and the last
+    // 2 Mi rays in 256 Ki-ray pieces so that little work is left when the last piece lands (12.01 -> 11.85 ms).  The 24 B form is
+    // bound by the kernel: 256 Ki-ray copies feed it more evenly (11.27 -> 10.94 ms).  PTB_STREAM_CHUNK_LOG2 / PTB_STREAM_TAPER_LOG2 override both.
+    static const int chunk_env = []{ const char* e = getenv("PTB_STREAM_CHUNK_LOG2"); const int v = e ? atoi(e) : 0; return v == 0 ? 0 : v < 16 ? 16 : v > 24 ? 24 : v; }();
+    static const unsigned taper_log2 = []{ const char* e = getenv("PTB_STREAM_TAPER_LOG2"); const int v = e ? atoi(e) : 21; return (unsigned)(v < 0 ? 0 : v > 30 ? 30 : v); }();
+    const unsigned chunk_log2 = chunk_env ? (unsigned)chunk_env : compact ? 18u : 20u;
+    const size_t chunk = (size_t)1 << chunk_log2;
+    const size_t small_chunk = std::min(chunk, (size_t)1 << 18);
+    const size_t taper_from = taper_log2 >= 18 && n > ((size_t)1 << taper_log2) ? n - ((size_t)1 << taper_log2) : n;
+    const size_t n_chunks = (n + chunk - 1) / chunk + (n - taper_from) / small_chunk + 4;
     if(aux_bytes > b.stream_aux_bytes){
         if(b.stream_aux){ cudaFree(b.stream_aux); b.stream_aux = nullptr; b.stream_aux_bytes = 0; }
         if(!cuda_ok(cudaMalloc(&b.stream_aux, aux_bytes), "cudaMalloc stream ctl"))return PT_ERR_CUDA;
@@ -175,6 +184,8 @@ static int trace_streamed(pt_scene* s, const void* rays, size_t n, bool any, Cop
     bool enqueue_failed = false;
     for(size_t off = 0; off < n && !enqueue_failed; k++){
         size_t m = k == 0 ? chunk / 16 : k == 1 ? chunk / 4 : chunk;
+        if(off >= taper_from)m = small_chunk;
+        else if(m > taper_from - off)m = taper_from - off;
         if(m > n - off)m = n - off;
         h_wm[k] = (unsigned long long)(off + m);
         if(!cuda_ok(cudaMemcpyAsync(d_rays + off * ray_bytes, (const char*)rays + off * ray_bytes, m * ray_bytes, cudaMemcpyHostToDevice, in), "H2D rays") ||
