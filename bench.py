@@ -276,7 +276,8 @@ def bench_render(a, key, torch, dist, world, rank, local, peak, peak_src):
     total = W * H * spp
     heavy = total > (1 << 25)
     very_heavy = total > (1 << 30)
-    steps = 1 if very_heavy else 3 if heavy else max(2, min(a.steps, 5))
+    # a light frame (C1: 5 ms) is timed 20 times: one host hiccup of 10 ms in five frames moved the mean by a third (r02_bench_v10.json)
+    steps = 1 if very_heavy else 3 if heavy else max(2, min(2 * a.steps, 20))
     # warm-up: whole frames, except for the very heavy config (C5: 2 G samples), which warms up on a 64-spp frame of the same
     # scene -- enough samples per rank to size the wavefront arena as the full frame does (64 Mi slots), so that the timed
     # frame does not pay a 16 GB cudaMalloc
