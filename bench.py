@@ -297,9 +297,11 @@ def bench_render(a, key, torch, dist, world, rank, local, peak, peak_src):
     # a light frame (C1: 5 ms) keeps warming up until the host side has settled: on some boxes the first frames behind the ray-cast part of this
     # script took 15-40 ms each against 5.3 ms on the device (r02_bench_v11.json frame_ms_rank0).  Up to 60 more frames, until three in a row are
     # within 10 % of the fastest one seen; every rank runs the same number (the decision is rank 0's, broadcast), a frame is a collective.
+    # The heavy frames (C3, C4: 0.2-0.6 s) get up to three more, until two in a row are within 5 % (r02_bench_n4_v2.json: C3's first timed frame 83 ms, then 69).
     extra_warm = 0
-    while not heavy and extra_warm < 60:
-        settled = len(warm_ms) >= 3 and max(warm_ms[-3:]) <= 1.1 * min(warm_ms)
+    max_extra, need, tol = (60, 3, 1.1) if not heavy else (3, 2, 1.05) if not very_heavy else (0, 0, 0.0)
+    while extra_warm < max_extra:
+        settled = len(warm_ms) >= need and max(warm_ms[-need:]) <= tol * min(warm_ms)
         if world > 1:
             flag = torch.tensor([1 if settled else 0], device="cuda", dtype=torch.int32)
             dist.broadcast(flag, 0)
