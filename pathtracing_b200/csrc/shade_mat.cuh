@@ -29,10 +29,12 @@ PT_HDN void mat_fetch(const ShadeScene& S, const SurfInt& si, MatCtx& m){
     if(M.kind == PT_MAT_CONDUCTOR){ m.color = ld3(M.albedo); return; }
     m.color = M.tex >= 0 ? tex_eval(S, M.tex, si.u, si.v, si.ns) : v3(1.0f);
     if(M.kind == PT_MAT_THIN_DIELECTRIC)return;
-    const float g = M.rough >= 0 ? tex_eval(S, M.rough, si.u, si.v, si.ns).y : (M.kind == PT_MAT_DIFFUSE ? 1.0f : 0.0f);
+    // roughness in .g, metallic in .b (Material.hpp:272-278): one lookup when both name the same texture (the usual packing), the value is the same
+    const V3 orm = M.rough >= 0 ? tex_eval(S, M.rough, si.u, si.v, si.ns) : v3(0.0f);
+    const float g = M.rough >= 0 ? orm.y : (M.kind == PT_MAT_DIFFUSE ? 1.0f : 0.0f);
     if(M.kind == PT_MAT_DIFFUSE){
         m.rough = fmaxf(g, 0.0001f);
-        m.metallic = M.metal >= 0 ? tex_eval(S, M.metal, si.u, si.v, si.ns).z : 0.0f;
+        m.metallic = M.metal >= 0 ? (M.metal == M.rough ? orm.z : tex_eval(S, M.metal, si.u, si.v, si.ns).z) : 0.0f;
     } else m.rough = g;
 }
 
